@@ -1,0 +1,112 @@
+"""ctypes binding of libvtn.so (include/vtn.h).  Plumbing only: every call goes to the CUDA library;
+there is no Python or CPU implementation behind these wrappers and loading fails loudly if the
+library is missing."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libvtn.so")
+
+c_u8p = C.POINTER(C.c_uint8)
+c_u16p = C.POINTER(C.c_uint16)
+c_u32p = C.POINTER(C.c_uint32)
+c_i32p = C.POINTER(C.c_int32)
+c_u64p = C.POINTER(C.c_uint64)
+c_i64p = C.POINTER(C.c_int64)
+
+
+class VtnBatch(C.Structure):
+    _fields_ = [
+        ("n_rec", C.c_uint32),
+        ("n_allele", C.c_uint32),
+        ("n_bytes", C.c_uint64),
+        ("pos1", c_i32p),
+        ("rid", c_i32p),
+        ("allele_beg", c_u32p),
+        ("allele_off", c_u32p),
+        ("bytes", c_u8p),
+    ]
+
+
+class VtnNormCounters(C.Structure):
+    _fields_ = [("bi", C.c_uint32 * 5), ("multi", C.c_uint32 * 5), ("no_variants", C.c_uint32), ("no_refs", C.c_uint32)]
+
+
+class VtnNormResult(C.Structure):
+    _fields_ = [
+        ("status", c_u8p),
+        ("vtype", c_u8p),
+        ("cap_changed", C.c_uint32),
+        ("cap_changed_bytes", C.c_uint64),
+        ("n_changed", C.c_uint32),
+        ("n_changed_bytes", C.c_uint64),
+        ("chg_rec", c_u32p),
+        ("chg_pos1", c_i32p),
+        ("chg_lt", c_u32p),
+        ("chg_le", c_u32p),
+        ("chg_rt", c_u32p),
+        ("chg_off", c_u64p),
+        ("chg_bytes", c_u8p),
+        ("counters", VtnNormCounters),
+    ]
+
+
+class VtnDecompCounters(C.Structure):
+    _fields_ = [
+        ("no_variants", C.c_uint32),
+        ("no_biallelic", C.c_uint32),
+        ("no_multiallelic", C.c_uint32),
+        ("no_additional_biallelic", C.c_uint32),
+    ]
+
+
+# name -> (restype, argtypes); also the list the CPU test checks against include/vtn.h
+SIGNATURES = {
+    "vtn_ctx_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
+    "vtn_ctx_destroy": (C.c_int, [C.c_void_p]),
+    "vtn_last_error": (C.c_char_p, [C.c_void_p]),
+    "vtn_sync": (C.c_int, [C.c_void_p]),
+    "vtn_host_alloc": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]),
+    "vtn_host_free": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "vtn_ref_load_fasta": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "vtn_ref_load_memory": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), c_i64p, C.POINTER(C.c_void_p)]),
+    "vtn_ref_n_contig": (C.c_int, [C.c_void_p]),
+    "vtn_ref_contig_id": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "vtn_ref_contig_len": (C.c_int64, [C.c_void_p, C.c_int]),
+    "vtn_ref_contig_name": (C.c_char_p, [C.c_void_p, C.c_int]),
+    "vtn_ref_resident_bytes": (C.c_int64, [C.c_void_p]),
+    "vtn_ref_fetch": (C.c_int64, [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_int, c_u8p, C.c_int64]),
+    "vtn_normalize": (C.c_int, [C.c_void_p, C.POINTER(VtnBatch), C.POINTER(VtnNormResult)]),
+    "vtn_dbatch_create": (C.c_int, [C.c_void_p, C.POINTER(VtnBatch), C.POINTER(C.c_void_p)]),
+    "vtn_dbatch_destroy": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "vtn_normalize_resident": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "vtn_dbatch_fetch_result": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VtnNormResult)]),
+    "vtn_decompose_out_bound": (C.c_uint64, [C.POINTER(VtnBatch)]),
+    "vtn_decompose": (C.c_int, [C.c_void_p, C.POINTER(VtnBatch), c_u32p, c_u16p, c_u64p, C.POINTER(VtnDecompCounters)]),
+    "vtn_decompose_normalize": (
+        C.c_int,
+        [C.c_void_p, C.POINTER(VtnBatch), c_u32p, c_u16p, c_u64p, C.POINTER(VtnDecompCounters), C.POINTER(VtnNormResult)],
+    ),
+    "vtn_decompose_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
+    "vtn_dbatch_fetch_decompose": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_u16p, c_u64p, C.POINTER(VtnDecompCounters)]),
+    "vtn_timer_start": (C.c_int, [C.c_void_p]),
+    "vtn_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "vtn_launch_count": (C.c_uint64, [C.c_void_p]),
+}
+
+_lib = None
+
+
+def load():
+    """dlopen libvtn.so (built in-tree by vt_b200/csrc/Makefile).  Raises if it is missing."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("libvtn.so not built (%s): run `python -c 'import __graft_entry__ as g; g.build()'`" % LIB_PATH)
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib

@@ -1,0 +1,227 @@
+"""Thin numpy-facing wrappers over the C ABI (include/vtn.h) for tests, bench and tooling.
+All arithmetic happens in libvtn.so on the GPU; these classes only hold buffers."""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib as L
+
+
+class VtnError(RuntimeError):
+    pass
+
+
+def _p(a, ty):
+    return a.ctypes.data_as(ty)
+
+
+class Batch:
+    """SoA record batch (see vtn_batch in include/vtn.h)."""
+
+    def __init__(self, pos1, rid, allele_beg, allele_off, data):
+        self.pos1 = np.ascontiguousarray(pos1, dtype=np.int32)
+        self.rid = np.ascontiguousarray(rid, dtype=np.int32)
+        self.allele_beg = np.ascontiguousarray(allele_beg, dtype=np.uint32)
+        self.allele_off = np.ascontiguousarray(allele_off, dtype=np.uint32)
+        self.data = np.ascontiguousarray(data, dtype=np.uint8)
+        self.n_rec = int(self.pos1.shape[0])
+        assert self.rid.shape[0] == self.n_rec and self.allele_beg.shape[0] == self.n_rec + 1
+        self.n_allele = int(self.allele_beg[-1]) if self.n_rec else 0
+        assert self.allele_off.shape[0] == self.n_allele + 1
+        self.n_bytes = int(self.allele_off[-1]) if self.n_allele else 0
+
+    @staticmethod
+    def from_records(records):
+        """records: iterable of (rid, pos1, [allele bytes/str, ...])."""
+        pos1, rid, abeg, aoff, chunks = [], [], [0], [0], []
+        for (c, p, alleles) in records:
+            rid.append(c)
+            pos1.append(p)
+            for a in alleles:
+                b = a.encode() if isinstance(a, str) else bytes(a)
+                chunks.append(b)
+                aoff.append(aoff[-1] + len(b))
+            abeg.append(abeg[-1] + len(alleles))
+        data = np.frombuffer(b"".join(chunks), dtype=np.uint8) if chunks else np.zeros(0, np.uint8)
+        return Batch(np.array(pos1, np.int32), np.array(rid, np.int32), np.array(abeg, np.uint32), np.array(aoff, np.uint32), data)
+
+    def alleles(self, r):
+        b, e = int(self.allele_beg[r]), int(self.allele_beg[r + 1])
+        return [bytes(self.data[int(self.allele_off[s]):int(self.allele_off[s + 1])]) for s in range(b, e)]
+
+    def as_c(self):
+        data = self.data if self.data.size else np.zeros(1, np.uint8)
+        self._keep = data
+        return L.VtnBatch(
+            self.n_rec, self.n_allele, self.n_bytes, _p(self.pos1, L.c_i32p), _p(self.rid, L.c_i32p),
+            _p(self.allele_beg, L.c_u32p), _p(self.allele_off, L.c_u32p), _p(data, L.c_u8p))
+
+
+class NormResult:
+    """Host arrays for vtn_norm_result, sized for the worst case of a batch."""
+
+    def __init__(self, n_rec, n_bytes):
+        self.status = np.zeros(max(n_rec, 1), np.uint8)
+        self.vtype = np.zeros(max(n_rec, 1), np.uint8)
+        self.chg_rec = np.zeros(max(n_rec, 1), np.uint32)
+        self.chg_pos1 = np.zeros(max(n_rec, 1), np.int32)
+        self.chg_lt = np.zeros(max(n_rec, 1), np.uint32)
+        self.chg_le = np.zeros(max(n_rec, 1), np.uint32)
+        self.chg_rt = np.zeros(max(n_rec, 1), np.uint32)
+        self.chg_off = np.zeros(n_rec + 1, np.uint64)
+        self.chg_bytes = np.zeros(max(n_bytes, 1), np.uint8)
+        self.c = L.VtnNormResult()
+        self.c.status = _p(self.status, L.c_u8p)
+        self.c.vtype = _p(self.vtype, L.c_u8p)
+        self.c.cap_changed = n_rec
+        self.c.cap_changed_bytes = n_bytes
+        self.c.chg_rec = _p(self.chg_rec, L.c_u32p)
+        self.c.chg_pos1 = _p(self.chg_pos1, L.c_i32p)
+        self.c.chg_lt = _p(self.chg_lt, L.c_u32p)
+        self.c.chg_le = _p(self.chg_le, L.c_u32p)
+        self.c.chg_rt = _p(self.chg_rt, L.c_u32p)
+        self.c.chg_off = _p(self.chg_off, L.c_u64p)
+        self.c.chg_bytes = _p(self.chg_bytes, L.c_u8p)
+        self.n_rec = n_rec
+
+    @property
+    def n_changed(self):
+        return int(self.c.n_changed)
+
+    @property
+    def n_changed_bytes(self):
+        return int(self.c.n_changed_bytes)
+
+    @property
+    def counters(self):
+        """12 counters in normalize.cpp:65-78 order: bi lt rt lt_rt rt_la la | multi ... | no_variants no_refs"""
+        k = self.c.counters
+        return list(k.bi) + list(k.multi) + [k.no_variants, k.no_refs]
+
+    def changed_alleles(self, k, old_lens):
+        """new alleles of compacted entry k given the record's old allele lengths"""
+        o = int(self.chg_off[k])
+        d = int(self.chg_le[k]) - int(self.chg_rt[k]) - int(self.chg_lt[k])
+        out = []
+        for l in old_lens:
+            nl = l + d
+            out.append(bytes(self.chg_bytes[o:o + nl]))
+            o += nl
+        assert o == int(self.chg_off[k + 1])
+        return out
+
+
+class Context:
+    """vtn_ctx: one GPU, its stream pair and the resident reference."""
+
+    def __init__(self, device=0):
+        self.lib = L.load()
+        h = C.c_void_p()
+        rc = self.lib.vtn_ctx_create(C.byref(h), device)
+        if rc:
+            raise VtnError("vtn_ctx_create: %s" % self.lib.vtn_last_error(None).decode())
+        self.h = h
+
+    def close(self):
+        if self.h:
+            self.lib.vtn_ctx_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _chk(self, rc, what):
+        if rc < 0:
+            raise VtnError("%s failed (%d): %s" % (what, rc, self.lib.vtn_last_error(self.h).decode()))
+        return rc
+
+    # ---- reference ----
+    def load_fasta(self, path):
+        self._chk(self.lib.vtn_ref_load_fasta(self.h, path.encode()), "vtn_ref_load_fasta")
+
+    def load_reference(self, names, seqs):
+        """seqs: list of bytes / uint8 arrays with the raw FASTA bases of each contig"""
+        arrs = [np.frombuffer(s, dtype=np.uint8) if isinstance(s, (bytes, bytearray)) else np.ascontiguousarray(s, np.uint8) for s in seqs]
+        n = len(arrs)
+        cn = (C.c_char_p * max(n, 1))(*[x.encode() for x in names])
+        ln = np.array([a.shape[0] for a in arrs], np.int64)
+        ptr = (C.c_void_p * max(n, 1))(*[a.ctypes.data if a.size else None for a in arrs])
+        self._chk(self.lib.vtn_ref_load_memory(self.h, n, cn, _p(ln, L.c_i64p), ptr), "vtn_ref_load_memory")
+
+    def contig_id(self, name):
+        return self.lib.vtn_ref_contig_id(self.h, name.encode())
+
+    def fetch(self, rid, beg0, end0, upper=False):
+        cap = max(end0 - beg0 + 1, 1)
+        out = np.zeros(cap, np.uint8)
+        n = self._chk(self.lib.vtn_ref_fetch(self.h, rid, beg0, end0, 1 if upper else 0, _p(out, L.c_u8p), cap), "vtn_ref_fetch")
+        return bytes(out[:n])
+
+    # ---- normalize / decompose through HOST buffers ----
+    def normalize(self, batch, result=None):
+        res = result or NormResult(batch.n_rec, batch.n_bytes)
+        cb = batch.as_c()
+        self._chk(self.lib.vtn_normalize(self.h, C.byref(cb), C.byref(res.c)), "vtn_normalize")
+        return res
+
+    def decompose(self, batch, normalize=False):
+        bound = int(self.lib.vtn_decompose_out_bound(C.byref(batch.as_c())))
+        src = np.zeros(max(bound, 1), np.uint32)
+        alt = np.zeros(max(bound, 1), np.uint16)
+        n_out = C.c_uint64(0)
+        dc = L.VtnDecompCounters()
+        cb = batch.as_c()
+        if not normalize:
+            self._chk(self.lib.vtn_decompose(self.h, C.byref(cb), _p(src, L.c_u32p), _p(alt, L.c_u16p), C.byref(n_out), C.byref(dc)), "vtn_decompose")
+            res = None
+        else:
+            # output bytes bound: every output record carries REF + one ALT
+            nb = 0
+            if batch.n_rec:
+                lens = np.diff(batch.allele_off.astype(np.int64))
+                na = np.diff(batch.allele_beg.astype(np.int64))
+                ref_len = lens[batch.allele_beg[:-1].astype(np.int64)]
+                nb = int((np.maximum(na - 1, 1) * ref_len).sum() + lens.sum())
+            res = NormResult(bound, nb)
+            self._chk(self.lib.vtn_decompose_normalize(self.h, C.byref(cb), _p(src, L.c_u32p), _p(alt, L.c_u16p), C.byref(n_out), C.byref(dc), C.byref(res.c)), "vtn_decompose_normalize")
+        k = int(n_out.value)
+        counters = [dc.no_variants, dc.no_biallelic, dc.no_multiallelic, dc.no_additional_biallelic]
+        return src[:k], alt[:k], counters, res
+
+    # ---- device-resident batches ----
+    def upload(self, batch):
+        h = C.c_void_p()
+        cb = batch.as_c()
+        self._chk(self.lib.vtn_dbatch_create(self.h, C.byref(cb), C.byref(h)), "vtn_dbatch_create")
+        return h
+
+    def free(self, db):
+        self.lib.vtn_dbatch_destroy(self.h, db)
+
+    def normalize_resident(self, db):
+        self._chk(self.lib.vtn_normalize_resident(self.h, db), "vtn_normalize_resident")
+
+    def decompose_resident(self, db, fuse_normalize):
+        self._chk(self.lib.vtn_decompose_resident(self.h, db, 1 if fuse_normalize else 0), "vtn_decompose_resident")
+
+    def fetch_result(self, db, batch):
+        res = NormResult(batch.n_rec, batch.n_bytes)
+        self._chk(self.lib.vtn_dbatch_fetch_result(self.h, db, C.byref(res.c)), "vtn_dbatch_fetch_result")
+        return res
+
+    def sync(self):
+        self._chk(self.lib.vtn_sync(self.h), "vtn_sync")
+
+    def timer_start(self):
+        self._chk(self.lib.vtn_timer_start(self.h), "vtn_timer_start")
+
+    def timer_stop(self):
+        ms = C.c_float(0)
+        self._chk(self.lib.vtn_timer_stop(self.h, C.byref(ms)), "vtn_timer_stop")
+        return float(ms.value)
+
+    def launch_count(self):
+        return int(self.lib.vtn_launch_count(self.h))

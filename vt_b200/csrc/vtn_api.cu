@@ -1,0 +1,379 @@
+// vtn_api.cu -- context, device batches and the host-buffer entry points of the C ABI (include/vtn.h).
+#include <string.h>
+#include "vtn_internal.h"
+
+static thread_local std::string g_create_err;
+
+int vtn_set_err(vtn_ctx* ctx, int code, const std::string& msg)
+{
+    if (ctx) ctx->err = msg;
+    else g_create_err = msg;
+    return code;
+}
+
+const char* vtn_last_error(const vtn_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+int vtn_ctx_create(vtn_ctx** out, int device)
+{
+    if (!out) return vtn_set_err(nullptr, VTN_E_ARG, "vtn_ctx_create: null out");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return vtn_set_err(nullptr, VTN_E_CUDA, std::string("no CUDA device (libvtn has no CPU fallback): ") + cudaGetErrorString(e));
+    if (device < 0 || device >= n) return vtn_set_err(nullptr, VTN_E_ARG, "vtn_ctx_create: bad device index");
+    vtn_ctx* ctx = new vtn_ctx();
+    ctx->device = device;
+    VTN_CUDA(nullptr, cudaSetDevice(device));
+    cudaDeviceProp prop;
+    VTN_CUDA(nullptr, cudaGetDeviceProperties(&prop, device));
+    ctx->sm_count = prop.multiProcessorCount;
+    VTN_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    VTN_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+    VTN_CUDA(nullptr, cudaEventCreate(&ctx->ev0));
+    VTN_CUDA(nullptr, cudaEventCreate(&ctx->ev1));
+    *out = ctx;
+    return VTN_OK;
+}
+
+int vtn_ctx_destroy(vtn_ctx* ctx)
+{
+    if (!ctx) return VTN_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->scratch) vtn_dbatch_destroy(ctx, ctx->scratch);
+    cudaFree(ctx->d_groups);
+    cudaFree(ctx->d_contig_goff);
+    cudaFree(ctx->d_contig_len);
+    cudaFree(ctx->d_exc_start);
+    cudaFree(ctx->d_exc_len);
+    cudaFree(ctx->d_exc_byte);
+    cudaEventDestroy(ctx->ev0);
+    cudaEventDestroy(ctx->ev1);
+    cudaStreamDestroy(ctx->stream);
+    cudaStreamDestroy(ctx->stream2);
+    delete ctx;
+    return VTN_OK;
+}
+
+int vtn_sync(vtn_ctx* ctx)
+{
+    if (!ctx) return VTN_E_ARG;
+    VTN_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    VTN_CUDA(ctx, cudaStreamSynchronize(ctx->stream2));
+    return VTN_OK;
+}
+
+int vtn_host_alloc(vtn_ctx* ctx, size_t bytes, void** p)
+{
+    if (!ctx || !p) return VTN_E_ARG;
+    VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    VTN_CUDA(ctx, cudaMallocHost(p, bytes ? bytes : 1));
+    return VTN_OK;
+}
+
+int vtn_host_free(vtn_ctx* ctx, void* p)
+{
+    if (!ctx) return VTN_E_ARG;
+    VTN_CUDA(ctx, cudaFreeHost(p));
+    return VTN_OK;
+}
+
+int vtn_timer_start(vtn_ctx* ctx)
+{
+    if (!ctx) return VTN_E_ARG;
+    VTN_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    return VTN_OK;
+}
+
+int vtn_timer_stop(vtn_ctx* ctx, float* ms)
+{
+    if (!ctx || !ms) return VTN_E_ARG;
+    VTN_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    VTN_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+    VTN_CUDA(ctx, cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+    return VTN_OK;
+}
+
+uint64_t vtn_launch_count(const vtn_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+// ---------------------------------------------------------------------------------------------------------
+
+template <typename T>
+static cudaError_t dalloc(T** p, size_t n)
+{
+    return cudaMalloc((void**)p, (n ? n : 1) * sizeof(T));
+}
+
+int vtn_dbatch_alloc(vtn_ctx* ctx, uint32_t n_rec, uint32_t n_allele, uint64_t n_bytes, bool with_inputs, vtn_dbatch** out)
+{
+    vtn_dbatch* d = new vtn_dbatch();
+    d->n_rec = n_rec;
+    d->n_allele = n_allele;
+    d->n_bytes = n_bytes;
+    d->owns_inputs = with_inputs;
+    d->cap_rec = n_rec;
+    d->cap_allele = n_allele;
+    d->cap_bytes = n_bytes;
+    const uint32_t tile = vtn_normalize_tile_records();
+    d->n_tiles = (n_rec + tile - 1) / tile;
+    cudaError_t e = cudaSuccess;
+#define A(x) if (e == cudaSuccess) e = (x)
+    if (with_inputs)
+    {
+        A(dalloc(&d->pos1, n_rec));
+        A(dalloc(&d->rid, n_rec));
+        A(dalloc(&d->allele_beg, (size_t)n_rec + 1));
+        A(dalloc(&d->allele_off, (size_t)n_allele + 1));
+        A(dalloc(&d->bytes, n_bytes + 16));
+    }
+    A(dalloc(&d->status, n_rec));
+    A(dalloc(&d->vtype, n_rec));
+    A(dalloc(&d->chg_rec, n_rec));
+    A(dalloc(&d->chg_pos1, n_rec));
+    A(dalloc(&d->chg_lt, n_rec));
+    A(dalloc(&d->chg_le, n_rec));
+    A(dalloc(&d->chg_rt, n_rec));
+    A(dalloc(&d->chg_off, (size_t)n_rec + 1));
+    A(dalloc(&d->chg_bytes, n_bytes + 16));
+    A(dalloc(&d->totals, 4));
+    A(dalloc(&d->counters, 16));
+    A(dalloc(&d->tile_state, 2 * (size_t)d->n_tiles));
+    A(dalloc(&d->tile_counter, 4));
+#undef A
+    if (e != cudaSuccess)
+    {
+        vtn_dbatch_destroy(ctx, d);
+        return vtn_set_err(ctx, VTN_E_NOMEM, std::string("device batch allocation: ") + cudaGetErrorString(e));
+    }
+    *out = d;
+    return VTN_OK;
+}
+
+bool vtn_dbatch_resize(vtn_dbatch* d, uint32_t n_rec, uint32_t n_allele, uint64_t n_bytes)
+{
+    if (n_rec > d->cap_rec || n_allele > d->cap_allele || n_bytes > d->cap_bytes) return false;
+    d->n_rec = n_rec;
+    d->n_allele = n_allele;
+    d->n_bytes = n_bytes;
+    const uint32_t tile = vtn_normalize_tile_records();
+    d->n_tiles = (n_rec + tile - 1) / tile;
+    return true;
+}
+
+int vtn_dbatch_destroy(vtn_ctx* ctx, vtn_dbatch* d)
+{
+    if (!d) return VTN_OK;
+    if (ctx) cudaSetDevice(ctx->device);
+    if (d->fused) vtn_dbatch_destroy(ctx, d->fused);
+    if (d->owns_inputs)
+    {
+        cudaFree(d->pos1); cudaFree(d->rid); cudaFree(d->allele_beg); cudaFree(d->allele_off); cudaFree(d->bytes);
+    }
+    cudaFree(d->status); cudaFree(d->vtype); cudaFree(d->chg_rec); cudaFree(d->chg_pos1); cudaFree(d->chg_lt);
+    cudaFree(d->chg_le); cudaFree(d->chg_rt); cudaFree(d->chg_off); cudaFree(d->chg_bytes); cudaFree(d->totals);
+    cudaFree(d->counters); cudaFree(d->tile_state); cudaFree(d->tile_counter); cudaFree(d->src_rec); cudaFree(d->alt_idx);
+    delete d;
+    return VTN_OK;
+}
+
+static int check_batch(vtn_ctx* ctx, const vtn_batch* in)
+{
+    if (!in) return vtn_set_err(ctx, VTN_E_ARG, "null batch");
+    if (in->n_rec && (!in->pos1 || !in->rid || !in->allele_beg || !in->allele_off || (in->n_bytes && !in->bytes)))
+        return vtn_set_err(ctx, VTN_E_ARG, "batch has null arrays");
+    if (in->n_bytes >= (1ull << 32)) return vtn_set_err(ctx, VTN_E_ARG, "batch allele bytes must be < 4 GiB");
+    if (in->n_rec && (in->allele_beg[in->n_rec] != in->n_allele || in->allele_off[in->n_allele] != in->n_bytes))
+        return vtn_set_err(ctx, VTN_E_ARG, "batch prefix arrays inconsistent with n_allele / n_bytes");
+    return VTN_OK;
+}
+
+static int upload_inputs(vtn_ctx* ctx, const vtn_batch* in, vtn_dbatch* d, cudaStream_t s)
+{
+    if (!in->n_rec) return VTN_OK;
+    VTN_CUDA(ctx, cudaMemcpyAsync(d->pos1, in->pos1, sizeof(int32_t) * in->n_rec, cudaMemcpyHostToDevice, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(d->rid, in->rid, sizeof(int32_t) * in->n_rec, cudaMemcpyHostToDevice, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(d->allele_beg, in->allele_beg, sizeof(uint32_t) * ((size_t)in->n_rec + 1), cudaMemcpyHostToDevice, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(d->allele_off, in->allele_off, sizeof(uint32_t) * ((size_t)in->n_allele + 1), cudaMemcpyHostToDevice, s));
+    if (in->n_bytes) VTN_CUDA(ctx, cudaMemcpyAsync(d->bytes, in->bytes, in->n_bytes, cudaMemcpyHostToDevice, s));
+    return VTN_OK;
+}
+
+int vtn_dbatch_create(vtn_ctx* ctx, const vtn_batch* in, vtn_dbatch** db)
+{
+    if (!ctx || !db) return VTN_E_ARG;
+    int rc = check_batch(ctx, in);
+    if (rc) return rc;
+    VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    rc = vtn_dbatch_alloc(ctx, in->n_rec, in->n_allele, in->n_bytes, true, db);
+    if (rc) return rc;
+    rc = upload_inputs(ctx, in, *db, ctx->stream);
+    if (rc) return rc;
+    VTN_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return VTN_OK;
+}
+
+int vtn_normalize_resident(vtn_ctx* ctx, vtn_dbatch* d)
+{
+    if (!ctx || !d) return VTN_E_ARG;
+    if (!ctx->ref_loaded) return vtn_set_err(ctx, VTN_E_STATE, "vtn_normalize: no reference loaded");
+    VtnDevBatchView v{d->n_rec, d->pos1, d->rid, d->allele_beg, d->allele_off, d->bytes};
+    VtnDevNormOut o{d->status, d->vtype, d->chg_rec, d->chg_pos1, d->chg_lt, d->chg_le, d->chg_rt, d->chg_off, d->chg_bytes, d->totals, d->counters};
+    return vtn_launch_normalize(ctx, v, o, d->tile_state, d->tile_counter, d->n_tiles);
+}
+
+static int fetch_norm(vtn_ctx* ctx, vtn_dbatch* d, vtn_norm_result* out)
+{
+    cudaStream_t s = ctx->stream;
+    unsigned long long totals[2] = {0, 0};
+    uint32_t counters[12];
+    VTN_CUDA(ctx, cudaMemcpyAsync(totals, d->totals, sizeof totals, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(counters, d->counters, sizeof counters, cudaMemcpyDeviceToHost, s));
+    if (d->n_rec)
+    {
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->status, d->status, d->n_rec, cudaMemcpyDeviceToHost, s));
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->vtype, d->vtype, d->n_rec, cudaMemcpyDeviceToHost, s));
+    }
+    VTN_CUDA(ctx, cudaStreamSynchronize(s));
+    out->n_changed = (uint32_t)totals[0];
+    out->n_changed_bytes = totals[1];
+    memcpy(out->counters.bi, counters, 5 * sizeof(uint32_t));
+    memcpy(out->counters.multi, counters + 5, 5 * sizeof(uint32_t));
+    out->counters.no_variants = counters[10];
+    out->counters.no_refs = counters[11];
+    if (totals[0] > out->cap_changed || totals[1] > out->cap_changed_bytes)
+        return vtn_set_err(ctx, VTN_E_CAPACITY, "vtn_normalize: result capacity too small (n_changed / n_changed_bytes are set)");
+    const size_t k = (size_t)totals[0];
+    if (k)
+    {
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_rec, d->chg_rec, k * 4, cudaMemcpyDeviceToHost, s));
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_pos1, d->chg_pos1, k * 4, cudaMemcpyDeviceToHost, s));
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_lt, d->chg_lt, k * 4, cudaMemcpyDeviceToHost, s));
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_le, d->chg_le, k * 4, cudaMemcpyDeviceToHost, s));
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_rt, d->chg_rt, k * 4, cudaMemcpyDeviceToHost, s));
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_bytes, d->chg_bytes, (size_t)totals[1], cudaMemcpyDeviceToHost, s));
+    }
+    VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_off, d->chg_off, (k + 1) * 8, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaStreamSynchronize(s));
+    return VTN_OK;
+}
+
+int vtn_dbatch_fetch_result(vtn_ctx* ctx, vtn_dbatch* db, vtn_norm_result* out)
+{
+    if (!ctx || !db || !out) return VTN_E_ARG;
+    return fetch_norm(ctx, db, out);
+}
+
+// make sure the ctx-owned scratch batch can hold (n_rec, n_allele, n_bytes)
+static int ensure_scratch(vtn_ctx* ctx, uint32_t n_rec, uint32_t n_allele, uint64_t n_bytes)
+{
+    if (ctx->scratch && vtn_dbatch_resize(ctx->scratch, n_rec, n_allele, n_bytes)) return VTN_OK;
+    if (ctx->scratch) vtn_dbatch_destroy(ctx, ctx->scratch);
+    ctx->scratch = nullptr;
+    uint32_t cr = n_rec + n_rec / 8 + 1024, ca = n_allele + n_allele / 8 + 2048;
+    uint64_t cb = n_bytes + n_bytes / 8 + 4096;
+    if (cr < n_rec) cr = n_rec;
+    if (ca < n_allele) ca = n_allele;
+    int rc = vtn_dbatch_alloc(ctx, cr, ca, cb, true, &ctx->scratch);
+    if (rc) return rc;
+    vtn_dbatch_resize(ctx->scratch, n_rec, n_allele, n_bytes);
+    return VTN_OK;
+}
+
+int vtn_normalize(vtn_ctx* ctx, const vtn_batch* in, vtn_norm_result* out)
+{
+    if (!ctx || !out) return VTN_E_ARG;
+    if (!ctx->ref_loaded) return vtn_set_err(ctx, VTN_E_STATE, "vtn_normalize: no reference loaded");
+    int rc = check_batch(ctx, in);
+    if (rc) return rc;
+    VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    rc = ensure_scratch(ctx, in->n_rec, in->n_allele, in->n_bytes);
+    if (rc) return rc;
+    vtn_dbatch* d = ctx->scratch;
+    rc = upload_inputs(ctx, in, d, ctx->stream);
+    if (rc) return rc;
+    rc = vtn_normalize_resident(ctx, d);
+    if (rc) return rc;
+    return fetch_norm(ctx, d, out);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// decompose
+uint64_t vtn_decompose_out_bound(const vtn_batch* in)
+{
+    if (!in || !in->n_rec) return 0;
+    uint64_t k = 0;
+    for (uint32_t r = 0; r < in->n_rec; ++r)
+    {
+        uint32_t n = in->allele_beg[r + 1] - in->allele_beg[r];
+        k += n > 2 ? n - 1 : 1;
+    }
+    return k;
+}
+
+int vtn_decompose_resident(vtn_ctx* ctx, vtn_dbatch* d, int fuse_normalize)
+{
+    if (!ctx || !d) return VTN_E_ARG;
+    if (fuse_normalize && !ctx->ref_loaded) return vtn_set_err(ctx, VTN_E_STATE, "vtn_decompose_normalize: no reference loaded");
+    int rc = vtn_launch_decompose(ctx, d, fuse_normalize != 0);
+    if (rc || !fuse_normalize) return rc;
+    return vtn_normalize_resident(ctx, d->fused);
+}
+
+int vtn_dbatch_fetch_decompose(vtn_ctx* ctx, vtn_dbatch* d, uint32_t* src_rec, uint16_t* alt_idx, uint64_t* n_out,
+                               vtn_decomp_counters* counters)
+{
+    if (!ctx || !d) return VTN_E_ARG;
+    cudaStream_t s = ctx->stream;
+    unsigned long long tot[3] = {0, 0, 0};
+    uint32_t c[4] = {0, 0, 0, 0};
+    VTN_CUDA(ctx, cudaMemcpyAsync(tot, d->totals, sizeof tot, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(c, d->counters + 12, sizeof c, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaStreamSynchronize(s));
+    if (n_out) *n_out = tot[0];
+    if (counters)
+    {
+        counters->no_variants = c[0];
+        counters->no_biallelic = c[1];
+        counters->no_multiallelic = c[2];
+        counters->no_additional_biallelic = c[3];
+    }
+    if (tot[0] && src_rec) VTN_CUDA(ctx, cudaMemcpyAsync(src_rec, d->src_rec, tot[0] * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    if (tot[0] && alt_idx) VTN_CUDA(ctx, cudaMemcpyAsync(alt_idx, d->alt_idx, tot[0] * sizeof(uint16_t), cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaStreamSynchronize(s));
+    return VTN_OK;
+}
+
+static int decompose_host(vtn_ctx* ctx, const vtn_batch* in, uint32_t* src_rec, uint16_t* alt_idx, uint64_t* n_out,
+                          vtn_decomp_counters* counters, vtn_norm_result* nout)
+{
+    if (!ctx) return VTN_E_ARG;
+    int rc = check_batch(ctx, in);
+    if (rc) return rc;
+    VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    rc = ensure_scratch(ctx, in->n_rec, in->n_allele, in->n_bytes);
+    if (rc) return rc;
+    vtn_dbatch* d = ctx->scratch;
+    rc = upload_inputs(ctx, in, d, ctx->stream);
+    if (rc) return rc;
+    rc = vtn_decompose_resident(ctx, d, nout ? 1 : 0);
+    if (rc) return rc;
+    rc = vtn_dbatch_fetch_decompose(ctx, d, src_rec, alt_idx, n_out, counters);
+    if (rc) return rc;
+    if (nout) rc = fetch_norm(ctx, d->fused, nout);
+    return rc;
+}
+
+int vtn_decompose(vtn_ctx* ctx, const vtn_batch* in, uint32_t* src_rec, uint16_t* alt_idx, uint64_t* n_out,
+                  vtn_decomp_counters* counters)
+{
+    return decompose_host(ctx, in, src_rec, alt_idx, n_out, counters, nullptr);
+}
+
+int vtn_decompose_normalize(vtn_ctx* ctx, const vtn_batch* in, uint32_t* src_rec, uint16_t* alt_idx, uint64_t* n_out,
+                            vtn_decomp_counters* dcounters, vtn_norm_result* out)
+{
+    if (!out) return VTN_E_ARG;
+    if (!ctx || !ctx->ref_loaded) return vtn_set_err(ctx, VTN_E_STATE, "vtn_decompose_normalize: no reference loaded");
+    return decompose_host(ctx, in, src_rec, alt_idx, n_out, dcounters, out);
+}

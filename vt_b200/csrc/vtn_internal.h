@@ -1,0 +1,141 @@
+// vtn_internal.h -- shared declarations of libvtn (host + device).  Not part of the ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/vtn.h"
+
+// ---------------------------------------------------------------------------------------------
+// Resident reference layout (HBM).
+// One 16-byte "group" per 32 bases: { u64 code (2 bits/base, A=0 C=1 G=2 T=3, base j at bits 2j..2j+1),
+// u32 nonstd (bit j: raw FASTA byte is not one of upper-case ACGT), u32 lower (bit j: raw byte is one of
+// acgt) }.  One LDG.128 therefore brings everything the hot path needs for 32 bases: the upper-cased
+// base (faidx_fetch_uc_seq, hts_utils.cpp:41-51) and whether the raw byte (faidx_fetch_seq,
+// faidx.c:875-881) differs from it.  Bytes that are neither ACGT nor acgt (N, IUPAC, ...) are kept
+// verbatim in a run-length table (exc_*), keyed by global base position, searched only on the slow path.
+// Contigs start on a group boundary; global position of base p0 of contig c = contig_goff[c]*32 + p0.
+// ---------------------------------------------------------------------------------------------
+struct VtnDevRef
+{
+    const uint4* groups;       // [n_groups]  (.x,.y = code lo/hi ; .z = nonstd ; .w = lower)
+    const uint64_t* contig_goff; // [n_contig] first group of contig
+    const int64_t* contig_len;   // [n_contig]
+    const uint64_t* exc_start; // [n_exc] global base position of run start (sorted)
+    const uint32_t* exc_len;   // [n_exc]
+    const uint8_t* exc_byte;   // [n_exc] the raw byte repeated over the run
+    uint32_t n_exc;
+    int32_t n_contig;
+};
+
+struct VtnContig
+{
+    std::string name;
+    int64_t len;
+    uint64_t goff;
+};
+
+// device-side view of a batch and its result buffers
+struct VtnDevBatchView
+{
+    uint32_t n_rec;
+    const int32_t* pos1;
+    const int32_t* rid;
+    const uint32_t* allele_beg;
+    const uint32_t* allele_off;
+    const uint8_t* bytes;
+};
+
+struct VtnDevNormOut
+{
+    uint8_t* status;
+    uint8_t* vtype;
+    uint32_t* chg_rec;
+    int32_t* chg_pos1;
+    uint32_t* chg_lt;
+    uint32_t* chg_le;
+    uint32_t* chg_rt;
+    uint64_t* chg_off;   // [n_changed+1]
+    uint8_t* chg_bytes;
+    unsigned long long* totals; // [0]=n_changed [1]=n_changed_bytes
+    uint32_t* counters;  // [12]
+};
+
+struct vtn_dbatch
+{
+    uint32_t n_rec = 0, n_allele = 0;
+    uint64_t n_bytes = 0;
+    uint32_t cap_rec = 0, cap_allele = 0; // allocated capacities (n_* <= cap_*)
+    uint64_t cap_bytes = 0;
+    // inputs
+    int32_t* pos1 = nullptr;
+    int32_t* rid = nullptr;
+    uint32_t* allele_beg = nullptr;
+    uint32_t* allele_off = nullptr;
+    uint8_t* bytes = nullptr;
+    // normalize outputs (capacity n_rec / n_bytes: new alleles never grow)
+    uint8_t* status = nullptr;
+    uint8_t* vtype = nullptr;
+    uint32_t* chg_rec = nullptr;
+    int32_t* chg_pos1 = nullptr;
+    uint32_t* chg_lt = nullptr;
+    uint32_t* chg_le = nullptr;
+    uint32_t* chg_rt = nullptr;
+    uint64_t* chg_off = nullptr;
+    uint8_t* chg_bytes = nullptr;
+    unsigned long long* totals = nullptr; // 2 (+ decompose: [2]=n_out)
+    uint32_t* counters = nullptr;         // 12 normalize + 4 decompose
+    // scan state
+    unsigned long long* tile_state = nullptr; // [2*n_tiles]
+    uint32_t* tile_counter = nullptr;
+    uint32_t n_tiles = 0;
+    // decompose outputs / fused intermediates
+    uint32_t* src_rec = nullptr;
+    uint16_t* alt_idx = nullptr;
+    uint64_t out_bound = 0;    // sum(max(n_allele-1,1))
+    struct vtn_dbatch* fused = nullptr; // biallelic batch materialised on device for the fused path
+    bool owns_inputs = true;
+};
+
+struct vtn_ctx
+{
+    int device = 0;
+    cudaStream_t stream = nullptr;   // compute + primary copies
+    cudaStream_t stream2 = nullptr;  // second copy stream for the pipelined host-buffer call
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int sm_count = 0;
+    std::string err;
+    uint64_t launches = 0;
+    // reference
+    std::vector<VtnContig> contigs;
+    VtnDevRef dref{};
+    void* d_groups = nullptr;
+    void* d_contig_goff = nullptr;
+    void* d_contig_len = nullptr;
+    void* d_exc_start = nullptr;
+    void* d_exc_len = nullptr;
+    void* d_exc_byte = nullptr;
+    int64_t ref_bytes = 0;
+    bool ref_loaded = false;
+    // reusable device arena for the host-buffer call
+    vtn_dbatch* scratch = nullptr;
+    uint32_t scratch_rec = 0, scratch_allele = 0;
+    uint64_t scratch_bytes = 0;
+};
+
+int vtn_set_err(vtn_ctx* ctx, int code, const std::string& msg);
+#define VTN_CUDA(ctx, call)                                                                              \
+    do                                                                                                   \
+    {                                                                                                    \
+        cudaError_t e__ = (call);                                                                        \
+        if (e__ != cudaSuccess)                                                                          \
+            return vtn_set_err((ctx), VTN_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__)); \
+    } while (0)
+
+// kernels' host launchers (vtn_normalize.cu / vtn_decompose.cu)
+int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNormOut& out,
+                         unsigned long long* tile_state, uint32_t* tile_counter, uint32_t n_tiles);
+uint32_t vtn_normalize_tile_records();
+int vtn_launch_decompose(vtn_ctx* ctx, vtn_dbatch* db, bool materialise);
+bool vtn_dbatch_resize(vtn_dbatch* d, uint32_t n_rec, uint32_t n_allele, uint64_t n_bytes);
+int vtn_dbatch_alloc(vtn_ctx* ctx, uint32_t n_rec, uint32_t n_allele, uint64_t n_bytes, bool with_inputs, vtn_dbatch** out);
