@@ -1,0 +1,290 @@
+#!/usr/bin/env python3
+"""bench.py -- vt normalize hot path on B200 (BASELINE.json metric: M records/s decompose+normalize).
+
+A "step" = one pass of the normalize path over one batch of 10 M synthetic biallelic SNV+indel records
+(config C2) against the synthetic 3.1 Gb GRCh38-shaped reference resident in HBM.
+  value : records/s with the batch already resident in HBM (CUDA events on the library's stream)
+  e2e   : the same through the reference-facing C-ABI call vtn_normalize() with pinned HOST buffers,
+          H2D + kernel + D2H inside the timed region
+  roofline / cpu_baseline : see DESIGN.md "Measurement"
+  --impl reference : the UNMODIFIED reference `vt normalize` (oracle/_ref/vt_ref) on the host cores.
+Launch: python bench.py --gpus N --steps K --warmup W   (N>1: torchrun, one rank per GPU, weak scaling)
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "normalize_records_per_s"
+UNIT = "M records/s"
+N_RECORDS = int(os.environ.get("VTN_BENCH_RECORDS", 10_000_000))
+REF_SCALE = float(os.environ.get("VTN_BENCH_REF_SCALE", 1.0))
+CPU_SAMPLE_RECORDS = int(os.environ.get("VTN_BENCH_CPU_SAMPLE", 1_000_000))
+VT_REF = os.path.join(ROOT, "oracle", "_ref", "vt_ref")
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.p, self.t = [], None, None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "20"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.05)
+        self.p.terminate()
+        sm, mx, reasons = [], None, set()
+        rows = [r for (t, r) in self.rows if t0 <= t <= t1 + 0.05] or [r for (_, r) in self.rows[-3:]]
+        for r in rows:
+            f = [x.strip() for x in r.split(",")]
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def write_vcf(path, names, seqs, batch, lo, hi):
+    with open(path, "w") as f:
+        f.write("##fileformat=VCFv4.2\n")
+        for n, s in zip(names, seqs):
+            f.write("##contig=<ID=%s,length=%d>\n" % (n, s.shape[0]))
+        f.write("#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\n")
+        data = batch.data.tobytes()
+        ao = batch.allele_off
+        lines = []
+        for r in range(lo, hi):
+            o0, o1, o2 = int(ao[2 * r]), int(ao[2 * r + 1]), int(ao[2 * r + 2])
+            lines.append("%s\t%d\t.\t%s\t%s\t.\t.\t.\n" % (names[batch.rid[r]], batch.pos1[r], data[o0:o1].decode(), data[o1:o2].decode()))
+        f.write("".join(lines))
+
+
+def cpu_reference_run(n_sample, steps, warmup):
+    """Times the unmodified reference `vt normalize` on a bounded sample of the C2 workload: n_sample records
+    on one chr21-sized contig of the same synthetic reference; P = host cores processes each normalise the
+    whole sample concurrently (vt itself is single-threaded); throughput = P * n_sample / slowest wall."""
+    from vt_b200 import synth
+    import helpers
+    if not os.path.exists(VT_REF):
+        raise RuntimeError("oracle/_ref/vt_ref missing: run __graft_entry__.build() in the build container")
+    cores = len(os.sched_getaffinity(0))
+    P = max(1, min(cores, 64))
+    contigs = [synth.GRCH38[20]]
+    names, seqs = synth.make_reference(scale=REF_SCALE, contigs=contigs)
+    batch = synth.make_biallelic(seqs, n_sample, seed=synth.SEED_VCF_C2)
+    tmp = tempfile.mkdtemp(prefix="vtn_cpu_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+    fa = os.path.join(tmp, "ref.fa")
+    helpers.write_fasta(fa, names, seqs)
+    vcf = os.path.join(tmp, "in.vcf")
+    write_vcf(vcf, names, seqs, batch, 0, batch.n_rec)
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        procs = [subprocess.Popen([VT_REF, "normalize", vcf, "-r", fa, "-o", os.path.join(tmp, "out%d.vcf" % p), "-q"],
+                                  stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL) for p in range(P)]
+        rcs = [p.wait() for p in procs]
+        dt = time.perf_counter() - t0
+        if any(rcs):
+            raise RuntimeError("reference vt normalize failed: %s" % rcs)
+        if it >= warmup:
+            times.append(dt)
+    import shutil
+    shutil.rmtree(tmp, ignore_errors=True)
+    ms = 1e3 * float(np.mean(times))
+    val = P * n_sample / (ms / 1e3) / 1e6
+    sample = "%d records (80%% SNV/10%% del/10%% ins, C2 generator) on one %d-bp contig of the synthetic reference, VCF text + FASTA on tmpfs, %d concurrent single-threaded `vt normalize` processes each over the whole sample" % (n_sample, seqs[0].shape[0], P)
+    return val, ms, P, sample
+
+
+def run_reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    val, ms, P, sample = cpu_reference_run(CPU_SAMPLE_RECORDS, args.steps, args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "C2: 10M synthetic biallelic SNV+indel records, synthetic 3.1 Gb GRCh38-shaped reference (bounded sample, see cpu_baseline.sample)"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": P, "kind": "reference", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def pinned_batch(ctx, batch):
+    """Copy a Batch into pinned host memory obtained from the library (vtn_host_alloc)."""
+    import ctypes as C
+    from vt_b200.api import Batch
+
+    def pin(a):
+        p = C.c_void_p()
+        ctx._chk(ctx.lib.vtn_host_alloc(ctx.h, max(a.nbytes, 1), C.byref(p)), "vtn_host_alloc")
+        buf = (C.c_uint8 * max(a.nbytes, 1)).from_address(p.value)
+        out = np.frombuffer(buf, dtype=a.dtype, count=a.size)
+        out[:] = a
+        return out
+    return Batch(pin(batch.pos1), pin(batch.rid), pin(batch.allele_beg), pin(batch.allele_off), pin(batch.data))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="vtn", choices=["vtn", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "vtn" else args.warmup
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from vt_b200 import Context, synth
+    from vt_b200.api import NormResult
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    t_setup = time.time()
+    names, seqs = synth.make_reference(scale=REF_SCALE)
+    batch = synth.make_biallelic(seqs, N_RECORDS, seed=synth.SEED_VCF_C2 + 1000 * rank)
+    ctx = Context(local)
+    ctx.load_reference(names, seqs)
+    ref_bases = sum(s.shape[0] for s in seqs)
+    del seqs
+    log("[rank %d] setup %.1fs: %d records, %d allele bytes, reference %d bases" % (rank, time.time() - t_setup, batch.n_rec, batch.n_bytes, ref_bases))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ctx.sync()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---------------- device-resident: value + roofline ----------------
+    db = ctx.upload(batch)
+    for _ in range(args.warmup):
+        ctx.normalize_resident(db)
+    ctx.sync()
+    res = ctx.fetch_result(db, batch)
+    alg_bytes = synth.algorithmic_bytes(batch, res)
+    sampler = ClockSampler(local)
+    barrier()
+    l0 = ctx.launch_count()
+    t0 = time.time()
+    ctx.timer_start()
+    for _ in range(args.steps):
+        ctx.normalize_resident(db)
+    ms_total = ctx.timer_stop()
+    barrier()
+    launches = ctx.launch_count() - l0
+    ms_step = max_over_ranks(ms_total / args.steps)
+    value = world * batch.n_rec / (ms_step / 1e3) / 1e6
+
+    # ---------------- end to end through the C ABI with pinned host buffers ----------------
+    hb = pinned_batch(ctx, batch)
+    hres = NormResult(batch.n_rec, batch.n_bytes)
+    e2e_steps = max(3, min(args.steps, 20))
+    for _ in range(3):
+        ctx.normalize(hb, hres)
+    barrier()
+    w0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        ctx.normalize(hb, hres)
+    barrier()
+    e2e_ms = max_over_ranks(1e3 * (time.perf_counter() - w0) / e2e_steps)
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1)
+    e2e_val = world * batch.n_rec / (e2e_ms / 1e3) / 1e6
+    h2d = 4 * batch.n_rec * 2 + 4 * (batch.n_rec + 1) + 4 * (batch.n_allele + 1) + batch.n_bytes
+    k = hres.n_changed
+    d2h = 2 * batch.n_rec + 16 + 48 + 20 * k + 8 * (k + 1) + hres.n_changed_bytes
+    assert hres.n_changed == res.n_changed and hres.counters == res.counters
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = alg_bytes / (ms_total / args.steps / 1e3) / 1e9
+
+    if rank != 0:
+        ctx.free(db)
+        return
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic",
+        "config": {
+            "workload": "C2: %d synthetic biallelic records per GPU (80%% SNV, 10%% del, 10%% ins, half of the indels unnormalized), synthetic %.2f Gb GRCh38-shaped reference resident in HBM" % (batch.n_rec, ref_bases / 1e9),
+            "records_per_gpu": batch.n_rec, "changed_per_gpu": res.n_changed,
+            "l2": "inputs+outputs per step (%d MB) exceed the 126 MB L2; no explicit flush" % ((h2d + d2h) // 1000000),
+            "sharding": "independent batch per rank, reference replicated, no collective",
+        },
+        "roofline": {
+            "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": None, "kernel": "vtn_normalize_kernel", "algorithmic_bytes_per_launch": alg_bytes,
+            "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
+        },
+        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms, "steps": e2e_steps},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+    }
+    if not args.no_cpu_baseline and world >= 1:
+        try:
+            cv, cms, P, sample = cpu_reference_run(CPU_SAMPLE_RECORDS, 2, 1)
+            line["cpu_baseline"] = {"value": cv, "unit": UNIT, "cores": P, "kind": "reference", "sample": sample}
+        except Exception as e:  # the checker binary is missing on this box
+            line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "unavailable: %s" % e}
+    print(json.dumps(line), flush=True)
+    ctx.free(db)
+
+
+if __name__ == "__main__":
+    main()

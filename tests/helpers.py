@@ -215,6 +215,8 @@ def synth_reference(rng, n_contig=3, length=20000, repeats=True, lower=False, n_
             p = 0
             while p < L - 300:
                 p += int(rng.integers(20, 400))
+                if p >= L:
+                    break
                 unit = rng.choice(np.frombuffer(b"ACGT", np.uint8), size=int(rng.integers(1, 7)))
                 tl = int(rng.integers(4, 200))
                 tract = np.resize(unit, tl)
