@@ -8,7 +8,7 @@
 
 // ---------------------------------------------------------------------------------------------
 // Resident reference layout (HBM).
-// One 16-byte "group" per 32 bases: { u64 code (2 bits/base, A=0 C=1 G=2 T=3, base j at bits 2j..2j+1),
+// One 16-byte "group" per 32 bases: { u64 code (2 bits/base, A=0 C=1 T=2 G=3 = (ascii>>1)&3, base j at bits 2j..2j+1),
 // u32 nonstd (bit j: raw FASTA byte is not one of upper-case ACGT), u32 lower (bit j: raw byte is one of
 // acgt) }.  One LDG.128 therefore brings everything the hot path needs for 32 bases: the upper-cased
 // base (faidx_fetch_uc_seq, hts_utils.cpp:41-51) and whether the raw byte (faidx_fetch_seq,

@@ -13,6 +13,7 @@
 #include "vtn_internal.h"
 #include "vtn_ref_dev.cuh"
 #include "vtn_scan.cuh"
+#include "vtn_fast.cuh"
 
 #define VTN_TILE 256
 
@@ -134,6 +135,223 @@ __device__ __forceinline__ uint8_t ext_byte(const VtnDevRef& R, VtnRefCursor& cu
     int64_t p0 = (int64_t)pos1 - 2 - (int64_t)(k - len);
     p0 = p0 < 0 ? 0 : (p0 >= clen ? clen - 1 : p0);
     return cur.uc(R, gbase + (uint64_t)p0);
+}
+
+// Phase C of the closed form for a biallelic record: every base of both alleles has been consumed
+// (T >= max len), so both streams read the reference, at a lag of |len0-len1| bases.  Walks down in 32-base
+// chunks (two packed windows, XOR, clz); per base only at contig edges or over N/IUPAC bases.
+// Returns the final T (<= cap).
+__device__ uint32_t lag_scan(const VtnDevRef& R, uint64_t gbase, int64_t clen, int32_t pos1, uint32_t len0, uint32_t len1,
+                             uint32_t T, uint32_t cap)
+{
+    VtnRefCursor cur;
+    while (T < cap)
+    {
+        // window of stream s ends (inclusive) at hi_s = pos1-2-T+len_s
+        int64_t hi0 = (int64_t)pos1 - 2 - (int64_t)T + (int64_t)len0;
+        int64_t hi1 = (int64_t)pos1 - 2 - (int64_t)T + (int64_t)len1;
+        int64_t lo = (hi0 < hi1 ? hi0 : hi1) - 31, hi = hi0 > hi1 ? hi0 : hi1;
+        bool fast = lo >= 0 && hi < clen;
+        uint32_t nm = 0;
+        if (fast)
+        {
+            uint64_t c0, c1;
+            uint32_t e0, e1;
+            vtn_ref_window32(R, gbase + (uint64_t)(hi0 - 31), c0, e0);
+            vtn_ref_window32(R, gbase + (uint64_t)(hi1 - 31), c1, e1);
+            if ((e0 | e1) == 0)
+            {
+                uint64_t x = c0 ^ c1;
+                uint64_t mm = (x | (x >> 1)) & 0x5555555555555555ull;
+                nm = mm ? (uint32_t)(__clzll((long long)mm) >> 1) : 32u;
+            }
+            else
+                fast = false;
+        }
+        if (fast)
+        {
+            uint32_t room = cap - T;
+            if (nm >= room) return cap;
+            T += nm;
+            if (nm < 32) return T;
+        }
+        else
+        {
+            // per base for up to 32 steps (contig edge, or N / IUPAC bases in the window)
+            uint32_t steps = 0;
+            while (T < cap && steps < 32)
+            {
+                uint8_t c0 = ext_byte(R, cur, gbase, clen, pos1, nullptr, len0, T);
+                uint8_t c1 = ext_byte(R, cur, gbase, clen, pos1, nullptr, len1, T);
+                if (c0 != c1) return T;
+                ++T;
+                ++steps;
+            }
+        }
+    }
+    return T;
+}
+
+// ---- fast path (see vtn_fast.cuh).  Returns false when the record is not eligible. ----
+__device__ bool fast_biallelic(const VtnDevRef& R, const uint8_t* bytes, uint32_t off0, uint32_t len0, uint32_t len1,
+                               int32_t pos1, int32_t rid, VtnFastRes& o)
+{
+    if (len0 > 32 || len1 > 32 || rid < 0 || rid >= R.n_contig || pos1 < 34) return false;
+    const int64_t clen = __ldg(R.contig_len + rid);
+    const int64_t p0 = (int64_t)pos1 - 1;
+    if (p0 + 32 > clen) return false; // keeps every window inside the contig (records at contig ends -> generic)
+    // ---- allele bytes -> 2-bit code stream (REF then ALT are contiguous) ----
+    const uint32_t L = len0 + len1;
+    uint64_t s0 = 0, s1 = 0, badacc = 0;
+    for (uint32_t c = 0; 8 * c < L; ++c)
+    {
+        uint64_t bad;
+        const uint32_t rem = L - 8 * c;
+        const uint64_t code = vtn_codes8(vtn_fetch8(bytes, off0 + 8 * c), rem, bad);
+        badacc |= bad;
+        if (c < 4) s0 |= code << (16 * c);
+        else s1 |= code << (16 * (c - 4));
+    }
+    if (badacc) return false;
+    const uint64_t Rc = s0 & vtn_mask2(len0);
+    const uint64_t Ac = (len0 == 32 ? s1 : ((s0 >> (2 * len0)) | (s1 << (64 - 2 * len0)))) & vtn_mask2(len1);
+    const uint32_t m = len0 < len1 ? len0 : len1, M = len0 < len1 ? len1 : len0;
+
+    // ---- classify_variant (variant_manip.cpp:337-505), all bases upper-case ACGT so compares are code compares ----
+    const bool same = (len0 == len1) && (Rc == Ac);
+    const uint64_t y = Rc ^ Ac;
+    const uint64_t mmy = (y | (y >> 1)) & 0x5555555555555555ull;
+    uint32_t cp_raw = mmy ? (uint32_t)(__ffsll((long long)mmy) - 1) >> 1 : 32u; // common prefix (may exceed m: capped below)
+    if (cp_raw > m) cp_raw = m;
+    uint32_t cs_raw = vtn_top_match(Rc << (64 - 2 * len0), Ac << (64 - 2 * len1)); // common suffix
+    if (cs_raw > m) cs_raw = m;
+    uint32_t vtype = VTN_VT_REF;
+    if (!same)
+    {
+        const uint32_t cs = cs_raw < m - 1 ? cs_raw : m - 1;
+        uint32_t rl = len0 - cs, al = len1 - cs;
+        const uint32_t mla = rl < al ? rl : al;
+        const uint32_t cp = cp_raw < mla - 1 ? cp_raw : mla - 1;
+        rl -= cp;
+        al -= cp;
+        const uint32_t mlen = rl < al ? rl : al;
+        uint32_t diff;
+        if (mlen == 1 && rl != al)
+        {
+            const uint64_t lg = rl > al ? Rc : Ac, sh = rl > al ? Ac : Rc;
+            const uint32_t ll = rl > al ? rl : al;
+            const uint32_t ls = (uint32_t)(lg >> (2 * cp)) & 3u, le_ = (uint32_t)(lg >> (2 * (cp + ll - 1))) & 3u;
+            const uint32_t ss = (uint32_t)(sh >> (2 * cp)) & 3u;
+            diff = (ls != ss && le_ != ss) ? 1u : 0u;
+        }
+        else
+            diff = (uint32_t)__popcll((mmy >> (2 * cp)) & vtn_mask2(mlen));
+        if (mlen == diff) vtype |= (mlen == 1) ? VTN_VT_SNP : VTN_VT_MNP;
+        if (rl != al) vtype |= VTN_VT_INDEL;
+        if (diff && diff < mlen) vtype |= VTN_VT_CLUMPED;
+        if (len0 == len1 && len0 > 1) vtype |= VTN_VT_MNP;
+    }
+    o.vtype = vtype;
+    o.T = o.le = o.lt = 0;
+    o.status = 0;
+    o.nlr = o.nla = 0;
+    o.newR = o.newA = 0;
+    if (vtype == VTN_VT_SNP) return true; // no REF check (normalize.cpp:205); a pure SNP is always normalized
+
+    // ---- reference windows and REF check (variant_manip.cpp:61-103) ----
+    const uint64_t gbase = __ldg(R.contig_goff + rid) << 5;
+    uint64_t V, W;
+    uint32_t ev, nw;
+    vtn_ref_window64(R, gbase + (uint64_t)(p0 - 32), V, W, ev, nw);
+    if (nw & (uint32_t)(len0 >= 32 ? 0xffffffffu : ((1u << len0) - 1u))) return false; // N / lower-case under REF
+    if ((W ^ Rc) & vtn_mask2(len0))
+    {
+        o.status = 2; // both sides are plain ACGT, so any mismatch is code 2
+        return true;
+    }
+    // ---- is_normalized (variant_manip.cpp:109-197) ----
+    if (same || (len0 == 1 && len1 == 1)) return true;
+    const bool exists_one = (m == 1);
+    const bool first_same = ((Rc ^ Ac) & 3ull) == 0;
+    const bool last_same = cs_raw >= 1;
+    if (!(last_same || (!exists_one && first_same))) return true;
+    o.status = VTN_ST_ENTERED;
+
+    // ---- right_trim_or_left_extend in closed form ----
+    uint32_t T;
+    if (cs_raw < m)
+        T = cs_raw;
+    else
+    {
+        // the shorter allele is a suffix of the longer one: the longer one's first D bases now face the
+        // reference bases left of POS ([p0-D, p0), the top D bases of V)
+        const uint32_t D = M - m;
+        const uint64_t X = len0 > len1 ? Rc : Ac;
+        const uint32_t dm = (D >= 32 ? 0xffffffffu : ((1u << D) - 1u));
+        if (ev & (dm << (32 - D))) return false; // N / IUPAC bases there
+        uint32_t e = vtn_top_match((X & vtn_mask2(D)) << (64 - 2 * D), V & ~vtn_mask2(32 - D));
+        if (e > D) e = D;
+        T = m + e;
+        if (e == D)
+        {
+            const int64_t cap64 = (int64_t)pos1 - 2 + (int64_t)m;
+            const uint32_t cap = cap64 > 0xffffffffll ? 0xffffffffu : (uint32_t)cap64;
+            T = lag_scan(R, gbase, clen, pos1, len0, len1, T, cap);
+        }
+    }
+    const uint32_t le = T >= m ? T - m + 1 : 0;
+    uint32_t lt = 0;
+    if (le == 0)
+    {
+        const uint32_t room = m - T - 1;
+        lt = cp_raw < room ? cp_raw : room;
+    }
+    o.T = T;
+    o.le = le;
+    o.lt = lt;
+    if (!(T | le | lt)) return true;
+    uint32_t cat; // normalize.cpp:254-311
+    if (le) cat = (T > le) ? 4 : 5;
+    else if (lt && T > le) cat = 3;
+    else if (lt) cat = 1;
+    else cat = 2;
+    o.status |= VTN_ST_CHANGED | (cat << VTN_ST_CAT_SHIFT);
+    // ---- new alleles as codes ----
+    if (le == 0)
+    {
+        o.nlr = len0 - T - lt;
+        o.nla = len1 - T - lt;
+        o.newR = (Rc >> (2 * lt)) & vtn_mask2(o.nlr);
+        o.newA = (Ac >> (2 * lt)) & vtn_mask2(o.nla);
+    }
+    else
+    {
+        // new allele i = (le reference bases [p0-le, p0) ++ allele_i)[0 : le + len_i - T]
+        const uint32_t D = M - m;
+        uint64_t Vl; // codes of [p0-le, p0-le+32)
+        uint32_t e2;
+        if (le <= 32)
+        {
+            Vl = le == 32 ? V : (V >> (2 * (32 - le))); // only the low le bases are reference; the rest is overlaid below
+            e2 = le == 32 ? ev : (ev >> (32 - le));
+        }
+        else
+            vtn_ref_window32(R, gbase + (uint64_t)(p0 - (int64_t)le), Vl, e2);
+        // the shift may have run through N / IUPAC bases (they compare like any base): those cannot be codes
+        if (e2 & (D + 1 >= 32 ? 0xffffffffu : ((1u << (D + 1)) - 1u))) return false;
+        const uint64_t X = len0 > len1 ? Rc : Ac;
+        uint64_t lg; // the longer allele's new form, D+1 bases
+        if (T < M && le < 32)
+            lg = (Vl & vtn_mask2(le)) | ((X & vtn_mask2(M - T)) << (2 * le));
+        else
+            lg = Vl;
+        lg &= vtn_mask2(D + 1);
+        const uint64_t shn = Vl & 3ull; // the shorter allele's new form: the single anchor base
+        if (D + 1 > 32) return false;   // cannot happen (D <= 31), keeps the compiler honest
+        if (len0 > len1) { o.newR = lg; o.nlr = D + 1; o.newA = shn; o.nla = 1; }
+        else { o.newA = lg; o.nla = D + 1; o.newR = shn; o.nlr = 1; }
+    }
+    return true;
 }
 
 // The whole per-record computation except writing the new alleles.
@@ -262,52 +480,7 @@ __device__ void normalize_record(const VtnDevRef& R, const VtnDevBatchView& B, u
         if (n == 2)
         {
             const uint32_t len1 = __ldg(B.allele_off + ab + 2) - off1;
-            // 32-base chunks, descending: window of stream s ends (inclusive) at hi_s = pos1-2-T+len_s
-            while (T < cap)
-            {
-                int64_t hi0 = (int64_t)pos1 - 2 - (int64_t)T + (int64_t)len0;
-                int64_t hi1 = (int64_t)pos1 - 2 - (int64_t)T + (int64_t)len1;
-                int64_t lo = (hi0 < hi1 ? hi0 : hi1) - 31, hi = hi0 > hi1 ? hi0 : hi1;
-                bool fast = lo >= 0 && hi < clen;
-                uint32_t nm = 0;
-                if (fast)
-                {
-                    uint64_t c0, c1;
-                    uint32_t e0, e1;
-                    vtn_ref_window32(R, gbase + (uint64_t)(hi0 - 31), c0, e0);
-                    vtn_ref_window32(R, gbase + (uint64_t)(hi1 - 31), c1, e1);
-                    if ((e0 | e1) == 0)
-                    {
-                        uint64_t x = c0 ^ c1;
-                        uint64_t mm = (x | (x >> 1)) & 0x5555555555555555ull;
-                        nm = mm ? (uint32_t)(__clzll((long long)mm) >> 1) : 32u;
-                    }
-                    else
-                        fast = false;
-                }
-                if (fast)
-                {
-                    uint32_t room = cap - T;
-                    if (nm >= room) { T = cap; break; }
-                    T += nm;
-                    if (nm < 32) break;
-                }
-                else
-                {
-                    // per-base for up to 32 steps (contig edge, or N / IUPAC bases in the window)
-                    uint32_t steps = 0;
-                    bool mism = false;
-                    while (T < cap && steps < 32)
-                    {
-                        uint8_t c0 = ext_byte(R, cur, gbase, clen, pos1, a0, len0, T);
-                        uint8_t c1 = ext_byte(R, cur, gbase, clen, pos1, a0, len1, T); // k >= len: pointer unused
-                        if (c0 != c1) { mism = true; break; }
-                        ++T;
-                        ++steps;
-                    }
-                    if (mism) break;
-                }
-            }
+            T = lag_scan(R, gbase, clen, pos1, len0, len1, T, cap);
         }
         else
         {
@@ -372,87 +545,208 @@ __device__ void normalize_record(const VtnDevRef& R, const VtnDevBatchView& B, u
 namespace
 {
 
+// Per-tile shared state.  Phase 1: every thread reads its record header and settles SNVs on the spot; other
+// records are queued.  Phase 2: queued records are processed DENSELY (lane i takes queue entry i), fast path
+// first, generic path for what it refuses.  Phase 3: block scan + look-back, then the changed records of
+// the tile are written by consecutive threads so that every output array is written coalesced.
+struct TileSmem
+{
+    uint64_t newR[VTN_TILE], newA[VTN_TILE];
+    uint32_t T[VTN_TILE], le[VTN_TILE], lt[VTN_TILE], nbytes[VTN_TILE], ob[VTN_TILE];
+    uint16_t queue[VTN_TILE], gqueue[VTN_TILE], cqueue[VTN_TILE];
+    uint8_t status[VTN_TILE], vtype[VTN_TILE], nlr[VTN_TILE], nla[VTN_TILE], fast[VTN_TILE];
+    uint32_t wcnt[VTN_TILE / 32], wbytes[VTN_TILE / 32];
+    unsigned long long base[2];
+    uint32_t counters[12];
+    uint32_t tile, nq, ngq;
+};
+
+__device__ __forceinline__ uint32_t warp_push(uint32_t* counter, bool pred, int lane)
+{
+    // warp-aggregated append: returns this lane's slot (valid when pred)
+    unsigned m = __ballot_sync(0xffffffffu, pred);
+    uint32_t base = 0;
+    if (lane == 0 && m) base = atomicAdd(counter, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    return base + __popc(m & ((1u << lane) - 1u));
+}
+
 __global__ void __launch_bounds__(VTN_TILE) vtn_normalize_kernel(VtnDevRef R, VtnDevBatchView B, VtnDevNormOut O,
                                                                  unsigned long long* tile_state, uint32_t* tile_counter,
                                                                  uint32_t n_tiles)
 {
-    __shared__ uint32_t s_tile;
-    __shared__ uint32_t s_wcnt[VTN_TILE / 32];
-    __shared__ uint32_t s_wbytes[VTN_TILE / 32];
-    __shared__ unsigned long long s_base[2];
-    __shared__ uint32_t s_counters[12];
+    __shared__ TileSmem S;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid < 12) s_counters[tid] = 0;
-
+    if (tid < 12) S.counters[tid] = 0;
     unsigned long long* st_cnt = tile_state;
     unsigned long long* st_bytes = tile_state + n_tiles;
 
     for (;;)
     {
-        __syncthreads(); // protects s_tile / s_w* / s_base reuse across iterations
-        if (tid == 0) s_tile = atomicAdd(tile_counter, 1u);
         __syncthreads();
-        const uint32_t tile = s_tile;
+        if (tid == 0)
+        {
+            S.tile = atomicAdd(tile_counter, 1u);
+            S.nq = 0;
+            S.ngq = 0;
+        }
+        __syncthreads();
+        const uint32_t tile = S.tile;
         if (tile >= n_tiles) break;
-        const uint32_t r = tile * VTN_TILE + tid;
+        const uint32_t r0 = tile * VTN_TILE;
+        const uint32_t r = r0 + tid;
         const bool live = r < B.n_rec;
 
-        RecResult res;
-        res.T = res.le = res.lt = res.nbytes = 0;
-        res.status = 0;
-        res.vtype = 0;
+        // ---------------- phase 1: headers, SNVs ----------------
+        uint32_t ab = 0, n = 0, off0 = 0, len0 = 0, len1 = 0;
+        bool queued = false;
+        uint8_t my_status = 0, my_vtype = 0;
         if (live)
         {
-            normalize_record(R, B, r, res);
-            O.status[r] = res.status;
-            O.vtype[r] = res.vtype;
+            ab = __ldg(B.allele_beg + r);
+            n = __ldg(B.allele_beg + r + 1) - ab;
+            off0 = __ldg(B.allele_off + ab);
+            const uint32_t off1 = __ldg(B.allele_off + ab + 1);
+            len0 = off1 - off0;
+            queued = true;
+            if (n == 2)
+            {
+                len1 = __ldg(B.allele_off + ab + 2) - off1;
+                if (len0 == 1 && len1 == 1)
+                {
+                    const uint8_t r0b = B.bytes[off0], c = B.bytes[off0 + 1];
+                    if (c != '<' && c != '[' && c != ']' && c != '.' && c != r0b)
+                    {
+                        my_vtype = VTN_VT_SNP; // variant_manip.cpp:462-465 with mlen == diff == 1; never REF-checked
+                        queued = false;
+                    }
+                }
+            }
         }
-        const bool changed = live && (res.status & VTN_ST_CHANGED);
-
-        // counters (warp-aggregated): 10 categories + no_variants / no_refs
+        S.T[tid] = 0;
+        S.le[tid] = 0;
+        S.lt[tid] = 0;
+        S.nbytes[tid] = 0;
+        S.fast[tid] = 0;
         {
-            uint32_t cat = changed ? (res.status >> VTN_ST_CAT_SHIFT) : 0;
-            uint32_t nall = live ? (__ldg(B.allele_beg + r + 1) - __ldg(B.allele_beg + r)) : 0;
-            uint32_t slot = cat ? ((nall == 2 ? 0u : 5u) + cat - 1u) : 0xffu;
+            const uint32_t slot = warp_push(&S.nq, queued, lane);
+            if (queued) S.queue[slot] = (uint16_t)tid;
+        }
+        if (!queued)
+        {
+            S.status[tid] = my_status;
+            S.vtype[tid] = my_vtype;
+        }
+        __syncthreads();
+
+        // ---------------- phase 2a: queued records, fast path, dense lanes ----------------
+        const uint32_t nq = S.nq;
+        for (uint32_t q = tid; q < ((nq + 31u) & ~31u); q += VTN_TILE)
+        {
+            bool generic = false;
+            uint32_t t = 0;
+            if (q < nq)
+            {
+                t = S.queue[q];
+                const uint32_t rr = r0 + t;
+                const uint32_t ab2 = __ldg(B.allele_beg + rr);
+                const uint32_t n2 = __ldg(B.allele_beg + rr + 1) - ab2;
+                generic = true;
+                if (n2 == 2)
+                {
+                    const uint32_t o0 = __ldg(B.allele_off + ab2), o1 = __ldg(B.allele_off + ab2 + 1), o2 = __ldg(B.allele_off + ab2 + 2);
+                    VtnFastRes f;
+                    if (fast_biallelic(R, B.bytes, o0, o1 - o0, o2 - o1, __ldg(B.pos1 + rr), __ldg(B.rid + rr), f))
+                    {
+                        generic = false;
+                        S.status[t] = (uint8_t)f.status;
+                        S.vtype[t] = (uint8_t)f.vtype;
+                        S.T[t] = f.T;
+                        S.le[t] = f.le;
+                        S.lt[t] = f.lt;
+                        S.nbytes[t] = f.nlr + f.nla;
+                        S.newR[t] = f.newR;
+                        S.newA[t] = f.newA;
+                        S.nlr[t] = (uint8_t)f.nlr;
+                        S.nla[t] = (uint8_t)f.nla;
+                        S.fast[t] = 1;
+                    }
+                }
+            }
+            const uint32_t slot = warp_push(&S.ngq, generic, lane);
+            if (generic) S.gqueue[slot] = (uint16_t)t;
+        }
+        __syncthreads();
+        // ---------------- phase 2b: what the fast path refused, generic byte-wise path ----------------
+        const uint32_t ngq = S.ngq;
+        for (uint32_t q = tid; q < ngq; q += VTN_TILE)
+        {
+            const uint32_t t = S.gqueue[q];
+            RecResult res;
+            normalize_record(R, B, r0 + t, res);
+            S.status[t] = res.status;
+            S.vtype[t] = res.vtype;
+            S.T[t] = res.T;
+            S.le[t] = res.le;
+            S.lt[t] = res.lt;
+            S.nbytes[t] = res.nbytes;
+        }
+        __syncthreads();
+
+        // ---------------- phase 3: per-record outputs, counters, ordered compaction ----------------
+        my_status = S.status[tid];
+        my_vtype = S.vtype[tid];
+        if (live)
+        {
+            O.status[r] = my_status;
+            O.vtype[r] = my_vtype;
+        }
+        const bool changed = live && (my_status & VTN_ST_CHANGED);
+        {
+            const uint32_t cat = changed ? (my_status >> VTN_ST_CAT_SHIFT) : 0;
+            const uint32_t slot = cat ? ((n == 2 ? 0u : 5u) + cat - 1u) : 0xffu;
             unsigned any = __ballot_sync(0xffffffffu, cat != 0);
             while (any)
             {
-                int leader = __ffs(any) - 1;
-                uint32_t ls = __shfl_sync(0xffffffffu, slot, leader);
-                unsigned peers = __ballot_sync(0xffffffffu, slot == ls);
-                if (lane == leader) atomicAdd(&s_counters[ls], __popc(peers));
+                const int leader = __ffs(any) - 1;
+                const uint32_t ls = __shfl_sync(0xffffffffu, slot, leader);
+                const unsigned peers = __ballot_sync(0xffffffffu, slot == ls);
+                if (lane == leader) atomicAdd(&S.counters[ls], __popc(peers));
                 any &= ~peers;
             }
-            unsigned refs = __ballot_sync(0xffffffffu, live && res.vtype == VTN_VT_REF);
-            unsigned vars = __ballot_sync(0xffffffffu, live && res.vtype != VTN_VT_REF);
+            const unsigned refs = __ballot_sync(0xffffffffu, live && my_vtype == VTN_VT_REF);
+            const unsigned vars = __ballot_sync(0xffffffffu, live && my_vtype != VTN_VT_REF);
             if (lane == 0)
             {
-                if (vars) atomicAdd(&s_counters[10], __popc(vars));
-                if (refs) atomicAdd(&s_counters[11], __popc(refs));
+                if (vars) atomicAdd(&S.counters[10], __popc(vars));
+                if (refs) atomicAdd(&S.counters[11], __popc(refs));
             }
         }
-
-        // block exclusive scan of (changed, nbytes)
-        uint32_t c = changed ? 1u : 0u, nb = res.nbytes;
+        const uint32_t c = changed ? 1u : 0u, nb = changed ? S.nbytes[tid] : 0u;
         uint32_t ic = c, ib = nb;
+#pragma unroll
         for (int o = 1; o < 32; o <<= 1)
         {
-            uint32_t tc = __shfl_up_sync(0xffffffffu, ic, o);
-            uint32_t tb = __shfl_up_sync(0xffffffffu, ib, o);
+            const uint32_t tc = __shfl_up_sync(0xffffffffu, ic, o);
+            const uint32_t tb = __shfl_up_sync(0xffffffffu, ib, o);
             if (lane >= o) { ic += tc; ib += tb; }
         }
-        if (lane == 31) { s_wcnt[warp] = ic; s_wbytes[warp] = ib; }
+        if (lane == 31) { S.wcnt[warp] = ic; S.wbytes[warp] = ib; }
         __syncthreads();
         uint32_t wc = 0, wb = 0, tot_c = 0, tot_b = 0;
 #pragma unroll
         for (int w = 0; w < VTN_TILE / 32; ++w)
         {
-            uint32_t xc = s_wcnt[w], xb = s_wbytes[w];
+            const uint32_t xc = S.wcnt[w], xb = S.wbytes[w];
             if (w < warp) { wc += xc; wb += xb; }
             tot_c += xc;
             tot_b += xb;
         }
-        // publish aggregate, look back, publish inclusive (warp 0)
+        if (changed)
+        {
+            S.cqueue[wc + ic - 1] = (uint16_t)tid; // rank inside the tile, input order
+            S.ob[tid] = wb + ib - nb;
+        }
         if (warp == 0)
         {
             if (lane == 0)
@@ -473,8 +767,8 @@ __global__ void __launch_bounds__(VTN_TILE) vtn_normalize_kernel(VtnDevRef R, Vt
             }
             if (lane == 0)
             {
-                s_base[0] = pc;
-                s_base[1] = pb;
+                S.base[0] = pc;
+                S.base[1] = pb;
                 if (tile == n_tiles - 1)
                 {
                     O.totals[0] = pc + tot_c;
@@ -484,52 +778,68 @@ __global__ void __launch_bounds__(VTN_TILE) vtn_normalize_kernel(VtnDevRef R, Vt
             }
         }
         __syncthreads();
-        if (changed)
+        // ---------------- phase 3b: changed records, one per consecutive thread ----------------
+        for (uint32_t i = tid; i < tot_c; i += VTN_TILE)
         {
-            const unsigned long long k = s_base[0] + wc + (ic - c);
-            const unsigned long long ob = s_base[1] + wb + (ib - nb);
-            O.chg_rec[k] = r;
-            O.chg_pos1[k] = __ldg(B.pos1 + r) - (int32_t)res.le + (int32_t)res.lt;
-            O.chg_lt[k] = res.lt;
-            O.chg_le[k] = res.le;
-            O.chg_rt[k] = res.T;
+            const uint32_t t = S.cqueue[i];
+            const uint32_t rr = r0 + t;
+            const unsigned long long k = S.base[0] + i;
+            const unsigned long long ob = S.base[1] + S.ob[t];
+            const int32_t pos1 = __ldg(B.pos1 + rr);
+            const uint32_t T = S.T[t], le = S.le[t], lt = S.lt[t];
+            O.chg_rec[k] = rr;
+            O.chg_pos1[k] = pos1 - (int32_t)le + (int32_t)lt;
+            O.chg_lt[k] = lt;
+            O.chg_le[k] = le;
+            O.chg_rt[k] = T;
             O.chg_off[k] = ob;
-            // new alleles: (le reference bases + upper(allele))[0 : le + len - T], or upper(allele)[lt : len - T]
-            const uint32_t ab = __ldg(B.allele_beg + r);
-            const uint32_t n = __ldg(B.allele_beg + r + 1) - ab;
-            const int32_t pos1 = __ldg(B.pos1 + r);
-            const int32_t rid = __ldg(B.rid + r);
-            const uint64_t gbase = __ldg(R.contig_goff + rid) << 5;
-            const int64_t clen = __ldg(R.contig_len + rid);
             uint8_t* dst = O.chg_bytes + ob;
-            VtnRefCursor cur;
-            uint32_t o = __ldg(B.allele_off + ab);
-            for (uint32_t i = 0; i < n; ++i)
+            if (S.fast[t])
             {
-                const uint32_t o2 = __ldg(B.allele_off + ab + i + 1);
-                const uint32_t len = o2 - o;
-                const uint32_t newlen = len + res.le - res.T - res.lt;
-                const uint8_t* a = B.bytes + o;
-                for (uint32_t j = 0; j < newlen; ++j)
+                uint64_t a = S.newR[t];
+                const uint32_t l0 = S.nlr[t], l1 = S.nla[t];
+                for (uint32_t j = 0; j < l0; ++j, a >>= 2) dst[j] = (uint8_t)(0x47544341u >> (8 * ((uint32_t)a & 3u)));
+                a = S.newA[t];
+                dst += l0;
+                for (uint32_t j = 0; j < l1; ++j, a >>= 2) dst[j] = (uint8_t)(0x47544341u >> (8 * ((uint32_t)a & 3u)));
+            }
+            else
+            {
+                // generic: (le reference bases + upper(allele))[0 : le + len - T], or upper(allele)[lt : len - T]
+                const uint32_t ab2 = __ldg(B.allele_beg + rr);
+                const uint32_t n2 = __ldg(B.allele_beg + rr + 1) - ab2;
+                const int32_t rid = __ldg(B.rid + rr);
+                const uint64_t gbase = __ldg(R.contig_goff + rid) << 5;
+                const int64_t clen = __ldg(R.contig_len + rid);
+                VtnRefCursor cur;
+                uint32_t o = __ldg(B.allele_off + ab2);
+                for (uint32_t ai = 0; ai < n2; ++ai)
                 {
-                    uint8_t ch;
-                    if (j < res.le)
+                    const uint32_t o2 = __ldg(B.allele_off + ab2 + ai + 1);
+                    const uint32_t len = o2 - o;
+                    const uint32_t newlen = len + le - T - lt;
+                    const uint8_t* a = B.bytes + o;
+                    for (uint32_t j = 0; j < newlen; ++j)
                     {
-                        int64_t p0 = (int64_t)pos1 - 1 - (int64_t)res.le + (int64_t)j;
-                        p0 = p0 < 0 ? 0 : (p0 >= clen ? clen - 1 : p0);
-                        ch = cur.uc(R, gbase + (uint64_t)p0);
+                        uint8_t ch;
+                        if (j < le)
+                        {
+                            int64_t p0 = (int64_t)pos1 - 1 - (int64_t)le + (int64_t)j;
+                            p0 = p0 < 0 ? 0 : (p0 >= clen ? clen - 1 : p0);
+                            ch = cur.uc(R, gbase + (uint64_t)p0);
+                        }
+                        else
+                            ch = vtn_toupper(a[j - le + lt]);
+                        dst[j] = ch;
                     }
-                    else
-                        ch = vtn_toupper(a[j - res.le + res.lt]);
-                    dst[j] = ch;
+                    dst += newlen;
+                    o = o2;
                 }
-                dst += newlen;
-                o = o2;
             }
         }
     }
     __syncthreads();
-    if (tid < 12 && s_counters[tid]) atomicAdd(O.counters + tid, s_counters[tid]);
+    if (tid < 12 && S.counters[tid]) atomicAdd(O.counters + tid, S.counters[tid]);
 }
 
 } // namespace

@@ -27,8 +27,8 @@ inline int base_code(uint8_t c)
     {
     case 'A': case 'a': return 0;
     case 'C': case 'c': return 1;
-    case 'G': case 'g': return 2;
-    case 'T': case 't': return 3;
+    case 'T': case 't': return 2; // (ascii >> 1) & 3, so allele bytes convert with one shift+mask
+    case 'G': case 'g': return 3;
     default: return -1;
     }
 }
@@ -198,10 +198,10 @@ int vtn_ref_load_memory(vtn_ctx* ctx, int32_t n_contig, const char* const* names
         k.name = names && names[c] ? names[c] : std::to_string(c);
         k.len = len[c];
         k.goff = n_groups;
-        n_groups += (uint64_t)((len[c] + 31) / 32) + 1; // +1 zero pad group: window loads may touch g+1
+        n_groups += (uint64_t)((len[c] + 31) / 32) + 2; // +2 zero pad groups: window loads may touch g+1, g+2
         ctx->contigs.push_back(k);
     }
-    n_groups += 1;
+    n_groups += 2;
     uint4* h_groups = nullptr;
     VTN_CUDA(ctx, cudaMallocHost(&h_groups, n_groups * sizeof(uint4)));
     memset(h_groups, 0, n_groups * sizeof(uint4));

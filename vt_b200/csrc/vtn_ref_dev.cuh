@@ -43,7 +43,7 @@ struct VtnRefCursor
         seek(R, gpos);
         uint32_t j = (uint32_t)gpos & 31u;
         uint32_t c = (uint32_t)(vtn_group_code(q) >> (2 * j)) & 3u;
-        uint8_t b = (uint8_t)((0x54474341u >> (8 * c)) & 0xff); // "ACGT"
+        uint8_t b = (uint8_t)((0x47544341u >> (8 * c)) & 0xff); // "ACTG": A=0 C=1 T=2 G=3 == (ascii >> 1) & 3
         if ((q.z >> j) & 1u)
         {
             if ((q.w >> j) & 1u) return b | 0x20;
@@ -57,7 +57,7 @@ struct VtnRefCursor
         seek(R, gpos);
         uint32_t j = (uint32_t)gpos & 31u;
         uint32_t c = (uint32_t)(vtn_group_code(q) >> (2 * j)) & 3u;
-        uint8_t b = (uint8_t)((0x54474341u >> (8 * c)) & 0xff);
+        uint8_t b = (uint8_t)((0x47544341u >> (8 * c)) & 0xff);
         if (((q.z & ~q.w) >> j) & 1u)
         {
             uint8_t e = vtn_exc_lookup(R, gpos);
