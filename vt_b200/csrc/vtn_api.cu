@@ -102,7 +102,7 @@ uint64_t vtn_launch_count(const vtn_ctx* ctx) { return ctx ? ctx->launches : 0; 
 template <typename T>
 static cudaError_t dalloc(T** p, size_t n)
 {
-    return cudaMalloc((void**)p, (n ? n : 1) * sizeof(T));
+    return cudaMalloc((void**)p, (n + 512) * sizeof(T)); // padded: tiles load whole 128-bit vectors
 }
 
 int vtn_dbatch_alloc(vtn_ctx* ctx, uint32_t n_rec, uint32_t n_allele, uint64_t n_bytes, bool with_inputs, vtn_dbatch** out)
@@ -138,6 +138,14 @@ int vtn_dbatch_alloc(vtn_ctx* ctx, uint32_t n_rec, uint32_t n_allele, uint64_t n
     A(dalloc(&d->chg_bytes, n_bytes + 16));
     A(dalloc(&d->totals, 4));
     A(dalloc(&d->counters, 16));
+    A(dalloc(&d->scr.rec, n_rec));
+    A(dalloc(&d->scr.pos1, n_rec));
+    A(dalloc(&d->scr.lt, n_rec));
+    A(dalloc(&d->scr.le, n_rec));
+    A(dalloc(&d->scr.rt, n_rec));
+    A(dalloc(&d->scr.ob, n_rec));
+    A(dalloc(&d->scr.bytes, n_bytes + 16));
+    A(dalloc(&d->scr.dir, (size_t)d->n_tiles));
     A(dalloc(&d->tile_state, 2 * (size_t)d->n_tiles));
     A(dalloc(&d->tile_counter, 4));
 #undef A
@@ -172,6 +180,8 @@ int vtn_dbatch_destroy(vtn_ctx* ctx, vtn_dbatch* d)
     }
     cudaFree(d->status); cudaFree(d->vtype); cudaFree(d->chg_rec); cudaFree(d->chg_pos1); cudaFree(d->chg_lt);
     cudaFree(d->chg_le); cudaFree(d->chg_rt); cudaFree(d->chg_off); cudaFree(d->chg_bytes); cudaFree(d->totals);
+    cudaFree(d->scr.rec); cudaFree(d->scr.pos1); cudaFree(d->scr.lt); cudaFree(d->scr.le); cudaFree(d->scr.rt);
+    cudaFree(d->scr.ob); cudaFree(d->scr.bytes); cudaFree(d->scr.dir);
     cudaFree(d->counters); cudaFree(d->tile_state); cudaFree(d->tile_counter); cudaFree(d->src_rec); cudaFree(d->alt_idx);
     delete d;
     return VTN_OK;
@@ -219,7 +229,7 @@ int vtn_normalize_resident(vtn_ctx* ctx, vtn_dbatch* d)
     if (!ctx->ref_loaded) return vtn_set_err(ctx, VTN_E_STATE, "vtn_normalize: no reference loaded");
     VtnDevBatchView v{d->n_rec, d->pos1, d->rid, d->allele_beg, d->allele_off, d->bytes};
     VtnDevNormOut o{d->status, d->vtype, d->chg_rec, d->chg_pos1, d->chg_lt, d->chg_le, d->chg_rt, d->chg_off, d->chg_bytes, d->totals, d->counters};
-    return vtn_launch_normalize(ctx, v, o, d->tile_state, d->tile_counter, d->n_tiles);
+    return vtn_launch_normalize(ctx, v, o, d->scr, d->tile_state, d->tile_counter, d->n_tiles);
 }
 
 static int fetch_norm(vtn_ctx* ctx, vtn_dbatch* d, vtn_norm_result* out)

@@ -19,14 +19,14 @@ struct VtnFastRes
 
 __device__ __forceinline__ uint64_t vtn_mask2(uint32_t nbases) { return nbases >= 32 ? ~0ull : ((1ull << (2 * nbases)) - 1ull); }
 
-// 8 allele bytes starting at byte offset off (any alignment) of a 16-byte-padded array
+// 8 allele bytes starting at byte offset off (any alignment) of a 16-byte-padded array (global or staged in smem)
 __device__ __forceinline__ uint64_t vtn_fetch8(const uint8_t* bytes, uint32_t off)
 {
     const uint64_t* p = reinterpret_cast<const uint64_t*>(bytes + (off & ~7u));
-    uint64_t w0 = __ldg(p);
+    uint64_t w0 = *p;
     uint32_t s = (off & 7u) * 8u;
     if (s == 0) return w0;
-    uint64_t w1 = __ldg(p + 1);
+    uint64_t w1 = p[1];
     return (w0 >> s) | (w1 << (64 - s));
 }
 

@@ -61,6 +61,19 @@ struct VtnDevNormOut
     uint32_t* counters;  // [12]
 };
 
+// per-tile scratch segments written by K1, gathered by K2 (vtn_normalize.cu)
+struct VtnDevScratch
+{
+    uint32_t* rec;
+    int32_t* pos1;
+    uint32_t* lt;
+    uint32_t* le;
+    uint32_t* rt;
+    uint32_t* ob;             // byte offset of the record's new alleles inside its tile's byte window
+    uint8_t* bytes;           // [n_bytes] tile t owns the byte window of its records' old alleles
+    unsigned long long* dir;  // [n_tiles] (changed count << 32) | new allele bytes
+};
+
 struct vtn_dbatch
 {
     uint32_t n_rec = 0, n_allele = 0;
@@ -85,6 +98,7 @@ struct vtn_dbatch
     uint8_t* chg_bytes = nullptr;
     unsigned long long* totals = nullptr; // 2 (+ decompose: [2]=n_out)
     uint32_t* counters = nullptr;         // 12 normalize + 4 decompose
+    VtnDevScratch scr{};
     // scan state
     unsigned long long* tile_state = nullptr; // [2*n_tiles]
     uint32_t* tile_counter = nullptr;
@@ -133,7 +147,7 @@ int vtn_set_err(vtn_ctx* ctx, int code, const std::string& msg);
     } while (0)
 
 // kernels' host launchers (vtn_normalize.cu / vtn_decompose.cu)
-int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNormOut& out,
+int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNormOut& out, const VtnDevScratch& scr,
                          unsigned long long* tile_state, uint32_t* tile_counter, uint32_t n_tiles);
 uint32_t vtn_normalize_tile_records();
 int vtn_launch_decompose(vtn_ctx* ctx, vtn_dbatch* db, bool materialise);

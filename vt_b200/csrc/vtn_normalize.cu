@@ -1,21 +1,19 @@
 // vtn_normalize.cu -- the normalize kernel (sm_100a) and its launcher.
 //
-// One thread owns one record; a CTA owns a tile of VTN_TILE consecutive records, fetched from a global
-// tile counter (persistent CTAs).  Per record, in closed form instead of the reference's per-base loop:
+// One warp owns a tile of consecutive records, fetched from a global tile counter (persistent warps); see the
+// kernel comment below.  Per record, in closed form instead of the reference's per-base loop:
 //   classify_variant          variant_manip.cpp:227-508
 //   is_not_ref_consistent     variant_manip.cpp:61-103      (skipped iff type == VT_SNP, normalize.cpp:205)
 //   is_normalized             variant_manip.cpp:109-197
 //   right_trim_or_left_extend variant_manip.cpp:513-583  ->  T = longest common suffix of E_i = prefix+allele_i
 //   left_trim                 variant_manip.cpp:588-615
 //   counters                  normalize.cpp:254-322
-// Changed records are compacted in input order with a single-pass (decoupled look-back) scan over tiles of
-// two quantities: number of changed records and bytes of their new alleles.
+// Changed records are compacted in input order: per-tile scratch segments (K1) + scan/gather (K2).
 #include "vtn_internal.h"
 #include "vtn_ref_dev.cuh"
 #include "vtn_scan.cuh"
 #include "vtn_fast.cuh"
 
-#define VTN_TILE 256
 
 namespace
 {
@@ -141,7 +139,7 @@ __device__ __forceinline__ uint8_t ext_byte(const VtnDevRef& R, VtnRefCursor& cu
 // (T >= max len), so both streams read the reference, at a lag of |len0-len1| bases.  Walks down in 32-base
 // chunks (two packed windows, XOR, clz); per base only at contig edges or over N/IUPAC bases.
 // Returns the final T (<= cap).
-__device__ uint32_t lag_scan(const VtnDevRef& R, uint64_t gbase, int64_t clen, int32_t pos1, uint32_t len0, uint32_t len1,
+__device__ __noinline__ uint32_t lag_scan(const VtnDevRef& R, uint64_t gbase, int64_t clen, int32_t pos1, uint32_t len0, uint32_t len1,
                              uint32_t T, uint32_t cap)
 {
     VtnRefCursor cur;
@@ -355,7 +353,7 @@ __device__ bool fast_biallelic(const VtnDevRef& R, const uint8_t* bytes, uint32_
 }
 
 // The whole per-record computation except writing the new alleles.
-__device__ void normalize_record(const VtnDevRef& R, const VtnDevBatchView& B, uint32_t r, RecResult& out)
+__device__ __noinline__ void normalize_record(const VtnDevRef& R, const VtnDevBatchView& B, uint32_t r, RecResult& out)
 {
     const uint32_t ab = __ldg(B.allele_beg + r);
     const uint32_t n = __ldg(B.allele_beg + r + 1) - ab;
@@ -545,323 +543,408 @@ __device__ void normalize_record(const VtnDevRef& R, const VtnDevBatchView& B, u
 namespace
 {
 
-// Per-tile shared state.  Phase 1: every thread reads its record header and settles SNVs on the spot; other
-// records are queued.  Phase 2: queued records are processed DENSELY (lane i takes queue entry i), fast path
-// first, generic path for what it refuses.  Phase 3: block scan + look-back, then the changed records of
-// the tile are written by consecutive threads so that every output array is written coalesced.
-struct TileSmem
+// ---------------------------------------------------------------------------------------------------------
+// K1  vtn_normalize_kernel: every WARP owns a tile of VTN_WTILE = 32 * VTN_RPL consecutive records and never
+//     waits for another warp or tile (no __syncthreads, no inter-tile dependency):
+//   phase 1  lane l owns records l*RPL .. l*RPL+RPL-1 of the tile: 128-bit loads of allele_beg; the tile's
+//            allele_off window and allele byte window are staged in shared memory with coalesced 128-bit
+//            loads; SNVs (80% of a real call set) are settled here; the rest is queued in record order.
+//   phase 2  queued records are processed densely (lane i <- queue entry 32p+i): 2-bit register fast path,
+//            generic byte-wise path for what it refuses.  Changed records are ranked with a warp scan (queue
+//            order == record order) and written straight from registers to the tile's own scratch segment
+//            (scratch index tile*WTILE + rank; new allele bytes inside the tile's old byte window, which they
+//            can never outgrow).  The tile's (count, bytes) go to the tile directory.
+//   phase 3  status / vtype of the tile as one 4-byte store per lane; counters stay in registers.
+// K2  vtn_compact_kernel: single-pass scan (decoupled look-back over blocks of 256 tiles; all aggregates are
+//     known up front so nobody waits on compute) of the tile directory + gather of the scratch segments
+//     into the final chg_* arrays, in input order.
+// ---------------------------------------------------------------------------------------------------------
+#define VTN_RPL 4
+#define VTN_WTILE (32 * VTN_RPL)
+#define VTN_WARPS 4
+#define VTN_AOFF_CAP (VTN_WTILE * 3 + 16)
+#define VTN_BYTES_CAP (VTN_WTILE * 8 + 64)
+
+struct __align__(16) WarpSmem
 {
-    uint64_t newR[VTN_TILE], newA[VTN_TILE];
-    uint32_t T[VTN_TILE], le[VTN_TILE], lt[VTN_TILE], nbytes[VTN_TILE], ob[VTN_TILE];
-    uint16_t queue[VTN_TILE], gqueue[VTN_TILE], cqueue[VTN_TILE];
-    uint8_t status[VTN_TILE], vtype[VTN_TILE], nlr[VTN_TILE], nla[VTN_TILE], fast[VTN_TILE];
-    uint32_t wcnt[VTN_TILE / 32], wbytes[VTN_TILE / 32];
-    unsigned long long base[2];
-    uint32_t counters[12];
-    uint32_t tile, nq, ngq;
+    uint32_t aoff[VTN_AOFF_CAP];
+    uint8_t bytes[VTN_BYTES_CAP];
+    uint8_t queue[VTN_WTILE];
+    uint8_t st[VTN_WTILE], vt[VTN_WTILE];
 };
 
-__device__ __forceinline__ uint32_t warp_push(uint32_t* counter, bool pred, int lane)
+__device__ __forceinline__ uint32_t warp_excl_scan(uint32_t v, int lane, uint32_t& total)
 {
-    // warp-aggregated append: returns this lane's slot (valid when pred)
-    unsigned m = __ballot_sync(0xffffffffu, pred);
-    uint32_t base = 0;
-    if (lane == 0 && m) base = atomicAdd(counter, __popc(m));
-    base = __shfl_sync(0xffffffffu, base, 0);
-    return base + __popc(m & ((1u << lane) - 1u));
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+    {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    total = __shfl_sync(0xffffffffu, inc, 31);
+    return inc - v;
 }
 
-__global__ void __launch_bounds__(VTN_TILE) vtn_normalize_kernel(VtnDevRef R, VtnDevBatchView B, VtnDevNormOut O,
-                                                                 unsigned long long* tile_state, uint32_t* tile_counter,
-                                                                 uint32_t n_tiles)
+// new alleles of a record handled by the generic path: (le reference bases + upper(allele))[0 : le + len - T],
+// or upper(allele)[lt : len - T]  (normalize.cpp:246-252 after variant_manip.cpp:513-615)
+__device__ __noinline__ void write_generic_alleles(const VtnDevRef& R, const VtnDevBatchView& B, uint32_t rr, uint32_t T, uint32_t le,
+                                      uint32_t lt, uint8_t* dst)
 {
-    __shared__ TileSmem S;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid < 12) S.counters[tid] = 0;
-    unsigned long long* st_cnt = tile_state;
-    unsigned long long* st_bytes = tile_state + n_tiles;
-
-    for (;;)
+    const uint32_t ab2 = __ldg(B.allele_beg + rr);
+    const uint32_t n2 = __ldg(B.allele_beg + rr + 1) - ab2;
+    const int32_t pos1 = __ldg(B.pos1 + rr);
+    const int32_t rid = __ldg(B.rid + rr);
+    const uint64_t gbase = __ldg(R.contig_goff + rid) << 5;
+    const int64_t clen = __ldg(R.contig_len + rid);
+    VtnRefCursor cur;
+    uint32_t o = __ldg(B.allele_off + ab2);
+    for (uint32_t ai = 0; ai < n2; ++ai)
     {
-        __syncthreads();
-        if (tid == 0)
+        const uint32_t o2 = __ldg(B.allele_off + ab2 + ai + 1);
+        const uint32_t len = o2 - o;
+        const uint32_t newlen = len + le - T - lt;
+        const uint8_t* a = B.bytes + o;
+        for (uint32_t j = 0; j < newlen; ++j)
         {
-            S.tile = atomicAdd(tile_counter, 1u);
-            S.nq = 0;
-            S.ngq = 0;
-        }
-        __syncthreads();
-        const uint32_t tile = S.tile;
-        if (tile >= n_tiles) break;
-        const uint32_t r0 = tile * VTN_TILE;
-        const uint32_t r = r0 + tid;
-        const bool live = r < B.n_rec;
-
-        // ---------------- phase 1: headers, SNVs ----------------
-        uint32_t ab = 0, n = 0, off0 = 0, len0 = 0, len1 = 0;
-        bool queued = false;
-        uint8_t my_status = 0, my_vtype = 0;
-        if (live)
-        {
-            ab = __ldg(B.allele_beg + r);
-            n = __ldg(B.allele_beg + r + 1) - ab;
-            off0 = __ldg(B.allele_off + ab);
-            const uint32_t off1 = __ldg(B.allele_off + ab + 1);
-            len0 = off1 - off0;
-            queued = true;
-            if (n == 2)
+            uint8_t ch;
+            if (j < le)
             {
-                len1 = __ldg(B.allele_off + ab + 2) - off1;
-                if (len0 == 1 && len1 == 1)
+                int64_t p0 = (int64_t)pos1 - 1 - (int64_t)le + (int64_t)j;
+                p0 = p0 < 0 ? 0 : (p0 >= clen ? clen - 1 : p0);
+                ch = cur.uc(R, gbase + (uint64_t)p0);
+            }
+            else
+                ch = vtn_toupper(a[j - le + lt]);
+            dst[j] = ch;
+        }
+        dst += newlen;
+        o = o2;
+    }
+}
+
+__global__ void __launch_bounds__(32 * VTN_WARPS) vtn_normalize_kernel(VtnDevRef R, VtnDevBatchView B, VtnDevNormOut O, VtnDevScratch X,
+                                                                      uint32_t* tile_counter, uint32_t n_tiles)
+{
+    __shared__ WarpSmem SM[VTN_WARPS];
+    const int lane = threadIdx.x & 31;
+    WarpSmem& S = SM[threadIdx.x >> 5];
+    uint32_t my_counter = 0; // lane k < 12 accumulates counter k of this warp
+
+    uint32_t tile = 0;
+    if (lane == 0) tile = atomicAdd(tile_counter, 1u);
+    tile = __shfl_sync(0xffffffffu, tile, 0);
+    while (tile < n_tiles)
+    {
+        // grab the next tile id now so that the atomic's latency overlaps this tile's work
+        uint32_t next_tile = 0;
+        if (lane == 0) next_tile = atomicAdd(tile_counter, 1u);
+
+        const uint32_t r0 = tile * VTN_WTILE;
+        const uint32_t n_live = min((uint32_t)VTN_WTILE, B.n_rec - r0);
+        // ---------------- phase 1 ----------------
+        uint32_t ab[VTN_RPL + 1];
+        {
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(B.allele_beg + r0) + lane); // arrays are padded
+            ab[0] = v.x; ab[1] = v.y; ab[2] = v.z; ab[3] = v.w;
+            uint32_t nxt = __shfl_down_sync(0xffffffffu, v.x, 1);
+            if (lane == 31) nxt = __ldg(B.allele_beg + r0 + VTN_WTILE);
+            ab[4] = nxt;
+        }
+        const uint32_t s_lo = __shfl_sync(0xffffffffu, ab[0], 0);
+        const uint32_t s_hi = __ldg(B.allele_beg + r0 + n_live); // one past the last live record's slots
+        // stage allele_off[s_lo .. s_hi]
+        const uint32_t a0 = s_lo & ~3u;
+        const bool aoff_staged = (s_hi + 1 - a0) <= VTN_AOFF_CAP;
+        if (aoff_staged)
+        {
+            for (uint32_t i = lane * 4; i < s_hi + 1 - a0; i += 128)
+                *reinterpret_cast<uint4*>(&S.aoff[i]) = __ldg(reinterpret_cast<const uint4*>(B.allele_off + a0 + i));
+        }
+        __syncwarp();
+#define AO(slot) (aoff_staged ? S.aoff[(slot) - a0] : __ldg(B.allele_off + (slot)))
+        const uint32_t b_lo = AO(s_lo), b_hi = AO(s_hi);
+        const uint32_t b0 = b_lo & ~15u;
+        const bool bytes_staged = (b_hi + 16 - b0) <= VTN_BYTES_CAP;
+        if (bytes_staged)
+        {
+            for (uint32_t i = lane * 16; i < b_hi + 16 - b0; i += 512)
+                *reinterpret_cast<uint4*>(&S.bytes[i]) = __ldg(reinterpret_cast<const uint4*>(B.bytes + b0 + i));
+        }
+        __syncwarp();
+        const uint8_t* BY = bytes_staged ? (S.bytes - b0) : B.bytes; // absolute offsets work on both
+
+        uint32_t qmask = 0;
+#pragma unroll
+        for (int j = 0; j < VTN_RPL; ++j)
+        {
+            const uint32_t idx = lane * VTN_RPL + j;
+            if (idx < n_live)
+            {
+                bool q = true;
+                if (ab[j + 1] - ab[j] == 2)
                 {
-                    const uint8_t r0b = B.bytes[off0], c = B.bytes[off0 + 1];
-                    if (c != '<' && c != '[' && c != ']' && c != '.' && c != r0b)
+                    const uint32_t o0 = AO(ab[j]), o2 = AO(ab[j] + 2);
+                    if (o2 - o0 == 2) // both alleles one byte
                     {
-                        my_vtype = VTN_VT_SNP; // variant_manip.cpp:462-465 with mlen == diff == 1; never REF-checked
-                        queued = false;
+                        const uint8_t r0b = BY[o0], c = BY[o0 + 1];
+                        q = (c == '<' || c == '[' || c == ']' || c == '.' || c == r0b);
                     }
                 }
+                if (q) qmask |= 1u << j;
             }
         }
-        S.T[tid] = 0;
-        S.le[tid] = 0;
-        S.lt[tid] = 0;
-        S.nbytes[tid] = 0;
-        S.fast[tid] = 0;
+        uint32_t nq;
         {
-            const uint32_t slot = warp_push(&S.nq, queued, lane);
-            if (queued) S.queue[slot] = (uint16_t)tid;
+            uint32_t slot = warp_excl_scan(__popc(qmask), lane, nq);
+#pragma unroll
+            for (int j = 0; j < VTN_RPL; ++j)
+                if (qmask & (1u << j)) S.queue[slot++] = (uint8_t)(lane * VTN_RPL + j);
         }
-        if (!queued)
-        {
-            S.status[tid] = my_status;
-            S.vtype[tid] = my_vtype;
-        }
-        __syncthreads();
+        __syncwarp();
 
-        // ---------------- phase 2a: queued records, fast path, dense lanes ----------------
-        const uint32_t nq = S.nq;
-        for (uint32_t q = tid; q < ((nq + 31u) & ~31u); q += VTN_TILE)
+        // ---------------- phase 2: dense passes over the queue ----------------
+        uint32_t tot_c = 0, tot_b = 0;
+        uint32_t cnt_vars = n_live - nq; // the SNVs settled in phase 1 (normalize.cpp:315-322)
+        uint32_t cnt_refs = 0;
+        for (uint32_t p = 0; p < nq; p += 32)
         {
-            bool generic = false;
-            uint32_t t = 0;
-            if (q < nq)
+            const uint32_t e = p + lane;
+            const bool act = e < nq;
+            uint32_t st = 0, vt = VTN_VT_SNP, T = 0, le = 0, lt = 0, nb = 0, n2 = 2, rr = 0;
+            int32_t pos1 = 0;
+            bool fast = false;
+            VtnFastRes f;
+            if (act)
             {
-                t = S.queue[q];
-                const uint32_t rr = r0 + t;
+                const uint32_t idx = S.queue[e];
+                rr = r0 + idx;
                 const uint32_t ab2 = __ldg(B.allele_beg + rr);
-                const uint32_t n2 = __ldg(B.allele_beg + rr + 1) - ab2;
-                generic = true;
+                n2 = __ldg(B.allele_beg + rr + 1) - ab2;
+                pos1 = __ldg(B.pos1 + rr);
                 if (n2 == 2)
                 {
-                    const uint32_t o0 = __ldg(B.allele_off + ab2), o1 = __ldg(B.allele_off + ab2 + 1), o2 = __ldg(B.allele_off + ab2 + 2);
-                    VtnFastRes f;
-                    if (fast_biallelic(R, B.bytes, o0, o1 - o0, o2 - o1, __ldg(B.pos1 + rr), __ldg(B.rid + rr), f))
-                    {
-                        generic = false;
-                        S.status[t] = (uint8_t)f.status;
-                        S.vtype[t] = (uint8_t)f.vtype;
-                        S.T[t] = f.T;
-                        S.le[t] = f.le;
-                        S.lt[t] = f.lt;
-                        S.nbytes[t] = f.nlr + f.nla;
-                        S.newR[t] = f.newR;
-                        S.newA[t] = f.newA;
-                        S.nlr[t] = (uint8_t)f.nlr;
-                        S.nla[t] = (uint8_t)f.nla;
-                        S.fast[t] = 1;
-                    }
+                    const uint32_t o0 = AO(ab2), o1 = AO(ab2 + 1), o2 = AO(ab2 + 2);
+                    fast = fast_biallelic(R, BY, o0, o1 - o0, o2 - o1, pos1, __ldg(B.rid + rr), f);
                 }
+                if (fast)
+                {
+                    st = f.status; vt = f.vtype; T = f.T; le = f.le; lt = f.lt; nb = f.nlr + f.nla;
+                }
+                else
+                {
+                    RecResult res;
+                    normalize_record(R, B, rr, res);
+                    st = res.status; vt = res.vtype; T = res.T; le = res.le; lt = res.lt; nb = res.nbytes;
+                }
+                S.st[idx] = (uint8_t)st;
+                S.vt[idx] = (uint8_t)vt;
             }
-            const uint32_t slot = warp_push(&S.ngq, generic, lane);
-            if (generic) S.gqueue[slot] = (uint16_t)t;
+            const uint32_t c = (st & VTN_ST_CHANGED) ? 1u : 0u;
+            uint32_t pc, pb;
+            const uint32_t ec = warp_excl_scan(c, lane, pc);
+            const uint32_t eb = warp_excl_scan(c ? nb : 0u, lane, pb);
+            if (c)
+            {
+                const uint32_t k = r0 + tot_c + ec;    // scratch slot: tile segment, rank in input order
+                const uint32_t obl = tot_b + eb;       // byte offset inside the tile's byte window
+                X.rec[k] = rr;
+                X.pos1[k] = pos1 - (int32_t)le + (int32_t)lt;
+                X.lt[k] = lt;
+                X.le[k] = le;
+                X.rt[k] = T;
+                X.ob[k] = obl;
+                uint8_t* dst = X.bytes + b_lo + obl;
+                if (fast)
+                {
+                    uint64_t a = f.newR;
+                    for (uint32_t j = 0; j < f.nlr; ++j, a >>= 2) dst[j] = (uint8_t)(0x47544341u >> (8 * ((uint32_t)a & 3u)));
+                    a = f.newA;
+                    dst += f.nlr;
+                    for (uint32_t j = 0; j < f.nla; ++j, a >>= 2) dst[j] = (uint8_t)(0x47544341u >> (8 * ((uint32_t)a & 3u)));
+                }
+                else
+                    write_generic_alleles(R, B, rr, T, le, lt, dst);
+            }
+            tot_c += pc;
+            tot_b += pb;
+            // counters: category by arity (normalize.cpp:254-311), refs / variants (:315-322)
+            const uint32_t cat = c ? (st >> VTN_ST_CAT_SHIFT) : 0u;
+            const uint32_t slot = cat ? ((n2 == 2 ? 0u : 5u) + cat - 1u) : 0xffu;
+#pragma unroll
+            for (uint32_t k = 0; k < 10; ++k)
+            {
+                const unsigned mk = __ballot_sync(0xffffffffu, slot == k);
+                if (lane == (int)k) my_counter += __popc(mk);
+            }
+            cnt_refs += __popc(__ballot_sync(0xffffffffu, act && vt == VTN_VT_REF));
+            cnt_vars += __popc(__ballot_sync(0xffffffffu, act && vt != VTN_VT_REF));
         }
-        __syncthreads();
-        // ---------------- phase 2b: what the fast path refused, generic byte-wise path ----------------
-        const uint32_t ngq = S.ngq;
-        for (uint32_t q = tid; q < ngq; q += VTN_TILE)
-        {
-            const uint32_t t = S.gqueue[q];
-            RecResult res;
-            normalize_record(R, B, r0 + t, res);
-            S.status[t] = res.status;
-            S.vtype[t] = res.vtype;
-            S.T[t] = res.T;
-            S.le[t] = res.le;
-            S.lt[t] = res.lt;
-            S.nbytes[t] = res.nbytes;
-        }
-        __syncthreads();
+        if (lane == 10) my_counter += cnt_vars;
+        if (lane == 11) my_counter += cnt_refs;
+        if (lane == 0) X.dir[tile] = ((unsigned long long)tot_c << 32) | tot_b;
+        __syncwarp();
 
-        // ---------------- phase 3: per-record outputs, counters, ordered compaction ----------------
-        my_status = S.status[tid];
-        my_vtype = S.vtype[tid];
-        if (live)
+        // ---------------- phase 3: status / vtype as one 4-byte store per lane ----------------
         {
-            O.status[r] = my_status;
-            O.vtype[r] = my_vtype;
-        }
-        const bool changed = live && (my_status & VTN_ST_CHANGED);
-        {
-            const uint32_t cat = changed ? (my_status >> VTN_ST_CAT_SHIFT) : 0;
-            const uint32_t slot = cat ? ((n == 2 ? 0u : 5u) + cat - 1u) : 0xffu;
-            unsigned any = __ballot_sync(0xffffffffu, cat != 0);
-            while (any)
-            {
-                const int leader = __ffs(any) - 1;
-                const uint32_t ls = __shfl_sync(0xffffffffu, slot, leader);
-                const unsigned peers = __ballot_sync(0xffffffffu, slot == ls);
-                if (lane == leader) atomicAdd(&S.counters[ls], __popc(peers));
-                any &= ~peers;
-            }
-            const unsigned refs = __ballot_sync(0xffffffffu, live && my_vtype == VTN_VT_REF);
-            const unsigned vars = __ballot_sync(0xffffffffu, live && my_vtype != VTN_VT_REF);
-            if (lane == 0)
-            {
-                if (vars) atomicAdd(&S.counters[10], __popc(vars));
-                if (refs) atomicAdd(&S.counters[11], __popc(refs));
-            }
-        }
-        const uint32_t c = changed ? 1u : 0u, nb = changed ? S.nbytes[tid] : 0u;
-        uint32_t ic = c, ib = nb;
+            uint8_t sv[VTN_RPL], vv[VTN_RPL];
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1)
-        {
-            const uint32_t tc = __shfl_up_sync(0xffffffffu, ic, o);
-            const uint32_t tb = __shfl_up_sync(0xffffffffu, ib, o);
-            if (lane >= o) { ic += tc; ib += tb; }
-        }
-        if (lane == 31) { S.wcnt[warp] = ic; S.wbytes[warp] = ib; }
-        __syncthreads();
-        uint32_t wc = 0, wb = 0, tot_c = 0, tot_b = 0;
-#pragma unroll
-        for (int w = 0; w < VTN_TILE / 32; ++w)
-        {
-            const uint32_t xc = S.wcnt[w], xb = S.wbytes[w];
-            if (w < warp) { wc += xc; wb += xb; }
-            tot_c += xc;
-            tot_b += xb;
-        }
-        if (changed)
-        {
-            S.cqueue[wc + ic - 1] = (uint16_t)tid; // rank inside the tile, input order
-            S.ob[tid] = wb + ib - nb;
-        }
-        if (warp == 0)
-        {
-            if (lane == 0)
+            for (int j = 0; j < VTN_RPL; ++j)
             {
-                st_state(st_cnt + tile, (tile == 0 ? VTN_FLAG_INC : VTN_FLAG_AGG) | tot_c);
-                st_state(st_bytes + tile, (tile == 0 ? VTN_FLAG_INC : VTN_FLAG_AGG) | tot_b);
+                const uint32_t idx = lane * VTN_RPL + j;
+                const bool q = qmask & (1u << j);
+                sv[j] = q ? S.st[idx] : 0;
+                vv[j] = q ? S.vt[idx] : VTN_VT_SNP;
             }
-            unsigned long long pc = 0, pb = 0;
-            if (tile)
+            if (lane * VTN_RPL + VTN_RPL <= n_live)
             {
-                pc = lookback(st_cnt, (int)tile, lane);
-                pb = lookback(st_bytes, (int)tile, lane);
-                if (lane == 0)
-                {
-                    st_state(st_cnt + tile, VTN_FLAG_INC | (pc + tot_c));
-                    st_state(st_bytes + tile, VTN_FLAG_INC | (pb + tot_b));
-                }
-            }
-            if (lane == 0)
-            {
-                S.base[0] = pc;
-                S.base[1] = pb;
-                if (tile == n_tiles - 1)
-                {
-                    O.totals[0] = pc + tot_c;
-                    O.totals[1] = pb + tot_b;
-                    O.chg_off[pc + tot_c] = pb + tot_b;
-                }
-            }
-        }
-        __syncthreads();
-        // ---------------- phase 3b: changed records, one per consecutive thread ----------------
-        for (uint32_t i = tid; i < tot_c; i += VTN_TILE)
-        {
-            const uint32_t t = S.cqueue[i];
-            const uint32_t rr = r0 + t;
-            const unsigned long long k = S.base[0] + i;
-            const unsigned long long ob = S.base[1] + S.ob[t];
-            const int32_t pos1 = __ldg(B.pos1 + rr);
-            const uint32_t T = S.T[t], le = S.le[t], lt = S.lt[t];
-            O.chg_rec[k] = rr;
-            O.chg_pos1[k] = pos1 - (int32_t)le + (int32_t)lt;
-            O.chg_lt[k] = lt;
-            O.chg_le[k] = le;
-            O.chg_rt[k] = T;
-            O.chg_off[k] = ob;
-            uint8_t* dst = O.chg_bytes + ob;
-            if (S.fast[t])
-            {
-                uint64_t a = S.newR[t];
-                const uint32_t l0 = S.nlr[t], l1 = S.nla[t];
-                for (uint32_t j = 0; j < l0; ++j, a >>= 2) dst[j] = (uint8_t)(0x47544341u >> (8 * ((uint32_t)a & 3u)));
-                a = S.newA[t];
-                dst += l0;
-                for (uint32_t j = 0; j < l1; ++j, a >>= 2) dst[j] = (uint8_t)(0x47544341u >> (8 * ((uint32_t)a & 3u)));
+                reinterpret_cast<uchar4*>(O.status + r0)[lane] = make_uchar4(sv[0], sv[1], sv[2], sv[3]);
+                reinterpret_cast<uchar4*>(O.vtype + r0)[lane] = make_uchar4(vv[0], vv[1], vv[2], vv[3]);
             }
             else
             {
-                // generic: (le reference bases + upper(allele))[0 : le + len - T], or upper(allele)[lt : len - T]
-                const uint32_t ab2 = __ldg(B.allele_beg + rr);
-                const uint32_t n2 = __ldg(B.allele_beg + rr + 1) - ab2;
-                const int32_t rid = __ldg(B.rid + rr);
-                const uint64_t gbase = __ldg(R.contig_goff + rid) << 5;
-                const int64_t clen = __ldg(R.contig_len + rid);
-                VtnRefCursor cur;
-                uint32_t o = __ldg(B.allele_off + ab2);
-                for (uint32_t ai = 0; ai < n2; ++ai)
-                {
-                    const uint32_t o2 = __ldg(B.allele_off + ab2 + ai + 1);
-                    const uint32_t len = o2 - o;
-                    const uint32_t newlen = len + le - T - lt;
-                    const uint8_t* a = B.bytes + o;
-                    for (uint32_t j = 0; j < newlen; ++j)
+#pragma unroll
+                for (int j = 0; j < VTN_RPL; ++j)
+                    if (lane * VTN_RPL + j < n_live)
                     {
-                        uint8_t ch;
-                        if (j < le)
-                        {
-                            int64_t p0 = (int64_t)pos1 - 1 - (int64_t)le + (int64_t)j;
-                            p0 = p0 < 0 ? 0 : (p0 >= clen ? clen - 1 : p0);
-                            ch = cur.uc(R, gbase + (uint64_t)p0);
-                        }
-                        else
-                            ch = vtn_toupper(a[j - le + lt]);
-                        dst[j] = ch;
+                        O.status[r0 + lane * VTN_RPL + j] = sv[j];
+                        O.vtype[r0 + lane * VTN_RPL + j] = vv[j];
                     }
-                    dst += newlen;
-                    o = o2;
-                }
+            }
+        }
+#undef AO
+        __syncwarp(); // the next tile reuses this warp's shared arrays
+        tile = __shfl_sync(0xffffffffu, next_tile, 0);
+    }
+    if (lane < 12 && my_counter) atomicAdd(O.counters + lane, my_counter);
+}
+
+// ---- K2: scan of the tile directory + gather of the scratch segments into the final, input-ordered arrays ----
+#define VTC_TPB 256
+__global__ void __launch_bounds__(VTC_TPB) vtn_compact_kernel(VtnDevBatchView B, VtnDevScratch X, VtnDevNormOut O, uint32_t n_tiles,
+                                                              unsigned long long* state, uint32_t* ticket, uint32_t n_blocks)
+{
+    __shared__ uint32_t s_blk;
+    __shared__ uint32_t s_wc[VTC_TPB / 32], s_wb[VTC_TPB / 32];
+    __shared__ unsigned long long s_base[2];
+    __shared__ uint32_t s_cnt[VTC_TPB], s_nb[VTC_TPB];
+    __shared__ unsigned long long s_bc[VTC_TPB], s_bb[VTC_TPB];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_blk = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t blk = s_blk;
+    unsigned long long* st_c = state;
+    unsigned long long* st_b = state + n_blocks;
+    const uint32_t t = blk * VTC_TPB + tid;
+    const unsigned long long d = t < n_tiles ? X.dir[t] : 0ull;
+    const uint32_t c = (uint32_t)(d >> 32), nb = (uint32_t)d;
+    uint32_t ic = c, ib = nb;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+    {
+        const uint32_t tc = __shfl_up_sync(0xffffffffu, ic, o);
+        const uint32_t tb = __shfl_up_sync(0xffffffffu, ib, o);
+        if (lane >= o) { ic += tc; ib += tb; }
+    }
+    if (lane == 31) { s_wc[warp] = ic; s_wb[warp] = ib; }
+    __syncthreads();
+    uint32_t wc = 0, wb = 0, tot_c = 0, tot_b = 0;
+#pragma unroll
+    for (int w = 0; w < VTC_TPB / 32; ++w)
+    {
+        const uint32_t xc = s_wc[w], xb = s_wb[w];
+        if (w < warp) { wc += xc; wb += xb; }
+        tot_c += xc;
+        tot_b += xb;
+    }
+    if (warp == 0)
+    {
+        if (lane == 0)
+        {
+            st_state(st_c + blk, (blk == 0 ? VTN_FLAG_INC : VTN_FLAG_AGG) | tot_c);
+            st_state(st_b + blk, (blk == 0 ? VTN_FLAG_INC : VTN_FLAG_AGG) | tot_b);
+        }
+        unsigned long long pc = 0, pb = 0;
+        if (blk)
+        {
+            pc = lookback(st_c, (int)blk, lane);
+            pb = lookback(st_b, (int)blk, lane);
+            if (lane == 0)
+            {
+                st_state(st_c + blk, VTN_FLAG_INC | (pc + tot_c));
+                st_state(st_b + blk, VTN_FLAG_INC | (pb + tot_b));
+            }
+        }
+        if (lane == 0)
+        {
+            s_base[0] = pc;
+            s_base[1] = pb;
+            if (blk == n_blocks - 1)
+            {
+                O.totals[0] = pc + tot_c;
+                O.totals[1] = pb + tot_b;
+                O.chg_off[pc + tot_c] = pb + tot_b;
             }
         }
     }
     __syncthreads();
-    if (tid < 12 && S.counters[tid]) atomicAdd(O.counters + tid, S.counters[tid]);
+    s_cnt[tid] = c;
+    s_nb[tid] = nb;
+    s_bc[tid] = s_base[0] + wc + (ic - c);
+    s_bb[tid] = s_base[1] + wb + (ib - nb);
+    __syncthreads();
+    for (uint32_t tt = warp; tt < VTC_TPB && blk * VTC_TPB + tt < n_tiles; tt += VTC_TPB / 32)
+    {
+        const uint32_t cnt = s_cnt[tt];
+        if (!cnt) continue;
+        const uint32_t nbytes = s_nb[tt];
+        const unsigned long long bc = s_bc[tt], bb = s_bb[tt];
+        const uint32_t r0 = (blk * VTC_TPB + tt) * VTN_WTILE;
+        for (uint32_t i = lane; i < cnt; i += 32)
+        {
+            const uint32_t src = r0 + i;
+            const unsigned long long k = bc + i;
+            O.chg_rec[k] = X.rec[src];
+            O.chg_pos1[k] = X.pos1[src];
+            O.chg_lt[k] = X.lt[src];
+            O.chg_le[k] = X.le[src];
+            O.chg_rt[k] = X.rt[src];
+            O.chg_off[k] = bb + X.ob[src];
+        }
+        const uint32_t b_lo = __ldg(B.allele_off + __ldg(B.allele_beg + r0));
+        const uint8_t* sb = X.bytes + b_lo;
+        uint8_t* db = O.chg_bytes + bb;
+        for (uint32_t i = lane; i < nbytes; i += 32) db[i] = sb[i];
+    }
 }
 
 } // namespace
 
-uint32_t vtn_normalize_tile_records() { return VTN_TILE; }
+uint32_t vtn_normalize_tile_records() { return VTN_WTILE; }
 
-int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNormOut& out, unsigned long long* tile_state,
-                         uint32_t* tile_counter, uint32_t n_tiles)
+int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNormOut& out, const VtnDevScratch& scr,
+                         unsigned long long* tile_state, uint32_t* tile_counter, uint32_t n_tiles)
 {
     VTN_CUDA(ctx, cudaMemsetAsync(out.totals, 0, 2 * sizeof(unsigned long long), ctx->stream));
     VTN_CUDA(ctx, cudaMemsetAsync(out.counters, 0, 12 * sizeof(uint32_t), ctx->stream));
     VTN_CUDA(ctx, cudaMemsetAsync(out.chg_off, 0, sizeof(uint64_t), ctx->stream));
     if (n_tiles == 0) return VTN_OK;
-    VTN_CUDA(ctx, cudaMemsetAsync(tile_state, 0, 2ull * n_tiles * sizeof(unsigned long long), ctx->stream));
-    VTN_CUDA(ctx, cudaMemsetAsync(tile_counter, 0, sizeof(uint32_t), ctx->stream));
-    int per_sm = 0;
-    VTN_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vtn_normalize_kernel, VTN_TILE, 0));
-    if (per_sm < 1) per_sm = 1;
+    const uint32_t n_blocks2 = (n_tiles + VTC_TPB - 1) / VTC_TPB;
+    VTN_CUDA(ctx, cudaMemsetAsync(tile_state, 0, 2ull * n_blocks2 * sizeof(unsigned long long), ctx->stream));
+    VTN_CUDA(ctx, cudaMemsetAsync(tile_counter, 0, 2 * sizeof(uint32_t), ctx->stream));
+    static int per_sm = 0;
+    if (!per_sm)
+    {
+        VTN_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vtn_normalize_kernel, 32 * VTN_WARPS, 0));
+        if (per_sm < 1) per_sm = 1;
+    }
     uint32_t grid = (uint32_t)(ctx->sm_count * per_sm);
-    if (grid > n_tiles) grid = n_tiles;
-    vtn_normalize_kernel<<<grid, VTN_TILE, 0, ctx->stream>>>(ctx->dref, in, out, tile_state, tile_counter, n_tiles);
+    const uint32_t need = (n_tiles + VTN_WARPS - 1) / VTN_WARPS;
+    if (grid > need) grid = need;
+    vtn_normalize_kernel<<<grid, 32 * VTN_WARPS, 0, ctx->stream>>>(ctx->dref, in, out, scr, tile_counter, n_tiles);
     VTN_CUDA(ctx, cudaGetLastError());
-    ctx->launches++;
+    vtn_compact_kernel<<<n_blocks2, VTC_TPB, 0, ctx->stream>>>(in, scr, out, n_tiles, tile_state, tile_counter + 1, n_blocks2);
+    VTN_CUDA(ctx, cudaGetLastError());
+    ctx->launches += 2;
     return VTN_OK;
 }
