@@ -4,7 +4,7 @@ kernel's cubin) and prints the hottest lines.  usage: ncu_lines.py report.ncu-re
 import csv, re, subprocess, sys, collections
 rep, cubin, kname = sys.argv[1], sys.argv[2], sys.argv[3]
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
-out = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv'], capture_output=True, text=True).stdout
+out = open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
 h = rows[1]
 iA, iS, iN, iI, iT = h.index('Address'), h.index('Source'), h.index('# Samples'), h.index('Instructions Executed'), h.index('Thread Instructions Executed')
@@ -29,5 +29,5 @@ for k, (src, ns, ni, nt, lsb, br) in enumerate(ins):
 tot_s = sum(a[0] for a in agg.values()); tot_i = sum(a[1] for a in agg.values())
 print('total samples %d, warp instr %d' % (tot_s, tot_i))
 print('%-28s %8s %6s %12s %6s %6s %8s %8s' % ('line', 'samples', '%', 'warp_instr', '%', 'thr/i', 'long_sb', 'branch'))
-for key, a in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+for key, a in sorted(agg.items(), key=lambda kv: -kv[1][int(sys.argv[5]) if len(sys.argv) > 5 else 0])[:top]:
     print('%-28s %8d %6.1f %12d %6.1f %6.1f %8d %8d' % ('%s:%s' % key if key else '?', a[0], 100.0 * a[0] / max(tot_s, 1), a[1], 100.0 * a[1] / max(tot_i, 1), a[2] / max(a[1], 1), a[3], a[4]))

@@ -5,7 +5,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvtn.so")
+LIB_PATH = os.environ.get("VTN_LIB_PATH") or os.path.join(_HERE, "libvtn.so")  # override only for kernel experiments
 
 c_u8p = C.POINTER(C.c_uint8)
 c_u16p = C.POINTER(C.c_uint16)

@@ -146,6 +146,7 @@ int vtn_dbatch_alloc(vtn_ctx* ctx, uint32_t n_rec, uint32_t n_allele, uint64_t n
     A(dalloc(&d->scr.ob, n_rec));
     A(dalloc(&d->scr.bytes, n_bytes + 16));
     A(dalloc(&d->scr.dir, (size_t)d->n_tiles));
+    A(dalloc(&d->scr.blo, (size_t)d->n_tiles));
     A(dalloc(&d->tile_state, 2 * (size_t)d->n_tiles));
     A(dalloc(&d->tile_counter, 4));
 #undef A
@@ -181,7 +182,7 @@ int vtn_dbatch_destroy(vtn_ctx* ctx, vtn_dbatch* d)
     cudaFree(d->status); cudaFree(d->vtype); cudaFree(d->chg_rec); cudaFree(d->chg_pos1); cudaFree(d->chg_lt);
     cudaFree(d->chg_le); cudaFree(d->chg_rt); cudaFree(d->chg_off); cudaFree(d->chg_bytes); cudaFree(d->totals);
     cudaFree(d->scr.rec); cudaFree(d->scr.pos1); cudaFree(d->scr.lt); cudaFree(d->scr.le); cudaFree(d->scr.rt);
-    cudaFree(d->scr.ob); cudaFree(d->scr.bytes); cudaFree(d->scr.dir);
+    cudaFree(d->scr.ob); cudaFree(d->scr.bytes); cudaFree(d->scr.dir); cudaFree(d->scr.blo);
     cudaFree(d->counters); cudaFree(d->tile_state); cudaFree(d->tile_counter); cudaFree(d->src_rec); cudaFree(d->alt_idx);
     delete d;
     return VTN_OK;

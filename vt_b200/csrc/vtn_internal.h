@@ -72,6 +72,7 @@ struct VtnDevScratch
     uint32_t* ob;             // byte offset of the record's new alleles inside its tile's byte window
     uint8_t* bytes;           // [n_bytes] tile t owns the byte window of its records' old alleles
     unsigned long long* dir;  // [n_tiles] (changed count << 32) | new allele bytes
+    uint32_t* blo;            // [n_tiles] start of the tile's byte window
 };
 
 struct vtn_dbatch

@@ -191,11 +191,10 @@ __device__ __noinline__ uint32_t lag_scan(const VtnDevRef& R, uint64_t gbase, in
 }
 
 // ---- fast path (see vtn_fast.cuh).  Returns false when the record is not eligible. ----
-__device__ bool fast_biallelic(const VtnDevRef& R, const uint8_t* bytes, uint32_t off0, uint32_t len0, uint32_t len1,
-                               int32_t pos1, int32_t rid, VtnFastRes& o)
+__device__ __forceinline__ bool fast_biallelic(const VtnDevRef& R, const uint8_t* bytes, uint32_t off0, uint32_t len0, uint32_t len1,
+                                               int32_t pos1, int64_t clen, uint64_t gbase, VtnFastRes& o)
 {
-    if (len0 > 32 || len1 > 32 || rid < 0 || rid >= R.n_contig || pos1 < 34) return false;
-    const int64_t clen = __ldg(R.contig_len + rid);
+    if (len0 > 32 || len1 > 32 || pos1 < 34) return false;
     const int64_t p0 = (int64_t)pos1 - 1;
     if (p0 + 32 > clen) return false; // keeps every window inside the contig (records at contig ends -> generic)
     // ---- allele bytes -> 2-bit code stream (REF then ALT are contiguous) ----
@@ -257,7 +256,6 @@ __device__ bool fast_biallelic(const VtnDevRef& R, const uint8_t* bytes, uint32_
     if (vtype == VTN_VT_SNP) return true; // no REF check (normalize.cpp:205); a pure SNP is always normalized
 
     // ---- reference windows and REF check (variant_manip.cpp:61-103) ----
-    const uint64_t gbase = __ldg(R.contig_goff + rid) << 5;
     uint64_t V, W;
     uint32_t ev, nw;
     vtn_ref_window64(R, gbase + (uint64_t)(p0 - 32), V, W, ev, nw);
@@ -562,6 +560,9 @@ namespace
 #define VTN_RPL 4
 #define VTN_WTILE (32 * VTN_RPL)
 #define VTN_WARPS 4
+#ifndef VTN_MIN_BLOCKS
+#define VTN_MIN_BLOCKS 5
+#endif
 #define VTN_AOFF_CAP (VTN_WTILE * 3 + 16)
 #define VTN_BYTES_CAP (VTN_WTILE * 8 + 64)
 
@@ -569,9 +570,11 @@ struct __align__(16) WarpSmem
 {
     uint32_t aoff[VTN_AOFF_CAP];
     uint8_t bytes[VTN_BYTES_CAP];
+    int32_t pos1[VTN_WTILE], rid[VTN_WTILE];
     uint8_t queue[VTN_WTILE];
     uint8_t st[VTN_WTILE], vt[VTN_WTILE];
 };
+#define VTN_CONTIG_CAP 256
 
 __device__ __forceinline__ uint32_t warp_excl_scan(uint32_t v, int lane, uint32_t& total)
 {
@@ -623,33 +626,63 @@ __device__ __noinline__ void write_generic_alleles(const VtnDevRef& R, const Vtn
     }
 }
 
-__global__ void __launch_bounds__(32 * VTN_WARPS) vtn_normalize_kernel(VtnDevRef R, VtnDevBatchView B, VtnDevNormOut O, VtnDevScratch X,
+__global__ void __launch_bounds__(32 * VTN_WARPS, VTN_MIN_BLOCKS) vtn_normalize_kernel(VtnDevRef R, VtnDevBatchView B, VtnDevNormOut O, VtnDevScratch X,
                                                                       uint32_t* tile_counter, uint32_t n_tiles)
 {
     __shared__ WarpSmem SM[VTN_WARPS];
+    __shared__ uint64_t s_gbase[VTN_CONTIG_CAP];
+    __shared__ int64_t s_clen[VTN_CONTIG_CAP];
     const int lane = threadIdx.x & 31;
     WarpSmem& S = SM[threadIdx.x >> 5];
     uint32_t my_counter = 0; // lane k < 12 accumulates counter k of this warp
+    // contig table (gbase, length) into shared memory: two dependent global loads fewer per queued record
+    const bool contigs_staged = R.n_contig <= VTN_CONTIG_CAP;
+    if (contigs_staged)
+        for (int c = threadIdx.x; c < R.n_contig; c += blockDim.x)
+        {
+            s_gbase[c] = __ldg(R.contig_goff + c) << 5;
+            s_clen[c] = __ldg(R.contig_len + c);
+        }
+    __syncthreads();
+    (void)tile_counter;
 
-    uint32_t tile = 0;
-    if (lane == 0) tile = atomicAdd(tile_counter, 1u);
-    tile = __shfl_sync(0xffffffffu, tile, 0);
+    // static round-robin tiles: tiles are independent, so no scheduling atomic is needed
+    const uint32_t tile_stride = gridDim.x * VTN_WARPS;
+    uint32_t tile = blockIdx.x * VTN_WARPS + (threadIdx.x >> 5);
+    // header vectors of the first tile; inside the loop the NEXT tile's are prefetched into registers
+    uint4 h_ab = make_uint4(0, 0, 0, 0);
+    int4 h_pos = make_int4(0, 0, 0, 0), h_rid = make_int4(0, 0, 0, 0);
+    uint32_t h_abx = 0;
+    if (tile < n_tiles)
+    {
+        const uint32_t r0 = tile * VTN_WTILE;
+        h_ab = __ldg(reinterpret_cast<const uint4*>(B.allele_beg + r0) + lane); // arrays are padded
+        h_pos = __ldg(reinterpret_cast<const int4*>(B.pos1 + r0) + lane);
+        h_rid = __ldg(reinterpret_cast<const int4*>(B.rid + r0) + lane);
+        if (lane == 31) h_abx = __ldg(B.allele_beg + r0 + VTN_WTILE);
+    }
     while (tile < n_tiles)
     {
-        // grab the next tile id now so that the atomic's latency overlaps this tile's work
-        uint32_t next_tile = 0;
-        if (lane == 0) next_tile = atomicAdd(tile_counter, 1u);
-
+        const uint32_t next_tile = tile + tile_stride;
         const uint32_t r0 = tile * VTN_WTILE;
         const uint32_t n_live = min((uint32_t)VTN_WTILE, B.n_rec - r0);
         // ---------------- phase 1 ----------------
         uint32_t ab[VTN_RPL + 1];
         {
-            const uint4 v = __ldg(reinterpret_cast<const uint4*>(B.allele_beg + r0) + lane); // arrays are padded
-            ab[0] = v.x; ab[1] = v.y; ab[2] = v.z; ab[3] = v.w;
-            uint32_t nxt = __shfl_down_sync(0xffffffffu, v.x, 1);
-            if (lane == 31) nxt = __ldg(B.allele_beg + r0 + VTN_WTILE);
+            ab[0] = h_ab.x; ab[1] = h_ab.y; ab[2] = h_ab.z; ab[3] = h_ab.w;
+            uint32_t nxt = __shfl_down_sync(0xffffffffu, h_ab.x, 1);
+            if (lane == 31) nxt = h_abx;
             ab[4] = nxt;
+            reinterpret_cast<int4*>(S.pos1)[lane] = h_pos;
+            reinterpret_cast<int4*>(S.rid)[lane] = h_rid;
+        }
+        if (next_tile < n_tiles)
+        {
+            const uint32_t r1 = next_tile * VTN_WTILE;
+            h_ab = __ldg(reinterpret_cast<const uint4*>(B.allele_beg + r1) + lane);
+            h_pos = __ldg(reinterpret_cast<const int4*>(B.pos1 + r1) + lane);
+            h_rid = __ldg(reinterpret_cast<const int4*>(B.rid + r1) + lane);
+            if (lane == 31) h_abx = __ldg(B.allele_beg + r1 + VTN_WTILE);
         }
         const uint32_t s_lo = __shfl_sync(0xffffffffu, ab[0], 0);
         const uint32_t s_hi = __ldg(B.allele_beg + r0 + n_live); // one past the last live record's slots
@@ -721,11 +754,14 @@ __global__ void __launch_bounds__(32 * VTN_WARPS) vtn_normalize_kernel(VtnDevRef
                 rr = r0 + idx;
                 const uint32_t ab2 = __ldg(B.allele_beg + rr);
                 n2 = __ldg(B.allele_beg + rr + 1) - ab2;
-                pos1 = __ldg(B.pos1 + rr);
-                if (n2 == 2)
+                pos1 = S.pos1[idx];
+                const int32_t rid = S.rid[idx];
+                if (n2 == 2 && rid >= 0 && rid < R.n_contig)
                 {
                     const uint32_t o0 = AO(ab2), o1 = AO(ab2 + 1), o2 = AO(ab2 + 2);
-                    fast = fast_biallelic(R, BY, o0, o1 - o0, o2 - o1, pos1, __ldg(B.rid + rr), f);
+                    const int64_t clen = contigs_staged ? s_clen[rid] : __ldg(R.contig_len + rid);
+                    const uint64_t gbase = contigs_staged ? s_gbase[rid] : (__ldg(R.contig_goff + rid) << 5);
+                    fast = fast_biallelic(R, BY, o0, o1 - o0, o2 - o1, pos1, clen, gbase, f);
                 }
                 if (fast)
                 {
@@ -782,7 +818,11 @@ __global__ void __launch_bounds__(32 * VTN_WARPS) vtn_normalize_kernel(VtnDevRef
         }
         if (lane == 10) my_counter += cnt_vars;
         if (lane == 11) my_counter += cnt_refs;
-        if (lane == 0) X.dir[tile] = ((unsigned long long)tot_c << 32) | tot_b;
+        if (lane == 0)
+        {
+            X.dir[tile] = ((unsigned long long)tot_c << 32) | tot_b;
+            X.blo[tile] = b_lo;
+        }
         __syncwarp();
 
         // ---------------- phase 3: status / vtype as one 4-byte store per lane ----------------
@@ -814,20 +854,21 @@ __global__ void __launch_bounds__(32 * VTN_WARPS) vtn_normalize_kernel(VtnDevRef
         }
 #undef AO
         __syncwarp(); // the next tile reuses this warp's shared arrays
-        tile = __shfl_sync(0xffffffffu, next_tile, 0);
+        tile = next_tile;
     }
     if (lane < 12 && my_counter) atomicAdd(O.counters + lane, my_counter);
 }
 
 // ---- K2: scan of the tile directory + gather of the scratch segments into the final, input-ordered arrays ----
-#define VTC_TPB 256
-__global__ void __launch_bounds__(VTC_TPB) vtn_compact_kernel(VtnDevBatchView B, VtnDevScratch X, VtnDevNormOut O, uint32_t n_tiles,
+#define VTC_TPB 256      // tiles per block
+#define VTC_THREADS 1024 // threads per block: the first VTC_TPB scan the directory, all of them gather
+__global__ void __launch_bounds__(VTC_THREADS) vtn_compact_kernel(VtnDevBatchView B, VtnDevScratch X, VtnDevNormOut O, uint32_t n_tiles,
                                                               unsigned long long* state, uint32_t* ticket, uint32_t n_blocks)
 {
     __shared__ uint32_t s_blk;
     __shared__ uint32_t s_wc[VTC_TPB / 32], s_wb[VTC_TPB / 32];
     __shared__ unsigned long long s_base[2];
-    __shared__ uint32_t s_cnt[VTC_TPB], s_nb[VTC_TPB];
+    __shared__ uint32_t s_cnt[VTC_TPB], s_nb2[VTC_TPB];
     __shared__ unsigned long long s_bc[VTC_TPB], s_bb[VTC_TPB];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s_blk = atomicAdd(ticket, 1u);
@@ -836,8 +877,9 @@ __global__ void __launch_bounds__(VTC_TPB) vtn_compact_kernel(VtnDevBatchView B,
     unsigned long long* st_c = state;
     unsigned long long* st_b = state + n_blocks;
     const uint32_t t = blk * VTC_TPB + tid;
-    const unsigned long long d = t < n_tiles ? X.dir[t] : 0ull;
+    const unsigned long long d = (tid < VTC_TPB && t < n_tiles) ? X.dir[t] : 0ull;
     const uint32_t c = (uint32_t)(d >> 32), nb = (uint32_t)d;
+    if (tid < VTC_TPB) s_nb2[tid] = nb;
     uint32_t ic = c, ib = nb;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1)
@@ -846,7 +888,7 @@ __global__ void __launch_bounds__(VTC_TPB) vtn_compact_kernel(VtnDevBatchView B,
         const uint32_t tb = __shfl_up_sync(0xffffffffu, ib, o);
         if (lane >= o) { ic += tc; ib += tb; }
     }
-    if (lane == 31) { s_wc[warp] = ic; s_wb[warp] = ib; }
+    if (lane == 31 && warp < VTC_TPB / 32) { s_wc[warp] = ic; s_wb[warp] = ib; }
     __syncthreads();
     uint32_t wc = 0, wb = 0, tot_c = 0, tot_b = 0;
 #pragma unroll
@@ -888,33 +930,42 @@ __global__ void __launch_bounds__(VTC_TPB) vtn_compact_kernel(VtnDevBatchView B,
         }
     }
     __syncthreads();
-    s_cnt[tid] = c;
-    s_nb[tid] = nb;
-    s_bc[tid] = s_base[0] + wc + (ic - c);
-    s_bb[tid] = s_base[1] + wb + (ib - nb);
-    __syncthreads();
-    for (uint32_t tt = warp; tt < VTC_TPB && blk * VTC_TPB + tt < n_tiles; tt += VTC_TPB / 32)
+    if (tid < VTC_TPB)
     {
-        const uint32_t cnt = s_cnt[tt];
-        if (!cnt) continue;
-        const uint32_t nbytes = s_nb[tt];
-        const unsigned long long bc = s_bc[tt], bb = s_bb[tt];
-        const uint32_t r0 = (blk * VTC_TPB + tt) * VTN_WTILE;
-        for (uint32_t i = lane; i < cnt; i += 32)
+        s_cnt[tid] = c;
+        s_bc[tid] = wc + (ic - c); // block-local exclusive prefix of changed records
+        s_bb[tid] = s_base[1] + wb + (ib - nb);
+    }
+    __syncthreads();
+    // flat gather: entry j of this block (0 <= j < tot_c) belongs to the tile found by binary search on the
+    // block-local prefix; every thread has many independent loads in flight
+    const unsigned long long kbase = s_base[0];
+    for (uint32_t j = tid; j < tot_c; j += VTC_THREADS)
+    {
+        uint32_t lo = 0, hi = VTC_TPB - 1; // last tile tt with s_bc[tt] <= j
+        while (lo < hi)
         {
-            const uint32_t src = r0 + i;
-            const unsigned long long k = bc + i;
-            O.chg_rec[k] = X.rec[src];
-            O.chg_pos1[k] = X.pos1[src];
-            O.chg_lt[k] = X.lt[src];
-            O.chg_le[k] = X.le[src];
-            O.chg_rt[k] = X.rt[src];
-            O.chg_off[k] = bb + X.ob[src];
+            const uint32_t mid = (lo + hi + 1) >> 1;
+            if ((uint32_t)s_bc[mid] <= j) lo = mid;
+            else hi = mid - 1;
         }
-        const uint32_t b_lo = __ldg(B.allele_off + __ldg(B.allele_beg + r0));
-        const uint8_t* sb = X.bytes + b_lo;
-        uint8_t* db = O.chg_bytes + bb;
-        for (uint32_t i = lane; i < nbytes; i += 32) db[i] = sb[i];
+        const uint32_t tt = lo;
+        const uint32_t i = j - (uint32_t)s_bc[tt];
+        const uint32_t tile = blk * VTC_TPB + tt;
+        const uint32_t src = tile * VTN_WTILE + i;
+        const unsigned long long k = kbase + j;
+        const uint32_t ob = X.ob[src];
+        const uint32_t ob_next = (i + 1 < s_cnt[tt]) ? X.ob[src + 1] : s_nb2[tt];
+        const unsigned long long dst_off = s_bb[tt] + ob;
+        O.chg_rec[k] = X.rec[src];
+        O.chg_pos1[k] = X.pos1[src];
+        O.chg_lt[k] = X.lt[src];
+        O.chg_le[k] = X.le[src];
+        O.chg_rt[k] = X.rt[src];
+        O.chg_off[k] = dst_off;
+        const uint8_t* sb = X.bytes + X.blo[tile] + ob;
+        uint8_t* db = O.chg_bytes + dst_off;
+        for (uint32_t q = 0; q < ob_next - ob; ++q) db[q] = sb[q];
     }
 }
 
@@ -943,7 +994,7 @@ int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNo
     if (grid > need) grid = need;
     vtn_normalize_kernel<<<grid, 32 * VTN_WARPS, 0, ctx->stream>>>(ctx->dref, in, out, scr, tile_counter, n_tiles);
     VTN_CUDA(ctx, cudaGetLastError());
-    vtn_compact_kernel<<<n_blocks2, VTC_TPB, 0, ctx->stream>>>(in, scr, out, n_tiles, tile_state, tile_counter + 1, n_blocks2);
+    vtn_compact_kernel<<<n_blocks2, VTC_THREADS, 0, ctx->stream>>>(in, scr, out, n_tiles, tile_state, tile_counter + 1, n_blocks2);
     VTN_CUDA(ctx, cudaGetLastError());
     ctx->launches += 2;
     return VTN_OK;
