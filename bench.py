@@ -151,10 +151,7 @@ def pinned_batch(ctx, batch):
     from vt_b200.api import Batch
 
     def pin(a):
-        p = C.c_void_p()
-        ctx._chk(ctx.lib.vtn_host_alloc(ctx.h, max(a.nbytes, 1), C.byref(p)), "vtn_host_alloc")
-        buf = (C.c_uint8 * max(a.nbytes, 1)).from_address(p.value)
-        out = np.frombuffer(buf, dtype=a.dtype, count=a.size)
+        out = ctx.pinned_empty(a.size, a.dtype)
         out[:] = a
         return out
     return Batch(pin(batch.pos1), pin(batch.rid), pin(batch.allele_beg), pin(batch.allele_off), pin(batch.data))
@@ -228,7 +225,7 @@ def main():
 
     # ---------------- end to end through the C ABI with pinned host buffers ----------------
     hb = pinned_batch(ctx, batch)
-    hres = NormResult(batch.n_rec, batch.n_bytes)
+    hres = NormResult(batch.n_rec, batch.n_bytes, ctx)
     e2e_steps = max(3, min(args.steps, 20))
     for _ in range(3):
         ctx.normalize(hb, hres)

@@ -94,3 +94,25 @@ def test_multi_tile_order_and_counts(ctx, oracle):
     got, exp = _run(ctx, oracle, names, seqs, recs)
     k = got.n_changed
     assert np.all(np.diff(got.chg_rec[:k].astype(np.int64)) > 0)  # compaction keeps input order
+
+
+def test_chunked_host_call_matches_single_chunk(oracle):
+    """vtn_normalize pipelines the batch in chunks; with a tiny chunk size the output must be identical."""
+    import os
+    from vt_b200 import Context
+    rng = np.random.default_rng(77)
+    names, seqs = helpers.synth_reference(rng, n_contig=2, length=30000)
+    recs = helpers.synth_records(rng, seqs, 20000)
+    b = Batch.from_records(recs)
+    os.environ["VTN_CHUNK_REC"] = "1024"
+    try:
+        c2 = Context(0)
+    finally:
+        del os.environ["VTN_CHUNK_REC"]
+    try:
+        c2.load_reference(names, seqs)
+        got = c2.normalize(b)
+    finally:
+        c2.close()
+    exp = oracle.normalize(seqs, b)
+    helpers.assert_norm_equal(got, exp, b.n_rec)

@@ -60,16 +60,18 @@ class Batch:
 class NormResult:
     """Host arrays for vtn_norm_result, sized for the worst case of a batch."""
 
-    def __init__(self, n_rec, n_bytes):
-        self.status = np.zeros(max(n_rec, 1), np.uint8)
-        self.vtype = np.zeros(max(n_rec, 1), np.uint8)
-        self.chg_rec = np.zeros(max(n_rec, 1), np.uint32)
-        self.chg_pos1 = np.zeros(max(n_rec, 1), np.int32)
-        self.chg_lt = np.zeros(max(n_rec, 1), np.uint32)
-        self.chg_le = np.zeros(max(n_rec, 1), np.uint32)
-        self.chg_rt = np.zeros(max(n_rec, 1), np.uint32)
-        self.chg_off = np.zeros(n_rec + 1, np.uint64)
-        self.chg_bytes = np.zeros(max(n_bytes, 1), np.uint8)
+    def __init__(self, n_rec, n_bytes, ctx=None):
+        """ctx given: the arrays live in pinned host memory from vtn_host_alloc (async D2H overlaps)."""
+        z = (lambda n, dt: ctx.pinned_empty(n, dt)) if ctx is not None else (lambda n, dt: np.zeros(n, dt))
+        self.status = z(max(n_rec, 1), np.uint8)
+        self.vtype = z(max(n_rec, 1), np.uint8)
+        self.chg_rec = z(max(n_rec, 1), np.uint32)
+        self.chg_pos1 = z(max(n_rec, 1), np.int32)
+        self.chg_lt = z(max(n_rec, 1), np.uint32)
+        self.chg_le = z(max(n_rec, 1), np.uint32)
+        self.chg_rt = z(max(n_rec, 1), np.uint32)
+        self.chg_off = z(n_rec + 1, np.uint64)
+        self.chg_bytes = z(max(n_bytes, 1), np.uint8)
         self.c = L.VtnNormResult()
         self.c.status = _p(self.status, L.c_u8p)
         self.c.vtype = _p(self.vtype, L.c_u8p)
@@ -137,6 +139,17 @@ class Context:
         if rc < 0:
             raise VtnError("%s failed (%d): %s" % (what, rc, self.lib.vtn_last_error(self.h).decode()))
         return rc
+
+    def pinned_empty(self, n, dtype):
+        """numpy array over pinned host memory owned by the library (never freed before the ctx)"""
+        dt = np.dtype(dtype)
+        p = C.c_void_p()
+        nbytes = max(int(n) * dt.itemsize, 1)
+        self._chk(self.lib.vtn_host_alloc(self.h, nbytes, C.byref(p)), "vtn_host_alloc")
+        buf = (C.c_uint8 * nbytes).from_address(p.value)
+        a = np.frombuffer(buf, dtype=dt, count=int(n))
+        a[...] = 0
+        return a
 
     # ---- reference ----
     def load_fasta(self, path):

@@ -1,4 +1,5 @@
 // vtn_api.cu -- context, device batches and the host-buffer entry points of the C ABI (include/vtn.h).
+#include <stdlib.h>
 #include <string.h>
 #include "vtn_internal.h"
 
@@ -28,8 +29,14 @@ int vtn_ctx_create(vtn_ctx** out, int device)
     cudaDeviceProp prop;
     VTN_CUDA(nullptr, cudaGetDeviceProperties(&prop, device));
     ctx->sm_count = prop.multiProcessorCount;
+    if (const char* e = getenv("VTN_CHUNK_REC")) // records per pipelined chunk of the host-buffer call (tests use a small one)
+    {
+        long v = atol(e);
+        if (v >= 128) ctx->chunk_rec = (uint32_t)(v / 128) * 128u;
+    }
     VTN_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     VTN_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+    VTN_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream3, cudaStreamNonBlocking));
     VTN_CUDA(nullptr, cudaEventCreate(&ctx->ev0));
     VTN_CUDA(nullptr, cudaEventCreate(&ctx->ev1));
     *out = ctx;
@@ -52,6 +59,9 @@ int vtn_ctx_destroy(vtn_ctx* ctx)
     cudaEventDestroy(ctx->ev1);
     cudaStreamDestroy(ctx->stream);
     cudaStreamDestroy(ctx->stream2);
+    cudaStreamDestroy(ctx->stream3);
+    for (auto e : ctx->chunk_events) cudaEventDestroy(e);
+    if (ctx->pinned_totals) cudaFreeHost(ctx->pinned_totals);
     delete ctx;
     return VTN_OK;
 }
@@ -61,6 +71,7 @@ int vtn_sync(vtn_ctx* ctx)
     if (!ctx) return VTN_E_ARG;
     VTN_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     VTN_CUDA(ctx, cudaStreamSynchronize(ctx->stream2));
+    VTN_CUDA(ctx, cudaStreamSynchronize(ctx->stream3));
     return VTN_OK;
 }
 
@@ -228,7 +239,7 @@ int vtn_normalize_resident(vtn_ctx* ctx, vtn_dbatch* d)
 {
     if (!ctx || !d) return VTN_E_ARG;
     if (!ctx->ref_loaded) return vtn_set_err(ctx, VTN_E_STATE, "vtn_normalize: no reference loaded");
-    VtnDevBatchView v{d->n_rec, d->pos1, d->rid, d->allele_beg, d->allele_off, d->bytes};
+    VtnDevBatchView v{d->n_rec, 0u, d->pos1, d->rid, d->allele_beg, d->allele_off, d->bytes};
     VtnDevNormOut o{d->status, d->vtype, d->chg_rec, d->chg_pos1, d->chg_lt, d->chg_le, d->chg_rt, d->chg_off, d->chg_bytes, d->totals, d->counters};
     return vtn_launch_normalize(ctx, v, o, d->scr, d->tile_state, d->tile_counter, d->n_tiles);
 }
@@ -291,6 +302,11 @@ static int ensure_scratch(vtn_ctx* ctx, uint32_t n_rec, uint32_t n_allele, uint6
     return VTN_OK;
 }
 
+// Host-buffer normalize, pipelined: the batch is cut into chunks of VTN_CHUNK_REC records; chunk c's H2D copies
+// (stream2), kernels (stream) and status/vtype + changed-record D2H copies (stream3) overlap with the other
+// chunks', so the call is bound by the PCIe direction that carries more bytes, not by the sum of the three.
+// Device arrays hold the whole batch at absolute positions, so a chunk is just a view (offset pointers); K2
+// continues the compaction after the previous chunk's totals, which keeps the output in input order.
 int vtn_normalize(vtn_ctx* ctx, const vtn_batch* in, vtn_norm_result* out)
 {
     if (!ctx || !out) return VTN_E_ARG;
@@ -301,11 +317,109 @@ int vtn_normalize(vtn_ctx* ctx, const vtn_batch* in, vtn_norm_result* out)
     rc = ensure_scratch(ctx, in->n_rec, in->n_allele, in->n_bytes);
     if (rc) return rc;
     vtn_dbatch* d = ctx->scratch;
-    rc = upload_inputs(ctx, in, d, ctx->stream);
+    const uint32_t n = in->n_rec;
+    const uint32_t tile = vtn_normalize_tile_records();
+    const uint32_t VTN_CHUNK_REC = ctx->chunk_rec;
+    const uint32_t n_chunks = (n + VTN_CHUNK_REC - 1) / VTN_CHUNK_REC;
+    if (ctx->chunk_events.size() < 3 * (size_t)n_chunks + 3)
+    {
+        size_t old = ctx->chunk_events.size();
+        ctx->chunk_events.resize(3 * (size_t)n_chunks + 3);
+        for (size_t i = old; i < ctx->chunk_events.size(); ++i) VTN_CUDA(ctx, cudaEventCreateWithFlags(&ctx->chunk_events[i], cudaEventDisableTiming));
+    }
+    if (!ctx->pinned_totals) VTN_CUDA(ctx, cudaMallocHost((void**)&ctx->pinned_totals, 4096 * 2 * sizeof(unsigned long long)));
+    if (n_chunks > 4096) return vtn_set_err(ctx, VTN_E_ARG, "vtn_normalize: batch too large (more than 2^32 records?)");
+    cudaStream_t sc = ctx->stream, sh = ctx->stream2, sd = ctx->stream3;
+    // everything on the side streams starts after what is already queued on the main stream
+    cudaEvent_t ev_start = ctx->chunk_events[3 * (size_t)n_chunks];
+    VTN_CUDA(ctx, cudaEventRecord(ev_start, sc));
+    VTN_CUDA(ctx, cudaStreamWaitEvent(sh, ev_start, 0));
+    VTN_CUDA(ctx, cudaStreamWaitEvent(sd, ev_start, 0));
+    unsigned long long done_c = 0, done_b = 0; // changed records / bytes already copied back
+    bool overflow = false;
+    auto copy_changed = [&](unsigned long long tc, unsigned long long tb) -> int {
+        if (tc > out->cap_changed || tb > out->cap_changed_bytes) { overflow = true; return VTN_OK; }
+        if (tc > done_c)
+        {
+            const size_t k0 = (size_t)done_c, k = (size_t)(tc - done_c);
+            VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_rec + k0, d->chg_rec + k0, k * 4, cudaMemcpyDeviceToHost, sd));
+            VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_pos1 + k0, d->chg_pos1 + k0, k * 4, cudaMemcpyDeviceToHost, sd));
+            VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_lt + k0, d->chg_lt + k0, k * 4, cudaMemcpyDeviceToHost, sd));
+            VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_le + k0, d->chg_le + k0, k * 4, cudaMemcpyDeviceToHost, sd));
+            VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_rt + k0, d->chg_rt + k0, k * 4, cudaMemcpyDeviceToHost, sd));
+            VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_off + k0, d->chg_off + k0, k * 8, cudaMemcpyDeviceToHost, sd));
+            if (tb > done_b)
+                VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_bytes + done_b, d->chg_bytes + done_b, (size_t)(tb - done_b), cudaMemcpyDeviceToHost, sd));
+            done_c = tc;
+            done_b = tb;
+        }
+        return VTN_OK;
+    };
+    if (n == 0)
+    {
+        rc = vtn_launch_normalize(ctx, VtnDevBatchView{0, 0, d->pos1, d->rid, d->allele_beg, d->allele_off, d->bytes},
+                                  VtnDevNormOut{d->status, d->vtype, d->chg_rec, d->chg_pos1, d->chg_lt, d->chg_le, d->chg_rt, d->chg_off, d->chg_bytes, d->totals, d->counters},
+                                  d->scr, d->tile_state, d->tile_counter, 0, false);
+        if (rc) return rc;
+    }
+    for (uint32_t c = 0; c < n_chunks; ++c)
+    {
+        const uint32_t r0 = c * VTN_CHUNK_REC, r1 = (c + 1 == n_chunks) ? n : r0 + VTN_CHUNK_REC, nr = r1 - r0;
+        const uint32_t s0 = in->allele_beg[r0], s1 = in->allele_beg[r1];
+        const uint32_t b0 = in->allele_off[s0], b1 = in->allele_off[s1];
+        cudaEvent_t ev_h = ctx->chunk_events[3 * (size_t)c], ev_k = ctx->chunk_events[3 * (size_t)c + 1], ev_t = ctx->chunk_events[3 * (size_t)c + 2];
+        // ---- H2D of the chunk's slices ----
+        VTN_CUDA(ctx, cudaMemcpyAsync(d->allele_beg + r0, in->allele_beg + r0, sizeof(uint32_t) * ((size_t)nr + 1), cudaMemcpyHostToDevice, sh));
+        VTN_CUDA(ctx, cudaMemcpyAsync(d->allele_off + s0, in->allele_off + s0, sizeof(uint32_t) * ((size_t)(s1 - s0) + 1), cudaMemcpyHostToDevice, sh));
+        if (b1 > b0) VTN_CUDA(ctx, cudaMemcpyAsync(d->bytes + b0, in->bytes + b0, (size_t)(b1 - b0), cudaMemcpyHostToDevice, sh));
+        VTN_CUDA(ctx, cudaMemcpyAsync(d->pos1 + r0, in->pos1 + r0, sizeof(int32_t) * nr, cudaMemcpyHostToDevice, sh));
+        VTN_CUDA(ctx, cudaMemcpyAsync(d->rid + r0, in->rid + r0, sizeof(int32_t) * nr, cudaMemcpyHostToDevice, sh));
+        VTN_CUDA(ctx, cudaEventRecord(ev_h, sh));
+        // ---- kernels on a view of the chunk ----
+        VTN_CUDA(ctx, cudaStreamWaitEvent(sc, ev_h, 0));
+        const uint32_t tile0 = r0 / tile, nt = (nr + tile - 1) / tile;
+        VtnDevBatchView v{nr, r0, d->pos1 + r0, d->rid + r0, d->allele_beg + r0, d->allele_off, d->bytes};
+        VtnDevNormOut o{d->status + r0, d->vtype + r0, d->chg_rec, d->chg_pos1, d->chg_lt, d->chg_le, d->chg_rt, d->chg_off, d->chg_bytes, d->totals, d->counters};
+        VtnDevScratch x = d->scr;
+        x.rec += r0; x.pos1 += r0; x.lt += r0; x.le += r0; x.rt += r0; x.ob += r0; x.dir += tile0; x.blo += tile0;
+        rc = vtn_launch_normalize(ctx, v, o, x, d->tile_state, d->tile_counter, nt, c != 0);
+        if (rc) return rc;
+        VTN_CUDA(ctx, cudaEventRecord(ev_k, sc));
+        // ---- D2H: per-record outputs of this chunk, running totals ----
+        VTN_CUDA(ctx, cudaStreamWaitEvent(sd, ev_k, 0));
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->status + r0, d->status + r0, nr, cudaMemcpyDeviceToHost, sd));
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->vtype + r0, d->vtype + r0, nr, cudaMemcpyDeviceToHost, sd));
+        VTN_CUDA(ctx, cudaMemcpyAsync(ctx->pinned_totals + 2 * (size_t)c, d->totals, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, sd));
+        VTN_CUDA(ctx, cudaEventRecord(ev_t, sd));
+        // the totals after chunk c-1 have surely landed by now: copy back that chunk's changed records
+        if (c >= 1)
+        {
+            VTN_CUDA(ctx, cudaEventSynchronize(ctx->chunk_events[3 * (size_t)(c - 1) + 2]));
+            rc = copy_changed(ctx->pinned_totals[2 * (size_t)(c - 1)], ctx->pinned_totals[2 * (size_t)(c - 1) + 1]);
+            if (rc) return rc;
+        }
+    }
+    uint32_t counters[12] = {0};
+    unsigned long long totals[2] = {0, 0};
+    VTN_CUDA(ctx, cudaStreamSynchronize(sc));
+    VTN_CUDA(ctx, cudaStreamSynchronize(sd)); // pinned_totals of the last chunk is valid now
+    VTN_CUDA(ctx, cudaMemcpyAsync(counters, d->counters, sizeof counters, cudaMemcpyDeviceToHost, sd));
+    VTN_CUDA(ctx, cudaMemcpyAsync(totals, d->totals, sizeof totals, cudaMemcpyDeviceToHost, sd));
+    VTN_CUDA(ctx, cudaStreamSynchronize(sd));
+    rc = copy_changed(totals[0], totals[1]);
     if (rc) return rc;
-    rc = vtn_normalize_resident(ctx, d);
-    if (rc) return rc;
-    return fetch_norm(ctx, d, out);
+    if (!overflow && totals[0] <= out->cap_changed)
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_off + totals[0], d->chg_off + totals[0], 8, cudaMemcpyDeviceToHost, sd));
+    VTN_CUDA(ctx, cudaStreamSynchronize(sd));
+    out->n_changed = (uint32_t)totals[0];
+    out->n_changed_bytes = totals[1];
+    memcpy(out->counters.bi, counters, 5 * sizeof(uint32_t));
+    memcpy(out->counters.multi, counters + 5, 5 * sizeof(uint32_t));
+    out->counters.no_variants = counters[10];
+    out->counters.no_refs = counters[11];
+    if (overflow || totals[0] > out->cap_changed || totals[1] > out->cap_changed_bytes)
+        return vtn_set_err(ctx, VTN_E_CAPACITY, "vtn_normalize: result capacity too small (n_changed / n_changed_bytes are set)");
+    return VTN_OK;
 }
 
 // ---------------------------------------------------------------------------------------------------------

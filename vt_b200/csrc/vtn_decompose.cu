@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(VTD_TILE) vtd_emit_kernel(VtnDevBatchView B, u
 int vtn_launch_decompose(vtn_ctx* ctx, vtn_dbatch* d, bool materialise)
 {
     cudaStream_t s = ctx->stream;
-    VtnDevBatchView v{d->n_rec, d->pos1, d->rid, d->allele_beg, d->allele_off, d->bytes};
+    VtnDevBatchView v{d->n_rec, 0u, d->pos1, d->rid, d->allele_beg, d->allele_off, d->bytes};
     VTN_CUDA(ctx, cudaMemsetAsync(d->totals, 0, 4 * sizeof(unsigned long long), s));
     VTN_CUDA(ctx, cudaMemsetAsync(d->counters + 12, 0, 4 * sizeof(uint32_t), s));
     unsigned long long tot[3] = {0, 0, 0};

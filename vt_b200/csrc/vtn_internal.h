@@ -39,6 +39,7 @@ struct VtnContig
 struct VtnDevBatchView
 {
     uint32_t n_rec;
+    uint32_t rec_base; // added to record indices written to chg_rec (chunked launches pass offset views)
     const int32_t* pos1;
     const int32_t* rid;
     const uint32_t* allele_beg;
@@ -116,7 +117,11 @@ struct vtn_ctx
 {
     int device = 0;
     cudaStream_t stream = nullptr;   // compute + primary copies
-    cudaStream_t stream2 = nullptr;  // second copy stream for the pipelined host-buffer call
+    cudaStream_t stream2 = nullptr;  // H2D stream of the pipelined host-buffer call
+    cudaStream_t stream3 = nullptr;  // D2H stream of the pipelined host-buffer call
+    std::vector<cudaEvent_t> chunk_events;
+    unsigned long long* pinned_totals = nullptr;
+    uint32_t chunk_rec = 1u << 20;   // records per chunk of the pipelined host-buffer call
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int sm_count = 0;
     std::string err;
@@ -149,7 +154,7 @@ int vtn_set_err(vtn_ctx* ctx, int code, const std::string& msg);
 
 // kernels' host launchers (vtn_normalize.cu / vtn_decompose.cu)
 int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNormOut& out, const VtnDevScratch& scr,
-                         unsigned long long* tile_state, uint32_t* tile_counter, uint32_t n_tiles);
+                         unsigned long long* tile_state, uint32_t* tile_counter, uint32_t n_tiles, bool accumulate = false);
 uint32_t vtn_normalize_tile_records();
 int vtn_launch_decompose(vtn_ctx* ctx, vtn_dbatch* db, bool materialise);
 bool vtn_dbatch_resize(vtn_dbatch* d, uint32_t n_rec, uint32_t n_allele, uint64_t n_bytes);

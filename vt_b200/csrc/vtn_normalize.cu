@@ -784,7 +784,7 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, VTN_MIN_BLOCKS) vtn_normalize_
             {
                 const uint32_t k = r0 + tot_c + ec;    // scratch slot: tile segment, rank in input order
                 const uint32_t obl = tot_b + eb;       // byte offset inside the tile's byte window
-                X.rec[k] = rr;
+                X.rec[k] = B.rec_base + rr;
                 X.pos1[k] = pos1 - (int32_t)le + (int32_t)lt;
                 X.lt[k] = lt;
                 X.le[k] = le;
@@ -863,7 +863,8 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, VTN_MIN_BLOCKS) vtn_normalize_
 #define VTC_TPB 256      // tiles per block
 #define VTC_THREADS 1024 // threads per block: the first VTC_TPB scan the directory, all of them gather
 __global__ void __launch_bounds__(VTC_THREADS) vtn_compact_kernel(VtnDevBatchView B, VtnDevScratch X, VtnDevNormOut O, uint32_t n_tiles,
-                                                              unsigned long long* state, uint32_t* ticket, uint32_t n_blocks)
+                                                              unsigned long long* state, uint32_t* ticket, uint32_t n_blocks,
+                                                              int accumulate)
 {
     __shared__ uint32_t s_blk;
     __shared__ uint32_t s_wc[VTC_TPB / 32], s_wb[VTC_TPB / 32];
@@ -901,12 +902,18 @@ __global__ void __launch_bounds__(VTC_THREADS) vtn_compact_kernel(VtnDevBatchVie
     }
     if (warp == 0)
     {
+        unsigned long long pc = 0, pb = 0;
+        if (blk == 0 && accumulate)
+        {
+            // chunked host call: continue after the previous chunk's totals (same stream, already final)
+            pc = O.totals[0];
+            pb = O.totals[1];
+        }
         if (lane == 0)
         {
-            st_state(st_c + blk, (blk == 0 ? VTN_FLAG_INC : VTN_FLAG_AGG) | tot_c);
-            st_state(st_b + blk, (blk == 0 ? VTN_FLAG_INC : VTN_FLAG_AGG) | tot_b);
+            st_state(st_c + blk, blk == 0 ? (VTN_FLAG_INC | (pc + tot_c)) : (VTN_FLAG_AGG | tot_c));
+            st_state(st_b + blk, blk == 0 ? (VTN_FLAG_INC | (pb + tot_b)) : (VTN_FLAG_AGG | tot_b));
         }
-        unsigned long long pc = 0, pb = 0;
         if (blk)
         {
             pc = lookback(st_c, (int)blk, lane);
@@ -974,15 +981,19 @@ __global__ void __launch_bounds__(VTC_THREADS) vtn_compact_kernel(VtnDevBatchVie
 uint32_t vtn_normalize_tile_records() { return VTN_WTILE; }
 
 int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNormOut& out, const VtnDevScratch& scr,
-                         unsigned long long* tile_state, uint32_t* tile_counter, uint32_t n_tiles)
+                         unsigned long long* tile_state, uint32_t* tile_counter, uint32_t n_tiles, bool accumulate)
 {
-    VTN_CUDA(ctx, cudaMemsetAsync(out.totals, 0, 2 * sizeof(unsigned long long), ctx->stream));
-    VTN_CUDA(ctx, cudaMemsetAsync(out.counters, 0, 12 * sizeof(uint32_t), ctx->stream));
-    VTN_CUDA(ctx, cudaMemsetAsync(out.chg_off, 0, sizeof(uint64_t), ctx->stream));
+    cudaStream_t s = ctx->stream;
+    if (!accumulate)
+    {
+        VTN_CUDA(ctx, cudaMemsetAsync(out.totals, 0, 2 * sizeof(unsigned long long), s));
+        VTN_CUDA(ctx, cudaMemsetAsync(out.counters, 0, 12 * sizeof(uint32_t), s));
+        VTN_CUDA(ctx, cudaMemsetAsync(out.chg_off, 0, sizeof(uint64_t), s));
+    }
     if (n_tiles == 0) return VTN_OK;
     const uint32_t n_blocks2 = (n_tiles + VTC_TPB - 1) / VTC_TPB;
-    VTN_CUDA(ctx, cudaMemsetAsync(tile_state, 0, 2ull * n_blocks2 * sizeof(unsigned long long), ctx->stream));
-    VTN_CUDA(ctx, cudaMemsetAsync(tile_counter, 0, 2 * sizeof(uint32_t), ctx->stream));
+    VTN_CUDA(ctx, cudaMemsetAsync(tile_state, 0, 2ull * n_blocks2 * sizeof(unsigned long long), s));
+    VTN_CUDA(ctx, cudaMemsetAsync(tile_counter, 0, 2 * sizeof(uint32_t), s));
     static int per_sm = 0;
     if (!per_sm)
     {
@@ -992,9 +1003,9 @@ int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNo
     uint32_t grid = (uint32_t)(ctx->sm_count * per_sm);
     const uint32_t need = (n_tiles + VTN_WARPS - 1) / VTN_WARPS;
     if (grid > need) grid = need;
-    vtn_normalize_kernel<<<grid, 32 * VTN_WARPS, 0, ctx->stream>>>(ctx->dref, in, out, scr, tile_counter, n_tiles);
+    vtn_normalize_kernel<<<grid, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, scr, tile_counter, n_tiles);
     VTN_CUDA(ctx, cudaGetLastError());
-    vtn_compact_kernel<<<n_blocks2, VTC_THREADS, 0, ctx->stream>>>(in, scr, out, n_tiles, tile_state, tile_counter + 1, n_blocks2);
+    vtn_compact_kernel<<<n_blocks2, VTC_THREADS, 0, s>>>(in, scr, out, n_tiles, tile_state, tile_counter + 1, n_blocks2, accumulate ? 1 : 0);
     VTN_CUDA(ctx, cudaGetLastError());
     ctx->launches += 2;
     return VTN_OK;
