@@ -6,6 +6,12 @@ rep, cubin, kname = sys.argv[1], sys.argv[2], sys.argv[3]
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
 out = open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
+# a report with several kernels has one table per kernel ("Kernel Name" row, header row, instructions): keep kname's
+starts = [i for i, r in enumerate(rows) if r and r[0] == 'Kernel Name']
+if starts:
+    pick = next((i for i in starts if kname in rows[i][1]), starts[0])
+    end = next((i for i in starts if i > pick), len(rows))
+    rows = rows[pick:end]
 h = rows[1]
 iA, iS, iN, iI, iT = h.index('Address'), h.index('Source'), h.index('# Samples'), h.index('Instructions Executed'), h.index('Thread Instructions Executed')
 ilsb = h.index('stall_long_sb'); ibr = h.index('stall_branch_resolving')
