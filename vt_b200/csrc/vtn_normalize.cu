@@ -860,7 +860,7 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, VTN_MIN_BLOCKS) vtn_normalize_
 }
 
 // ---- K2: scan of the tile directory + gather of the scratch segments into the final, input-ordered arrays ----
-#define VTC_TPB 256      // tiles per block
+#define VTC_TPB 512      // tiles per block: 10 M records -> 153 blocks, one resident wave on 148 SMs x 2
 #define VTC_THREADS 1024 // threads per block: the first VTC_TPB scan the directory, all of them gather
 __global__ void __launch_bounds__(VTC_THREADS) vtn_compact_kernel(VtnDevBatchView B, VtnDevScratch X, VtnDevNormOut O, uint32_t n_tiles,
                                                               unsigned long long* state, uint32_t* ticket, uint32_t n_blocks,
