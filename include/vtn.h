@@ -154,6 +154,79 @@ int vtn_decompose_resident(vtn_ctx* ctx, vtn_dbatch* db, int fuse_normalize); /*
 int vtn_dbatch_fetch_decompose(vtn_ctx* ctx, vtn_dbatch* db, uint32_t* src_rec, uint16_t* alt_idx,
                                uint64_t* n_out, vtn_decomp_counters* counters);
 
+/* ---- HMM family: AHMM / LFHMM / RFHMM Viterbi realignment (annotate_indels' FlankDetector) ----
+ * Replaces <model>::set_model + <model>::align + the result members/getters:
+ *   AHMM  ahmm.h:94-557, ahmm.cpp:240-247 (set_model), :468-587 (align), :592-730 (trace_path, collect_statistics)
+ *   LFHMM lfhmm.h, lfhmm.cpp:281-292, :489-654, :659-861
+ *   RFHMM rfhmm.h, rfhmm.cpp:306-318, :516-648, :650-840
+ * and the set_delta/epsilon/tau/eta/mismatch_penalty + initialize_T sequence (flank_detector.cpp:50-72).
+ * One alignment per warp on the device; scores are computed with the reference's float expression order and
+ * come out bit-identical, paths and integer results exactly (tolerance stated in north_star: 1e-4 abs on the
+ * score; observed difference 0). */
+#define VTN_HMM_AHMM 0
+#define VTN_HMM_LFHMM 1
+#define VTN_HMM_RFHMM 2
+
+typedef struct vtn_hmm_params
+{
+    float delta, epsilon, tau, eta, mismatch_penalty; /* ahmm.h:74-92; FlankDetector: 1e-7,1e-7,.01,.01,5 */
+    int32_t pl; /* base quality - 33 of every read base; FlankDetector passes 'K' = 42 (flank_detector.cpp:74) */
+} vtn_hmm_params;
+
+/* Alignment a: kind[a]; motif = bytes[seq_off[3a] .. seq_off[3a+1]), flank = [seq_off[3a+1] .. seq_off[3a+2])
+ * (left flank for LFHMM, right flank for RFHMM, empty for AHMM), read = [seq_off[3a+2] .. seq_off[3a+3]).
+ * Limits: read <= 1023 (AHMM truncates longer reads to 1023 like ahmm.cpp:476-480; the flanked models report
+ * VTN_HMM_ST_TOO_LONG where the reference exits), motif 1..255, flank 1..31. */
+typedef struct vtn_hmm_batch
+{
+    uint32_t n;
+    const uint8_t* kind;     /* [n] */
+    const uint32_t* seq_off; /* [3n+1] */
+    const uint8_t* bytes;
+    uint64_t n_bytes;
+} vtn_hmm_batch;
+
+#define VTN_HMM_ST_OK 0
+#define VTN_HMM_ST_TOO_LONG 1 /* lfhmm.cpp:498-502 / rfhmm.cpp:524-528: the reference prints and exit(1)s */
+#define VTN_HMM_ST_BAD_MODEL 2 /* empty motif/read, flank or motif longer than the limits above */
+#define VTN_HMM_ST_NOPATH 3    /* no finite end cell: the reference would index outside its arrays */
+
+/* What align() leaves in the object (ahmm.h:109-132); 96 bytes per alignment.
+ * pos[] = lflank_start[MODEL,READ], lflank_end[..], motif_start, motif_end, rflank_start, rflank_end.
+ * Members the reference does not (re)compute in a call are reported as: last_motif_pos -1 (LFHMM unless the path
+ * leaves Z), motif_count 0 (RFHMM unless the path goes MR->M/D); exact_motif_count / motif_concordance /
+ * trf_score / frac_no_repeats are 0 for RFHMM (not members of its align). */
+typedef struct vtn_hmm_result
+{
+    float optimal_score;
+    int32_t optimal_state, optimal_probe_len, path_len;
+    int32_t pos[12];
+    int32_t motif_count, exact_motif_count;
+    float motif_concordance;
+    int32_t trf_score;
+    float frac_no_repeats;
+    int32_t last_motif_pos;
+    int32_t status; /* VTN_HMM_ST_* */
+    int32_t reserved;
+} vtn_hmm_result;
+
+/* Host-buffer call: H2D, one kernel, D2H; returns after completion.  path (optional, may be NULL) receives the
+ * optimal path of alignment a as reference track words [u:5|d:3|c:12|p:12] (ahmm.h:57-67) in forward order at
+ * path[a*path_stride ...]; entries beyond path_stride are dropped (path_len still reports the full length). */
+int vtn_hmm_align(vtn_ctx* ctx, const vtn_hmm_params* par, const vtn_hmm_batch* in, vtn_hmm_result* out,
+                  int32_t* path, uint32_t path_stride);
+/* Device-resident variant for bench / pipelines. */
+typedef struct vtn_hmm_dbatch vtn_hmm_dbatch;
+int vtn_hmm_dbatch_create(vtn_ctx* ctx, const vtn_hmm_params* par, const vtn_hmm_batch* in, uint32_t path_stride,
+                          vtn_hmm_dbatch** db);
+int vtn_hmm_dbatch_destroy(vtn_ctx* ctx, vtn_hmm_dbatch* db);
+int vtn_hmm_align_resident(vtn_ctx* ctx, vtn_hmm_dbatch* db); /* async on the ctx stream */
+int vtn_hmm_dbatch_fetch(vtn_ctx* ctx, vtn_hmm_dbatch* db, vtn_hmm_result* out, int32_t* path);
+/* the transition table initialize_T would build (7x7 row-major, reference state numbering of that model) */
+int vtn_hmm_transitions(int kind, const vtn_hmm_params* par, float* T49);
+/* DP cells / predecessor evaluations (SURVEY 8d "W") of the last resident run, for roofline accounting */
+int vtn_hmm_dbatch_work(vtn_ctx* ctx, vtn_hmm_dbatch* db, uint64_t* cells, uint64_t* proc_comps);
+
 /* ---- timing on the ctx stream (CUDA events) ---- */
 int vtn_timer_start(vtn_ctx* ctx);
 int vtn_timer_stop(vtn_ctx* ctx, float* ms); /* records, synchronises, returns elapsed ms */
