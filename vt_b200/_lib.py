@@ -60,6 +60,23 @@ class VtnDecompCounters(C.Structure):
     ]
 
 
+class VtnHmmParams(C.Structure):
+    _fields_ = [("delta", C.c_float), ("epsilon", C.c_float), ("tau", C.c_float), ("eta", C.c_float),
+                ("mismatch_penalty", C.c_float), ("pl", C.c_int32)]
+
+
+class VtnHmmBatch(C.Structure):
+    _fields_ = [("n", C.c_uint32), ("kind", c_u8p), ("seq_off", c_u32p), ("bytes", c_u8p), ("n_bytes", C.c_uint64)]
+
+
+class VtnHmmResult(C.Structure):
+    _fields_ = [("optimal_score", C.c_float), ("optimal_state", C.c_int32), ("optimal_probe_len", C.c_int32),
+                ("path_len", C.c_int32), ("pos", C.c_int32 * 12), ("motif_count", C.c_int32),
+                ("exact_motif_count", C.c_int32), ("motif_concordance", C.c_float), ("trf_score", C.c_int32),
+                ("frac_no_repeats", C.c_float), ("last_motif_pos", C.c_int32), ("status", C.c_int32),
+                ("reserved", C.c_int32)]
+
+
 # name -> (restype, argtypes); also the list the CPU test checks against include/vtn.h
 SIGNATURES = {
     "vtn_ctx_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
@@ -89,6 +106,13 @@ SIGNATURES = {
     ),
     "vtn_decompose_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "vtn_dbatch_fetch_decompose": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_u16p, c_u64p, C.POINTER(VtnDecompCounters)]),
+    "vtn_hmm_align": (C.c_int, [C.c_void_p, C.POINTER(VtnHmmParams), C.POINTER(VtnHmmBatch), C.c_void_p, c_i32p, C.c_uint32]),
+    "vtn_hmm_dbatch_create": (C.c_int, [C.c_void_p, C.POINTER(VtnHmmParams), C.POINTER(VtnHmmBatch), C.c_uint32, C.POINTER(C.c_void_p)]),
+    "vtn_hmm_dbatch_destroy": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "vtn_hmm_align_resident": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "vtn_hmm_dbatch_fetch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, c_i32p]),
+    "vtn_hmm_transitions": (C.c_int, [C.c_int, C.POINTER(VtnHmmParams), C.POINTER(C.c_float)]),
+    "vtn_hmm_dbatch_work": (C.c_int, [C.c_void_p, C.c_void_p, c_u64p, c_u64p]),
     "vtn_timer_start": (C.c_int, [C.c_void_p]),
     "vtn_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "vtn_launch_count": (C.c_uint64, [C.c_void_p]),

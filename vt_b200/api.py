@@ -238,3 +238,98 @@ class Context:
 
     def launch_count(self):
         return int(self.lib.vtn_launch_count(self.h))
+
+
+# ---------------------------------------------------------------------------------------------------------
+# HMM family (AHMM / LFHMM / RFHMM): host-side mirror of set_model + align + the result members
+# ---------------------------------------------------------------------------------------------------------
+AHMM, LFHMM, RFHMM = 0, 1, 2
+# FlankDetector's parameters (flank_detector.cpp:44-48) and qual 'K' (:74)
+FLANK_DETECTOR_PARAMS = (1e-7, 1e-7, 0.01, 0.01, 5.0, 42)
+
+HMM_RESULT_DTYPE = np.dtype([
+    ("optimal_score", np.float32), ("optimal_state", np.int32), ("optimal_probe_len", np.int32), ("path_len", np.int32),
+    ("pos", np.int32, (12,)), ("motif_count", np.int32), ("exact_motif_count", np.int32),
+    ("motif_concordance", np.float32), ("trf_score", np.int32), ("frac_no_repeats", np.float32),
+    ("last_motif_pos", np.int32), ("status", np.int32), ("reserved", np.int32)])
+assert HMM_RESULT_DTYPE.itemsize == C.sizeof(L.VtnHmmResult) == 96
+
+
+class HmmBatch:
+    """Alignments as (kind, motif, flank, read) with flank = '' for AHMM; packed as vtn_hmm_batch."""
+
+    def __init__(self, cases):
+        self.n = len(cases)
+        self.kind = np.array([c[0] for c in cases], dtype=np.uint8)
+        parts, off, o = [], [0], 0
+        for _, motif, flank, read in cases:
+            for s in (motif, flank or "", read):
+                b = s.encode() if isinstance(s, str) else bytes(s)
+                parts.append(b)
+                o += len(b)
+                off.append(o)
+        self.seq_off = np.array(off, dtype=np.uint32)
+        self.data = np.frombuffer(b"".join(parts) + b"\0", dtype=np.uint8).copy()
+        self.n_bytes = o
+
+    def as_c(self):
+        return L.VtnHmmBatch(self.n, _p(self.kind, L.c_u8p), _p(self.seq_off, L.c_u32p), _p(self.data, L.c_u8p), self.n_bytes)
+
+
+def hmm_transitions(kind, params=FLANK_DETECTOR_PARAMS):
+    """initialize_T's table (7x7, reference state numbering) as libvtn computes it (host code, no device needed)."""
+    T = (C.c_float * 49)()
+    par = L.VtnHmmParams(*params)
+    rc = L.load().vtn_hmm_transitions(kind, C.byref(par), T)
+    if rc:
+        raise VtnError("vtn_hmm_transitions failed (%d)" % rc)
+    return np.frombuffer(T, dtype=np.float32).copy().reshape(7, 7)
+
+
+def _hmm_align(self, batch, params=FLANK_DETECTOR_PARAMS, path_stride=0):
+    """Host-buffer call -> (structured result array [n], path array [n, path_stride] or None)."""
+    par = L.VtnHmmParams(*params)
+    out = np.zeros(batch.n, dtype=HMM_RESULT_DTYPE)
+    path = np.zeros((batch.n, path_stride), dtype=np.int32) if path_stride else None
+    cb = batch.as_c()
+    self._chk(self.lib.vtn_hmm_align(self.h, C.byref(par), C.byref(cb), out.ctypes.data_as(C.c_void_p),
+                                     _p(path, L.c_i32p) if path_stride else None, path_stride), "vtn_hmm_align")
+    return out, path
+
+
+def _hmm_upload(self, batch, params=FLANK_DETECTOR_PARAMS, path_stride=0):
+    par = L.VtnHmmParams(*params)
+    cb = batch.as_c()
+    db = C.c_void_p()
+    self._chk(self.lib.vtn_hmm_dbatch_create(self.h, C.byref(par), C.byref(cb), path_stride, C.byref(db)), "vtn_hmm_dbatch_create")
+    return db
+
+
+def _hmm_align_resident(self, db):
+    self._chk(self.lib.vtn_hmm_align_resident(self.h, db), "vtn_hmm_align_resident")
+
+
+def _hmm_fetch(self, db, n, path_stride=0):
+    out = np.zeros(n, dtype=HMM_RESULT_DTYPE)
+    path = np.zeros((n, path_stride), dtype=np.int32) if path_stride else None
+    self._chk(self.lib.vtn_hmm_dbatch_fetch(self.h, db, out.ctypes.data_as(C.c_void_p),
+                                            _p(path, L.c_i32p) if path_stride else None), "vtn_hmm_dbatch_fetch")
+    return out, path
+
+
+def _hmm_work(self, db):
+    cells, pc = C.c_uint64(), C.c_uint64()
+    self._chk(self.lib.vtn_hmm_dbatch_work(self.h, db, C.byref(cells), C.byref(pc)), "vtn_hmm_dbatch_work")
+    return cells.value, pc.value
+
+
+def _hmm_free(self, db):
+    self.lib.vtn_hmm_dbatch_destroy(self.h, db)
+
+
+Context.hmm_align = _hmm_align
+Context.hmm_upload = _hmm_upload
+Context.hmm_align_resident = _hmm_align_resident
+Context.hmm_fetch = _hmm_fetch
+Context.hmm_work = _hmm_work
+Context.hmm_free = _hmm_free

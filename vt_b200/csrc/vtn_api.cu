@@ -49,6 +49,7 @@ int vtn_ctx_destroy(vtn_ctx* ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->scratch) vtn_dbatch_destroy(ctx, ctx->scratch);
+    vtn_hmm_ctx_release(ctx);
     cudaFree(ctx->d_groups);
     cudaFree(ctx->d_contig_goff);
     cudaFree(ctx->d_contig_len);

@@ -141,7 +141,12 @@ struct vtn_ctx
     vtn_dbatch* scratch = nullptr;
     uint32_t scratch_rec = 0, scratch_allele = 0;
     uint64_t scratch_bytes = 0;
+    // HMM family (vtn_hmm.cu): per-warp DP scratch (band boundary rows, back-pointers, reversed path) + work counter
+    void* hmm_scratch = nullptr;
+    size_t hmm_scratch_bytes = 0;
+    unsigned* hmm_counter = nullptr;
 };
+void vtn_hmm_ctx_release(vtn_ctx* ctx);
 
 int vtn_set_err(vtn_ctx* ctx, int code, const std::string& msg);
 #define VTN_CUDA(ctx, call)                                                                              \
