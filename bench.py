@@ -145,6 +145,141 @@ def run_reference_arm(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+C5_SITES = int(os.environ.get("VTN_BENCH_C5_SITES", 20000))
+C5_CPU_SAMPLE = int(os.environ.get("VTN_BENCH_C5_CPU_SAMPLE", 400))
+HMM_REF = os.path.join(ROOT, "oracle", "_ref", "hmm_ref")
+# warp instructions per reference proc_comp in the DP inner loop, counted from the SASS of vtn_hmm_kernel
+# (profiles/r1h_hmm_sass_count.txt, dynamic count profiles/r1h_ncu_hmm.txt): the issue-rate roofline of SURVEY.md 8d
+HMM_WARP_INSTR_PER_PROC_COMP = float(os.environ.get("VTN_HMM_IPP", 9.0))
+
+
+def hmm_cpu_reference(cases, params):
+    """The unmodified reference classes (oracle/_ref/hmm_ref) on a bounded sample, one process per host core."""
+    import hmm_helpers as H
+    if not os.path.exists(HMM_REF):
+        raise RuntimeError("oracle/_ref/hmm_ref missing: run __graft_entry__.build() in the build container")
+    cores = len(os.sched_getaffinity(0))
+    P = max(1, min(cores, 64))
+    text = H.cases_text(cases).encode()
+    t0 = time.perf_counter()
+    procs = [subprocess.Popen([HMM_REF] + [repr(float(p)) for p in params[:5]], stdin=subprocess.PIPE, stdout=subprocess.DEVNULL,
+                              stderr=subprocess.DEVNULL) for _ in range(P)]
+    for p in procs:
+        p.stdin.write(text)
+        p.stdin.close()
+    rcs = [p.wait() for p in procs]
+    dt = time.perf_counter() - t0
+    if any(rcs):
+        raise RuntimeError("hmm_ref failed: %s" % rcs)
+    return P * len(cases) / dt / 1e6, P, dt
+
+
+def run_c5(args, rank, world, local):
+    """C5: the (model, sequence) pairs FlankDetector's fuzzy detection issues for synthetic STR indels
+    (vt_b200/flank_detector.py drives the rounds on the GPU), then all of them re-timed as one resident batch."""
+    import torch
+    import torch.distributed as dist
+    from vt_b200 import Context, synth, flank_detector as FD, api as A
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ctx = Context(local)
+    t_setup = time.time()
+    contig, end1, motifs = synth.make_c5_sites(C5_SITES, seed=synth.SEED_C5 + 1000 * rank)
+    sites = [FD.Site(contig, end1[i], motifs[i]) for i in range(C5_SITES)]
+    issued = FD.detect_flanks_fuzzy(sites, lambda cases: ctx.hmm_align(A.HmmBatch(cases))[0], log=log if rank == 0 else None)
+    pcases, _ = FD.purity_cases(sites)
+    cases = [c for rnd in issued for c in rnd] + pcases
+    n_large = sum(1 for s_ in sites if s_.large)
+    batch = A.HmmBatch(cases)
+    log("[rank %d] C5 setup %.1fs: %d sites -> %d alignments (%d AHMM), %d large tracts, %d sequence bytes" %
+        (rank, time.time() - t_setup, C5_SITES, batch.n, len(pcases), n_large, batch.n_bytes))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ctx.sync()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    db = ctx.hmm_upload(batch)
+    cells, pcs = ctx.hmm_work(db)
+    for _ in range(args.warmup):
+        ctx.hmm_align_resident(db)
+    ctx.sync()
+    sampler = ClockSampler(local)
+    barrier()
+    l0 = ctx.launch_count()
+    t0 = time.time()
+    ctx.timer_start()
+    for _ in range(args.steps):
+        ctx.hmm_align_resident(db)
+    ms_total = ctx.timer_stop()
+    barrier()
+    launches = ctx.launch_count() - l0
+    ms_step = max_over_ranks(ms_total / args.steps)
+    value = world * batch.n / (ms_step / 1e3) / 1e6
+    res_dev, _ = ctx.hmm_fetch(db, batch.n)
+    # end to end: host buffers in, results out, through vtn_hmm_align
+    e2e_steps = max(3, min(args.steps, 10))
+    ctx.hmm_align(batch)
+    barrier()
+    w0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        res_host, _ = ctx.hmm_align(batch)
+    barrier()
+    e2e_ms = max_over_ranks(1e3 * (time.perf_counter() - w0) / e2e_steps)
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1)
+    assert res_host.tobytes() == res_dev.tobytes()
+    ctx.hmm_free(db)
+    if rank != 0:
+        return
+    sm_mhz = clocks.get("sm_mhz") or 1965.0
+    peak_pc = 148 * 4 * 32 * sm_mhz * 1e6 / HMM_WARP_INSTR_PER_PROC_COMP / 1e9  # G proc_comp/s at full issue rate
+    ach_pc = pcs / (ms_total / args.steps / 1e3) / 1e9
+    h2d = batch.n + 4 * (3 * batch.n + 1) + batch.n_bytes
+    d2h = 96 * batch.n
+    line = {
+        "metric": "hmm_alignments_per_s", "value": value, "unit": "M alignments/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {
+            "workload": "C5: AHMM/LFHMM/RFHMM Viterbi realignment of %d synthetic STR indel sites per GPU (sample of the 5M-site config) -> %d alignments issued by the FlankDetector fuzzy-detection rounds (%d RFHMM/LFHMM + %d AHMM), reads 105-1006 bp" % (C5_SITES, batch.n, batch.n - len(pcases), len(pcases)),
+            "alignments_per_gpu": batch.n, "dp_cells_per_step": int(cells), "reference_proc_comps_per_step": int(pcs),
+            "g_cell_updates_per_s": world * cells / (ms_step / 1e3) / 1e9,
+            "l2": "back-pointer scratch of the resident warps (>= 148*16 warps x up to 1.1 MB) exceeds the 126 MB L2 for long reads; no explicit flush",
+            "sharding": "independent sites per rank, no collective",
+            "tolerance": "optimal_score bit-identical to the reference's float32 (stated tolerance 1e-4 abs), paths and integer results exact",
+        },
+        "roofline": {
+            "bound": "issue", "achieved": ach_pc, "peak": peak_pc, "unit": "G proc_comp/s", "frac": ach_pc / peak_pc,
+            "traffic": None, "kernel": "vtn_hmm_kernel",
+            "peak_source": "148 SM x 4 sub-cores x 32 lanes x %.0f MHz (median SM clock sampled under load) / %.1f warp instructions per reference proc_comp (SASS count)" % (sm_mhz, HMM_WARP_INSTR_PER_PROC_COMP),
+        },
+        "e2e": {"value": world * batch.n / (e2e_ms / 1e3) / 1e6, "unit": "M alignments/s", "h2d_bytes_per_step": int(h2d),
+                "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms, "steps": e2e_steps},
+        "gpu_launches": int(launches), "clocks": clocks,
+    }
+    if not args.no_cpu_baseline:
+        try:
+            rng = np.random.default_rng(5)
+            pick = sorted(rng.choice(len(cases), size=min(C5_CPU_SAMPLE, len(cases)), replace=False))
+            sample = [cases[i] for i in pick]
+            cv, P, dt = hmm_cpu_reference(sample, A.FLANK_DETECTOR_PARAMS)
+            line["cpu_baseline"] = {"value": cv, "unit": "M alignments/s", "cores": P, "kind": "reference",
+                                    "sample": "%d alignments drawn uniformly from this batch, each of %d concurrent single-threaded processes of the unmodified AHMM/LFHMM/RFHMM classes (oracle/_ref/hmm_ref) over the whole sample, %.1f s wall" % (len(sample), P, dt)}
+        except Exception as e:
+            line["cpu_baseline"] = {"value": None, "unit": "M alignments/s", "cores": 0, "kind": "reference", "sample": "unavailable: %s" % e}
+    print(json.dumps(line), flush=True)
+
+
 def pinned_batch(ctx, batch):
     """Copy a Batch into pinned host memory obtained from the library (vtn_host_alloc)."""
     import ctypes as C
@@ -164,6 +299,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="vtn", choices=["vtn", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c4", "c5"],
+                    help="c2 (default, the metric's configuration), c4 = STR/homopolymer reference with maximal left shifts, "
+                         "c5 = AHMM/LFHMM/RFHMM realignment (its own metric)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "vtn" else args.warmup
     rank = int(os.environ.get("RANK", 0))
@@ -171,6 +309,9 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
+        return
+    if args.workload == "c5":
+        run_c5(args, rank, world, local)
         return
 
     import torch
@@ -182,8 +323,14 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     t_setup = time.time()
-    names, seqs = synth.make_reference(scale=REF_SCALE)
-    batch = synth.make_biallelic(seqs, N_RECORDS, seed=synth.SEED_VCF_C2 + 1000 * rank)
+    if args.workload == "c4":
+        tracts = []
+        names, seqs = synth.make_reference(seed=synth.SEED_REF_C4, scale=REF_SCALE, str_frac=0.3, tracts_out=tracts)
+        batch = synth.make_str_indels(seqs, tracts, N_RECORDS, seed=synth.SEED_VCF_C4 + 1000 * rank)
+        del tracts
+    else:
+        names, seqs = synth.make_reference(scale=REF_SCALE)
+        batch = synth.make_biallelic(seqs, N_RECORDS, seed=synth.SEED_VCF_C2 + 1000 * rank)
     ctx = Context(local)
     ctx.load_reference(names, seqs)
     ref_bases = sum(s.shape[0] for s in seqs)
@@ -259,7 +406,8 @@ def main():
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
         "config": {
-            "workload": "C2: %d synthetic biallelic records per GPU (80%% SNV, 10%% del, 10%% ins, half of the indels unnormalized), synthetic %.2f Gb GRCh38-shaped reference resident in HBM" % (batch.n_rec, ref_bases / 1e9),
+            "workload": ("C2: %d synthetic biallelic records per GPU (80%% SNV, 10%% del, 10%% ins, half of the indels unnormalized), synthetic %.2f Gb GRCh38-shaped reference resident in HBM" if args.workload == "c2" else
+                         "C4: %d synthetic STR/homopolymer indels per GPU (k=1..4 whole units, 90%% at the rightmost copy of the tract), synthetic %.2f Gb reference with 30%% tandem repeats resident in HBM") % (batch.n_rec, ref_bases / 1e9),
             "records_per_gpu": batch.n_rec, "changed_per_gpu": res.n_changed,
             "l2": "inputs+outputs per step (%d MB) exceed the 126 MB L2; no explicit flush" % ((h2d + d2h) // 1000000),
             "sharding": "independent batch per rank, reference replicated, no collective",
@@ -273,7 +421,13 @@ def main():
         "gpu_launches": int(launches),
         "clocks": clocks,
     }
-    if not args.no_cpu_baseline and world >= 1:
+    if args.workload == "c4":
+        k_ = res.n_changed
+        le = np.asarray(res.chg_le[:k_], dtype=np.int64)
+        hist = np.bincount(np.minimum(np.floor(np.log2(np.maximum(le, 1))).astype(np.int64), 14), minlength=15)
+        line["config"]["left_shift_histogram_log2_bins"] = [int(x) for x in hist]
+        line["config"]["left_shift_mean"] = float(le.mean()) if k_ else 0.0
+    if not args.no_cpu_baseline and world >= 1 and args.workload == "c2":
         try:
             cv, cms, P, sample = cpu_reference_run(CPU_SAMPLE_RECORDS, 2, 1)
             line["cpu_baseline"] = {"value": cv, "unit": UNIT, "cores": P, "kind": "reference", "sample": sample}

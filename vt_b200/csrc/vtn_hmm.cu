@@ -48,6 +48,8 @@ struct HmmWarpSmem
     uint8_t motif[HMM_MAX_MOTIF + 1];
     uint8_t flank[HMM_MAX_FLANK + 1];
     uint16_t disc[HMM_MAXLEN + 8];
+    float4 bchunk[32]; // 32 columns of the previous band's last row {m,d,i,x}
+    int bpchunk[32];   // ... and its MR positions (RFHMM)
     vtn_hmm_result res;
 };
 
@@ -83,7 +85,7 @@ struct BpReader
 };
 
 template <int KIND>
-__device__ __forceinline__ void hmm_fill(const HmmConsts& T, const HmmDims& D, const HmmWarpSmem& sm, float4* bnd,
+__device__ __forceinline__ void hmm_fill(const HmmConsts& T, const HmmDims& D, HmmWarpSmem& sm, float4* bnd,
                                          int* bndp, uint32_t* bpw, int S4, int lane, HmmEnd& end)
 {
     const int rlen = D.rlen, plen = D.plen, mlen = D.mlen;
@@ -91,9 +93,10 @@ __device__ __forceinline__ void hmm_fill(const HmmConsts& T, const HmmDims& D, c
     const int rflen = KIND == VTN_HMM_RFHMM ? D.flen : 0;
     const int body = rlen - rflen;
     const int nbands = (plen + 31) >> 5;
-    const int nsteps = rlen + 31;
+    const int nsteps4 = S4 << 2; // rlen + 31 rounded up to a multiple of 4: the extra steps fall outside every row
     constexpr bool WANT_X = KIND != VTN_HMM_AHMM;
     constexpr bool WANT_P = KIND == VTN_HMM_RFHMM;
+    const bool lane0 = lane == 0;
     for (int b = 0; b < nbands; ++b)
     {
         const int i = (b << 5) + lane + 1;
@@ -114,57 +117,68 @@ __device__ __forceinline__ void hmm_fill(const HmmConsts& T, const HmmDims& D, c
         const bool p_is_mlen = row_on && k >= 1 && p_row == mlen;
         // motif position of row i-1 == mlen  <=>  this row starts a new copy (p_row == 1), for i >= 2
         const bool dg_p_is_mlen = row_on && i >= 2 && p_row == 1;
+        const unsigned ncol = row_on ? (unsigned)rlen : 0u; // columns this lane fills: 1 <= j <= ncol
         HmmCell cur = hmm_dead_cell(), dg = hmm_dead_cell();
-        uint32_t w = 0;
-        // lane 0: boundary row of the previous band, prefetched one column ahead
-        float4 nb = make_float4(HMM_NEG_INF, HMM_NEG_INF, HMM_NEG_INF, HMM_NEG_INF);
-        int nbp = 0;
-        if (lane == 0 && b > 0)
-        {
-            nb = bnd[1];
-            if (WANT_P) nbp = bndp[1];
-        }
         const bool last_band = b == nbands - 1;
-        for (int t = 0; t < nsteps; ++t)
+        uint32_t* bpo = bpw + (size_t)b * S4 * 32 + lane;
+        for (int t4 = 0; t4 < nsteps4; t4 += 4)
         {
-            const int j = t - lane + 1;
-            HmmCell up = shfl_up_cell(cur, WANT_X, WANT_P);
-            if (lane == 0)
+            // every 32 steps: the next 32 columns of the previous band's last row -> shared memory (coalesced);
+            // lane 0 then takes its "up" neighbour from there with a broadcast LDS, no divergent branch
+            if ((t4 & 31) == 0)
             {
-                up.m = nb.x, up.d = nb.y, up.i = nb.z, up.x = WANT_X ? nb.w : HMM_NEG_INF, up.pmr = nbp;
-                if (b > 0 && j + 1 <= rlen)
+                __syncwarp();
+                const int col = t4 + 1 + lane;
+                float4 v = make_float4(HMM_NEG_INF, HMM_NEG_INF, HMM_NEG_INF, HMM_NEG_INF);
+                int vp = 0;
+                if (b > 0 && col <= rlen)
                 {
-                    nb = bnd[j + 1];
-                    if (WANT_P) nbp = bndp[j + 1];
+                    v = bnd[col];
+                    if (WANT_P) vp = bndp[col];
                 }
+                sm.bchunk[lane] = v;
+                if (WANT_P) sm.bpchunk[lane] = vp;
+                __syncwarp();
             }
-            uint8_t bpb = 0;
-            if (row_on && j >= 1 && j <= rlen)
+            uint32_t w = 0;
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
             {
-                const uint8_t rb = sm.read[j - 1];
-                const float emis = base != rb ? T.e_mismatch : T.e_match;
-                HmmCell nc;
-                if (KIND == VTN_HMM_AHMM)
-                    nc = hmm_cell_ahmm(T, i, j, emis, dg, up, cur, bpb);
-                else if (KIND == VTN_HMM_LFHMM)
-                    nc = hmm_cell_lfhmm(T, i, j, lflen, p_is_mlen, emis, dg, up, cur, bpb);
-                else
-                    nc = hmm_cell_rfhmm(T, i, j, body, rflen, dg_p_is_mlen, emis, sm.flank, rb, dg, up, cur, bpb);
-                cur = nc;
-                if (j == rlen) hmm_end_row(end, KIND, i, lflen, cur);
-                if (lane == 31 && !last_band)
+                const int t = t4 + u;
+                const int j = t - lane + 1;
+                HmmCell up = shfl_up_cell(cur, WANT_X, WANT_P);
                 {
-                    bnd[j] = make_float4(cur.m, cur.d, cur.i, cur.x);
-                    if (WANT_P) bndp[j] = cur.pmr;
+                    const float4 nb = sm.bchunk[t & 31];
+                    up.m = lane0 ? nb.x : up.m;
+                    up.d = lane0 ? nb.y : up.d;
+                    up.i = lane0 ? nb.z : up.i;
+                    if (WANT_X) up.x = lane0 ? nb.w : up.x;
+                    if (WANT_P) up.pmr = lane0 ? sm.bpchunk[t & 31] : up.pmr;
                 }
+                uint8_t bpb = 0;
+                if ((unsigned)(j - 1) < ncol)
+                {
+                    const uint8_t rb = sm.read[j - 1];
+                    const float emis = base != rb ? T.e_mismatch : T.e_match;
+                    HmmCell nc;
+                    if (KIND == VTN_HMM_AHMM)
+                        nc = hmm_cell_ahmm(T, i, j, emis, dg, up, cur, bpb);
+                    else if (KIND == VTN_HMM_LFHMM)
+                        nc = hmm_cell_lfhmm(T, i, j, lflen, p_is_mlen, emis, dg, up, cur, bpb);
+                    else
+                        nc = hmm_cell_rfhmm(T, i, j, body, rflen, dg_p_is_mlen, emis, sm.flank, rb, dg, up, cur, bpb);
+                    cur = nc;
+                    if (j == rlen) hmm_end_row(end, KIND, i, lflen, cur);
+                    if (lane == 31 && !last_band)
+                    {
+                        bnd[j] = make_float4(cur.m, cur.d, cur.i, cur.x);
+                        if (WANT_P) bndp[j] = cur.pmr;
+                    }
+                }
+                dg = up;
+                w |= (uint32_t)bpb << (8 * u);
             }
-            dg = up;
-            w |= (uint32_t)bpb << (8 * (t & 3));
-            if ((t & 3) == 3 || t == nsteps - 1)
-            {
-                bpw[((size_t)b * S4 + (t >> 2)) * 32 + lane] = w;
-                w = 0;
-            }
+            bpo[(size_t)(t4 >> 2) * 32] = w;
         }
         __syncwarp();
     }

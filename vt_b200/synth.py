@@ -30,7 +30,7 @@ def _base_lut():
     return lut
 
 
-def make_contig(rng, length, str_frac=0.0, n_telomere=10000, n_block=True):
+def make_contig(rng, length, str_frac=0.0, n_telomere=10000, n_block=True, tracts_out=None):
     """One contig: i.i.d. ACGT (GC 41%), N runs at both ends and one 1-3 Mb (scaled) N block; optionally
     str_frac of the contig covered by tandem repeats (C4: unit 1-6, 40% homopolymers, tract 10-2000 bp
     log-uniform, 0-2% interruptions)."""
@@ -51,6 +51,8 @@ def make_contig(rng, length, str_frac=0.0, n_telomere=10000, n_block=True):
         vals = np.where(inter, _ACGT[rng.integers(0, 4, size=total)], vals)
         idx = np.minimum(np.repeat(starts, tl) + within, length - 1)
         s[idx] = vals
+        if tracts_out is not None:
+            tracts_out.append((starts.astype(np.int64), tl, ul.astype(np.int64)))
     t = min(n_telomere, length // 20)
     s[:t] = ord("N")
     s[length - t:] = ord("N")
@@ -62,14 +64,77 @@ def make_contig(rng, length, str_frac=0.0, n_telomere=10000, n_block=True):
     return s
 
 
-def make_reference(seed=SEED_REF_C2, scale=1.0, str_frac=0.0, contigs=None):
-    """-> (names, [uint8 arrays]).  scale < 1 shrinks every contig (tests)."""
+def make_reference(seed=SEED_REF_C2, scale=1.0, str_frac=0.0, contigs=None, tracts_out=None):
+    """-> (names, [uint8 arrays]).  scale < 1 shrinks every contig (tests).  tracts_out (a list) receives one
+    (starts, lengths, unit_lengths) triple per contig when str_frac > 0 (C4)."""
     names, seqs = [], []
     for i, (name, ln) in enumerate(contigs or GRCH38):
         rng = np.random.default_rng([seed, i])
         names.append(name)
-        seqs.append(make_contig(rng, max(int(ln * scale), 1000), str_frac=str_frac))
+        seqs.append(make_contig(rng, max(int(ln * scale), 1000), str_frac=str_frac, tracts_out=tracts_out))
     return names, seqs
+
+
+def _gather(seqs, base, gpos):
+    """global position -> base, contig by contig (keeps peak memory low)"""
+    out = np.empty(gpos.shape[0], np.uint8)
+    c = np.searchsorted(base, gpos, side="right") - 1
+    for ci in np.unique(c):
+        m = c == ci
+        out[m] = seqs[ci][gpos[m] - base[ci]]
+    return out
+
+
+def _ragged(lens):
+    """(segment id, index within segment) for segments of the given lengths"""
+    seg = np.repeat(np.arange(lens.shape[0]), lens)
+    within = np.arange(int(lens.sum())) - np.repeat(np.cumsum(lens) - lens, lens)
+    return seg, within
+
+
+def make_str_indels(seqs, tracts, n, seed=SEED_VCF_C4):
+    """C4 records: each an insertion/deletion of k in 1..4 whole repeat units, 90% at the RIGHTMOST
+    copy of a tandem-repeat tract (maximal left shift), 5% mid-tract, 5% outside tracts.  Both alleles are
+    reference substrings: deletion REF=ref[a..a+D] ALT=ref[a]; insertion REF=ref[a] ALT=ref[a]+ref[a+1-D..a]."""
+    rng = np.random.default_rng(seed)
+    lens = np.array([s.shape[0] for s in seqs], np.int64)
+    base = np.concatenate([[0], np.cumsum(lens)])[:-1]
+    n_tr = np.array([t[0].shape[0] for t in tracts], np.int64)
+    tcum = np.concatenate([[0], np.cumsum(n_tr)])
+    starts = np.concatenate([t[0] for t in tracts])
+    tls = np.concatenate([t[1] for t in tracts])
+    uls = np.concatenate([t[2] for t in tracts])
+    tcontig = np.repeat(np.arange(len(tracts)), n_tr)
+    pick = rng.integers(0, tcum[-1], size=n)
+    c = tcontig[pick]
+    ul = uls[pick]
+    k = rng.integers(1, 5, size=n)
+    D = np.minimum(k * ul, np.maximum(tls[pick] - 2, 1))
+    e = np.minimum(starts[pick] + tls[pick], lens[c] - 64)          # exclusive end of the tract
+    where = rng.random(n)
+    e = np.where(where < 0.05, e - tls[pick] // 2, e)                # mid-tract
+    e = np.where(where > 0.95, e + rng.integers(60, 5000, size=n), e)  # outside
+    e = np.clip(e, 128, lens[c] - 64)
+    is_ins = rng.random(n) < 0.5
+    a = np.where(is_ins, e - 1, e - D - 1)                            # 0-based anchor
+    o = np.lexsort((a, c))
+    c, a, D, is_ins = c[o], a[o], D[o], is_ins[o]
+    ref_len = np.where(is_ins, 1, 1 + D)
+    alt_len = np.where(is_ins, 1 + D, 1)
+    tot = ref_len + alt_len
+    off = np.concatenate([[0], np.cumsum(tot)])
+    data = np.empty(int(off[-1]), np.uint8)
+    g0 = base[c] + a
+    seg, within = _ragged(ref_len)
+    data[np.repeat(off[:-1], ref_len) + within] = _gather(seqs, base, g0[seg] + within)
+    seg, within = _ragged(alt_len)
+    src = np.where(within == 0, 0, within - D[seg])                  # insertion body = the D bases ending at the anchor
+    data[np.repeat(off[:-1] + ref_len, alt_len) + within] = _gather(seqs, base, g0[seg] + src)
+    allele_off = np.empty(2 * n + 1, np.uint32)
+    allele_off[0:2 * n:2] = off[:-1]
+    allele_off[1:2 * n:2] = off[:-1] + ref_len
+    allele_off[2 * n] = off[-1]
+    return Batch((a + 1).astype(np.int32), c.astype(np.int32), (np.arange(n + 1) * 2).astype(np.uint32), allele_off, data)
 
 
 def _sample_positions(rng, seqs, n, margin=64):
@@ -180,3 +245,32 @@ def algorithmic_bytes(batch, res):
     total = 16 * n + int(tot_allele.sum()) + int(((C * rl + S + 3) // 4).sum()) + 16 * n + 12 * k + res.n_changed_bytes
     total += int((2 * (na - 2)).sum())  # multiallelic input header: 16 + 2n
     return int(total)
+
+
+SEED_C5 = 20260106
+
+
+def make_c5_sites(n, seed=SEED_C5):
+    """C5: n indel sites, each at the right end of a tandem-repeat tract drawn like C4's (unit 1-6,
+    40% homopolymers, tract 10-2000 bp log-uniform, 0-2% interruptions) with 1200 bp of random flank on either
+    side.  -> (contig uint8 array, exact_end1[n], motifs[n]) for vt_b200.flank_detector."""
+    rng = np.random.default_rng(seed)
+    tl = np.exp(rng.uniform(np.log(10), np.log(2000), size=n)).astype(np.int64)
+    ul = np.where(rng.random(n) < 0.4, 1, rng.integers(2, 7, size=n)).astype(np.int64)
+    units = _ACGT[rng.integers(0, 4, size=(n, 6))]
+    # a unit must not be a repeat of a shorter one in its first base at least: force unit[1] != unit[0] for ul > 1
+    units[:, 1] = np.where((ul > 1) & (units[:, 1] == units[:, 0]), _ACGT[(np.searchsorted(_ACGT, units[:, 0]) + 1) % 4], units[:, 1])
+    flank = 1200
+    blk = flank + tl
+    starts = np.concatenate([[0], np.cumsum(blk)])[:-1] + flank
+    total = int(blk.sum()) + flank
+    lut = _base_lut()
+    s = lut[rng.integers(0, 256, size=total, dtype=np.uint8)]
+    seg, within = _ragged(tl)
+    vals = units[seg, within % ul[seg]]
+    inter = rng.random(vals.shape[0]) < np.repeat(rng.uniform(0, 0.02, size=n), tl)
+    vals = np.where(inter, _ACGT[rng.integers(0, 4, size=vals.shape[0])], vals)
+    s[np.repeat(starts, tl) + within] = vals
+    exact_end1 = starts + tl  # 1-based position of the tract's last base
+    motifs = [units[i, :ul[i]].tobytes().decode() for i in range(n)]
+    return s, exact_end1, motifs
