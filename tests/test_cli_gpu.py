@@ -1,0 +1,153 @@
+"""GPU: the command-line shim vt_b200/vtn (vt's `normalize` / `decompose` surface over the C ABI) against
+ (a) the reference's own golden fixtures, byte for byte: VCF output and the stripped stderr (test/test.sh:4-7 strips
+     `file.*` and `Time elapsed.*`), configuration C1;
+ (b) the UNMODIFIED reference binary oracle/_ref/vt_ref (where it was built) on synthetic VCFs with INFO / FORMAT
+     payloads, incl. `decompose -s`, `normalize -n` and window-limited ordering."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+import helpers
+
+pytestmark = pytest.mark.gpu
+VTN = os.path.join(helpers.ROOT, "vt_b200", "vtn")
+
+
+def _strip(err):
+    out = []
+    for line in err.splitlines():
+        line = re.sub(r"file.*", "file <stripped>", line)
+        line = re.sub(r"Time elapsed.*", "Time elapsed <stripped>", line)
+        out.append(line)
+    return "\n".join(out).strip()
+
+
+def _run(tool, args):
+    p = subprocess.run([tool] + args, capture_output=True, text=True)
+    return p.returncode, p.stderr
+
+
+@pytest.fixture(scope="module")
+def chr20_fasta(tmp_path_factory):
+    d = tmp_path_factory.mktemp("chr20")
+    fa = str(d / "20.fa")
+    helpers.write_fasta(fa, ["20"], [helpers.chr20_reference()])
+    return fa
+
+
+def test_c1_normalize_golden_bytes(chr20_fasta, tmp_path):
+    out = str(tmp_path / "out.vcf")
+    rc, err = _run(VTN, ["normalize", os.path.join(helpers.GOLDEN, "c1_normalize_in.vcf"), "-r", chr20_fasta, "-o", out])
+    assert rc == 0, err
+    assert open(out).read() == open(os.path.join(helpers.GOLDEN, "c1_normalize_out.vcf")).read()
+    assert _strip(err) == _strip(open(os.path.join(helpers.GOLDEN, "c1_normalize_out.stderr")).read())
+
+
+def test_c1_decompose_golden_bytes(tmp_path):
+    out = str(tmp_path / "out.vcf")
+    rc, err = _run(VTN, ["decompose", os.path.join(helpers.GOLDEN, "c1_decompose_in.vcf"), "-o", out])
+    assert rc == 0, err
+    assert open(out).read() == open(os.path.join(helpers.GOLDEN, "c1_decompose_out.vcf")).read()
+    assert _strip(err) == _strip(open(os.path.join(helpers.GOLDEN, "c1_decompose_out.stderr")).read())
+
+
+HDR = """##fileformat=VCFv4.2
+##FILTER=<ID=PASS,Description="All filters passed">
+%s##INFO=<ID=AC,Number=A,Type=Integer,Description="x">
+##INFO=<ID=AF,Number=A,Type=Float,Description="x">
+##INFO=<ID=AN,Number=1,Type=Integer,Description="x">
+##INFO=<ID=ADR,Number=R,Type=Integer,Description="x">
+##INFO=<ID=GLX,Number=G,Type=Float,Description="x">
+##INFO=<ID=DB,Number=0,Type=Flag,Description="x">
+##INFO=<ID=NM,Number=.,Type=String,Description="x">
+##FORMAT=<ID=GT,Number=1,Type=String,Description="x">
+##FORMAT=<ID=AD,Number=R,Type=Integer,Description="x">
+##FORMAT=<ID=DP,Number=1,Type=Integer,Description="x">
+##FORMAT=<ID=GQ,Number=1,Type=Integer,Description="x">
+##FORMAT=<ID=PL,Number=G,Type=Integer,Description="x">
+##FORMAT=<ID=GL,Number=G,Type=Float,Description="x">
+#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\tFORMAT\tS1\tS2\tS3
+"""
+
+
+def _synthetic_vcf(path, rng, names, seqs, n, multi):
+    """records with REF from the reference (so that normalize's REF check passes), INFO/FORMAT payloads of every
+    Number kind, floats that need re-serialisation"""
+    with open(path, "w") as f:
+        f.write(HDR % "".join("##contig=<ID=%s,length=%d>\n" % (nm, s.shape[0]) for nm, s in zip(names, seqs)))
+        for c, s in enumerate(seqs):
+            pos = np.sort(rng.choice(np.arange(50, s.shape[0] - 60), size=n, replace=False))
+            for p in pos:
+                p = int(p)
+                n_alt = int(rng.integers(2, 5)) if multi else 1
+                rl = int(rng.integers(1, 5))
+                ref = bytes(s[p:p + rl]).decode()
+                alts = []
+                while len(alts) < n_alt:
+                    k = int(rng.integers(0, 3))
+                    if k == 0:
+                        a = "ACGT"[int(rng.integers(0, 4))] + ref[1:]
+                    elif k == 1:
+                        a = ref[:1] + bytes(s[p + 1:p + 1 + int(rng.integers(1, 4))]).decode() + ref[1:]
+                    else:
+                        a = ref[:max(1, rl - int(rng.integers(1, 3)))]
+                    if a != ref and a not in alts:
+                        alts.append(a)
+                na = n_alt + 1
+                ng = na * (na + 1) // 2
+                info = "AC=%s;AF=%s;AN=6;ADR=%s;GLX=%s;NM=a,b%s" % (
+                    ",".join(str(int(x)) for x in rng.integers(0, 7, n_alt)),
+                    ",".join("%.7f" % x for x in rng.random(n_alt)),
+                    ",".join(str(int(x)) for x in rng.integers(0, 90, na)),
+                    ",".join("%.4f" % (-x * 30) for x in rng.random(ng)),
+                    ";DB" if rng.random() < 0.3 else "")
+                samples = []
+                for _ in range(3):
+                    g = sorted(int(x) for x in rng.integers(0, na, 2))
+                    sep = "|" if rng.random() < 0.3 else "/"
+                    gt = "./." if rng.random() < 0.1 else "%d%s%d" % (g[0], sep, g[1])
+                    samples.append("%s:%s:%d:%d:%s:%s" % (
+                        gt, ",".join(str(int(x)) for x in rng.integers(0, 40, na)), int(rng.integers(1, 90)), int(rng.integers(0, 99)),
+                        ",".join(str(int(x)) for x in rng.integers(0, 255, ng)), ",".join("%.3f" % (-x * 20) for x in rng.random(ng))))
+                qual = "%.2f" % (rng.random() * 3000) if rng.random() < 0.8 else "."
+                f.write("%s\t%d\t.\t%s\t%s\t%s\tPASS\t%s\tGT:AD:DP:GQ:PL:GL\t%s\n" % (names[c], p + 1, ref, ",".join(alts), qual, info, "\t".join(samples)))
+
+
+needs_ref = pytest.mark.skipif(not os.path.exists(helpers.VT_REF), reason="reference binary only exists where oracle/_ref was built")
+
+
+@needs_ref
+@pytest.mark.parametrize("smart", [False, True])
+def test_decompose_matches_reference_binary(tmp_path, smart):
+    rng = np.random.default_rng(31 + smart)
+    names, seqs = helpers.synth_reference(rng, n_contig=2, length=6000)
+    vcf = str(tmp_path / "in.vcf")
+    _synthetic_vcf(vcf, rng, names, seqs, 400, multi=True)
+    flags = ["-s"] if smart else []
+    o1, o2 = str(tmp_path / "a.vcf"), str(tmp_path / "b.vcf")
+    rc1, e1 = _run(VTN, ["decompose", vcf, "-o", o1] + flags)
+    rc2, e2 = _run(helpers.VT_REF, ["decompose", vcf, "-o", o2] + flags)
+    assert rc1 == 0 and rc2 == 0, (e1, e2)
+    assert open(o1).read() == open(o2).read()
+    assert _strip(e1) == _strip(e2)
+
+
+@needs_ref
+@pytest.mark.parametrize("flags", [[], ["-w", "50"], ["-n"]])
+def test_normalize_matches_reference_binary(tmp_path, flags):
+    rng = np.random.default_rng(41 + len(flags))
+    names, seqs = helpers.synth_reference(rng, n_contig=2, length=8000, n_runs=False)
+    fa = str(tmp_path / "ref.fa")
+    helpers.write_fasta(fa, names, seqs)
+    vcf = str(tmp_path / "in.vcf")
+    _synthetic_vcf(vcf, rng, names, seqs, 600, multi=False)
+    o1, o2 = str(tmp_path / "a.vcf"), str(tmp_path / "b.vcf")
+    rc1, e1 = _run(VTN, ["normalize", vcf, "-r", fa, "-o", o1] + flags)
+    rc2, e2 = _run(helpers.VT_REF, ["normalize", vcf, "-r", fa, "-o", o2] + flags)
+    assert rc1 == rc2 == 0, (e1[-2000:], e2[-2000:])
+    assert open(o1).read() == open(o2).read()
+    keep = lambda e: "\n".join(l for l in _strip(e).splitlines() if "Might not be sorted" not in l and not l.startswith("["))
+    assert keep(e1) == keep(e2)

@@ -1,0 +1,1050 @@
+// vtn_cli.cpp -- host shim that keeps vt's command surface for the path:  `vtn normalize`, `vtn decompose`.
+//
+// Mirrors the reference tools' flags, stderr text and VCF output (normalize.cpp:84-171, :332-382; decompose.cpp:
+// 80-150, :960-995) while the per-record arithmetic runs in libvtn's CUDA kernels through the C ABI (include/vtn.h):
+//   normalize : records are parsed from VCF text into struct-of-arrays batches -> vtn_normalize -> changed records get
+//               the new POS/alleles and INFO/OLD_VARIANT (bcf_variant2string, hts_utils.cpp:1013-1026) -> a windowed
+//               ordered writer with BCFOrderedWriter's insertion/flush rules (bcf_ordered_writer.cpp:141-300).
+//   decompose : vtn_decompose gives the (source record, ALT index) fan-out plan and the counters; the INFO/FORMAT
+//               sub-setting of each emitted record is host-side text work (decompose.cpp:210-392 plain, :393-957 -s).
+// VCF text only (plain or gzip/bgzip in, plain out); BCF and the -f filter / -i intervals are not handled here
+// (SURVEY.md 8f).  Values of Type=Float fields and QUAL are re-serialised the way htslib does when it formats a
+// record it has parsed (float32 storage, 6 significant digits), because the reference's output goes through that.
+// No CPU fallback: without a CUDA device vtn_ctx_create fails and the tool exits 1.
+#include <zlib.h>
+#include <cctype>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <ctime>
+#include <list>
+#include <map>
+#include <string>
+#include <vector>
+#include "../../include/vtn.h"
+
+namespace
+{
+const char* VERSION = "0.5"; // normalize.cpp:88 / decompose.cpp:84
+
+typedef std::pair<const char*, size_t> Tok; // a slice of the current line
+
+struct Tag
+{
+    char len_kind = '.'; // 'A','R','G','.' or 'N' (fixed count)
+    int count = 0;
+    char type = 'S'; // I(nteger) F(loat) S(tring) C(haracter) f(L)ag
+};
+
+struct Header
+{
+    std::vector<std::string> meta; // ## lines
+    std::string columns;           // #CHROM line
+    std::map<std::string, Tag> info, fmt;
+    int n_samples = 0;
+};
+
+std::string attr(const std::string& line, const char* key)
+{
+    std::string k = std::string(key) + "=";
+    size_t p = line.find(k);
+    while (p != std::string::npos && p > 0 && line[p - 1] != '<' && line[p - 1] != ',') p = line.find(k, p + 1);
+    if (p == std::string::npos) return "";
+    p += k.size();
+    size_t e = p;
+    while (e < line.size() && line[e] != ',' && line[e] != '>') ++e;
+    return line.substr(p, e - p);
+}
+
+void add_tag(std::map<std::string, Tag>& m, const std::string& line)
+{
+    Tag t;
+    std::string id = attr(line, "ID"), num = attr(line, "Number"), ty = attr(line, "Type");
+    if (num == "A" || num == "R" || num == "G" || num == ".")
+        t.len_kind = num[0];
+    else
+    {
+        t.len_kind = 'N';
+        t.count = atoi(num.c_str());
+    }
+    t.type = ty == "Integer" ? 'I' : ty == "Float" ? 'F' : ty == "Flag" ? 'L' : ty == "Character" ? 'C' : 'S';
+    m[id] = t;
+}
+
+// gz/plain line reader
+struct Reader
+{
+    gzFile f = nullptr;
+    std::vector<char> buf;
+    bool open(const std::string& path)
+    {
+        f = path == "-" ? gzdopen(0, "rb") : gzopen(path.c_str(), "rb");
+        if (f) gzbuffer(f, 1 << 20);
+        buf.resize(1 << 16);
+        return f != nullptr;
+    }
+    bool getline(std::string& out)
+    {
+        out.clear();
+        for (;;)
+        {
+            if (!gzgets(f, buf.data(), (int)buf.size())) return !out.empty();
+            size_t n = strlen(buf.data());
+            out.append(buf.data(), n);
+            if (n && out.back() == '\n')
+            {
+                out.pop_back();
+                if (!out.empty() && out.back() == '\r') out.pop_back();
+                return true;
+            }
+        }
+    }
+    ~Reader()
+    {
+        if (f) gzclose(f);
+    }
+};
+
+bool read_header(Reader& rd, Header& h, std::string& first_record)
+{
+    std::string line;
+    while (rd.getline(line))
+    {
+        if (line.compare(0, 2, "##") == 0)
+        {
+            if (line.compare(0, 7, "##INFO=") == 0) add_tag(h.info, line);
+            if (line.compare(0, 9, "##FORMAT=") == 0) add_tag(h.fmt, line);
+            h.meta.push_back(line);
+        }
+        else if (!line.empty() && line[0] == '#')
+        {
+            h.columns = line;
+            int tabs = 0;
+            for (char c : line) tabs += c == '\t';
+            h.n_samples = tabs > 8 ? tabs - 8 : 0;
+        }
+        else
+        {
+            first_record = line;
+            return true;
+        }
+    }
+    first_record.clear();
+    return !h.columns.empty();
+}
+
+// htslib formats a parsed Float (float32) with 6 significant digits: fixed notation inside [1e-4, 999999], rounding
+// half-up on the decimal expansion truncated at 1e-10, trailing zeros removed; "%g" outside (kstring.c:38-147, kputd).
+// Restated here: scale to an integer count of 1e-10 units, add half a unit of the 6th significant digit, cut.
+void put_float(std::string& out, const char* s, size_t n)
+{
+    if (n == 1 && s[0] == '.')
+    {
+        out.push_back('.');
+        return;
+    }
+    std::string tmp(s, n);
+    char* end = nullptr;
+    double d = (double)strtof(tmp.c_str(), &end);
+    if (end == tmp.c_str() || std::isnan(d) || std::isinf(d))
+    { // nan / inf / not a number: as written
+        out.append(s, n);
+        return;
+    }
+    if (d == 0)
+    {
+        out += std::signbit(d) ? "-0" : "0";
+        return;
+    }
+    if (d < 0)
+    {
+        out.push_back('-');
+        d = -d;
+    }
+    if (!(d >= 0.0001 && d <= 999999))
+    {
+        char b[64];
+        snprintf(b, sizeof b, "%g", d);
+        out += b;
+        return;
+    }
+    uint64_t units = (uint64_t)(d * 10000000000LL);
+    uint64_t half = 5; // half of the 6th significant digit, in 1e-10 units, for d in [1e-4, 1e-3)
+    for (double lim = 0.001; d >= lim && lim < 1e6; lim *= 10) half *= 10;
+    units += half;
+    char dig[32];
+    int p = snprintf(dig, sizeof dig, "%llu", (unsigned long long)units);
+    std::string r;
+    if (p <= 10)
+    { // d < 1
+        r = "0." + std::string(10 - p, '0') + std::string(dig, dig + (p < 6 ? p : 6));
+    }
+    else
+    {
+        int ni = p - 10;
+        r.assign(dig, dig + ni);
+        if (ni < 6)
+        {
+            r.push_back('.');
+            r.append(dig + ni, dig + 6);
+        }
+    }
+    if (r.find('.') != std::string::npos)
+    {
+        while (r.back() == '0') r.pop_back();
+        if (r.back() == '.') r.pop_back();
+    }
+    out += r;
+}
+
+void put_float_list(std::string& out, const char* s, size_t n)
+{
+    size_t b = 0;
+    for (size_t k = 0; k <= n; ++k)
+        if (k == n || s[k] == ',')
+        {
+            if (b) out.push_back(',');
+            put_float(out, s + b, k - b);
+            b = k + 1;
+        }
+}
+
+std::vector<Tok> split(const char* s, size_t n, char sep)
+{
+    std::vector<Tok> v;
+    size_t b = 0;
+    for (size_t k = 0; k <= n; ++k)
+        if (k == n || s[k] == sep)
+        {
+            v.push_back(Tok(s + b, k - b));
+            b = k + 1;
+        }
+    return v;
+}
+
+// INFO column as htslib re-emits it: Float-typed values canonicalised, everything else as written
+void put_info(std::string& out, const Header& h, const char* s, size_t n)
+{
+    if (n == 1 && s[0] == '.')
+    {
+        out.push_back('.');
+        return;
+    }
+    bool first = true;
+    for (const Tok& kv : split(s, n, ';'))
+    {
+        if (!kv.second) continue;
+        if (!first) out.push_back(';');
+        first = false;
+        const char* eq = (const char*)memchr(kv.first, '=', kv.second);
+        if (!eq)
+        {
+            out.append(kv.first, kv.second);
+            continue;
+        }
+        std::string key(kv.first, eq - kv.first);
+        auto it = h.info.find(key);
+        out.append(kv.first, eq - kv.first + 1);
+        if (it != h.info.end() && it->second.type == 'F')
+            put_float_list(out, eq + 1, kv.second - (eq - kv.first) - 1);
+        else
+            out.append(eq + 1, kv.second - (eq - kv.first) - 1);
+    }
+    if (first) out.push_back('.');
+}
+
+// one sample column, FORMAT keys given; Float-typed values canonicalised
+void put_sample(std::string& out, const Header& h, const std::vector<Tok>& keys, const char* s, size_t n)
+{
+    std::vector<Tok> vals = split(s, n, ':');
+    for (size_t k = 0; k < keys.size(); ++k)
+    {
+        if (k) out.push_back(':');
+        if (k >= vals.size())
+        {
+            out.push_back('.');
+            continue;
+        }
+        auto it = h.fmt.find(std::string(keys[k].first, keys[k].second));
+        if (it != h.fmt.end() && it->second.type == 'F')
+            put_float_list(out, vals[k].first, vals[k].second);
+        else
+            out.append(vals[k].first, vals[k].second);
+    }
+}
+
+// columns 6.. of a record (QUAL FILTER INFO [FORMAT samples]) re-emitted; extra_info is appended to INFO
+void put_tail(std::string& out, const Header& h, const std::vector<Tok>& col, const std::string& extra_info)
+{
+    out.push_back('\t');
+    put_float(out, col[5].first, col[5].second);
+    out.push_back('\t');
+    out.append(col[6].first, col[6].second);
+    out.push_back('\t');
+    if (extra_info.empty())
+        put_info(out, h, col[7].first, col[7].second);
+    else
+    {
+        if (!(col[7].second == 1 && col[7].first[0] == '.'))
+        {
+            put_info(out, h, col[7].first, col[7].second);
+            out.push_back(';');
+        }
+        out += extra_info;
+    }
+    if (col.size() > 8)
+    {
+        out.push_back('\t');
+        out.append(col[8].first, col[8].second);
+        std::vector<Tok> keys = split(col[8].first, col[8].second, ':');
+        for (size_t c = 9; c < col.size(); ++c)
+        {
+            out.push_back('\t');
+            put_sample(out, h, keys, col[c].first, col[c].second);
+        }
+    }
+}
+
+// BCFOrderedWriter (bcf_ordered_writer.cpp:141-300): front of the list = largest POS.
+struct OrderedWriter
+{
+    struct Rec
+    {
+        int rid;
+        int32_t pos1;
+        std::string chrom, line;
+    };
+    FILE* out = stdout;
+    int window = 0;
+    std::list<Rec> buffer;
+    void emit(const Rec& r)
+    {
+        fwrite(r.line.data(), 1, r.line.size(), out);
+        fputc('\n', out);
+    }
+    void flush(bool force)
+    {
+        if (force)
+        {
+            while (!buffer.empty())
+            {
+                emit(buffer.back());
+                buffer.pop_back();
+            }
+        }
+        else if (buffer.size() > 1)
+        {
+            int32_t cutoff = std::max(buffer.front().pos1 - window, 1);
+            while (buffer.size() > 1 && buffer.back().pos1 <= cutoff)
+            {
+                emit(buffer.back());
+                buffer.pop_back();
+            }
+        }
+    }
+    void write(Rec&& v)
+    {
+        if (!window)
+        {
+            emit(v);
+            return;
+        }
+        if (buffer.empty())
+        {
+            buffer.push_front(std::move(v));
+            return;
+        }
+        if (v.rid != buffer.back().rid)
+        {
+            flush(true);
+            buffer.push_front(std::move(v));
+            return;
+        }
+        auto i = buffer.begin();
+        for (; i != buffer.end(); ++i)
+            if (v.pos1 >= i->pos1) break; // >= keeps records of equal POS in arrival order
+        if (i == buffer.end())
+        {
+            int32_t cutoff = std::max(buffer.front().pos1 - window, 1);
+            if (v.pos1 < cutoff)
+                fprintf(stderr, "[bcf_ordered_writer.cpp:165 write] Might not be sorted for window size %d at current record %s:%d < %d (%d [last record] - %d), please increase window size to at least %d.\n",
+                        window, v.chrom.c_str(), v.pos1, cutoff, buffer.front().pos1, window, buffer.front().pos1 - v.pos1 + 1);
+        }
+        buffer.insert(i, std::move(v));
+        flush(false);
+    }
+};
+
+struct Args
+{
+    std::string in = "-", out = "-", ref;
+    int window = 10000;
+    bool quiet = false, debug = false, smart = false, opt_n = false, opt_m = false;
+    int device = 0;
+};
+
+void usage_and_exit(const char* cmd, const char* msg)
+{
+    fprintf(stderr, "%s\nusage: vtn %s [options] <in.vcf>\n", msg, cmd);
+    exit(1);
+}
+
+Args parse_args(const char* cmd, int argc, char** argv)
+{
+    Args a;
+    if (!strcmp(cmd, "decompose")) a.window = 0;
+    bool have_in = false;
+    for (int k = 1; k < argc; ++k)
+    {
+        std::string s = argv[k];
+        auto need = [&](const char* what) -> std::string {
+            if (k + 1 >= argc) usage_and_exit(cmd, (std::string("missing value for ") + what).c_str());
+            return argv[++k];
+        };
+        if (s == "-o")
+            a.out = need("-o");
+        else if (s == "-r")
+            a.ref = need("-r");
+        else if (s == "-w")
+            a.window = atoi(need("-w").c_str());
+        else if (s == "-q")
+            a.quiet = true;
+        else if (s == "-d")
+            a.debug = true;
+        else if (s == "-s")
+            a.smart = true;
+        else if (s == "-n")
+            a.opt_n = true;
+        else if (s == "-m")
+            a.opt_m = true;
+        else if (s == "--device")
+            a.device = atoi(need("--device").c_str());
+        else if (s == "-f" || s == "-i" || s == "-I")
+            usage_and_exit(cmd, "filters and intervals are not supported by this shim");
+        else if (s == "-" || s[0] != '-')
+        {
+            a.in = s;
+            have_in = true;
+        }
+        else
+            usage_and_exit(cmd, ("unknown option " + s).c_str());
+    }
+    (void)have_in;
+    return a;
+}
+
+void die(vtn_ctx* ctx, const char* what)
+{
+    fprintf(stderr, "[vtn] %s: %s\n", what, vtn_last_error(ctx));
+    exit(1);
+}
+
+FILE* open_out(const std::string& path)
+{
+    if (path == "-") return stdout;
+    FILE* f = fopen(path.c_str(), "w");
+    if (!f)
+    {
+        fprintf(stderr, "[vtn] cannot open %s for writing\n", path.c_str());
+        exit(1);
+    }
+    return f;
+}
+
+void write_header(FILE* out, const Header& h, const char* extra_line)
+{
+    for (const std::string& l : h.meta) fprintf(out, "%s\n", l.c_str());
+    fprintf(out, "%s\n", extra_line);
+    fprintf(out, "%s\n", h.columns.c_str());
+}
+
+// SoA batch under construction (vtn_batch)
+struct BatchBuf
+{
+    std::vector<std::string> lines;
+    std::vector<int32_t> pos1, rid;
+    std::vector<uint32_t> allele_beg{0}, allele_off{0};
+    std::vector<uint8_t> bytes;
+    void clear()
+    {
+        lines.clear(), pos1.clear(), rid.clear(), bytes.clear();
+        allele_beg.assign(1, 0);
+        allele_off.assign(1, 0);
+    }
+    void add_allele(const char* s, size_t n)
+    {
+        bytes.insert(bytes.end(), s, s + n);
+        allele_off.push_back((uint32_t)bytes.size());
+    }
+    vtn_batch view()
+    {
+        vtn_batch b;
+        b.n_rec = (uint32_t)pos1.size();
+        b.n_allele = (uint32_t)allele_off.size() - 1;
+        b.n_bytes = bytes.size();
+        if (bytes.empty()) bytes.push_back(0);
+        b.pos1 = pos1.data(), b.rid = rid.data(), b.allele_beg = allele_beg.data(), b.allele_off = allele_off.data();
+        b.bytes = bytes.data();
+        return b;
+    }
+};
+
+// parse CHROM POS REF ALT of one line into the batch; ALT "." = no alternate allele (as htslib's parser)
+void add_record(BatchBuf& bb, vtn_ctx* ctx, std::map<std::string, int>& rid_cache, std::string&& line)
+{
+    std::vector<Tok> col = split(line.data(), line.size(), '\t');
+    if (col.size() < 8)
+    {
+        fprintf(stderr, "[vtn] malformed VCF record (fewer than 8 columns): %s\n", line.c_str());
+        exit(1);
+    }
+    std::string chrom(col[0].first, col[0].second);
+    auto it = rid_cache.find(chrom);
+    if (it == rid_cache.end()) it = rid_cache.emplace(chrom, ctx ? vtn_ref_contig_id(ctx, chrom.c_str()) : (int)rid_cache.size()).first;
+    bb.rid.push_back(it->second);
+    bb.pos1.push_back((int32_t)strtol(col[1].first, nullptr, 10));
+    bb.add_allele(col[3].first, col[3].second);
+    if (!(col[4].second == 1 && col[4].first[0] == '.'))
+        for (const Tok& a : split(col[4].first, col[4].second, ',')) bb.add_allele(a.first, a.second);
+    bb.allele_beg.push_back((uint32_t)bb.allele_off.size() - 1);
+    bb.lines.push_back(std::move(line));
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// normalize  (Igor::normalize, normalize.cpp:174-330)
+// ------------------------------------------------------------------------------------------------------------
+int cmd_normalize(int argc, char** argv)
+{
+    Args a = parse_args("normalize", argc, argv);
+    const int strict_level = a.opt_n ? 0 : a.opt_m ? 1 : 2; // normalize.cpp:120-121
+    if (a.ref.empty()) usage_and_exit("normalize", "required: -r <reference FASTA>");
+    const bool print = !a.quiet;
+    if (print)
+    { // print_options, normalize.cpp:332-349
+        fprintf(stderr, "normalize v%s\n\n", VERSION);
+        fprintf(stderr, "options:     input VCF file                                  %s\n", a.in.c_str());
+        fprintf(stderr, "         [o] output VCF file                                 %s\n", a.out.c_str());
+        fprintf(stderr, "         [w] sorting window size                             %d\n", a.window);
+        fprintf(stderr, "         [m] no fail on masked reference inconsistency       %s\n", strict_level == 1 ? "true" : "false");
+        fprintf(stderr, "         [n] no fail on reference inconsistency              %s\n", strict_level == 0 ? "true" : "false");
+        fprintf(stderr, "         [q] quiet                                           %s\n", "false");
+        fprintf(stderr, "         [d] debug                                           %s\n", a.debug ? "true" : "false");
+        fprintf(stderr, "         [r] reference FASTA file                            %s\n\n", a.ref.c_str());
+    }
+    vtn_ctx* ctx = nullptr;
+    if (vtn_ctx_create(&ctx, a.device)) die(nullptr, "vtn_ctx_create");
+    if (vtn_ref_load_fasta(ctx, a.ref.c_str())) die(ctx, "loading the reference");
+    Reader rd;
+    if (!rd.open(a.in))
+    {
+        fprintf(stderr, "[vtn] cannot open %s\n", a.in.c_str());
+        return 1;
+    }
+    Header h;
+    std::string line;
+    if (!read_header(rd, h, line))
+    {
+        fprintf(stderr, "[vtn] %s has no VCF header\n", a.in.c_str());
+        return 1;
+    }
+    OrderedWriter ow;
+    ow.out = open_out(a.out);
+    ow.window = a.window;
+    write_header(ow.out, h, "##INFO=<ID=OLD_VARIANT,Number=.,Type=String,Description=\"Original chr:pos:ref:alt encoding\">");
+
+    const size_t BATCH = 1u << 20;
+    BatchBuf bb;
+    std::map<std::string, int> rid_cache;
+    std::vector<uint8_t> status, vtype, chg_bytes;
+    std::vector<uint32_t> chg_rec, chg_lt, chg_le, chg_rt;
+    std::vector<int32_t> chg_pos1;
+    std::vector<uint64_t> chg_off;
+    vtn_norm_counters tot;
+    memset(&tot, 0, sizeof tot);
+    bool more = !line.empty();
+    while (more)
+    {
+        bb.clear();
+        while (more && bb.lines.size() < BATCH)
+        {
+            add_record(bb, ctx, rid_cache, std::move(line));
+            more = rd.getline(line);
+        }
+        vtn_batch in = bb.view();
+        const size_t n = in.n_rec;
+        status.resize(n + 1), vtype.resize(n + 1);
+        chg_rec.resize(n + 1), chg_lt.resize(n + 1), chg_le.resize(n + 1), chg_rt.resize(n + 1), chg_pos1.resize(n + 1);
+        chg_off.resize(n + 2), chg_bytes.resize(in.n_bytes + 16);
+        vtn_norm_result out;
+        memset(&out, 0, sizeof out);
+        out.status = status.data(), out.vtype = vtype.data();
+        out.cap_changed = (uint32_t)n, out.cap_changed_bytes = in.n_bytes;
+        out.chg_rec = chg_rec.data(), out.chg_pos1 = chg_pos1.data(), out.chg_lt = chg_lt.data(), out.chg_le = chg_le.data();
+        out.chg_rt = chg_rt.data(), out.chg_off = chg_off.data(), out.chg_bytes = chg_bytes.data();
+        if (vtn_normalize(ctx, &in, &out)) die(ctx, "vtn_normalize");
+        size_t k = 0; // cursor in the changed list (input order)
+        for (size_t r = 0; r < n; ++r)
+        {
+            const std::string& ln = bb.lines[r];
+            std::vector<Tok> col = split(ln.data(), ln.size(), '\t');
+            const uint8_t st = status[r];
+            const uint32_t a0 = in.allele_beg[r], a1 = in.allele_beg[r + 1];
+            const int code = st & VTN_ST_REFCODE_MASK;
+            std::string chrom(col[0].first, col[0].second);
+            if (st & VTN_ST_FETCH_FAIL)
+            { // faidx_fetch_seq returned NULL: variant_manip.cpp:70-75
+                fprintf(stderr, "[variant_manip.cpp:72 is_not_ref_consistent] failure to extrac base from fasta file: %s:%d: >%.*s<\n",
+                        chrom.c_str(), in.pos1[r] - 1, (int)col[3].second, col[3].first);
+                exit(1);
+            }
+            if (code)
+            { // variant_manip.cpp:94-98 then normalize.cpp:205-215
+                const int64_t pos0 = in.pos1[r] - 1, rl = (int64_t)col[3].second;
+                std::vector<uint8_t> fa((size_t)rl + 1, 0);
+                int64_t got = vtn_ref_fetch(ctx, in.rid[r], pos0, pos0 + rl - 1, 0, fa.data(), rl);
+                fprintf(stderr, "[variant_manip.cpp:95 is_not_ref_consistent] reference bases not consistent: %s:%d-%d  %.*s(REF) vs %.*s(FASTA)\n",
+                        chrom.c_str(), (int)pos0, (int)(pos0 + rl - 1), (int)rl, col[3].first, (int)(got > 0 ? got : 0), (const char*)fa.data());
+                if (code > 2 - strict_level)
+                {
+                    fprintf(stderr, "[normalize.cpp:209 normalize] Normalization not performed due to inconsistent reference sequences. (use -n or -m option to relax this)\n");
+                    exit(1);
+                }
+                fprintf(stderr, "[normalize.cpp:214 normalize] Normalization skipped due to inconsistent reference sequences\n");
+            }
+            OrderedWriter::Rec rec;
+            rec.rid = in.rid[r];
+            rec.chrom = chrom;
+            rec.pos1 = in.pos1[r];
+            std::string& o = rec.line;
+            o.reserve(ln.size() + 64);
+            const bool changed = (st & VTN_ST_CHANGED) && k < out.n_changed && chg_rec[k] == r;
+            std::string extra;
+            if (changed)
+            {
+                // OLD_VARIANT = CHROM:POS:REF/ALT.. of the record after the in-place upper-casing (normalize.cpp:241-243)
+                extra = "OLD_VARIANT=" + chrom + ":" + std::to_string(in.pos1[r]) + ":";
+                for (uint32_t s = a0; s < a1; ++s)
+                {
+                    if (s > a0) extra.push_back('/');
+                    for (uint32_t q = in.allele_off[s]; q < in.allele_off[s + 1]; ++q) extra.push_back((char)toupper(in.bytes[q]));
+                }
+                rec.pos1 = chg_pos1[k];
+                o += chrom;
+                o.push_back('\t');
+                o += std::to_string(rec.pos1);
+                o.push_back('\t');
+                o.append(col[2].first, col[2].second);
+                uint64_t q = chg_off[k];
+                for (uint32_t s = a0; s < a1; ++s)
+                {
+                    const uint32_t old_len = in.allele_off[s + 1] - in.allele_off[s];
+                    const uint32_t new_len = old_len - chg_rt[k] + chg_le[k] - chg_lt[k];
+                    o.push_back(s == a0 ? '\t' : (s == a0 + 1 ? '\t' : ','));
+                    o.append((const char*)chg_bytes.data() + q, new_len);
+                    q += new_len;
+                }
+                ++k;
+            }
+            else
+            {
+                o.append(col[0].first, col[0].second);
+                o.push_back('\t');
+                o.append(col[1].first, col[1].second);
+                o.push_back('\t');
+                o.append(col[2].first, col[2].second);
+                o.push_back('\t');
+                size_t b0 = o.size();
+                o.append(col[3].first, col[3].second);
+                o.push_back('\t');
+                o.append(col[4].first, col[4].second);
+                // entered the trim path but came out unchanged: the alleles were upper-cased in place and the VCF text
+                // writer prints them that way
+                if (st & VTN_ST_ENTERED)
+                    for (size_t q = b0; q < o.size(); ++q) o[q] = (char)toupper(o[q]);
+            }
+            put_tail(o, h, col, extra);
+            ow.write(std::move(rec));
+        }
+        for (int c = 0; c < 5; ++c) tot.bi[c] += out.counters.bi[c], tot.multi[c] += out.counters.multi[c];
+        tot.no_variants += out.counters.no_variants;
+        tot.no_refs += out.counters.no_refs;
+    }
+    ow.flush(true);
+    if (ow.out != stdout) fclose(ow.out);
+    if (print)
+    { // print_stats, normalize.cpp:351-382
+        const int32_t nb = tot.bi[0] + tot.bi[1] + tot.bi[2] + tot.bi[3] + tot.bi[4];
+        const int32_t nm = tot.multi[0] + tot.multi[1] + tot.multi[2] + tot.multi[3] + tot.multi[4];
+        static const char* names[5] = {"left trimmed                      ", "right trimmed                     ", "left and right trimmed            ",
+                                       "right trimmed and left aligned    ", "left aligned                      "};
+        fprintf(stderr, "\nstats: biallelic\n");
+        for (int c = 0; c < 5; ++c) fprintf(stderr, "          no. %s: %u\n", names[c], tot.bi[c]);
+        fprintf(stderr, "\n       total no. biallelic normalized           : %d\n\n       multiallelic\n", nb);
+        for (int c = 0; c < 5; ++c) fprintf(stderr, "          no. %s: %u\n", names[c], tot.multi[c]);
+        fprintf(stderr, "\n       total no. multiallelic normalized        : %d\n\n", nm);
+        fprintf(stderr, "       total no. variants normalized            : %d\n", nb + nm);
+        fprintf(stderr, "       total no. variants observed              : %u\n", tot.no_variants);
+        fprintf(stderr, "       total no. reference observed             : %u\n\n", tot.no_refs);
+    }
+    vtn_ctx_destroy(ctx);
+    return print ? 1 : 0; // normalize() returns `print` so that main reports the elapsed time (normalize.cpp:391-400)
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// decompose  (Igor::decompose, decompose.cpp:189-958)
+// ------------------------------------------------------------------------------------------------------------
+uint32_t choose(uint32_t n, uint32_t r) // n choose r with the reference's integer arithmetic (decompose.cpp:154-186)
+{
+    if (r > n) return 0;
+    if (r == n || r == 0) return 1;
+    if (r > (n >> 1)) r = n - r;
+    uint32_t num = n, den = 1;
+    for (uint32_t i = 1; i < r; ++i)
+    {
+        num *= n - i;
+        den *= i + 1;
+    }
+    return num / den;
+}
+uint32_t ap2g(uint32_t na, uint32_t pl) // hts_utils.cpp:838-856
+{
+    if (!pl || !na) return 0;
+    if (pl == 1) return na;
+    if (pl == 2) return ((na + 1) * na) >> 1;
+    return choose(pl + na - 1, na - 1);
+}
+uint32_t ag2p(uint32_t na, uint32_t ng) // hts_utils.cpp:871-909
+{
+    if (na == ng) return 1;
+    for (uint32_t pl = 1;; ++pl)
+    {
+        uint32_t k = choose(pl + na - 1, na - 1);
+        if (k == ng) return pl;
+        if (k > ng) return 0;
+    }
+}
+
+void join(std::string& out, const std::vector<Tok>& v, bool is_float)
+{
+    // trailing holes (indices past the end of a short vector) are dropped; an empty vector prints as "."
+    size_t n = v.size();
+    while (n && !v[n - 1].first) --n;
+    if (!n)
+    {
+        out.push_back('.');
+        return;
+    }
+    for (size_t k = 0; k < n; ++k)
+    {
+        if (k) out.push_back(',');
+        if (!v[k].first)
+            out.push_back('.');
+        else if (is_float)
+            put_float(out, v[k].first, v[k].second);
+        else
+            out.append(v[k].first, v[k].second);
+    }
+}
+
+// genotype-indexed vector -> the entries of the biallelic genotypes {0, i}: entry 0 plus the cumulative-choose indices
+// (decompose.cpp:323-343, :451-511)
+std::vector<Tok> pick_g(const std::vector<Tok>& g, uint32_t ploidy, uint32_t i)
+{
+    std::vector<Tok> o;
+    const uint32_t ng2 = ap2g(2, ploidy);
+    if (!ng2) return o;
+    auto at = [&](uint32_t x) { return x < g.size() ? g[x] : Tok(nullptr, 0); };
+    o.push_back(at(0));
+    uint32_t index = 0;
+    for (uint32_t k = 1; k < ng2; ++k)
+    {
+        index += choose(ploidy - (k - 1) + i - 1, i - 1);
+        o.push_back(at(index));
+    }
+    return o;
+}
+
+// GT recode: allele 0 -> 0, allele i -> 1, any other -> missing; phase kept (decompose.cpp:300-321)
+void put_gt(std::string& out, const char* s, size_t n, uint32_t i)
+{
+    size_t b = 0;
+    for (size_t k = 0; k <= n; ++k)
+        if (k == n || s[k] == '/' || s[k] == '|')
+        {
+            if (k - b == 1 && s[b] == '.')
+                out.push_back('.');
+            else
+            {
+                uint32_t a = (uint32_t)strtoul(std::string(s + b, k - b).c_str(), nullptr, 10);
+                out.push_back(a == 0 ? '0' : a == i ? '1' : '.');
+            }
+            if (k < n) out.push_back(s[k]);
+            b = k + 1;
+        }
+}
+
+uint32_t gt_ploidy(const char* s, size_t n)
+{
+    uint32_t p = 1;
+    for (size_t k = 0; k < n; ++k) p += s[k] == '/' || s[k] == '|';
+    return p;
+}
+
+int cmd_decompose(int argc, char** argv)
+{
+    Args a = parse_args("decompose", argc, argv);
+    const bool print = !a.quiet;
+    if (print)
+    { // print_options, decompose.cpp:960-975
+        fprintf(stderr, "decompose v%s\n\n", VERSION);
+        fprintf(stderr, "options:     input VCF file        %s\n", a.in.c_str());
+        fprintf(stderr, "         [s] smart decomposition   %s (experimental)\n", a.smart ? "true" : "false");
+        fprintf(stderr, "         [o] output VCF file       %s\n\n", a.out.c_str());
+    }
+    vtn_ctx* ctx = nullptr;
+    if (vtn_ctx_create(&ctx, a.device)) die(nullptr, "vtn_ctx_create");
+    Reader rd;
+    if (!rd.open(a.in))
+    {
+        fprintf(stderr, "[vtn] cannot open %s\n", a.in.c_str());
+        return 1;
+    }
+    Header h;
+    std::string line;
+    if (!read_header(rd, h, line))
+    {
+        fprintf(stderr, "[vtn] %s has no VCF header\n", a.in.c_str());
+        return 1;
+    }
+    FILE* out = open_out(a.out);
+    write_header(out, h, "##INFO=<ID=OLD_MULTIALLELIC,Number=1,Type=String,Description=\"Original chr:pos:ref:alt encoding\">");
+    const size_t BATCH = 1u << 20;
+    BatchBuf bb;
+    std::map<std::string, int> rid_cache;
+    std::vector<uint32_t> src_rec;
+    std::vector<uint16_t> alt_idx;
+    vtn_decomp_counters tot;
+    memset(&tot, 0, sizeof tot);
+    bool more = !line.empty();
+    std::string o;
+    while (more)
+    {
+        bb.clear();
+        while (more && bb.lines.size() < BATCH)
+        {
+            add_record(bb, nullptr, rid_cache, std::move(line));
+            more = rd.getline(line);
+        }
+        vtn_batch in = bb.view();
+        const uint64_t bound = vtn_decompose_out_bound(&in);
+        src_rec.resize(bound + 1), alt_idx.resize(bound + 1);
+        uint64_t n_out = 0;
+        vtn_decomp_counters c;
+        if (vtn_decompose(ctx, &in, src_rec.data(), alt_idx.data(), &n_out, &c)) die(ctx, "vtn_decompose");
+        tot.no_variants += c.no_variants, tot.no_biallelic += c.no_biallelic, tot.no_multiallelic += c.no_multiallelic;
+        tot.no_additional_biallelic += c.no_additional_biallelic;
+        for (uint64_t q = 0; q < n_out; ++q)
+        {
+            const uint32_t r = src_rec[q], i = alt_idx[q];
+            const std::string& ln = bb.lines[r];
+            std::vector<Tok> col = split(ln.data(), ln.size(), '\t');
+            const uint32_t n_allele = in.allele_beg[r + 1] - in.allele_beg[r];
+            o.clear();
+            if (n_allele <= 2)
+            { // passes through (decompose.cpp:946-951); still re-serialised by the writer
+                o.append(col[0].first, col[4].first + col[4].second - col[0].first);
+                put_tail(o, h, col, "");
+                fwrite(o.data(), 1, o.size(), out);
+                fputc('\n', out);
+                continue;
+            }
+            std::vector<Tok> alts = split(col[4].first, col[4].second, ',');
+            o.append(col[0].first, col[3].first + col[3].second - col[0].first);
+            o.push_back('\t');
+            o.append(alts[i - 1].first, alts[i - 1].second);
+            o.push_back('\t');
+            put_float(o, col[5].first, col[5].second);
+            o.push_back('\t');
+            o.append(col[6].first, col[6].second);
+            o.push_back('\t');
+            // ---- INFO
+            std::string old = "OLD_MULTIALLELIC=" + std::string(col[0].first, col[0].second) + ":" + std::string(col[1].first, col[1].second) + ":" +
+                              std::string(col[3].first, col[3].second);
+            for (const Tok& t : alts) old += "/" + std::string(t.first, t.second);
+            bool first = true;
+            if (!(col[7].second == 1 && col[7].first[0] == '.'))
+                for (const Tok& kv : split(col[7].first, col[7].second, ';'))
+                {
+                    if (!kv.second) continue;
+                    const char* eq = (const char*)memchr(kv.first, '=', kv.second);
+                    std::string key(kv.first, eq ? (size_t)(eq - kv.first) : kv.second);
+                    auto it = h.info.find(key);
+                    const Tag* tg = it == h.info.end() ? nullptr : &it->second;
+                    std::string item;
+                    if (!eq)
+                        item = key;
+                    else
+                    {
+                        const char* vs = eq + 1;
+                        const size_t vn = kv.second - (eq - kv.first) - 1;
+                        const bool fl = tg && tg->type == 'F';
+                        const bool numeric = tg && (tg->type == 'I' || tg->type == 'F');
+                        item = key + "=";
+                        if (a.smart && tg && tg->len_kind == 'G' && numeric)
+                        { // decompose.cpp:451-511
+                            std::vector<Tok> g = split(vs, vn, ',');
+                            std::vector<Tok> sel = pick_g(g, ag2p(n_allele, (uint32_t)g.size()), i);
+                            if (sel.empty()) continue; // update with n=0 removes the tag
+                            join(item, sel, fl);
+                        }
+                        else if (a.smart && tg && tg->len_kind == 'A' && (numeric || tg->type == 'S'))
+                        { // decompose.cpp:517-586
+                            std::vector<Tok> g = split(vs, vn, ',');
+                            join(item, std::vector<Tok>{i - 1 < g.size() ? g[i - 1] : Tok(nullptr, 0)}, fl);
+                        }
+                        else if (a.smart && tg && tg->len_kind == 'R' && (numeric || tg->type == 'S'))
+                        { // decompose.cpp:587-663
+                            std::vector<Tok> g = split(vs, vn, ',');
+                            join(item, std::vector<Tok>{g[0], i < g.size() ? g[i] : Tok(nullptr, 0)}, fl);
+                        }
+                        else if (fl)
+                            put_float_list(item, vs, vn);
+                        else
+                            item.append(vs, vn);
+                    }
+                    if (!first) o.push_back(';');
+                    first = false;
+                    o += item;
+                }
+            if (!first) o.push_back(';');
+            o += old;
+            // ---- FORMAT / samples
+            if (col.size() > 9)
+            {
+                std::vector<Tok> keys = split(col[8].first, col[8].second, ':');
+                std::vector<int> keep;
+                for (size_t k = 0; k < keys.size(); ++k)
+                {
+                    std::string key(keys[k].first, keys[k].second);
+                    if (a.smart || key == "GT" || key == "PL" || key == "GL" || key == "DP") keep.push_back((int)k);
+                }
+                // ploidy = the longest GT of the record (bcf_get_genotypes pads to the maximum, decompose.cpp:247-251)
+                uint32_t ploidy = 0;
+                size_t n_g_max[64] = {0};
+                for (size_t cidx = 9; cidx < col.size(); ++cidx)
+                {
+                    std::vector<Tok> vals = split(col[cidx].first, col[cidx].second, ':');
+                    for (size_t k = 0; k < keys.size() && k < vals.size(); ++k)
+                    {
+                        if (keys[k].second == 2 && !memcmp(keys[k].first, "GT", 2)) ploidy = std::max(ploidy, gt_ploidy(vals[k].first, vals[k].second));
+                        if (k < 64)
+                        {
+                            size_t cnt = 1;
+                            for (size_t z = 0; z < vals[k].second; ++z) cnt += vals[k].first[z] == ',';
+                            n_g_max[k] = std::max(n_g_max[k], cnt);
+                        }
+                    }
+                }
+                o.push_back('\t');
+                if (keep.empty())
+                    o.push_back('.');
+                for (size_t z = 0; z < keep.size(); ++z)
+                {
+                    if (z) o.push_back(':');
+                    o.append(keys[keep[z]].first, keys[keep[z]].second);
+                }
+                for (size_t cidx = 9; cidx < col.size(); ++cidx)
+                {
+                    o.push_back('\t');
+                    if (keep.empty())
+                    {
+                        o.push_back('.');
+                        continue;
+                    }
+                    std::vector<Tok> vals = split(col[cidx].first, col[cidx].second, ':');
+                    for (size_t z = 0; z < keep.size(); ++z)
+                    {
+                        if (z) o.push_back(':');
+                        const size_t k = (size_t)keep[z];
+                        if (k >= vals.size())
+                        {
+                            o.push_back('.');
+                            continue;
+                        }
+                        std::string key(keys[k].first, keys[k].second);
+                        auto it = h.fmt.find(key);
+                        const Tag* tg = it == h.fmt.end() ? nullptr : &it->second;
+                        const bool fl = tg && tg->type == 'F';
+                        const bool numeric = tg && (tg->type == 'I' || tg->type == 'F');
+                        const bool missing = vals[k].second == 1 && vals[k].first[0] == '.';
+                        if (key == "GT")
+                            put_gt(o, vals[k].first, vals[k].second, i);
+                        else if (missing)
+                            o.push_back('.');
+                        else if (!a.smart && (key == "PL" || key == "GL"))
+                            join(o, pick_g(split(vals[k].first, vals[k].second, ','), ploidy, i), key == "GL");
+                        else if (a.smart && tg && tg->len_kind == 'G' && numeric)
+                            join(o, pick_g(split(vals[k].first, vals[k].second, ','), ag2p(n_allele, (uint32_t)(k < 64 ? n_g_max[k] : 0)), i), fl);
+                        else if (a.smart && tg && tg->len_kind == 'A' && (numeric || tg->type == 'S'))
+                        {
+                            std::vector<Tok> g = split(vals[k].first, vals[k].second, ',');
+                            join(o, std::vector<Tok>{i - 1 < g.size() ? g[i - 1] : Tok(nullptr, 0)}, fl);
+                        }
+                        else if (a.smart && tg && tg->len_kind == 'R' && (numeric || tg->type == 'S'))
+                        {
+                            std::vector<Tok> g = split(vals[k].first, vals[k].second, ',');
+                            join(o, std::vector<Tok>{g[0], i < g.size() ? g[i] : Tok(nullptr, 0)}, fl);
+                        }
+                        else if (fl)
+                            put_float_list(o, vals[k].first, vals[k].second);
+                        else
+                            o.append(vals[k].first, vals[k].second);
+                    }
+                }
+            }
+            fwrite(o.data(), 1, o.size(), out);
+            fputc('\n', out);
+        }
+    }
+    if (out != stdout) fclose(out);
+    if (print)
+    { // print_stats, decompose.cpp:977-993
+        fprintf(stderr, "\nstats: no. variants                 : %u\n", tot.no_variants);
+        fprintf(stderr, "       no. biallelic variants       : %u\n", tot.no_biallelic);
+        fprintf(stderr, "       no. multiallelic variants    : %u\n\n", tot.no_multiallelic);
+        fprintf(stderr, "       no. additional biallelics    : %u\n", tot.no_additional_biallelic);
+        fprintf(stderr, "       total no. of biallelics      : %u\n\n", tot.no_additional_biallelic + tot.no_variants);
+    }
+    vtn_ctx_destroy(ctx);
+    return 0;
+}
+} // namespace
+
+int main(int argc, char** argv)
+{
+    clock_t t0 = clock();
+    if (argc < 2)
+    {
+        fprintf(stderr, "usage: vtn normalize|decompose [options] <in.vcf>   (B200 drop-in for vt's decompose/normalize path)\n");
+        return 1;
+    }
+    std::string cmd = argv[1];
+    bool print = false;
+    if (cmd == "normalize")
+        print = cmd_normalize(argc - 1, argv + 1) != 0;
+    else if (cmd == "decompose")
+    {
+        cmd_decompose(argc - 1, argv + 1);
+        print = true;
+        for (int k = 2; k < argc; ++k) print = print && strcmp(argv[k], "-q");
+    }
+    else
+    {
+        fprintf(stderr, "Command not found: %s\n", argv[1]);
+        return 1;
+    }
+    if (print) fprintf(stderr, "Time elapsed: %.2fs\n\n", (double)(clock() - t0) / CLOCKS_PER_SEC); // main.cpp:428-433
+    return 0;
+}
