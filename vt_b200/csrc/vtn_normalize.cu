@@ -563,6 +563,9 @@ namespace
 #ifndef VTN_MIN_BLOCKS
 #define VTN_MIN_BLOCKS 5
 #endif
+#ifndef VTN_MIN_BLOCKS_FAST
+#define VTN_MIN_BLOCKS_FAST 7 // measured: 6 -> 0.297 ms, 7 -> 0.296 ms, 8 -> 0.304 ms per 10 M records (72 registers, 28 warps/SM)
+#endif
 #define VTN_AOFF_CAP (VTN_WTILE * 3 + 16)
 #define VTN_BYTES_CAP (VTN_WTILE * 8 + 64)
 
@@ -626,8 +629,14 @@ __device__ __noinline__ void write_generic_alleles(const VtnDevRef& R, const Vtn
     }
 }
 
-__global__ void __launch_bounds__(32 * VTN_WARPS, VTN_MIN_BLOCKS) vtn_normalize_kernel(VtnDevRef R, VtnDevBatchView B, VtnDevNormOut O, VtnDevScratch X,
-                                                                      uint32_t* tile_counter, uint32_t n_tiles)
+// FAST_ONLY = true : the common kernel.  Only the 2-bit register fast path is compiled in, which roughly halves the
+//                     register footprint (more resident warps); a tile in which ANY queued record is refused by the
+//                     fast path is abandoned and appended to defer_list.
+// FAST_ONLY = false: the same code with the generic byte-wise path, run over the deferred tiles only.
+// A tile is produced by exactly one of the two launches, so the tile directory / scratch contract of K2 is unchanged.
+template <bool FAST_ONLY>
+__global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAST : VTN_MIN_BLOCKS) vtn_normalize_kernel(
+    VtnDevRef R, VtnDevBatchView B, VtnDevNormOut O, VtnDevScratch X, uint32_t* defer_list, uint32_t* defer_count, uint32_t n_tiles_all)
 {
     __shared__ WarpSmem SM[VTN_WARPS];
     __shared__ uint64_t s_gbase[VTN_CONTIG_CAP];
@@ -644,16 +653,19 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, VTN_MIN_BLOCKS) vtn_normalize_
             s_clen[c] = __ldg(R.contig_len + c);
         }
     __syncthreads();
-    (void)tile_counter;
 
-    // static round-robin tiles: tiles are independent, so no scheduling atomic is needed
+    // static round-robin tiles: tiles are independent, so no scheduling atomic is needed.  The deferred launch walks
+    // defer_list instead of 0..n_tiles-1 (ti = position, tile = tile number).
+    const uint32_t n_tiles = FAST_ONLY ? n_tiles_all : min(*defer_count, n_tiles_all);
     const uint32_t tile_stride = gridDim.x * VTN_WARPS;
-    uint32_t tile = blockIdx.x * VTN_WARPS + (threadIdx.x >> 5);
+    uint32_t ti = blockIdx.x * VTN_WARPS + (threadIdx.x >> 5);
+#define TILE_OF(i) (FAST_ONLY ? (i) : __ldg(defer_list + (i)))
+    uint32_t tile = ti < n_tiles ? TILE_OF(ti) : 0;
     // header vectors of the first tile; inside the loop the NEXT tile's are prefetched into registers
     uint4 h_ab = make_uint4(0, 0, 0, 0);
     int4 h_pos = make_int4(0, 0, 0, 0), h_rid = make_int4(0, 0, 0, 0);
     uint32_t h_abx = 0;
-    if (tile < n_tiles)
+    if (ti < n_tiles)
     {
         const uint32_t r0 = tile * VTN_WTILE;
         h_ab = __ldg(reinterpret_cast<const uint4*>(B.allele_beg + r0) + lane); // arrays are padded
@@ -661,9 +673,10 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, VTN_MIN_BLOCKS) vtn_normalize_
         h_rid = __ldg(reinterpret_cast<const int4*>(B.rid + r0) + lane);
         if (lane == 31) h_abx = __ldg(B.allele_beg + r0 + VTN_WTILE);
     }
-    while (tile < n_tiles)
+    while (ti < n_tiles)
     {
-        const uint32_t next_tile = tile + tile_stride;
+        const uint32_t next_ti = ti + tile_stride;
+        const uint32_t next_tile = next_ti < n_tiles ? TILE_OF(next_ti) : 0;
         const uint32_t r0 = tile * VTN_WTILE;
         const uint32_t n_live = min((uint32_t)VTN_WTILE, B.n_rec - r0);
         // ---------------- phase 1 ----------------
@@ -676,7 +689,7 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, VTN_MIN_BLOCKS) vtn_normalize_
             reinterpret_cast<int4*>(S.pos1)[lane] = h_pos;
             reinterpret_cast<int4*>(S.rid)[lane] = h_rid;
         }
-        if (next_tile < n_tiles)
+        if (next_ti < n_tiles)
         {
             const uint32_t r1 = next_tile * VTN_WTILE;
             h_ab = __ldg(reinterpret_cast<const uint4*>(B.allele_beg + r1) + lane);
@@ -740,6 +753,8 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, VTN_MIN_BLOCKS) vtn_normalize_
         uint32_t tot_c = 0, tot_b = 0;
         uint32_t cnt_vars = n_live - nq; // the SNVs settled in phase 1 (normalize.cpp:315-322)
         uint32_t cnt_refs = 0;
+        uint32_t tile_cat = 0; // lane k < 10: category counter k of THIS tile (committed only if the tile is kept)
+        bool deferred = false;
         for (uint32_t p = 0; p < nq; p += 32)
         {
             const uint32_t e = p + lane;
@@ -767,7 +782,7 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, VTN_MIN_BLOCKS) vtn_normalize_
                 {
                     st = f.status; vt = f.vtype; T = f.T; le = f.le; lt = f.lt; nb = f.nlr + f.nla;
                 }
-                else
+                else if (!FAST_ONLY)
                 {
                     RecResult res;
                     normalize_record(R, B, rr, res);
@@ -775,6 +790,11 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, VTN_MIN_BLOCKS) vtn_normalize_
                 }
                 S.st[idx] = (uint8_t)st;
                 S.vt[idx] = (uint8_t)vt;
+            }
+            if (FAST_ONLY && __any_sync(0xffffffffu, act && !fast))
+            {
+                deferred = true; // some record needs the generic path: the whole tile goes to the second launch
+                break;
             }
             const uint32_t c = (st & VTN_ST_CHANGED) ? 1u : 0u;
             uint32_t pc, pb;
@@ -799,7 +819,7 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, VTN_MIN_BLOCKS) vtn_normalize_
                     dst += f.nlr;
                     for (uint32_t j = 0; j < f.nla; ++j, a >>= 2) dst[j] = (uint8_t)(0x47544341u >> (8 * ((uint32_t)a & 3u)));
                 }
-                else
+                else if (!FAST_ONLY)
                     write_generic_alleles(R, B, rr, T, le, lt, dst);
             }
             tot_c += pc;
@@ -811,11 +831,20 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, VTN_MIN_BLOCKS) vtn_normalize_
             for (uint32_t k = 0; k < 10; ++k)
             {
                 const unsigned mk = __ballot_sync(0xffffffffu, slot == k);
-                if (lane == (int)k) my_counter += __popc(mk);
+                if (lane == (int)k) tile_cat += __popc(mk);
             }
             cnt_refs += __popc(__ballot_sync(0xffffffffu, act && vt == VTN_VT_REF));
             cnt_vars += __popc(__ballot_sync(0xffffffffu, act && vt != VTN_VT_REF));
         }
+        if (deferred)
+        {
+            if (lane == 0) defer_list[atomicAdd(defer_count, 1u)] = tile;
+            __syncwarp();
+            ti = next_ti;
+            tile = next_tile;
+            continue;
+        }
+        my_counter += tile_cat;
         if (lane == 10) my_counter += cnt_vars;
         if (lane == 11) my_counter += cnt_refs;
         if (lane == 0)
@@ -854,8 +883,10 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, VTN_MIN_BLOCKS) vtn_normalize_
         }
 #undef AO
         __syncwarp(); // the next tile reuses this warp's shared arrays
+        ti = next_ti;
         tile = next_tile;
     }
+#undef TILE_OF
     if (lane < 12 && my_counter) atomicAdd(O.counters + lane, my_counter);
 }
 
@@ -994,19 +1025,28 @@ int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNo
     const uint32_t n_blocks2 = (n_tiles + VTC_TPB - 1) / VTC_TPB;
     VTN_CUDA(ctx, cudaMemsetAsync(tile_state, 0, 2ull * n_blocks2 * sizeof(unsigned long long), s));
     VTN_CUDA(ctx, cudaMemsetAsync(tile_counter, 0, 2 * sizeof(uint32_t), s));
-    static int per_sm = 0;
+    static int per_sm = 0, per_sm_slow = 0;
     if (!per_sm)
     {
-        VTN_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vtn_normalize_kernel, 32 * VTN_WARPS, 0));
+        VTN_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vtn_normalize_kernel<true>, 32 * VTN_WARPS, 0));
+        VTN_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_slow, vtn_normalize_kernel<false>, 32 * VTN_WARPS, 0));
         if (per_sm < 1) per_sm = 1;
+        if (per_sm_slow < 1) per_sm_slow = 1;
     }
     uint32_t grid = (uint32_t)(ctx->sm_count * per_sm);
     const uint32_t need = (n_tiles + VTN_WARPS - 1) / VTN_WARPS;
     if (grid > need) grid = need;
-    vtn_normalize_kernel<<<grid, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, scr, tile_counter, n_tiles);
+    // tile_counter[0] = number of deferred tiles, [1] = K2's ticket; the deferred-tile list lives behind K2's scan
+    // state (tile_state holds 2*n_blocks2 words of it; the allocation has 2*n_tiles words)
+    uint32_t* defer_list = reinterpret_cast<uint32_t*>(tile_state + 2ull * n_blocks2);
+    vtn_normalize_kernel<true><<<grid, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, scr, defer_list, tile_counter, n_tiles);
+    VTN_CUDA(ctx, cudaGetLastError());
+    uint32_t grid2 = (uint32_t)(ctx->sm_count * per_sm_slow);
+    if (grid2 > need) grid2 = need;
+    vtn_normalize_kernel<false><<<grid2, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, scr, defer_list, tile_counter, n_tiles);
     VTN_CUDA(ctx, cudaGetLastError());
     vtn_compact_kernel<<<n_blocks2, VTC_THREADS, 0, s>>>(in, scr, out, n_tiles, tile_state, tile_counter + 1, n_blocks2, accumulate ? 1 : 0);
     VTN_CUDA(ctx, cudaGetLastError());
-    ctx->launches += 2;
+    ctx->launches += 3;
     return VTN_OK;
 }
