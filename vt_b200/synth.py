@@ -117,6 +117,12 @@ def make_str_indels(seqs, tracts, n, seed=SEED_VCF_C4):
     e = np.clip(e, 128, lens[c] - 64)
     is_ins = rng.random(n) < 0.5
     a = np.where(is_ins, e - 1, e - D - 1)                            # 0-based anchor
+    # no variants inside / next to the N blocks (a run of N is a homopolymer millions of bases long: real call sets
+    # have no records there, and the per-base reference loop would never finish on them)
+    g_chk = base[c] + a
+    ok = (_gather(seqs, base, g_chk) != 78) & (_gather(seqs, base, g_chk - 100) != 78) & (_gather(seqs, base, g_chk + 60) != 78)
+    c, a, D, is_ins = c[ok], a[ok], D[ok], is_ins[ok]
+    n = int(c.shape[0])
     o = np.lexsort((a, c))
     c, a, D, is_ins = c[o], a[o], D[o], is_ins[o]
     ref_len = np.where(is_ins, 1, 1 + D)
@@ -274,3 +280,54 @@ def make_c5_sites(n, seed=SEED_C5):
     exact_end1 = starts + tl  # 1-based position of the tract's last base
     motifs = [units[i, :ul[i]].tobytes().decode() for i in range(n)]
     return s, exact_end1, motifs
+
+
+def make_multiallelic(seqs, n, seed=SEED_VCF_C3, max_indel=50):
+    """C3 records: every record multiallelic, n_alt = clip(1 + geometric(0.5), 2, 6); each ALT is an
+    SNV (80%), deletion (10%) or insertion (10%) with geometric(0.4) length capped at max_indel, all sharing one REF
+    that spans the longest deletion: SNV = REF with a different first base, deletion of L = REF[0] + REF[1+L:],
+    insertion of L = REF[0] + L literal bases + REF[1:]."""
+    rng = np.random.default_rng(seed)
+    rid, p0 = _sample_positions(rng, seqs, n, margin=max_indel + 8)
+    lens = np.array([s.shape[0] for s in seqs], np.int64)
+    base = np.concatenate([[0], np.cumsum(lens)])[:-1]
+    n_alt = np.clip(1 + rng.geometric(0.5, size=n), 2, 6).astype(np.int64)
+    A = int(n_alt.sum())
+    arec = np.repeat(np.arange(n), n_alt)
+    aidx = np.arange(A) - np.repeat(np.cumsum(n_alt) - n_alt, n_alt)
+    u = rng.random(A)
+    akind = np.where(u < 0.8, 0, np.where(u < 0.9, 1, 2))  # 0 snv 1 del 2 ins
+    aL = np.minimum(rng.geometric(0.4, size=A), max_indel).astype(np.int64)
+    aL[akind == 0] = 0
+    dmax = np.maximum.reduceat(np.where(akind == 1, aL, 0), np.cumsum(n_alt) - n_alt)
+    ref_len = 1 + dmax
+    alt_len = np.where(akind == 0, ref_len[arec], np.where(akind == 1, ref_len[arec] - aL, ref_len[arec] + aL))
+    # allele slots in record order: REF, ALT1..ALTk
+    n_slot = n + A
+    slot_of_ref = np.cumsum(np.concatenate([[0], 1 + n_alt]))[:-1]
+    slot_of_alt = slot_of_ref[arec] + 1 + aidx
+    slen = np.empty(n_slot, np.int64)
+    slen[slot_of_ref] = ref_len
+    slen[slot_of_alt] = alt_len
+    skind = np.full(n_slot, -1, np.int64)
+    skind[slot_of_alt] = akind
+    sL = np.zeros(n_slot, np.int64)
+    sL[slot_of_alt] = aL
+    srec = np.empty(n_slot, np.int64)
+    srec[slot_of_ref] = np.arange(n)
+    srec[slot_of_alt] = arec
+    sidx = np.zeros(n_slot, np.int64)
+    sidx[slot_of_alt] = aidx
+    off = np.concatenate([[0], np.cumsum(slen)])
+    seg, within = _ragged(slen)
+    k, L = skind[seg], sL[seg]
+    src = np.where(k == 1, np.where(within == 0, 0, within + L), np.where((k == 2) & (within > L), within - L, within))
+    g0 = base[rid] + p0
+    vals = _gather(seqs, base, g0[srec[seg]] + src)
+    body = (k == 2) & (within >= 1) & (within <= L)
+    vals = np.where(body, _ACGT[rng.integers(0, 4, size=vals.shape[0])], vals)
+    snv0 = (k == 0) & (within == 0)
+    code = np.searchsorted(_ACGT, np.where(vals == 78, 65, vals))
+    vals = np.where(snv0, _ACGT[(code + 1 + sidx[seg] % 3) % 4], vals)
+    allele_beg = np.concatenate([slot_of_ref, [n_slot]]).astype(np.uint32)
+    return Batch((p0 + 1).astype(np.int32), rid, allele_beg, off.astype(np.uint32), vals.astype(np.uint8))
