@@ -61,3 +61,35 @@ def test_decompose_empty(ctx):
     b = Batch.from_records([])
     src, alt, cnt, _ = ctx.decompose(b)
     assert len(src) == 0 and cnt == [0, 0, 0, 0]
+
+
+def test_decompose_many_alts_per_record(ctx, oracle):
+    """records with dozens of ALTs: more than 2048 outputs per 256-record tile, i.e. the emit kernel's binary-search
+    path instead of its expansion table; fused result checked against the oracle as well"""
+    rng = np.random.default_rng(51)
+    names, seqs = helpers.synth_reference(rng, n_contig=1, length=30000, n_runs=False)
+    s = seqs[0]
+    recs = []
+    for p in np.sort(rng.choice(np.arange(100, s.shape[0] - 100), size=3000, replace=False)):
+        p = int(p)
+        ref = bytes(s[p:p + 3])
+        n_alt = int(rng.integers(1, 60))
+        alts = []
+        for q in range(n_alt):
+            k = q % 3
+            if k == 0:
+                alts.append(ref[:1] + bytes(rng.choice(np.frombuffer(b"ACGT", np.uint8), size=1 + q // 3)) + ref[1:])
+            elif k == 1:
+                alts.append(ref[:1] if q < 3 else ref[:2] + bytes(rng.choice(np.frombuffer(b"ACGT", np.uint8), size=q // 3)))
+            else:
+                alts.append(bytes([b"ACGT"[(b"ACGT".index(ref[0]) + 1 + q // 3) % 4]]) + ref[1:])
+        recs.append((0, p + 1, [ref] + alts))
+    b = Batch.from_records(recs)
+    ctx.load_reference(names, seqs)
+    src, alt, cnt, got = ctx.decompose(b, normalize=True)
+    esrc, ealt, ecnt = oracle.decompose_plan(b)
+    np.testing.assert_array_equal(src, esrc)
+    np.testing.assert_array_equal(alt, ealt)
+    assert cnt == ecnt and len(src) > 60000
+    b2 = Batch.from_records(_decomposed_records(recs, esrc, ealt))
+    helpers.assert_norm_equal(got, oracle.normalize(seqs, b2), b2.n_rec)

@@ -7,6 +7,7 @@
 #include "vtn_scan.cuh"
 
 #define VTD_TILE 256
+#define VTD_XCAP 2048 // outputs per tile covered by the output->source expansion table
 
 namespace
 {
@@ -20,45 +21,74 @@ struct FusedOut
     uint8_t* bytes;
 };
 
-// totals[0] = output records, totals[1] = output allele bytes, totals[2] = records with a single allele
-__global__ void __launch_bounds__(256) vtd_count_kernel(VtnDevBatchView B, unsigned long long* totals, uint32_t* counters)
+// totals[0] = output records, totals[1] = output allele bytes, totals[2] = records with a single allele.
+// Also publishes, per tile of VTD_TILE input records, the scan words the emit kernel needs:
+//   agg_a[tile] = (output records << 31) | single-allele records,  agg_b[tile] = output allele bytes
+// so that the emit kernel never waits on another tile (every aggregate is known before it starts).
+__global__ void __launch_bounds__(VTD_TILE) vtd_count_kernel(VtnDevBatchView B, unsigned long long* totals, uint32_t* counters,
+                                                              unsigned long long* agg_a, unsigned long long* agg_b, uint32_t n_tiles)
 {
+    __shared__ unsigned long long s_ra[VTD_TILE / 32], s_rb[VTD_TILE / 32];
     unsigned long long recs = 0, bytes = 0, singles = 0;
     uint32_t nbi = 0, nmulti = 0, nadd = 0;
-    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < B.n_rec; r += gridDim.x * blockDim.x)
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x)
     {
-        uint32_t ab = __ldg(B.allele_beg + r), ae = __ldg(B.allele_beg + r + 1);
-        uint32_t n = ae - ab;
-        uint32_t o0 = __ldg(B.allele_off + ab), o1 = __ldg(B.allele_off + ab + 1), oe = __ldg(B.allele_off + ae);
-        uint32_t len0 = o1 - o0;
-        if (n > 2) { ++nmulti; nadd += n - 2; }
-        else ++nbi;
-        if (n >= 2)
+        const uint32_t r = tile * VTD_TILE + threadIdx.x;
+        unsigned long long va = 0, vb = 0;
+        if (r < B.n_rec)
         {
-            recs += n - 1;
-            bytes += (unsigned long long)(n - 1) * len0 + (oe - o1);
+            uint32_t ab = __ldg(B.allele_beg + r), ae = __ldg(B.allele_beg + r + 1);
+            uint32_t n = ae - ab;
+            uint32_t o0 = __ldg(B.allele_off + ab), o1 = __ldg(B.allele_off + ab + 1), oe = __ldg(B.allele_off + ae);
+            uint32_t len0 = o1 - o0;
+            if (n > 2) { ++nmulti; nadd += n - 2; }
+            else ++nbi;
+            if (n >= 2)
+            {
+                va = (unsigned long long)(n - 1) << 31;
+                vb = (unsigned long long)(n - 1) * len0 + (oe - o1);
+            }
+            else
+            {
+                va = (1ull << 31) | 1ull;
+                vb = len0;
+            }
         }
-        else
+        unsigned long long ra = va, rb = vb;
+        for (int o = 16; o; o >>= 1)
         {
-            recs += 1;
-            bytes += len0;
-            singles += 1;
+            ra += __shfl_xor_sync(0xffffffffu, ra, o);
+            rb += __shfl_xor_sync(0xffffffffu, rb, o);
+        }
+        __syncthreads();
+        if (lane == 0) { s_ra[warp] = ra; s_rb[warp] = rb; }
+        __syncthreads();
+        if (threadIdx.x == 0)
+        {
+            unsigned long long ta = 0, tb = 0;
+            for (int w = 0; w < VTD_TILE / 32; ++w) { ta += s_ra[w]; tb += s_rb[w]; }
+            agg_a[tile] = ta;
+            agg_b[tile] = tb;
+            recs += ta >> 31;
+            singles += ta & 0x7fffffffull;
+            bytes += tb;
         }
     }
     for (int o = 16; o; o >>= 1)
     {
-        recs += __shfl_xor_sync(0xffffffffu, recs, o);
-        bytes += __shfl_xor_sync(0xffffffffu, bytes, o);
-        singles += __shfl_xor_sync(0xffffffffu, singles, o);
         nbi += __shfl_xor_sync(0xffffffffu, nbi, o);
         nmulti += __shfl_xor_sync(0xffffffffu, nmulti, o);
         nadd += __shfl_xor_sync(0xffffffffu, nadd, o);
     }
-    if ((threadIdx.x & 31) == 0)
+    if (threadIdx.x == 0)
     {
         if (recs) atomicAdd(totals + 0, recs);
         if (bytes) atomicAdd(totals + 1, bytes);
         if (singles) atomicAdd(totals + 2, singles);
+    }
+    if (lane == 0)
+    {
         if (nbi + nmulti) atomicAdd(counters + 0, nbi + nmulti);
         if (nbi) atomicAdd(counters + 1, nbi);
         if (nmulti) atomicAdd(counters + 2, nmulti);
@@ -66,25 +96,54 @@ __global__ void __launch_bounds__(256) vtd_count_kernel(VtnDevBatchView B, unsig
     }
 }
 
+// exclusive scan of the tile aggregates in place (one block; n_tiles is a few 10^4)
+__global__ void __launch_bounds__(1024) vtd_scan_kernel(unsigned long long* agg_a, unsigned long long* agg_b, uint32_t n_tiles)
+{
+    __shared__ unsigned long long s_a[1024], s_b[1024];
+    const uint32_t per = (n_tiles + 1023) / 1024;
+    const uint32_t lo = threadIdx.x * per, hi = min(lo + per, n_tiles);
+    unsigned long long sa = 0, sb = 0;
+    for (uint32_t t = lo; t < hi; ++t) { sa += agg_a[t]; sb += agg_b[t]; }
+    s_a[threadIdx.x] = sa;
+    s_b[threadIdx.x] = sb;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1)
+    {
+        unsigned long long xa = 0, xb = 0;
+        if ((int)threadIdx.x >= o) { xa = s_a[threadIdx.x - o]; xb = s_b[threadIdx.x - o]; }
+        __syncthreads();
+        s_a[threadIdx.x] += xa;
+        s_b[threadIdx.x] += xb;
+        __syncthreads();
+    }
+    unsigned long long pa = s_a[threadIdx.x] - sa, pb = s_b[threadIdx.x] - sb;
+    for (uint32_t t = lo; t < hi; ++t)
+    {
+        const unsigned long long xa = agg_a[t], xb = agg_b[t];
+        agg_a[t] = pa;
+        agg_b[t] = pb;
+        pa += xa;
+        pb += xb;
+    }
+}
+
 // scan word A: (out_recs << 31) | singles ; scan word B: out bytes
 __global__ void __launch_bounds__(VTD_TILE) vtd_emit_kernel(VtnDevBatchView B, uint32_t* src_rec, uint16_t* alt_idx, FusedOut F,
-                                                             int materialise, unsigned long long* tile_state,
-                                                             uint32_t* tile_counter, uint32_t n_tiles)
+                                                             int materialise, const unsigned long long* tile_state,
+                                                             uint32_t n_tiles)
 {
-    __shared__ uint32_t s_tile;
     __shared__ unsigned long long s_wa[VTD_TILE / 32];
     __shared__ unsigned long long s_wb[VTD_TILE / 32];
     __shared__ unsigned long long s_base[2];
+    __shared__ unsigned long long s_ea[VTD_TILE], s_ob[VTD_TILE];
+    __shared__ uint32_t s_ab[VTD_TILE], s_n[VTD_TILE], s_k[VTD_TILE];
+    __shared__ uint16_t s_src[VTD_XCAP];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    unsigned long long* st_a = tile_state;
-    unsigned long long* st_b = tile_state + n_tiles;
-    for (;;)
+    const unsigned long long* st_a = tile_state;          // exclusive prefixes written by vtd_scan_kernel
+    const unsigned long long* st_b = tile_state + n_tiles;
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x)
     {
         __syncthreads();
-        if (tid == 0) s_tile = atomicAdd(tile_counter, 1u);
-        __syncthreads();
-        const uint32_t tile = s_tile;
-        if (tile >= n_tiles) break;
         const uint32_t r = tile * VTD_TILE + tid;
         const bool live = r < B.n_rec;
         uint32_t ab = 0, n = 0, o0 = 0, o1 = 0, oe = 0;
@@ -126,80 +185,94 @@ __global__ void __launch_bounds__(VTD_TILE) vtd_emit_kernel(VtnDevBatchView B, u
             ta += xa;
             tb += xb;
         }
-        if (warp == 0)
+        if (tid == 0)
         {
-            if (lane == 0)
+            const unsigned long long pa = __ldg(st_a + tile), pb = __ldg(st_b + tile);
+            s_base[0] = pa;
+            s_base[1] = pb;
+            if (materialise && tile == n_tiles - 1)
             {
-                st_state(st_a + tile, (tile == 0 ? VTN_FLAG_INC : VTN_FLAG_AGG) | ta);
-                st_state(st_b + tile, (tile == 0 ? VTN_FLAG_INC : VTN_FLAG_AGG) | tb);
-            }
-            unsigned long long pa = 0, pb = 0;
-            if (tile)
-            {
-                pa = lookback(st_a, (int)tile, lane);
-                pb = lookback(st_b, (int)tile, lane);
-                if (lane == 0)
-                {
-                    st_state(st_a + tile, VTN_FLAG_INC | (pa + ta));
-                    st_state(st_b + tile, VTN_FLAG_INC | (pb + tb));
-                }
-            }
-            if (lane == 0)
-            {
-                s_base[0] = pa;
-                s_base[1] = pb;
-                if (materialise && tile == n_tiles - 1)
-                {
-                    unsigned long long nr = (pa + ta) >> 31, ns = (pa + ta) & 0x7fffffffull;
-                    F.allele_beg[nr] = (uint32_t)(2 * nr - ns);
-                    F.allele_off[2 * nr - ns] = (uint32_t)(pb + tb);
-                }
+                unsigned long long nr = (pa + ta) >> 31, ns = (pa + ta) & 0x7fffffffull;
+                F.allele_beg[nr] = (uint32_t)(2 * nr - ns);
+                F.allele_off[2 * nr - ns] = (uint32_t)(pb + tb);
             }
         }
         __syncthreads();
-        if (live)
+        // ---- emission, OUTPUT-centric: thread j writes output record j of the tile, so that every store stream
+        // (src_rec, alt_idx, pos1, rid, allele_beg, allele_off pairs, bytes) is coalesced; the source record is found
+        // by binary search on the tile-local output prefix (every record emits at least one output).
+        const unsigned long long ea_t = s_base[0] + wa + (ia - va); // this thread's record: (outputs << 31 | singles) before it
+        s_ea[tid] = live ? ea_t : ~0ull;
+        s_ob[tid] = s_base[1] + wb + (ib - vb);
+        s_ab[tid] = ab;
+        s_n[tid] = n;
+        const unsigned long long k0 = s_base[0] >> 31;                 // first output of the tile
+        const uint32_t tot = (uint32_t)(ta >> 31);
+        const uint32_t krel = (uint32_t)((ea_t >> 31) - k0);           // tile-local index of this record's first output
+        s_k[tid] = live ? krel : 0xffffffffu;
+        // expansion table output -> source record (tiles with at most VTD_XCAP outputs, i.e. practically all)
+        const bool expanded = tot <= VTD_XCAP;
+        if (expanded && live)
         {
-            const unsigned long long ea = s_base[0] + wa + (ia - va);
-            unsigned long long ob = s_base[1] + wb + (ib - vb);
-            unsigned long long k = ea >> 31;
-            unsigned long long slot = 2 * k - (ea & 0x7fffffffull);
-            const int32_t pos1 = __ldg(B.pos1 + r), rid = __ldg(B.rid + r);
-            const uint32_t len0 = o1 - o0;
-            if (n < 2)
+            const uint32_t cnt = n >= 2 ? n - 1 : 1;
+            for (uint32_t q = 0; q < cnt; ++q) s_src[krel + q] = (uint16_t)tid;
+        }
+        __syncthreads();
+        const uint32_t n_in = min((uint32_t)VTD_TILE, B.n_rec - tile * VTD_TILE);
+        for (uint32_t j = tid; j < tot; j += VTD_TILE)
+        {
+            uint32_t lo;
+            if (expanded)
+                lo = s_src[j];
+            else
             {
-                src_rec[k] = r;
+                uint32_t hi = n_in - 1; // last record whose first output <= j
+                lo = 0;
+                while (lo < hi)
+                {
+                    const uint32_t mid = (lo + hi + 1) >> 1;
+                    if (s_k[mid] <= j) lo = mid;
+                    else hi = mid - 1;
+                }
+            }
+            const uint32_t rec = lo;
+            const unsigned long long ea = s_ea[rec];
+            const uint32_t rr = tile * VTD_TILE + rec;
+            const unsigned long long k = k0 + j;
+            const uint32_t i = j - s_k[rec] + 1;                       // ALT index (1-based) for n >= 2
+            const uint32_t rab = s_ab[rec], rn = s_n[rec];
+            const uint32_t ro0 = __ldg(B.allele_off + rab), ro1 = __ldg(B.allele_off + rab + 1);
+            const uint32_t len0 = ro1 - ro0;
+            const unsigned long long slot = 2 * (ea >> 31) - (ea & 0x7fffffffull) + 2ull * (i - 1);
+            src_rec[k] = rr;
+            if (rn < 2)
+            {
                 alt_idx[k] = 0;
                 if (materialise)
                 {
-                    F.pos1[k] = pos1;
-                    F.rid[k] = rid;
+                    const unsigned long long ob = s_ob[rec];
+                    F.pos1[k] = __ldg(B.pos1 + rr);
+                    F.rid[k] = __ldg(B.rid + rr);
                     F.allele_beg[k] = (uint32_t)slot;
                     F.allele_off[slot] = (uint32_t)ob;
-                    for (uint32_t j = 0; j < len0; ++j) F.bytes[ob + j] = B.bytes[o0 + j];
+                    for (uint32_t q = 0; q < len0; ++q) F.bytes[ob + q] = B.bytes[ro0 + q];
                 }
             }
             else
             {
-                uint32_t oa = o1;
-                for (uint32_t i = 1; i < n; ++i, ++k, slot += 2)
+                alt_idx[k] = (uint16_t)i;
+                if (materialise)
                 {
-                    const uint32_t oa2 = __ldg(B.allele_off + ab + i + 1);
-                    src_rec[k] = r;
-                    alt_idx[k] = (uint16_t)i;
-                    if (materialise)
-                    {
-                        F.pos1[k] = pos1;
-                        F.rid[k] = rid;
-                        F.allele_beg[k] = (uint32_t)slot;
-                        F.allele_off[slot] = (uint32_t)ob;
-                        F.allele_off[slot + 1] = (uint32_t)(ob + len0);
-                        for (uint32_t j = 0; j < len0; ++j) F.bytes[ob + j] = B.bytes[o0 + j];
-                        ob += len0;
-                        const uint32_t la = oa2 - oa;
-                        for (uint32_t j = 0; j < la; ++j) F.bytes[ob + j] = B.bytes[oa + j];
-                        ob += la;
-                    }
-                    oa = oa2;
+                    const uint32_t oa = __ldg(B.allele_off + rab + i), oa2 = __ldg(B.allele_off + rab + i + 1);
+                    const unsigned long long ob = s_ob[rec] + (unsigned long long)(i - 1) * len0 + (oa - ro1);
+                    F.pos1[k] = __ldg(B.pos1 + rr);
+                    F.rid[k] = __ldg(B.rid + rr);
+                    F.allele_beg[k] = (uint32_t)slot;
+                    F.allele_off[slot] = (uint32_t)ob;
+                    F.allele_off[slot + 1] = (uint32_t)(ob + len0);
+                    for (uint32_t q = 0; q < len0; ++q) F.bytes[ob + q] = B.bytes[ro0 + q];
+                    const uint32_t la = oa2 - oa;
+                    for (uint32_t q = 0; q < la; ++q) F.bytes[ob + len0 + q] = B.bytes[oa + q];
                 }
             }
         }
@@ -218,12 +291,16 @@ int vtn_launch_decompose(vtn_ctx* ctx, vtn_dbatch* d, bool materialise)
     unsigned long long tot[3] = {0, 0, 0};
     if (d->n_rec)
     {
-        uint32_t grid = (d->n_rec + 255) / 256;
+        const uint32_t n_tiles = (d->n_rec + VTD_TILE - 1) / VTD_TILE;
+        if (n_tiles > d->n_tiles) return vtn_set_err(ctx, VTN_E_STATE, "decompose: tile state too small");
+        uint32_t grid = n_tiles;
         uint32_t maxg = (uint32_t)ctx->sm_count * 8;
         if (grid > maxg) grid = maxg;
-        vtd_count_kernel<<<grid, 256, 0, s>>>(v, d->totals, d->counters + 12);
+        vtd_count_kernel<<<grid, VTD_TILE, 0, s>>>(v, d->totals, d->counters + 12, d->tile_state, d->tile_state + n_tiles, n_tiles);
         VTN_CUDA(ctx, cudaGetLastError());
-        ctx->launches++;
+        vtd_scan_kernel<<<1, 1024, 0, s>>>(d->tile_state, d->tile_state + n_tiles, n_tiles);
+        VTN_CUDA(ctx, cudaGetLastError());
+        ctx->launches += 2;
         VTN_CUDA(ctx, cudaMemcpyAsync(tot, d->totals, sizeof tot, cudaMemcpyDeviceToHost, s));
         VTN_CUDA(ctx, cudaStreamSynchronize(s));
     }
@@ -259,14 +336,12 @@ int vtn_launch_decompose(vtn_ctx* ctx, vtn_dbatch* d, bool materialise)
     {
         const uint32_t n_tiles = (d->n_rec + VTD_TILE - 1) / VTD_TILE;
         if (n_tiles > d->n_tiles) return vtn_set_err(ctx, VTN_E_STATE, "decompose: tile state too small");
-        VTN_CUDA(ctx, cudaMemsetAsync(d->tile_state, 0, 2ull * n_tiles * sizeof(unsigned long long), s));
-        VTN_CUDA(ctx, cudaMemsetAsync(d->tile_counter, 0, sizeof(uint32_t), s));
         int per_sm = 0;
         VTN_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vtd_emit_kernel, VTD_TILE, 0));
         if (per_sm < 1) per_sm = 1;
         uint32_t grid = (uint32_t)(ctx->sm_count * per_sm);
         if (grid > n_tiles) grid = n_tiles;
-        vtd_emit_kernel<<<grid, VTD_TILE, 0, s>>>(v, d->src_rec, d->alt_idx, F, materialise ? 1 : 0, d->tile_state, d->tile_counter, n_tiles);
+        vtd_emit_kernel<<<grid, VTD_TILE, 0, s>>>(v, d->src_rec, d->alt_idx, F, materialise ? 1 : 0, d->tile_state, n_tiles);
         VTN_CUDA(ctx, cudaGetLastError());
         ctx->launches++;
     }
