@@ -150,7 +150,7 @@ C5_CPU_SAMPLE = int(os.environ.get("VTN_BENCH_C5_CPU_SAMPLE", 400))
 HMM_REF = os.path.join(ROOT, "oracle", "_ref", "hmm_ref")
 # warp instructions per reference proc_comp in the DP inner loop, counted from the SASS of vtn_hmm_kernel
 # (profiles/r1h_hmm_sass_count.txt, dynamic count profiles/r1h_ncu_hmm.txt): the issue-rate roofline of SURVEY.md 8d
-HMM_WARP_INSTR_PER_PROC_COMP = float(os.environ.get("VTN_HMM_IPP", 9.0))
+HMM_WARP_INSTR_PER_PROC_COMP = float(os.environ.get("VTN_HMM_IPP", 7.65))
 
 
 def hmm_cpu_reference(cases, params):

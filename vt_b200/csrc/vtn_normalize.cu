@@ -636,15 +636,29 @@ __device__ __noinline__ void write_generic_alleles(const VtnDevRef& R, const Vtn
 // A tile is produced by exactly one of the two launches, so the tile directory / scratch contract of K2 is unchanged.
 template <bool FAST_ONLY>
 __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAST : VTN_MIN_BLOCKS) vtn_normalize_kernel(
-    VtnDevRef R, VtnDevBatchView B, VtnDevNormOut O, VtnDevScratch X, uint32_t* defer_list, uint32_t* defer_count, uint32_t n_tiles_all)
+    VtnDevRef R, VtnDevBatchView B, VtnDevNormOut O, VtnDevScratch X, uint32_t* defer_list, uint32_t* defer_count, uint32_t n_tiles_all,
+    unsigned long long* k2_state, uint32_t k2_state_words, int fresh)
 {
     __shared__ WarpSmem SM[VTN_WARPS];
+    __shared__ uint32_t s_lut[256]; // 4 packed 2-bit codes -> their 4 ASCII bytes (A=0 C=1 T=2 G=3)
     __shared__ uint64_t s_gbase[VTN_CONTIG_CAP];
     __shared__ int64_t s_clen[VTN_CONTIG_CAP];
     const int lane = threadIdx.x & 31;
+    if (!FAST_ONLY && *defer_count == 0) return; // nothing was deferred (the usual case): leave before any staging
     WarpSmem& S = SM[threadIdx.x >> 5];
     uint32_t my_counter = 0; // lane k < 12 accumulates counter k of this warp
     // contig table (gbase, length) into shared memory: two dependent global loads fewer per queued record
+    if (FAST_ONLY && blockIdx.x == 0)
+    { // K2's control words (it starts after this kernel): scan state, and for a fresh (non-accumulating) run the totals
+        for (uint32_t v = threadIdx.x; v < k2_state_words; v += blockDim.x) k2_state[v] = 0ull;
+        if (fresh && threadIdx.x < 2) O.totals[threadIdx.x] = 0ull;
+    }
+    for (int v = threadIdx.x; v < 256; v += blockDim.x)
+    {
+        uint32_t w = 0;
+        for (int q = 0; q < 4; ++q) w |= ((0x47544341u >> (8 * ((v >> (2 * q)) & 3))) & 0xffu) << (8 * q);
+        s_lut[v] = w;
+    }
     const bool contigs_staged = R.n_contig <= VTN_CONTIG_CAP;
     if (contigs_staged)
         for (int c = threadIdx.x; c < R.n_contig; c += blockDim.x)
@@ -813,11 +827,26 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAS
                 uint8_t* dst = X.bytes + b_lo + obl;
                 if (fast)
                 {
-                    uint64_t a = f.newR;
-                    for (uint32_t j = 0; j < f.nlr; ++j, a >>= 2) dst[j] = (uint8_t)(0x47544341u >> (8 * ((uint32_t)a & 3u)));
-                    a = f.newA;
-                    dst += f.nlr;
-                    for (uint32_t j = 0; j < f.nla; ++j, a >>= 2) dst[j] = (uint8_t)(0x47544341u >> (8 * ((uint32_t)a & 3u)));
+                    // new REF then new ALT as one code stream (<= 64 bases), expanded 4 bases per LUT lookup
+                    const uint32_t ntot = f.nlr + f.nla;
+                    uint64_t lo = f.newR, hi = 0;
+                    if (f.nlr >= 32)
+                        hi = f.newA;
+                    else
+                    {
+                        lo |= f.newA << (2 * f.nlr);
+                        hi = f.nlr ? (f.newA >> (64 - 2 * f.nlr)) : 0;
+                    }
+                    for (uint32_t j = 0; j < ntot; j += 4)
+                    {
+                        const uint32_t w = s_lut[(uint32_t)lo & 0xffu];
+                        dst[j] = (uint8_t)w;
+                        if (j + 1 < ntot) dst[j + 1] = (uint8_t)(w >> 8);
+                        if (j + 2 < ntot) dst[j + 2] = (uint8_t)(w >> 16);
+                        if (j + 3 < ntot) dst[j + 3] = (uint8_t)(w >> 24);
+                        lo = (lo >> 8) | (hi << 56);
+                        hi >>= 8;
+                    }
                 }
                 else if (!FAST_ONLY)
                     write_generic_alleles(R, B, rr, T, le, lt, dst);
@@ -891,11 +920,11 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAS
 }
 
 // ---- K2: scan of the tile directory + gather of the scratch segments into the final, input-ordered arrays ----
-#define VTC_TPB 512      // tiles per block: 10 M records -> 153 blocks, one resident wave on 148 SMs x 2
+#define VTC_TPB 512      // maximum tiles per block; the launch picks tpb <= VTC_TPB so that all blocks are resident at once, 2 per SM
 #define VTC_THREADS 1024 // threads per block: the first VTC_TPB scan the directory, all of them gather
 __global__ void __launch_bounds__(VTC_THREADS) vtn_compact_kernel(VtnDevBatchView B, VtnDevScratch X, VtnDevNormOut O, uint32_t n_tiles,
                                                               unsigned long long* state, uint32_t* ticket, uint32_t n_blocks,
-                                                              int accumulate)
+                                                              int accumulate, uint32_t tpb)
 {
     __shared__ uint32_t s_blk;
     __shared__ uint32_t s_wc[VTC_TPB / 32], s_wb[VTC_TPB / 32];
@@ -906,12 +935,13 @@ __global__ void __launch_bounds__(VTC_THREADS) vtn_compact_kernel(VtnDevBatchVie
     if (tid == 0) s_blk = atomicAdd(ticket, 1u);
     __syncthreads();
     const uint32_t blk = s_blk;
+    if (blk == 0 && tid == 0 && !accumulate) O.chg_off[0] = 0;
     unsigned long long* st_c = state;
     unsigned long long* st_b = state + n_blocks;
-    const uint32_t t = blk * VTC_TPB + tid;
-    const unsigned long long d = (tid < VTC_TPB && t < n_tiles) ? X.dir[t] : 0ull;
+    const uint32_t t = blk * tpb + tid;
+    const unsigned long long d = (tid < tpb && t < n_tiles) ? X.dir[t] : 0ull;
     const uint32_t c = (uint32_t)(d >> 32), nb = (uint32_t)d;
-    if (tid < VTC_TPB) s_nb2[tid] = nb;
+    if (tid < tpb) s_nb2[tid] = nb;
     uint32_t ic = c, ib = nb;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1)
@@ -920,11 +950,10 @@ __global__ void __launch_bounds__(VTC_THREADS) vtn_compact_kernel(VtnDevBatchVie
         const uint32_t tb = __shfl_up_sync(0xffffffffu, ib, o);
         if (lane >= o) { ic += tc; ib += tb; }
     }
-    if (lane == 31 && warp < VTC_TPB / 32) { s_wc[warp] = ic; s_wb[warp] = ib; }
+    if (lane == 31 && warp < (int)(tpb / 32)) { s_wc[warp] = ic; s_wb[warp] = ib; }
     __syncthreads();
     uint32_t wc = 0, wb = 0, tot_c = 0, tot_b = 0;
-#pragma unroll
-    for (int w = 0; w < VTC_TPB / 32; ++w)
+    for (int w = 0; w < (int)(tpb / 32); ++w)
     {
         const uint32_t xc = s_wc[w], xb = s_wb[w];
         if (w < warp) { wc += xc; wb += xb; }
@@ -968,7 +997,7 @@ __global__ void __launch_bounds__(VTC_THREADS) vtn_compact_kernel(VtnDevBatchVie
         }
     }
     __syncthreads();
-    if (tid < VTC_TPB)
+    if (tid < tpb)
     {
         s_cnt[tid] = c;
         s_bc[tid] = wc + (ic - c); // block-local exclusive prefix of changed records
@@ -980,7 +1009,7 @@ __global__ void __launch_bounds__(VTC_THREADS) vtn_compact_kernel(VtnDevBatchVie
     const unsigned long long kbase = s_base[0];
     for (uint32_t j = tid; j < tot_c; j += VTC_THREADS)
     {
-        uint32_t lo = 0, hi = VTC_TPB - 1; // last tile tt with s_bc[tt] <= j
+        uint32_t lo = 0, hi = tpb - 1; // last tile tt with s_bc[tt] <= j
         while (lo < hi)
         {
             const uint32_t mid = (lo + hi + 1) >> 1;
@@ -989,7 +1018,7 @@ __global__ void __launch_bounds__(VTC_THREADS) vtn_compact_kernel(VtnDevBatchVie
         }
         const uint32_t tt = lo;
         const uint32_t i = j - (uint32_t)s_bc[tt];
-        const uint32_t tile = blk * VTC_TPB + tt;
+        const uint32_t tile = blk * tpb + tt;
         const uint32_t src = tile * VTN_WTILE + i;
         const unsigned long long k = kbase + j;
         const uint32_t ob = X.ob[src];
@@ -1017,13 +1046,22 @@ int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNo
     cudaStream_t s = ctx->stream;
     if (!accumulate)
     {
-        VTN_CUDA(ctx, cudaMemsetAsync(out.totals, 0, 2 * sizeof(unsigned long long), s));
         VTN_CUDA(ctx, cudaMemsetAsync(out.counters, 0, 12 * sizeof(uint32_t), s));
-        VTN_CUDA(ctx, cudaMemsetAsync(out.chg_off, 0, sizeof(uint64_t), s));
+        if (n_tiles == 0)
+        {
+            VTN_CUDA(ctx, cudaMemsetAsync(out.totals, 0, 2 * sizeof(unsigned long long), s));
+            VTN_CUDA(ctx, cudaMemsetAsync(out.chg_off, 0, sizeof(uint64_t), s));
+        }
     }
     if (n_tiles == 0) return VTN_OK;
-    const uint32_t n_blocks2 = (n_tiles + VTC_TPB - 1) / VTC_TPB;
-    VTN_CUDA(ctx, cudaMemsetAsync(tile_state, 0, 2ull * n_blocks2 * sizeof(unsigned long long), s));
+    // K2 geometry: tiles per block chosen so that every block is resident at once with two blocks per SM
+    // (full occupancy, a single wave): tpb = ceil(n_tiles / (2 * SMs)) rounded up to a warp, within [32, VTC_TPB]
+    uint32_t tpb = (n_tiles + 2 * (uint32_t)ctx->sm_count - 1) / (2 * (uint32_t)ctx->sm_count);
+    tpb = (tpb + 31) & ~31u;
+    if (tpb < 32) tpb = 32;
+    if (tpb > VTC_TPB) tpb = VTC_TPB;
+    const uint32_t n_blocks2 = (n_tiles + tpb - 1) / tpb;
+    // totals, chg_off[0] and K2's scan state are zeroed by the kernels themselves (K1 block 0 / K2 block 0)
     VTN_CUDA(ctx, cudaMemsetAsync(tile_counter, 0, 2 * sizeof(uint32_t), s));
     static int per_sm = 0, per_sm_slow = 0;
     if (!per_sm)
@@ -1039,13 +1077,13 @@ int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNo
     // tile_counter[0] = number of deferred tiles, [1] = K2's ticket; the deferred-tile list lives behind K2's scan
     // state (tile_state holds 2*n_blocks2 words of it; the allocation has 2*n_tiles words)
     uint32_t* defer_list = reinterpret_cast<uint32_t*>(tile_state + 2ull * n_blocks2);
-    vtn_normalize_kernel<true><<<grid, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, scr, defer_list, tile_counter, n_tiles);
+    vtn_normalize_kernel<true><<<grid, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, scr, defer_list, tile_counter, n_tiles, tile_state, 2 * n_blocks2, accumulate ? 0 : 1);
     VTN_CUDA(ctx, cudaGetLastError());
     uint32_t grid2 = (uint32_t)(ctx->sm_count * per_sm_slow);
     if (grid2 > need) grid2 = need;
-    vtn_normalize_kernel<false><<<grid2, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, scr, defer_list, tile_counter, n_tiles);
+    vtn_normalize_kernel<false><<<grid2, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, scr, defer_list, tile_counter, n_tiles, tile_state, 0u, 0);
     VTN_CUDA(ctx, cudaGetLastError());
-    vtn_compact_kernel<<<n_blocks2, VTC_THREADS, 0, s>>>(in, scr, out, n_tiles, tile_state, tile_counter + 1, n_blocks2, accumulate ? 1 : 0);
+    vtn_compact_kernel<<<n_blocks2, VTC_THREADS, 0, s>>>(in, scr, out, n_tiles, tile_state, tile_counter + 1, n_blocks2, accumulate ? 1 : 0, tpb);
     VTN_CUDA(ctx, cudaGetLastError());
     ctx->launches += 3;
     return VTN_OK;
