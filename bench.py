@@ -519,7 +519,9 @@ def main():
         },
         "roofline": {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "traffic": None, "kernel": "vtn_normalize_kernel", "algorithmic_bytes_per_launch": alg_bytes,
+            "traffic": (607.4e6 if (args.workload == "c2" and N_RECORDS == 10_000_000 and REF_SCALE == 1.0) else None),
+            "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of vtn_normalize_kernel<fast>, one ncu --set full capture of this command (profiles/r1j_ncu_normalize_v6_split.txt); K2 adds 87.5 MB",
+            "kernel": "vtn_normalize_kernel", "algorithmic_bytes_per_launch": alg_bytes,
             "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
         },
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms, "steps": e2e_steps},
