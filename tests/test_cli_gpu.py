@@ -151,3 +151,56 @@ def test_normalize_matches_reference_binary(tmp_path, flags):
     assert open(o1).read() == open(o2).read()
     keep = lambda e: "\n".join(l for l in _strip(e).splitlines() if "Might not be sorted" not in l and not l.startswith("["))
     assert keep(e1) == keep(e2)
+
+
+def _msgs(err):
+    """bracketed messages with the source path of the reference build stripped: [/x/y/variant_manip.cpp:96 f] -> [variant_manip.cpp:96 f]"""
+    out = []
+    for l in err.splitlines():
+        if l.startswith("[") or l.startswith("FAQ"):
+            out.append(re.sub(r"^\[[^\] ]*/", "[", l))
+    return out
+
+
+@needs_ref
+@pytest.mark.parametrize("flags", [[], ["-m"], ["-n"]])
+def test_strictness_messages_and_exit_codes_match_reference(tmp_path, flags):
+    """soft-masked and N reference bases under REF: same messages, same exit code, same output"""
+    fa = str(tmp_path / "lc.fa")
+    open(fa, "w").write(">c1\nACGTACGTacgtACGTACGTAAAAAAAAAACCCCCGGGGGTTTTTACGTNNNNACGTACGT\n")
+    vcf = str(tmp_path / "lc.vcf")
+    open(vcf, "w").write("##fileformat=VCFv4.2\n##contig=<ID=c1,length=60>\n#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\n"
+                         "c1\t3\t.\tGT\tG\t.\t.\t.\nc1\t9\t.\tAC\tA\t.\t.\t.\nc1\t22\t.\taa\ta\t.\t.\t.\nc1\t48\t.\tTN\tT\t.\t.\t.\nc1\t55\t.\tCG\tC\t.\t.\t.\n")
+    o1, o2 = str(tmp_path / "a.vcf"), str(tmp_path / "b.vcf")
+    p1 = subprocess.run([VTN, "normalize", vcf, "-r", fa, "-o", o1] + flags, capture_output=True, text=True)
+    p2 = subprocess.run([helpers.VT_REF, "normalize", vcf, "-r", fa, "-o", o2] + flags, capture_output=True, text=True)
+    assert p1.returncode == p2.returncode
+    assert _msgs(p1.stderr) == _msgs(p2.stderr)
+    if p2.returncode == 0 and "-n" in flags:
+        assert open(o1).read() == open(o2).read()
+
+
+@needs_ref
+def test_unknown_contig_message_matches_reference(tmp_path):
+    fa = str(tmp_path / "lc.fa")
+    open(fa, "w").write(">c1\nACGTACGTACGTACGTACGTAAAAAAAAAACCCCCGGGGGTTTTTACGT\n")
+    vcf = str(tmp_path / "uc.vcf")
+    open(vcf, "w").write("##fileformat=VCFv4.2\n##contig=<ID=zz,length=60>\n#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\nzz\t5\t.\tAC\tA\t.\t.\t.\n")
+    p1 = subprocess.run([VTN, "normalize", vcf, "-r", fa, "-o", str(tmp_path / "a.vcf")], capture_output=True, text=True)
+    p2 = subprocess.run([helpers.VT_REF, "normalize", vcf, "-r", fa, "-o", str(tmp_path / "b.vcf")], capture_output=True, text=True)
+    assert p1.returncode == p2.returncode == 1
+    assert _msgs(p1.stderr) == _msgs(p2.stderr)
+
+
+@needs_ref
+def test_header_pass_filter_placement_matches_reference(tmp_path):
+    """htslib registers FILTER PASS right after the first header line and drops a later copy (vcf.c:809-829)"""
+    vcf = str(tmp_path / "h.vcf")
+    open(vcf, "w").write("##fileformat=VCFv4.2\n##contig=<ID=c1,length=60>\n##FILTER=<ID=q10,Description=\"x\">\n"
+                         "##FILTER=<ID=PASS,Description=\"All filters passed\">\n#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\n"
+                         "c1\t3\t.\tGT\tG,GA\t.\t.\t.\nc1\t9\t.\tA\tC\t.\tq10\t.\n")
+    o1, o2 = str(tmp_path / "a.vcf"), str(tmp_path / "b.vcf")
+    rc1, e1 = _run(VTN, ["decompose", vcf, "-o", o1])
+    rc2, e2 = _run(helpers.VT_REF, ["decompose", vcf, "-o", o2])
+    assert rc1 == rc2 == 0, (e1[-1000:], e2[-1000:])
+    assert open(o1).read() == open(o2).read()

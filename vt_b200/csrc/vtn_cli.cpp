@@ -455,7 +455,21 @@ FILE* open_out(const std::string& path)
 
 void write_header(FILE* out, const Header& h, const char* extra_line)
 {
-    for (const std::string& l : h.meta) fprintf(out, "%s\n", l.c_str());
+    // htslib parses the first line, registers FILTER PASS, then the rest (a repeated PASS line is dropped): vcf.c:809-829
+    static const char* pass_line = "##FILTER=<ID=PASS,Description=\"All filters passed\">";
+    bool pass_done = false;
+    for (size_t i = 0; i < h.meta.size(); i++)
+    {
+        const std::string& l = h.meta[i];
+        if (i > 0 && l.compare(0, 18, "##FILTER=<ID=PASS,") == 0) continue;
+        fprintf(out, "%s\n", l.c_str());
+        if (i == 0)
+        {
+            fprintf(out, "%s\n", pass_line);
+            pass_done = true;
+        }
+    }
+    if (!pass_done) fprintf(out, "%s\n", pass_line);
     fprintf(out, "%s\n", extra_line);
     fprintf(out, "%s\n", h.columns.c_str());
 }
@@ -595,8 +609,10 @@ int cmd_normalize(int argc, char** argv)
             std::string chrom(col[0].first, col[0].second);
             if (st & VTN_ST_FETCH_FAIL)
             { // faidx_fetch_seq returned NULL: variant_manip.cpp:70-75
-                fprintf(stderr, "[variant_manip.cpp:72 is_not_ref_consistent] failure to extrac base from fasta file: %s:%d: >%.*s<\n",
-                        chrom.c_str(), in.pos1[r] - 1, (int)col[3].second, col[3].first);
+                fprintf(stderr, "[E::faidx_adjust_position] The sequence \"%s\" was not found\n", chrom.c_str());
+                fprintf(stderr, "[variant_manip.cpp:72 is_not_ref_consistent] failure to extract base from fasta file: %s:%d-%d\n",
+                        chrom.c_str(), in.pos1[r] - 1, in.pos1[r] - 1 + (int)col[3].second - 1);
+                fprintf(stderr, "FAQ: http://genome.sph.umich.edu/wiki/Vt#1._vt_cannot_retrieve_sequences_from_my_reference_sequence_file\n");
                 exit(1);
             }
             if (code)
@@ -604,7 +620,7 @@ int cmd_normalize(int argc, char** argv)
                 const int64_t pos0 = in.pos1[r] - 1, rl = (int64_t)col[3].second;
                 std::vector<uint8_t> fa((size_t)rl + 1, 0);
                 int64_t got = vtn_ref_fetch(ctx, in.rid[r], pos0, pos0 + rl - 1, 0, fa.data(), rl);
-                fprintf(stderr, "[variant_manip.cpp:95 is_not_ref_consistent] reference bases not consistent: %s:%d-%d  %.*s(REF) vs %.*s(FASTA)\n",
+                fprintf(stderr, "[variant_manip.cpp:96 is_not_ref_consistent] reference bases not consistent: %s:%d-%d  %.*s(REF) vs %.*s(FASTA)\n",
                         chrom.c_str(), (int)pos0, (int)(pos0 + rl - 1), (int)rl, col[3].first, (int)(got > 0 ? got : 0), (const char*)fa.data());
                 if (code > 2 - strict_level)
                 {
