@@ -159,8 +159,8 @@ int vtn_dbatch_alloc(vtn_ctx* ctx, uint32_t n_rec, uint32_t n_allele, uint64_t n
     A(dalloc(&d->scr.bytes, n_bytes + 16));
     A(dalloc(&d->scr.dir, (size_t)d->n_tiles));
     A(dalloc(&d->scr.blo, (size_t)d->n_tiles));
-    A(dalloc(&d->tile_state, 2 * (size_t)d->n_tiles + 16)); // K2 scan state + the deferred-tile list (vtn_launch_normalize)
-    A(dalloc(&d->tile_counter, 4));
+    A(dalloc(&d->tile_state, 2 * (size_t)d->n_tiles + 16)); // decompose's tile prefixes / the deferred-tile list (vtn_launch_normalize)
+    A(dalloc(&d->tile_counter, 2 * vtn_normalize_ctl_words(d->n_tiles)));
 #undef A
     if (e != cudaSuccess)
     {

@@ -103,7 +103,7 @@ struct vtn_dbatch
     VtnDevScratch scr{};
     // scan state
     unsigned long long* tile_state = nullptr; // [2*n_tiles]
-    uint32_t* tile_counter = nullptr;
+    uint32_t* tile_counter = nullptr; // control block of vtn_launch_normalize: 2 * vtn_normalize_ctl_words(n_tiles) words
     uint32_t n_tiles = 0;
     // decompose outputs / fused intermediates
     uint32_t* src_rec = nullptr;
@@ -161,6 +161,7 @@ int vtn_set_err(vtn_ctx* ctx, int code, const std::string& msg);
 int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNormOut& out, const VtnDevScratch& scr,
                          unsigned long long* tile_state, uint32_t* tile_counter, uint32_t n_tiles, bool accumulate = false);
 uint32_t vtn_normalize_tile_records();
+size_t vtn_normalize_ctl_words(uint32_t n_tiles); // 64-bit words behind vtn_dbatch::tile_counter
 int vtn_launch_decompose(vtn_ctx* ctx, vtn_dbatch* db, bool materialise);
 bool vtn_dbatch_resize(vtn_dbatch* d, uint32_t n_rec, uint32_t n_allele, uint64_t n_bytes);
 int vtn_dbatch_alloc(vtn_ctx* ctx, uint32_t n_rec, uint32_t n_allele, uint64_t n_bytes, bool with_inputs, vtn_dbatch** out);

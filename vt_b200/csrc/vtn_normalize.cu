@@ -578,6 +578,10 @@ struct __align__(16) WarpSmem
     uint8_t st[VTN_WTILE], vt[VTN_WTILE];
 };
 #define VTN_CONTIG_CAP 256
+// K2's control block, in 64-bit words (see vtn_launch_normalize); vtn_normalize_ctl_words() sizes the allocation
+#define VTC_CTL_BASE 2
+#define VTC_CTL_AGG 4
+#define VTC_AGG_SHIFT 44
 
 __device__ __forceinline__ uint32_t warp_excl_scan(uint32_t v, int lane, uint32_t& total)
 {
@@ -637,7 +641,7 @@ __device__ __noinline__ void write_generic_alleles(const VtnDevRef& R, const Vtn
 template <bool FAST_ONLY>
 __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAST : VTN_MIN_BLOCKS) vtn_normalize_kernel(
     VtnDevRef R, VtnDevBatchView B, VtnDevNormOut O, VtnDevScratch X, uint32_t* defer_list, uint32_t* defer_count, uint32_t n_tiles_all,
-    unsigned long long* k2_state, uint32_t k2_state_words, int fresh)
+    unsigned long long* k2_ctl, uint32_t tpb, int fresh)
 {
     __shared__ WarpSmem SM[VTN_WARPS];
     __shared__ uint32_t s_lut[256]; // 4 packed 2-bit codes -> their 4 ASCII bytes (A=0 C=1 T=2 G=3)
@@ -649,9 +653,8 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAS
     uint32_t my_counter = 0; // lane k < 12 accumulates counter k of this warp
     // contig table (gbase, length) into shared memory: two dependent global loads fewer per queued record
     if (FAST_ONLY && blockIdx.x == 0)
-    { // K2's control words (it starts after this kernel): scan state, and for a fresh (non-accumulating) run the totals
-        for (uint32_t v = threadIdx.x; v < k2_state_words; v += blockDim.x) k2_state[v] = 0ull;
-        if (fresh && threadIdx.x < 2) O.totals[threadIdx.x] = 0ull;
+    { // K2's base (it starts after this kernel): the totals of the previous chunk of a chunked host call, or 0
+        if (threadIdx.x < 2) k2_ctl[VTC_CTL_BASE + threadIdx.x] = fresh ? 0ull : O.totals[threadIdx.x];
     }
     for (int v = threadIdx.x; v < 256; v += blockDim.x)
     {
@@ -880,6 +883,8 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAS
         {
             X.dir[tile] = ((unsigned long long)tot_c << 32) | tot_b;
             X.blo[tile] = b_lo;
+            // aggregate of the K2 block this tile belongs to (count << 44 | bytes): K2 sums its predecessors directly
+            if (tot_c) atomicAdd(k2_ctl + VTC_CTL_AGG + tile / tpb, ((unsigned long long)tot_c << VTC_AGG_SHIFT) | tot_b);
         }
         __syncwarp();
 
@@ -920,28 +925,30 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAS
 }
 
 // ---- K2: scan of the tile directory + gather of the scratch segments into the final, input-ordered arrays ----
+// Block b owns tiles [b*tpb, (b+1)*tpb).  Its base offsets are the plain sum of the aggregates K1 accumulated for
+// blocks 0..b-1 (one 64-bit reduction per tile there), so no block waits on another: no look-back, no ticket.
 #define VTC_TPB 512      // maximum tiles per block; the launch picks tpb <= VTC_TPB so that all blocks are resident at once, 2 per SM
-#define VTC_THREADS 1024 // threads per block: the first VTC_TPB scan the directory, all of them gather
-__global__ void __launch_bounds__(VTC_THREADS) vtn_compact_kernel(VtnDevBatchView B, VtnDevScratch X, VtnDevNormOut O, uint32_t n_tiles,
-                                                              unsigned long long* state, uint32_t* ticket, uint32_t n_blocks,
-                                                              int accumulate, uint32_t tpb)
+#define VTC_THREADS 1024 // threads per block: the first tpb scan the directory, all of them gather
+__global__ void __launch_bounds__(VTC_THREADS, 2) vtn_compact_kernel(VtnDevBatchView B, VtnDevScratch X, VtnDevNormOut O, uint32_t n_tiles,
+                                                              const unsigned long long* __restrict__ ctl, uint32_t n_blocks, uint32_t tpb)
 {
-    __shared__ uint32_t s_blk;
     __shared__ uint32_t s_wc[VTC_TPB / 32], s_wb[VTC_TPB / 32];
-    __shared__ unsigned long long s_base[2];
-    __shared__ uint32_t s_cnt[VTC_TPB], s_nb2[VTC_TPB];
-    __shared__ unsigned long long s_bc[VTC_TPB], s_bb[VTC_TPB];
+    __shared__ unsigned long long s_pc[VTC_THREADS / 32], s_pb[VTC_THREADS / 32];
+    __shared__ uint32_t s_cnt[VTC_TPB], s_nb2[VTC_TPB], s_bc[VTC_TPB + 1];
+    __shared__ unsigned long long s_bb[VTC_TPB];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_blk = atomicAdd(ticket, 1u);
-    __syncthreads();
-    const uint32_t blk = s_blk;
-    if (blk == 0 && tid == 0 && !accumulate) O.chg_off[0] = 0;
-    unsigned long long* st_c = state;
-    unsigned long long* st_b = state + n_blocks;
+    const uint32_t blk = blockIdx.x;
     const uint32_t t = blk * tpb + tid;
-    const unsigned long long d = (tid < tpb && t < n_tiles) ? X.dir[t] : 0ull;
+    const unsigned long long d = (tid < (int)tpb && t < n_tiles) ? X.dir[t] : 0ull;
+    // predecessors' aggregates (issued together with the directory load: one memory latency for both)
+    unsigned long long pc = 0, pb = 0;
+    for (uint32_t i = tid; i < blk; i += VTC_THREADS)
+    {
+        const unsigned long long a = ctl[VTC_CTL_AGG + i];
+        pc += a >> VTC_AGG_SHIFT;
+        pb += a & ((1ull << VTC_AGG_SHIFT) - 1ull);
+    }
     const uint32_t c = (uint32_t)(d >> 32), nb = (uint32_t)d;
-    if (tid < tpb) s_nb2[tid] = nb;
     uint32_t ic = c, ib = nb;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1)
@@ -950,7 +957,17 @@ __global__ void __launch_bounds__(VTC_THREADS) vtn_compact_kernel(VtnDevBatchVie
         const uint32_t tb = __shfl_up_sync(0xffffffffu, ib, o);
         if (lane >= o) { ic += tc; ib += tb; }
     }
+    if (blk > (uint32_t)(warp * 32)) // warps that loaded no aggregate skip the reduction (uniform per warp)
+    {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+        {
+            pc += __shfl_xor_sync(0xffffffffu, pc, o);
+            pb += __shfl_xor_sync(0xffffffffu, pb, o);
+        }
+    }
     if (lane == 31 && warp < (int)(tpb / 32)) { s_wc[warp] = ic; s_wb[warp] = ib; }
+    if (lane == 0) { s_pc[warp] = pc; s_pb[warp] = pb; }
     __syncthreads();
     uint32_t wc = 0, wb = 0, tot_c = 0, tot_b = 0;
     for (int w = 0; w < (int)(tpb / 32); ++w)
@@ -960,85 +977,74 @@ __global__ void __launch_bounds__(VTC_THREADS) vtn_compact_kernel(VtnDevBatchVie
         tot_c += xc;
         tot_b += xb;
     }
-    if (warp == 0)
+    unsigned long long base_c = ctl[VTC_CTL_BASE], base_b = ctl[VTC_CTL_BASE + 1];
     {
-        unsigned long long pc = 0, pb = 0;
-        if (blk == 0 && accumulate)
+        const int nw = (int)min((blk + 31u) / 32u, (uint32_t)(VTC_THREADS / 32));
+        for (int w = 0; w < nw; ++w) { base_c += s_pc[w]; base_b += s_pb[w]; }
+    }
+    if (tid == 0)
+    {
+        if (blk == 0) O.chg_off[base_c] = base_b; // a fresh run: chg_off[0] = 0; a later chunk rewrites the same value
+        if (blk == n_blocks - 1)
         {
-            // chunked host call: continue after the previous chunk's totals (same stream, already final)
-            pc = O.totals[0];
-            pb = O.totals[1];
-        }
-        if (lane == 0)
-        {
-            st_state(st_c + blk, blk == 0 ? (VTN_FLAG_INC | (pc + tot_c)) : (VTN_FLAG_AGG | tot_c));
-            st_state(st_b + blk, blk == 0 ? (VTN_FLAG_INC | (pb + tot_b)) : (VTN_FLAG_AGG | tot_b));
-        }
-        if (blk)
-        {
-            pc = lookback(st_c, (int)blk, lane);
-            pb = lookback(st_b, (int)blk, lane);
-            if (lane == 0)
-            {
-                st_state(st_c + blk, VTN_FLAG_INC | (pc + tot_c));
-                st_state(st_b + blk, VTN_FLAG_INC | (pb + tot_b));
-            }
-        }
-        if (lane == 0)
-        {
-            s_base[0] = pc;
-            s_base[1] = pb;
-            if (blk == n_blocks - 1)
-            {
-                O.totals[0] = pc + tot_c;
-                O.totals[1] = pb + tot_b;
-                O.chg_off[pc + tot_c] = pb + tot_b;
-            }
+            O.totals[0] = base_c + tot_c;
+            O.totals[1] = base_b + tot_b;
+            O.chg_off[base_c + tot_c] = base_b + tot_b;
         }
     }
-    __syncthreads();
-    if (tid < tpb)
+    if (tid < (int)tpb)
     {
         s_cnt[tid] = c;
+        s_nb2[tid] = nb;
         s_bc[tid] = wc + (ic - c); // block-local exclusive prefix of changed records
-        s_bb[tid] = s_base[1] + wb + (ib - nb);
+        s_bb[tid] = base_b + wb + (ib - nb);
     }
     __syncthreads();
     // flat gather: entry j of this block (0 <= j < tot_c) belongs to the tile found by binary search on the
     // block-local prefix; every thread has many independent loads in flight
-    const unsigned long long kbase = s_base[0];
     for (uint32_t j = tid; j < tot_c; j += VTC_THREADS)
     {
         uint32_t lo = 0, hi = tpb - 1; // last tile tt with s_bc[tt] <= j
         while (lo < hi)
         {
             const uint32_t mid = (lo + hi + 1) >> 1;
-            if ((uint32_t)s_bc[mid] <= j) lo = mid;
+            if (s_bc[mid] <= j) lo = mid;
             else hi = mid - 1;
         }
         const uint32_t tt = lo;
-        const uint32_t i = j - (uint32_t)s_bc[tt];
+        const uint32_t i = j - s_bc[tt];
         const uint32_t tile = blk * tpb + tt;
         const uint32_t src = tile * VTN_WTILE + i;
-        const unsigned long long k = kbase + j;
+        const unsigned long long k = base_c + j;
         const uint32_t ob = X.ob[src];
         const uint32_t ob_next = (i + 1 < s_cnt[tt]) ? X.ob[src + 1] : s_nb2[tt];
         const unsigned long long dst_off = s_bb[tt] + ob;
+        const uint8_t* __restrict__ sb = X.bytes + X.blo[tile] + ob;
+        uint8_t* __restrict__ db = O.chg_bytes + dst_off;
+        const uint32_t n = ob_next - ob;
         O.chg_rec[k] = X.rec[src];
         O.chg_pos1[k] = X.pos1[src];
         O.chg_lt[k] = X.lt[src];
         O.chg_le[k] = X.le[src];
         O.chg_rt[k] = X.rt[src];
         O.chg_off[k] = dst_off;
-        const uint8_t* sb = X.bytes + X.blo[tile] + ob;
-        uint8_t* db = O.chg_bytes + dst_off;
-        for (uint32_t q = 0; q < ob_next - ob; ++q) db[q] = sb[q];
+        for (uint32_t q0 = 0; q0 < n; q0 += 8)
+        { // eight byte loads in flight before the first store (one round for the usual short indel)
+            uint8_t tmp[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) tmp[q] = q0 + q < n ? sb[q0 + q] : (uint8_t)0;
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+                if (q0 + q < n) db[q0 + q] = tmp[q];
+        }
     }
 }
 
 } // namespace
 
 uint32_t vtn_normalize_tile_records() { return VTN_WTILE; }
+// 64-bit words of control block for a batch of n_tiles tiles: K2 never has more than n_tiles/32 + 1 blocks
+size_t vtn_normalize_ctl_words(uint32_t n_tiles) { return VTC_CTL_AGG + (size_t)n_tiles / 32 + 2; }
 
 int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNormOut& out, const VtnDevScratch& scr,
                          unsigned long long* tile_state, uint32_t* tile_counter, uint32_t n_tiles, bool accumulate)
@@ -1061,8 +1067,11 @@ int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNo
     if (tpb < 32) tpb = 32;
     if (tpb > VTC_TPB) tpb = VTC_TPB;
     const uint32_t n_blocks2 = (n_tiles + tpb - 1) / tpb;
-    // totals, chg_off[0] and K2's scan state are zeroed by the kernels themselves (K1 block 0 / K2 block 0)
-    VTN_CUDA(ctx, cudaMemsetAsync(tile_counter, 0, 2 * sizeof(uint32_t), s));
+    // control block (tile_counter viewed as 64-bit words): [0] low half = number of deferred tiles, [VTC_CTL_BASE..+1] =
+    // totals before this launch (written by K1 block 0), [VTC_CTL_AGG + b] = aggregate of K2 block b (accumulated by K1).
+    // One memset clears it; totals / chg_off[0] are written by the kernels themselves.
+    unsigned long long* ctl = reinterpret_cast<unsigned long long*>(tile_counter);
+    VTN_CUDA(ctx, cudaMemsetAsync(ctl, 0, (VTC_CTL_AGG + (size_t)n_blocks2) * sizeof(unsigned long long), s));
     static int per_sm = 0, per_sm_slow = 0;
     if (!per_sm)
     {
@@ -1074,16 +1083,14 @@ int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNo
     uint32_t grid = (uint32_t)(ctx->sm_count * per_sm);
     const uint32_t need = (n_tiles + VTN_WARPS - 1) / VTN_WARPS;
     if (grid > need) grid = need;
-    // tile_counter[0] = number of deferred tiles, [1] = K2's ticket; the deferred-tile list lives behind K2's scan
-    // state (tile_state holds 2*n_blocks2 words of it; the allocation has 2*n_tiles words)
-    uint32_t* defer_list = reinterpret_cast<uint32_t*>(tile_state + 2ull * n_blocks2);
-    vtn_normalize_kernel<true><<<grid, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, scr, defer_list, tile_counter, n_tiles, tile_state, 2 * n_blocks2, accumulate ? 0 : 1);
+    uint32_t* defer_list = reinterpret_cast<uint32_t*>(tile_state); // at most n_tiles entries
+    vtn_normalize_kernel<true><<<grid, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, scr, defer_list, tile_counter, n_tiles, ctl, tpb, accumulate ? 0 : 1);
     VTN_CUDA(ctx, cudaGetLastError());
     uint32_t grid2 = (uint32_t)(ctx->sm_count * per_sm_slow);
     if (grid2 > need) grid2 = need;
-    vtn_normalize_kernel<false><<<grid2, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, scr, defer_list, tile_counter, n_tiles, tile_state, 0u, 0);
+    vtn_normalize_kernel<false><<<grid2, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, scr, defer_list, tile_counter, n_tiles, ctl, tpb, 0);
     VTN_CUDA(ctx, cudaGetLastError());
-    vtn_compact_kernel<<<n_blocks2, VTC_THREADS, 0, s>>>(in, scr, out, n_tiles, tile_state, tile_counter + 1, n_blocks2, accumulate ? 1 : 0, tpb);
+    vtn_compact_kernel<<<n_blocks2, VTC_THREADS, 0, s>>>(in, scr, out, n_tiles, ctl, n_blocks2, tpb);
     VTN_CUDA(ctx, cudaGetLastError());
     ctx->launches += 3;
     return VTN_OK;
