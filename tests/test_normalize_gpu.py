@@ -87,6 +87,62 @@ def test_long_shift_and_long_alleles(ctx, oracle):
     assert int(got.chg_le.max()) > 20000
 
 
+def test_tandem_repeat_tracts_warp_lookahead(ctx, oracle):
+    """Short indels (fast path) at the right end of tandem-repeat tracts of 10..6000 bases: shifts beyond 64 bases go
+    through the warp-cooperative look-ahead.  Tracts start at the contig start, contain N / lower-case / IUPAC bases and
+    interruptions, so the look-ahead must hand back to the per-base walk at the right place."""
+    rng = np.random.default_rng(77)
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+    parts, tracts, at = [], [], 0
+
+    def add(a):
+        nonlocal at
+        parts.append(a)
+        at += a.shape[0]
+    # a tract right at the contig start (cap reached), then flank / tract pairs
+    for k in range(160):
+        ulen = int(rng.integers(1, 7))
+        unit = rng.choice(acgt, size=ulen)
+        tlen = int(np.exp(rng.uniform(np.log(10), np.log(6000))))
+        if k == 0:
+            tlen = 2500
+        else:
+            add(rng.choice(acgt, size=int(rng.integers(40, 120))))
+        tract = np.resize(unit, tlen).copy()
+        kind = k % 8
+        if kind == 3 and tlen > 200:   # an interruption somewhere inside
+            tract[int(rng.integers(20, tlen - 20))] = ord("ACGT"[(int("ACGT".index(chr(tract[50]))) + 1) % 4])
+        if kind == 4 and tlen > 300:   # N run inside the tract (compares equal at lag ulen only inside the run)
+            q = int(rng.integers(100, tlen - 100))
+            tract[q:q + int(rng.integers(1, 40))] = ord("N")
+        if kind == 5 and tlen > 300:   # soft-masked stretch and an IUPAC code
+            q = int(rng.integers(100, tlen - 100))
+            tract[q:q + 30] = np.frombuffer(bytes(tract[q:q + 30]).lower(), np.uint8)
+            tract[q + 40] = ord("R")
+        tracts.append((at, tlen, ulen))
+        add(tract)
+    add(rng.choice(acgt, size=200))
+    seq = np.concatenate(parts)
+    recs = []
+    for (t0, tlen, ulen) in tracts:
+        for units in (1, 2, 4):
+            L = ulen * units
+            if L + 2 > tlen or L > 30:
+                continue
+            p = t0 + tlen - L  # 1-based position of the base before the last L tract bases
+            if p < 2:
+                continue
+            anchor = bytes(seq[p - 1:p])
+            recs.append((0, p, [bytes(seq[p - 1:p + L]), anchor]))              # deletion of the last copies
+            recs.append((0, p + L, [bytes(seq[p + L - 1:p + L]), bytes(seq[p + L - 1:p + L]) + bytes(seq[p:p + L])]))  # insertion after the tract
+            m = t0 + tlen // 2
+            recs.append((0, m, [bytes(seq[m - 1:m + L]), bytes(seq[m - 1:m])]))   # mid-tract
+    recs.sort(key=lambda r: r[1])
+    got, exp = _run(ctx, oracle, ["c1"], [seq], recs)
+    k = got.n_changed
+    assert int(got.chg_le[:k].max()) > 2000 and int((got.chg_le[:k] > 64).sum()) > 100
+
+
 def test_multi_tile_order_and_counts(ctx, oracle):
     rng = np.random.default_rng(21)
     names, seqs = helpers.synth_reference(rng, n_contig=2, length=200000, n_runs=False)
