@@ -150,12 +150,8 @@ int vtn_dbatch_alloc(vtn_ctx* ctx, uint32_t n_rec, uint32_t n_allele, uint64_t n
     A(dalloc(&d->chg_bytes, n_bytes + 16));
     A(dalloc(&d->totals, 4));
     A(dalloc(&d->counters, 16));
-    A(dalloc(&d->scr.rec, n_rec));
-    A(dalloc(&d->scr.pos1, n_rec));
-    A(dalloc(&d->scr.lt, n_rec));
-    A(dalloc(&d->scr.le, n_rec));
-    A(dalloc(&d->scr.rt, n_rec));
-    A(dalloc(&d->scr.ob, n_rec));
+    A(dalloc(&d->scr.q0, n_rec));
+    A(dalloc(&d->scr.q1, n_rec));
     A(dalloc(&d->scr.bytes, n_bytes + 16));
     A(dalloc(&d->scr.dir, (size_t)d->n_tiles));
     A(dalloc(&d->scr.blo, (size_t)d->n_tiles));
@@ -193,8 +189,7 @@ int vtn_dbatch_destroy(vtn_ctx* ctx, vtn_dbatch* d)
     }
     cudaFree(d->status); cudaFree(d->vtype); cudaFree(d->chg_rec); cudaFree(d->chg_pos1); cudaFree(d->chg_lt);
     cudaFree(d->chg_le); cudaFree(d->chg_rt); cudaFree(d->chg_off); cudaFree(d->chg_bytes); cudaFree(d->totals);
-    cudaFree(d->scr.rec); cudaFree(d->scr.pos1); cudaFree(d->scr.lt); cudaFree(d->scr.le); cudaFree(d->scr.rt);
-    cudaFree(d->scr.ob); cudaFree(d->scr.bytes); cudaFree(d->scr.dir); cudaFree(d->scr.blo);
+    cudaFree(d->scr.q0); cudaFree(d->scr.q1); cudaFree(d->scr.bytes); cudaFree(d->scr.dir); cudaFree(d->scr.blo);
     cudaFree(d->counters); cudaFree(d->tile_state); cudaFree(d->tile_counter); cudaFree(d->src_rec); cudaFree(d->alt_idx);
     delete d;
     return VTN_OK;
@@ -382,7 +377,7 @@ int vtn_normalize(vtn_ctx* ctx, const vtn_batch* in, vtn_norm_result* out)
         VtnDevBatchView v{nr, r0, d->pos1 + r0, d->rid + r0, d->allele_beg + r0, d->allele_off, d->bytes};
         VtnDevNormOut o{d->status + r0, d->vtype + r0, d->chg_rec, d->chg_pos1, d->chg_lt, d->chg_le, d->chg_rt, d->chg_off, d->chg_bytes, d->totals, d->counters};
         VtnDevScratch x = d->scr;
-        x.rec += r0; x.pos1 += r0; x.lt += r0; x.le += r0; x.rt += r0; x.ob += r0; x.dir += tile0; x.blo += tile0;
+        x.q0 += r0; x.q1 += r0; x.dir += tile0; x.blo += tile0;
         rc = vtn_launch_normalize(ctx, v, o, x, d->tile_state, d->tile_counter, nt, c != 0);
         if (rc) return rc;
         VTN_CUDA(ctx, cudaEventRecord(ev_k, sc));

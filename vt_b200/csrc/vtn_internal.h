@@ -65,12 +65,9 @@ struct VtnDevNormOut
 // per-tile scratch segments written by K1, gathered by K2 (vtn_normalize.cu)
 struct VtnDevScratch
 {
-    uint32_t* rec;
-    int32_t* pos1;
-    uint32_t* lt;
-    uint32_t* le;
-    uint32_t* rt;
-    uint32_t* ob;             // byte offset of the record's new alleles inside its tile's byte window
+    uint4* q0;                // [n_rec] {record, new pos1, left_trimmed, left_extended}
+    uint4* q1;                // [n_rec] {right_trimmed, byte offset of the new alleles inside the tile's byte window | bit 31: the
+                              //          alleles are the 2-bit code stream in .z/.w (<= 32 bases) instead of bytes, code lo, code hi}
     uint8_t* bytes;           // [n_bytes] tile t owns the byte window of its records' old alleles
     unsigned long long* dir;  // [n_tiles] (changed count << 32) | new allele bytes
     uint32_t* blo;            // [n_tiles] start of the tile's byte window

@@ -290,9 +290,22 @@ __device__ __forceinline__ bool fast_biallelic(const VtnDevRef& R, const uint8_t
         T = m + e;
         if (e == D)
         {
+            // every base of both alleles is consumed: from here both streams read the reference, D bases apart
+            // (lag_scan).  Its first 32-D comparisons are V against itself shifted by D bases: base index j of V
+            // (= p0-32+j) faces index j-D, from j = 31 downwards -- no load.  pos1 >= 34 keeps the cap
+            // (pos1-2+m >= M+32-D) out of reach of this step.
             const int64_t cap64 = (int64_t)pos1 - 2 + (int64_t)m;
             const uint32_t cap = cap64 > 0xffffffffll ? 0xffffffffu : (uint32_t)cap64;
-            T = lag_scan(R, gbase, clen, pos1, len0, len1, T, cap);
+            bool more = true;
+            if (ev == 0)
+            {
+                const uint64_t xs = V ^ (V << (2 * D));
+                const uint64_t ms = (xs | (xs >> 1)) & 0x5555555555555555ull & ~vtn_mask2(D);
+                const uint32_t nm = ms ? (uint32_t)(__clzll((long long)ms) >> 1) : 32u - D;
+                T += nm;
+                more = (nm == 32u - D);
+            }
+            if (more) T = lag_scan(R, gbase, clen, pos1, len0, len1, T, cap);
         }
     }
     const uint32_t le = T >= m ? T - m + 1 : 0;
@@ -651,6 +664,7 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAS
     if (!FAST_ONLY && *defer_count == 0) return; // nothing was deferred (the usual case): leave before any staging
     WarpSmem& S = SM[threadIdx.x >> 5];
     uint32_t my_counter = 0; // lane k < 12 accumulates counter k of this warp
+    const uint32_t cat_shift = 6u * (uint32_t)(lane < 5 ? lane : (lane < 10 ? lane - 5 : 0));
     // contig table (gbase, length) into shared memory: two dependent global loads fewer per queued record
     if (FAST_ONLY && blockIdx.x == 0)
     { // K2's base (it starts after this kernel): the totals of the previous chunk of a chunked host call, or 0
@@ -815,24 +829,21 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAS
             }
             const uint32_t c = (st & VTN_ST_CHANGED) ? 1u : 0u;
             uint32_t pc, pb;
-            const uint32_t ec = warp_excl_scan(c, lane, pc);
+            const unsigned cmask = __ballot_sync(0xffffffffu, c);
+            const uint32_t ec = __popc(cmask & ((1u << lane) - 1u));
+            pc = __popc(cmask);
             const uint32_t eb = warp_excl_scan(c ? nb : 0u, lane, pb);
             if (c)
             {
                 const uint32_t k = r0 + tot_c + ec;    // scratch slot: tile segment, rank in input order
                 const uint32_t obl = tot_b + eb;       // byte offset inside the tile's byte window
-                X.rec[k] = B.rec_base + rr;
-                X.pos1[k] = pos1 - (int32_t)le + (int32_t)lt;
-                X.lt[k] = lt;
-                X.le[k] = le;
-                X.rt[k] = T;
-                X.ob[k] = obl;
-                uint8_t* dst = X.bytes + b_lo + obl;
+                // new REF then new ALT as one 2-bit code stream: up to 32 bases travel inside the scratch entry and are
+                // expanded to ASCII by K2; longer ones (and everything from the generic path) are written as bytes here
+                const uint32_t ntot = fast ? f.nlr + f.nla : 0u;
+                const bool coded = fast && ntot <= 32u;
+                uint64_t lo = f.newR, hi = 0;
                 if (fast)
                 {
-                    // new REF then new ALT as one code stream (<= 64 bases), expanded 4 bases per LUT lookup
-                    const uint32_t ntot = f.nlr + f.nla;
-                    uint64_t lo = f.newR, hi = 0;
                     if (f.nlr >= 32)
                         hi = f.newA;
                     else
@@ -840,6 +851,12 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAS
                         lo |= f.newA << (2 * f.nlr);
                         hi = f.nlr ? (f.newA >> (64 - 2 * f.nlr)) : 0;
                     }
+                }
+                X.q0[k] = make_uint4(B.rec_base + rr, (uint32_t)(pos1 - (int32_t)le + (int32_t)lt), lt, le);
+                X.q1[k] = make_uint4(T, obl | (coded ? 0x80000000u : 0u), (uint32_t)lo, (uint32_t)(lo >> 32));
+                uint8_t* dst = X.bytes + b_lo + obl;
+                if (fast && !coded)
+                {
                     for (uint32_t j = 0; j < ntot; j += 4)
                     {
                         const uint32_t w = s_lut[(uint32_t)lo & 0xffu];
@@ -857,16 +874,15 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAS
             tot_c += pc;
             tot_b += pb;
             // counters: category by arity (normalize.cpp:254-311), refs / variants (:315-322)
+            // one-hot 6-bit fields (a pass adds at most 32 to any of them), summed over the warp by three REDUX
             const uint32_t cat = c ? (st >> VTN_ST_CAT_SHIFT) : 0u;
-            const uint32_t slot = cat ? ((n2 == 2 ? 0u : 5u) + cat - 1u) : 0xffu;
-#pragma unroll
-            for (uint32_t k = 0; k < 10; ++k)
-            {
-                const unsigned mk = __ballot_sync(0xffffffffu, slot == k);
-                if (lane == (int)k) tile_cat += __popc(mk);
-            }
-            cnt_refs += __popc(__ballot_sync(0xffffffffu, act && vt == VTN_VT_REF));
-            cnt_vars += __popc(__ballot_sync(0xffffffffu, act && vt != VTN_VT_REF));
+            const uint32_t fld = cat ? (1u << (6u * (cat - 1u))) : 0u;
+            const uint32_t r_bi = __reduce_add_sync(0xffffffffu, n2 == 2 ? fld : 0u);
+            const uint32_t r_mu = FAST_ONLY ? 0u : __reduce_add_sync(0xffffffffu, n2 == 2 ? 0u : fld); // the fast launch keeps biallelic tiles only
+            const uint32_t r_rv = __reduce_add_sync(0xffffffffu, act ? (vt == VTN_VT_REF ? 1u : 0x100u) : 0u);
+            if (lane < 10) tile_cat += ((lane < 5 ? r_bi : r_mu) >> cat_shift) & 63u;
+            cnt_refs += r_rv & 0xffu;
+            cnt_vars += r_rv >> 8;
         }
         if (deferred)
         {
@@ -936,7 +952,14 @@ __global__ void __launch_bounds__(VTC_THREADS, 2) vtn_compact_kernel(VtnDevBatch
     __shared__ unsigned long long s_pc[VTC_THREADS / 32], s_pb[VTC_THREADS / 32];
     __shared__ uint32_t s_cnt[VTC_TPB], s_nb2[VTC_TPB], s_bc[VTC_TPB + 1];
     __shared__ unsigned long long s_bb[VTC_TPB];
+    __shared__ uint32_t s_lut[256]; // 4 packed 2-bit codes -> their 4 ASCII bytes (A=0 C=1 T=2 G=3)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid < 256)
+    {
+        uint32_t w = 0;
+        for (int q = 0; q < 4; ++q) w |= ((0x47544341u >> (8 * ((tid >> (2 * q)) & 3))) & 0xffu) << (8 * q);
+        s_lut[tid] = w;
+    }
     const uint32_t blk = blockIdx.x;
     const uint32_t t = blk * tpb + tid;
     const unsigned long long d = (tid < (int)tpb && t < n_tiles) ? X.dir[t] : 0ull;
@@ -1016,26 +1039,44 @@ __global__ void __launch_bounds__(VTC_THREADS, 2) vtn_compact_kernel(VtnDevBatch
         const uint32_t tile = blk * tpb + tt;
         const uint32_t src = tile * VTN_WTILE + i;
         const unsigned long long k = base_c + j;
-        const uint32_t ob = X.ob[src];
-        const uint32_t ob_next = (i + 1 < s_cnt[tt]) ? X.ob[src + 1] : s_nb2[tt];
+        const uint4 e0 = X.q0[src], e1 = X.q1[src];
+        const uint32_t ob = e1.y & 0x7fffffffu;
+        const uint32_t ob_next = (i + 1 < s_cnt[tt]) ? (X.q1[src + 1].y & 0x7fffffffu) : s_nb2[tt];
         const unsigned long long dst_off = s_bb[tt] + ob;
-        const uint8_t* __restrict__ sb = X.bytes + X.blo[tile] + ob;
         uint8_t* __restrict__ db = O.chg_bytes + dst_off;
         const uint32_t n = ob_next - ob;
-        O.chg_rec[k] = X.rec[src];
-        O.chg_pos1[k] = X.pos1[src];
-        O.chg_lt[k] = X.lt[src];
-        O.chg_le[k] = X.le[src];
-        O.chg_rt[k] = X.rt[src];
+        O.chg_rec[k] = e0.x;
+        O.chg_pos1[k] = (int32_t)e0.y;
+        O.chg_lt[k] = e0.z;
+        O.chg_le[k] = e0.w;
+        O.chg_rt[k] = e1.x;
         O.chg_off[k] = dst_off;
-        for (uint32_t q0 = 0; q0 < n; q0 += 8)
-        { // eight byte loads in flight before the first store (one round for the usual short indel)
-            uint8_t tmp[8];
+        if (e1.y >> 31)
+        { // the new alleles came as 2-bit codes (n <= 32 bases): four bases per table lookup
+            uint32_t lo = e1.z, hi = e1.w;
+            for (uint32_t q0 = 0; q0 < n; q0 += 4)
+            {
+                const uint32_t w = s_lut[lo & 0xffu];
+                db[q0] = (uint8_t)w;
+                if (q0 + 1 < n) db[q0 + 1] = (uint8_t)(w >> 8);
+                if (q0 + 2 < n) db[q0 + 2] = (uint8_t)(w >> 16);
+                if (q0 + 3 < n) db[q0 + 3] = (uint8_t)(w >> 24);
+                lo = __funnelshift_r(lo, hi, 8);
+                hi >>= 8;
+            }
+        }
+        else
+        {
+            const uint8_t* __restrict__ sb = X.bytes + X.blo[tile] + ob;
+            for (uint32_t q0 = 0; q0 < n; q0 += 8)
+            { // eight byte loads in flight before the first store
+                uint8_t tmp[8];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) tmp[q] = q0 + q < n ? sb[q0 + q] : (uint8_t)0;
+                for (int q = 0; q < 8; ++q) tmp[q] = q0 + q < n ? sb[q0 + q] : (uint8_t)0;
 #pragma unroll
-            for (int q = 0; q < 8; ++q)
-                if (q0 + q < n) db[q0 + q] = tmp[q];
+                for (int q = 0; q < 8; ++q)
+                    if (q0 + q < n) db[q0 + q] = tmp[q];
+            }
         }
     }
 }
