@@ -363,6 +363,189 @@ __device__ __forceinline__ bool fast_biallelic(const VtnDevRef& R, const uint8_t
     return true;
 }
 
+// ---- the same fast path in 32-bit words, for records whose alleles are both <= 16 bases (nearly all of a real call set):
+// every 2-bit operation is one instruction instead of a 64-bit pair, the window is 32 bases [p0-16, p0+16) = two groups,
+// and the two loads are issued before the allele conversion so that their latency overlaps it.  Line references as in
+// fast_biallelic; the two must return identical results wherever both accept a record.
+__device__ __forceinline__ uint32_t vtn_m32(uint32_t nbases) { return __funnelshift_lc(0xffffffffu, 0u, 2u * nbases); } // low 2n bits, n in [0,16]
+
+__device__ __forceinline__ uint32_t vtn_top_match32(uint32_t a, uint32_t b)
+{
+    const uint32_t x = a ^ b;
+    const uint32_t mm = (x | (x >> 1)) & 0x55555555u;
+    return mm ? (uint32_t)(__clz((int)mm) >> 1) : 16u;
+}
+
+__device__ __forceinline__ bool fast_biallelic16(const VtnDevRef& R, const uint8_t* bytes, uint32_t off0, uint32_t len0, uint32_t len1,
+                                                 int32_t pos1, int64_t clen, uint64_t gbase, VtnFastRes& o)
+{
+    if (len0 - 1u > 15u || len1 - 1u > 15u || pos1 < 18) return false;
+    const int64_t p0 = (int64_t)pos1 - 1;
+    if (p0 + 16 > clen) return false; // keeps the window inside the contig
+    const uint64_t gp = gbase + (uint64_t)(p0 - 16);
+    const uint4 ga = vtn_ldg_group(R, gp >> 5), gb = vtn_ldg_group(R, (gp >> 5) + 1); // contigs carry two pad groups
+    const uint32_t gs = (uint32_t)gp & 31u;
+    // ---- allele bytes -> 2-bit code stream (REF then ALT are contiguous), <= 32 bases ----
+    const uint32_t L = len0 + len1;
+    uint64_t s0 = 0, badacc = 0;
+    for (uint32_t c = 0; 8 * c < L; ++c)
+    {
+        uint64_t bad;
+        const uint64_t code = vtn_codes8(vtn_fetch8(bytes, off0 + 8 * c), L - 8 * c, bad);
+        badacc |= bad;
+        s0 |= code << (16 * c);
+    }
+    if (badacc) return false;
+    const uint32_t Rc = (uint32_t)s0 & vtn_m32(len0);
+    const uint32_t Ac = (uint32_t)(s0 >> (2 * len0)) & vtn_m32(len1);
+    const uint32_t m = len0 < len1 ? len0 : len1, M = len0 < len1 ? len1 : len0;
+
+    // ---- classify_variant (variant_manip.cpp:337-505) ----
+    const bool same = (len0 == len1) && (Rc == Ac);
+    const uint32_t y = Rc ^ Ac;
+    const uint32_t mmy = (y | (y >> 1)) & 0x55555555u;
+    uint32_t cp_raw = mmy ? (uint32_t)(__ffs((int)mmy) - 1) >> 1 : 16u;
+    if (cp_raw > m) cp_raw = m;
+    uint32_t cs_raw = vtn_top_match32(Rc << (32 - 2 * len0), Ac << (32 - 2 * len1));
+    if (cs_raw > m) cs_raw = m;
+    uint32_t vtype = VTN_VT_REF;
+    if (!same)
+    {
+        const uint32_t cs = cs_raw < m - 1 ? cs_raw : m - 1;
+        uint32_t rl = len0 - cs, al = len1 - cs;
+        const uint32_t mla = rl < al ? rl : al;
+        const uint32_t cp = cp_raw < mla - 1 ? cp_raw : mla - 1;
+        rl -= cp;
+        al -= cp;
+        const uint32_t mlen = rl < al ? rl : al;
+        uint32_t diff;
+        if (mlen == 1 && rl != al)
+        {
+            const uint32_t lg = rl > al ? Rc : Ac, sh = rl > al ? Ac : Rc;
+            const uint32_t ll = rl > al ? rl : al;
+            const uint32_t ls = (lg >> (2 * cp)) & 3u, le_ = (lg >> (2 * (cp + ll - 1))) & 3u;
+            const uint32_t ss = (sh >> (2 * cp)) & 3u;
+            diff = (ls != ss && le_ != ss) ? 1u : 0u;
+        }
+        else
+            diff = (uint32_t)__popc((mmy >> (2 * cp)) & vtn_m32(mlen));
+        if (mlen == diff) vtype |= (mlen == 1) ? VTN_VT_SNP : VTN_VT_MNP;
+        if (rl != al) vtype |= VTN_VT_INDEL;
+        if (diff && diff < mlen) vtype |= VTN_VT_CLUMPED;
+        if (len0 == len1 && len0 > 1) vtype |= VTN_VT_MNP;
+    }
+    o.vtype = vtype;
+    o.T = o.le = o.lt = 0;
+    o.status = 0;
+    o.nlr = o.nla = 0;
+    o.newR = o.newA = 0;
+    if (vtype == VTN_VT_SNP) return true; // no REF check (normalize.cpp:205)
+
+    // ---- the window: V = codes of [p0-16, p0), W = codes of [p0, p0+16); ev / nw as in vtn_ref_window64 ----
+    uint32_t V, W, ev, nw;
+    {
+        const uint32_t w0 = gs < 16 ? ga.x : ga.y, w1 = gs < 16 ? ga.y : gb.x, w2 = gs < 16 ? gb.x : gb.y;
+        V = __funnelshift_r(w0, w1, 2 * gs); // the shift wraps at 32, which is what the word selection above expects
+        W = __funnelshift_r(w1, w2, 2 * gs);
+        ev = __funnelshift_r(ga.z & ~ga.w, gb.z & ~gb.w, gs) & 0xffffu;
+        nw = __funnelshift_r(ga.z, gb.z, gs) >> 16;
+    }
+    if (nw & ((1u << len0) - 1u)) return false; // N / lower-case under REF
+    if ((W ^ Rc) & vtn_m32(len0))
+    {
+        o.status = 2;
+        return true;
+    }
+    // ---- is_normalized (variant_manip.cpp:109-197) ----
+    if (same || (len0 == 1 && len1 == 1)) return true;
+    const bool exists_one = (m == 1);
+    const bool first_same = (y & 3u) == 0;
+    const bool last_same = cs_raw >= 1;
+    if (!(last_same || (!exists_one && first_same))) return true;
+    o.status = VTN_ST_ENTERED;
+
+    // ---- right_trim_or_left_extend in closed form ----
+    const uint32_t D = M - m;
+    const uint32_t X = len0 > len1 ? Rc : Ac;
+    uint32_t T;
+    if (cs_raw < m)
+        T = cs_raw;
+    else
+    {
+        if (ev & (((1u << D) - 1u) << (16 - D))) return false; // N / IUPAC bases among the D bases left of POS
+        uint32_t e = vtn_top_match32((X & vtn_m32(D)) << (32 - 2 * D), V & ~vtn_m32(16 - D));
+        if (e > D) e = D;
+        T = m + e;
+        if (e == D)
+        {
+            const int64_t cap64 = (int64_t)pos1 - 2 + (int64_t)m;
+            const uint32_t cap = cap64 > 0xffffffffll ? 0xffffffffu : (uint32_t)cap64;
+            bool more = true;
+            if (ev == 0)
+            { // first 16-D lag comparisons from V itself; pos1 >= 18 keeps the cap (>= m+16) out of reach
+                const uint32_t xs = V ^ (V << (2 * D));
+                const uint32_t ms = (xs | (xs >> 1)) & 0x55555555u & ~vtn_m32(D);
+                const uint32_t nm = ms ? (uint32_t)(__clz((int)ms) >> 1) : 16u - D;
+                T += nm;
+                more = (nm == 16u - D);
+            }
+            if (more) T = lag_scan(R, gbase, clen, pos1, len0, len1, T, cap);
+        }
+    }
+    const uint32_t le = T >= m ? T - m + 1 : 0;
+    uint32_t lt = 0;
+    if (le == 0)
+    {
+        const uint32_t room = m - T - 1;
+        lt = cp_raw < room ? cp_raw : room;
+    }
+    o.T = T;
+    o.le = le;
+    o.lt = lt;
+    if (!(T | le | lt)) return true;
+    uint32_t cat; // normalize.cpp:254-311
+    if (le) cat = (T > le) ? 4 : 5;
+    else if (lt && T > le) cat = 3;
+    else if (lt) cat = 1;
+    else cat = 2;
+    o.status |= VTN_ST_CHANGED | (cat << VTN_ST_CAT_SHIFT);
+    // ---- new alleles as codes ----
+    if (le == 0)
+    {
+        o.nlr = len0 - T - lt;
+        o.nla = len1 - T - lt;
+        o.newR = (Rc >> (2 * lt)) & vtn_m32(o.nlr);
+        o.newA = (Ac >> (2 * lt)) & vtn_m32(o.nla);
+    }
+    else
+    {
+        // new allele i = (le reference bases [p0-le, p0) ++ allele_i)[0 : le + len_i - T]; the longer one has D+1 bases
+        uint32_t Vl, e2; // codes / exception bits of [p0-le, p0-le+16)
+        if (le <= 16)
+        {
+            Vl = le == 16 ? V : (V >> (2 * (16 - le)));
+            e2 = le == 16 ? ev : (ev >> (16 - le));
+        }
+        else
+        {
+            uint64_t Vl64;
+            vtn_ref_window32(R, gbase + (uint64_t)(p0 - (int64_t)le), Vl64, e2);
+            Vl = (uint32_t)Vl64;
+        }
+        if (e2 & ((1u << (D + 1)) - 1u)) return false; // the shift ran through N / IUPAC bases: those cannot be codes
+        uint32_t lg;
+        if (T < M) // then le <= D <= 15
+            lg = (Vl & vtn_m32(le)) | ((X & vtn_m32(M - T)) << (2 * le));
+        else
+            lg = Vl;
+        lg &= vtn_m32(D + 1);
+        const uint32_t shn = Vl & 3u;
+        if (len0 > len1) { o.newR = lg; o.nlr = D + 1; o.newA = shn; o.nla = 1; }
+        else { o.newA = lg; o.nla = D + 1; o.newR = shn; o.nlr = 1; }
+    }
+    return true;
+}
+
 // The whole per-record computation except writing the new alleles.
 __device__ __noinline__ void normalize_record(const VtnDevRef& R, const VtnDevBatchView& B, uint32_t r, RecResult& out)
 {
@@ -792,11 +975,14 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAS
             const bool act = e < nq;
             uint32_t st = 0, vt = VTN_VT_SNP, T = 0, le = 0, lt = 0, nb = 0, n2 = 2, rr = 0;
             int32_t pos1 = 0;
-            bool fast = false;
+            bool fast = false, elig = false;
             VtnFastRes f;
+            uint32_t o0 = 0, l0 = 0, l1 = 0, idx = 0;
+            int64_t clen = 0;
+            uint64_t gbase = 0;
             if (act)
             {
-                const uint32_t idx = S.queue[e];
+                idx = S.queue[e];
                 rr = r0 + idx;
                 const uint32_t ab2 = __ldg(B.allele_beg + rr);
                 n2 = __ldg(B.allele_beg + rr + 1) - ab2;
@@ -804,11 +990,21 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAS
                 const int32_t rid = S.rid[idx];
                 if (n2 == 2 && rid >= 0 && rid < R.n_contig)
                 {
-                    const uint32_t o0 = AO(ab2), o1 = AO(ab2 + 1), o2 = AO(ab2 + 2);
-                    const int64_t clen = contigs_staged ? s_clen[rid] : __ldg(R.contig_len + rid);
-                    const uint64_t gbase = contigs_staged ? s_gbase[rid] : (__ldg(R.contig_goff + rid) << 5);
-                    fast = fast_biallelic(R, BY, o0, o1 - o0, o2 - o1, pos1, clen, gbase, f);
+                    elig = true;
+                    o0 = AO(ab2);
+                    const uint32_t o1 = AO(ab2 + 1), o2 = AO(ab2 + 2);
+                    l0 = o1 - o0;
+                    l1 = o2 - o1;
+                    clen = contigs_staged ? s_clen[rid] : __ldg(R.contig_len + rid);
+                    gbase = contigs_staged ? s_gbase[rid] : (__ldg(R.contig_goff + rid) << 5);
                 }
+            }
+            // 32-bit words when every eligible record of this pass has alleles of <= 16 bases (warp-uniform choice)
+            const bool use16 = __all_sync(0xffffffffu, !elig || (l0 - 1u < 16u && l1 - 1u < 16u));
+            if (act)
+            {
+                if (elig)
+                    fast = use16 ? fast_biallelic16(R, BY, o0, l0, l1, pos1, clen, gbase, f) : fast_biallelic(R, BY, o0, l0, l1, pos1, clen, gbase, f);
                 if (fast)
                 {
                     st = f.status; vt = f.vtype; T = f.T; le = f.le; lt = f.lt; nb = f.nlr + f.nla;
