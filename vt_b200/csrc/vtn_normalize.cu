@@ -770,10 +770,12 @@ struct __align__(16) WarpSmem
     uint32_t aoff[VTN_AOFF_CAP];
     uint8_t bytes[VTN_BYTES_CAP];
     int32_t pos1[VTN_WTILE], rid[VTN_WTILE];
-    uint8_t queue[VTN_WTILE];
+    uint32_t queue[VTN_WTILE]; // record index in the tile | biallelic flag << 7 | (first allele slot - tile's first slot) << 8
     uint8_t st[VTN_WTILE], vt[VTN_WTILE];
 };
+#ifndef VTN_CONTIG_CAP
 #define VTN_CONTIG_CAP 256
+#endif
 // K2's control block, in 64-bit words (see vtn_launch_normalize); vtn_normalize_ctl_words() sizes the allocation
 #define VTC_CTL_BASE 2
 #define VTC_CTL_AGG 4
@@ -912,7 +914,9 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAS
             if (lane == 31) h_abx = __ldg(B.allele_beg + r1 + VTN_WTILE);
         }
         const uint32_t s_lo = __shfl_sync(0xffffffffu, ab[0], 0);
-        const uint32_t s_hi = __ldg(B.allele_beg + r0 + n_live); // one past the last live record's slots
+        // one past the last live record's slots: lane 31 holds allele_beg[r0 + WTILE] for a full tile
+        const uint32_t s_hi31 = __shfl_sync(0xffffffffu, ab[VTN_RPL], 31);
+        const uint32_t s_hi = n_live == VTN_WTILE ? s_hi31 : __ldg(B.allele_beg + r0 + n_live);
         // stage allele_off[s_lo .. s_hi]
         const uint32_t a0 = s_lo & ~3u;
         const bool aoff_staged = (s_hi + 1 - a0) <= VTN_AOFF_CAP;
@@ -959,7 +963,7 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAS
             uint32_t slot = warp_excl_scan(__popc(qmask), lane, nq);
 #pragma unroll
             for (int j = 0; j < VTN_RPL; ++j)
-                if (qmask & (1u << j)) S.queue[slot++] = (uint8_t)(lane * VTN_RPL + j);
+                if (qmask & (1u << j)) S.queue[slot++] = (uint32_t)(lane * VTN_RPL + j) | (ab[j + 1] - ab[j] == 2 ? 0x80u : 0u) | ((ab[j] - s_lo) << 8);
         }
         __syncwarp();
 
@@ -982,10 +986,11 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTN_MIN_BLOCKS_FAS
             uint64_t gbase = 0;
             if (act)
             {
-                idx = S.queue[e];
+                const uint32_t qe = S.queue[e];
+                idx = qe & 0x7fu;
                 rr = r0 + idx;
-                const uint32_t ab2 = __ldg(B.allele_beg + rr);
-                n2 = __ldg(B.allele_beg + rr + 1) - ab2;
+                const uint32_t ab2 = s_lo + (qe >> 8);
+                n2 = (qe & 0x80u) ? 2u : 3u; // only "biallelic or not" matters below (eligibility, counter arity)
                 pos1 = S.pos1[idx];
                 const int32_t rid = S.rid[idx];
                 if (n2 == 2 && rid >= 0 && rid < R.n_contig)
