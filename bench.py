@@ -550,8 +550,8 @@ def main():
         },
         "roofline": {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "traffic": (607.4e6 if (args.workload == "c2" and N_RECORDS == 10_000_000 and REF_SCALE == 1.0) else None),
-            "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of vtn_normalize_kernel<fast>, one ncu --set full capture of this command (profiles/r1j_ncu_normalize_v6_split.txt); K2 adds 87.5 MB",
+            "traffic": (558.1e6 if (args.workload == "c2" and N_RECORDS == 10_000_000 and REF_SCALE == 1.0) else None),
+            "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of vtn_normalize_kernel<fast>, one ncu --set full capture of this command (profiles/r1o_ncu_normalize_v9.txt: 493.9 MB read + 64.2 MB written)",
             "kernel": "vtn_normalize_kernel", "algorithmic_bytes_per_launch": alg_bytes,
             "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
         },
