@@ -414,3 +414,237 @@ int32_t vto_decompose_plan(const vto_batch* in, uint32_t* src_rec, uint16_t* alt
     *n_out = k;
     return 0;
 }
+
+/* ---------------------------------------------------------------------------------------------------------
+ * vt uniq: uniq.cpp:110-156 over BCFSyncedReader(SYNC_BY_VAR) with ONE input file, sequential
+ * (non-indexed) reading.  Restated literally: a record buffer that is topped up until it holds records of two
+ * different (rid,pos) (bcf_synced_reader.cpp:497-640, the `else` branch :594-637), a priority queue ordered by
+ * CompareBCFPtr (bcf_synced_reader.h:86-122) on (rid, pos1, strcmp of the sorted allele string
+ * hts_utils.cpp:1136-1167), and read_next_position (:388-433) popping all records that compare equal to the top.
+ * std::priority_queue is libstdc++'s: push = push_back + std::push_heap, pop = std::pop_heap + pop_back
+ * (bits/stl_queue.h, bits/stl_heap.h __push_heap / __adjust_heap), restated below because WHICH of several equal
+ * records surfaces first (= crecs[0], the record uniq keeps) depends on the heap's sift order, not on file order.
+ * --------------------------------------------------------------------------------------------------------- */
+typedef struct uq_rec
+{
+    int32_t rid, pos1;
+    char* key; /* bcf_alleles2string_sorted: REF,ALT (n==2) or REF,sorted ALTs */
+    uint32_t idx;
+} uq_rec;
+
+static int uq_cmpstr(const void* a, const void* b) { return strcmp(*(char* const*)a, *(char* const*)b); } /* hts_utils.cpp:1031-1037 */
+
+static char* uq_key(const vto_batch* in, uint32_t r)
+{
+    uint32_t ab = in->allele_beg[r], n = in->allele_beg[r + 1] - ab;
+    uint32_t total = in->allele_off[ab + n] - in->allele_off[ab];
+    char* s = (char*)malloc(total + n + 1);
+    char** al = (char**)malloc(sizeof(char*) * (n ? n : 1));
+    if (!s || !al) return NULL;
+    for (uint32_t i = 0; i < n; ++i)
+    {
+        uint32_t o = in->allele_off[ab + i], l = in->allele_off[ab + i + 1] - o;
+        al[i] = (char*)malloc(l + 1);
+        memcpy(al[i], in->bytes + o, l);
+        al[i][l] = 0;
+    }
+    if (n > 2) qsort(al + 1, n - 1, sizeof(char*), uq_cmpstr); /* :1156 (n==2 needs no sort, :1141-1146) */
+    size_t k = 0;
+    for (uint32_t i = 0; i < n; ++i)
+    {
+        if (i) s[k++] = ',';
+        size_t l = strlen(al[i]);
+        memcpy(s + k, al[i], l);
+        k += l;
+        free(al[i]);
+    }
+    s[k] = 0;
+    free(al);
+    return s;
+}
+
+/* CompareBCFPtr::operator() (bcf_synced_reader.h:89-121), one file => file_index equal => false on ties */
+static int uq_comp(const uq_rec* a, const uq_rec* b)
+{
+    if (a->rid == b->rid)
+    {
+        if (a->pos1 == b->pos1)
+        {
+            int d = strcmp(a->key, b->key);
+            if (d == 0) return 0;
+            return d > 0;
+        }
+        return a->pos1 > b->pos1;
+    }
+    return a->rid > b->rid;
+}
+
+/* BCFSyncedReader::bcfptr_cmp, sequential branch (bcf_synced_reader.cpp:361-383) */
+static int uq_cmp3(const uq_rec* a, const uq_rec* b)
+{
+    if (a->rid == b->rid)
+    {
+        if (a->pos1 == b->pos1) return strcmp(a->key, b->key);
+        return a->pos1 >= b->pos1 ? 1 : -1;
+    }
+    return a->rid >= b->rid ? 1 : -1;
+}
+
+/* libstdc++ bits/stl_heap.h */
+static void uq_push_heap(uq_rec** first, long hole, long top, uq_rec* value)
+{
+    long parent = (hole - 1) / 2;
+    while (hole > top && uq_comp(first[parent], value))
+    {
+        first[hole] = first[parent];
+        hole = parent;
+        parent = (hole - 1) / 2;
+    }
+    first[hole] = value;
+}
+
+static void uq_adjust_heap(uq_rec** first, long hole, long len, uq_rec* value)
+{
+    const long top = hole;
+    long child = hole;
+    while (child < (len - 1) / 2)
+    {
+        child = 2 * (child + 1);
+        if (uq_comp(first[child], first[child - 1])) child--;
+        first[hole] = first[child];
+        hole = child;
+    }
+    if ((len & 1) == 0 && child == (len - 2) / 2)
+    {
+        child = 2 * (child + 1);
+        first[hole] = first[child - 1];
+        hole = child - 1;
+    }
+    uq_push_heap(first, hole, top, value);
+}
+
+typedef struct uq_state
+{
+    const vto_batch* in;
+    uq_rec* recs;
+    uint32_t next;       /* next record bcf_read would return */
+    uint32_t* buf;       /* buffer[0] as an array list of record indices (front = buf[0]) */
+    uint32_t nbuf;
+    uq_rec** pq;
+    long npq;
+    int64_t bad;
+} uq_state;
+
+static void uq_pq_push(uq_state* S, uq_rec* v)
+{
+    S->pq[S->npq++] = v; /* c.push_back(x); std::push_heap(c.begin(), c.end(), comp) */
+    uq_push_heap(S->pq, S->npq - 1, 0, S->pq[S->npq - 1]);
+}
+
+static void uq_pq_pop(uq_state* S)
+{
+    if (S->npq > 1)
+    { /* std::pop_heap: --last; value = *last; *last = *first; __adjust_heap(first, 0, last-first, value) */
+        uq_rec* value = S->pq[S->npq - 1];
+        S->pq[S->npq - 1] = S->pq[0];
+        uq_adjust_heap(S->pq, 0, S->npq - 1, value);
+    }
+    S->npq--;
+}
+
+/* BCFSyncedReader::fill_buffer, sequential branch (bcf_synced_reader.cpp:594-637) */
+static void uq_fill_buffer(uq_state* S)
+{
+    if (S->nbuf >= 2 || S->bad >= 0) return;
+    int32_t rid = S->nbuf == 0 ? -1 : S->recs[S->buf[0]].rid;
+    int32_t pos1 = S->nbuf == 0 ? 0 : S->recs[S->buf[0]].pos1;
+    while (S->next < S->in->n_rec)
+    {
+        uq_rec* v = &S->recs[S->next];
+        if (S->nbuf)
+        { /* bcf_is_in_order(buffer.back(), v), hts_utils.cpp:1042-1050 */
+            const uq_rec* a = &S->recs[S->buf[S->nbuf - 1]];
+            int ok = a->rid == v->rid ? a->pos1 <= v->pos1 : a->rid < v->rid;
+            if (!ok)
+            {
+                S->bad = S->next; /* "VCF file not in order" + exit(1) */
+                return;
+            }
+        }
+        S->next++;
+        S->buf[S->nbuf++] = v->idx;
+        uq_pq_push(S, v);
+        if (rid == -1)
+        {
+            rid = v->rid;
+            pos1 = v->pos1;
+        }
+        if (v->rid != rid || v->pos1 != pos1) break;
+    }
+}
+
+/* order[k] = input index of the k-th record popped; first[k] = 1 iff it is crecs[0] of a read_next_position
+ * call (the record uniq writes; the following first[]==0 entries are the duplicates whose OLD_VARIANT values are
+ * merged into it, uniq.cpp:114-143).  counters: no_total_variants, no_unique_variants (uniq.cpp:147-148).
+ * *not_in_order = -1, or the index of the record at which the reference prints "VCF file not in order" and exits
+ * (outputs up to that point are what was produced before).  rid must be >= 0. */
+int32_t vto_uniq_plan(const vto_batch* in, uint32_t* order, uint8_t* first, uint32_t counters[2], int64_t* not_in_order)
+{
+    uq_state S;
+    memset(&S, 0, sizeof S);
+    S.in = in;
+    S.bad = -1;
+    S.recs = (uq_rec*)calloc(in->n_rec ? in->n_rec : 1, sizeof(uq_rec));
+    S.buf = (uint32_t*)malloc(sizeof(uint32_t) * ((size_t)in->n_rec + 2));
+    S.pq = (uq_rec**)malloc(sizeof(uq_rec*) * ((size_t)in->n_rec + 2));
+    if (!S.recs || !S.buf || !S.pq) return -1;
+    for (uint32_t r = 0; r < in->n_rec; ++r)
+    { /* bcfptr ctor, bcf_synced_reader.h:57-70 */
+        S.recs[r].rid = in->rid[r];
+        S.recs[r].pos1 = in->pos1[r];
+        S.recs[r].idx = r;
+        S.recs[r].key = uq_key(in, r);
+        if (!S.recs[r].key) return -1;
+    }
+    counters[0] = counters[1] = 0;
+    uint32_t k = 0;
+    for (;;)
+    { /* read_next_position, :388-433 */
+        if (S.npq == 0)
+        {
+            uq_fill_buffer(&S); /* initialize_next_interval, sequential branch :476-489 */
+            if (S.npq == 0) break;
+        }
+        uq_rec* variant = S.pq[0];
+        uq_rec* cvariant = variant;
+        uint32_t ncrecs = 0;
+        while (uq_cmp3(cvariant, variant) == 0)
+        {
+            uq_rec* b = S.pq[0];
+            order[k] = b->idx;
+            first[k] = ncrecs == 0;
+            ++k;
+            ++ncrecs;
+            uint32_t j = 0; /* buffer.remove(b->v) */
+            while (j < S.nbuf && S.buf[j] != b->idx) ++j;
+            if (j < S.nbuf)
+            {
+                memmove(S.buf + j, S.buf + j + 1, sizeof(uint32_t) * (S.nbuf - j - 1));
+                S.nbuf--;
+            }
+            uq_fill_buffer(&S);
+            uq_pq_pop(&S);
+            if (S.npq == 0) break;
+            cvariant = S.pq[0];
+        }
+        counters[1]++;          /* ++no_unique_variants */
+        counters[0] += ncrecs;  /* no_total_variants += crecs.size() */
+        if (S.bad >= 0) break;
+    }
+    *not_in_order = S.bad;
+    for (uint32_t r = 0; r < in->n_rec; ++r) free(S.recs[r].key);
+    free(S.recs);
+    free(S.buf);
+    free(S.pq);
+    return 0;
+}

@@ -75,6 +75,12 @@ int32_t vto_normalize_batch(const vto_ref* ref, const vto_batch* in, vto_norm_ou
  * counters: no_variants, no_biallelic, no_multiallelic, no_additional_biallelic (decompose.cpp:139-143) */
 int32_t vto_decompose_plan(const vto_batch* in, uint32_t* src_rec, uint16_t* alt_idx, uint64_t* n_out, uint32_t counters[4]);
 
+/* vt uniq (uniq.cpp:110-156 over BCFSyncedReader SYNC_BY_VAR, one file, sequential reading): pop order of the
+ * reader's priority queue (libstdc++ heap restated), crecs[0] flags, counters {no_total_variants,
+ * no_unique_variants}; *not_in_order = index of the record where the reference exits with "VCF file not in
+ * order", else -1.  Pinned against oracle/_ref/vt_ref uniq (tests/test_uniq_oracle.py, tests/golden/uniq_*). */
+int32_t vto_uniq_plan(const vto_batch* in, uint32_t* order, uint8_t* first, uint32_t counters[2], int64_t* not_in_order);
+
 #ifdef __cplusplus
 }
 #endif

@@ -58,6 +58,8 @@ class Oracle:
         self.lib.vto_normalize_batch.argtypes = [C.POINTER(VtoRef), C.POINTER(VtoBatch), C.POINTER(VtoNormOut)]
         self.lib.vto_decompose_plan.restype = C.c_int32
         self.lib.vto_decompose_plan.argtypes = [C.POINTER(VtoBatch), u32p, u16p, u64p, u32p]
+        self.lib.vto_uniq_plan.restype = C.c_int32
+        self.lib.vto_uniq_plan.argtypes = [C.POINTER(VtoBatch), u32p, u8p, u32p, i64p]
 
     @staticmethod
     def _ref(seqs):
@@ -111,6 +113,19 @@ class Oracle:
         assert rc == 0
         k = int(n_out.value)
         return src[:k], alt[:k], list(cnt)
+
+
+    def uniq_plan(self, b):
+        """-> (order, first, [no_total_variants, no_unique_variants], not_in_order)"""
+        order = np.zeros(max(b.n_rec, 1), np.uint32)
+        first = np.zeros(max(b.n_rec, 1), np.uint8)
+        cnt = (C.c_uint32 * 2)()
+        bad = C.c_int64(-1)
+        vb = self._batch(b)
+        rc = self.lib.vto_uniq_plan(C.byref(vb), order.ctypes.data_as(u32p), first.ctypes.data_as(u8p), cnt, C.byref(bad))
+        assert rc == 0
+        k = int(cnt[0])
+        return order[:k], first[:k], list(cnt), int(bad.value)
 
 
 def assert_norm_equal(got, exp, n_rec):
