@@ -11,6 +11,8 @@
  *                        and the ten category counters + no_variants/no_refs (normalize.cpp:254-322)
  *   vtn_decompose*       the allele fan-out of Igor::decompose(), decompose.cpp:210-392 / :393-957, and its
  *                        four counters (:139-143)
+ *   vtn_uniq*            the record loop of Igor::uniq(), uniq.cpp:110-156, over BCFSyncedReader::read_next_position
+ *                        (bcf_synced_reader.cpp:388-433, :594-637; comparator bcf_synced_reader.h:86-122)
  *   vtn_hmm_*            AHMM/LFHMM/RFHMM::align (ahmm.cpp:468-587, lfhmm.cpp:489-654, rfhmm.cpp:516+)
  *
  * The library never exits or prints: every call returns 0 on success or a negative vtn_err code, and
@@ -153,6 +155,26 @@ int vtn_decompose_normalize(vtn_ctx* ctx, const vtn_batch* in, uint32_t* src_rec
 int vtn_decompose_resident(vtn_ctx* ctx, vtn_dbatch* db, int fuse_normalize); /* async; for bench */
 int vtn_dbatch_fetch_decompose(vtn_ctx* ctx, vtn_dbatch* db, uint32_t* src_rec, uint16_t* alt_idx,
                                uint64_t* n_out, vtn_decomp_counters* counters);
+
+/* ---- uniq: drop duplicate variants (vt uniq) ----
+ * The input must be sorted like vt requires (bcf_is_in_order, hts_utils.cpp:1042-1050: rid ascending, pos ascending
+ * within a rid; rid >= 0).  order[k] = input index of the k-th record the reference's synced reader hands out: records
+ * are grouped by (rid, pos1) in input order, and inside a position group they come out sorted by strcmp of
+ * "REF,ALT" (ALTs of a multiallelic record sorted first, hts_utils.cpp:1136-1167), equal records in the order
+ * libstdc++'s priority queue surfaces them (which is NOT file order; reproduced exactly).  first[k] = 1 iff order[k] is
+ * crecs[0] of a read_next_position call = the record `vt uniq` writes; the entries with first[k] == 0 that follow are its
+ * duplicates, whose OLD_VARIANT values uniq merges into it in this order (uniq.cpp:114-143).
+ * *not_in_order = -1, or the index of the first record that is smaller than its predecessor (the reference prints
+ * "VCF file not in order" and exits; order/first are unspecified then). */
+typedef struct vtn_uniq_counters
+{
+    uint32_t no_total_variants, no_unique_variants; /* uniq.cpp:48-49, :147-148 */
+} vtn_uniq_counters;
+int vtn_uniq(vtn_ctx* ctx, const vtn_batch* in, uint32_t* order, uint8_t* first, vtn_uniq_counters* counters,
+             int64_t* not_in_order);
+int vtn_uniq_resident(vtn_ctx* ctx, vtn_dbatch* db); /* async on the ctx stream; for bench / pipelines */
+int vtn_dbatch_fetch_uniq(vtn_ctx* ctx, vtn_dbatch* db, uint32_t* order, uint8_t* first, vtn_uniq_counters* counters,
+                          int64_t* not_in_order);
 
 /* ---- HMM family: AHMM / LFHMM / RFHMM Viterbi realignment (annotate_indels' FlankDetector) ----
  * Replaces <model>::set_model + <model>::align + the result members/getters:

@@ -51,6 +51,10 @@ class VtnNormResult(C.Structure):
     ]
 
 
+class VtnUniqCounters(C.Structure):
+    _fields_ = [("no_total_variants", C.c_uint32), ("no_unique_variants", C.c_uint32)]
+
+
 class VtnDecompCounters(C.Structure):
     _fields_ = [
         ("no_variants", C.c_uint32),
@@ -105,6 +109,9 @@ SIGNATURES = {
         [C.c_void_p, C.POINTER(VtnBatch), c_u32p, c_u16p, c_u64p, C.POINTER(VtnDecompCounters), C.POINTER(VtnNormResult)],
     ),
     "vtn_decompose_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
+    "vtn_uniq": (C.c_int, [C.c_void_p, C.POINTER(VtnBatch), c_u32p, c_u8p, C.POINTER(VtnUniqCounters), C.POINTER(C.c_int64)]),
+    "vtn_uniq_resident": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "vtn_dbatch_fetch_uniq": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_u8p, C.POINTER(VtnUniqCounters), C.POINTER(C.c_int64)]),
     "vtn_dbatch_fetch_decompose": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_u16p, c_u64p, C.POINTER(VtnDecompCounters)]),
     "vtn_hmm_align": (C.c_int, [C.c_void_p, C.POINTER(VtnHmmParams), C.POINTER(VtnHmmBatch), C.c_void_p, c_i32p, C.c_uint32]),
     "vtn_hmm_dbatch_create": (C.c_int, [C.c_void_p, C.POINTER(VtnHmmParams), C.POINTER(VtnHmmBatch), C.c_uint32, C.POINTER(C.c_void_p)]),

@@ -204,6 +204,27 @@ class Context:
         counters = [dc.no_variants, dc.no_biallelic, dc.no_multiallelic, dc.no_additional_biallelic]
         return src[:k], alt[:k], counters, res
 
+    def uniq(self, batch):
+        """vt uniq plan (include/vtn.h vtn_uniq): -> (order, first, [no_total_variants, no_unique_variants], not_in_order)"""
+        order = np.zeros(max(batch.n_rec, 1), np.uint32)
+        first = np.zeros(max(batch.n_rec, 1), np.uint8)
+        uc = L.VtnUniqCounters()
+        bad = C.c_int64(-1)
+        cb = batch.as_c()
+        self._chk(self.lib.vtn_uniq(self.h, C.byref(cb), _p(order, L.c_u32p), _p(first, L.c_u8p), C.byref(uc), C.byref(bad)), "vtn_uniq")
+        return order[:batch.n_rec], first[:batch.n_rec], [uc.no_total_variants, uc.no_unique_variants], int(bad.value)
+
+    def uniq_resident(self, db):
+        self._chk(self.lib.vtn_uniq_resident(self.h, db), "vtn_uniq_resident")
+
+    def fetch_uniq(self, db, n_rec):
+        order = np.zeros(max(n_rec, 1), np.uint32)
+        first = np.zeros(max(n_rec, 1), np.uint8)
+        uc = L.VtnUniqCounters()
+        bad = C.c_int64(-1)
+        self._chk(self.lib.vtn_dbatch_fetch_uniq(self.h, db, _p(order, L.c_u32p), _p(first, L.c_u8p), C.byref(uc), C.byref(bad)), "vtn_dbatch_fetch_uniq")
+        return order[:n_rec], first[:n_rec], [uc.no_total_variants, uc.no_unique_variants], int(bad.value)
+
     # ---- device-resident batches ----
     def upload(self, batch):
         h = C.c_void_p()

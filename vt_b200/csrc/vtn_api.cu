@@ -183,6 +183,7 @@ int vtn_dbatch_destroy(vtn_ctx* ctx, vtn_dbatch* d)
     if (!d) return VTN_OK;
     if (ctx) cudaSetDevice(ctx->device);
     if (d->fused) vtn_dbatch_destroy(ctx, d->fused);
+    vtn_uniq_dbatch_release(d);
     if (d->owns_inputs)
     {
         cudaFree(d->pos1); cudaFree(d->rid); cudaFree(d->allele_beg); cudaFree(d->allele_off); cudaFree(d->bytes);
@@ -497,4 +498,21 @@ int vtn_decompose_normalize(vtn_ctx* ctx, const vtn_batch* in, uint32_t* src_rec
     if (!out) return VTN_E_ARG;
     if (!ctx || !ctx->ref_loaded) return vtn_set_err(ctx, VTN_E_STATE, "vtn_decompose_normalize: no reference loaded");
     return decompose_host(ctx, in, src_rec, alt_idx, n_out, dcounters, out);
+}
+
+// Host-buffer uniq: H2D of the batch, one kernel, D2H of order / first and the two counters.
+int vtn_uniq(vtn_ctx* ctx, const vtn_batch* in, uint32_t* order, uint8_t* first, vtn_uniq_counters* counters, int64_t* not_in_order)
+{
+    if (!ctx) return VTN_E_ARG;
+    int rc = check_batch(ctx, in);
+    if (rc) return rc;
+    if (in->n_rec && (!order || !first)) return vtn_set_err(ctx, VTN_E_ARG, "vtn_uniq: null output arrays");
+    VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    rc = ensure_scratch(ctx, in->n_rec, in->n_allele, in->n_bytes);
+    if (rc) return rc;
+    rc = upload_inputs(ctx, in, ctx->scratch, ctx->stream);
+    if (rc) return rc;
+    rc = vtn_uniq_resident(ctx, ctx->scratch);
+    if (rc) return rc;
+    return vtn_dbatch_fetch_uniq(ctx, ctx->scratch, order, first, counters, not_in_order);
 }
