@@ -291,6 +291,110 @@ def run_c5(args, rank, world, local):
     emit(line)
 
 
+U1_RECORDS = int(os.environ.get("VTN_BENCH_U1_RECORDS", 20_000_000))
+
+
+def run_u1(args, rank, world, local):
+    """U1 (its own metric): `vt uniq` over sorted biallelic records with natural position collisions --
+    which duplicate survives and the reader's output order, decided on the device (vtn_uniq_kernel)."""
+    import torch
+    import torch.distributed as dist
+    from vt_b200 import Context
+    from vt_b200.api import Batch
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rng = np.random.default_rng(20260106 + 1000 * rank)
+    n = U1_RECORDS
+    pos = np.sort(rng.integers(1, 4 * n, n)).astype(np.int32)
+    rid = np.zeros(n, np.int32)
+    lens = np.ones(2 * n, np.int64)
+    indel = rng.random(n) < 0.2
+    lens[1::2][indel] = rng.integers(2, 5, int(indel.sum()))
+    aoff = np.zeros(2 * n + 1, np.uint32)
+    aoff[1:] = np.cumsum(lens)
+    data = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, int(aoff[-1]))]
+    batch = Batch(pos, rid, np.arange(0, 2 * n + 1, 2, dtype=np.uint32), aoff, data)
+    ctx = Context(local)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ctx.sync()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    db = ctx.upload(batch)
+    for _ in range(args.warmup):
+        ctx.uniq_resident(db)
+    ctx.sync()
+    sampler = ClockSampler(local)
+    barrier()
+    l0 = ctx.launch_count()
+    t0 = time.time()
+    ctx.timer_start()
+    for _ in range(args.steps):
+        ctx.uniq_resident(db)
+    ms_total = ctx.timer_stop()
+    barrier()
+    launches = ctx.launch_count() - l0
+    ms_step = max_over_ranks(ms_total / args.steps)
+    order, first, cnt, bad = ctx.fetch_uniq(db, n)
+    assert bad == -1 and cnt[0] == n
+    # end to end: host buffers in, order / first out, through vtn_uniq
+    e2e_steps = max(3, min(args.steps, 10))
+    ctx.uniq(batch)
+    barrier()
+    w0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        o2, f2, c2, _ = ctx.uniq(batch)
+    barrier()
+    e2e_ms = max_over_ranks(1e3 * (time.perf_counter() - w0) / e2e_steps)
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1)
+    assert c2 == cnt and np.array_equal(o2, order) and np.array_equal(f2, first)
+    ctx.free(db)
+    if rank != 0:
+        return
+    # algorithmic bytes: every record reads pos + rid (8 B) and writes order + first (5 B); a record of a position group of
+    # >= 2 also reads its allele_beg (4 B), allele_off (8 B) and allele bytes
+    same_prev = np.zeros(n, bool)
+    same_prev[1:] = pos[1:] == pos[:-1]
+    grouped = same_prev.copy()
+    grouped[:-1] |= same_prev[1:]
+    rec_bytes = (aoff[2::2].astype(np.int64) - aoff[:-1:2].astype(np.int64))
+    alg = 13 * n + int((12 + rec_bytes[grouped]).sum())
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = alg / (ms_total / args.steps / 1e3) / 1e9
+    h2d = 8 * n + 4 * (n + 1) + 4 * (2 * n + 1) + batch.n_bytes
+    d2h = 5 * n + 8
+    emit({
+        "metric": "uniq_records_per_s", "value": world * n / (ms_step / 1e3) / 1e6, "unit": "M records/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "U1: vt uniq over %d sorted synthetic biallelic records per GPU (80%% SNV, 20%% short insertions), %d in position groups of >= 2, %d unique" % (n, int(grouped.sum()), cnt[1]),
+                   "records_per_gpu": n, "l2": "inputs+outputs per step (%d MB) exceed the 126 MB L2; no explicit flush" % ((8 * n + 5 * n) // 1000000),
+                   "sharding": "independent batch per rank (a shard boundary must fall between position groups), no collective"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "kernel": "vtn_uniq_kernel", "algorithmic_bytes_per_launch": alg,
+                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)"},
+        "e2e": {"value": world * n / (e2e_ms / 1e3) / 1e6, "unit": "M records/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": e2e_ms, "steps": e2e_steps},
+        "gpu_launches": int(launches), "clocks": clocks,
+    })
+
+
 C3_RECORDS = int(os.environ.get("VTN_BENCH_C3_RECORDS", 12_500_000))
 
 
@@ -430,7 +534,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="vtn", choices=["vtn", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5"],
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5", "u1"],
                     help="c2 (default, the metric's configuration), c3 = multiallelic decompose+normalize fused, c4 = STR/homopolymer reference with maximal left shifts, "
                          "c5 = AHMM/LFHMM/RFHMM realignment (its own metric)")
     args = ap.parse_args()
@@ -446,6 +550,9 @@ def main():
         return
     if args.workload == "c3":
         run_c3(args, rank, world, local)
+        return
+    if args.workload == "u1":
+        run_u1(args, rank, world, local)
         return
 
     import torch

@@ -204,3 +204,23 @@ def test_header_pass_filter_placement_matches_reference(tmp_path):
     rc2, e2 = _run(helpers.VT_REF, ["decompose", vcf, "-o", o2])
     assert rc1 == rc2 == 0, (e1[-1000:], e2[-1000:])
     assert open(o1).read() == open(o2).read()
+
+
+# ---- vt uniq ----
+@pytest.mark.parametrize("name", ["uniq_a", "uniq_b"])
+def test_uniq_cli_reference_golden_bytes(name, tmp_path):
+    """vtn uniq against the output of the unmodified reference binary (tests/golden/make_uniq_golden.py), byte for byte"""
+    out = str(tmp_path / "out.vcf")
+    rc, err = _run(VTN, ["uniq", os.path.join(helpers.GOLDEN, name + "_in.vcf"), "-o", out])
+    assert rc == 0, err
+    assert open(out).read() == open(os.path.join(helpers.GOLDEN, name + "_out.vcf")).read()
+    exp = open(os.path.join(helpers.GOLDEN, name + "_out.stderr")).read()
+    assert _strip(err) == _strip(exp)
+
+
+def test_uniq_cli_not_in_order(tmp_path):
+    import uniq_helpers as U
+    vin = str(tmp_path / "in.vcf")
+    U.write_uniq_vcf(vin, [(0, 10, ["A", "C"], None), (0, 9, ["A", "C"], None)])
+    rc, err = _run(VTN, ["uniq", vin, "-o", str(tmp_path / "o.vcf")])
+    assert rc == 1 and "VCF file not in order" in err

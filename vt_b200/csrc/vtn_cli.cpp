@@ -12,6 +12,7 @@
 // record it has parsed (float32 storage, 6 significant digits), because the reference's output goes through that.
 // No CPU fallback: without a CUDA device vtn_ctx_create fails and the tool exits 1.
 #include <zlib.h>
+#include <algorithm>
 #include <cctype>
 #include <cmath>
 #include <cstdint>
@@ -470,7 +471,7 @@ void write_header(FILE* out, const Header& h, const char* extra_line)
         }
     }
     if (!pass_done) fprintf(out, "%s\n", pass_line);
-    fprintf(out, "%s\n", extra_line);
+    if (extra_line) fprintf(out, "%s\n", extra_line);
     fprintf(out, "%s\n", h.columns.c_str());
 }
 
@@ -1038,12 +1039,141 @@ int cmd_decompose(int argc, char** argv)
 }
 } // namespace
 
+// ------------------------------------------------------------------------------------------------------------
+// uniq  (Igor::uniq, uniq.cpp:110-156): the device decides which duplicate survives and in which order records leave
+// the synced reader (vtn_uniq); the host merges the OLD_VARIANT values of a group into its first record (:114-143).
+// ------------------------------------------------------------------------------------------------------------
+std::string info_value(const Tok& info, const char* key)
+{
+    const size_t kl = strlen(key);
+    for (const Tok& kv : split(info.first, info.second, ';'))
+        if (kv.second > kl && !memcmp(kv.first, key, kl) && kv.first[kl] == '=') return std::string(kv.first + kl + 1, kv.second - kl - 1);
+    return "";
+}
+
+int cmd_uniq(int argc, char** argv)
+{
+    Args a = parse_args("uniq", argc, argv);
+    fprintf(stderr, "uniq v0.57\n\n"); // print_options, uniq.cpp:158-165
+    fprintf(stderr, "options:     input VCF file        %s\n", a.in.c_str());
+    fprintf(stderr, "         [o] output VCF file       %s\n", a.out.c_str());
+    vtn_ctx* ctx = nullptr;
+    if (vtn_ctx_create(&ctx, a.device)) die(nullptr, "vtn_ctx_create");
+    Reader rd;
+    if (!rd.open(a.in))
+    {
+        fprintf(stderr, "[vtn] cannot open %s\n", a.in.c_str());
+        return 1;
+    }
+    Header h;
+    std::string line;
+    if (!read_header(rd, h, line))
+    {
+        fprintf(stderr, "[vtn] %s has no VCF header\n", a.in.c_str());
+        return 1;
+    }
+    FILE* out = open_out(a.out);
+    write_header(out, h, nullptr);
+    // rid = index in the header's contig dictionary (contigs missing from the header are appended as met, like htslib)
+    std::map<std::string, int> rid_cache;
+    for (const std::string& m : h.meta)
+        if (m.compare(0, 9, "##contig=") == 0)
+        {
+            std::string id = attr(m, "ID");
+            if (!rid_cache.count(id))
+            {
+                const int k = (int)rid_cache.size();
+                rid_cache[id] = k;
+            }
+        }
+    // the whole file is one batch: a position group must not be cut (see vtn_uniq.cu)
+    BatchBuf bb;
+    bool more = !line.empty();
+    while (more)
+    {
+        add_record(bb, nullptr, rid_cache, std::move(line));
+        more = rd.getline(line);
+    }
+    vtn_batch in = bb.view();
+    const size_t n = in.n_rec;
+    std::vector<uint32_t> order(n + 1);
+    std::vector<uint8_t> first(n + 1);
+    vtn_uniq_counters cnt = {0, 0};
+    int64_t bad = -1;
+    if (vtn_uniq(ctx, &in, order.data(), first.data(), &cnt, &bad)) die(ctx, "vtn_uniq");
+    if (bad >= 0)
+    { // fill_buffer, bcf_synced_reader.cpp:597-601
+        fprintf(stderr, "[E:bcf_synced_reader.cpp:599 fill_buffer] VCF file not in order: %s\n", a.in.c_str());
+        exit(1);
+    }
+    std::string o;
+    for (size_t k = 0; k < n;)
+    {
+        size_t e = k + 1;
+        while (e < n && !first[e]) ++e;
+        const std::string& ln = bb.lines[order[k]];
+        std::vector<Tok> col = split(ln.data(), ln.size(), '\t');
+        std::string merged;
+        if (e - k > 1)
+        { // uniq.cpp:114-143: distinct OLD_VARIANT values of the group in pop order
+            std::vector<std::string> seen;
+            for (size_t j = k; j < e; ++j)
+            {
+                const std::string& lj = bb.lines[order[j]];
+                std::vector<Tok> cj = split(lj.data(), lj.size(), '\t');
+                std::string v = info_value(cj[7], "OLD_VARIANT");
+                if (v.empty() || std::find(seen.begin(), seen.end(), v) != seen.end()) continue;
+                seen.push_back(v);
+                if (!merged.empty()) merged.push_back(',');
+                merged += v;
+            }
+        }
+        o.clear();
+        for (int c = 0; c < 5; ++c)
+        {
+            if (c) o.push_back('\t');
+            o.append(col[c].first, col[c].second);
+        }
+        if (merged.empty())
+            put_tail(o, h, col, "");
+        else
+        { // bcf_update_info_string: an existing OLD_VARIANT keeps its place, a new one goes last
+            std::string info;
+            bool replaced = false;
+            for (const Tok& kv : split(col[7].first, col[7].second, ';'))
+            {
+                if (!kv.second || (kv.second == 1 && kv.first[0] == '.')) continue;
+                if (!info.empty()) info.push_back(';');
+                if (kv.second > 12 && !memcmp(kv.first, "OLD_VARIANT=", 12))
+                {
+                    info += "OLD_VARIANT=" + merged;
+                    replaced = true;
+                }
+                else
+                    info.append(kv.first, kv.second);
+            }
+            if (!replaced) info += (info.empty() ? "" : ";") + ("OLD_VARIANT=" + merged);
+            std::vector<Tok> c2 = col;
+            c2[7] = Tok(info.data(), info.size());
+            put_tail(o, h, c2, "");
+        }
+        fwrite(o.data(), 1, o.size(), out);
+        fputc('\n', out);
+        k = e;
+    }
+    if (out != stdout) fclose(out);
+    fprintf(stderr, "\nstats: Total number of observed variants   %u\n", cnt.no_total_variants); // print_stats, uniq.cpp:167-171
+    fprintf(stderr, "       Total number of unique variants     %u\n\n", cnt.no_unique_variants);
+    vtn_ctx_destroy(ctx);
+    return 0;
+}
+
 int main(int argc, char** argv)
 {
     clock_t t0 = clock();
     if (argc < 2)
     {
-        fprintf(stderr, "usage: vtn normalize|decompose [options] <in.vcf>   (B200 drop-in for vt's decompose/normalize path)\n");
+        fprintf(stderr, "usage: vtn normalize|decompose|uniq [options] <in.vcf>   (B200 drop-in for vt's decompose/normalize path)\n");
         return 1;
     }
     std::string cmd = argv[1];
@@ -1055,6 +1185,11 @@ int main(int argc, char** argv)
         cmd_decompose(argc - 1, argv + 1);
         print = true;
         for (int k = 2; k < argc; ++k) print = print && strcmp(argv[k], "-q");
+    }
+    else if (cmd == "uniq")
+    {
+        cmd_uniq(argc - 1, argv + 1);
+        print = true;
     }
     else
     {
