@@ -648,3 +648,56 @@ int32_t vto_uniq_plan(const vto_batch* in, uint32_t* order, uint8_t* first, uint
     free(S.pq);
     return 0;
 }
+
+/* ---------------------------------------------------------------------------------------------------------
+ * BCFOrderedWriter (bcf_ordered_writer.cpp:141-210 write, :252-300 flush), restated literally with the buffer as a
+ * list whose front holds the largest position.  order[k] = arrival index of the k-th record written;
+ * late_front[v] = position of the buffer's front when record v triggered the "Might not be sorted" warning (:163-179),
+ * INT32_MIN otherwise.  window == 0 writes straight through (:193-203).
+ * --------------------------------------------------------------------------------------------------------- */
+int32_t vto_writer_order(uint32_t n, const int32_t* rid, const int32_t* pos1, int32_t window, uint32_t* order, int32_t* late_front)
+{
+    uint32_t* buf = (uint32_t*)malloc(sizeof(uint32_t) * ((size_t)n + 1)); /* buf[0] = front */
+    uint32_t nb = 0, k = 0;
+    if (!buf) return -1;
+    for (uint32_t v = 0; v < n; ++v)
+    {
+        late_front[v] = INT32_MIN;
+        if (!window)
+        {
+            order[k++] = v;
+            continue;
+        }
+        if (nb == 0)
+        {
+            buf[nb++] = v; /* push_front on an empty list */
+            continue;
+        }
+        if (rid[v] != rid[buf[nb - 1]])
+        { /* flush(true) then push_front */
+            while (nb) order[k++] = buf[--nb];
+            buf[nb++] = v;
+            continue;
+        }
+        uint32_t i = 0;
+        while (i < nb && !(pos1[v] >= pos1[buf[i]])) ++i; /* the equal sign keeps records in original order */
+        if (i == nb)
+        {
+            int32_t cutoff = pos1[buf[0]] - window;
+            if (cutoff < 1) cutoff = 1;
+            if (pos1[v] < cutoff) late_front[v] = pos1[buf[0]];
+        }
+        memmove(buf + i + 1, buf + i, sizeof(uint32_t) * (nb - i));
+        buf[i] = v;
+        ++nb;
+        if (nb > 1)
+        { /* flush(false) */
+            int32_t cutoff = pos1[buf[0]] - window;
+            if (cutoff < 1) cutoff = 1;
+            while (nb > 1 && pos1[buf[nb - 1]] <= cutoff) order[k++] = buf[--nb];
+        }
+    }
+    while (nb) order[k++] = buf[--nb]; /* close(): flush(true) */
+    free(buf);
+    return 0;
+}

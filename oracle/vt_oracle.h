@@ -81,6 +81,11 @@ int32_t vto_decompose_plan(const vto_batch* in, uint32_t* src_rec, uint16_t* alt
  * order", else -1.  Pinned against oracle/_ref/vt_ref uniq (tests/test_uniq_oracle.py, tests/golden/uniq_*). */
 int32_t vto_uniq_plan(const vto_batch* in, uint32_t* order, uint8_t* first, uint32_t counters[2], int64_t* not_in_order);
 
+/* BCFOrderedWriter::write / flush (bcf_ordered_writer.cpp:141-210, :252-300) as a literal list emulation: order[k] = arrival
+ * index of the k-th record written, late_front[v] = front position when v triggered the "Might not be sorted" warning
+ * (INT32_MIN otherwise).  Pinned through the command-line tests against oracle/_ref/vt_ref (window-limited ordering). */
+int32_t vto_writer_order(uint32_t n, const int32_t* rid, const int32_t* pos1, int32_t window, uint32_t* order, int32_t* late_front);
+
 #ifdef __cplusplus
 }
 #endif

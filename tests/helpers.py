@@ -58,6 +58,8 @@ class Oracle:
         self.lib.vto_normalize_batch.argtypes = [C.POINTER(VtoRef), C.POINTER(VtoBatch), C.POINTER(VtoNormOut)]
         self.lib.vto_decompose_plan.restype = C.c_int32
         self.lib.vto_decompose_plan.argtypes = [C.POINTER(VtoBatch), u32p, u16p, u64p, u32p]
+        self.lib.vto_writer_order.restype = C.c_int32
+        self.lib.vto_writer_order.argtypes = [C.c_uint32, i32p, i32p, C.c_int32, u32p, i32p]
         self.lib.vto_uniq_plan.restype = C.c_int32
         self.lib.vto_uniq_plan.argtypes = [C.POINTER(VtoBatch), u32p, u8p, u32p, i64p]
 
@@ -114,6 +116,16 @@ class Oracle:
         k = int(n_out.value)
         return src[:k], alt[:k], list(cnt)
 
+
+    def writer_order(self, rid, pos1, window):
+        rid = np.ascontiguousarray(rid, np.int32)
+        pos1 = np.ascontiguousarray(pos1, np.int32)
+        n = len(rid)
+        order = np.zeros(max(n, 1), np.uint32)
+        late = np.zeros(max(n, 1), np.int32)
+        rc = self.lib.vto_writer_order(n, rid.ctypes.data_as(i32p), pos1.ctypes.data_as(i32p), window, order.ctypes.data_as(u32p), late.ctypes.data_as(i32p))
+        assert rc == 0
+        return order[:n], late[:n]
 
     def uniq_plan(self, b):
         """-> (order, first, [no_total_variants, no_unique_variants], not_in_order)"""
