@@ -13,6 +13,7 @@
  *                        four counters (:139-143)
  *   vtn_uniq*            the record loop of Igor::uniq(), uniq.cpp:110-156, over BCFSyncedReader::read_next_position
  *                        (bcf_synced_reader.cpp:388-433, :594-637; comparator bcf_synced_reader.h:86-122)
+ *   vtn_writer_order     BCFOrderedWriter::write / flush, bcf_ordered_writer.cpp:141-210, :252-300
  *   vtn_hmm_*            AHMM/LFHMM/RFHMM::align (ahmm.cpp:468-587, lfhmm.cpp:489-654, rfhmm.cpp:516+)
  *
  * The library never exits or prints: every call returns 0 on success or a negative vtn_err code, and
@@ -175,6 +176,16 @@ int vtn_uniq(vtn_ctx* ctx, const vtn_batch* in, uint32_t* order, uint8_t* first,
 int vtn_uniq_resident(vtn_ctx* ctx, vtn_dbatch* db); /* async on the ctx stream; for bench / pipelines */
 int vtn_dbatch_fetch_uniq(vtn_ctx* ctx, vtn_dbatch* db, uint32_t* order, uint8_t* first, vtn_uniq_counters* counters,
                           int64_t* not_in_order);
+
+/* ---- ordered writer: the order in which BCFOrderedWriter (bcf_ordered_writer.cpp:141-210, :252-300) writes a stream ----
+ * rid[i] / pos1[i] = contig id and (new) 1-based position of the i-th record handed to the writer, window = its sorting
+ * window in bp (normalize: 10000, normalize.cpp:101,139; 0 = write straight through).  order[k] = index of the k-th record
+ * written: the list-insertion / windowed-flush rules are reproduced exactly, including records that arrive more than
+ * `window` behind (they are written late, not sorted in) and the flush at every rid change.  late_front (optional, may
+ * be NULL): for a record that triggers the writer's "Might not be sorted for window size" warning (:163-179) the position
+ * of the buffer's front at that moment (the text's "[last record]"), INT32_MIN otherwise. */
+int vtn_writer_order(vtn_ctx* ctx, uint32_t n, const int32_t* rid, const int32_t* pos1, int32_t window, uint32_t* order,
+                     int32_t* late_front);
 
 /* ---- HMM family: AHMM / LFHMM / RFHMM Viterbi realignment (annotate_indels' FlankDetector) ----
  * Replaces <model>::set_model + <model>::align + the result members/getters:
