@@ -183,9 +183,17 @@ int vtn_dbatch_fetch_uniq(vtn_ctx* ctx, vtn_dbatch* db, uint32_t* order, uint8_t
  * written: the list-insertion / windowed-flush rules are reproduced exactly, including records that arrive more than
  * `window` behind (they are written late, not sorted in) and the flush at every rid change.  late_front (optional, may
  * be NULL): for a record that triggers the writer's "Might not be sorted for window size" warning (:163-179) the position
- * of the buffer's front at that moment (the text's "[last record]"), INT32_MIN otherwise. */
+ * of the buffer's front at that moment (the text's "[last record]"), INT32_MIN otherwise.
+ * Streaming: n_pending (optional) receives how many records at the END of order[] are still inside the writer's buffer
+ * after the last record (they would only leave with the closing flush).  A caller with more input writes
+ * order[0 .. n - n_pending) now and hands the pending records, in arrival order, to the next call in front of the new
+ * records: replaying them rebuilds the same buffer without writing anything, so the concatenated output equals one call
+ * over the whole stream (tests/test_writer_gpu.py). */
 int vtn_writer_order(vtn_ctx* ctx, uint32_t n, const int32_t* rid, const int32_t* pos1, int32_t window, uint32_t* order,
-                     int32_t* late_front);
+                     int32_t* late_front, uint32_t* n_pending);
+/* Device-resident variant over the batch's own rid / pos1 (bench / pipelines; window > 0): async on the ctx stream. */
+int vtn_writer_order_resident(vtn_ctx* ctx, vtn_dbatch* db, int32_t window);
+int vtn_dbatch_fetch_writer_order(vtn_ctx* ctx, vtn_dbatch* db, uint32_t* order, int32_t* late_front, uint32_t* n_pending);
 
 /* ---- HMM family: AHMM / LFHMM / RFHMM Viterbi realignment (annotate_indels' FlankDetector) ----
  * Replaces <model>::set_model + <model>::align + the result members/getters:

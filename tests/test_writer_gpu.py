@@ -70,3 +70,24 @@ def test_writer_fullsize_property(ctx):
     assert (late == NONE).all()
     exp = np.lexsort((np.arange(n), pos, rid)).astype(np.uint32)
     np.testing.assert_array_equal(order, exp)
+
+
+@pytest.mark.parametrize("seed,window,chunk", [(1, 50, 700), (2, 5, 333), (3, 10000, 1000), (4, 1, 97)])
+def test_writer_streaming_equals_whole(ctx, oracle, seed, window, chunk):
+    """chunks + carried-over pending records == one call over the whole stream (order and warnings of the new records)"""
+    rid, pos = W.gen_jittered(np.random.default_rng(100 + seed), 6000, 12)
+    whole, late_whole = oracle.writer_order(rid, pos, window)
+    out, warned = [], []
+    carry = np.zeros(0, np.int64)  # global indices still buffered, in arrival order
+    for lo in range(0, len(rid), chunk):
+        new = np.arange(lo, min(lo + chunk, len(rid)))
+        idx = np.concatenate([carry, new])
+        order, late, pend = ctx.writer_order(rid[idx], pos[idx], window, want_pending=True)
+        done = len(idx) - pend
+        out.extend(idx[order[:done]])
+        carry = np.sort(idx[order[done:]])
+        fresh = np.arange(len(carry_prev := idx[:len(idx) - len(new)]), len(idx))
+        warned.extend(int(idx[k]) for k in fresh if late[k] != NONE)
+    out.extend(carry[np.lexsort((carry, pos[carry]))])  # closing flush: ascending (pos, arrival); all of one contig run
+    np.testing.assert_array_equal(np.array(out, np.uint32), whole)
+    assert warned == [int(v) for v in np.nonzero(late_whole != NONE)[0]]

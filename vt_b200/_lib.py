@@ -110,7 +110,9 @@ SIGNATURES = {
     ),
     "vtn_decompose_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "vtn_uniq": (C.c_int, [C.c_void_p, C.POINTER(VtnBatch), c_u32p, c_u8p, C.POINTER(VtnUniqCounters), C.POINTER(C.c_int64)]),
-    "vtn_writer_order": (C.c_int, [C.c_void_p, C.c_uint32, c_i32p, c_i32p, C.c_int32, c_u32p, c_i32p]),
+    "vtn_writer_order": (C.c_int, [C.c_void_p, C.c_uint32, c_i32p, c_i32p, C.c_int32, c_u32p, c_i32p, c_u32p]),
+    "vtn_writer_order_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
+    "vtn_dbatch_fetch_writer_order": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_i32p, c_u32p]),
     "vtn_uniq_resident": (C.c_int, [C.c_void_p, C.c_void_p]),
     "vtn_dbatch_fetch_uniq": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_u8p, C.POINTER(VtnUniqCounters), C.POINTER(C.c_int64)]),
     "vtn_dbatch_fetch_decompose": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_u16p, c_u64p, C.POINTER(VtnDecompCounters)]),

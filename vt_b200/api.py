@@ -214,16 +214,29 @@ class Context:
         self._chk(self.lib.vtn_uniq(self.h, C.byref(cb), _p(order, L.c_u32p), _p(first, L.c_u8p), C.byref(uc), C.byref(bad)), "vtn_uniq")
         return order[:batch.n_rec], first[:batch.n_rec], [uc.no_total_variants, uc.no_unique_variants], int(bad.value)
 
-    def writer_order(self, rid, pos1, window, want_late=True):
-        """BCFOrderedWriter's output order (include/vtn.h vtn_writer_order) -> (order, late_front or None)"""
+    def writer_order(self, rid, pos1, window, want_late=True, want_pending=False):
+        """BCFOrderedWriter's output order (include/vtn.h vtn_writer_order) -> (order, late_front or None[, n_pending])"""
         rid = np.ascontiguousarray(rid, np.int32)
         pos1 = np.ascontiguousarray(pos1, np.int32)
         n = int(rid.shape[0])
         order = np.zeros(max(n, 1), np.uint32)
         late = np.zeros(max(n, 1), np.int32) if want_late else None
+        pend = C.c_uint32(0)
         self._chk(self.lib.vtn_writer_order(self.h, n, _p(rid, L.c_i32p), _p(pos1, L.c_i32p), int(window), _p(order, L.c_u32p),
-                                            _p(late, L.c_i32p) if want_late else None), "vtn_writer_order")
+                                            _p(late, L.c_i32p) if want_late else None, C.byref(pend)), "vtn_writer_order")
+        if want_pending:
+            return order[:n], (late[:n] if want_late else None), int(pend.value)
         return order[:n], (late[:n] if want_late else None)
+
+    def writer_order_resident(self, db, window):
+        self._chk(self.lib.vtn_writer_order_resident(self.h, db, int(window)), "vtn_writer_order_resident")
+
+    def fetch_writer_order(self, db, n_rec):
+        order = np.zeros(max(n_rec, 1), np.uint32)
+        late = np.zeros(max(n_rec, 1), np.int32)
+        pend = C.c_uint32(0)
+        self._chk(self.lib.vtn_dbatch_fetch_writer_order(self.h, db, _p(order, L.c_u32p), _p(late, L.c_i32p), C.byref(pend)), "vtn_dbatch_fetch_writer_order")
+        return order[:n_rec], late[:n_rec], int(pend.value)
 
     def uniq_resident(self, db):
         self._chk(self.lib.vtn_uniq_resident(self.h, db), "vtn_uniq_resident")

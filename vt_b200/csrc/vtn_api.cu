@@ -184,6 +184,7 @@ int vtn_dbatch_destroy(vtn_ctx* ctx, vtn_dbatch* d)
     if (ctx) cudaSetDevice(ctx->device);
     if (d->fused) vtn_dbatch_destroy(ctx, d->fused);
     vtn_uniq_dbatch_release(d);
+    vtn_order_dbatch_release(d);
     if (d->owns_inputs)
     {
         cudaFree(d->pos1); cudaFree(d->rid); cudaFree(d->allele_beg); cudaFree(d->allele_off); cudaFree(d->bytes);

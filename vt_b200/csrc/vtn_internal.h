@@ -73,7 +73,8 @@ struct VtnDevScratch
     uint32_t* blo;            // [n_tiles] start of the tile's byte window
 };
 
-struct vtn_uniq_buffers; // vtn_uniq.cu
+struct vtn_uniq_buffers;  // vtn_uniq.cu
+struct vtn_order_buffers; // vtn_order.cu
 struct vtn_dbatch
 {
     uint32_t n_rec = 0, n_allele = 0;
@@ -110,6 +111,7 @@ struct vtn_dbatch
     struct vtn_dbatch* fused = nullptr; // biallelic batch materialised on device for the fused path
     bool owns_inputs = true;
     vtn_uniq_buffers* uniq = nullptr; // order / first / heap scratch of vtn_uniq_resident (allocated on first use)
+    vtn_order_buffers* order = nullptr; // arena of vtn_writer_order_resident (allocated on first use)
 };
 
 struct vtn_ctx
@@ -147,6 +149,7 @@ struct vtn_ctx
 };
 void vtn_hmm_ctx_release(vtn_ctx* ctx);
 void vtn_uniq_dbatch_release(vtn_dbatch* d);
+void vtn_order_dbatch_release(vtn_dbatch* d);
 
 int vtn_set_err(vtn_ctx* ctx, int code, const std::string& msg);
 #define VTN_CUDA(ctx, call)                                                                              \
