@@ -224,3 +224,23 @@ def test_uniq_cli_not_in_order(tmp_path):
     U.write_uniq_vcf(vin, [(0, 10, ["A", "C"], None), (0, 9, ["A", "C"], None)])
     rc, err = _run(VTN, ["uniq", vin, "-o", str(tmp_path / "o.vcf")])
     assert rc == 1 and "VCF file not in order" in err
+
+
+@needs_ref
+@pytest.mark.parametrize("window,batch", [(50, 64), (3, 37), (10, 1000000), (10000, 100)])
+def test_normalize_device_writer_order_streaming(tmp_path, window, batch):
+    """the writer's order comes from the device (vtn_writer_order), batch by batch with carried-over records: same bytes and the
+    same `Might not be sorted` warnings, in the same order, as the reference's sequential BCFOrderedWriter"""
+    rng = np.random.default_rng(77)
+    names, seqs = helpers.synth_reference(rng, n_contig=2, length=8000, n_runs=False)
+    fa = str(tmp_path / "ref.fa")
+    helpers.write_fasta(fa, names, seqs)
+    vcf = str(tmp_path / "in.vcf")
+    _synthetic_vcf(vcf, rng, names, seqs, 900, multi=False)
+    o1, o2 = str(tmp_path / "a.vcf"), str(tmp_path / "b.vcf")
+    p1 = subprocess.run([VTN, "normalize", vcf, "-r", fa, "-o", o1, "-w", str(window)], capture_output=True, text=True,
+                        env=dict(os.environ, VTN_CLI_BATCH=str(batch)))
+    p2 = subprocess.run([helpers.VT_REF, "normalize", vcf, "-r", fa, "-o", o2, "-w", str(window)], capture_output=True, text=True)
+    assert p1.returncode == p2.returncode == 0, (p1.stderr[-2000:], p2.stderr[-2000:])
+    assert open(o1).read() == open(o2).read()
+    assert _msgs(p1.stderr) == _msgs(p2.stderr)

@@ -316,6 +316,7 @@ struct OrderedWriter
         int rid;
         int32_t pos1;
         std::string chrom, line;
+        std::string msg; // stderr text of this record (printed when the record is handed to the writer)
     };
     FILE* out = stdout;
     int window = 0;
@@ -370,11 +371,74 @@ struct OrderedWriter
         {
             int32_t cutoff = std::max(buffer.front().pos1 - window, 1);
             if (v.pos1 < cutoff)
-                fprintf(stderr, "[bcf_ordered_writer.cpp:165 write] Might not be sorted for window size %d at current record %s:%d < %d (%d [last record] - %d), please increase window size to at least %d.\n",
+                fprintf(stderr, "[bcf_ordered_writer.cpp:170 write] Might not be sorted for window size %d at current record %s:%d < %d (%d [last record] - %d), please increase window size to at least %d.\n",
                         window, v.chrom.c_str(), v.pos1, cutoff, buffer.front().pos1, window, buffer.front().pos1 - v.pos1 + 1);
         }
         buffer.insert(i, std::move(v));
         flush(false);
+    }
+};
+
+// The same writer with the ORDER computed on the device (vtn_writer_order): records are collected per batch, the device
+// returns the order in which BCFOrderedWriter would have written them and how many are still inside its buffer; those are
+// carried into the next batch (replaying them rebuilds the buffer, include/vtn.h).  stderr text of a record (its own
+// messages, then the writer's warning for it) is printed in arrival order, like the sequential reference.
+struct DeviceWriter
+{
+    typedef OrderedWriter::Rec Rec;
+    FILE* out = stdout;
+    int window = 0;
+    vtn_ctx* ctx = nullptr;
+    std::vector<Rec> pend;
+    size_t n_carry = 0;
+    std::vector<int32_t> rid, pos, late;
+    std::vector<uint32_t> order;
+    void emit(const Rec& r)
+    {
+        fwrite(r.line.data(), 1, r.line.size(), out);
+        fputc('\n', out);
+    }
+    void write(Rec&& v)
+    {
+        if (!window)
+        {
+            if (!v.msg.empty()) fputs(v.msg.c_str(), stderr);
+            emit(v);
+            return;
+        }
+        pend.push_back(std::move(v));
+    }
+    void drain(bool final)
+    {
+        const size_t n = pend.size();
+        if (!n) return;
+        rid.resize(n), pos.resize(n), late.resize(n), order.resize(n);
+        for (size_t k = 0; k < n; ++k) rid[k] = pend[k].rid, pos[k] = pend[k].pos1;
+        uint32_t n_pending = 0;
+        if (vtn_writer_order(ctx, (uint32_t)n, rid.data(), pos.data(), window, order.data(), late.data(), &n_pending))
+        {
+            fprintf(stderr, "[vtn] vtn_writer_order: %s\n", vtn_last_error(ctx));
+            exit(1);
+        }
+        for (size_t k = n_carry; k < n; ++k)
+        {
+            if (!pend[k].msg.empty()) fputs(pend[k].msg.c_str(), stderr);
+            if (late[k] != INT32_MIN)
+            { // bcf_ordered_writer.cpp:163-179
+                const int32_t front = late[k], cutoff = std::max(front - window, 1);
+                fprintf(stderr, "[bcf_ordered_writer.cpp:170 write] Might not be sorted for window size %d at current record %s:%d < %d (%d [last record] - %d), please increase window size to at least %d.\n",
+                        window, pend[k].chrom.c_str(), pend[k].pos1, cutoff, front, window, front - pend[k].pos1 + 1);
+            }
+        }
+        const size_t done = final ? n : n - n_pending;
+        for (size_t k = 0; k < done; ++k) emit(pend[order[k]]);
+        std::vector<uint32_t> keep(order.begin() + done, order.end());
+        std::sort(keep.begin(), keep.end()); // arrival order
+        std::vector<Rec> next;
+        next.reserve(keep.size());
+        for (uint32_t k : keep) next.push_back(std::move(pend[k]));
+        pend.swap(next);
+        n_carry = pend.size();
     }
 };
 
@@ -564,12 +628,15 @@ int cmd_normalize(int argc, char** argv)
         fprintf(stderr, "[vtn] %s has no VCF header\n", a.in.c_str());
         return 1;
     }
-    OrderedWriter ow;
+    DeviceWriter ow;
     ow.out = open_out(a.out);
     ow.window = a.window;
+    ow.ctx = ctx;
     write_header(ow.out, h, "##INFO=<ID=OLD_VARIANT,Number=.,Type=String,Description=\"Original chr:pos:ref:alt encoding\">");
 
-    const size_t BATCH = 1u << 20;
+    size_t BATCH = 1u << 20;
+    if (const char* e = getenv("VTN_CLI_BATCH")) // records per device batch (tests use a small one to exercise the carry-over)
+        if (atol(e) > 0) BATCH = (size_t)atol(e);
     BatchBuf bb;
     std::map<std::string, int> rid_cache;
     std::vector<uint8_t> status, vtype, chg_bytes;
@@ -608,8 +675,10 @@ int cmd_normalize(int argc, char** argv)
             const uint32_t a0 = in.allele_beg[r], a1 = in.allele_beg[r + 1];
             const int code = st & VTN_ST_REFCODE_MASK;
             std::string chrom(col[0].first, col[0].second);
+            std::string msg;
             if (st & VTN_ST_FETCH_FAIL)
             { // faidx_fetch_seq returned NULL: variant_manip.cpp:70-75
+                ow.drain(false); // what the sequential writer had written / printed before this record
                 fprintf(stderr, "[E::faidx_adjust_position] The sequence \"%s\" was not found\n", chrom.c_str());
                 fprintf(stderr, "[variant_manip.cpp:72 is_not_ref_consistent] failure to extract base from fasta file: %s:%d-%d\n",
                         chrom.c_str(), in.pos1[r] - 1, in.pos1[r] - 1 + (int)col[3].second - 1);
@@ -621,16 +690,24 @@ int cmd_normalize(int argc, char** argv)
                 const int64_t pos0 = in.pos1[r] - 1, rl = (int64_t)col[3].second;
                 std::vector<uint8_t> fa((size_t)rl + 1, 0);
                 int64_t got = vtn_ref_fetch(ctx, in.rid[r], pos0, pos0 + rl - 1, 0, fa.data(), rl);
-                fprintf(stderr, "[variant_manip.cpp:96 is_not_ref_consistent] reference bases not consistent: %s:%d-%d  %.*s(REF) vs %.*s(FASTA)\n",
-                        chrom.c_str(), (int)pos0, (int)(pos0 + rl - 1), (int)rl, col[3].first, (int)(got > 0 ? got : 0), (const char*)fa.data());
+                char hdrbuf[256];
+                snprintf(hdrbuf, sizeof hdrbuf, "[variant_manip.cpp:96 is_not_ref_consistent] reference bases not consistent: %s:%d-%d  ", chrom.c_str(), (int)pos0, (int)(pos0 + rl - 1));
+                msg = hdrbuf;
+                msg.append(col[3].first, (size_t)rl);
+                msg += "(REF) vs ";
+                msg.append((const char*)fa.data(), (size_t)(got > 0 ? got : 0));
+                msg += "(FASTA)\n";
                 if (code > 2 - strict_level)
                 {
+                    ow.drain(false);
+                    fputs(msg.c_str(), stderr);
                     fprintf(stderr, "[normalize.cpp:209 normalize] Normalization not performed due to inconsistent reference sequences. (use -n or -m option to relax this)\n");
                     exit(1);
                 }
-                fprintf(stderr, "[normalize.cpp:214 normalize] Normalization skipped due to inconsistent reference sequences\n");
+                msg += "[normalize.cpp:214 normalize] Normalization skipped due to inconsistent reference sequences\n";
             }
             OrderedWriter::Rec rec;
+            rec.msg = std::move(msg);
             rec.rid = in.rid[r];
             rec.chrom = chrom;
             rec.pos1 = in.pos1[r];
@@ -684,11 +761,12 @@ int cmd_normalize(int argc, char** argv)
             put_tail(o, h, col, extra);
             ow.write(std::move(rec));
         }
+        ow.drain(false);
         for (int c = 0; c < 5; ++c) tot.bi[c] += out.counters.bi[c], tot.multi[c] += out.counters.multi[c];
         tot.no_variants += out.counters.no_variants;
         tot.no_refs += out.counters.no_refs;
     }
-    ow.flush(true);
+    ow.drain(true);
     if (ow.out != stdout) fclose(ow.out);
     if (print)
     { // print_stats, normalize.cpp:351-382
