@@ -14,6 +14,8 @@
  *   vtn_uniq*            the record loop of Igor::uniq(), uniq.cpp:110-156, over BCFSyncedReader::read_next_position
  *                        (bcf_synced_reader.cpp:388-433, :594-637; comparator bcf_synced_reader.h:86-122)
  *   vtn_writer_order     BCFOrderedWriter::write / flush, bcf_ordered_writer.cpp:141-210, :252-300
+ *   vtn_vcf_tokenize     vcf_parse1 + bcf_unpack(BCF_UN_STR) for CHROM/POS/REF/ALT (lib/htslib/vcf.c) behind
+ *                        BCFOrderedReader::read, bcf_ordered_reader.cpp:238-298
  *   vtn_hmm_*            AHMM/LFHMM/RFHMM::align (ahmm.cpp:468-587, lfhmm.cpp:489-654, rfhmm.cpp:516+)
  *
  * The library never exits or prints: every call returns 0 on success or a negative vtn_err code, and
@@ -194,6 +196,33 @@ int vtn_writer_order(vtn_ctx* ctx, uint32_t n, const int32_t* rid, const int32_t
 /* Device-resident variant over the batch's own rid / pos1 (bench / pipelines; window > 0): async on the ctx stream. */
 int vtn_writer_order_resident(vtn_ctx* ctx, vtn_dbatch* db, int32_t window);
 int vtn_dbatch_fetch_writer_order(vtn_ctx* ctx, vtn_dbatch* db, uint32_t* order, int32_t* late_front, uint32_t* n_pending);
+
+/* ---- VCF text -> batch: the five site columns of every record line, parsed on the device ----
+ * Replaces htslib's per-line text parse for what the path reads: vcf_parse1 (lib/htslib/vcf.c; tab split, CHROM, POS,
+ * "REF,ALT" -> d.allele[], ALT "." = no alternate allele) + bcf_unpack(BCF_UN_STR)/bcf_get_allele, i.e. what
+ * BCFOrderedReader::read (bcf_ordered_reader.cpp:238-298) hands to normalize.cpp:196 / decompose.cpp:205.
+ * text = record lines only (no '#' header), each ended by '\n' (a final line without one is accepted, "\r\n" too).
+ * Record r is text[line_off[r] .. line_off[r+1]) (with its line end); CHROM is its first chrom_len[r] bytes; the columns
+ * from QUAL on start at line_off[r] + tail_off[r] and are not parsed (pass them through).  pos1 / allele_beg /
+ * allele_off / bytes are exactly the arrays of vtn_batch; rid is the caller's (header dictionary) lookup of CHROM.
+ * status[r] = 1 for a line with fewer than 8 columns (no alleles are emitted for it).
+ * All arrays are caller-allocated with the capacities given; on VTN_E_CAPACITY the n_* fields hold what is needed. */
+typedef struct vtn_vcf_fields
+{
+    uint32_t cap_rec, cap_allele; /* in */
+    uint64_t cap_bytes;           /* in */
+    uint32_t n_rec, n_allele;     /* out */
+    uint64_t n_bytes;             /* out */
+    uint64_t* line_off;           /* [cap_rec+1] */
+    uint32_t* chrom_len;          /* [cap_rec] */
+    int32_t* pos1;                /* [cap_rec] */
+    uint32_t* tail_off;           /* [cap_rec] */
+    uint8_t* status;              /* [cap_rec] */
+    uint32_t* allele_beg;         /* [cap_rec+1] */
+    uint32_t* allele_off;         /* [cap_allele+1] */
+    uint8_t* bytes;               /* [cap_bytes] */
+} vtn_vcf_fields;
+int vtn_vcf_tokenize(vtn_ctx* ctx, const char* text, uint64_t n_text, vtn_vcf_fields* out);
 
 /* ---- HMM family: AHMM / LFHMM / RFHMM Viterbi realignment (annotate_indels' FlankDetector) ----
  * Replaces <model>::set_model + <model>::align + the result members/getters:

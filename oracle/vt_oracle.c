@@ -701,3 +701,71 @@ int32_t vto_writer_order(uint32_t n, const int32_t* rid, const int32_t* pos1, in
     free(buf);
     return 0;
 }
+
+/* ---------------------------------------------------------------------------------------------------------
+ * VCF text -> site columns: what the reference gets from htslib for every record line before the hot path
+ * sees it: vcf_parse1 (lib/htslib/vcf.c) splits the line on tabs, CHROM = column 1, POS = column 2 as a decimal integer,
+ * REF = column 4, ALT = column 5 split on ',' unless it is "." (then the record has the REF allele only; vcf.c fills
+ * d.allele[] from "REF,ALT"), and bcf_unpack(BCF_UN_STR) exposes them as the allele strings the path reads
+ * (bcf_get_allele, normalize.cpp:196, decompose.cpp:205).  Restated with memchr / strtol, one line at a time.
+ * text = record lines only (no header), '\n'-terminated (a missing final '\n' is accepted; a '\r' before it is stripped).
+ * status[r] = 0, or 1 when the line has fewer than 8 columns (vcf.c would report a truncated record).
+ * Returns the number of records, or -1 when a capacity is too small.
+ * --------------------------------------------------------------------------------------------------------- */
+int64_t vto_vcf_tokenize(const char* text, uint64_t n_text, uint64_t cap_rec, uint64_t cap_allele, uint64_t cap_bytes,
+                         uint64_t* line_off, uint32_t* chrom_len, int32_t* pos1, uint32_t* tail_off, uint8_t* status,
+                         uint32_t* allele_beg, uint32_t* allele_off, uint8_t* bytes)
+{
+    uint64_t r = 0, na = 0, nb = 0, o = 0;
+    allele_beg[0] = 0;
+    allele_off[0] = 0;
+    while (o < n_text)
+    {
+        const char* nl = (const char*)memchr(text + o, '\n', n_text - o);
+        uint64_t next = nl ? (uint64_t)(nl - text) + 1 : n_text;
+        uint64_t end = nl ? next - 1 : n_text; /* without the '\n' */
+        if (end > o && text[end - 1] == '\r') --end;
+        if (r >= cap_rec) return -1;
+        line_off[r] = o;
+        /* the first seven tabs */
+        uint64_t tab[7];
+        int nt = 0;
+        for (uint64_t i = o; i < end && nt < 7; ++i)
+            if (text[i] == '\t') tab[nt++] = i;
+        status[r] = nt < 7 ? 1 : 0;
+        chrom_len[r] = 0;
+        pos1[r] = 0;
+        tail_off[r] = 0;
+        if (nt >= 7)
+        {
+            chrom_len[r] = (uint32_t)(tab[0] - o);
+            pos1[r] = (int32_t)strtol(text + tab[0] + 1, NULL, 10);
+            tail_off[r] = (uint32_t)(tab[4] + 1 - o); /* QUAL column: everything from here on passes through untouched */
+            /* REF */
+            uint64_t len = tab[3] - (tab[2] + 1);
+            if (na + 1 > cap_allele || nb + len > cap_bytes) return -1;
+            memcpy(bytes + nb, text + tab[2] + 1, len);
+            nb += len;
+            allele_off[++na] = (uint32_t)nb;
+            /* ALT */
+            uint64_t a = tab[3] + 1, e = tab[4];
+            if (!(e - a == 1 && text[a] == '.'))
+            {
+                while (a <= e)
+                {
+                    uint64_t c = a;
+                    while (c < e && text[c] != ',') ++c;
+                    if (na + 1 > cap_allele || nb + (c - a) > cap_bytes) return -1;
+                    memcpy(bytes + nb, text + a, c - a);
+                    nb += c - a;
+                    allele_off[++na] = (uint32_t)nb;
+                    a = c + 1;
+                }
+            }
+        }
+        allele_beg[++r] = (uint32_t)na;
+        o = next;
+    }
+    line_off[r] = n_text;
+    return (int64_t)r;
+}

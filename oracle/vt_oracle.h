@@ -86,6 +86,12 @@ int32_t vto_uniq_plan(const vto_batch* in, uint32_t* order, uint8_t* first, uint
  * (INT32_MIN otherwise).  Pinned through the command-line tests against oracle/_ref/vt_ref (window-limited ordering). */
 int32_t vto_writer_order(uint32_t n, const int32_t* rid, const int32_t* pos1, int32_t window, uint32_t* order, int32_t* late_front);
 
+/* VCF record text -> CHROM length, POS, REF / ALT alleles (SoA of include/vtn.h) and the offset of the pass-through tail, as
+ * htslib's vcf_parse1 + bcf_unpack(BCF_UN_STR) hand them to the path; see vt_oracle.c.  Returns n_rec or -1 (capacity). */
+int64_t vto_vcf_tokenize(const char* text, uint64_t n_text, uint64_t cap_rec, uint64_t cap_allele, uint64_t cap_bytes,
+                         uint64_t* line_off, uint32_t* chrom_len, int32_t* pos1, uint32_t* tail_off, uint8_t* status,
+                         uint32_t* allele_beg, uint32_t* allele_off, uint8_t* bytes);
+
 #ifdef __cplusplus
 }
 #endif

@@ -58,6 +58,8 @@ class Oracle:
         self.lib.vto_normalize_batch.argtypes = [C.POINTER(VtoRef), C.POINTER(VtoBatch), C.POINTER(VtoNormOut)]
         self.lib.vto_decompose_plan.restype = C.c_int32
         self.lib.vto_decompose_plan.argtypes = [C.POINTER(VtoBatch), u32p, u16p, u64p, u32p]
+        self.lib.vto_vcf_tokenize.restype = C.c_int64
+        self.lib.vto_vcf_tokenize.argtypes = [C.c_char_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, u64p, u32p, i32p, u32p, u8p, u32p, u32p, u8p]
         self.lib.vto_writer_order.restype = C.c_int32
         self.lib.vto_writer_order.argtypes = [C.c_uint32, i32p, i32p, C.c_int32, u32p, i32p]
         self.lib.vto_uniq_plan.restype = C.c_int32
@@ -116,6 +118,24 @@ class Oracle:
         k = int(n_out.value)
         return src[:k], alt[:k], list(cnt)
 
+
+    def vcf_tokenize(self, text):
+        n = len(text)
+        cap_rec = text.count(b"\n") + 1
+        cap_allele = text.count(b",") + 2 * cap_rec
+        a = {"line_off": np.zeros(cap_rec + 1, np.uint64), "chrom_len": np.zeros(cap_rec, np.uint32), "pos1": np.zeros(cap_rec, np.int32),
+             "tail_off": np.zeros(cap_rec, np.uint32), "status": np.zeros(cap_rec, np.uint8), "allele_beg": np.zeros(cap_rec + 1, np.uint32),
+             "allele_off": np.zeros(cap_allele + 1, np.uint32), "bytes": np.zeros(max(n, 1), np.uint8)}
+        r = self.lib.vto_vcf_tokenize(text, n, cap_rec, cap_allele, n, a["line_off"].ctypes.data_as(u64p), a["chrom_len"].ctypes.data_as(u32p),
+                                      a["pos1"].ctypes.data_as(i32p), a["tail_off"].ctypes.data_as(u32p), a["status"].ctypes.data_as(u8p),
+                                      a["allele_beg"].ctypes.data_as(u32p), a["allele_off"].ctypes.data_as(u32p), a["bytes"].ctypes.data_as(u8p))
+        assert r >= 0
+        r = int(r)
+        na = int(a["allele_beg"][r])
+        nb = int(a["allele_off"][na])
+        return {"n_rec": r, "n_allele": na, "n_bytes": nb, "line_off": a["line_off"][:r + 1], "chrom_len": a["chrom_len"][:r], "pos1": a["pos1"][:r],
+                "tail_off": a["tail_off"][:r], "status": a["status"][:r], "allele_beg": a["allele_beg"][:r + 1], "allele_off": a["allele_off"][:na + 1],
+                "bytes": a["bytes"][:nb]}
 
     def writer_order(self, rid, pos1, window):
         rid = np.ascontiguousarray(rid, np.int32)

@@ -51,6 +51,13 @@ class VtnNormResult(C.Structure):
     ]
 
 
+class VtnVcfFields(C.Structure):
+    _fields_ = [("cap_rec", C.c_uint32), ("cap_allele", C.c_uint32), ("cap_bytes", C.c_uint64), ("n_rec", C.c_uint32), ("n_allele", C.c_uint32),
+                ("n_bytes", C.c_uint64), ("line_off", C.POINTER(C.c_uint64)), ("chrom_len", C.POINTER(C.c_uint32)), ("pos1", C.POINTER(C.c_int32)),
+                ("tail_off", C.POINTER(C.c_uint32)), ("status", C.POINTER(C.c_uint8)), ("allele_beg", C.POINTER(C.c_uint32)),
+                ("allele_off", C.POINTER(C.c_uint32)), ("bytes", C.POINTER(C.c_uint8))]
+
+
 class VtnUniqCounters(C.Structure):
     _fields_ = [("no_total_variants", C.c_uint32), ("no_unique_variants", C.c_uint32)]
 
@@ -113,6 +120,7 @@ SIGNATURES = {
     "vtn_writer_order": (C.c_int, [C.c_void_p, C.c_uint32, c_i32p, c_i32p, C.c_int32, c_u32p, c_i32p, c_u32p]),
     "vtn_writer_order_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
     "vtn_dbatch_fetch_writer_order": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_i32p, c_u32p]),
+    "vtn_vcf_tokenize": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint64, C.POINTER(VtnVcfFields)]),
     "vtn_uniq_resident": (C.c_int, [C.c_void_p, C.c_void_p]),
     "vtn_dbatch_fetch_uniq": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_u8p, C.POINTER(VtnUniqCounters), C.POINTER(C.c_int64)]),
     "vtn_dbatch_fetch_decompose": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_u16p, c_u64p, C.POINTER(VtnDecompCounters)]),
