@@ -395,6 +395,102 @@ def run_u1(args, rank, world, local):
     })
 
 
+T1_RECORDS = int(os.environ.get("VTN_BENCH_T1_RECORDS", 4_000_000))
+
+
+def run_t1(args, rank, world, local):
+    """T1 (its own metric): VCF record text -> SoA batch on the device (vtn_vcf_tokenize: eight launches), sites-only
+    lines shaped like C2 (80 % SNV, 20 % short indels / multiallelic)."""
+    import torch
+    import torch.distributed as dist
+    from vt_b200 import Context
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rng = np.random.default_rng(20260108 + 1000 * rank)
+    n = T1_RECORDS
+    pos = np.sort(rng.integers(1, 248_000_000, n))
+    b = np.array(list("ACGT"))
+    ref = b[rng.integers(0, 4, n)]
+    alt = b[rng.integers(0, 4, n)]
+    kind = rng.random(n)
+    ext = np.array(["", "AC", "GTT", ",T", ",TAA,G"])[np.where(kind < 0.8, 0, rng.integers(1, 5, n))]
+    lines = ["chr1\t%d\t.\t%s\t%s%s\t.\tPASS\tAC=1;AN=2" % (pos[i], ref[i], alt[i], ext[i]) for i in range(n)]
+    text = ("\n".join(lines) + "\n").encode()
+    del lines
+    ctx = Context(local)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ctx.sync()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    h, caps = ctx.vcf_upload(text)
+    for _ in range(args.warmup):
+        ctx.vcf_tokenize_resident(h)
+    ctx.sync()
+    sampler = ClockSampler(local)
+    barrier()
+    l0 = ctx.launch_count()
+    t0 = time.time()
+    ctx.timer_start()
+    for _ in range(args.steps):
+        ctx.vcf_tokenize_resident(h)
+    ms_total = ctx.timer_stop()
+    barrier()
+    launches = ctx.launch_count() - l0
+    ms_step = max_over_ranks(ms_total / args.steps)
+    f = ctx.vcf_fetch(h, caps)
+    assert f["n_rec"] == n and not f["status"].any() and np.array_equal(f["pos1"], pos.astype(np.int32))
+    e2e_steps = max(3, min(args.steps, 5))
+    ctx.vcf_tokenize(text)
+    barrier()
+    w0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        f2 = ctx.vcf_tokenize(text)
+    barrier()
+    e2e_ms = max_over_ranks(1e3 * (time.perf_counter() - w0) / e2e_steps)
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1)
+    assert all(np.array_equal(f[k], f2[k]) for k in ("line_off", "pos1", "allele_beg", "allele_off", "bytes", "tail_off", "chrom_len"))
+    ctx.vcf_free(h)
+    if rank != 0:
+        return
+    d2h = 25 * n + 8 + 4 * (f["n_allele"] + 1) + f["n_bytes"]
+    alg = len(text) + d2h
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = alg / (ms_total / args.steps / 1e3) / 1e9
+    emit({
+        "metric": "vcf_tokenize_records_per_s", "value": world * n / (ms_step / 1e3) / 1e6, "unit": "M records/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "T1: %d sites-only VCF record lines per GPU (%.1f MB of text, %.1f B per line; 80%% SNV, 20%% indel / multiallelic) -> pos1, allele_beg/off/bytes, line and tail offsets" % (n, len(text) / 1e6, len(text) / n),
+                   "records_per_gpu": n, "text_gb_per_s": world * len(text) / (ms_step / 1e3) / 1e9,
+                   "l2": "text + outputs per step (%d MB) exceed the 126 MB L2; no explicit flush" % (alg // 1000000),
+                   "host_sync": "one 4-byte readback of the line count per step sizes the record-level grids",
+                   "sharding": "independent text chunk per rank (cut at a line end), no collective"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "kernel": "vtk_* (eight launches)", "algorithmic_bytes_per_launch": alg,
+                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)"},
+        "e2e": {"value": world * n / (e2e_ms / 1e3) / 1e6, "unit": "M records/s", "h2d_bytes_per_step": len(text), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": e2e_ms, "steps": e2e_steps},
+        "gpu_launches": int(launches), "clocks": clocks,
+    })
+
+
 W1_RECORDS = int(os.environ.get("VTN_BENCH_W1_RECORDS", 20_000_000))
 
 
@@ -632,7 +728,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="vtn", choices=["vtn", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5", "u1", "w1"],
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5", "u1", "w1", "t1"],
                     help="c2 (default, the metric's configuration), c3 = multiallelic decompose+normalize fused, c4 = STR/homopolymer reference with maximal left shifts, "
                          "c5 = AHMM/LFHMM/RFHMM realignment (its own metric)")
     args = ap.parse_args()
@@ -654,6 +750,9 @@ def main():
         return
     if args.workload == "w1":
         run_w1(args, rank, world, local)
+        return
+    if args.workload == "t1":
+        run_t1(args, rank, world, local)
         return
 
     import torch

@@ -223,6 +223,13 @@ typedef struct vtn_vcf_fields
     uint8_t* bytes;               /* [cap_bytes] */
 } vtn_vcf_fields;
 int vtn_vcf_tokenize(vtn_ctx* ctx, const char* text, uint64_t n_text, vtn_vcf_fields* out);
+/* Device-resident variant (bench / pipelines): upload once, tokenize many times, fetch the arrays of the last run. */
+typedef struct vtn_vcf_dtext vtn_vcf_dtext;
+int vtn_vcf_dtext_create(vtn_ctx* ctx, const char* text, uint64_t n_text, uint32_t cap_rec, uint32_t cap_allele,
+                         uint64_t cap_bytes, vtn_vcf_dtext** h);
+int vtn_vcf_dtext_destroy(vtn_ctx* ctx, vtn_vcf_dtext* h);
+int vtn_vcf_tokenize_resident(vtn_ctx* ctx, vtn_vcf_dtext* h);
+int vtn_vcf_dtext_fetch(vtn_ctx* ctx, vtn_vcf_dtext* h, vtn_vcf_fields* out);
 
 /* ---- HMM family: AHMM / LFHMM / RFHMM Viterbi realignment (annotate_indels' FlankDetector) ----
  * Replaces <model>::set_model + <model>::align + the result members/getters:

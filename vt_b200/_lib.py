@@ -121,6 +121,10 @@ SIGNATURES = {
     "vtn_writer_order_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
     "vtn_dbatch_fetch_writer_order": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_i32p, c_u32p]),
     "vtn_vcf_tokenize": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint64, C.POINTER(VtnVcfFields)]),
+    "vtn_vcf_dtext_create": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint64, C.POINTER(C.c_void_p)]),
+    "vtn_vcf_dtext_destroy": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "vtn_vcf_tokenize_resident": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "vtn_vcf_dtext_fetch": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VtnVcfFields)]),
     "vtn_uniq_resident": (C.c_int, [C.c_void_p, C.c_void_p]),
     "vtn_dbatch_fetch_uniq": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_u8p, C.POINTER(VtnUniqCounters), C.POINTER(C.c_int64)]),
     "vtn_dbatch_fetch_decompose": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_u16p, c_u64p, C.POINTER(VtnDecompCounters)]),

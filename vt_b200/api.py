@@ -238,12 +238,8 @@ class Context:
         self._chk(self.lib.vtn_dbatch_fetch_writer_order(self.h, db, _p(order, L.c_u32p), _p(late, L.c_i32p), C.byref(pend)), "vtn_dbatch_fetch_writer_order")
         return order[:n_rec], late[:n_rec], int(pend.value)
 
-    def vcf_tokenize(self, text, cap_rec=None, cap_allele=None, cap_bytes=None):
-        """VCF record text (bytes) -> dict of the vtn_vcf_fields arrays (include/vtn.h vtn_vcf_tokenize)"""
-        n = len(text)
-        cap_rec = text.count(b"\n") + 1 if cap_rec is None else cap_rec
-        cap_allele = text.count(b",") + 2 * cap_rec if cap_allele is None else cap_allele
-        cap_bytes = n if cap_bytes is None else cap_bytes
+    @staticmethod
+    def _vcf_fields(cap_rec, cap_allele, cap_bytes):
         f = L.VtnVcfFields()
         f.cap_rec, f.cap_allele, f.cap_bytes = cap_rec, cap_allele, cap_bytes
         arr = {"line_off": np.zeros(cap_rec + 1, np.uint64), "chrom_len": np.zeros(max(cap_rec, 1), np.uint32), "pos1": np.zeros(max(cap_rec, 1), np.int32),
@@ -251,11 +247,43 @@ class Context:
                "allele_off": np.zeros(cap_allele + 1, np.uint32), "bytes": np.zeros(max(cap_bytes, 1), np.uint8)}
         for k, a in arr.items():
             setattr(f, k, a.ctypes.data_as(type(getattr(f, k))))
-        self._chk(self.lib.vtn_vcf_tokenize(self.h, text, n, C.byref(f)), "vtn_vcf_tokenize")
+        return f, arr
+
+    @staticmethod
+    def _vcf_result(f, arr):
         r, na, nb = int(f.n_rec), int(f.n_allele), int(f.n_bytes)
         return {"n_rec": r, "n_allele": na, "n_bytes": nb, "line_off": arr["line_off"][:r + 1], "chrom_len": arr["chrom_len"][:r], "pos1": arr["pos1"][:r],
                 "tail_off": arr["tail_off"][:r], "status": arr["status"][:r], "allele_beg": arr["allele_beg"][:r + 1],
                 "allele_off": arr["allele_off"][:na + 1], "bytes": arr["bytes"][:nb]}
+
+    @staticmethod
+    def _vcf_caps(text, cap_rec, cap_allele, cap_bytes):
+        cap_rec = text.count(b"\n") + 1 if cap_rec is None else cap_rec
+        cap_allele = text.count(b",") + 2 * cap_rec if cap_allele is None else cap_allele
+        return cap_rec, cap_allele, (len(text) if cap_bytes is None else cap_bytes)
+
+    def vcf_tokenize(self, text, cap_rec=None, cap_allele=None, cap_bytes=None):
+        """VCF record text (bytes) -> dict of the vtn_vcf_fields arrays (include/vtn.h vtn_vcf_tokenize)"""
+        f, arr = self._vcf_fields(*self._vcf_caps(text, cap_rec, cap_allele, cap_bytes))
+        self._chk(self.lib.vtn_vcf_tokenize(self.h, text, len(text), C.byref(f)), "vtn_vcf_tokenize")
+        return self._vcf_result(f, arr)
+
+    def vcf_upload(self, text, cap_rec=None, cap_allele=None, cap_bytes=None):
+        caps = self._vcf_caps(text, cap_rec, cap_allele, cap_bytes)
+        h = C.c_void_p()
+        self._chk(self.lib.vtn_vcf_dtext_create(self.h, text, len(text), caps[0], caps[1], caps[2], C.byref(h)), "vtn_vcf_dtext_create")
+        return h, caps
+
+    def vcf_tokenize_resident(self, h):
+        self._chk(self.lib.vtn_vcf_tokenize_resident(self.h, h), "vtn_vcf_tokenize_resident")
+
+    def vcf_fetch(self, h, caps):
+        f, arr = self._vcf_fields(*caps)
+        self._chk(self.lib.vtn_vcf_dtext_fetch(self.h, h, C.byref(f)), "vtn_vcf_dtext_fetch")
+        return self._vcf_result(f, arr)
+
+    def vcf_free(self, h):
+        self.lib.vtn_vcf_dtext_destroy(self.h, h)
 
     def uniq_resident(self, db):
         self._chk(self.lib.vtn_uniq_resident(self.h, db), "vtn_uniq_resident")

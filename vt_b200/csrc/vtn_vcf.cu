@@ -266,10 +266,11 @@ __global__ void __launch_bounds__(VTK_THREADS) vtk_alleles_kernel(const uint8_t*
                                                                   const unsigned long long* __restrict__ pre, const uint32_t* __restrict__ ref_off,
                                                                   const uint8_t* __restrict__ status, uint32_t* __restrict__ allele_off,
                                                                   uint8_t* __restrict__ bytes, uint32_t cap_allele, uint64_t cap_bytes,
-                                                                  unsigned long long total)
+                                                                  const unsigned long long* __restrict__ total_ptr)
 {
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n_rec) return;
+    const unsigned long long total = *total_ptr;
     if (r == 0) allele_off[0] = 0;
     if (status[r]) return;
     const unsigned long long pr = pre[r];
@@ -302,132 +303,173 @@ __global__ void __launch_bounds__(VTK_THREADS) vtk_alleles_kernel(const uint8_t*
 
 } // namespace
 
-// Host-buffer call: H2D of the text, the kernels above, D2H of every output array.
-int vtn_vcf_tokenize(vtn_ctx* ctx, const char* text, uint64_t n_text, vtn_vcf_fields* out)
+// ---- device-resident text + output buffers sized by the caller's capacities ----
+struct vtn_vcf_dtext
 {
-    if (!ctx || !out || (n_text && !text)) return vtn_set_err(ctx, VTN_E_ARG, "vtn_vcf_tokenize: bad arguments");
+    uint64_t n_text = 0;
+    bool open_tail = false;
+    uint32_t cap_rec = 0, cap_allele = 0;
+    uint64_t cap_bytes = 0;
+    uint32_t n_rec = 0; // of the last run
+    bool overflow_rec = false;
+    uint64_t n_rec_needed = 0;
+    uint8_t* text = nullptr;
+    uint32_t *agg = nullptr, *nl = nullptr;
+    uint64_t* line = nullptr;
+    unsigned long long *cnt = nullptr, *agg2 = nullptr, *tot = nullptr;
+    uint32_t *chrom = nullptr, *tail = nullptr, *ref = nullptr, *abeg = nullptr, *aoff = nullptr;
+    int32_t* pos = nullptr;
+    uint8_t *st = nullptr, *bytes = nullptr;
+};
+
+int vtn_vcf_dtext_destroy(vtn_ctx* ctx, vtn_vcf_dtext* h)
+{
+    if (!h) return VTN_OK;
+    if (ctx) cudaSetDevice(ctx->device);
+    cudaFree(h->text); cudaFree(h->agg); cudaFree(h->nl); cudaFree(h->line); cudaFree(h->cnt); cudaFree(h->agg2); cudaFree(h->tot);
+    cudaFree(h->chrom); cudaFree(h->tail); cudaFree(h->ref); cudaFree(h->abeg); cudaFree(h->aoff); cudaFree(h->pos); cudaFree(h->st);
+    cudaFree(h->bytes);
+    delete h;
+    return VTN_OK;
+}
+
+int vtn_vcf_dtext_create(vtn_ctx* ctx, const char* text, uint64_t n_text, uint32_t cap_rec, uint32_t cap_allele, uint64_t cap_bytes,
+                         vtn_vcf_dtext** out)
+{
+    if (!ctx || !out || (n_text && !text)) return vtn_set_err(ctx, VTN_E_ARG, "vtn_vcf_dtext_create: bad arguments");
+    if (n_text >= (1ull << 32)) return vtn_set_err(ctx, VTN_E_ARG, "vtn_vcf_tokenize: text must be < 4 GiB per call (allele bytes of a batch are 32-bit offsets)");
+    VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    vtn_vcf_dtext* h = new vtn_vcf_dtext();
+    h->n_text = n_text;
+    h->open_tail = n_text && text[n_text - 1] != '\n';
+    h->cap_rec = cap_rec;
+    h->cap_allele = cap_allele;
+    h->cap_bytes = cap_bytes;
+    const uint32_t n_tiles = (uint32_t)((n_text + VTK_TILE - 1) / VTK_TILE);
+    const uint32_t r_tiles = (cap_rec + VTK_RTILE - 1) / VTK_RTILE;
+    const size_t nr = (size_t)cap_rec + 16;
+    cudaError_t e = cudaSuccess;
+#define A(p, bytes) if (e == cudaSuccess) e = cudaMalloc((void**)&(p), (bytes))
+    A(h->text, n_text + 64);
+    A(h->agg, ((size_t)n_tiles + 1) * 4);
+    A(h->nl, 4);
+    A(h->line, nr * 8);
+    A(h->cnt, nr * 8);
+    A(h->agg2, ((size_t)r_tiles + 1) * 8);
+    A(h->tot, 8);
+    A(h->chrom, nr * 4);
+    A(h->tail, nr * 4);
+    A(h->ref, nr * 4);
+    A(h->abeg, nr * 4);
+    A(h->pos, nr * 4);
+    A(h->st, nr);
+    A(h->aoff, ((size_t)cap_allele + 16) * 4);
+    A(h->bytes, (size_t)cap_bytes + 16);
+#undef A
+    if (e == cudaSuccess && n_text) e = cudaMemcpyAsync(h->text, text, n_text, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(h->text + n_text, 0, 64, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess)
+    {
+        vtn_vcf_dtext_destroy(ctx, h);
+        return vtn_set_err(ctx, VTN_E_NOMEM, std::string("vtn_vcf_dtext_create: ") + cudaGetErrorString(e));
+    }
+    *out = h;
+    return VTN_OK;
+}
+
+// The eight launches on the ctx stream.  One 4-byte readback (the line count) sizes the record-level grids; everything else,
+// including the capacity checks, stays on the device until vtn_vcf_dtext_fetch.
+int vtn_vcf_tokenize_resident(vtn_ctx* ctx, vtn_vcf_dtext* h)
+{
+    if (!ctx || !h) return VTN_E_ARG;
+    cudaStream_t s = ctx->stream;
+    h->n_rec = 0;
+    h->overflow_rec = false;
+    if (!h->n_text) return VTN_OK;
+    const uint32_t n_tiles = (uint32_t)((h->n_text + VTK_TILE - 1) / VTK_TILE);
+    vtk_count_kernel<<<n_tiles, VTK_THREADS, 0, s>>>(h->text, h->n_text, h->agg);
+    vtk_scan_kernel<uint32_t><<<1, 1024, 0, s>>>(h->agg, n_tiles, h->nl);
+    uint32_t n_nl = 0;
+    VTN_CUDA(ctx, cudaMemcpyAsync(&n_nl, h->nl, sizeof n_nl, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaStreamSynchronize(s));
+    ctx->launches += 2;
+    h->n_rec_needed = (uint64_t)n_nl + (h->open_tail ? 1 : 0);
+    if (h->n_rec_needed > h->cap_rec)
+    {
+        h->overflow_rec = true;
+        return VTN_OK; // reported by fetch
+    }
+    const uint32_t n_rec = h->n_rec = (uint32_t)h->n_rec_needed;
+    if (!n_rec) return VTN_OK;
+    const uint32_t r_tiles = (n_rec + VTK_RTILE - 1) / VTK_RTILE;
+    const uint64_t zero = 0;
+    VTN_CUDA(ctx, cudaMemcpyAsync(h->line, &zero, 8, cudaMemcpyHostToDevice, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(h->line + n_rec, &h->n_text, 8, cudaMemcpyHostToDevice, s)); // rewritten with the same value when the text ends in a line end
+    vtk_lines_kernel<<<n_tiles, VTK_THREADS, 0, s>>>(h->text, h->n_text, h->agg, h->line, n_rec);
+    const uint32_t g = (n_rec + VTK_THREADS - 1) / VTK_THREADS;
+    VtkFields F{h->chrom, h->pos, h->tail, h->st, h->cnt, h->ref};
+    vtk_fields_kernel<<<g, VTK_THREADS, 0, s>>>(h->text, h->n_text, h->line, n_rec, F);
+    vtk_rsum_reduce_kernel<<<r_tiles, VTK_THREADS, 0, s>>>(h->cnt, n_rec, h->agg2);
+    vtk_scan_kernel<unsigned long long><<<1, 1024, 0, s>>>(h->agg2, r_tiles, h->tot);
+    vtk_rsum_apply_kernel<<<r_tiles, VTK_THREADS, 0, s>>>(h->cnt, n_rec, h->agg2, h->abeg);
+    vtk_alleles_kernel<<<g, VTK_THREADS, 0, s>>>(h->text, h->line, n_rec, h->cnt, h->ref, h->st, h->aoff, h->bytes, h->cap_allele, h->cap_bytes, h->tot);
+    VTN_CUDA(ctx, cudaGetLastError());
+    ctx->launches += 6;
+    return VTN_OK;
+}
+
+int vtn_vcf_dtext_fetch(vtn_ctx* ctx, vtn_vcf_dtext* h, vtn_vcf_fields* out)
+{
+    if (!ctx || !h || !out) return VTN_E_ARG;
+    cudaStream_t s = ctx->stream;
     out->n_rec = 0;
     out->n_allele = 0;
     out->n_bytes = 0;
-    if (!n_text)
+    if (h->overflow_rec)
+    {
+        out->n_rec = (uint32_t)(h->n_rec_needed > 0xffffffffull ? 0xffffffffu : h->n_rec_needed);
+        return vtn_set_err(ctx, VTN_E_CAPACITY, "vtn_vcf_tokenize: more records than cap_rec (n_rec is set)");
+    }
+    const uint32_t n_rec = h->n_rec;
+    if (!n_rec)
     {
         if (out->line_off) out->line_off[0] = 0;
         if (out->allele_beg) out->allele_beg[0] = 0;
         if (out->allele_off) out->allele_off[0] = 0;
         return VTN_OK;
     }
-    if (n_text >= (1ull << 32)) return vtn_set_err(ctx, VTN_E_ARG, "vtn_vcf_tokenize: text must be < 4 GiB per call (allele bytes of a batch are 32-bit offsets)");
-    VTN_CUDA(ctx, cudaSetDevice(ctx->device));
-    cudaStream_t s = ctx->stream;
-    const uint32_t n_tiles = (uint32_t)((n_text + VTK_TILE - 1) / VTK_TILE);
-    uint8_t* d_text = nullptr;
-    uint32_t* d_agg = nullptr;
-    uint32_t* d_nl = nullptr;
-    int rc = VTN_OK;
-    void* to_free[16];
-    int n_free = 0;
-#define VTK_TRY(call)                                                                                        \
-    do                                                                                                       \
-    {                                                                                                        \
-        cudaError_t e__ = (call);                                                                            \
-        if (e__ != cudaSuccess && rc == VTN_OK)                                                              \
-            rc = vtn_set_err(ctx, VTN_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__));          \
-    } while (0)
-#define VTK_ALLOC(ptr, bytes)                                       \
-    do                                                              \
-    {                                                               \
-        VTK_TRY(cudaMalloc((void**)&(ptr), (bytes)));               \
-        if (rc == VTN_OK) to_free[n_free++] = (void*)(ptr);         \
-    } while (0)
-    VTK_ALLOC(d_text, n_text + 64);
-    VTK_ALLOC(d_agg, ((size_t)n_tiles + 1) * sizeof(uint32_t));
-    VTK_ALLOC(d_nl, sizeof(uint32_t));
-    uint32_t n_nl = 0;
-    if (rc == VTN_OK)
-    {
-        VTK_TRY(cudaMemcpyAsync(d_text, text, n_text, cudaMemcpyHostToDevice, s));
-        VTK_TRY(cudaMemsetAsync(d_text + n_text, 0, 64, s));
-        vtk_count_kernel<<<n_tiles, VTK_THREADS, 0, s>>>(d_text, n_text, d_agg);
-        vtk_scan_kernel<uint32_t><<<1, 1024, 0, s>>>(d_agg, n_tiles, d_nl);
-        VTK_TRY(cudaMemcpyAsync(&n_nl, d_nl, sizeof n_nl, cudaMemcpyDeviceToHost, s));
-        VTK_TRY(cudaStreamSynchronize(s));
-        ctx->launches += 2;
-    }
-    const bool open_tail = text[n_text - 1] != '\n';
-    const uint64_t n_rec64 = (uint64_t)n_nl + (open_tail ? 1 : 0);
-    uint64_t* d_line = nullptr;
-    unsigned long long *d_cnt = nullptr, *d_agg2 = nullptr, *d_tot = nullptr;
-    uint32_t *d_chrom = nullptr, *d_tail = nullptr, *d_ref = nullptr, *d_abeg = nullptr, *d_aoff = nullptr;
-    int32_t* d_pos = nullptr;
-    uint8_t *d_st = nullptr, *d_bytes = nullptr;
-    if (rc == VTN_OK && n_rec64 > out->cap_rec)
-    {
-        out->n_rec = (uint32_t)(n_rec64 > 0xffffffffull ? 0xffffffffu : n_rec64);
-        rc = vtn_set_err(ctx, VTN_E_CAPACITY, "vtn_vcf_tokenize: more records than cap_rec (n_rec is set)");
-    }
-    const uint32_t n_rec = (uint32_t)n_rec64;
-    const uint32_t r_tiles = (n_rec + VTK_RTILE - 1) / VTK_RTILE;
+    if (n_rec > out->cap_rec) return vtn_set_err(ctx, VTN_E_CAPACITY, "vtn_vcf_dtext_fetch: cap_rec too small");
     unsigned long long total = 0;
-    if (rc == VTN_OK && n_rec)
-    {
-        const size_t nr = (size_t)n_rec + 16;
-        VTK_ALLOC(d_line, nr * 8);
-        VTK_ALLOC(d_cnt, nr * 8);
-        VTK_ALLOC(d_agg2, ((size_t)r_tiles + 1) * 8);
-        VTK_ALLOC(d_tot, 8);
-        VTK_ALLOC(d_chrom, nr * 4);
-        VTK_ALLOC(d_tail, nr * 4);
-        VTK_ALLOC(d_ref, nr * 4);
-        VTK_ALLOC(d_abeg, nr * 4);
-        VTK_ALLOC(d_pos, nr * 4);
-        VTK_ALLOC(d_st, nr);
-    }
-    if (rc == VTN_OK && n_rec)
-    {
-        const uint64_t zero = 0;
-        VTK_TRY(cudaMemcpyAsync(d_line, &zero, 8, cudaMemcpyHostToDevice, s));
-        VTK_TRY(cudaMemcpyAsync(d_line + n_rec, &n_text, 8, cudaMemcpyHostToDevice, s)); // overwritten with the same value when the text ends in '\n'
-        vtk_lines_kernel<<<n_tiles, VTK_THREADS, 0, s>>>(d_text, n_text, d_agg, d_line, n_rec);
-        const uint32_t g = (n_rec + VTK_THREADS - 1) / VTK_THREADS;
-        VtkFields F{d_chrom, d_pos, d_tail, d_st, d_cnt, d_ref};
-        vtk_fields_kernel<<<g, VTK_THREADS, 0, s>>>(d_text, n_text, d_line, n_rec, F);
-        vtk_rsum_reduce_kernel<<<r_tiles, VTK_THREADS, 0, s>>>(d_cnt, n_rec, d_agg2);
-        vtk_scan_kernel<unsigned long long><<<1, 1024, 0, s>>>(d_agg2, r_tiles, d_tot);
-        vtk_rsum_apply_kernel<<<r_tiles, VTK_THREADS, 0, s>>>(d_cnt, n_rec, d_agg2, d_abeg);
-        VTK_TRY(cudaMemcpyAsync(&total, d_tot, 8, cudaMemcpyDeviceToHost, s));
-        VTK_TRY(cudaStreamSynchronize(s));
-        VTK_TRY(cudaGetLastError());
-        ctx->launches += 5;
-    }
-    const uint64_t n_allele = total >> 32, n_bytes = total & ((1ull << 32) - 1);
+    VTN_CUDA(ctx, cudaMemcpyAsync(&total, h->tot, 8, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaStreamSynchronize(s));
+    const uint64_t n_allele = total >> 32, n_bytes = total & 0xffffffffull;
     out->n_rec = n_rec;
     out->n_allele = (uint32_t)n_allele;
     out->n_bytes = n_bytes;
-    if (rc == VTN_OK && (n_allele > out->cap_allele || n_bytes > out->cap_bytes || n_bytes >= (1ull << 32)))
-        rc = vtn_set_err(ctx, VTN_E_CAPACITY, "vtn_vcf_tokenize: allele capacity too small (n_allele / n_bytes are set)");
-    if (rc == VTN_OK && n_rec)
-    {
-        VTK_ALLOC(d_aoff, ((size_t)n_allele + 16) * 4);
-        VTK_ALLOC(d_bytes, (size_t)n_bytes + 16);
-    }
-    if (rc == VTN_OK && n_rec)
-    {
-        const uint32_t g = (n_rec + VTK_THREADS - 1) / VTK_THREADS;
-        vtk_alleles_kernel<<<g, VTK_THREADS, 0, s>>>(d_text, d_line, n_rec, d_cnt, d_ref, d_st, d_aoff, d_bytes, (uint32_t)n_allele, n_bytes, total);
-        VTK_TRY(cudaGetLastError());
-        ctx->launches += 1;
-        VTK_TRY(cudaMemcpyAsync(out->line_off, d_line, ((size_t)n_rec + 1) * 8, cudaMemcpyDeviceToHost, s));
-        VTK_TRY(cudaMemcpyAsync(out->chrom_len, d_chrom, (size_t)n_rec * 4, cudaMemcpyDeviceToHost, s));
-        VTK_TRY(cudaMemcpyAsync(out->pos1, d_pos, (size_t)n_rec * 4, cudaMemcpyDeviceToHost, s));
-        VTK_TRY(cudaMemcpyAsync(out->tail_off, d_tail, (size_t)n_rec * 4, cudaMemcpyDeviceToHost, s));
-        VTK_TRY(cudaMemcpyAsync(out->status, d_st, (size_t)n_rec, cudaMemcpyDeviceToHost, s));
-        VTK_TRY(cudaMemcpyAsync(out->allele_beg, d_abeg, ((size_t)n_rec + 1) * 4, cudaMemcpyDeviceToHost, s));
-        VTK_TRY(cudaMemcpyAsync(out->allele_off, d_aoff, ((size_t)n_allele + 1) * 4, cudaMemcpyDeviceToHost, s));
-        if (n_bytes) VTK_TRY(cudaMemcpyAsync(out->bytes, d_bytes, (size_t)n_bytes, cudaMemcpyDeviceToHost, s));
-        VTK_TRY(cudaStreamSynchronize(s));
-    }
-    for (int i = 0; i < n_free; ++i) cudaFree(to_free[i]);
-#undef VTK_TRY
-#undef VTK_ALLOC
+    if (n_allele > h->cap_allele || n_bytes > h->cap_bytes || n_allele > out->cap_allele || n_bytes > out->cap_bytes)
+        return vtn_set_err(ctx, VTN_E_CAPACITY, "vtn_vcf_tokenize: allele capacity too small (n_allele / n_bytes are set)");
+    VTN_CUDA(ctx, cudaMemcpyAsync(out->line_off, h->line, ((size_t)n_rec + 1) * 8, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(out->chrom_len, h->chrom, (size_t)n_rec * 4, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(out->pos1, h->pos, (size_t)n_rec * 4, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(out->tail_off, h->tail, (size_t)n_rec * 4, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(out->status, h->st, (size_t)n_rec, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(out->allele_beg, h->abeg, ((size_t)n_rec + 1) * 4, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(out->allele_off, h->aoff, ((size_t)n_allele + 1) * 4, cudaMemcpyDeviceToHost, s));
+    if (n_bytes) VTN_CUDA(ctx, cudaMemcpyAsync(out->bytes, h->bytes, (size_t)n_bytes, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaStreamSynchronize(s));
+    return VTN_OK;
+}
+
+// Host-buffer call: H2D of the text, the kernels above, D2H of every output array.
+int vtn_vcf_tokenize(vtn_ctx* ctx, const char* text, uint64_t n_text, vtn_vcf_fields* out)
+{
+    if (!ctx || !out || (n_text && !text)) return vtn_set_err(ctx, VTN_E_ARG, "vtn_vcf_tokenize: bad arguments");
+    vtn_vcf_dtext* h = nullptr;
+    int rc = vtn_vcf_dtext_create(ctx, text, n_text, out->cap_rec, out->cap_allele, out->cap_bytes, &h);
+    if (rc) return rc;
+    rc = vtn_vcf_tokenize_resident(ctx, h);
+    if (rc == VTN_OK) rc = vtn_vcf_dtext_fetch(ctx, h, out);
+    vtn_vcf_dtext_destroy(ctx, h);
     return rc;
 }
