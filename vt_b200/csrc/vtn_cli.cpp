@@ -570,26 +570,65 @@ struct BatchBuf
     }
 };
 
-// parse CHROM POS REF ALT of one line into the batch; ALT "." = no alternate allele (as htslib's parser)
-void add_record(BatchBuf& bb, vtn_ctx* ctx, std::map<std::string, int>& rid_cache, std::string&& line)
+// The site columns of a batch of record lines, parsed on the DEVICE (vtn_vcf_tokenize) instead of line by line on the host:
+// reads up to max_lines lines (the first one is already in `line`), fills the SoA batch; rid comes from the reference
+// (ref_ids) or from the order of appearance / the header dictionary in rid_cache, looked up once per run of equal CHROM.
+struct LineParser
 {
-    std::vector<Tok> col = split(line.data(), line.size(), '\t');
-    if (col.size() < 8)
+    std::string text;
+    std::vector<uint64_t> line_off;
+    std::vector<uint32_t> chrom_len, tail_off;
+    std::vector<uint8_t> status;
+    bool read_batch(Reader& rd, std::string& line, bool& more, size_t max_lines, BatchBuf& bb, vtn_ctx* ctx, bool ref_ids,
+                    std::map<std::string, int>& rid_cache)
     {
-        fprintf(stderr, "[vtn] malformed VCF record (fewer than 8 columns): %s\n", line.c_str());
-        exit(1);
+        bb.clear();
+        text.clear();
+        size_t commas = 0;
+        while (more && bb.lines.size() < max_lines)
+        {
+            text += line;
+            text.push_back('\n');
+            commas += (size_t)std::count(line.begin(), line.end(), ',');
+            bb.lines.push_back(std::move(line));
+            more = rd.getline(line);
+        }
+        const size_t n = bb.lines.size();
+        if (!n) return false;
+        line_off.resize(n + 1), chrom_len.resize(n), tail_off.resize(n), status.resize(n);
+        bb.pos1.resize(n), bb.allele_beg.resize(n + 1), bb.allele_off.resize(commas + 2 * n + 1), bb.bytes.resize(text.size() + 1);
+        vtn_vcf_fields f;
+        memset(&f, 0, sizeof f);
+        f.cap_rec = (uint32_t)n, f.cap_allele = (uint32_t)(commas + 2 * n), f.cap_bytes = text.size();
+        f.line_off = line_off.data(), f.chrom_len = chrom_len.data(), f.pos1 = bb.pos1.data(), f.tail_off = tail_off.data();
+        f.status = status.data(), f.allele_beg = bb.allele_beg.data(), f.allele_off = bb.allele_off.data(), f.bytes = bb.bytes.data();
+        if (vtn_vcf_tokenize(ctx, text.data(), text.size(), &f)) die(ctx, "vtn_vcf_tokenize");
+        bb.allele_off.resize((size_t)f.n_allele + 1);
+        bb.bytes.resize((size_t)f.n_bytes);
+        bb.rid.resize(n);
+        const char* prev = nullptr;
+        uint32_t prev_len = 0;
+        int prev_rid = -1;
+        for (size_t r = 0; r < n; ++r)
+        {
+            if (status[r])
+            {
+                fprintf(stderr, "[vtn] malformed VCF record (fewer than 8 columns): %s\n", bb.lines[r].c_str());
+                exit(1);
+            }
+            const char* c = text.data() + line_off[r];
+            if (!(prev && prev_len == chrom_len[r] && !memcmp(prev, c, prev_len)))
+            {
+                std::string chrom(c, chrom_len[r]);
+                auto it = rid_cache.find(chrom);
+                if (it == rid_cache.end()) it = rid_cache.emplace(chrom, ref_ids ? vtn_ref_contig_id(ctx, chrom.c_str()) : (int)rid_cache.size()).first;
+                prev = c, prev_len = chrom_len[r], prev_rid = it->second;
+            }
+            bb.rid[r] = prev_rid;
+        }
+        return true;
     }
-    std::string chrom(col[0].first, col[0].second);
-    auto it = rid_cache.find(chrom);
-    if (it == rid_cache.end()) it = rid_cache.emplace(chrom, ctx ? vtn_ref_contig_id(ctx, chrom.c_str()) : (int)rid_cache.size()).first;
-    bb.rid.push_back(it->second);
-    bb.pos1.push_back((int32_t)strtol(col[1].first, nullptr, 10));
-    bb.add_allele(col[3].first, col[3].second);
-    if (!(col[4].second == 1 && col[4].first[0] == '.'))
-        for (const Tok& a : split(col[4].first, col[4].second, ',')) bb.add_allele(a.first, a.second);
-    bb.allele_beg.push_back((uint32_t)bb.allele_off.size() - 1);
-    bb.lines.push_back(std::move(line));
-}
+};
 
 // ------------------------------------------------------------------------------------------------------------
 // normalize  (Igor::normalize, normalize.cpp:174-330)
@@ -646,14 +685,10 @@ int cmd_normalize(int argc, char** argv)
     vtn_norm_counters tot;
     memset(&tot, 0, sizeof tot);
     bool more = !line.empty();
+    LineParser lp;
     while (more)
     {
-        bb.clear();
-        while (more && bb.lines.size() < BATCH)
-        {
-            add_record(bb, ctx, rid_cache, std::move(line));
-            more = rd.getline(line);
-        }
+        lp.read_batch(rd, line, more, BATCH, bb, ctx, true, rid_cache);
         vtn_batch in = bb.view();
         const size_t n = in.n_rec;
         status.resize(n + 1), vtype.resize(n + 1);
@@ -924,14 +959,10 @@ int cmd_decompose(int argc, char** argv)
     memset(&tot, 0, sizeof tot);
     bool more = !line.empty();
     std::string o;
+    LineParser lp;
     while (more)
     {
-        bb.clear();
-        while (more && bb.lines.size() < BATCH)
-        {
-            add_record(bb, nullptr, rid_cache, std::move(line));
-            more = rd.getline(line);
-        }
+        lp.read_batch(rd, line, more, BATCH, bb, ctx, false, rid_cache);
         vtn_batch in = bb.view();
         const uint64_t bound = vtn_decompose_out_bound(&in);
         src_rec.resize(bound + 1), alt_idx.resize(bound + 1);
@@ -1167,11 +1198,8 @@ int cmd_uniq(int argc, char** argv)
     // the whole file is one batch: a position group must not be cut (see vtn_uniq.cu)
     BatchBuf bb;
     bool more = !line.empty();
-    while (more)
-    {
-        add_record(bb, nullptr, rid_cache, std::move(line));
-        more = rd.getline(line);
-    }
+    LineParser lp;
+    lp.read_batch(rd, line, more, (size_t)-1, bb, ctx, false, rid_cache);
     vtn_batch in = bb.view();
     const size_t n = in.n_rec;
     std::vector<uint32_t> order(n + 1);
