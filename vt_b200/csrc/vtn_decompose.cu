@@ -96,34 +96,83 @@ __global__ void __launch_bounds__(VTD_TILE) vtd_count_kernel(VtnDevBatchView B, 
     }
 }
 
-// exclusive scan of the tile aggregates in place (one block; n_tiles is a few 10^4)
+// exclusive scan of the tile aggregates in place (one block; n_tiles is a few 10^4).  Every warp owns a contiguous chunk and
+// walks it 32 tiles at a time with coalesced loads (four steps' loads in flight before the first warp scan); pass 1 reduces
+// the chunk, the 32 chunk totals are scanned through shared memory, pass 2 rescans with the carry and writes.
 __global__ void __launch_bounds__(1024) vtd_scan_kernel(unsigned long long* agg_a, unsigned long long* agg_b, uint32_t n_tiles)
 {
-    __shared__ unsigned long long s_a[1024], s_b[1024];
-    const uint32_t per = (n_tiles + 1023) / 1024;
-    const uint32_t lo = threadIdx.x * per, hi = min(lo + per, n_tiles);
-    unsigned long long sa = 0, sb = 0;
-    for (uint32_t t = lo; t < hi; ++t) { sa += agg_a[t]; sb += agg_b[t]; }
-    s_a[threadIdx.x] = sa;
-    s_b[threadIdx.x] = sb;
-    __syncthreads();
-    for (int o = 1; o < 1024; o <<= 1)
+    __shared__ unsigned long long s_a[32], s_b[32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t per = ((n_tiles + 31) / 32 + 31) & ~31u; // tiles per warp, a multiple of 32
+    const uint32_t lo = min(warp * per, n_tiles), hi = min(lo + per, n_tiles);
+    unsigned long long ta = 0, tb = 0;
+    for (uint32_t t = lo; t < hi; t += 128)
     {
-        unsigned long long xa = 0, xb = 0;
-        if ((int)threadIdx.x >= o) { xa = s_a[threadIdx.x - o]; xb = s_b[threadIdx.x - o]; }
-        __syncthreads();
-        s_a[threadIdx.x] += xa;
-        s_b[threadIdx.x] += xb;
-        __syncthreads();
+        unsigned long long xa[4], xb[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+        {
+            const uint32_t i = t + 32 * u + lane;
+            xa[u] = i < hi ? agg_a[i] : 0ull;
+            xb[u] = i < hi ? agg_b[i] : 0ull;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+        {
+            ta += xa[u];
+            tb += xb[u];
+        }
     }
-    unsigned long long pa = s_a[threadIdx.x] - sa, pb = s_b[threadIdx.x] - sb;
-    for (uint32_t t = lo; t < hi; ++t)
+    for (int o = 16; o; o >>= 1)
     {
-        const unsigned long long xa = agg_a[t], xb = agg_b[t];
-        agg_a[t] = pa;
-        agg_b[t] = pb;
-        pa += xa;
-        pb += xb;
+        ta += __shfl_xor_sync(0xffffffffu, ta, o);
+        tb += __shfl_xor_sync(0xffffffffu, tb, o);
+    }
+    if (lane == 0)
+    {
+        s_a[warp] = ta;
+        s_b[warp] = tb;
+    }
+    __syncthreads();
+    unsigned long long ca = 0, cb = 0; // carry into this warp's chunk
+    for (int w = 0; w < warp; ++w)
+    {
+        ca += s_a[w];
+        cb += s_b[w];
+    }
+    for (uint32_t t = lo; t < hi; t += 128)
+    {
+        unsigned long long xa[4], xb[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+        {
+            const uint32_t i = t + 32 * u + lane;
+            xa[u] = i < hi ? agg_a[i] : 0ull;
+            xb[u] = i < hi ? agg_b[i] : 0ull;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+        {
+            unsigned long long ia = xa[u], ib = xb[u];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1)
+            {
+                const unsigned long long pa = __shfl_up_sync(0xffffffffu, ia, o), pb = __shfl_up_sync(0xffffffffu, ib, o);
+                if (lane >= o)
+                {
+                    ia += pa;
+                    ib += pb;
+                }
+            }
+            const uint32_t i = t + 32 * u + lane;
+            if (i < hi)
+            {
+                agg_a[i] = ca + ia - xa[u];
+                agg_b[i] = cb + ib - xb[u];
+            }
+            ca += __shfl_sync(0xffffffffu, ia, 31);
+            cb += __shfl_sync(0xffffffffu, ib, 31);
+        }
     }
 }
 
@@ -219,60 +268,95 @@ __global__ void __launch_bounds__(VTD_TILE) vtd_emit_kernel(VtnDevBatchView B, u
         }
         __syncthreads();
         const uint32_t n_in = min((uint32_t)VTD_TILE, B.n_rec - tile * VTD_TILE);
-        for (uint32_t j = tid; j < tot; j += VTD_TILE)
+        for (uint32_t jb = 0; jb < tot; jb += VTD_TILE)
         {
-            uint32_t lo;
-            if (expanded)
-                lo = s_src[j];
-            else
+            const uint32_t j = jb + tid;
+            const bool act = j < tot;
+            // byte segments of this output: REF (src0 -> dst0, l0) and ALT (src1 -> dst1, l1); the first four bytes of each are
+            // copied inline, longer ones by the whole warp afterwards, so a long allele does not make 31 lanes wait
+            uint32_t src0 = 0, l0 = 0, src1 = 0, l1 = 0;
+            unsigned long long dst0 = 0, dst1 = 0;
+            if (act)
             {
-                uint32_t hi = n_in - 1; // last record whose first output <= j
-                lo = 0;
-                while (lo < hi)
+                uint32_t lo;
+                if (expanded)
+                    lo = s_src[j];
+                else
                 {
-                    const uint32_t mid = (lo + hi + 1) >> 1;
-                    if (s_k[mid] <= j) lo = mid;
-                    else hi = mid - 1;
+                    uint32_t hi = n_in - 1; // last record whose first output <= j
+                    lo = 0;
+                    while (lo < hi)
+                    {
+                        const uint32_t mid = (lo + hi + 1) >> 1;
+                        if (s_k[mid] <= j) lo = mid;
+                        else hi = mid - 1;
+                    }
+                }
+                const uint32_t rec = lo;
+                const unsigned long long ea = s_ea[rec];
+                const uint32_t rr = tile * VTD_TILE + rec;
+                const unsigned long long k = k0 + j;
+                const uint32_t i = j - s_k[rec] + 1;                       // ALT index (1-based) for n >= 2
+                const uint32_t rab = s_ab[rec], rn = s_n[rec];
+                const uint32_t ro0 = __ldg(B.allele_off + rab), ro1 = __ldg(B.allele_off + rab + 1);
+                const uint32_t len0 = ro1 - ro0;
+                const unsigned long long slot = 2 * (ea >> 31) - (ea & 0x7fffffffull) + 2ull * (i - 1);
+                src_rec[k] = rr;
+                if (rn < 2)
+                {
+                    alt_idx[k] = 0;
+                    if (materialise)
+                    {
+                        const unsigned long long ob = s_ob[rec];
+                        F.pos1[k] = __ldg(B.pos1 + rr);
+                        F.rid[k] = __ldg(B.rid + rr);
+                        F.allele_beg[k] = (uint32_t)slot;
+                        F.allele_off[slot] = (uint32_t)ob;
+                        src0 = ro0, dst0 = ob, l0 = len0;
+                    }
+                }
+                else
+                {
+                    alt_idx[k] = (uint16_t)i;
+                    if (materialise)
+                    {
+                        const uint32_t oa = __ldg(B.allele_off + rab + i), oa2 = __ldg(B.allele_off + rab + i + 1);
+                        const unsigned long long ob = s_ob[rec] + (unsigned long long)(i - 1) * len0 + (oa - ro1);
+                        F.pos1[k] = __ldg(B.pos1 + rr);
+                        F.rid[k] = __ldg(B.rid + rr);
+                        F.allele_beg[k] = (uint32_t)slot;
+                        F.allele_off[slot] = (uint32_t)ob;
+                        F.allele_off[slot + 1] = (uint32_t)(ob + len0);
+                        src0 = ro0, dst0 = ob, l0 = len0;
+                        src1 = oa, dst1 = ob + len0, l1 = oa2 - oa;
+                    }
                 }
             }
-            const uint32_t rec = lo;
-            const unsigned long long ea = s_ea[rec];
-            const uint32_t rr = tile * VTD_TILE + rec;
-            const unsigned long long k = k0 + j;
-            const uint32_t i = j - s_k[rec] + 1;                       // ALT index (1-based) for n >= 2
-            const uint32_t rab = s_ab[rec], rn = s_n[rec];
-            const uint32_t ro0 = __ldg(B.allele_off + rab), ro1 = __ldg(B.allele_off + rab + 1);
-            const uint32_t len0 = ro1 - ro0;
-            const unsigned long long slot = 2 * (ea >> 31) - (ea & 0x7fffffffull) + 2ull * (i - 1);
-            src_rec[k] = rr;
-            if (rn < 2)
+            if (materialise)
             {
-                alt_idx[k] = 0;
-                if (materialise)
+#pragma unroll
+                for (uint32_t q = 0; q < 4; ++q)
                 {
-                    const unsigned long long ob = s_ob[rec];
-                    F.pos1[k] = __ldg(B.pos1 + rr);
-                    F.rid[k] = __ldg(B.rid + rr);
-                    F.allele_beg[k] = (uint32_t)slot;
-                    F.allele_off[slot] = (uint32_t)ob;
-                    for (uint32_t q = 0; q < len0; ++q) F.bytes[ob + q] = B.bytes[ro0 + q];
+                    if (q < l0) F.bytes[dst0 + q] = B.bytes[src0 + q];
+                    if (q < l1) F.bytes[dst1 + q] = B.bytes[src1 + q];
                 }
-            }
-            else
-            {
-                alt_idx[k] = (uint16_t)i;
-                if (materialise)
+                const int lane_ = tid & 31;
+                unsigned m0 = __ballot_sync(0xffffffffu, l0 > 4), m1 = __ballot_sync(0xffffffffu, l1 > 4);
+                while (m0)
                 {
-                    const uint32_t oa = __ldg(B.allele_off + rab + i), oa2 = __ldg(B.allele_off + rab + i + 1);
-                    const unsigned long long ob = s_ob[rec] + (unsigned long long)(i - 1) * len0 + (oa - ro1);
-                    F.pos1[k] = __ldg(B.pos1 + rr);
-                    F.rid[k] = __ldg(B.rid + rr);
-                    F.allele_beg[k] = (uint32_t)slot;
-                    F.allele_off[slot] = (uint32_t)ob;
-                    F.allele_off[slot + 1] = (uint32_t)(ob + len0);
-                    for (uint32_t q = 0; q < len0; ++q) F.bytes[ob + q] = B.bytes[ro0 + q];
-                    const uint32_t la = oa2 - oa;
-                    for (uint32_t q = 0; q < la; ++q) F.bytes[ob + len0 + q] = B.bytes[oa + q];
+                    const int l = __ffs(m0) - 1;
+                    m0 &= m0 - 1;
+                    const uint32_t sl = __shfl_sync(0xffffffffu, src0, l), ll = __shfl_sync(0xffffffffu, l0, l);
+                    const unsigned long long dl = __shfl_sync(0xffffffffu, dst0, l);
+                    for (uint32_t q = 4 + lane_; q < ll; q += 32) F.bytes[dl + q] = B.bytes[sl + q];
+                }
+                while (m1)
+                {
+                    const int l = __ffs(m1) - 1;
+                    m1 &= m1 - 1;
+                    const uint32_t sl = __shfl_sync(0xffffffffu, src1, l), ll = __shfl_sync(0xffffffffu, l1, l);
+                    const unsigned long long dl = __shfl_sync(0xffffffffu, dst1, l);
+                    for (uint32_t q = 4 + lane_; q < ll; q += 32) F.bytes[dl + q] = B.bytes[sl + q];
                 }
             }
         }
