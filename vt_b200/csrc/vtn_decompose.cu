@@ -8,6 +8,8 @@
 
 #define VTD_TILE 256
 #define VTD_XCAP 2048 // outputs per tile covered by the output->source expansion table
+#define VTD_INCAP 4096  // allele bytes of a tile's input records staged in shared memory (fallback: global loads)
+#define VTD_OUTCAP 8192 // allele bytes of a tile's output records staged in shared memory (fallback: global stores)
 
 namespace
 {
@@ -176,6 +178,28 @@ __global__ void __launch_bounds__(1024) vtd_scan_kernel(unsigned long long* agg_
     }
 }
 
+// one allele: input bytes [src, src+len) -> output bytes [dst, dst+len), through the shared-memory windows when staged
+__device__ __forceinline__ void copy_bytes(bool in_staged, bool out_staged, const uint8_t* s_in, uint8_t* s_out, const uint8_t* g_in, uint8_t* g_out,
+                                           uint32_t in_lo, unsigned long long out_base, uint32_t out_shift, uint32_t src, unsigned long long dst,
+                                           uint32_t len)
+{
+    if (in_staged && out_staged)
+    {
+        const uint8_t* a = s_in + (src - in_lo);
+        uint8_t* b = s_out + out_shift + (uint32_t)(dst - out_base);
+        for (uint32_t q = 0; q < len; ++q) b[q] = a[q];
+    }
+    else
+    {
+        for (uint32_t q = 0; q < len; ++q)
+        {
+            const uint8_t ch = in_staged ? s_in[src - in_lo + q] : g_in[src + q];
+            if (out_staged) s_out[out_shift + (uint32_t)(dst - out_base) + q] = ch;
+            else g_out[dst + q] = ch;
+        }
+    }
+}
+
 // scan word A: (out_recs << 31) | singles ; scan word B: out bytes
 __global__ void __launch_bounds__(VTD_TILE) vtd_emit_kernel(VtnDevBatchView B, uint32_t* src_rec, uint16_t* alt_idx, FusedOut F,
                                                              int materialise, const unsigned long long* tile_state,
@@ -187,6 +211,8 @@ __global__ void __launch_bounds__(VTD_TILE) vtd_emit_kernel(VtnDevBatchView B, u
     __shared__ unsigned long long s_ea[VTD_TILE], s_ob[VTD_TILE];
     __shared__ uint32_t s_ab[VTD_TILE], s_n[VTD_TILE], s_k[VTD_TILE];
     __shared__ uint16_t s_src[VTD_XCAP];
+    __shared__ __align__(16) uint8_t s_in[VTD_INCAP + 16], s_out[VTD_OUTCAP + 16];
+    __shared__ uint32_t s_io[2]; // first / one-past-last allele byte of the tile's input records
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned long long* st_a = tile_state;          // exclusive prefixes written by vtd_scan_kernel
     const unsigned long long* st_b = tile_state + n_tiles;
@@ -224,6 +250,8 @@ __global__ void __launch_bounds__(VTD_TILE) vtd_emit_kernel(VtnDevBatchView B, u
             if (lane >= o) { ia += ta; ib += tb; }
         }
         if (lane == 31) { s_wa[warp] = ia; s_wb[warp] = ib; }
+        if (tid == 0) s_io[0] = o0;
+        if (live && (r + 1 == B.n_rec || tid == VTD_TILE - 1)) s_io[1] = oe;
         __syncthreads();
         unsigned long long wa = 0, wb = 0, ta = 0, tb = 0;
 #pragma unroll
@@ -250,6 +278,16 @@ __global__ void __launch_bounds__(VTD_TILE) vtd_emit_kernel(VtnDevBatchView B, u
         // ---- emission, OUTPUT-centric: thread j writes output record j of the tile, so that every store stream
         // (src_rec, alt_idx, pos1, rid, allele_beg, allele_off pairs, bytes) is coalesced; the source record is found
         // by binary search on the tile-local output prefix (every record emits at least one output).
+        // the tile's input allele bytes -> shared memory (coalesced 128-bit loads; the byte-wise copies below then never wait on
+        // global memory), and its output bytes are assembled in shared memory and leave with 128-bit stores
+        const uint32_t in_lo = s_io[0] & ~15u, in_n = s_io[1] - in_lo;
+        const bool in_staged = materialise && in_n <= VTD_INCAP;
+        const unsigned long long out_base = s_base[1];
+        const uint32_t out_shift = (uint32_t)out_base & 15u, out_n = (uint32_t)tb;
+        const bool out_staged = materialise && tb + out_shift <= VTD_OUTCAP;
+        if (in_staged)
+            for (uint32_t i = tid * 16; i < in_n; i += VTD_TILE * 16)
+                *reinterpret_cast<uint4*>(&s_in[i]) = __ldg(reinterpret_cast<const uint4*>(B.bytes + in_lo + i));
         const unsigned long long ea_t = s_base[0] + wa + (ia - va); // this thread's record: (outputs << 31 | singles) before it
         s_ea[tid] = live ? ea_t : ~0ull;
         s_ob[tid] = s_base[1] + wb + (ib - vb);
@@ -268,96 +306,73 @@ __global__ void __launch_bounds__(VTD_TILE) vtd_emit_kernel(VtnDevBatchView B, u
         }
         __syncthreads();
         const uint32_t n_in = min((uint32_t)VTD_TILE, B.n_rec - tile * VTD_TILE);
-        for (uint32_t jb = 0; jb < tot; jb += VTD_TILE)
+        for (uint32_t j = tid; j < tot; j += VTD_TILE)
         {
-            const uint32_t j = jb + tid;
-            const bool act = j < tot;
-            // byte segments of this output: REF (src0 -> dst0, l0) and ALT (src1 -> dst1, l1); the first four bytes of each are
-            // copied inline, longer ones by the whole warp afterwards, so a long allele does not make 31 lanes wait
-            uint32_t src0 = 0, l0 = 0, src1 = 0, l1 = 0;
-            unsigned long long dst0 = 0, dst1 = 0;
-            if (act)
+            uint32_t lo;
+            if (expanded)
+                lo = s_src[j];
+            else
             {
-                uint32_t lo;
-                if (expanded)
-                    lo = s_src[j];
-                else
+                uint32_t hi = n_in - 1; // last record whose first output <= j
+                lo = 0;
+                while (lo < hi)
                 {
-                    uint32_t hi = n_in - 1; // last record whose first output <= j
-                    lo = 0;
-                    while (lo < hi)
-                    {
-                        const uint32_t mid = (lo + hi + 1) >> 1;
-                        if (s_k[mid] <= j) lo = mid;
-                        else hi = mid - 1;
-                    }
-                }
-                const uint32_t rec = lo;
-                const unsigned long long ea = s_ea[rec];
-                const uint32_t rr = tile * VTD_TILE + rec;
-                const unsigned long long k = k0 + j;
-                const uint32_t i = j - s_k[rec] + 1;                       // ALT index (1-based) for n >= 2
-                const uint32_t rab = s_ab[rec], rn = s_n[rec];
-                const uint32_t ro0 = __ldg(B.allele_off + rab), ro1 = __ldg(B.allele_off + rab + 1);
-                const uint32_t len0 = ro1 - ro0;
-                const unsigned long long slot = 2 * (ea >> 31) - (ea & 0x7fffffffull) + 2ull * (i - 1);
-                src_rec[k] = rr;
-                if (rn < 2)
-                {
-                    alt_idx[k] = 0;
-                    if (materialise)
-                    {
-                        const unsigned long long ob = s_ob[rec];
-                        F.pos1[k] = __ldg(B.pos1 + rr);
-                        F.rid[k] = __ldg(B.rid + rr);
-                        F.allele_beg[k] = (uint32_t)slot;
-                        F.allele_off[slot] = (uint32_t)ob;
-                        src0 = ro0, dst0 = ob, l0 = len0;
-                    }
-                }
-                else
-                {
-                    alt_idx[k] = (uint16_t)i;
-                    if (materialise)
-                    {
-                        const uint32_t oa = __ldg(B.allele_off + rab + i), oa2 = __ldg(B.allele_off + rab + i + 1);
-                        const unsigned long long ob = s_ob[rec] + (unsigned long long)(i - 1) * len0 + (oa - ro1);
-                        F.pos1[k] = __ldg(B.pos1 + rr);
-                        F.rid[k] = __ldg(B.rid + rr);
-                        F.allele_beg[k] = (uint32_t)slot;
-                        F.allele_off[slot] = (uint32_t)ob;
-                        F.allele_off[slot + 1] = (uint32_t)(ob + len0);
-                        src0 = ro0, dst0 = ob, l0 = len0;
-                        src1 = oa, dst1 = ob + len0, l1 = oa2 - oa;
-                    }
+                    const uint32_t mid = (lo + hi + 1) >> 1;
+                    if (s_k[mid] <= j) lo = mid;
+                    else hi = mid - 1;
                 }
             }
-            if (materialise)
+            const uint32_t rec = lo;
+            const unsigned long long ea = s_ea[rec];
+            const uint32_t rr = tile * VTD_TILE + rec;
+            const unsigned long long k = k0 + j;
+            const uint32_t i = j - s_k[rec] + 1;                       // ALT index (1-based) for n >= 2
+            const uint32_t rab = s_ab[rec], rn = s_n[rec];
+            const uint32_t ro0 = __ldg(B.allele_off + rab), ro1 = __ldg(B.allele_off + rab + 1);
+            const uint32_t len0 = ro1 - ro0;
+            const unsigned long long slot = 2 * (ea >> 31) - (ea & 0x7fffffffull) + 2ull * (i - 1);
+            src_rec[k] = rr;
+            if (rn < 2)
             {
-#pragma unroll
-                for (uint32_t q = 0; q < 4; ++q)
+                alt_idx[k] = 0;
+                if (materialise)
                 {
-                    if (q < l0) F.bytes[dst0 + q] = B.bytes[src0 + q];
-                    if (q < l1) F.bytes[dst1 + q] = B.bytes[src1 + q];
+                    const unsigned long long ob = s_ob[rec];
+                    F.pos1[k] = __ldg(B.pos1 + rr);
+                    F.rid[k] = __ldg(B.rid + rr);
+                    F.allele_beg[k] = (uint32_t)slot;
+                    F.allele_off[slot] = (uint32_t)ob;
+                    copy_bytes(in_staged, out_staged, s_in, s_out, B.bytes, F.bytes, in_lo, out_base, out_shift, ro0, ob, len0);
                 }
-                const int lane_ = tid & 31;
-                unsigned m0 = __ballot_sync(0xffffffffu, l0 > 4), m1 = __ballot_sync(0xffffffffu, l1 > 4);
-                while (m0)
+            }
+            else
+            {
+                alt_idx[k] = (uint16_t)i;
+                if (materialise)
                 {
-                    const int l = __ffs(m0) - 1;
-                    m0 &= m0 - 1;
-                    const uint32_t sl = __shfl_sync(0xffffffffu, src0, l), ll = __shfl_sync(0xffffffffu, l0, l);
-                    const unsigned long long dl = __shfl_sync(0xffffffffu, dst0, l);
-                    for (uint32_t q = 4 + lane_; q < ll; q += 32) F.bytes[dl + q] = B.bytes[sl + q];
+                    const uint32_t oa = __ldg(B.allele_off + rab + i), oa2 = __ldg(B.allele_off + rab + i + 1);
+                    const unsigned long long ob = s_ob[rec] + (unsigned long long)(i - 1) * len0 + (oa - ro1);
+                    F.pos1[k] = __ldg(B.pos1 + rr);
+                    F.rid[k] = __ldg(B.rid + rr);
+                    F.allele_beg[k] = (uint32_t)slot;
+                    F.allele_off[slot] = (uint32_t)ob;
+                    F.allele_off[slot + 1] = (uint32_t)(ob + len0);
+                    copy_bytes(in_staged, out_staged, s_in, s_out, B.bytes, F.bytes, in_lo, out_base, out_shift, ro0, ob, len0);
+                    copy_bytes(in_staged, out_staged, s_in, s_out, B.bytes, F.bytes, in_lo, out_base, out_shift, oa, ob + len0, oa2 - oa);
                 }
-                while (m1)
-                {
-                    const int l = __ffs(m1) - 1;
-                    m1 &= m1 - 1;
-                    const uint32_t sl = __shfl_sync(0xffffffffu, src1, l), ll = __shfl_sync(0xffffffffu, l1, l);
-                    const unsigned long long dl = __shfl_sync(0xffffffffu, dst1, l);
-                    for (uint32_t q = 4 + lane_; q < ll; q += 32) F.bytes[dl + q] = B.bytes[sl + q];
-                }
+            }
+        }
+        if (out_staged)
+        {
+            __syncthreads();
+            const uint32_t total = out_shift + out_n;
+            uint8_t* gdst = F.bytes + (out_base - out_shift); // 16-byte aligned
+            for (uint32_t c = tid * 16; c < total; c += VTD_TILE * 16)
+            {
+                if (c >= out_shift && c + 16 <= total)
+                    *reinterpret_cast<uint4*>(gdst + c) = *reinterpret_cast<const uint4*>(&s_out[c]);
+                else
+                    for (uint32_t q = (c > out_shift ? c : out_shift); q < c + 16 && q < total; ++q) gdst[q] = s_out[q];
             }
         }
     }
