@@ -1,10 +1,13 @@
-// vtn_cli.cpp -- host shim that keeps vt's command surface for the path:  `vtn normalize`, `vtn decompose`.
+// vtn_cli.cpp -- host shim that keeps vt's command surface for the path:  `vtn normalize`, `vtn decompose`, `vtn uniq`.
 //
 // Mirrors the reference tools' flags, stderr text and VCF output (normalize.cpp:84-171, :332-382; decompose.cpp:
 // 80-150, :960-995) while the per-record arithmetic runs in libvtn's CUDA kernels through the C ABI (include/vtn.h):
-//   normalize : records are parsed from VCF text into struct-of-arrays batches -> vtn_normalize -> changed records get
-//               the new POS/alleles and INFO/OLD_VARIANT (bcf_variant2string, hts_utils.cpp:1013-1026) -> a windowed
-//               ordered writer with BCFOrderedWriter's insertion/flush rules (bcf_ordered_writer.cpp:141-300).
+//   normalize : record lines -> struct-of-arrays batches on the device (vtn_vcf_tokenize) -> vtn_normalize -> changed records
+//               get the new POS/alleles and INFO/OLD_VARIANT (bcf_variant2string, hts_utils.cpp:1013-1026) -> written in the
+//               order of BCFOrderedWriter's insertion/flush rules (bcf_ordered_writer.cpp:141-300), computed on the device
+//               (vtn_writer_order).
+//   uniq      : vtn_uniq decides which duplicate survives and the reader's output order (uniq.cpp:110-156); the host merges
+//               the OLD_VARIANT values of a group.
 //   decompose : vtn_decompose gives the (source record, ALT index) fan-out plan and the counters; the INFO/FORMAT
 //               sub-setting of each emitted record is host-side text work (decompose.cpp:210-392 plain, :393-957 -s).
 // VCF text only (plain or gzip/bgzip in, plain out); BCF and the -f filter / -i intervals are not handled here
@@ -308,8 +311,11 @@ void put_tail(std::string& out, const Header& h, const std::vector<Tok>& col, co
     }
 }
 
-// BCFOrderedWriter (bcf_ordered_writer.cpp:141-300): front of the list = largest POS.
-struct OrderedWriter
+// BCFOrderedWriter (bcf_ordered_writer.cpp:141-300) with the ORDER computed on the device (vtn_writer_order): records are
+// collected per batch, the device returns the order in which BCFOrderedWriter would have written them and how many are still inside its buffer; those are
+// carried into the next batch (replaying them rebuilds the buffer, include/vtn.h).  stderr text of a record (its own
+// messages, then the writer's warning for it) is printed in arrival order, like the sequential reference.
+struct DeviceWriter
 {
     struct Rec
     {
@@ -318,74 +324,6 @@ struct OrderedWriter
         std::string chrom, line;
         std::string msg; // stderr text of this record (printed when the record is handed to the writer)
     };
-    FILE* out = stdout;
-    int window = 0;
-    std::list<Rec> buffer;
-    void emit(const Rec& r)
-    {
-        fwrite(r.line.data(), 1, r.line.size(), out);
-        fputc('\n', out);
-    }
-    void flush(bool force)
-    {
-        if (force)
-        {
-            while (!buffer.empty())
-            {
-                emit(buffer.back());
-                buffer.pop_back();
-            }
-        }
-        else if (buffer.size() > 1)
-        {
-            int32_t cutoff = std::max(buffer.front().pos1 - window, 1);
-            while (buffer.size() > 1 && buffer.back().pos1 <= cutoff)
-            {
-                emit(buffer.back());
-                buffer.pop_back();
-            }
-        }
-    }
-    void write(Rec&& v)
-    {
-        if (!window)
-        {
-            emit(v);
-            return;
-        }
-        if (buffer.empty())
-        {
-            buffer.push_front(std::move(v));
-            return;
-        }
-        if (v.rid != buffer.back().rid)
-        {
-            flush(true);
-            buffer.push_front(std::move(v));
-            return;
-        }
-        auto i = buffer.begin();
-        for (; i != buffer.end(); ++i)
-            if (v.pos1 >= i->pos1) break; // >= keeps records of equal POS in arrival order
-        if (i == buffer.end())
-        {
-            int32_t cutoff = std::max(buffer.front().pos1 - window, 1);
-            if (v.pos1 < cutoff)
-                fprintf(stderr, "[bcf_ordered_writer.cpp:170 write] Might not be sorted for window size %d at current record %s:%d < %d (%d [last record] - %d), please increase window size to at least %d.\n",
-                        window, v.chrom.c_str(), v.pos1, cutoff, buffer.front().pos1, window, buffer.front().pos1 - v.pos1 + 1);
-        }
-        buffer.insert(i, std::move(v));
-        flush(false);
-    }
-};
-
-// The same writer with the ORDER computed on the device (vtn_writer_order): records are collected per batch, the device
-// returns the order in which BCFOrderedWriter would have written them and how many are still inside its buffer; those are
-// carried into the next batch (replaying them rebuilds the buffer, include/vtn.h).  stderr text of a record (its own
-// messages, then the writer's warning for it) is printed in arrival order, like the sequential reference.
-struct DeviceWriter
-{
-    typedef OrderedWriter::Rec Rec;
     FILE* out = stdout;
     int window = 0;
     vtn_ctx* ctx = nullptr;
@@ -741,7 +679,7 @@ int cmd_normalize(int argc, char** argv)
                 }
                 msg += "[normalize.cpp:214 normalize] Normalization skipped due to inconsistent reference sequences\n";
             }
-            OrderedWriter::Rec rec;
+            DeviceWriter::Rec rec;
             rec.msg = std::move(msg);
             rec.rid = in.rid[r];
             rec.chrom = chrom;
