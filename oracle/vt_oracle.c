@@ -769,3 +769,106 @@ int64_t vto_vcf_tokenize(const char* text, uint64_t n_text, uint64_t cap_rec, ui
     line_off[r] = n_text;
     return (int64_t)r;
 }
+
+/* ---------------------------------------------------------------------------------------------------------
+ * vt decompose_blocksub, record loop of Igor::decompose_blocksub(), decompose_blocksub.cpp:185-421, without
+ * the alignment mode (-a, :198-303, needs needle.cpp: not restated).  A biallelic record whose REF and ALT have the same
+ * length > 1 (:304) is replaced by one SNP per differing position (:341-375) or, with keep_mnv (-m), by one record per run
+ * of differences that are at most max_mnv_dist apart (:322-337, :382-401, :405-410; the kstring buffers of the reference
+ * are restated as such, with the truncation at the last difference).  Everything else passes through (:413-418).
+ * Output k: src_rec[k], off[k], len[k]: new POS = pos1 + off, alleles REF[off, off+len) / ALT[off, off+len);
+ * len 0 = the record itself, unchanged.
+ * counters: no_variants, no_biallelic_blocksub, no_additional_snps, new_no_variants (:157-160, :377-378, :412, :417, :420;
+ * the last two count DIFFERENCES also in -m mode, like the reference).
+ * --------------------------------------------------------------------------------------------------------- */
+int32_t vto_blocksub_plan(const vto_batch* in, int32_t keep_mnv, int32_t max_mnv_dist, uint32_t* src_rec, uint32_t* off, uint32_t* len,
+                          uint64_t* n_out, uint32_t counters[4])
+{
+    uint64_t k = 0;
+    counters[0] = counters[1] = counters[2] = counters[3] = 0;
+    for (uint32_t r = 0; r < in->n_rec; ++r)
+    {
+        const uint32_t ab = in->allele_beg[r], n_allele = in->allele_beg[r + 1] - ab;
+        const uint32_t o0 = in->allele_off[ab], o1 = in->allele_off[ab + 1];
+        const size_t ref_len = o1 - o0;
+        const uint8_t* ref = in->bytes + o0;
+        if (n_allele == 2 && ref_len != 1 && ref_len == (size_t)(in->allele_off[ab + 2] - o1))
+        {
+            const uint8_t* alt = in->bytes + o1;
+            int prev_snv_pos = -1, mnv_start_pos = -1;
+            char* ref_mnv = (char*)malloc(ref_len + 1);
+            char* alt_mnv = (char*)malloc(ref_len + 1);
+            size_t l_mnv = 0; /* ref_mnv.l == alt_mnv.l throughout */
+            if (!ref_mnv || !alt_mnv) return -1;
+            for (size_t i = 0; i < ref_len; ++i)
+            {
+                if (ref[i] != alt[i])
+                {
+                    if (keep_mnv)
+                    {
+                        if (prev_snv_pos == -1 || i - (size_t)prev_snv_pos <= (size_t)max_mnv_dist)
+                        {
+                            prev_snv_pos = (int)i;
+                            if (mnv_start_pos == -1) mnv_start_pos = (int)i;
+                            ref_mnv[l_mnv] = (char)ref[i];
+                            alt_mnv[l_mnv] = (char)alt[i];
+                            ++l_mnv;
+                        }
+                    }
+                    else
+                    {
+                        src_rec[k] = r;
+                        off[k] = (uint32_t)i;
+                        len[k] = 1;
+                        ++k;
+                    }
+                    counters[3]++; /* ++new_no_variants */
+                    counters[2]++; /* ++no_additional_snps */
+                }
+                else if (keep_mnv)
+                {
+                    if (prev_snv_pos != -1 && i - (size_t)prev_snv_pos < (size_t)max_mnv_dist)
+                    {
+                        ref_mnv[l_mnv] = (char)ref[i];
+                        alt_mnv[l_mnv] = (char)alt[i];
+                        ++l_mnv;
+                    }
+                    else if (prev_snv_pos != -1)
+                    { /* print_decomposed_var(v, pos1 + mnv_start_pos, ref_mnv.s, alt_mnv.s) after the truncation */
+                        src_rec[k] = r;
+                        off[k] = (uint32_t)mnv_start_pos;
+                        len[k] = (uint32_t)(prev_snv_pos - mnv_start_pos + 1);
+                        /* the buffers hold exactly REF/ALT[mnv_start_pos ...]: check the restated kstrings against the substring form */
+                        if (memcmp(ref_mnv, ref + mnv_start_pos, len[k]) || memcmp(alt_mnv, alt + mnv_start_pos, len[k])) return -2;
+                        ++k;
+                        prev_snv_pos = -1;
+                        mnv_start_pos = -1;
+                        l_mnv = 0;
+                    }
+                }
+            }
+            if (keep_mnv && prev_snv_pos != -1)
+            {
+                src_rec[k] = r;
+                off[k] = (uint32_t)mnv_start_pos;
+                len[k] = (uint32_t)(prev_snv_pos - mnv_start_pos + 1);
+                if (memcmp(ref_mnv, ref + mnv_start_pos, len[k]) || memcmp(alt_mnv, alt + mnv_start_pos, len[k])) return -2;
+                ++k;
+            }
+            free(ref_mnv);
+            free(alt_mnv);
+            counters[1]++; /* ++no_biallelic_blocksub */
+        }
+        else
+        {
+            src_rec[k] = r;
+            off[k] = 0;
+            len[k] = 0;
+            ++k;
+            counters[3]++; /* ++new_no_variants */
+        }
+        counters[0]++; /* ++no_variants */
+    }
+    *n_out = k;
+    return 0;
+}

@@ -92,6 +92,12 @@ int64_t vto_vcf_tokenize(const char* text, uint64_t n_text, uint64_t cap_rec, ui
                          uint64_t* line_off, uint32_t* chrom_len, int32_t* pos1, uint32_t* tail_off, uint8_t* status,
                          uint32_t* allele_beg, uint32_t* allele_off, uint8_t* bytes);
 
+/* vt decompose_blocksub without -a (decompose_blocksub.cpp:185-421): output k = (src_rec, off, len), len 0 = the record itself;
+ * counters no_variants, no_biallelic_blocksub, no_additional_snps, new_no_variants.  Pinned to the reference's own fixtures
+ * (test/decompose_blocksub 01, 03 and the mnv directory) and to oracle/_ref/vt_ref (tests/test_blocksub_oracle.py). */
+int32_t vto_blocksub_plan(const vto_batch* in, int32_t keep_mnv, int32_t max_mnv_dist, uint32_t* src_rec, uint32_t* off, uint32_t* len,
+                          uint64_t* n_out, uint32_t counters[4]);
+
 #ifdef __cplusplus
 }
 #endif

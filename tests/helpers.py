@@ -58,6 +58,8 @@ class Oracle:
         self.lib.vto_normalize_batch.argtypes = [C.POINTER(VtoRef), C.POINTER(VtoBatch), C.POINTER(VtoNormOut)]
         self.lib.vto_decompose_plan.restype = C.c_int32
         self.lib.vto_decompose_plan.argtypes = [C.POINTER(VtoBatch), u32p, u16p, u64p, u32p]
+        self.lib.vto_blocksub_plan.restype = C.c_int32
+        self.lib.vto_blocksub_plan.argtypes = [C.POINTER(VtoBatch), C.c_int32, C.c_int32, u32p, u32p, u32p, u64p, u32p]
         self.lib.vto_vcf_tokenize.restype = C.c_int64
         self.lib.vto_vcf_tokenize.argtypes = [C.c_char_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, u64p, u32p, i32p, u32p, u8p, u32p, u32p, u8p]
         self.lib.vto_writer_order.restype = C.c_int32
@@ -118,6 +120,19 @@ class Oracle:
         k = int(n_out.value)
         return src[:k], alt[:k], list(cnt)
 
+
+    def blocksub_plan(self, b, keep_mnv=False, max_mnv_dist=2):
+        """-> (src_rec, off, len, [no_variants, no_biallelic_blocksub, no_additional_snps, new_no_variants])"""
+        bound = int(b.n_bytes) + int(b.n_rec) + 1
+        src, off, ln = np.zeros(bound, np.uint32), np.zeros(bound, np.uint32), np.zeros(bound, np.uint32)
+        n_out = C.c_uint64(0)
+        cnt = (C.c_uint32 * 4)()
+        vb = self._batch(b)
+        rc = self.lib.vto_blocksub_plan(C.byref(vb), 1 if keep_mnv else 0, max_mnv_dist, src.ctypes.data_as(u32p), off.ctypes.data_as(u32p),
+                                        ln.ctypes.data_as(u32p), C.byref(n_out), cnt)
+        assert rc == 0, rc
+        k = int(n_out.value)
+        return src[:k], off[:k], ln[:k], list(cnt)
 
     def vcf_tokenize(self, text):
         n = len(text)
