@@ -16,6 +16,7 @@
  *   vtn_writer_order     BCFOrderedWriter::write / flush, bcf_ordered_writer.cpp:141-210, :252-300
  *   vtn_vcf_tokenize     vcf_parse1 + bcf_unpack(BCF_UN_STR) for CHROM/POS/REF/ALT (lib/htslib/vcf.c) behind
  *                        BCFOrderedReader::read, bcf_ordered_reader.cpp:238-298
+ *   vtn_blocksub*        the record loop of Igor::decompose_blocksub(), decompose_blocksub.cpp:185-421 (without -a)
  *   vtn_hmm_*            AHMM/LFHMM/RFHMM::align (ahmm.cpp:468-587, lfhmm.cpp:489-654, rfhmm.cpp:516+)
  *
  * The library never exits or prints: every call returns 0 on success or a negative vtn_err code, and
@@ -230,6 +231,24 @@ int vtn_vcf_dtext_create(vtn_ctx* ctx, const char* text, uint64_t n_text, uint32
 int vtn_vcf_dtext_destroy(vtn_ctx* ctx, vtn_vcf_dtext* h);
 int vtn_vcf_tokenize_resident(vtn_ctx* ctx, vtn_vcf_dtext* h);
 int vtn_vcf_dtext_fetch(vtn_ctx* ctx, vtn_vcf_dtext* h, vtn_vcf_fields* out);
+
+/* ---- decompose_blocksub: block substitutions -> SNPs (or MNVs) ----
+ * Replaces the record loop of Igor::decompose_blocksub() (decompose_blocksub.cpp:185-421) without its alignment mode (-a).
+ * Output k comes from input record src_rec[k]: len[k] == 0 -> the record itself, unchanged; otherwise a new record at
+ * POS = pos1 + off[k] with alleles REF[off, off+len) / ALT[off, off+len) (one base per differing position; with keep_mnv
+ * (-m) one run of differences at most max_mnv_dist (-d, default 2) apart).  Outputs are in input order; the reference then
+ * writes them through a 1000-bp ordered writer (decompose_blocksub.cpp:133; vtn_writer_order).  A block substitution without
+ * any difference emits nothing, like the reference.  Capacity: vtn_blocksub_out_bound(in). */
+typedef struct vtn_blocksub_counters
+{
+    uint32_t no_variants, no_biallelic_blocksub, no_additional_snps, new_no_variants; /* decompose_blocksub.cpp:157-160 */
+} vtn_blocksub_counters;
+uint64_t vtn_blocksub_out_bound(const vtn_batch* in);
+int vtn_blocksub(vtn_ctx* ctx, const vtn_batch* in, int keep_mnv, int max_mnv_dist, uint32_t* src_rec, uint32_t* off,
+                 uint32_t* len, uint64_t cap_out, uint64_t* n_out, vtn_blocksub_counters* counters);
+int vtn_blocksub_resident(vtn_ctx* ctx, vtn_dbatch* db, int keep_mnv, int max_mnv_dist); /* async; bench / pipelines */
+int vtn_dbatch_fetch_blocksub(vtn_ctx* ctx, vtn_dbatch* db, uint32_t* src_rec, uint32_t* off, uint32_t* len, uint64_t cap_out,
+                              uint64_t* n_out, vtn_blocksub_counters* counters);
 
 /* ---- HMM family: AHMM / LFHMM / RFHMM Viterbi realignment (annotate_indels' FlankDetector) ----
  * Replaces <model>::set_model + <model>::align + the result members/getters:

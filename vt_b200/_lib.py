@@ -58,6 +58,10 @@ class VtnVcfFields(C.Structure):
                 ("allele_off", C.POINTER(C.c_uint32)), ("bytes", C.POINTER(C.c_uint8))]
 
 
+class VtnBlocksubCounters(C.Structure):
+    _fields_ = [("no_variants", C.c_uint32), ("no_biallelic_blocksub", C.c_uint32), ("no_additional_snps", C.c_uint32), ("new_no_variants", C.c_uint32)]
+
+
 class VtnUniqCounters(C.Structure):
     _fields_ = [("no_total_variants", C.c_uint32), ("no_unique_variants", C.c_uint32)]
 
@@ -125,6 +129,10 @@ SIGNATURES = {
     "vtn_vcf_dtext_destroy": (C.c_int, [C.c_void_p, C.c_void_p]),
     "vtn_vcf_tokenize_resident": (C.c_int, [C.c_void_p, C.c_void_p]),
     "vtn_vcf_dtext_fetch": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VtnVcfFields)]),
+    "vtn_blocksub_out_bound": (C.c_uint64, [C.POINTER(VtnBatch)]),
+    "vtn_blocksub": (C.c_int, [C.c_void_p, C.POINTER(VtnBatch), C.c_int, C.c_int, c_u32p, c_u32p, c_u32p, C.c_uint64, c_u64p, C.POINTER(VtnBlocksubCounters)]),
+    "vtn_blocksub_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "vtn_dbatch_fetch_blocksub": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_u32p, c_u32p, C.c_uint64, c_u64p, C.POINTER(VtnBlocksubCounters)]),
     "vtn_uniq_resident": (C.c_int, [C.c_void_p, C.c_void_p]),
     "vtn_dbatch_fetch_uniq": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_u8p, C.POINTER(VtnUniqCounters), C.POINTER(C.c_int64)]),
     "vtn_dbatch_fetch_decompose": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_u16p, c_u64p, C.POINTER(VtnDecompCounters)]),

@@ -285,6 +285,21 @@ class Context:
     def vcf_free(self, h):
         self.lib.vtn_vcf_dtext_destroy(self.h, h)
 
+    def blocksub(self, batch, keep_mnv=False, max_mnv_dist=2):
+        """decompose_blocksub plan (include/vtn.h vtn_blocksub) -> (src_rec, off, len, [4 counters])"""
+        cb = batch.as_c()
+        bound = int(self.lib.vtn_blocksub_out_bound(C.byref(cb)))
+        src, off, ln = np.zeros(bound, np.uint32), np.zeros(bound, np.uint32), np.zeros(bound, np.uint32)
+        n_out = C.c_uint64(0)
+        bc = L.VtnBlocksubCounters()
+        self._chk(self.lib.vtn_blocksub(self.h, C.byref(cb), 1 if keep_mnv else 0, int(max_mnv_dist), _p(src, L.c_u32p), _p(off, L.c_u32p),
+                                        _p(ln, L.c_u32p), bound, C.byref(n_out), C.byref(bc)), "vtn_blocksub")
+        k = int(n_out.value)
+        return src[:k], off[:k], ln[:k], [bc.no_variants, bc.no_biallelic_blocksub, bc.no_additional_snps, bc.new_no_variants]
+
+    def blocksub_resident(self, db, keep_mnv=False, max_mnv_dist=2):
+        self._chk(self.lib.vtn_blocksub_resident(self.h, db, 1 if keep_mnv else 0, int(max_mnv_dist)), "vtn_blocksub_resident")
+
     def uniq_resident(self, db):
         self._chk(self.lib.vtn_uniq_resident(self.h, db), "vtn_uniq_resident")
 

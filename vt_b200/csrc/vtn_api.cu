@@ -185,6 +185,7 @@ int vtn_dbatch_destroy(vtn_ctx* ctx, vtn_dbatch* d)
     if (d->fused) vtn_dbatch_destroy(ctx, d->fused);
     vtn_uniq_dbatch_release(d);
     vtn_order_dbatch_release(d);
+    vtn_blocksub_dbatch_release(d);
     if (d->owns_inputs)
     {
         cudaFree(d->pos1); cudaFree(d->rid); cudaFree(d->allele_beg); cudaFree(d->allele_off); cudaFree(d->bytes);
@@ -516,4 +517,21 @@ int vtn_uniq(vtn_ctx* ctx, const vtn_batch* in, uint32_t* order, uint8_t* first,
     rc = vtn_uniq_resident(ctx, ctx->scratch);
     if (rc) return rc;
     return vtn_dbatch_fetch_uniq(ctx, ctx->scratch, order, first, counters, not_in_order);
+}
+
+// Host-buffer decompose_blocksub plan: H2D of the batch, three kernels, D2H of the plan and the counters.
+int vtn_blocksub(vtn_ctx* ctx, const vtn_batch* in, int keep_mnv, int max_mnv_dist, uint32_t* src_rec, uint32_t* off, uint32_t* len,
+                 uint64_t cap_out, uint64_t* n_out, vtn_blocksub_counters* counters)
+{
+    if (!ctx || !n_out) return VTN_E_ARG;
+    int rc = check_batch(ctx, in);
+    if (rc) return rc;
+    VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    rc = ensure_scratch(ctx, in->n_rec, in->n_allele, in->n_bytes);
+    if (rc) return rc;
+    rc = upload_inputs(ctx, in, ctx->scratch, ctx->stream);
+    if (rc) return rc;
+    rc = vtn_blocksub_resident(ctx, ctx->scratch, keep_mnv, max_mnv_dist);
+    if (rc) return rc;
+    return vtn_dbatch_fetch_blocksub(ctx, ctx->scratch, src_rec, off, len, cap_out, n_out, counters);
 }

@@ -1,0 +1,312 @@
+// vtn_blocksub.cu -- vt decompose_blocksub on the device: the fan-out plan of block substitutions.
+//
+// Replaces the record loop of Igor::decompose_blocksub() (decompose_blocksub.cpp:185-421) except its alignment mode (-a,
+// :198-303, Needleman-Wunsch over needle.cpp: not built).  A biallelic record whose REF and ALT have the same length > 1
+// (:304) becomes one SNP per differing position (:341-375) or, with keep_mnv (-m), one record per run of differences at
+// most max_mnv_dist apart (:322-337, :382-401, :405-410); every other record passes through (:413-418).
+// Output k = (src_rec, off, len): new POS = pos1 + off, alleles REF[off, off+len) / ALT[off, off+len); len 0 = the record
+// itself.  Counters as the reference counts them (:377-378 count differences also in -m mode).
+//
+// Kernels: vtb_count_kernel (one thread per record: outputs and counter contributions; the state machine of the reference
+// loop is kept literally, including what it does for -d <= 0), reduce / scan / apply of the output counts, vtb_emit_kernel
+// (the same walk again, writing at the record's offset).  Records that are not block substitutions never touch allele bytes.
+#include "vtn_internal.h"
+
+namespace
+{
+
+#define VTB_THREADS 256
+#define VTB_ITEMS 8
+#define VTB_TILE (VTB_THREADS * VTB_ITEMS)
+
+struct BsView
+{
+    uint32_t n_rec;
+    const uint32_t* allele_beg;
+    const uint32_t* allele_off;
+    const uint8_t* bytes;
+};
+
+// Walks one record.  EMIT = false: returns the number of outputs, adds the differences to n_diff and tells whether the record is a
+// block substitution.  EMIT = true: also writes the outputs at src/off/len + k0.
+template <bool EMIT>
+__device__ __forceinline__ uint32_t walk_record(const BsView& B, uint32_t r, int keep_mnv, int max_dist, bool& is_bs, uint32_t& n_diff,
+                                                uint32_t* src, uint32_t* off, uint32_t* len, uint64_t k0)
+{
+    const uint32_t ab = __ldg(B.allele_beg + r), n_allele = __ldg(B.allele_beg + r + 1) - ab;
+    is_bs = false;
+    n_diff = 0;
+    if (n_allele == 2)
+    {
+        const uint32_t o0 = __ldg(B.allele_off + ab), o1 = __ldg(B.allele_off + ab + 1), o2 = __ldg(B.allele_off + ab + 2);
+        const uint32_t ref_len = o1 - o0;
+        if (ref_len != 1 && ref_len == o2 - o1)
+        {
+            is_bs = true;
+            const uint8_t* ref = B.bytes + o0;
+            const uint8_t* alt = B.bytes + o1;
+            uint32_t k = 0;
+            int prev = -1, start = -1;
+            // the reference compares size_t(i - prev) with the int option: a negative -d converts to a huge unsigned value
+            const unsigned long long md = (unsigned long long)(long long)max_dist;
+            for (uint32_t i = 0; i < ref_len; ++i)
+            {
+                if (ref[i] != alt[i])
+                {
+                    ++n_diff;
+                    if (keep_mnv)
+                    {
+                        if (prev == -1 || (unsigned long long)(i - (uint32_t)prev) <= md)
+                        {
+                            prev = (int)i;
+                            if (start == -1) start = (int)i;
+                        }
+                    }
+                    else
+                    {
+                        if (EMIT)
+                        {
+                            src[k0 + k] = r;
+                            off[k0 + k] = i;
+                            len[k0 + k] = 1;
+                        }
+                        ++k;
+                    }
+                }
+                else if (keep_mnv && prev != -1 && !((unsigned long long)(i - (uint32_t)prev) < md))
+                {
+                    if (EMIT)
+                    {
+                        src[k0 + k] = r;
+                        off[k0 + k] = (uint32_t)start;
+                        len[k0 + k] = (uint32_t)(prev - start + 1);
+                    }
+                    ++k;
+                    prev = -1;
+                    start = -1;
+                }
+            }
+            if (keep_mnv && prev != -1)
+            {
+                if (EMIT)
+                {
+                    src[k0 + k] = r;
+                    off[k0 + k] = (uint32_t)start;
+                    len[k0 + k] = (uint32_t)(prev - start + 1);
+                }
+                ++k;
+            }
+            return k;
+        }
+    }
+    if (EMIT)
+    {
+        src[k0] = r;
+        off[k0] = 0;
+        len[k0] = 0;
+    }
+    return 1;
+}
+
+__device__ __forceinline__ uint32_t block_excl_sum_u32(uint32_t v, uint32_t* s_warp, uint32_t& total)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+    {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t wpre = 0, tot = 0;
+    for (int w = 0; w < VTB_THREADS / 32; ++w)
+    {
+        if (w < warp) wpre += s_warp[w];
+        tot += s_warp[w];
+    }
+    total = tot;
+    __syncthreads();
+    return wpre + inc - v;
+}
+
+// per record: number of outputs -> cnt[r]; per tile: total outputs -> agg[tile]; counters
+// counters: [0] no_variants [1] no_biallelic_blocksub [2] no_additional_snps [3] new_no_variants
+__global__ void __launch_bounds__(VTB_THREADS) vtb_count_kernel(BsView B, int keep_mnv, int max_dist, uint32_t* __restrict__ cnt,
+                                                                unsigned long long* __restrict__ agg, uint32_t* __restrict__ counters)
+{
+    __shared__ uint32_t s_warp[VTB_THREADS / 32];
+    uint32_t mine = 0, n_bs = 0, n_diff_all = 0, n_pass = 0;
+    // record r of the tile is handled by thread r % VTB_THREADS (coalesced allele_beg loads); the tile total is all that is kept
+    for (int j = 0; j < VTB_ITEMS; ++j)
+    {
+        const uint32_t r = blockIdx.x * VTB_TILE + j * VTB_THREADS + threadIdx.x;
+        if (r < B.n_rec)
+        {
+            bool is_bs;
+            uint32_t nd;
+            const uint32_t k = walk_record<false>(B, r, keep_mnv, max_dist, is_bs, nd, nullptr, nullptr, nullptr, 0);
+            cnt[r] = k;
+            mine += k;
+            n_bs += is_bs ? 1u : 0u;
+            n_pass += is_bs ? 0u : 1u;
+            n_diff_all += nd;
+        }
+    }
+    uint32_t total;
+    block_excl_sum_u32(mine, s_warp, total);
+    if (threadIdx.x == 0) agg[blockIdx.x] = total;
+    n_bs = __reduce_add_sync(0xffffffffu, n_bs);
+    n_pass = __reduce_add_sync(0xffffffffu, n_pass);
+    n_diff_all = __reduce_add_sync(0xffffffffu, n_diff_all);
+    if ((threadIdx.x & 31) == 0)
+    {
+        if (n_bs + n_pass) atomicAdd(counters + 0, n_bs + n_pass);
+        if (n_bs) atomicAdd(counters + 1, n_bs);
+        if (n_diff_all) atomicAdd(counters + 2, n_diff_all);
+        if (n_diff_all + n_pass) atomicAdd(counters + 3, n_diff_all + n_pass);
+    }
+}
+
+// exclusive scan of the tile totals in place (one block), grand total -> *total_out
+__global__ void __launch_bounds__(1024) vtb_scan_kernel(unsigned long long* agg, uint32_t n_tiles, unsigned long long* total_out)
+{
+    __shared__ unsigned long long s[1024];
+    const uint32_t per = (n_tiles + 1023) / 1024;
+    const uint32_t lo = threadIdx.x * per, hi = min(lo + per, n_tiles);
+    unsigned long long mine = 0;
+    for (uint32_t t = lo; t < hi; ++t) mine += agg[t];
+    s[threadIdx.x] = mine;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1)
+    {
+        unsigned long long x = 0;
+        if ((int)threadIdx.x >= o) x = s[threadIdx.x - o];
+        __syncthreads();
+        s[threadIdx.x] += x;
+        __syncthreads();
+    }
+    unsigned long long pre = s[threadIdx.x] - mine;
+    for (uint32_t t = lo; t < hi; ++t)
+    {
+        const unsigned long long x = agg[t];
+        agg[t] = pre;
+        pre += x;
+    }
+    if (threadIdx.x == 1023) *total_out = s[1023];
+}
+
+// the same tiles again: exclusive prefix of every record inside its tile (record order!), then the walk that writes
+__global__ void __launch_bounds__(VTB_THREADS) vtb_emit_kernel(BsView B, int keep_mnv, int max_dist, const uint32_t* __restrict__ cnt,
+                                                               const unsigned long long* __restrict__ agg, uint32_t* __restrict__ src,
+                                                               uint32_t* __restrict__ off, uint32_t* __restrict__ len, unsigned long long cap_out)
+{
+    __shared__ uint32_t s_warp[VTB_THREADS / 32];
+    unsigned long long base = agg[blockIdx.x];
+    for (int j = 0; j < VTB_ITEMS; ++j) // rows of VTB_THREADS consecutive records, in order
+    {
+        const uint32_t r = blockIdx.x * VTB_TILE + j * VTB_THREADS + threadIdx.x;
+        const uint32_t c = r < B.n_rec ? cnt[r] : 0u;
+        uint32_t row_total;
+        const uint32_t pre = block_excl_sum_u32(c, s_warp, row_total);
+        if (r < B.n_rec && base + pre + c <= cap_out)
+        {
+            bool is_bs;
+            uint32_t nd;
+            walk_record<true>(B, r, keep_mnv, max_dist, is_bs, nd, src, off, len, base + pre);
+        }
+        base += row_total;
+    }
+}
+
+} // namespace
+
+struct vtn_blocksub_buffers
+{
+    uint32_t cap_rec = 0;
+    unsigned long long cap_out = 0;
+    uint32_t *cnt = nullptr, *src = nullptr, *off = nullptr, *len = nullptr, *counters = nullptr;
+    unsigned long long *agg = nullptr, *total = nullptr;
+};
+
+static void blocksub_release(vtn_blocksub_buffers* b)
+{
+    if (!b) return;
+    cudaFree(b->cnt); cudaFree(b->src); cudaFree(b->off); cudaFree(b->len); cudaFree(b->counters); cudaFree(b->agg); cudaFree(b->total);
+    delete b;
+}
+
+void vtn_blocksub_dbatch_release(vtn_dbatch* d)
+{
+    blocksub_release(d->blocksub);
+    d->blocksub = nullptr;
+}
+
+uint64_t vtn_blocksub_out_bound(const vtn_batch* in) { return in ? (uint64_t)in->n_rec + in->n_bytes / 2 + 1 : 0; }
+
+int vtn_blocksub_resident(vtn_ctx* ctx, vtn_dbatch* d, int keep_mnv, int max_mnv_dist)
+{
+    if (!ctx || !d) return VTN_E_ARG;
+    VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    const unsigned long long need_out = (unsigned long long)d->cap_rec + d->cap_bytes / 2 + 1;
+    if (!d->blocksub || d->blocksub->cap_rec < d->n_rec || d->blocksub->cap_out < need_out)
+    {
+        blocksub_release(d->blocksub);
+        vtn_blocksub_buffers* b = d->blocksub = new vtn_blocksub_buffers();
+        b->cap_rec = d->cap_rec;
+        b->cap_out = need_out;
+        const size_t n_tiles = ((size_t)d->cap_rec + VTB_TILE - 1) / VTB_TILE + 1;
+        VTN_CUDA(ctx, cudaMalloc((void**)&b->cnt, ((size_t)d->cap_rec + 16) * 4));
+        VTN_CUDA(ctx, cudaMalloc((void**)&b->src, (size_t)(need_out + 16) * 4));
+        VTN_CUDA(ctx, cudaMalloc((void**)&b->off, (size_t)(need_out + 16) * 4));
+        VTN_CUDA(ctx, cudaMalloc((void**)&b->len, (size_t)(need_out + 16) * 4));
+        VTN_CUDA(ctx, cudaMalloc((void**)&b->counters, 4 * 4));
+        VTN_CUDA(ctx, cudaMalloc((void**)&b->agg, n_tiles * 8));
+        VTN_CUDA(ctx, cudaMalloc((void**)&b->total, 8));
+    }
+    vtn_blocksub_buffers* b = d->blocksub;
+    cudaStream_t s = ctx->stream;
+    VTN_CUDA(ctx, cudaMemsetAsync(b->counters, 0, 16, s));
+    VTN_CUDA(ctx, cudaMemsetAsync(b->total, 0, 8, s));
+    if (d->n_rec)
+    {
+        const uint32_t n_tiles = (d->n_rec + VTB_TILE - 1) / VTB_TILE;
+        BsView v{d->n_rec, d->allele_beg, d->allele_off, d->bytes};
+        vtb_count_kernel<<<n_tiles, VTB_THREADS, 0, s>>>(v, keep_mnv, max_mnv_dist, b->cnt, b->agg, b->counters);
+        vtb_scan_kernel<<<1, 1024, 0, s>>>(b->agg, n_tiles, b->total);
+        vtb_emit_kernel<<<n_tiles, VTB_THREADS, 0, s>>>(v, keep_mnv, max_mnv_dist, b->cnt, b->agg, b->src, b->off, b->len, b->cap_out);
+        VTN_CUDA(ctx, cudaGetLastError());
+        ctx->launches += 3;
+    }
+    return VTN_OK;
+}
+
+int vtn_dbatch_fetch_blocksub(vtn_ctx* ctx, vtn_dbatch* d, uint32_t* src_rec, uint32_t* off, uint32_t* len, uint64_t cap_out, uint64_t* n_out,
+                              vtn_blocksub_counters* counters)
+{
+    if (!ctx || !d || !d->blocksub || !n_out) return VTN_E_ARG;
+    cudaStream_t s = ctx->stream;
+    unsigned long long total = 0;
+    uint32_t c[4] = {0, 0, 0, 0};
+    VTN_CUDA(ctx, cudaMemcpyAsync(&total, d->blocksub->total, 8, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(c, d->blocksub->counters, 16, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaStreamSynchronize(s));
+    *n_out = total;
+    if (counters)
+    {
+        counters->no_variants = c[0];
+        counters->no_biallelic_blocksub = c[1];
+        counters->no_additional_snps = c[2];
+        counters->new_no_variants = c[3];
+    }
+    if (total > cap_out || total > d->blocksub->cap_out) return vtn_set_err(ctx, VTN_E_CAPACITY, "vtn_blocksub: output capacity too small (n_out is set)");
+    if (total)
+    {
+        VTN_CUDA(ctx, cudaMemcpyAsync(src_rec, d->blocksub->src, (size_t)total * 4, cudaMemcpyDeviceToHost, s));
+        VTN_CUDA(ctx, cudaMemcpyAsync(off, d->blocksub->off, (size_t)total * 4, cudaMemcpyDeviceToHost, s));
+        VTN_CUDA(ctx, cudaMemcpyAsync(len, d->blocksub->len, (size_t)total * 4, cudaMemcpyDeviceToHost, s));
+        VTN_CUDA(ctx, cudaStreamSynchronize(s));
+    }
+    return VTN_OK;
+}

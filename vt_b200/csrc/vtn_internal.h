@@ -75,6 +75,7 @@ struct VtnDevScratch
 
 struct vtn_uniq_buffers;  // vtn_uniq.cu
 struct vtn_order_buffers; // vtn_order.cu
+struct vtn_blocksub_buffers; // vtn_blocksub.cu
 struct vtn_dbatch
 {
     uint32_t n_rec = 0, n_allele = 0;
@@ -112,6 +113,7 @@ struct vtn_dbatch
     bool owns_inputs = true;
     vtn_uniq_buffers* uniq = nullptr; // order / first / heap scratch of vtn_uniq_resident (allocated on first use)
     vtn_order_buffers* order = nullptr; // arena of vtn_writer_order_resident (allocated on first use)
+    vtn_blocksub_buffers* blocksub = nullptr; // plan buffers of vtn_blocksub_resident (allocated on first use)
 };
 
 struct vtn_ctx
@@ -150,6 +152,7 @@ struct vtn_ctx
 void vtn_hmm_ctx_release(vtn_ctx* ctx);
 void vtn_uniq_dbatch_release(vtn_dbatch* d);
 void vtn_order_dbatch_release(vtn_dbatch* d);
+void vtn_blocksub_dbatch_release(vtn_dbatch* d);
 
 int vtn_set_err(vtn_ctx* ctx, int code, const std::string& msg);
 #define VTN_CUDA(ctx, call)                                                                              \
