@@ -244,3 +244,26 @@ def test_normalize_device_writer_order_streaming(tmp_path, window, batch):
     assert p1.returncode == p2.returncode == 0, (p1.stderr[-2000:], p2.stderr[-2000:])
     assert open(o1).read() == open(o2).read()
     assert _msgs(p1.stderr) == _msgs(p2.stderr)
+
+
+# ---- vt decompose_blocksub ----
+import blocksub_helpers as BS  # noqa: E402
+
+
+@pytest.mark.parametrize("stem,flags,tag", BS.CASES)
+def test_blocksub_cli_reference_golden_bytes(stem, flags, tag, tmp_path):
+    """vtn decompose_blocksub [-m] [-d N] [-p] against the reference's own fixtures (01, 03) and vt_ref outputs, byte for byte"""
+    vin, vout, verr = BS.paths(stem, tag)
+    out = str(tmp_path / "out.vcf")
+    rc, err = _run(VTN, ["decompose_blocksub"] + flags + [vin, "-o", out])
+    assert rc == 0, err
+    assert open(out).read() == open(vout).read()
+    assert _strip(err) == _strip(open(verr).read())
+
+
+def test_blocksub_cli_small_batches(tmp_path):
+    vin, vout, _ = BS.paths("synth", "m")
+    out = str(tmp_path / "out.vcf")
+    p = subprocess.run([VTN, "decompose_blocksub", "-m", vin, "-o", out], capture_output=True, text=True, env=dict(os.environ, VTN_CLI_BATCH="23"))
+    assert p.returncode == 0, p.stderr
+    assert open(out).read() == open(vout).read()

@@ -1212,12 +1212,170 @@ int cmd_uniq(int argc, char** argv)
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// decompose_blocksub  (Igor::decompose_blocksub, decompose_blocksub.cpp:185-421; -a alignment mode is not available):
+// vtn_blocksub gives the fan-out plan; each planned record keeps the source record's columns with new POS / REF / ALT and
+// INFO/OLD_CLUMPED (print_decomposed_var :166-183, :341-372), -p adds FORMAT/PS and phased GT; 1000-bp ordered writer (:133).
+// ------------------------------------------------------------------------------------------------------------
+int cmd_blocksub(int argc, char** argv)
+{
+    std::string in = "-", outp = "-";
+    bool keep_mnv = false, phased = false;
+    int max_dist = 2, device = 0;
+    for (int k = 1; k < argc; ++k)
+    {
+        std::string a = argv[k];
+        if (a == "-o" && k + 1 < argc) outp = argv[++k];
+        else if (a == "-d" && k + 1 < argc) max_dist = atoi(argv[++k]);
+        else if (a == "--device" && k + 1 < argc) device = atoi(argv[++k]);
+        else if (a == "-m") keep_mnv = true;
+        else if (a == "-p") phased = true;
+        else if (a == "-a") usage_and_exit("decompose_blocksub", "the alignment mode (-a) is not available in this shim");
+        else if (a == "-i" || a == "-I") usage_and_exit("decompose_blocksub", "intervals are not supported by this shim");
+        else if (a == "-" || a[0] != '-') in = a;
+        else usage_and_exit("decompose_blocksub", ("unknown option " + a).c_str());
+    }
+    fprintf(stderr, "decompose_blocksub v%s\n\n", VERSION); // print_options, decompose_blocksub.cpp:423-436
+    fprintf(stderr, "options:     input VCF file          %s\n", in.c_str());
+    fprintf(stderr, "         [o] output VCF file         %s\n", outp.c_str());
+    fprintf(stderr, "         [a] align/aggressive mode   false\n");
+    fprintf(stderr, "         [m] keep MNVs (Multi-Nucleotide Variants)   %s\n", keep_mnv ? "true" : "false");
+    fprintf(stderr, "         [d] MNVs max distance (when -m option is used)   %s\n", max_dist ? "true" : "false");
+    fprintf(stderr, "         [p] output phased genotypes %s\n\n", phased ? "true" : "false");
+    vtn_ctx* ctx = nullptr;
+    if (vtn_ctx_create(&ctx, device)) die(nullptr, "vtn_ctx_create");
+    Reader rd;
+    if (!rd.open(in))
+    {
+        fprintf(stderr, "[vtn] cannot open %s\n", in.c_str());
+        return 1;
+    }
+    Header h;
+    std::string line;
+    if (!read_header(rd, h, line))
+    {
+        fprintf(stderr, "[vtn] %s has no VCF header\n", in.c_str());
+        return 1;
+    }
+    DeviceWriter ow;
+    ow.out = open_out(outp);
+    ow.window = 1000;
+    ow.ctx = ctx;
+    std::string extra_hdr = "##INFO=<ID=OLD_CLUMPED,Number=1,Type=String,Description=\"Original chr:pos:ref:alt encoding\">";
+    if (phased) extra_hdr += "\n##FORMAT=<ID=PS,Number=1,Type=Integer,Description=\"ID for set of phased genotypes\">";
+    write_header(ow.out, h, extra_hdr.c_str());
+    size_t BATCH = 1u << 20;
+    if (const char* e = getenv("VTN_CLI_BATCH"))
+        if (atol(e) > 0) BATCH = (size_t)atol(e);
+    BatchBuf bb;
+    std::map<std::string, int> rid_cache;
+    LineParser lp;
+    std::vector<uint32_t> src, off, len;
+    vtn_blocksub_counters tot = {0, 0, 0, 0};
+    bool more = !line.empty();
+    while (more)
+    {
+        lp.read_batch(rd, line, more, BATCH, bb, ctx, false, rid_cache);
+        vtn_batch b = bb.view();
+        const uint64_t bound = vtn_blocksub_out_bound(&b);
+        src.resize(bound + 1), off.resize(bound + 1), len.resize(bound + 1);
+        uint64_t n_out = 0;
+        vtn_blocksub_counters c;
+        if (vtn_blocksub(ctx, &b, keep_mnv ? 1 : 0, max_dist, src.data(), off.data(), len.data(), bound, &n_out, &c)) die(ctx, "vtn_blocksub");
+        uint32_t cur = 0xffffffffu;
+        std::vector<Tok> col;
+        int32_t ps = 0;
+        for (uint64_t k = 0; k < n_out; ++k)
+        {
+            const uint32_t r = src[k];
+            const std::string& ln = bb.lines[r];
+            if (r != cur)
+            {
+                col = split(ln.data(), ln.size(), '\t');
+                cur = r;
+                ps = b.pos1[r] + (int32_t)off[k]; // the PS vector is sized at the record's first SNP and keeps that value (:343, resize)
+            }
+            DeviceWriter::Rec rec;
+            rec.rid = b.rid[r];
+            rec.chrom.assign(col[0].first, col[0].second);
+            std::string& o = rec.line;
+            if (!len[k])
+            {
+                rec.pos1 = b.pos1[r];
+                for (int q = 0; q < 5; ++q)
+                {
+                    if (q) o.push_back('\t');
+                    o.append(col[q].first, col[q].second);
+                }
+                put_tail(o, h, col, "");
+            }
+            else
+            {
+                rec.pos1 = b.pos1[r] + (int32_t)off[k];
+                o = rec.chrom + "\t" + std::to_string(rec.pos1) + "\t";
+                o.append(col[2].first, col[2].second);
+                o.push_back('\t');
+                o.append(col[3].first + off[k], len[k]);
+                o.push_back('\t');
+                o.append(col[4].first + off[k], len[k]);
+                std::string extra = "OLD_CLUMPED=" + rec.chrom + ":" + std::to_string(b.pos1[r]) + ":";
+                extra.append(col[3].first, col[3].second);
+                extra.push_back('/');
+                extra.append(col[4].first, col[4].second);
+                if (phased && !keep_mnv && col.size() > 9)
+                { // FORMAT gains PS, every GT separator becomes '|' (:346-366)
+                    std::vector<Tok> c2(col.begin(), col.begin() + 8);
+                    put_tail(o, h, c2, extra);
+                    std::vector<Tok> keys = split(col[8].first, col[8].second, ':');
+                    size_t gt_idx = keys.size();
+                    for (size_t q = 0; q < keys.size(); ++q)
+                        if (keys[q].second == 2 && !memcmp(keys[q].first, "GT", 2)) gt_idx = q;
+                    o.push_back('\t');
+                    o.append(col[8].first, col[8].second);
+                    o += ":PS";
+                    for (size_t cidx = 9; cidx < col.size(); ++cidx)
+                    {
+                        o.push_back('\t');
+                        std::string smp;
+                        put_sample(smp, h, keys, col[cidx].first, col[cidx].second);
+                        if (gt_idx < keys.size())
+                        {
+                            size_t f0 = 0;
+                            for (size_t q = 0; q < gt_idx; ++q) f0 = smp.find(':', f0) + 1;
+                            size_t f1 = smp.find(':', f0);
+                            if (f1 == std::string::npos) f1 = smp.size();
+                            for (size_t q = f0; q < f1; ++q)
+                                if (smp[q] == '/') smp[q] = '|';
+                        }
+                        o += smp;
+                        o += ":" + std::to_string(ps);
+                    }
+                }
+                else
+                    put_tail(o, h, col, extra);
+            }
+            ow.write(std::move(rec));
+        }
+        ow.drain(false);
+        tot.no_variants += c.no_variants, tot.no_biallelic_blocksub += c.no_biallelic_blocksub;
+        tot.no_additional_snps += c.no_additional_snps, tot.new_no_variants += c.new_no_variants;
+    }
+    ow.drain(true);
+    if (ow.out != stdout) fclose(ow.out);
+    fprintf(stderr, "\nstats: no. variants                       : %u\n", tot.no_variants); // print_stats, :438-447
+    fprintf(stderr, "       no. biallelic block substitutions  : %u\n\n", tot.no_biallelic_blocksub);
+    fprintf(stderr, "       no. additional SNPs                : %u\n", tot.no_additional_snps);
+    fprintf(stderr, "       no. variants after decomposition   : %u\n\n", tot.new_no_variants);
+    vtn_ctx_destroy(ctx);
+    return 0;
+}
+
 int main(int argc, char** argv)
 {
     clock_t t0 = clock();
     if (argc < 2)
     {
-        fprintf(stderr, "usage: vtn normalize|decompose|uniq [options] <in.vcf>   (B200 drop-in for vt's decompose/normalize path)\n");
+        fprintf(stderr, "usage: vtn normalize|decompose|decompose_blocksub|uniq [options] <in.vcf>   (B200 drop-in for vt's decompose/normalize path)\n");
         return 1;
     }
     std::string cmd = argv[1];
@@ -1233,6 +1391,11 @@ int main(int argc, char** argv)
     else if (cmd == "uniq")
     {
         cmd_uniq(argc - 1, argv + 1);
+        print = true;
+    }
+    else if (cmd == "decompose_blocksub")
+    {
+        cmd_blocksub(argc - 1, argv + 1);
         print = true;
     }
     else
