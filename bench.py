@@ -395,6 +395,101 @@ def run_u1(args, rank, world, local):
     })
 
 
+B1_RECORDS = int(os.environ.get("VTN_BENCH_B1_RECORDS", 20_000_000))
+
+
+def run_b1(args, rank, world, local):
+    """B1 (its own metric): vt decompose_blocksub's fan-out plan on the device (vtn_blocksub: three launches) over
+    biallelic records of which 10 % are block substitutions of 2..8 bases."""
+    import torch
+    import torch.distributed as dist
+    from vt_b200 import Context
+    from vt_b200.api import Batch
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rng = np.random.default_rng(20260109 + 1000 * rank)
+    n = B1_RECORDS
+    is_bs = rng.random(n) < 0.1
+    L = np.where(is_bs, rng.integers(2, 9, n), 1).astype(np.int64)
+    aoff = np.zeros(2 * n + 1, np.int64)
+    aoff[1::2] = np.cumsum(2 * L) - L
+    aoff[2::2] = np.cumsum(2 * L)
+    data = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, int(aoff[-1]))]
+    batch = Batch(np.arange(1, 20 * n + 1, 20, dtype=np.int64).astype(np.int32), np.zeros(n, np.int32), np.arange(0, 2 * n + 1, 2, dtype=np.uint32),
+                  aoff.astype(np.uint32), data)
+    ctx = Context(local)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ctx.sync()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    db = ctx.upload(batch)
+    for _ in range(args.warmup):
+        ctx.blocksub_resident(db)
+    ctx.sync()
+    sampler = ClockSampler(local)
+    barrier()
+    l0 = ctx.launch_count()
+    t0 = time.time()
+    ctx.timer_start()
+    for _ in range(args.steps):
+        ctx.blocksub_resident(db)
+    ms_total = ctx.timer_stop()
+    barrier()
+    launches = ctx.launch_count() - l0
+    ms_step = max_over_ranks(ms_total / args.steps)
+    e2e_steps = max(3, min(args.steps, 10))
+    ctx.blocksub(batch)
+    barrier()
+    w0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        src, off, ln, cnt = ctx.blocksub(batch)
+    barrier()
+    e2e_ms = max_over_ranks(1e3 * (time.perf_counter() - w0) / e2e_steps)
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1)
+    n_out = len(src)
+    assert cnt[0] == n and cnt[1] == int(is_bs.sum()) and n_out == cnt[3] and np.all(np.diff(src.astype(np.int64)) >= 0)
+    ctx.free(db)
+    if rank != 0:
+        return
+    # algorithmic bytes: allele_beg (4 B) + the output triple (12 B per output) for everyone; allele_off (12 B) for biallelic records;
+    # the allele bytes of the block substitutions twice (count and emit walk them)
+    alg = 4 * n + 12 * n_out + 12 * n + 2 * int((2 * L[is_bs]).sum())
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = alg / (ms_total / args.steps / 1e3) / 1e9
+    h2d = 8 * n + 4 * (n + 1) + 4 * (2 * n + 1) + batch.n_bytes
+    emit({
+        "metric": "blocksub_records_per_s", "value": world * n / (ms_step / 1e3) / 1e6, "unit": "M records/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "B1: vt decompose_blocksub plan over %d biallelic records per GPU, %d block substitutions of 2..8 bases -> %d output records" % (n, int(is_bs.sum()), n_out),
+                   "records_per_gpu": n, "l2": "inputs+outputs per step (%d MB) exceed the 126 MB L2; no explicit flush" % (alg // 1000000),
+                   "sharding": "independent batch per rank, no collective"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "kernel": "vtb_count_kernel + vtb_emit_kernel", "algorithmic_bytes_per_launch": alg,
+                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)"},
+        "e2e": {"value": world * n / (e2e_ms / 1e3) / 1e6, "unit": "M records/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 12 * n_out + 24,
+                "ms_per_step": e2e_ms, "steps": e2e_steps},
+        "gpu_launches": int(launches), "clocks": clocks,
+    })
+
+
 T1_RECORDS = int(os.environ.get("VTN_BENCH_T1_RECORDS", 4_000_000))
 
 
@@ -728,7 +823,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="vtn", choices=["vtn", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5", "u1", "w1", "t1"],
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5", "u1", "w1", "t1", "b1"],
                     help="c2 (default, the metric's configuration), c3 = multiallelic decompose+normalize fused, c4 = STR/homopolymer reference with maximal left shifts, "
                          "c5 = AHMM/LFHMM/RFHMM realignment (its own metric)")
     args = ap.parse_args()
@@ -753,6 +848,9 @@ def main():
         return
     if args.workload == "t1":
         run_t1(args, rank, world, local)
+        return
+    if args.workload == "b1":
+        run_b1(args, rank, world, local)
         return
 
     import torch

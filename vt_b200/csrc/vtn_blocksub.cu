@@ -9,7 +9,9 @@
 //
 // Kernels: vtb_count_kernel (one thread per record: outputs and counter contributions; the state machine of the reference
 // loop is kept literally, including what it does for -d <= 0), reduce / scan / apply of the output counts, vtb_emit_kernel
-// (the same walk again, writing at the record's offset).  Records that are not block substitutions never touch allele bytes.
+// (writing at the record's offset: it replays the state machine on the difference mask the count pass left in cnt[], so it reads
+// nothing of the record; only block substitutions longer than 25 bases walk their bytes again).  Records that are not block
+// substitutions never touch allele bytes.
 #include "vtn_internal.h"
 
 namespace
@@ -29,84 +31,93 @@ struct BsView
 
 // Walks one record.  EMIT = false: returns the number of outputs, adds the differences to n_diff and tells whether the record is a
 // block substitution.  EMIT = true: also writes the outputs at src/off/len + k0.
-template <bool EMIT>
-__device__ __forceinline__ uint32_t walk_record(const BsView& B, uint32_t r, int keep_mnv, int max_dist, bool& is_bs, uint32_t& n_diff,
-                                                uint32_t* src, uint32_t* off, uint32_t* len, uint64_t k0)
+// what decides whether a record is walked: offset of REF and its length; ref_len 0 = not a block substitution
+struct BsHead
 {
-    const uint32_t ab = __ldg(B.allele_beg + r), n_allele = __ldg(B.allele_beg + r + 1) - ab;
-    is_bs = false;
-    n_diff = 0;
+    uint32_t o0, ref_len;
+};
+
+__device__ __forceinline__ BsHead head_of(const BsView& B, uint32_t ab, uint32_t n_allele)
+{
+    BsHead h{0u, 0u};
     if (n_allele == 2)
     {
         const uint32_t o0 = __ldg(B.allele_off + ab), o1 = __ldg(B.allele_off + ab + 1), o2 = __ldg(B.allele_off + ab + 2);
         const uint32_t ref_len = o1 - o0;
-        if (ref_len != 1 && ref_len == o2 - o1)
+        if (ref_len != 1 && ref_len == o2 - o1) h = BsHead{o0, ref_len}; // ref_len 0 == alt_len 0 cannot come out of a VCF line
+    }
+    return h;
+}
+
+// The reference's loop over the positions of a block substitution (decompose_blocksub.cpp:306-411), the state machine kept
+// literally; differs(i) tells whether REF[i] != ALT[i].  Returns the number of outputs; EMIT writes them at src/off/len + k0.
+template <bool EMIT, class Differs>
+__device__ __forceinline__ uint32_t walk_positions(uint32_t r, uint32_t n_pos, Differs differs, int keep_mnv, int max_dist, uint32_t& n_diff,
+                                                   uint32_t* src, uint32_t* off, uint32_t* len, uint64_t k0)
+{
+    uint32_t k = 0;
+    int prev = -1, start = -1;
+    // the reference compares size_t(i - prev) with the int option: a negative -d converts to a huge unsigned value
+    const unsigned long long md = (unsigned long long)(long long)max_dist;
+    for (uint32_t i = 0; i < n_pos; ++i)
+    {
+        if (differs(i))
         {
-            is_bs = true;
-            const uint8_t* ref = B.bytes + o0;
-            const uint8_t* alt = B.bytes + o1;
-            uint32_t k = 0;
-            int prev = -1, start = -1;
-            // the reference compares size_t(i - prev) with the int option: a negative -d converts to a huge unsigned value
-            const unsigned long long md = (unsigned long long)(long long)max_dist;
-            for (uint32_t i = 0; i < ref_len; ++i)
+            ++n_diff;
+            if (keep_mnv)
             {
-                if (ref[i] != alt[i])
+                if (prev == -1 || (unsigned long long)(i - (uint32_t)prev) <= md)
                 {
-                    ++n_diff;
-                    if (keep_mnv)
-                    {
-                        if (prev == -1 || (unsigned long long)(i - (uint32_t)prev) <= md)
-                        {
-                            prev = (int)i;
-                            if (start == -1) start = (int)i;
-                        }
-                    }
-                    else
-                    {
-                        if (EMIT)
-                        {
-                            src[k0 + k] = r;
-                            off[k0 + k] = i;
-                            len[k0 + k] = 1;
-                        }
-                        ++k;
-                    }
-                }
-                else if (keep_mnv && prev != -1 && !((unsigned long long)(i - (uint32_t)prev) < md))
-                {
-                    if (EMIT)
-                    {
-                        src[k0 + k] = r;
-                        off[k0 + k] = (uint32_t)start;
-                        len[k0 + k] = (uint32_t)(prev - start + 1);
-                    }
-                    ++k;
-                    prev = -1;
-                    start = -1;
+                    prev = (int)i;
+                    if (start == -1) start = (int)i;
                 }
             }
-            if (keep_mnv && prev != -1)
+            else
             {
                 if (EMIT)
                 {
                     src[k0 + k] = r;
-                    off[k0 + k] = (uint32_t)start;
-                    len[k0 + k] = (uint32_t)(prev - start + 1);
+                    off[k0 + k] = i;
+                    len[k0 + k] = 1;
                 }
                 ++k;
             }
-            return k;
+        }
+        else if (keep_mnv && prev != -1 && !((unsigned long long)(i - (uint32_t)prev) < md))
+        {
+            if (EMIT)
+            {
+                src[k0 + k] = r;
+                off[k0 + k] = (uint32_t)start;
+                len[k0 + k] = (uint32_t)(prev - start + 1);
+            }
+            ++k;
+            prev = -1;
+            start = -1;
         }
     }
-    if (EMIT)
+    if (keep_mnv && prev != -1)
     {
-        src[k0] = r;
-        off[k0] = 0;
-        len[k0] = 0;
+        if (EMIT)
+        {
+            src[k0 + k] = r;
+            off[k0 + k] = (uint32_t)start;
+            len[k0 + k] = (uint32_t)(prev - start + 1);
+        }
+        ++k;
     }
-    return 1;
+    return k;
 }
+
+// cnt[r] carries the count pass's findings to the emit pass:
+//   mode (bits 31:30) 0: pass-through record, one output;
+//                     2: block substitution of at most VTB_MASK_BITS bases: outputs in bits 29:25, difference mask in bits 24:0 --
+//                        the emit pass replays the state machine on the mask and loads nothing of the record.  Positions past the
+//                        last difference are equal ones: an open run is written either by the distance rule or after the loop, the
+//                        same (start, prev) both ways, so the replay stops at the last set bit;
+//                     3: longer block substitution: outputs in bits 29:0, the emit pass walks the bytes again.
+#define VTB_MASK_BITS 25
+__device__ __forceinline__ uint32_t outputs_of(uint32_t cf) { return (cf >> 30) == 2u ? (cf >> VTB_MASK_BITS) & 31u : cf & 0x3fffffffu; }
 
 __device__ __forceinline__ uint32_t block_excl_sum_u32(uint32_t v, uint32_t* s_warp, uint32_t& total)
 {
@@ -138,16 +149,41 @@ __global__ void __launch_bounds__(VTB_THREADS) vtb_count_kernel(BsView B, int ke
 {
     __shared__ uint32_t s_warp[VTB_THREADS / 32];
     uint32_t mine = 0, n_bs = 0, n_diff_all = 0, n_pass = 0;
-    // record r of the tile is handled by thread r % VTB_THREADS (coalesced allele_beg loads); the tile total is all that is kept
+    // record r of the tile is handled by thread r % VTB_THREADS (coalesced allele_beg loads); the tile total is all that is kept.
+    // The loads that decide whether a record is walked are issued for all the thread's records before any walk (two rounds of
+    // independent loads instead of VTB_ITEMS dependent chains).
+    uint32_t ab[VTB_ITEMS], na[VTB_ITEMS];
+    BsHead h[VTB_ITEMS];
+#pragma unroll
+    for (int j = 0; j < VTB_ITEMS; ++j)
+    {
+        const uint32_t r = blockIdx.x * VTB_TILE + j * VTB_THREADS + threadIdx.x;
+        ab[j] = r < B.n_rec ? __ldg(B.allele_beg + r) : 0u;
+        na[j] = r < B.n_rec ? __ldg(B.allele_beg + r + 1) - ab[j] : 0u;
+    }
+#pragma unroll
+    for (int j = 0; j < VTB_ITEMS; ++j) h[j] = head_of(B, ab[j], na[j]);
+#pragma unroll
     for (int j = 0; j < VTB_ITEMS; ++j)
     {
         const uint32_t r = blockIdx.x * VTB_TILE + j * VTB_THREADS + threadIdx.x;
         if (r < B.n_rec)
         {
-            bool is_bs;
-            uint32_t nd;
-            const uint32_t k = walk_record<false>(B, r, keep_mnv, max_dist, is_bs, nd, nullptr, nullptr, nullptr, 0);
-            cnt[r] = k;
+            const bool is_bs = h[j].ref_len != 0;
+            uint32_t nd = 0, k = 1, cf = 1;
+            if (is_bs)
+            {
+                const uint8_t* ref = B.bytes + h[j].o0;
+                const uint8_t* alt = ref + h[j].ref_len;
+                uint32_t mask = 0;
+                k = walk_positions<false>(r, h[j].ref_len, [&](uint32_t i) {
+                        const bool d = ref[i] != alt[i];
+                        if (i < VTB_MASK_BITS) mask |= (d ? 1u : 0u) << i;
+                        return d;
+                    }, keep_mnv, max_dist, nd, nullptr, nullptr, nullptr, 0);
+                cf = h[j].ref_len <= VTB_MASK_BITS ? (0x80000000u | (k << VTB_MASK_BITS) | mask) : (0xC0000000u | k);
+            }
+            cnt[r] = cf;
             mine += k;
             n_bs += is_bs ? 1u : 0u;
             n_pass += is_bs ? 0u : 1u;
@@ -207,14 +243,33 @@ __global__ void __launch_bounds__(VTB_THREADS) vtb_emit_kernel(BsView B, int kee
     for (int j = 0; j < VTB_ITEMS; ++j) // rows of VTB_THREADS consecutive records, in order
     {
         const uint32_t r = blockIdx.x * VTB_TILE + j * VTB_THREADS + threadIdx.x;
-        const uint32_t c = r < B.n_rec ? cnt[r] : 0u;
+        const uint32_t cf = r < B.n_rec ? cnt[r] : 0u;
+        const uint32_t c = outputs_of(cf);
         uint32_t row_total;
         const uint32_t pre = block_excl_sum_u32(c, s_warp, row_total);
         if (r < B.n_rec && base + pre + c <= cap_out)
         {
-            bool is_bs;
-            uint32_t nd;
-            walk_record<true>(B, r, keep_mnv, max_dist, is_bs, nd, src, off, len, base + pre);
+            const uint32_t mode = cf >> 30;
+            uint32_t nd = 0;
+            if (mode == 2u)
+            {
+                const uint32_t mask = cf & ((1u << VTB_MASK_BITS) - 1u);
+                walk_positions<true>(r, 32u - (uint32_t)__clz(mask), [&](uint32_t i) { return ((mask >> i) & 1u) != 0u; }, keep_mnv, max_dist, nd,
+                                     src, off, len, base + pre);
+            }
+            else if (mode == 3u)
+            {
+                const BsHead h = head_of(B, __ldg(B.allele_beg + r), 2u);
+                const uint8_t* ref = B.bytes + h.o0;
+                const uint8_t* alt = ref + h.ref_len;
+                walk_positions<true>(r, h.ref_len, [&](uint32_t i) { return ref[i] != alt[i]; }, keep_mnv, max_dist, nd, src, off, len, base + pre);
+            }
+            else
+            {
+                src[base + pre] = r;
+                off[base + pre] = 0;
+                len[base + pre] = 0;
+            }
         }
         base += row_total;
     }
