@@ -1,4 +1,5 @@
-// vtn_cli.cpp -- host shim that keeps vt's command surface for the path:  `vtn normalize`, `vtn decompose`, `vtn uniq`.
+// vtn_cli.cpp -- host shim that keeps vt's command surface for the path:  `vtn normalize`, `vtn decompose`, `vtn uniq`,
+// `vtn decompose_blocksub`.
 //
 // Mirrors the reference tools' flags, stderr text and VCF output (normalize.cpp:84-171, :332-382; decompose.cpp:
 // 80-150, :960-995) while the per-record arithmetic runs in libvtn's CUDA kernels through the C ABI (include/vtn.h):
@@ -10,6 +11,8 @@
 //               the OLD_VARIANT values of a group.
 //   decompose : vtn_decompose gives the (source record, ALT index) fan-out plan and the counters; the INFO/FORMAT
 //               sub-setting of each emitted record is host-side text work (decompose.cpp:210-392 plain, :393-957 -s).
+//   decompose_blocksub : vtn_blocksub gives the (source record, offset, length) plan and the counters (decompose_blocksub.cpp:
+//               185-421 without -a); the host writes POS/REF/ALT, OLD_CLUMPED and with -p the PS field (:352-372).
 // VCF text only (plain or gzip/bgzip in, plain out); BCF and the -f filter / -i intervals are not handled here
 // (SURVEY.md 8f).  Values of Type=Float fields and QUAL are re-serialised the way htslib does when it formats a
 // record it has parsed (float32 storage, 6 significant digits), because the reference's output goes through that.
