@@ -152,17 +152,52 @@ __global__ void __launch_bounds__(VTB_THREADS) vtb_count_kernel(BsView B, int ke
     // record r of the tile is handled by thread r % VTB_THREADS (coalesced allele_beg loads); the tile total is all that is kept.
     // The loads that decide whether a record is walked are issued for all the thread's records before any walk (two rounds of
     // independent loads instead of VTB_ITEMS dependent chains).
+    const int lane = threadIdx.x & 31;
     uint32_t ab[VTB_ITEMS], na[VTB_ITEMS];
     BsHead h[VTB_ITEMS];
 #pragma unroll
     for (int j = 0; j < VTB_ITEMS; ++j)
     {
         const uint32_t r = blockIdx.x * VTB_TILE + j * VTB_THREADS + threadIdx.x;
+        // allele_beg[r + 1] is the next lane's allele_beg[r]: one load per record, lane 31 (or the last record) loads its own end
         ab[j] = r < B.n_rec ? __ldg(B.allele_beg + r) : 0u;
-        na[j] = r < B.n_rec ? __ldg(B.allele_beg + r + 1) - ab[j] : 0u;
+        const uint32_t nxt = __shfl_down_sync(0xffffffffu, ab[j], 1);
+        const bool own = lane == 31 || r + 1 >= B.n_rec;
+        na[j] = r < B.n_rec ? (own ? __ldg(B.allele_beg + r + 1) : nxt) - ab[j] : 0u;
     }
 #pragma unroll
-    for (int j = 0; j < VTB_ITEMS; ++j) h[j] = head_of(B, ab[j], na[j]);
+    for (int j = 0; j < VTB_ITEMS; ++j)
+    {
+        // the same for allele_off: the end of a biallelic record's ALT is the next record's REF offset.  REF/ALT offsets are one
+        // 8-byte load when the record's first allele index is even (always, in a batch of biallelic records).
+        const uint32_t r = blockIdx.x * VTB_TILE + j * VTB_THREADS + threadIdx.x;
+        const bool two = na[j] == 2u;
+        uint32_t o0 = 0, o1 = 0;
+        if (two)
+        {
+            if ((ab[j] & 1u) == 0u)
+            {
+                const uint2 o = __ldg(reinterpret_cast<const uint2*>(B.allele_off + ab[j]));
+                o0 = o.x;
+                o1 = o.y;
+            }
+            else
+            {
+                o0 = __ldg(B.allele_off + ab[j]);
+                o1 = __ldg(B.allele_off + ab[j] + 1);
+            }
+        }
+        const uint32_t nxt = __shfl_down_sync(0xffffffffu, o0, 1);
+        const bool nxt_two = __shfl_down_sync(0xffffffffu, two ? 1 : 0, 1) != 0;
+        h[j] = BsHead{0u, 0u};
+        if (two)
+        {
+            const bool own = lane == 31 || r + 1 >= B.n_rec || !nxt_two;
+            const uint32_t o2 = own ? __ldg(B.allele_off + ab[j] + 2) : nxt;
+            const uint32_t ref_len = o1 - o0;
+            if (ref_len != 1 && ref_len == o2 - o1) h[j] = BsHead{o0, ref_len};
+        }
+    }
 #pragma unroll
     for (int j = 0; j < VTB_ITEMS; ++j)
     {
@@ -254,6 +289,17 @@ __global__ void __launch_bounds__(VTB_THREADS) vtb_emit_kernel(BsView B, int kee
             if (mode == 2u)
             {
                 const uint32_t mask = cf & ((1u << VTB_MASK_BITS) - 1u);
+                if (!keep_mnv) // one SNP per set bit (:341-375): no need to step through the equal positions
+                {
+                    uint64_t k = base + pre;
+                    for (uint32_t m = mask; m; m &= m - 1u, ++k)
+                    {
+                        src[k] = r;
+                        off[k] = (uint32_t)__ffs((int)m) - 1u;
+                        len[k] = 1;
+                    }
+                }
+                else
                 walk_positions<true>(r, 32u - (uint32_t)__clz(mask), [&](uint32_t i) { return ((mask >> i) & 1u) != 0u; }, keep_mnv, max_dist, nd,
                                      src, off, len, base + pre);
             }
