@@ -117,6 +117,24 @@ __device__ __forceinline__ uint32_t walk_positions(uint32_t r, uint32_t n_pos, D
 //                        same (start, prev) both ways, so the replay stops at the last set bit;
 //                     3: longer block substitution: outputs in bits 29:0, the emit pass walks the bytes again.
 #define VTB_MASK_BITS 25
+
+// eight bytes from any address: three aligned words and two funnel shifts (the batch's byte buffer is padded past its end)
+__device__ __forceinline__ unsigned long long load8(const uint8_t* p)
+{
+    const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+    const uint32_t sh = (uint32_t)(a & 3u) * 8u;
+    const uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
+    return (unsigned long long)__funnelshift_r(w0, w1, sh) | ((unsigned long long)__funnelshift_r(w1, w2, sh) << 32);
+}
+
+// bit i = byte i of x is not zero
+__device__ __forceinline__ uint32_t nonzero_bytes(unsigned long long x)
+{
+    const unsigned long long m7 = 0x7f7f7f7f7f7f7f7fULL;
+    const unsigned long long t = ((((x & m7) + m7) | x) >> 7) & 0x0101010101010101ULL;
+    return (uint32_t)((t * 0x0102040810204080ULL) >> 56);
+}
 __device__ __forceinline__ uint32_t outputs_of(uint32_t cf) { return (cf >> 30) == 2u ? (cf >> VTB_MASK_BITS) & 31u : cf & 0x3fffffffu; }
 
 __device__ __forceinline__ uint32_t block_excl_sum_u32(uint32_t v, uint32_t* s_warp, uint32_t& total)
@@ -208,15 +226,31 @@ __global__ void __launch_bounds__(VTB_THREADS) vtb_count_kernel(BsView B, int ke
             uint32_t nd = 0, k = 1, cf = 1;
             if (is_bs)
             {
+                const uint32_t L = h[j].ref_len;
                 const uint8_t* ref = B.bytes + h[j].o0;
-                const uint8_t* alt = ref + h[j].ref_len;
-                uint32_t mask = 0;
-                k = walk_positions<false>(r, h[j].ref_len, [&](uint32_t i) {
-                        const bool d = ref[i] != alt[i];
-                        if (i < VTB_MASK_BITS) mask |= (d ? 1u : 0u) << i;
-                        return d;
-                    }, keep_mnv, max_dist, nd, nullptr, nullptr, nullptr, 0);
-                cf = h[j].ref_len <= VTB_MASK_BITS ? (0x80000000u | (k << VTB_MASK_BITS) | mask) : (0xC0000000u | k);
+                const uint8_t* alt = ref + L;
+                if (L <= VTB_MASK_BITS)
+                {
+                    // difference mask eight bases at a time (unaligned 8-byte windows of REF and ALT, XOR, non-zero bytes -> bits);
+                    // the outputs then follow from the mask alone, as in the emit pass
+                    uint32_t mask = 0;
+                    for (uint32_t c = 0; c < L; c += 8) mask |= nonzero_bytes(load8(ref + c) ^ load8(alt + c)) << c;
+                    mask &= (1u << L) - 1u;
+                    nd = (uint32_t)__popc(mask);
+                    k = nd;
+                    if (keep_mnv)
+                    {
+                        uint32_t unused = 0;
+                        k = walk_positions<false>(r, 32u - (uint32_t)__clz(mask), [&](uint32_t i) { return ((mask >> i) & 1u) != 0u; }, keep_mnv, max_dist,
+                                                  unused, nullptr, nullptr, nullptr, 0);
+                    }
+                    cf = 0x80000000u | (k << VTB_MASK_BITS) | mask;
+                }
+                else
+                {
+                    k = walk_positions<false>(r, L, [&](uint32_t i) { return ref[i] != alt[i]; }, keep_mnv, max_dist, nd, nullptr, nullptr, nullptr, 0);
+                    cf = 0xC0000000u | k;
+                }
             }
             cnt[r] = cf;
             mine += k;
