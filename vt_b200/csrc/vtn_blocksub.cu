@@ -163,9 +163,10 @@ __device__ __forceinline__ uint32_t block_excl_sum_u32(uint32_t v, uint32_t* s_w
 // per record: number of outputs -> cnt[r]; per tile: total outputs -> agg[tile]; counters
 // counters: [0] no_variants [1] no_biallelic_blocksub [2] no_additional_snps [3] new_no_variants
 __global__ void __launch_bounds__(VTB_THREADS) vtb_count_kernel(BsView B, int keep_mnv, int max_dist, uint32_t* __restrict__ cnt,
-                                                                unsigned long long* __restrict__ agg, uint32_t* __restrict__ counters)
+                                                                unsigned long long* __restrict__ agg, unsigned long long* __restrict__ tile_cnt)
 {
     __shared__ uint32_t s_warp[VTB_THREADS / 32];
+    __shared__ uint32_t s_bs[VTB_THREADS / 32], s_diff[VTB_THREADS / 32];
     uint32_t mine = 0, n_bs = 0, n_diff_all = 0, n_pass = 0;
     // record r of the tile is handled by thread r % VTB_THREADS (coalesced allele_beg loads); the tile total is all that is kept.
     // The loads that decide whether a record is walked are issued for all the thread's records before any walk (two rounds of
@@ -261,27 +262,51 @@ __global__ void __launch_bounds__(VTB_THREADS) vtb_count_kernel(BsView B, int ke
     }
     uint32_t total;
     block_excl_sum_u32(mine, s_warp, total);
-    if (threadIdx.x == 0) agg[blockIdx.x] = total;
+    // the tile's counter contributions go to tile_cnt[] (block substitutions | differences << 32) and are summed by the scan
+    // kernel: atomics on four shared words (one L2 sector) from every warp of 9766 blocks were what the whole pass waited for
     n_bs = __reduce_add_sync(0xffffffffu, n_bs);
-    n_pass = __reduce_add_sync(0xffffffffu, n_pass);
     n_diff_all = __reduce_add_sync(0xffffffffu, n_diff_all);
     if ((threadIdx.x & 31) == 0)
     {
-        if (n_bs + n_pass) atomicAdd(counters + 0, n_bs + n_pass);
-        if (n_bs) atomicAdd(counters + 1, n_bs);
-        if (n_diff_all) atomicAdd(counters + 2, n_diff_all);
-        if (n_diff_all + n_pass) atomicAdd(counters + 3, n_diff_all + n_pass);
+        s_bs[threadIdx.x >> 5] = n_bs;
+        s_diff[threadIdx.x >> 5] = n_diff_all;
     }
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        uint32_t b = 0, d = 0;
+        for (int w = 0; w < VTB_THREADS / 32; ++w)
+        {
+            b += s_bs[w];
+            d += s_diff[w];
+        }
+        agg[blockIdx.x] = total;
+        tile_cnt[blockIdx.x] = (unsigned long long)b | ((unsigned long long)d << 32);
+    }
+    (void)n_pass;
 }
 
 // exclusive scan of the tile totals in place (one block), grand total -> *total_out
-__global__ void __launch_bounds__(1024) vtb_scan_kernel(unsigned long long* agg, uint32_t n_tiles, unsigned long long* total_out)
+// counters: [0] no_variants [1] no_biallelic_blocksub [2] no_additional_snps [3] new_no_variants
+__global__ void __launch_bounds__(1024) vtb_scan_kernel(unsigned long long* agg, uint32_t n_tiles, unsigned long long* total_out,
+                                                        const unsigned long long* __restrict__ tile_cnt, uint32_t n_rec, uint32_t* counters)
 {
     __shared__ unsigned long long s[1024];
+    __shared__ unsigned long long s_c[32];
     const uint32_t per = (n_tiles + 1023) / 1024;
     const uint32_t lo = threadIdx.x * per, hi = min(lo + per, n_tiles);
     unsigned long long mine = 0;
-    for (uint32_t t = lo; t < hi; ++t) mine += agg[t];
+    uint32_t c_bs = 0, c_diff = 0;
+    for (uint32_t t = lo; t < hi; ++t)
+    {
+        mine += agg[t];
+        const unsigned long long x = tile_cnt[t];
+        c_bs += (uint32_t)x;
+        c_diff += (uint32_t)(x >> 32);
+    }
+    c_bs = __reduce_add_sync(0xffffffffu, c_bs);
+    c_diff = __reduce_add_sync(0xffffffffu, c_diff);
+    if ((threadIdx.x & 31) == 0) s_c[threadIdx.x >> 5] = (unsigned long long)c_bs | ((unsigned long long)c_diff << 32);
     s[threadIdx.x] = mine;
     __syncthreads();
     for (int o = 1; o < 1024; o <<= 1)
@@ -300,6 +325,19 @@ __global__ void __launch_bounds__(1024) vtb_scan_kernel(unsigned long long* agg,
         pre += x;
     }
     if (threadIdx.x == 1023) *total_out = s[1023];
+    if (threadIdx.x == 0) // the barriers of the scan above order s_c
+    {
+        uint32_t n_bs = 0, n_diff = 0;
+        for (int w = 0; w < 32; ++w)
+        {
+            n_bs += (uint32_t)s_c[w];
+            n_diff += (uint32_t)(s_c[w] >> 32);
+        }
+        counters[0] = n_rec;
+        counters[1] = n_bs;
+        counters[2] = n_diff;
+        counters[3] = n_diff + (n_rec - n_bs);
+    }
 }
 
 // the same tiles again: exclusive prefix of every record inside its tile (record order!), then the walk that writes
@@ -362,13 +400,13 @@ struct vtn_blocksub_buffers
     uint32_t cap_rec = 0;
     unsigned long long cap_out = 0;
     uint32_t *cnt = nullptr, *src = nullptr, *off = nullptr, *len = nullptr, *counters = nullptr;
-    unsigned long long *agg = nullptr, *total = nullptr;
+    unsigned long long *agg = nullptr, *total = nullptr, *tile_cnt = nullptr;
 };
 
 static void blocksub_release(vtn_blocksub_buffers* b)
 {
     if (!b) return;
-    cudaFree(b->cnt); cudaFree(b->src); cudaFree(b->off); cudaFree(b->len); cudaFree(b->counters); cudaFree(b->agg); cudaFree(b->total);
+    cudaFree(b->cnt); cudaFree(b->src); cudaFree(b->off); cudaFree(b->len); cudaFree(b->counters); cudaFree(b->agg); cudaFree(b->total); cudaFree(b->tile_cnt);
     delete b;
 }
 
@@ -398,6 +436,7 @@ int vtn_blocksub_resident(vtn_ctx* ctx, vtn_dbatch* d, int keep_mnv, int max_mnv
         VTN_CUDA(ctx, cudaMalloc((void**)&b->len, (size_t)(need_out + 16) * 4));
         VTN_CUDA(ctx, cudaMalloc((void**)&b->counters, 4 * 4));
         VTN_CUDA(ctx, cudaMalloc((void**)&b->agg, n_tiles * 8));
+        VTN_CUDA(ctx, cudaMalloc((void**)&b->tile_cnt, n_tiles * 8));
         VTN_CUDA(ctx, cudaMalloc((void**)&b->total, 8));
     }
     vtn_blocksub_buffers* b = d->blocksub;
@@ -408,8 +447,8 @@ int vtn_blocksub_resident(vtn_ctx* ctx, vtn_dbatch* d, int keep_mnv, int max_mnv
     {
         const uint32_t n_tiles = (d->n_rec + VTB_TILE - 1) / VTB_TILE;
         BsView v{d->n_rec, d->allele_beg, d->allele_off, d->bytes};
-        vtb_count_kernel<<<n_tiles, VTB_THREADS, 0, s>>>(v, keep_mnv, max_mnv_dist, b->cnt, b->agg, b->counters);
-        vtb_scan_kernel<<<1, 1024, 0, s>>>(b->agg, n_tiles, b->total);
+        vtb_count_kernel<<<n_tiles, VTB_THREADS, 0, s>>>(v, keep_mnv, max_mnv_dist, b->cnt, b->agg, b->tile_cnt);
+        vtb_scan_kernel<<<1, 1024, 0, s>>>(b->agg, n_tiles, b->total, b->tile_cnt, d->n_rec, b->counters);
         vtb_emit_kernel<<<n_tiles, VTB_THREADS, 0, s>>>(v, keep_mnv, max_mnv_dist, b->cnt, b->agg, b->src, b->off, b->len, b->cap_out);
         VTN_CUDA(ctx, cudaGetLastError());
         ctx->launches += 3;
