@@ -11,7 +11,7 @@
 // loop is kept literally, including what it does for -d <= 0), reduce / scan / apply of the output counts, vtb_emit_kernel
 // (writing at the record's offset: it replays the state machine on the difference mask the count pass left in cnt[], so it reads
 // nothing of the record; only block substitutions longer than 25 bases walk their bytes again).  Records that are not block
-// substitutions never touch allele bytes.
+// substitutions never touch allele bytes.  The counters are summed per tile and added up by the scan kernel (no atomics).
 #include "vtn_internal.h"
 
 namespace
