@@ -345,15 +345,50 @@ __global__ void __launch_bounds__(VTB_THREADS) vtb_emit_kernel(BsView B, int kee
                                                                const unsigned long long* __restrict__ agg, uint32_t* __restrict__ src,
                                                                uint32_t* __restrict__ off, uint32_t* __restrict__ len, unsigned long long cap_out)
 {
-    __shared__ uint32_t s_warp[VTB_THREADS / 32];
-    unsigned long long base = agg[blockIdx.x];
+    // one scan per tile: every thread's eight counts are loaded together, scanned inside their warp (row j, warp w), the 64
+    // (row, warp) totals are scanned by warp 0, and the write loop below only adds three numbers
+    __shared__ uint32_t s_tot[VTB_ITEMS * (VTB_THREADS / 32)];
+    __shared__ uint32_t s_pre[VTB_ITEMS][VTB_THREADS];
+    static_assert(VTB_ITEMS * (VTB_THREADS / 32) == 64, "warp 0 scans two (row, warp) totals per lane");
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int j = 0; j < VTB_ITEMS; ++j)
+    {
+        const uint32_t r = blockIdx.x * VTB_TILE + j * VTB_THREADS + threadIdx.x;
+        const uint32_t c = r < B.n_rec ? outputs_of(__ldg(cnt + r)) : 0u;
+        uint32_t inc = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+        {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        s_pre[j][threadIdx.x] = inc - c;
+        if (lane == 31) s_tot[j * (VTB_THREADS / 32) + warp] = inc;
+    }
+    __syncthreads();
+    if (warp == 0)
+    {
+        const uint32_t a = s_tot[2 * lane], b = s_tot[2 * lane + 1];
+        uint32_t inc = a + b;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+        {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        s_tot[2 * lane] = inc - a - b;
+        s_tot[2 * lane + 1] = inc - b;
+    }
+    __syncthreads();
+    const unsigned long long base = agg[blockIdx.x];
+#pragma unroll 1
     for (int j = 0; j < VTB_ITEMS; ++j) // rows of VTB_THREADS consecutive records, in order
     {
         const uint32_t r = blockIdx.x * VTB_TILE + j * VTB_THREADS + threadIdx.x;
-        const uint32_t cf = r < B.n_rec ? cnt[r] : 0u;
+        const uint32_t cf = r < B.n_rec ? __ldg(cnt + r) : 0u; // second read of the tile's counts: L1
         const uint32_t c = outputs_of(cf);
-        uint32_t row_total;
-        const uint32_t pre = block_excl_sum_u32(c, s_warp, row_total);
+        const uint32_t pre = s_tot[j * (VTB_THREADS / 32) + warp] + s_pre[j][threadIdx.x];
         if (r < B.n_rec && base + pre + c <= cap_out)
         {
             const uint32_t mode = cf >> 30;
@@ -389,7 +424,6 @@ __global__ void __launch_bounds__(VTB_THREADS) vtb_emit_kernel(BsView B, int kee
                 len[base + pre] = 0;
             }
         }
-        base += row_total;
     }
 }
 
