@@ -352,29 +352,55 @@ __global__ void __launch_bounds__(VTO_THREADS) vto_sum_apply_kernel(const uint32
 
 // scatter: a record that leaves alone at its step goes straight to its output position; the others into their step's list
 // (arbitrary order inside the list)
-__global__ void __launch_bounds__(VTO_THREADS) vto_scatter_kernel(uint32_t n, const uint32_t* __restrict__ slot, const uint32_t* __restrict__ base,
-                                                                  const uint32_t* __restrict__ cnt, uint32_t* __restrict__ fill,
-                                                                  uint32_t* __restrict__ tmp, uint32_t* __restrict__ order)
+#define VTO_SC_ITEMS 4
+// cnt[sl] is not read again: the records of step sl are base[sl + 1] - base[sl] (the same sector as base[sl]; every record has
+// exactly one step, so the sum is n).  Four records per thread, their loads issued together: one record per thread left the
+// kernel waiting out three dependent round trips (slot -> base -> list) with nothing else in flight.
+__device__ __forceinline__ uint32_t step_end(const uint32_t* __restrict__ base, uint32_t sl, uint32_t n)
 {
-    const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
-    if (v >= n) return;
-    const uint32_t sl = slot[v];
-    const uint32_t b = __ldg(base + sl);
-    if (__ldg(cnt + sl) == 1) order[b] = v;
-    else tmp[b + atomicAdd(fill + sl, 1u)] = v;
+    return sl + 1 < n ? __ldg(base + sl + 1) : n;
+}
+
+__global__ void __launch_bounds__(VTO_THREADS) vto_scatter_kernel(uint32_t n, const uint32_t* __restrict__ slot, const uint32_t* __restrict__ base,
+                                                                  uint32_t* __restrict__ fill, uint32_t* __restrict__ tmp,
+                                                                  uint32_t* __restrict__ order)
+{
+    const uint32_t v0 = blockIdx.x * (VTO_THREADS * VTO_SC_ITEMS) + threadIdx.x; // rows of VTO_THREADS consecutive records
+    uint32_t sl[VTO_SC_ITEMS], b[VTO_SC_ITEMS], e[VTO_SC_ITEMS];
+#pragma unroll
+    for (int j = 0; j < VTO_SC_ITEMS; ++j)
+    {
+        const uint32_t v = v0 + j * VTO_THREADS;
+        sl[j] = v < n ? __ldg(slot + v) : 0u;
+    }
+#pragma unroll
+    for (int j = 0; j < VTO_SC_ITEMS; ++j)
+    {
+        const uint32_t v = v0 + j * VTO_THREADS;
+        b[j] = v < n ? __ldg(base + sl[j]) : 0u;
+        e[j] = v < n ? step_end(base, sl[j], n) : 0u;
+    }
+#pragma unroll
+    for (int j = 0; j < VTO_SC_ITEMS; ++j)
+    {
+        const uint32_t v = v0 + j * VTO_THREADS;
+        if (v >= n) continue;
+        if (e[j] - b[j] == 1) order[b[j]] = v;
+        else tmp[b[j] + atomicAdd(fill + sl[j], 1u)] = v;
+    }
 }
 
 // rank by (pos, arrival) inside the lists of more than one record: the writer empties its buffer from the back, smallest
 // position first, equal positions in arrival order
 __global__ void __launch_bounds__(VTO_THREADS) vto_rank_kernel(uint32_t n, const int32_t* __restrict__ pos, const uint32_t* __restrict__ slot,
-                                                               const uint32_t* __restrict__ base, const uint32_t* __restrict__ cnt,
-                                                               const uint32_t* __restrict__ tmp, uint32_t* __restrict__ order)
+                                                               const uint32_t* __restrict__ base, const uint32_t* __restrict__ tmp,
+                                                               uint32_t* __restrict__ order)
 {
     const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= n) return;
-    const uint32_t sl = slot[v], c = __ldg(cnt + sl);
+    const uint32_t sl = slot[v];
+    const uint32_t b = __ldg(base + sl), c = step_end(base, sl, n) - b;
     if (c <= 1) return;
-    const uint32_t b = __ldg(base + sl);
     const int32_t p = __ldg(pos + v);
     uint32_t rank = 0;
     for (uint32_t k = b; k < b + c; ++k)
@@ -455,8 +481,9 @@ static int order_launch(vtn_ctx* ctx, vtn_order_buffers* o, const int32_t* d_rid
     vto_sum_reduce_kernel<<<n_tiles, VTO_THREADS, 0, s>>>(o->cnt, n, o->agg2);
     vto_sum_scan_kernel<<<1, 1024, 0, s>>>(o->agg2, n_tiles);
     vto_sum_apply_kernel<<<n_tiles, VTO_THREADS, 0, s>>>(o->cnt, n, o->agg2, o->base);
-    vto_scatter_kernel<<<g1, VTO_THREADS, 0, s>>>(n, o->slot, o->base, o->cnt, o->fill, o->tmp, o->order);
-    vto_rank_kernel<<<g1, VTO_THREADS, 0, s>>>(n, d_pos, o->slot, o->base, o->cnt, o->tmp, o->order);
+    vto_scatter_kernel<<<(n + VTO_THREADS * VTO_SC_ITEMS - 1) / (VTO_THREADS * VTO_SC_ITEMS), VTO_THREADS, 0, s>>>(n, o->slot, o->base, o->fill, o->tmp,
+                                                                                                                   o->order);
+    vto_rank_kernel<<<g1, VTO_THREADS, 0, s>>>(n, d_pos, o->slot, o->base, o->tmp, o->order);
     VTN_CUDA(ctx, cudaGetLastError());
     ctx->launches += 9;
     return VTN_OK;
