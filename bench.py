@@ -29,7 +29,8 @@ METRIC = "normalize_records_per_s"
 UNIT = "M records/s"
 N_RECORDS = int(os.environ.get("VTN_BENCH_RECORDS", 10_000_000))
 REF_SCALE = float(os.environ.get("VTN_BENCH_REF_SCALE", 1.0))
-CPU_SAMPLE_RECORDS = int(os.environ.get("VTN_BENCH_CPU_SAMPLE", 1_000_000))
+CPU_SAMPLE_RECORDS = int(os.environ.get("VTN_BENCH_CPU_SAMPLE", 4_000_000))
+CHECK_RECORDS = int(os.environ.get("VTN_BENCH_CHECK_RECORDS", 100_000))
 VT_REF = os.path.join(ROOT, "oracle", "_ref", "vt_ref")
 
 
@@ -89,54 +90,77 @@ class ClockSampler:
 
 
 def write_vcf(path, names, seqs, batch, lo, hi):
-    with open(path, "w") as f:
-        f.write("##fileformat=VCFv4.2\n")
+    """records [lo, hi) of a biallelic batch as a sites-only VCF (vectorised: one bytes join per column)"""
+    with open(path, "wb") as f:
+        f.write(b"##fileformat=VCFv4.2\n")
         for n, s in zip(names, seqs):
-            f.write("##contig=<ID=%s,length=%d>\n" % (n, s.shape[0]))
-        f.write("#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\n")
+            f.write(("##contig=<ID=%s,length=%d>\n" % (n, s.shape[0])).encode())
+        f.write(b"#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\n")
         data = batch.data.tobytes()
         ao = batch.allele_off
-        lines = []
-        for r in range(lo, hi):
-            o0, o1, o2 = int(ao[2 * r]), int(ao[2 * r + 1]), int(ao[2 * r + 2])
-            lines.append("%s\t%d\t.\t%s\t%s\t.\t.\t.\n" % (names[batch.rid[r]], batch.pos1[r], data[o0:o1].decode(), data[o1:o2].decode()))
-        f.write("".join(lines))
+        bnames = [n.encode() for n in names]
+        rid, pos = batch.rid, batch.pos1
+        CH = 200000
+        for c0 in range(lo, hi, CH):
+            c1 = min(hi, c0 + CH)
+            o = ao[2 * c0:2 * c1 + 1].tolist()
+            rr = rid[c0:c1].tolist()
+            pp = pos[c0:c1].tolist()
+            f.write(b"".join(b"%s\t%d\t.\t%s\t%s\t.\t.\t.\n" % (bnames[rr[i]], pp[i], data[o[2 * i]:o[2 * i + 1]], data[o[2 * i + 1]:o[2 * i + 2]])
+                             for i in range(c1 - c0)))
 
 
-def cpu_reference_run(n_sample, steps, warmup):
-    """Times the unmodified reference `vt normalize` on a bounded sample of the C2 workload: n_sample records
-    on one chr21-sized contig of the same synthetic reference; P = host cores processes each normalise the
-    whole sample concurrently (vt itself is single-threaded); throughput = P * n_sample / slowest wall."""
+def _run_procs(cmds):
+    t0 = time.perf_counter()
+    procs = [subprocess.Popen(c, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL) for c in cmds]
+    rcs = [p.wait() for p in procs]
+    dt = time.perf_counter() - t0
+    if any(rcs):
+        raise RuntimeError("reference vt failed: %s" % rcs)
+    return dt
+
+
+def cpu_reference_run(n_sample, steps, warmup, names=None, seqs=None, batch=None):
+    """Times the unmodified reference `vt normalize` (oracle/_ref/vt_ref) on a bounded sample OF THE SAME WORKLOAD: the first
+    n_sample records of the C2 batch (sorted by contig, position) against the same full synthetic reference as a FASTA + .fai
+    on tmpfs, cut into P = host cores consecutive range shards, one single-threaded `vt normalize` process per shard with its
+    own output file (BASELINE.md 4 (ii); vt's own way to go parallel is one process per interval, program.cpp:152-190);
+    throughput = n_sample / slowest wall.  Also: one process alone on one shard (its native mode), and `vt view` on that
+    shard (the parse + write floor)."""
     from vt_b200 import synth
     import helpers
     if not os.path.exists(VT_REF):
         raise RuntimeError("oracle/_ref/vt_ref missing: run __graft_entry__.build() in the build container")
     cores = len(os.sched_getaffinity(0))
     P = max(1, min(cores, 64))
-    contigs = [synth.GRCH38[20]]
-    names, seqs = synth.make_reference(scale=REF_SCALE, contigs=contigs)
-    batch = synth.make_biallelic(seqs, n_sample, seed=synth.SEED_VCF_C2)
+    if seqs is None:
+        names, seqs, batch = load_workload("c2", 0)
+    n_sample = min(n_sample, batch.n_rec)
     tmp = tempfile.mkdtemp(prefix="vtn_cpu_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
-    fa = os.path.join(tmp, "ref.fa")
-    helpers.write_fasta(fa, names, seqs)
-    vcf = os.path.join(tmp, "in.vcf")
-    write_vcf(vcf, names, seqs, batch, 0, batch.n_rec)
-    times = []
-    for it in range(warmup + steps):
-        t0 = time.perf_counter()
-        procs = [subprocess.Popen([VT_REF, "normalize", vcf, "-r", fa, "-o", os.path.join(tmp, "out%d.vcf" % p), "-q"],
-                                  stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL) for p in range(P)]
-        rcs = [p.wait() for p in procs]
-        dt = time.perf_counter() - t0
-        if any(rcs):
-            raise RuntimeError("reference vt normalize failed: %s" % rcs)
-        if it >= warmup:
-            times.append(dt)
-    import shutil
-    shutil.rmtree(tmp, ignore_errors=True)
+    try:
+        fa = os.path.join(tmp, "ref.fa")
+        helpers.write_fasta(fa, names, seqs)
+        cuts = [n_sample * i // P for i in range(P + 1)]
+        for i in range(P):
+            write_vcf(os.path.join(tmp, "in%d.vcf" % i), names, seqs, batch, cuts[i], cuts[i + 1])
+        cmds = [[VT_REF, "normalize", os.path.join(tmp, "in%d.vcf" % i), "-r", fa, "-o", os.path.join(tmp, "out%d.vcf" % i), "-q"] for i in range(P)]
+        times = []
+        for it in range(warmup + steps):
+            dt = _run_procs(cmds)
+            if it >= warmup:
+                times.append(dt)
+        one = _run_procs(cmds[:1])
+        view = _run_procs([[VT_REF, "view", os.path.join(tmp, "in0.vcf"), "-o", os.path.join(tmp, "view0.vcf")]])
+    finally:
+        import shutil
+        shutil.rmtree(tmp, ignore_errors=True)
     ms = 1e3 * float(np.mean(times))
-    val = P * n_sample / (ms / 1e3) / 1e6
-    sample = "%d records (80%% SNV/10%% del/10%% ins, C2 generator) on one %d-bp contig of the synthetic reference, VCF text + FASTA on tmpfs, %d concurrent single-threaded `vt normalize` processes each over the whole sample" % (n_sample, seqs[0].shape[0], P)
+    val = n_sample / (ms / 1e3) / 1e6
+    n0 = cuts[1] - cuts[0]
+    sample = ("the first %d records of the C2 batch (80%% SNV/10%% del/10%% ins) against the same %.2f Gb synthetic reference (FASTA + .fai on tmpfs), "
+              "cut into %d consecutive range shards, one single-threaded unmodified `vt normalize` process per shard, VCF text in and out, wall = slowest; "
+              "one process alone on one shard: %.3f M records/s; `vt view` on that shard (parse + write floor): %.3f M records/s"
+              % (n_sample, sum(s.shape[0] for s in seqs) / 1e9, P, n0 / one / 1e6, n0 / view / 1e6))
     return val, ms, P, sample
 
 
@@ -823,6 +847,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="vtn", choices=["vtn", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--layout", default="bi", choices=["bi", "general"], help="c2 / c4: compact biallelic batch (vtn_normalize_bi, default) or the general vtn_batch")
+    ap.add_argument("--resident-only", action="store_true", help="c2 / c4: only the device-resident loop (profiling passes); prints a reduced line")
+    ap.add_argument("--no-compare", action="store_true", help="c2 / c4: skip the side measurement of the general layout")
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5", "u1", "w1", "t1", "b1"],
                     help="c2 (default, the metric's configuration), c3 = multiallelic decompose+normalize fused, c4 = STR/homopolymer reference with maximal left shifts, "
                          "c5 = AHMM/LFHMM/RFHMM realignment (its own metric)")
@@ -853,18 +880,22 @@ def main():
         run_b1(args, rank, world, local)
         return
 
-    import torch
-    import torch.distributed as dist
-    from vt_b200 import Context, synth
-    from vt_b200.api import NormResult
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        import atexit
-        atexit.register(lambda: dist.is_initialized() and dist.destroy_process_group())
+    run_c2_c4(args, rank, world, local)
 
-    t_setup = time.time()
-    if args.workload == "c4":
+
+def load_workload(workload, rank):
+    """(names, seqs, batch) of C2 / C4 for this rank.  VTN_BENCH_CACHE=<dir> keeps the generated arrays as .npy files there so
+    that several bench invocations of one session (variants, the ncu passes) do not regenerate 3.1 Gb each."""
+    from vt_b200 import synth
+    from vt_b200.api import Batch
+    cache = os.environ.get("VTN_BENCH_CACHE")
+    tag = "%s_%d_%g_%d" % (workload, N_RECORDS, REF_SCALE, rank)
+    if cache and os.path.exists(os.path.join(cache, tag + ".done")):
+        names = open(os.path.join(cache, tag + ".names")).read().split()
+        seqs = [np.load(os.path.join(cache, "%s_seq%d.npy" % (tag, i))) for i in range(len(names))]
+        b = [np.load(os.path.join(cache, "%s_b%d.npy" % (tag, i))) for i in range(5)]
+        return names, seqs, Batch(*b)
+    if workload == "c4":
         tracts = []
         names, seqs = synth.make_reference(seed=synth.SEED_REF_C4, scale=REF_SCALE, str_frac=0.3, tracts_out=tracts)
         batch = synth.make_str_indels(seqs, tracts, N_RECORDS, seed=synth.SEED_VCF_C4 + 1000 * rank)
@@ -872,10 +903,87 @@ def main():
     else:
         names, seqs = synth.make_reference(scale=REF_SCALE)
         batch = synth.make_biallelic(seqs, N_RECORDS, seed=synth.SEED_VCF_C2 + 1000 * rank)
+    if cache:
+        os.makedirs(cache, exist_ok=True)
+        open(os.path.join(cache, tag + ".names"), "w").write(" ".join(names))
+        for i, x in enumerate(seqs):
+            np.save(os.path.join(cache, "%s_seq%d.npy" % (tag, i)), x)
+        for i, x in enumerate((batch.pos1, batch.rid, batch.allele_beg, batch.allele_off, batch.data)):
+            np.save(os.path.join(cache, "%s_b%d.npy" % (tag, i)), x)
+        open(os.path.join(cache, tag + ".done"), "w").write("ok")
+    return names, seqs, batch
+
+
+def slice_batch(batch, a, b):
+    """records [a, b) of a Batch as a Batch of their own (checker leg)"""
+    from vt_b200.api import Batch
+    s0, s1 = int(batch.allele_beg[a]), int(batch.allele_beg[b])
+    o0, o1 = int(batch.allele_off[s0]), int(batch.allele_off[s1])
+    return Batch(batch.pos1[a:b], batch.rid[a:b], batch.allele_beg[a:b + 1] - np.uint32(s0), batch.allele_off[s0:s1 + 1] - np.uint32(o0), batch.data[o0:o1])
+
+
+def oracle_check_slice(seqs, batch, status, vtype, res, a, b):
+    """Untimed checker leg (the only use of oracle/ in this arm): records [a, b) of the timed batch through the CPU oracle,
+    compared bit for bit with what the device left for them.  -> number of records checked."""
+    import helpers
+    sub = slice_batch(batch, a, b)
+    exp = helpers.Oracle().normalize(seqs, sub)
+    n = b - a
+    assert np.array_equal(status[a:b], exp.status[:n]), "bench: status differs from the oracle on the checked slice"
+    assert np.array_equal(vtype[a:b], exp.vtype[:n]), "bench: vtype differs from the oracle on the checked slice"
+    k = res.n_changed
+    rec = res.chg_rec[:k]
+    lo, hi = int(np.searchsorted(rec, a)), int(np.searchsorted(rec, b))
+    ke = exp.n_changed
+    assert hi - lo == ke, "bench: changed-record count differs from the oracle on the checked slice (%d vs %d)" % (hi - lo, ke)
+    assert np.array_equal(rec[lo:hi] - np.uint32(a), exp.chg_rec[:ke])
+    for name in ("chg_pos1", "chg_lt", "chg_le", "chg_rt"):
+        assert np.array_equal(getattr(res, name)[lo:hi], getattr(exp, name)[:ke]), "bench: %s differs from the oracle" % name
+    b0, b1 = int(res.chg_off[lo]), int(res.chg_off[hi])
+    assert b1 - b0 == exp.n_changed_bytes and np.array_equal(res.chg_bytes[b0:b1], exp.chg_bytes[:exp.n_changed_bytes]), "bench: new allele bytes differ from the oracle"
+    return n
+
+
+def kernel_source_hash():
+    """sha1 over the sources of the normalize kernels: keys the ncu traffic record in profiles/traffic.json"""
+    import hashlib
+    h = hashlib.sha1()
+    for f in ("vtn_normalize.cu", "vtn_fast.cuh", "vtn_ref_dev.cuh", "vtn_internal.h", "vtn_scan.cuh"):
+        h.update(open(os.path.join(ROOT, "vt_b200", "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def measured_traffic(workload, layout):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel from an ncu --set full capture made with
+    THESE kernel sources (profiles/traffic.json, written by profiles/ncu_traffic.py); None when no capture matches."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+    except Exception:
+        return None, None
+    e = t.get("%s:%s:%s" % (kernel_source_hash(), workload, layout))
+    if not e or e.get("records") != N_RECORDS or e.get("ref_scale") != REF_SCALE:
+        return None, None
+    return float(e["dram_bytes"]), e.get("source")
+
+
+def run_c2_c4(args, rank, world, local):
+    import torch
+    import torch.distributed as dist
+    from vt_b200 import Context, synth
+    from vt_b200.api import NormResult, NormResultBi
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import atexit
+        atexit.register(lambda: dist.is_initialized() and dist.destroy_process_group())
+
+    t_setup = time.time()
+    names, seqs, batch = load_workload(args.workload, rank)
     ctx = Context(local)
     ctx.load_reference(names, seqs)
     ref_bases = sum(s.shape[0] for s in seqs)
-    del seqs
+    if rank != 0:
+        del seqs
     log("[rank %d] setup %.1fs: %d records, %d allele bytes, reference %d bases" % (rank, time.time() - t_setup, batch.n_rec, batch.n_bytes, ref_bases))
 
     def barrier():
@@ -891,45 +999,108 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    # ---------------- device-resident: value + roofline ----------------
-    db = ctx.upload(batch)
-    for _ in range(args.warmup):
-        ctx.normalize_resident(db)
-    ctx.sync()
-    res = ctx.fetch_result(db, batch)
-    alg_bytes = synth.algorithmic_bytes(batch, res)
-    sampler = ClockSampler(local)
-    barrier()
-    l0 = ctx.launch_count()
-    t0 = time.time()
-    ctx.timer_start()
-    for _ in range(args.steps):
-        ctx.normalize_resident(db)
-    ms_total = ctx.timer_stop()
-    barrier()
-    launches = ctx.launch_count() - l0
-    ms_step = max_over_ranks(ms_total / args.steps)
-    value = world * batch.n_rec / (ms_step / 1e3) / 1e6
+    def all_ranks(x):
+        if world == 1:
+            return [x]
+        t = torch.zeros(world, dtype=torch.float64, device="cuda")
+        t[rank] = x
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return [float(v) for v in t.tolist()]
 
+    bi_layout = args.layout == "bi"
+    bi = ctx.bi_pack(batch) if bi_layout else None
+
+    def timed_resident(db, steps):
+        for _ in range(args.warmup):
+            ctx.normalize_resident(db)
+        ctx.sync()
+        barrier()
+        l0 = ctx.launch_count()
+        ctx.timer_start()
+        for _ in range(steps):
+            ctx.normalize_resident(db)
+        ms = ctx.timer_stop()
+        barrier()
+        return ms / steps, ctx.launch_count() - l0
+
+    # ---------------- device-resident: value + roofline ----------------
+    db = ctx.upload_bi(bi) if bi_layout else ctx.upload(batch)
+    ctx.normalize_resident(db)
+    ctx.sync()
+    if bi_layout:
+        res = ctx.fetch_result_bi(db, bi)
+        status, vtype = res.expand()
+    else:
+        res = ctx.fetch_result(db, batch)
+        status, vtype = res.status, res.vtype
+
+    class _R:  # what synth.algorithmic_bytes reads
+        pass
+    ar = _R()
+    ar.vtype, ar.n_changed, ar.chg_rec, ar.chg_le, ar.n_changed_bytes = vtype, res.n_changed, res.chg_rec, res.chg_le, res.n_changed_bytes
+    alg_bytes = synth.algorithmic_bytes(batch, ar)
+    sampler = ClockSampler(local)
+    t0 = time.time()
+    ms_local, launches = timed_resident(db, args.steps)
+    ms_step = max_over_ranks(ms_local)
+    per_rank_ms = all_ranks(ms_local)
+    value = world * batch.n_rec / (ms_step / 1e3) / 1e6
+    # the timed result once more, after the timed loop: this is what the checker leg below looks at
+    if bi_layout:
+        res = ctx.fetch_result_bi(db, bi)
+        status, vtype = res.expand()
+    else:
+        res = ctx.fetch_result(db, batch)
+        status, vtype = res.status, res.vtype
+
+    if args.resident_only:
+        if rank == 0:
+            emit({"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+                  "resident_only": True, "layout": args.layout, "gpu_launches": int(launches), "algorithmic_bytes_per_launch": alg_bytes, "clocks": sampler.stop(t0, time.time())})
+        ctx.free(db)
+        return
     # ---------------- end to end through the C ABI with pinned host buffers ----------------
-    hb = pinned_batch(ctx, batch)
-    hres = NormResult(batch.n_rec, batch.n_bytes, ctx)
     e2e_steps = max(3, min(args.steps, 20))
+    if bi_layout:
+        hres = NormResultBi(batch.n_rec, batch.n_bytes, ctx)
+        call = lambda: ctx.normalize_bi(bi, hres)
+    else:
+        hb = pinned_batch(ctx, batch)
+        hres = NormResult(batch.n_rec, batch.n_bytes, ctx)
+        call = lambda: ctx.normalize(hb, hres)
     for _ in range(3):
-        ctx.normalize(hb, hres)
+        call()
     barrier()
     w0 = time.perf_counter()
     for _ in range(e2e_steps):
-        ctx.normalize(hb, hres)
+        call()
     barrier()
-    e2e_ms = max_over_ranks(1e3 * (time.perf_counter() - w0) / e2e_steps)
+    e2e_local = 1e3 * (time.perf_counter() - w0) / e2e_steps
+    e2e_ms = max_over_ranks(e2e_local)
+    per_rank_e2e = all_ranks(e2e_local)
     t1 = time.time()
     clocks = sampler.stop(t0, t1)
     e2e_val = world * batch.n_rec / (e2e_ms / 1e3) / 1e6
-    h2d = 4 * batch.n_rec * 2 + 4 * (batch.n_rec + 1) + 4 * (batch.n_allele + 1) + batch.n_bytes
     k = hres.n_changed
-    d2h = 2 * batch.n_rec + 16 + 48 + 20 * k + 8 * (k + 1) + hres.n_changed_bytes
+    if bi_layout:
+        h2d = bi.h2d_bytes
+        d2h = batch.n_rec + 16 + 48 + 4 + 20 * k + 8 * (k + 1) + hres.n_changed_bytes + 5 * hres.n_notes
+    else:
+        h2d = 4 * batch.n_rec * 2 + 4 * (batch.n_rec + 1) + 4 * (batch.n_allele + 1) + batch.n_bytes
+        d2h = 2 * batch.n_rec + 16 + 48 + 20 * k + 8 * (k + 1) + hres.n_changed_bytes
     assert hres.n_changed == res.n_changed and hres.counters == res.counters
+    assert np.array_equal(hres.chg_rec[:k], res.chg_rec[:k]) and np.array_equal(hres.chg_pos1[:k], res.chg_pos1[:k])
+
+    # the general layout beside it (same records, vtn_batch): what the compact layout is measured against
+    other = None
+    if bi_layout and not args.no_compare:
+        db2 = ctx.upload(batch)
+        o_ms, _ = timed_resident(db2, max(3, min(args.steps, 10)))
+        r2 = ctx.fetch_result(db2, batch)
+        assert np.array_equal(r2.status[:batch.n_rec], status) and np.array_equal(r2.vtype[:batch.n_rec], vtype) and r2.n_changed == res.n_changed
+        assert np.array_equal(r2.chg_bytes[:r2.n_changed_bytes], res.chg_bytes[:res.n_changed_bytes])
+        ctx.free(db2)
+        other = {"layout": "general (vtn_batch)", "ms_per_step": max_over_ranks(o_ms)}
 
     peaks = {}
     try:
@@ -937,11 +1108,16 @@ def main():
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    achieved = alg_bytes / (ms_total / args.steps / 1e3) / 1e9
+    achieved = alg_bytes / (ms_local / 1e3) / 1e9
 
     if rank != 0:
         ctx.free(db)
         return
+    # ---------------- checker leg (untimed): a fixed slice of the timed batch against the CPU oracle ----------------
+    n_chk = min(batch.n_rec, CHECK_RECORDS)
+    a_chk = (batch.n_rec - n_chk) // 2
+    checked = oracle_check_slice(seqs, batch, status, vtype, res, a_chk, a_chk + n_chk)
+    traffic, traffic_src = measured_traffic(args.workload, args.layout)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
@@ -949,21 +1125,25 @@ def main():
         "config": {
             "workload": ("C2: %d synthetic biallelic records per GPU (80%% SNV, 10%% del, 10%% ins, half of the indels unnormalized), synthetic %.2f Gb GRCh38-shaped reference resident in HBM" if args.workload == "c2" else
                          "C4: %d synthetic STR/homopolymer indels per GPU (k=1..4 whole units, 90%% at the rightmost copy of the tract), synthetic %.2f Gb reference with 30%% tandem repeats resident in HBM") % (batch.n_rec, ref_bases / 1e9),
+            "layout": "compact biallelic batch (vtn_batch_bi: pos1 + 2 length bytes + allele bytes per record, contig runs)" if bi_layout else "general batch (vtn_batch)",
             "records_per_gpu": batch.n_rec, "changed_per_gpu": res.n_changed,
             "l2": "inputs+outputs per step (%d MB) exceed the 126 MB L2; no explicit flush" % ((h2d + d2h) // 1000000),
             "sharding": "independent batch per rank, reference replicated, no collective",
+            "per_rank_ms_per_step": per_rank_ms, "per_rank_e2e_ms_per_step": per_rank_e2e,
+            "checked_against_oracle": "%d records [%d, %d) of the timed batch: status, vtype, changed records and new allele bytes bit-exact (untimed checker leg)" % (checked, a_chk, a_chk + n_chk),
         },
         "roofline": {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "traffic": (558.1e6 if (args.workload == "c2" and N_RECORDS == 10_000_000 and REF_SCALE == 1.0) else None),
-            "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of vtn_normalize_kernel<fast>, one ncu --set full capture of this command (profiles/r1o_ncu_normalize_v9.txt: 493.9 MB read + 64.2 MB written)",
-            "kernel": "vtn_normalize_kernel", "algorithmic_bytes_per_launch": alg_bytes,
+            "traffic": traffic, "traffic_source": traffic_src,
+            "kernel": "vtn_normalize_bi_kernel" if bi_layout else "vtn_normalize_kernel", "algorithmic_bytes_per_launch": alg_bytes,
             "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
         },
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms, "steps": e2e_steps},
         "gpu_launches": int(launches),
         "clocks": clocks,
     }
+    if other:
+        line["config"]["general_layout"] = other
     if args.workload == "c4":
         k_ = res.n_changed
         le = np.asarray(res.chg_le[:k_], dtype=np.int64)
@@ -972,7 +1152,7 @@ def main():
         line["config"]["left_shift_mean"] = float(le.mean()) if k_ else 0.0
     if not args.no_cpu_baseline and world >= 1 and args.workload == "c2":
         try:
-            cv, cms, P, sample = cpu_reference_run(CPU_SAMPLE_RECORDS, 2, 1)
+            cv, cms, P, sample = cpu_reference_run(CPU_SAMPLE_RECORDS, 2, 1, names, seqs, batch)
             line["cpu_baseline"] = {"value": cv, "unit": UNIT, "cores": P, "kind": "reference", "sample": sample}
         except Exception as e:  # the checker binary is missing on this box
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "unavailable: %s" % e}

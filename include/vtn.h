@@ -9,6 +9,7 @@
  *                        classify_variant (variant_manip.cpp:227-508), is_not_ref_consistent (:61-103),
  *                        is_normalized (:109-197), right_trim_or_left_extend (:513-583), left_trim (:588-615),
  *                        and the ten category counters + no_variants/no_refs (normalize.cpp:254-322)
+ *   vtn_normalize_bi     the same loop over the compact biallelic layout (vtn_batch_bi)
  *   vtn_decompose*       the allele fan-out of Igor::decompose(), decompose.cpp:210-392 / :393-957, and its
  *                        four counters (:139-143)
  *   vtn_uniq*            the record loop of Igor::uniq(), uniq.cpp:110-156, over BCFSyncedReader::read_next_position
@@ -146,6 +147,71 @@ int vtn_dbatch_create(vtn_ctx* ctx, const vtn_batch* in, vtn_dbatch** db);
 int vtn_dbatch_destroy(vtn_ctx* ctx, vtn_dbatch* db);
 int vtn_normalize_resident(vtn_ctx* ctx, vtn_dbatch* db);                       /* async on the ctx stream */
 int vtn_dbatch_fetch_result(vtn_ctx* ctx, vtn_dbatch* db, vtn_norm_result* out); /* D2H of the last run */
+
+/* ---- compact biallelic batch (the common case of `vt normalize` input: a sorted, decomposed call set) ----
+ * The same records as a vtn_batch whose records all have two alleles, in a layout that costs an SNV 8 bytes instead of 22
+ * (pos1 4 + lens 2 + its two bases), on PCIe and in HBM alike:
+ *   lens[r]     = REF length | ALT length << 8; VTN_BI_LEN_ESC (255) in either byte = an allele of 255 bases or more, whose
+ *                 lengths are in ext_len[2k], ext_len[2k+1] with ext_rec[k] == r (ext_rec ascending)
+ *   bytes       = REF then ALT of record 0, of record 1, ... (what vtn_batch::bytes holds for biallelic records)
+ *   tile_off[t] = offset in bytes of the first record of tile t (VTN_BI_TILE records); tile_off[n_tiles] = n_bytes.  The host
+ *                 knows it while it appends records; the device needs no batch-wide scan.
+ *   contig ids as RUNS: records [run_start[k], run_start[k+1]) lie on contig run_rid[k] (vtn_ref_contig_id, or -1); a sorted
+ *                 VCF has one run per contig.  run_start[0] = 0, run_start[n_run] = n_rec.
+ * Result (vtn_norm_result_bi): the changed records exactly as in vtn_norm_result; per record one byte sv[r] = VT_* bits |
+ * is_not_ref_consistent code << 6 (optional: NULL = not copied back); the rare records whose status carries more than that
+ * and is not implied by the changed list (VTN_ST_FETCH_FAIL, or VTN_ST_ENTERED without VTN_ST_CHANGED) are listed in
+ * note_rec / note_status (ascending).  status of a changed record = VTN_ST_ENTERED | VTN_ST_CHANGED | category of (lt, le, rt). */
+#define VTN_BI_TILE 128
+#define VTN_BI_LEN_ESC 255
+typedef struct vtn_batch_bi
+{
+    uint32_t n_rec;
+    uint32_t n_run;
+    uint32_t n_ext;
+    uint64_t n_bytes;          /* < 2^32 */
+    const int32_t* pos1;       /* [n_rec] */
+    const uint16_t* lens;      /* [n_rec] */
+    const uint8_t* bytes;      /* [n_bytes] */
+    const uint32_t* tile_off;  /* [ceil(n_rec / VTN_BI_TILE) + 1] */
+    const uint32_t* run_start; /* [n_run + 1] */
+    const int32_t* run_rid;    /* [n_run] */
+    const uint32_t* ext_rec;   /* [n_ext] */
+    const uint32_t* ext_len;   /* [2 * n_ext] */
+} vtn_batch_bi;
+
+typedef struct vtn_norm_result_bi
+{
+    uint8_t* sv;                /* [n_rec] or NULL */
+    uint32_t cap_changed;       /* in */
+    uint64_t cap_changed_bytes; /* in */
+    uint32_t n_changed;         /* out */
+    uint64_t n_changed_bytes;   /* out */
+    uint32_t* chg_rec;
+    int32_t* chg_pos1;
+    uint32_t* chg_lt;
+    uint32_t* chg_le;
+    uint32_t* chg_rt;
+    uint64_t* chg_off;          /* [n_changed+1] */
+    uint8_t* chg_bytes;
+    uint32_t cap_notes;         /* in */
+    uint32_t n_notes;           /* out */
+    uint32_t* note_rec;
+    uint8_t* note_status;       /* full VTN_ST_* byte of that record */
+    vtn_norm_counters counters;
+} vtn_norm_result_bi;
+
+/* Host helper: re-pack a vtn_batch whose records are all biallelic (VTN_E_ARG otherwise) into pinned host arrays owned by
+ * the returned object (what a reader that fills the compact layout directly would hold). */
+typedef struct vtn_bi_host vtn_bi_host;
+int vtn_bi_host_create(vtn_ctx* ctx, const vtn_batch* in, vtn_bi_host** h);
+const vtn_batch_bi* vtn_bi_host_view(const vtn_bi_host* h);
+int vtn_bi_host_destroy(vtn_ctx* ctx, vtn_bi_host* h);
+/* Host-buffer call, pipelined in chunks like vtn_normalize (H2D, kernels, D2H overlap); returns after completion. */
+int vtn_normalize_bi(vtn_ctx* ctx, const vtn_batch_bi* in, vtn_norm_result_bi* out);
+/* Device-resident variant: vtn_normalize_resident / vtn_dbatch_destroy work on the handle. */
+int vtn_dbatch_create_bi(vtn_ctx* ctx, const vtn_batch_bi* in, vtn_dbatch** db);
+int vtn_dbatch_fetch_result_bi(vtn_ctx* ctx, vtn_dbatch* db, vtn_norm_result_bi* out);
 
 /* ---- decompose ---- */
 /* Fan-out plan: out record k comes from input record src_rec[k] and keeps alleles {0, alt_idx[k]}

@@ -51,6 +51,19 @@ class VtnNormResult(C.Structure):
     ]
 
 
+class VtnBatchBi(C.Structure):
+    _fields_ = [("n_rec", C.c_uint32), ("n_run", C.c_uint32), ("n_ext", C.c_uint32), ("n_bytes", C.c_uint64), ("pos1", c_i32p),
+                ("lens", c_u16p), ("bytes", c_u8p), ("tile_off", c_u32p), ("run_start", c_u32p), ("run_rid", c_i32p),
+                ("ext_rec", c_u32p), ("ext_len", c_u32p)]
+
+
+class VtnNormResultBi(C.Structure):
+    _fields_ = [("sv", c_u8p), ("cap_changed", C.c_uint32), ("cap_changed_bytes", C.c_uint64), ("n_changed", C.c_uint32),
+                ("n_changed_bytes", C.c_uint64), ("chg_rec", c_u32p), ("chg_pos1", c_i32p), ("chg_lt", c_u32p), ("chg_le", c_u32p),
+                ("chg_rt", c_u32p), ("chg_off", c_u64p), ("chg_bytes", c_u8p), ("cap_notes", C.c_uint32), ("n_notes", C.c_uint32),
+                ("note_rec", c_u32p), ("note_status", c_u8p), ("counters", VtnNormCounters)]
+
+
 class VtnVcfFields(C.Structure):
     _fields_ = [("cap_rec", C.c_uint32), ("cap_allele", C.c_uint32), ("cap_bytes", C.c_uint64), ("n_rec", C.c_uint32), ("n_allele", C.c_uint32),
                 ("n_bytes", C.c_uint64), ("line_off", C.POINTER(C.c_uint64)), ("chrom_len", C.POINTER(C.c_uint32)), ("pos1", C.POINTER(C.c_int32)),
@@ -113,6 +126,12 @@ SIGNATURES = {
     "vtn_dbatch_destroy": (C.c_int, [C.c_void_p, C.c_void_p]),
     "vtn_normalize_resident": (C.c_int, [C.c_void_p, C.c_void_p]),
     "vtn_dbatch_fetch_result": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VtnNormResult)]),
+    "vtn_bi_host_create": (C.c_int, [C.c_void_p, C.POINTER(VtnBatch), C.POINTER(C.c_void_p)]),
+    "vtn_bi_host_view": (C.POINTER(VtnBatchBi), [C.c_void_p]),
+    "vtn_bi_host_destroy": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "vtn_normalize_bi": (C.c_int, [C.c_void_p, C.POINTER(VtnBatchBi), C.POINTER(VtnNormResultBi)]),
+    "vtn_dbatch_create_bi": (C.c_int, [C.c_void_p, C.POINTER(VtnBatchBi), C.POINTER(C.c_void_p)]),
+    "vtn_dbatch_fetch_result_bi": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VtnNormResultBi)]),
     "vtn_decompose_out_bound": (C.c_uint64, [C.POINTER(VtnBatch)]),
     "vtn_decompose": (C.c_int, [C.c_void_p, C.POINTER(VtnBatch), c_u32p, c_u16p, c_u64p, C.POINTER(VtnDecompCounters)]),
     "vtn_decompose_normalize": (

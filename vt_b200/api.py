@@ -113,6 +113,80 @@ class NormResult:
         return out
 
 
+class NormResultBi:
+    """Host arrays for vtn_norm_result_bi (compact biallelic layout), sized for the worst case of a batch."""
+
+    def __init__(self, n_rec, n_bytes, ctx=None, want_sv=True):
+        z = (lambda n, dt: ctx.pinned_empty(n, dt)) if ctx is not None else (lambda n, dt: np.zeros(n, dt))
+        self.sv = z(max(n_rec, 1), np.uint8) if want_sv else None
+        self.chg_rec = z(max(n_rec, 1), np.uint32)
+        self.chg_pos1 = z(max(n_rec, 1), np.int32)
+        self.chg_lt = z(max(n_rec, 1), np.uint32)
+        self.chg_le = z(max(n_rec, 1), np.uint32)
+        self.chg_rt = z(max(n_rec, 1), np.uint32)
+        self.chg_off = z(n_rec + 1, np.uint64)
+        self.chg_bytes = z(max(n_bytes, 1), np.uint8)
+        self.note_rec = z(max(n_rec, 1), np.uint32)
+        self.note_status = z(max(n_rec, 1), np.uint8)
+        self.c = L.VtnNormResultBi()
+        self.c.sv = _p(self.sv, L.c_u8p) if want_sv else None
+        self.c.cap_changed = n_rec
+        self.c.cap_changed_bytes = n_bytes
+        self.c.cap_notes = n_rec
+        self.c.chg_rec = _p(self.chg_rec, L.c_u32p)
+        self.c.chg_pos1 = _p(self.chg_pos1, L.c_i32p)
+        self.c.chg_lt = _p(self.chg_lt, L.c_u32p)
+        self.c.chg_le = _p(self.chg_le, L.c_u32p)
+        self.c.chg_rt = _p(self.chg_rt, L.c_u32p)
+        self.c.chg_off = _p(self.chg_off, L.c_u64p)
+        self.c.chg_bytes = _p(self.chg_bytes, L.c_u8p)
+        self.c.note_rec = _p(self.note_rec, L.c_u32p)
+        self.c.note_status = _p(self.note_status, L.c_u8p)
+        self.n_rec = n_rec
+
+    n_changed = property(lambda self: int(self.c.n_changed))
+    n_changed_bytes = property(lambda self: int(self.c.n_changed_bytes))
+    n_notes = property(lambda self: int(self.c.n_notes))
+    counters = NormResult.counters
+    changed_alleles = NormResult.changed_alleles
+
+    def expand(self):
+        """(status[n_rec], vtype[n_rec]) as vtn_norm_result would hold them: sv split into its two fields, the status of a
+        changed record rebuilt from (lt, le, rt) with normalize.cpp:254-311's category rule, the notes laid over."""
+        n = self.n_rec
+        sv = self.sv[:n]
+        vtype = (sv & 0x3f).astype(np.uint8)
+        status = (sv >> 6).astype(np.uint8)
+        k = self.n_changed
+        lt, le, rt = (x[:k].astype(np.int64) for x in (self.chg_lt, self.chg_le, self.chg_rt))
+        cat = np.where(le > 0, np.where(rt > le, 4, 5), np.where((lt > 0) & (rt > le), 3, np.where(lt > 0, 1, np.where(rt > le, 2, 0))))
+        status[self.chg_rec[:k]] |= (0x08 | 0x10 | (cat << 5)).astype(np.uint8)
+        m = self.n_notes
+        status[self.note_rec[:m]] = self.note_status[:m]
+        return status, vtype
+
+
+class BiBatch:
+    """A biallelic Batch re-packed into the compact layout (vtn_batch_bi) by the library's host helper; pinned memory."""
+
+    def __init__(self, ctx, batch):
+        self.ctx = ctx
+        self.n_rec, self.n_bytes = batch.n_rec, batch.n_bytes
+        self.h = C.c_void_p()
+        cb = batch.as_c()
+        ctx._chk(ctx.lib.vtn_bi_host_create(ctx.h, C.byref(cb), C.byref(self.h)), "vtn_bi_host_create")
+        self.view = ctx.lib.vtn_bi_host_view(self.h)
+        v = self.view.contents
+        self.n_run, self.n_ext = int(v.n_run), int(v.n_ext)
+        n_tiles = (self.n_rec + 127) // 128
+        self.h2d_bytes = 4 * self.n_rec + 2 * self.n_rec + self.n_bytes + 4 * (n_tiles + 1) + 8 * self.n_run + 4 + 12 * self.n_ext
+
+    def close(self):
+        if self.h:
+            self.ctx.lib.vtn_bi_host_destroy(self.ctx.h, self.h)
+            self.h = None
+
+
 class Context:
     """vtn_ctx: one GPU, its stream pair and the resident reference."""
 
@@ -178,6 +252,25 @@ class Context:
         res = result or NormResult(batch.n_rec, batch.n_bytes)
         cb = batch.as_c()
         self._chk(self.lib.vtn_normalize(self.h, C.byref(cb), C.byref(res.c)), "vtn_normalize")
+        return res
+
+    def bi_pack(self, batch):
+        return BiBatch(self, batch)
+
+    def normalize_bi(self, bi, result=None):
+        """vtn_normalize_bi through HOST buffers (compact biallelic layout)"""
+        res = result or NormResultBi(bi.n_rec, bi.n_bytes)
+        self._chk(self.lib.vtn_normalize_bi(self.h, bi.view, C.byref(res.c)), "vtn_normalize_bi")
+        return res
+
+    def upload_bi(self, bi):
+        h = C.c_void_p()
+        self._chk(self.lib.vtn_dbatch_create_bi(self.h, bi.view, C.byref(h)), "vtn_dbatch_create_bi")
+        return h
+
+    def fetch_result_bi(self, db, bi):
+        res = NormResultBi(bi.n_rec, bi.n_bytes)
+        self._chk(self.lib.vtn_dbatch_fetch_result_bi(self.h, db, C.byref(res.c)), "vtn_dbatch_fetch_result_bi")
         return res
 
     def decompose(self, batch, normalize=False):

@@ -34,6 +34,11 @@ int vtn_ctx_create(vtn_ctx** out, int device)
         long v = atol(e);
         if (v >= 128) ctx->chunk_rec = (uint32_t)(v / 128) * 128u;
     }
+    if (const char* e = getenv("VTN_L2_FETCH")) // L2 fetch granularity in bytes (32 / 64 / 128): the reference gathers touch one or two 16-byte groups
+    {
+        long v = atol(e);
+        if (v == 32 || v == 64 || v == 128) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)v);
+    }
     VTN_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     VTN_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
     VTN_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream3, cudaStreamNonBlocking));
@@ -49,6 +54,7 @@ int vtn_ctx_destroy(vtn_ctx* ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->scratch) vtn_dbatch_destroy(ctx, ctx->scratch);
+    if (ctx->scratch_bi) vtn_dbatch_destroy(ctx, ctx->scratch_bi);
     vtn_hmm_ctx_release(ctx);
     cudaFree(ctx->d_groups);
     cudaFree(ctx->d_contig_goff);
@@ -194,6 +200,8 @@ int vtn_dbatch_destroy(vtn_ctx* ctx, vtn_dbatch* d)
     cudaFree(d->chg_le); cudaFree(d->chg_rt); cudaFree(d->chg_off); cudaFree(d->chg_bytes); cudaFree(d->totals);
     cudaFree(d->scr.q0); cudaFree(d->scr.q1); cudaFree(d->scr.bytes); cudaFree(d->scr.dir); cudaFree(d->scr.blo);
     cudaFree(d->counters); cudaFree(d->tile_state); cudaFree(d->tile_counter); cudaFree(d->src_rec); cudaFree(d->alt_idx);
+    cudaFree(d->lens); cudaFree(d->tile_off); cudaFree(d->run_start); cudaFree(d->run_rid); cudaFree(d->ext_rec); cudaFree(d->ext_len);
+    cudaFree(d->note_rec); cudaFree(d->note_status); cudaFree(d->note_count);
     delete d;
     return VTN_OK;
 }
@@ -238,6 +246,7 @@ int vtn_normalize_resident(vtn_ctx* ctx, vtn_dbatch* d)
 {
     if (!ctx || !d) return VTN_E_ARG;
     if (!ctx->ref_loaded) return vtn_set_err(ctx, VTN_E_STATE, "vtn_normalize: no reference loaded");
+    if (d->lens) return vtn_normalize_resident_bi(ctx, d);
     VtnDevBatchView v{d->n_rec, 0u, d->pos1, d->rid, d->allele_beg, d->allele_off, d->bytes};
     VtnDevNormOut o{d->status, d->vtype, d->chg_rec, d->chg_pos1, d->chg_lt, d->chg_le, d->chg_rt, d->chg_off, d->chg_bytes, d->totals, d->counters};
     return vtn_launch_normalize(ctx, v, o, d->scr, d->tile_state, d->tile_counter, d->n_tiles);

@@ -47,6 +47,32 @@ struct VtnDevBatchView
     const uint8_t* bytes;
 };
 
+// device-side view of a compact biallelic batch (vtn_batch_bi); chunked launches pass offset views: pos1 / lens / tile_off
+// are relative to the chunk, bytes / run_* / ext_* absolute (rec_base = first record of the chunk)
+struct VtnDevBiView
+{
+    uint32_t n_rec;
+    uint32_t rec_base;
+    const int32_t* pos1;
+    const uint16_t* lens;
+    const uint8_t* bytes;
+    const uint32_t* tile_off;
+    const uint32_t* run_start;
+    const int32_t* run_rid;
+    uint32_t n_run;
+    const uint32_t* ext_rec;
+    const uint32_t* ext_len;
+    uint32_t n_ext;
+};
+
+struct VtnDevNotes
+{
+    uint32_t* rec;     // absolute record index
+    uint8_t* status;
+    uint32_t* count;
+    uint32_t cap;
+};
+
 struct VtnDevNormOut
 {
     uint8_t* status;
@@ -111,6 +137,17 @@ struct vtn_dbatch
     uint64_t out_bound = 0;    // sum(max(n_allele-1,1))
     struct vtn_dbatch* fused = nullptr; // biallelic batch materialised on device for the fused path
     bool owns_inputs = true;
+    // compact biallelic layout (vtn_batch_bi): lens != nullptr; status doubles as sv, vtype / rid / allele_* stay null
+    uint16_t* lens = nullptr;
+    uint32_t* tile_off = nullptr;
+    uint32_t* run_start = nullptr;
+    int32_t* run_rid = nullptr;
+    uint32_t* ext_rec = nullptr;
+    uint32_t* ext_len = nullptr;
+    uint32_t n_run = 0, n_ext = 0, cap_run = 0, cap_ext = 0;
+    uint32_t* note_rec = nullptr;
+    uint8_t* note_status = nullptr;
+    uint32_t* note_count = nullptr;
     vtn_uniq_buffers* uniq = nullptr; // order / first / heap scratch of vtn_uniq_resident (allocated on first use)
     vtn_order_buffers* order = nullptr; // arena of vtn_writer_order_resident (allocated on first use)
     vtn_blocksub_buffers* blocksub = nullptr; // plan buffers of vtn_blocksub_resident (allocated on first use)
@@ -142,6 +179,7 @@ struct vtn_ctx
     bool ref_loaded = false;
     // reusable device arena for the host-buffer call
     vtn_dbatch* scratch = nullptr;
+    vtn_dbatch* scratch_bi = nullptr; // the same for vtn_normalize_bi
     uint32_t scratch_rec = 0, scratch_allele = 0;
     uint64_t scratch_bytes = 0;
     // HMM family (vtn_hmm.cu): per-warp DP scratch (band boundary rows, back-pointers, reversed path) + work counter
@@ -166,6 +204,9 @@ int vtn_set_err(vtn_ctx* ctx, int code, const std::string& msg);
 // kernels' host launchers (vtn_normalize.cu / vtn_decompose.cu)
 int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNormOut& out, const VtnDevScratch& scr,
                          unsigned long long* tile_state, uint32_t* tile_counter, uint32_t n_tiles, bool accumulate = false);
+int vtn_launch_normalize_bi(vtn_ctx* ctx, const VtnDevBiView& in, const VtnDevNormOut& out, const VtnDevNotes& notes, const VtnDevScratch& scr,
+                            unsigned long long* tile_state, uint32_t* tile_counter, uint32_t n_tiles, bool accumulate = false);
+int vtn_normalize_resident_bi(vtn_ctx* ctx, vtn_dbatch* d);
 uint32_t vtn_normalize_tile_records();
 size_t vtn_normalize_ctl_words(uint32_t n_tiles); // 64-bit words behind vtn_dbatch::tile_counter
 int vtn_launch_decompose(vtn_ctx* ctx, vtn_dbatch* db, bool materialise);

@@ -549,12 +549,12 @@ __device__ __forceinline__ bool fast_biallelic16(const VtnDevRef& R, const uint8
 // The whole per-record computation except writing the new alleles.
 __device__ __noinline__ void normalize_record(const VtnDevRef& R, const VtnDevBatchView& B, uint32_t r, RecResult& out)
 {
-    const uint32_t ab = __ldg(B.allele_beg + r);
-    const uint32_t n = __ldg(B.allele_beg + r + 1) - ab;
-    const int32_t pos1 = __ldg(B.pos1 + r);
-    const int32_t rid = __ldg(B.rid + r);
-    const uint32_t off0 = __ldg(B.allele_off + ab);
-    const uint32_t off1 = __ldg(B.allele_off + ab + 1);
+    const uint32_t ab = B.allele_beg[r];
+    const uint32_t n = B.allele_beg[r + 1] - ab;
+    const int32_t pos1 = B.pos1[r];
+    const int32_t rid = B.rid[r];
+    const uint32_t off0 = B.allele_off[ab];
+    const uint32_t off1 = B.allele_off[ab + 1];
     const uint8_t* a0 = B.bytes + off0;
     const uint32_t len0 = off1 - off0;
     out.T = out.le = out.lt = out.nbytes = 0;
@@ -562,7 +562,7 @@ __device__ __noinline__ void normalize_record(const VtnDevRef& R, const VtnDevBa
     // ---- SNV fast path: biallelic, both alleles one byte ----
     if (n == 2)
     {
-        const uint32_t off2 = __ldg(B.allele_off + ab + 2);
+        const uint32_t off2 = B.allele_off[ab + 2];
         if (len0 == 1 && off2 - off1 == 1)
         {
             uint8_t r0 = a0[0], c = a0[1];
@@ -583,7 +583,7 @@ __device__ __noinline__ void normalize_record(const VtnDevRef& R, const VtnDevBa
         uint32_t o = off1;
         for (uint32_t i = 1; i < n; ++i)
         {
-            uint32_t o2 = __ldg(B.allele_off + ab + i + 1);
+            uint32_t o2 = B.allele_off[ab + i + 1];
             uint32_t l = o2 - o;
             vtype |= classify_alt(a0, len0, B.bytes + o, l, homog);
             m = l < m ? l : m;
@@ -620,7 +620,7 @@ __device__ __noinline__ void normalize_record(const VtnDevRef& R, const VtnDevBa
         uint32_t o = off1;
         for (uint32_t i = 1; i < n; ++i)
         {
-            uint32_t o2 = __ldg(B.allele_off + ab + i + 1);
+            uint32_t o2 = B.allele_off[ab + i + 1];
             uint32_t l = o2 - o;
             const uint8_t* a = B.bytes + o;
             exists_one |= (l == 1);
@@ -659,7 +659,7 @@ __device__ __noinline__ void normalize_record(const VtnDevRef& R, const VtnDevBa
         uint32_t o = off1;
         for (uint32_t i = 1; i < n; ++i)
         {
-            uint32_t o2 = __ldg(B.allele_off + ab + i + 1);
+            uint32_t o2 = B.allele_off[ab + i + 1];
             uint8_t c = ext_byte(R, cur, gbase, clen, pos1, B.bytes + o, o2 - o, T);
             if (c != c0) { stop = true; break; }
             o = o2;
@@ -671,7 +671,7 @@ __device__ __noinline__ void normalize_record(const VtnDevRef& R, const VtnDevBa
     {
         if (n == 2)
         {
-            const uint32_t len1 = __ldg(B.allele_off + ab + 2) - off1;
+            const uint32_t len1 = B.allele_off[ab + 2] - off1;
             T = lag_scan(R, gbase, clen, pos1, len0, len1, T, cap);
         }
         else
@@ -683,7 +683,7 @@ __device__ __noinline__ void normalize_record(const VtnDevRef& R, const VtnDevBa
                 bool mism = false;
                 for (uint32_t i = 1; i < n; ++i)
                 {
-                    uint32_t o2 = __ldg(B.allele_off + ab + i + 1);
+                    uint32_t o2 = B.allele_off[ab + i + 1];
                     uint8_t c = ext_byte(R, cur, gbase, clen, pos1, B.bytes + o, o2 - o, T);
                     if (c != c0) { mism = true; break; }
                     o = o2;
@@ -707,7 +707,7 @@ __device__ __noinline__ void normalize_record(const VtnDevRef& R, const VtnDevBa
             for (uint32_t i = 1; i < n; ++i)
             {
                 if (vtn_toupper(B.bytes[o + lt]) != c0) { mism = true; break; }
-                o = __ldg(B.allele_off + ab + i + 1);
+                o = B.allele_off[ab + i + 1];
             }
             if (mism) break;
             ++lt;
@@ -726,7 +726,7 @@ __device__ __noinline__ void normalize_record(const VtnDevRef& R, const VtnDevBa
         else if (T > le) cat = 2;
         st |= cat << VTN_ST_CAT_SHIFT;
         // sum of new lengths = sum(len_i) - n*(T - le + lt)
-        const uint32_t total = __ldg(B.allele_off + ab + n) - off0;
+        const uint32_t total = B.allele_off[ab + n] - off0;
         out.nbytes = total + n * le - n * T - n * lt;
     }
     out.status = (uint8_t)st;
@@ -799,17 +799,17 @@ __device__ __forceinline__ uint32_t warp_excl_scan(uint32_t v, int lane, uint32_
 __device__ __noinline__ void write_generic_alleles(const VtnDevRef& R, const VtnDevBatchView& B, uint32_t rr, uint32_t T, uint32_t le,
                                       uint32_t lt, uint8_t* dst)
 {
-    const uint32_t ab2 = __ldg(B.allele_beg + rr);
-    const uint32_t n2 = __ldg(B.allele_beg + rr + 1) - ab2;
-    const int32_t pos1 = __ldg(B.pos1 + rr);
-    const int32_t rid = __ldg(B.rid + rr);
+    const uint32_t ab2 = B.allele_beg[rr];
+    const uint32_t n2 = B.allele_beg[rr + 1] - ab2;
+    const int32_t pos1 = B.pos1[rr];
+    const int32_t rid = B.rid[rr];
     const uint64_t gbase = __ldg(R.contig_goff + rid) << 5;
     const int64_t clen = __ldg(R.contig_len + rid);
     VtnRefCursor cur;
-    uint32_t o = __ldg(B.allele_off + ab2);
+    uint32_t o = B.allele_off[ab2];
     for (uint32_t ai = 0; ai < n2; ++ai)
     {
-        const uint32_t o2 = __ldg(B.allele_off + ab2 + ai + 1);
+        const uint32_t o2 = B.allele_off[ab2 + ai + 1];
         const uint32_t len = o2 - o;
         const uint32_t newlen = len + le - T - lt;
         const uint8_t* a = B.bytes + o;
@@ -1282,6 +1282,411 @@ __global__ void __launch_bounds__(VTC_THREADS, 2) vtn_compact_kernel(VtnDevBatch
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// K1 for the compact biallelic layout (vtn_batch_bi): the same tile scheme and the same per-record code (fast_biallelic16 /
+// fast_biallelic / normalize_record) as vtn_normalize_kernel, with a front end that reads 6 header bytes per record instead
+// of 20: lens as one 8-byte load per lane, the tile's byte offsets by a warp scan from tile_off[tile], contig ids from the
+// run table (one binary search per tile).  Per record it leaves ONE byte (VT_* bits | REF-check code << 6); statuses that the
+// changed list does not imply go to the notes list.  The scratch / tile-directory contract towards K2 is unchanged.
+// FAST_ONLY as above: a tile with an escape length, more bytes than the staging window, or a record the register path
+// refuses is appended to defer_list and redone by the <false> launch, which lays a small vtn_batch view of the tile
+// (allele_beg / allele_off / rid in shared memory) under normalize_record.
+// ---------------------------------------------------------------------------------------------------------
+#define VTB_BYTES_CAP (VTN_WTILE * 8 + 64)
+#ifndef VTB_MIN_BLOCKS_FAST
+#define VTB_MIN_BLOCKS_FAST 8
+#endif
+
+struct __align__(16) BiWarpSmem
+{
+    uint8_t bytes[VTB_BYTES_CAP];
+    int32_t pos1[VTN_WTILE];
+    uint32_t queue[VTN_WTILE]; // record index in the tile | REF length << 8 | ALT length << 16 (lengths < 255 on the fast launch)
+    uint16_t qoff[VTN_WTILE];  // byte offset of the queued record inside the tile (fast launch: tile bytes <= VTB_BYTES_CAP)
+    uint8_t sv[VTN_WTILE];
+};
+struct BiWarpGen // the generic launch's view of one tile as a vtn_batch
+{
+    uint32_t ao[2 * VTN_WTILE + 1];
+    uint32_t ab[VTN_WTILE + 1];
+    int32_t rid[VTN_WTILE];
+};
+
+__device__ __forceinline__ void vtn_note(const VtnDevNotes& N, uint32_t rec, uint32_t st)
+{
+    const uint32_t k = atomicAdd(N.count, 1u);
+    if (k < N.cap)
+    {
+        N.rec[k] = rec;
+        N.status[k] = (uint8_t)st;
+    }
+}
+
+template <bool FAST_ONLY>
+__global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTB_MIN_BLOCKS_FAST : VTN_MIN_BLOCKS) vtn_normalize_bi_kernel(
+    VtnDevRef R, VtnDevBiView B, VtnDevNormOut O, VtnDevNotes NT, VtnDevScratch X, uint32_t* defer_list, uint32_t* defer_count,
+    uint32_t n_tiles_all, unsigned long long* k2_ctl, uint32_t tpb, int fresh)
+{
+    __shared__ BiWarpSmem SM[VTN_WARPS];
+    __shared__ BiWarpGen GM[FAST_ONLY ? 1 : VTN_WARPS];
+    __shared__ uint32_t s_lut[256];
+    __shared__ uint64_t s_gbase[VTN_CONTIG_CAP];
+    __shared__ int64_t s_clen[VTN_CONTIG_CAP];
+    const int lane = threadIdx.x & 31;
+    if (!FAST_ONLY && *defer_count == 0) return;
+    BiWarpSmem& S = SM[threadIdx.x >> 5];
+    BiWarpGen& G = GM[FAST_ONLY ? 0 : (threadIdx.x >> 5)];
+    uint32_t my_counter = 0;
+    const uint32_t cat_shift = 6u * (uint32_t)(lane < 5 ? lane : 0);
+    if (FAST_ONLY && blockIdx.x == 0)
+    {
+        if (threadIdx.x < 2) k2_ctl[VTC_CTL_BASE + threadIdx.x] = fresh ? 0ull : O.totals[threadIdx.x];
+    }
+    for (int v = threadIdx.x; v < 256; v += blockDim.x)
+    {
+        uint32_t w = 0;
+        for (int q = 0; q < 4; ++q) w |= ((0x47544341u >> (8 * ((v >> (2 * q)) & 3))) & 0xffu) << (8 * q);
+        s_lut[v] = w;
+    }
+    const bool contigs_staged = R.n_contig <= VTN_CONTIG_CAP;
+    if (contigs_staged)
+        for (int c = threadIdx.x; c < R.n_contig; c += blockDim.x)
+        {
+            s_gbase[c] = __ldg(R.contig_goff + c) << 5;
+            s_clen[c] = __ldg(R.contig_len + c);
+        }
+    if (!FAST_ONLY)
+        for (int i = lane; i <= VTN_WTILE; i += 32) G.ab[i] = 2u * (uint32_t)i;
+    __syncthreads();
+
+    const uint32_t n_tiles = FAST_ONLY ? n_tiles_all : min(*defer_count, n_tiles_all);
+    const uint32_t tile_stride = gridDim.x * VTN_WARPS;
+    uint32_t ti = blockIdx.x * VTN_WARPS + (threadIdx.x >> 5);
+#define TILE_OF(i) (FAST_ONLY ? (i) : __ldg(defer_list + (i)))
+    uint32_t tile = ti < n_tiles ? TILE_OF(ti) : 0;
+    uint2 h_len = make_uint2(0, 0);
+    int4 h_pos = make_int4(0, 0, 0, 0);
+    uint32_t h_blo = 0;
+    uint32_t run_k = 0, run_lo = 1, run_next = 0; // empty interval: the first tile searches
+    if (ti < n_tiles)
+    {
+        const uint32_t r0 = tile * VTN_WTILE;
+        h_len = __ldg(reinterpret_cast<const uint2*>(B.lens + r0) + lane); // arrays are padded
+        h_pos = __ldg(reinterpret_cast<const int4*>(B.pos1 + r0) + lane);
+        h_blo = __ldg(B.tile_off + tile);
+    }
+    while (ti < n_tiles)
+    {
+        const uint32_t next_ti = ti + tile_stride;
+        const uint32_t next_tile = next_ti < n_tiles ? TILE_OF(next_ti) : 0;
+        const uint32_t r0 = tile * VTN_WTILE;
+        const uint32_t n_live = min((uint32_t)VTN_WTILE, B.n_rec - r0);
+        const uint32_t abs0 = B.rec_base + r0;
+        const uint32_t b_lo = h_blo;
+        // ---------------- phase 1 ----------------
+        uint32_t l0[VTN_RPL], l1[VTN_RPL];
+        {
+            const uint32_t w[2] = {h_len.x, h_len.y};
+#pragma unroll
+            for (int j = 0; j < VTN_RPL; ++j)
+            {
+                const uint32_t x = (w[j >> 1] >> (16 * (j & 1))) & 0xffffu;
+                const bool live = (uint32_t)(lane * VTN_RPL + j) < n_live;
+                l0[j] = live ? (x & 0xffu) : 0u;
+                l1[j] = live ? (x >> 8) : 0u;
+            }
+            reinterpret_cast<int4*>(S.pos1)[lane] = h_pos;
+        }
+        if (next_ti < n_tiles)
+        {
+            const uint32_t r1 = next_tile * VTN_WTILE;
+            h_len = __ldg(reinterpret_cast<const uint2*>(B.lens + r1) + lane);
+            h_pos = __ldg(reinterpret_cast<const int4*>(B.pos1 + r1) + lane);
+            h_blo = __ldg(B.tile_off + next_tile);
+        }
+        bool esc = false;
+#pragma unroll
+        for (int j = 0; j < VTN_RPL; ++j) esc |= (l0[j] == VTN_BI_LEN_ESC) | (l1[j] == VTN_BI_LEN_ESC);
+        bool deferred = false;
+        if (FAST_ONLY)
+            deferred = __any_sync(0xffffffffu, esc);
+        else if (esc)
+        {
+#pragma unroll
+            for (int j = 0; j < VTN_RPL; ++j)
+                if (l0[j] == VTN_BI_LEN_ESC || l1[j] == VTN_BI_LEN_ESC)
+                {
+                    const uint32_t ar = abs0 + lane * VTN_RPL + j;
+                    uint32_t lo = 0, hi = B.n_ext; // first ext_rec >= ar
+                    while (lo < hi)
+                    {
+                        const uint32_t mid = (lo + hi) >> 1;
+                        if (__ldg(B.ext_rec + mid) < ar) lo = mid + 1;
+                        else hi = mid;
+                    }
+                    if (lo < B.n_ext && __ldg(B.ext_rec + lo) == ar)
+                    {
+                        l0[j] = __ldg(B.ext_len + 2 * lo);
+                        l1[j] = __ldg(B.ext_len + 2 * lo + 1);
+                    }
+                }
+        }
+        uint32_t tile_bytes = 0;
+        uint32_t o[VTN_RPL]; // byte offset of my records inside the tile
+        {
+            uint32_t tot = 0;
+#pragma unroll
+            for (int j = 0; j < VTN_RPL; ++j) tot += l0[j] + l1[j];
+            uint32_t e = warp_excl_scan(tot, lane, tile_bytes);
+#pragma unroll
+            for (int j = 0; j < VTN_RPL; ++j)
+            {
+                o[j] = e;
+                e += l0[j] + l1[j];
+            }
+        }
+        const uint32_t b0 = b_lo & ~15u;
+        const bool bytes_staged = (b_lo - b0) + tile_bytes + 16 <= VTB_BYTES_CAP;
+        if (FAST_ONLY && !bytes_staged) deferred = true;
+        if (FAST_ONLY && deferred)
+        {
+            if (lane == 0) defer_list[atomicAdd(defer_count, 1u)] = tile;
+            __syncwarp();
+            ti = next_ti;
+            tile = next_tile;
+            continue;
+        }
+        if (bytes_staged)
+        {
+            for (uint32_t i = lane * 16; i < (b_lo - b0) + tile_bytes + 16; i += 512)
+                *reinterpret_cast<uint4*>(&S.bytes[i]) = __ldg(reinterpret_cast<const uint4*>(B.bytes + b0 + i));
+        }
+        // contig run of the tile's first record: last k with run_start[k] <= abs0 (uniform over the warp).  A warp's tiles
+        // ascend, so the run of its previous tile is tried first
+        if (abs0 < run_lo || abs0 >= run_next)
+        {
+            uint32_t lo = 0, hi = B.n_run - 1;
+            while (lo < hi)
+            {
+                const uint32_t mid = (lo + hi + 1) >> 1;
+                if (__ldg(B.run_start + mid) <= abs0) lo = mid;
+                else hi = mid - 1;
+            }
+            run_k = lo;
+            run_lo = __ldg(B.run_start + run_k);
+            run_next = __ldg(B.run_start + run_k + 1);
+        }
+        __syncwarp();
+        // absolute offsets work on both; the fast launch always stages, which keeps its loads in the shared window (LDS)
+        const uint8_t* BY = FAST_ONLY ? (S.bytes - b0) : (bytes_staged ? (S.bytes - b0) : B.bytes);
+
+        uint32_t qmask = 0;
+#pragma unroll
+        for (int j = 0; j < VTN_RPL; ++j)
+        {
+            const uint32_t idx = lane * VTN_RPL + j;
+            if (idx < n_live)
+            {
+                bool q = true;
+                if (l0[j] == 1 && l1[j] == 1)
+                {
+                    const uint8_t r0b = BY[b_lo + o[j]], c = BY[b_lo + o[j] + 1];
+                    q = (c == '<' || c == '[' || c == ']' || c == '.' || c == r0b);
+                }
+                if (q) qmask |= 1u << j;
+                if (!FAST_ONLY)
+                {
+                    G.ao[2 * idx] = b_lo + o[j];
+                    G.ao[2 * idx + 1] = b_lo + o[j] + l0[j];
+                    uint32_t k = run_k;
+                    if (abs0 + idx >= run_next)
+                        while (k + 1 < B.n_run && __ldg(B.run_start + k + 1) <= abs0 + idx) ++k;
+                    G.rid[idx] = __ldg(B.run_rid + k);
+                }
+            }
+        }
+        if (!FAST_ONLY && lane == 0) G.ao[2 * n_live] = b_lo + tile_bytes;
+        uint32_t nq;
+        {
+            uint32_t slot = warp_excl_scan(__popc(qmask), lane, nq);
+#pragma unroll
+            for (int j = 0; j < VTN_RPL; ++j)
+                if (qmask & (1u << j))
+                {
+                    S.queue[slot] = (uint32_t)(lane * VTN_RPL + j) | (FAST_ONLY ? ((l0[j] << 8) | (l1[j] << 16)) : 0u);
+                    S.qoff[slot] = (uint16_t)o[j];
+                    ++slot;
+                }
+        }
+        __syncwarp();
+
+        // ---------------- phase 2: dense passes over the queue ----------------
+        uint32_t tot_c = 0, tot_b = 0;
+        uint32_t cnt_vars = n_live - nq; // the SNVs settled in phase 1 (normalize.cpp:315-322)
+        uint32_t cnt_refs = 0;
+        uint32_t tile_cat = 0; // lane k < 5: category counter k of THIS tile (committed only if the tile is kept)
+        for (uint32_t p = 0; p < nq; p += 32)
+        {
+            const uint32_t e = p + lane;
+            const bool act = e < nq;
+            uint32_t st = 0, vt = VTN_VT_SNP, T = 0, le = 0, lt = 0, nb = 0, rr = 0;
+            int32_t pos1 = 0;
+            bool fast = false, elig = false;
+            VtnFastRes f;
+            uint32_t o0 = 0, ql0 = 0, ql1 = 0, idx = 0;
+            int64_t clen = 0;
+            uint64_t gbase = 0;
+            if (act)
+            {
+                const uint32_t qe = S.queue[e];
+                idx = qe & 0xffu;
+                rr = r0 + idx;
+                pos1 = S.pos1[idx];
+                int32_t rid;
+                if (FAST_ONLY)
+                {
+                    ql0 = (qe >> 8) & 0xffu;
+                    ql1 = (qe >> 16) & 0xffu;
+                    o0 = b_lo + S.qoff[e];
+                    uint32_t k = run_k;
+                    if (abs0 + idx >= run_next)
+                        while (k + 1 < B.n_run && __ldg(B.run_start + k + 1) <= abs0 + idx) ++k;
+                    rid = __ldg(B.run_rid + k);
+                }
+                else
+                {
+                    o0 = G.ao[2 * idx];
+                    ql0 = G.ao[2 * idx + 1] - o0;
+                    ql1 = G.ao[2 * idx + 2] - G.ao[2 * idx + 1];
+                    rid = G.rid[idx];
+                }
+                if (rid >= 0 && rid < R.n_contig)
+                {
+                    elig = true;
+                    clen = contigs_staged ? s_clen[rid] : __ldg(R.contig_len + rid);
+                    gbase = contigs_staged ? s_gbase[rid] : (__ldg(R.contig_goff + rid) << 5);
+                }
+            }
+            const bool use16 = __all_sync(0xffffffffu, !elig || (ql0 - 1u < 16u && ql1 - 1u < 16u));
+            if (act)
+            {
+                if (elig)
+                    fast = use16 ? fast_biallelic16(R, BY, o0, ql0, ql1, pos1, clen, gbase, f) : fast_biallelic(R, BY, o0, ql0, ql1, pos1, clen, gbase, f);
+                if (fast)
+                {
+                    st = f.status; vt = f.vtype; T = f.T; le = f.le; lt = f.lt; nb = f.nlr + f.nla;
+                }
+                else if (!FAST_ONLY)
+                {
+                    VtnDevBatchView V{n_live, 0u, B.pos1 + r0, G.rid, G.ab, G.ao, B.bytes};
+                    RecResult res;
+                    normalize_record(R, V, idx, res);
+                    st = res.status; vt = res.vtype; T = res.T; le = res.le; lt = res.lt; nb = res.nbytes;
+                }
+                S.sv[idx] = (uint8_t)(vt | ((st & VTN_ST_REFCODE_MASK) << 6));
+            }
+            if (FAST_ONLY && __any_sync(0xffffffffu, act && !fast))
+            {
+                deferred = true;
+                break;
+            }
+            if (act && ((st & VTN_ST_FETCH_FAIL) || ((st & VTN_ST_ENTERED) && !(st & VTN_ST_CHANGED)))) vtn_note(NT, abs0 + idx, st);
+            const uint32_t c = (st & VTN_ST_CHANGED) ? 1u : 0u;
+            uint32_t pc, pb;
+            const unsigned cmask = __ballot_sync(0xffffffffu, c);
+            const uint32_t ec = __popc(cmask & ((1u << lane) - 1u));
+            pc = __popc(cmask);
+            const uint32_t eb = warp_excl_scan(c ? nb : 0u, lane, pb);
+            if (c)
+            {
+                const uint32_t k = r0 + tot_c + ec;
+                const uint32_t obl = tot_b + eb;
+                const uint32_t ntot = fast ? f.nlr + f.nla : 0u;
+                const bool coded = fast && ntot <= 32u;
+                uint64_t lo = f.newR, hi = 0;
+                if (fast)
+                {
+                    if (f.nlr >= 32)
+                        hi = f.newA;
+                    else
+                    {
+                        lo |= f.newA << (2 * f.nlr);
+                        hi = f.nlr ? (f.newA >> (64 - 2 * f.nlr)) : 0;
+                    }
+                }
+                X.q0[k] = make_uint4(B.rec_base + rr, (uint32_t)(pos1 - (int32_t)le + (int32_t)lt), lt, le);
+                X.q1[k] = make_uint4(T, obl | (coded ? 0x80000000u : 0u), (uint32_t)lo, (uint32_t)(lo >> 32));
+                uint8_t* dst = X.bytes + b_lo + obl;
+                if (fast && !coded)
+                {
+                    for (uint32_t j = 0; j < ntot; j += 4)
+                    {
+                        const uint32_t w = s_lut[(uint32_t)lo & 0xffu];
+                        dst[j] = (uint8_t)w;
+                        if (j + 1 < ntot) dst[j + 1] = (uint8_t)(w >> 8);
+                        if (j + 2 < ntot) dst[j + 2] = (uint8_t)(w >> 16);
+                        if (j + 3 < ntot) dst[j + 3] = (uint8_t)(w >> 24);
+                        lo = (lo >> 8) | (hi << 56);
+                        hi >>= 8;
+                    }
+                }
+                else if (!FAST_ONLY)
+                {
+                    VtnDevBatchView V{n_live, 0u, B.pos1 + r0, G.rid, G.ab, G.ao, B.bytes};
+                    write_generic_alleles(R, V, idx, T, le, lt, dst);
+                }
+            }
+            tot_c += pc;
+            tot_b += pb;
+            const uint32_t cat = c ? (st >> VTN_ST_CAT_SHIFT) : 0u;
+            const uint32_t fld = cat ? (1u << (6u * (cat - 1u))) : 0u;
+            const uint32_t r_bi = __reduce_add_sync(0xffffffffu, fld);
+            const uint32_t r_rv = __reduce_add_sync(0xffffffffu, act ? (vt == VTN_VT_REF ? 1u : 0x100u) : 0u);
+            if (lane < 5) tile_cat += (r_bi >> cat_shift) & 63u;
+            cnt_refs += r_rv & 0xffu;
+            cnt_vars += r_rv >> 8;
+        }
+        if (deferred)
+        {
+            if (lane == 0) defer_list[atomicAdd(defer_count, 1u)] = tile;
+            __syncwarp();
+            ti = next_ti;
+            tile = next_tile;
+            continue;
+        }
+        my_counter += tile_cat;
+        if (lane == 10) my_counter += cnt_vars;
+        if (lane == 11) my_counter += cnt_refs;
+        if (lane == 0)
+        {
+            X.dir[tile] = ((unsigned long long)tot_c << 32) | tot_b;
+            X.blo[tile] = b_lo;
+            if (tot_c) atomicAdd(k2_ctl + VTC_CTL_AGG + tile / tpb, ((unsigned long long)tot_c << VTC_AGG_SHIFT) | tot_b);
+        }
+        __syncwarp();
+
+        // ---------------- phase 3: one byte per record, four per lane ----------------
+        {
+            uint8_t sv[VTN_RPL];
+#pragma unroll
+            for (int j = 0; j < VTN_RPL; ++j) sv[j] = (qmask & (1u << j)) ? S.sv[lane * VTN_RPL + j] : (uint8_t)VTN_VT_SNP;
+            if (lane * VTN_RPL + VTN_RPL <= n_live)
+                reinterpret_cast<uchar4*>(O.status + r0)[lane] = make_uchar4(sv[0], sv[1], sv[2], sv[3]);
+            else
+            {
+#pragma unroll
+                for (int j = 0; j < VTN_RPL; ++j)
+                    if (lane * VTN_RPL + j < n_live) O.status[r0 + lane * VTN_RPL + j] = sv[j];
+            }
+        }
+        __syncwarp();
+        ti = next_ti;
+        tile = next_tile;
+    }
+#undef TILE_OF
+    if (lane < 12 && my_counter) atomicAdd(O.counters + lane, my_counter);
+}
+
 } // namespace
 
 uint32_t vtn_normalize_tile_records() { return VTN_WTILE; }
@@ -1333,6 +1738,52 @@ int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNo
     vtn_normalize_kernel<false><<<grid2, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, scr, defer_list, tile_counter, n_tiles, ctl, tpb, 0);
     VTN_CUDA(ctx, cudaGetLastError());
     vtn_compact_kernel<<<n_blocks2, VTC_THREADS, 0, s>>>(in, scr, out, n_tiles, ctl, n_blocks2, tpb);
+    VTN_CUDA(ctx, cudaGetLastError());
+    ctx->launches += 3;
+    return VTN_OK;
+}
+
+int vtn_launch_normalize_bi(vtn_ctx* ctx, const VtnDevBiView& in, const VtnDevNormOut& out, const VtnDevNotes& notes, const VtnDevScratch& scr,
+                            unsigned long long* tile_state, uint32_t* tile_counter, uint32_t n_tiles, bool accumulate)
+{
+    cudaStream_t s = ctx->stream;
+    if (!accumulate)
+    {
+        VTN_CUDA(ctx, cudaMemsetAsync(out.counters, 0, 12 * sizeof(uint32_t), s));
+        VTN_CUDA(ctx, cudaMemsetAsync(notes.count, 0, sizeof(uint32_t), s));
+        if (n_tiles == 0)
+        {
+            VTN_CUDA(ctx, cudaMemsetAsync(out.totals, 0, 2 * sizeof(unsigned long long), s));
+            VTN_CUDA(ctx, cudaMemsetAsync(out.chg_off, 0, sizeof(uint64_t), s));
+        }
+    }
+    if (n_tiles == 0) return VTN_OK;
+    uint32_t tpb = (n_tiles + 2 * (uint32_t)ctx->sm_count - 1) / (2 * (uint32_t)ctx->sm_count);
+    tpb = (tpb + 31) & ~31u;
+    if (tpb < 32) tpb = 32;
+    if (tpb > VTC_TPB) tpb = VTC_TPB;
+    const uint32_t n_blocks2 = (n_tiles + tpb - 1) / tpb;
+    unsigned long long* ctl = reinterpret_cast<unsigned long long*>(tile_counter);
+    VTN_CUDA(ctx, cudaMemsetAsync(ctl, 0, (VTC_CTL_AGG + (size_t)n_blocks2) * sizeof(unsigned long long), s));
+    static int per_sm = 0, per_sm_slow = 0;
+    if (!per_sm)
+    {
+        VTN_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vtn_normalize_bi_kernel<true>, 32 * VTN_WARPS, 0));
+        VTN_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_slow, vtn_normalize_bi_kernel<false>, 32 * VTN_WARPS, 0));
+        if (per_sm < 1) per_sm = 1;
+        if (per_sm_slow < 1) per_sm_slow = 1;
+    }
+    uint32_t grid = (uint32_t)(ctx->sm_count * per_sm);
+    const uint32_t need = (n_tiles + VTN_WARPS - 1) / VTN_WARPS;
+    if (grid > need) grid = need;
+    uint32_t* defer_list = reinterpret_cast<uint32_t*>(tile_state);
+    vtn_normalize_bi_kernel<true><<<grid, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, notes, scr, defer_list, tile_counter, n_tiles, ctl, tpb, accumulate ? 0 : 1);
+    VTN_CUDA(ctx, cudaGetLastError());
+    uint32_t grid2 = (uint32_t)(ctx->sm_count * 2); // the deferred tiles are few: two blocks per SM walk the list
+    if (grid2 > need) grid2 = need;
+    vtn_normalize_bi_kernel<false><<<grid2, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, notes, scr, defer_list, tile_counter, n_tiles, ctl, tpb, 0);
+    VTN_CUDA(ctx, cudaGetLastError());
+    vtn_compact_kernel<<<n_blocks2, VTC_THREADS, 0, s>>>(VtnDevBatchView{}, scr, out, n_tiles, ctl, n_blocks2, tpb);
     VTN_CUDA(ctx, cudaGetLastError());
     ctx->launches += 3;
     return VTN_OK;
