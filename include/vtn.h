@@ -18,6 +18,7 @@
  *   vtn_vcf_tokenize     vcf_parse1 + bcf_unpack(BCF_UN_STR) for CHROM/POS/REF/ALT (lib/htslib/vcf.c) behind
  *                        BCFOrderedReader::read, bcf_ordered_reader.cpp:238-298
  *   vtn_blocksub*        the record loop of Igor::decompose_blocksub(), decompose_blocksub.cpp:185-421 (without -a)
+ *   vtn_annotate_indels  the record loop of Igor::annotate_indels(), annotate_indels.cpp:293-410, and VNTRAnnotator::annotate under it
  *   vtn_hmm_*            AHMM/LFHMM/RFHMM::align (ahmm.cpp:468-587, lfhmm.cpp:489-654, rfhmm.cpp:516+)
  *
  * The library never exits or prints: every call returns 0 on success or a negative vtn_err code, and
@@ -388,6 +389,67 @@ int vtn_hmm_dbatch_fetch(vtn_ctx* ctx, vtn_hmm_dbatch* db, vtn_hmm_result* out, 
 int vtn_hmm_transitions(int kind, const vtn_hmm_params* par, float* T49);
 /* DP cells / predecessor evaluations (SURVEY 8d "W") of the last resident run, for roofline accounting */
 int vtn_hmm_dbatch_work(vtn_ctx* ctx, vtn_hmm_dbatch* db, uint64_t* cells, uint64_t* proc_comps);
+
+/* ---- annotate_indels: VNTR annotation of indels ----
+ * Replaces the record loop of Igor::annotate_indels() (annotate_indels.cpp:293-410) and everything under
+ * VNTRAnnotator::annotate (vntr_annotator.cpp:62-149) for a batch of records:
+ *   classify_variant, is_normalized, contains_N (variant_manip.cpp:227-508, :109-197, :202-222)             device
+ *   CandidateRegionExtractor::pick_candidate_region(EXACT_LEFT_RIGHT_ALIGNMENT) (candidate_region_extractor.cpp:162-267)  device
+ *   CandidateMotifPicker::update_exact_repeat_unit / generate_candidate_motifs / next_motif (candidate_motif_picker.cpp)   host
+ *   FlankDetector::detect_flanks(EXACT|FUZZY), compute_purity_score, compute_composition_and_entropy (flank_detector.cpp:103-887):
+ *   every RFHMM / LFHMM / AHMM alignment on the device (vtn_hmm_*), one batched launch per slen round over all indels still open;
+ *   the reference fetches (ReferenceSequence::fetch_seq / fetch_base) from the resident reference by vtn_ref_fetch_batch's kernel.
+ * flags[r]: VTN_ANNOT_KEEP = the reference writes the record (it drops records that are not normalized or contain N,
+ * annotate_indels.cpp:306-323); VTN_ANNOT_INDEL = it is annotated, vntr[indel_idx[r]] holds the 34 INFO values (:342-387).
+ * Per allele slot of an annotated record (optional, all three or none): what trim() took from the left / right of REF and that
+ * ALT and how many bases right_align moved them -- enough to reprint the two stderr lines per ALT the reference writes
+ * unconditionally (candidate_region_extractor.cpp:195, :199). */
+#define VTN_ANNOT_KEEP 1
+#define VTN_ANNOT_INDEL 2
+typedef struct vtn_vntr_side /* the exact_* or fuzzy_* members of VNTR (vntr.h) */
+{
+    int32_t beg1, end1;           /* *_REPEAT_TRACT */
+    int32_t mlen, blen;           /* *_MLEN, *_BLEN */
+    int32_t comp[4];              /* *_COMP */
+    int32_t rl, ll;               /* *_RL, *_LL */
+    int32_t no_perfect_ru, no_ru; /* *_RU_COUNTS */
+    int32_t trf_score;            /* *_TRF_SCORE */
+    float entropy, entropy2, kl_divergence, kl_divergence2, ref, score;
+    uint32_t str_off[3], str_len[3]; /* motif, ru, basis inside vtn_annot_result::strings */
+} vtn_vntr_side;
+typedef struct vtn_vntr_annot
+{
+    uint32_t rec;                 /* input record */
+    uint8_t exact_ru_ambiguous;   /* EXACT_RU_AMBIGUOUS flag */
+    uint8_t is_large_repeat_tract;
+    uint8_t reserved[2];
+    vtn_vntr_side exact, fuzzy;
+} vtn_vntr_annot;
+typedef struct vtn_annot_result
+{
+    uint8_t* flags;        /* [n_rec] */
+    uint8_t* vtype;        /* [n_rec] */
+    uint32_t* indel_idx;   /* [n_rec] index into vntr[], UINT32_MAX otherwise */
+    uint32_t* trim_left;   /* [n_allele] or NULL */
+    uint32_t* trim_right;  /* [n_allele] or NULL */
+    uint32_t* shift;       /* [n_allele] or NULL */
+    uint32_t cap_indel;    /* in */
+    uint64_t cap_str;      /* in */
+    uint32_t n_indel;      /* out */
+    uint64_t n_str;        /* out */
+    uint64_t n_alignments; /* out: HMM alignments run on the device */
+    vtn_vntr_annot* vntr;  /* [cap_indel] */
+    char* strings;         /* [cap_str] */
+} vtn_annot_result;
+int vtn_annotate_indels(vtn_ctx* ctx, const vtn_batch* in, vtn_annot_result* out);
+/* Test / diagnostic tap: every alignment the driver issues is written to `path` as "<indel> <stage> <kind> <motif> <flank> <read>
+ * <what the driver reads back>" (stage 0 exact purity, 1 RFHMM rounds, 2 LFHMM rounds, 3 fuzzy purity) -- the format of
+ * oracle/fd_trace.cpp, which taps the unmodified reference classes the same way.  NULL or "" switches it off. */
+int vtn_annot_set_trace(vtn_ctx* ctx, const char* path);
+/* ReferenceSequence::fetch_seq for a list of windows (0-based inclusive, clipped like faidx.c:832-860), one kernel:
+ * out[off[k] .. off[k+1]) = window k; upper != 0 = faidx_fetch_uc_seq.  An unknown contig yields an empty window. */
+int vtn_ref_fetch_batch(vtn_ctx* ctx, uint32_t n, const int32_t* rid, const int64_t* beg0, const int64_t* end0, int upper, uint64_t* off,
+                        uint8_t* out, uint64_t cap);
 
 /* ---- timing on the ctx stream (CUDA events) ---- */
 int vtn_timer_start(vtn_ctx* ctx);

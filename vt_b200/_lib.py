@@ -105,6 +105,24 @@ class VtnHmmResult(C.Structure):
                 ("reserved", C.c_int32)]
 
 
+class VtnVntrSide(C.Structure):
+    _fields_ = [("beg1", C.c_int32), ("end1", C.c_int32), ("mlen", C.c_int32), ("blen", C.c_int32), ("comp", C.c_int32 * 4), ("rl", C.c_int32),
+                ("ll", C.c_int32), ("no_perfect_ru", C.c_int32), ("no_ru", C.c_int32), ("trf_score", C.c_int32), ("entropy", C.c_float),
+                ("entropy2", C.c_float), ("kl_divergence", C.c_float), ("kl_divergence2", C.c_float), ("ref", C.c_float), ("score", C.c_float),
+                ("str_off", C.c_uint32 * 3), ("str_len", C.c_uint32 * 3)]
+
+
+class VtnVntrAnnot(C.Structure):
+    _fields_ = [("rec", C.c_uint32), ("exact_ru_ambiguous", C.c_uint8), ("is_large_repeat_tract", C.c_uint8), ("reserved", C.c_uint8 * 2),
+                ("exact", VtnVntrSide), ("fuzzy", VtnVntrSide)]
+
+
+class VtnAnnotResult(C.Structure):
+    _fields_ = [("flags", c_u8p), ("vtype", c_u8p), ("indel_idx", c_u32p), ("trim_left", c_u32p), ("trim_right", c_u32p), ("shift", c_u32p),
+                ("cap_indel", C.c_uint32), ("cap_str", C.c_uint64), ("n_indel", C.c_uint32), ("n_str", C.c_uint64), ("n_alignments", C.c_uint64),
+                ("vntr", C.POINTER(VtnVntrAnnot)), ("strings", C.c_char_p)]
+
+
 # name -> (restype, argtypes); also the list the CPU test checks against include/vtn.h
 SIGNATURES = {
     "vtn_ctx_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
@@ -162,6 +180,9 @@ SIGNATURES = {
     "vtn_hmm_dbatch_fetch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, c_i32p]),
     "vtn_hmm_transitions": (C.c_int, [C.c_int, C.POINTER(VtnHmmParams), C.POINTER(C.c_float)]),
     "vtn_hmm_dbatch_work": (C.c_int, [C.c_void_p, C.c_void_p, c_u64p, c_u64p]),
+    "vtn_annotate_indels": (C.c_int, [C.c_void_p, C.POINTER(VtnBatch), C.POINTER(VtnAnnotResult)]),
+    "vtn_annot_set_trace": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "vtn_ref_fetch_batch": (C.c_int, [C.c_void_p, C.c_uint32, c_i32p, c_i64p, c_i64p, C.c_int, c_u64p, c_u8p, C.c_uint64]),
     "vtn_timer_start": (C.c_int, [C.c_void_p]),
     "vtn_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "vtn_launch_count": (C.c_uint64, [C.c_void_p]),

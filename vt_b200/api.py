@@ -425,6 +425,53 @@ class Context:
         self._chk(self.lib.vtn_dbatch_fetch_result(self.h, db, C.byref(res.c)), "vtn_dbatch_fetch_result")
         return res
 
+    def annotate_indels(self, batch, trace=None):
+        """vt annotate_indels for a batch (include/vtn.h vtn_annotate_indels) -> dict: flags, vtype, indel_idx, trim_left / trim_right /
+        shift per allele slot, vntr (list of dicts with the 34 INFO values per indel), n_alignments."""
+        n = batch.n_rec
+        flags, vtype = np.zeros(max(n, 1), np.uint8), np.zeros(max(n, 1), np.uint8)
+        idx = np.zeros(max(n, 1), np.uint32)
+        tl, tr, sh = (np.zeros(batch.n_allele + 1, np.uint32) for _ in range(3))
+        vn = (L.VtnVntrAnnot * max(n, 1))()
+        cap_str = 4 * batch.n_bytes + 64 * n + 4096
+        strs = C.create_string_buffer(cap_str)
+        r = L.VtnAnnotResult(_p(flags, L.c_u8p), _p(vtype, L.c_u8p), _p(idx, L.c_u32p), _p(tl, L.c_u32p), _p(tr, L.c_u32p), _p(sh, L.c_u32p),
+                             n, cap_str, 0, 0, 0, vn, C.cast(strs, C.c_char_p))
+        self._chk(self.lib.vtn_annot_set_trace(self.h, trace.encode() if trace else None), "vtn_annot_set_trace")
+        cb = batch.as_c()
+        try:
+            self._chk(self.lib.vtn_annotate_indels(self.h, C.byref(cb), C.byref(r)), "vtn_annotate_indels")
+        finally:
+            self.lib.vtn_annot_set_trace(self.h, None)
+        raw = strs.raw
+        out = []
+        for k in range(int(r.n_indel)):
+            a = vn[k]
+            d = {"rec": int(a.rec), "exact_ru_ambiguous": bool(a.exact_ru_ambiguous), "is_large_repeat_tract": bool(a.is_large_repeat_tract)}
+            for pre, sd in (("EX", a.exact), ("FZ", a.fuzzy)):
+                st = [raw[sd.str_off[i]:sd.str_off[i] + sd.str_len[i]].decode() for i in range(3)]
+                d.update({pre + "_MOTIF": st[0], pre + "_RU": st[1], pre + "_BASIS": st[2], pre + "_MLEN": int(sd.mlen), pre + "_BLEN": int(sd.blen),
+                          pre + "_REPEAT_TRACT": (int(sd.beg1), int(sd.end1)), pre + "_COMP": tuple(int(x) for x in sd.comp),
+                          pre + "_ENTROPY": np.float32(sd.entropy), pre + "_ENTROPY2": np.float32(sd.entropy2), pre + "_KL_DIVERGENCE": np.float32(sd.kl_divergence),
+                          pre + "_KL_DIVERGENCE2": np.float32(sd.kl_divergence2), pre + "_REF": np.float32(sd.ref), pre + "_RL": int(sd.rl), pre + "_LL": int(sd.ll),
+                          pre + "_RU_COUNTS": (int(sd.no_perfect_ru), int(sd.no_ru)), pre + "_SCORE": np.float32(sd.score), pre + "_TRF_SCORE": int(sd.trf_score)})
+            out.append(d)
+        return {"flags": flags[:n], "vtype": vtype[:n], "indel_idx": idx[:n], "trim_left": tl[:batch.n_allele], "trim_right": tr[:batch.n_allele],
+                "shift": sh[:batch.n_allele], "vntr": out, "n_alignments": int(r.n_alignments)}
+
+    def fetch_batch(self, rid, beg0, end0, upper=True):
+        """list of reference windows in one kernel (include/vtn.h vtn_ref_fetch_batch) -> list of bytes"""
+        rid = np.ascontiguousarray(rid, np.int32)
+        beg0 = np.ascontiguousarray(beg0, np.int64)
+        end0 = np.ascontiguousarray(end0, np.int64)
+        n = int(rid.shape[0])
+        cap = int(np.maximum(end0 - beg0 + 1, 1).sum()) + 1
+        off = np.zeros(n + 1, np.uint64)
+        out = np.zeros(cap, np.uint8)
+        self._chk(self.lib.vtn_ref_fetch_batch(self.h, n, _p(rid, L.c_i32p), _p(beg0, L.c_i64p), _p(end0, L.c_i64p), 1 if upper else 0,
+                                               _p(off, L.c_u64p), _p(out, L.c_u8p), cap), "vtn_ref_fetch_batch")
+        return [bytes(out[int(off[k]):int(off[k + 1])]) for k in range(n)]
+
     def sync(self):
         self._chk(self.lib.vtn_sync(self.h), "vtn_sync")
 

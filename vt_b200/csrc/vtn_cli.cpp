@@ -1,5 +1,5 @@
 // vtn_cli.cpp -- host shim that keeps vt's command surface for the path:  `vtn normalize`, `vtn decompose`, `vtn uniq`,
-// `vtn decompose_blocksub`.
+// `vtn decompose_blocksub`, `vtn annotate_indels`.
 //
 // Mirrors the reference tools' flags, stderr text and VCF output (normalize.cpp:84-171, :332-382; decompose.cpp:
 // 80-150, :960-995) while the per-record arithmetic runs in libvtn's CUDA kernels through the C ABI (include/vtn.h):
@@ -1373,12 +1373,285 @@ int cmd_blocksub(int argc, char** argv)
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// annotate_indels  (Igor::annotate_indels, annotate_indels.cpp:155-410): vtn_annotate_indels decides which records the reference
+// keeps and computes the 34 VNTR values of every indel (regions, motifs and the HMM rounds on the device); the host writes the
+// INFO tags in the reference's bcf_update_info_* order (an existing key keeps its place), FLANKSEQ from batched reference
+// fetches (:277-291), the two stderr lines per ALT that CandidateRegionExtractor prints unconditionally, 10000-bp ordered writer.
+// ------------------------------------------------------------------------------------------------------------
+struct InfoList
+{
+    std::vector<std::pair<std::string, std::string>> kv; // value "\x01" = flag
+    void parse(const char* s, size_t n)
+    {
+        kv.clear();
+        if (n == 1 && s[0] == '.') return;
+        for (const Tok& t : split(s, n, ';'))
+        {
+            if (!t.second) continue;
+            const char* eq = (const char*)memchr(t.first, '=', t.second);
+            if (eq) kv.emplace_back(std::string(t.first, eq - t.first), std::string(eq + 1, t.second - (eq - t.first) - 1));
+            else kv.emplace_back(std::string(t.first, t.second), std::string("\x01"));
+        }
+    }
+    void set(const std::string& k, const std::string& v) // bcf_update_info: replace in place, else append
+    {
+        for (auto& e : kv)
+            if (e.first == k)
+            {
+                e.second = v;
+                return;
+            }
+        kv.emplace_back(k, v);
+    }
+    std::string str() const
+    {
+        if (kv.empty()) return ".";
+        std::string o;
+        for (size_t i = 0; i < kv.size(); ++i)
+        {
+            if (i) o.push_back(';');
+            o += kv[i].first;
+            if (kv[i].second != "\x01")
+            {
+                o.push_back('=');
+                o += kv[i].second;
+            }
+        }
+        return o;
+    }
+};
+
+std::string fmt_float(float x)
+{
+    char b[64];
+    snprintf(b, sizeof b, "%.9g", (double)x);
+    std::string o;
+    put_float(o, b, strlen(b));
+    return o;
+}
+
+int cmd_annotate_indels(int argc, char** argv)
+{
+    Args a = parse_args("annotate_indels", argc, argv);
+    if (a.ref.empty()) usage_and_exit("annotate_indels", "required: -r <reference FASTA>");
+    // print_options, annotate_indels.cpp:241-252 (add_flank_annotation is never set there; it prints as false)
+    fprintf(stderr, "annotate_indels v%s\n\n", VERSION);
+    fprintf(stderr, "options:     input VCF file(s)        %s\n", a.in.c_str());
+    fprintf(stderr, "         [o] output VCF file          %s\n", a.out.c_str());
+    fprintf(stderr, "         [k] add_flank_annotation     false\n");
+    fprintf(stderr, "         [d] debug                    %s\n", a.debug ? "true" : "false");
+    fprintf(stderr, "         [r] ref FASTA file           %s\n\n", a.ref.c_str());
+    vtn_ctx* ctx = nullptr;
+    if (vtn_ctx_create(&ctx, a.device)) die(nullptr, "vtn_ctx_create");
+    if (vtn_ref_load_fasta(ctx, a.ref.c_str())) die(ctx, "loading the reference");
+    Reader rd;
+    if (!rd.open(a.in))
+    {
+        fprintf(stderr, "[vtn] cannot open %s\n", a.in.c_str());
+        return 1;
+    }
+    Header h;
+    std::string line;
+    if (!read_header(rd, h, line))
+    {
+        fprintf(stderr, "[vtn] %s has no VCF header\n", a.in.c_str());
+        return 1;
+    }
+    // the 36 INFO lines of initialize() (:168-229), each only if the ID is not in the header dictionary yet
+    static const char* TAGS[][4] = {
+        {"EX_MOTIF", "1", "String", "Canonical motif in a VNTR."}, {"EX_RU", "1", "String", "Repeat unit in the reference sequence."},
+        {"EX_BASIS", "1", "String", "Basis nucleotides in the motif."}, {"EX_MLEN", "1", "Integer", "Motif length."}, {"EX_BLEN", "1", "Integer", "Basis length."},
+        {"EX_REPEAT_TRACT", "2", "Integer", "Boundary of the repeat tract detected by exact alignment."},
+        {"EX_COMP", "4", "Integer", "Composition(%) of bases in an exact repeat tract."}, {"EX_ENTROPY", "1", "Float", "Entropy measure of an exact repeat tract [0,2]."},
+        {"EX_ENTROPY2", "1", "Float", "Dinucleotide entropy measure of an exact repeat tract [0,4]."},
+        {"EX_KL_DIVERGENCE", "1", "Float", "Kullback-Leibler Divergence of an exact repeat tract."},
+        {"EX_KL_DIVERGENCE2", "1", "Float", "Dinucleotide Kullback-Leibler Divergence of an exact repeat tract."},
+        {"EX_REF", ".", "Float", "Allele lengths in repeat units from exact alignment."}, {"EX_RL", "1", "Integer", "Reference exact repeat tract length in bases."},
+        {"EX_LL", "1", "Integer", "Longest exact repeat tract length in bases."},
+        {"EX_RU_COUNTS", "2", "Integer", "Number of exact repeat units and total number of repeat units in exact repeat tract."},
+        {"EX_SCORE", "1", "Float", "Score of repeat unit in exact repeat tract."}, {"EX_TRF_SCORE", "1", "Integer", "TRF Score for M/I/D as 2/-7/-7 in exact repeat tract."},
+        {"FZ_MOTIF", "1", "String", "Canonical motif in a VNTR."}, {"FZ_RU", "1", "String", "Repeat unit in the reference sequence."},
+        {"FZ_BASIS", "1", "String", "Basis nucleotides in the motif."}, {"FZ_MLEN", "1", "Integer", "Motif length."}, {"FZ_BLEN", "1", "Integer", "Basis length."},
+        {"FZ_REPEAT_TRACT", "2", "Integer", "Boundary of the repeat tract detected by fuzzy alignment."},
+        {"FZ_COMP", "4", "Integer", "Composition(%) of bases in a fuzzy repeat tract."}, {"FZ_ENTROPY", "1", "Float", "Entropy measure of a fuzzy repeat tract (0-2)."},
+        {"FZ_ENTROPY2", "1", "Float", "Dinucleotide entropy measure of a fuzzy repeat tract (0-2)."},
+        {"FZ_KL_DIVERGENCE", "1", "Float", "Kullback-Leibler Divergence of a fuzzyt repeat tract."},
+        {"FZ_KL_DIVERGENCE2", "1", "Float", "Dinucleotide Kullback-Leibler Divergence of a fuzzy repeat tract."},
+        {"FZ_REF", ".", "Float", "Allele lengths in repeat units from fuzzy alignment."}, {"FZ_RL", "1", "Integer", "Reference fuzzy repeat tract length in bases."},
+        {"FZ_LL", "1", "Integer", "Longest fuzzy repeat tract length in bases."},
+        {"FZ_RU_COUNTS", "2", "Integer", "Number of exact repeat units and total number of repeat units in fuzzy repeat tract."},
+        {"FZ_SCORE", "1", "Float", "Score of repeat unit in fuzzy repeat tract."}, {"FZ_TRF_SCORE", "1", "Integer", "TRF Score for M/I/D as 2/-7/-7 in fuzzy repeat tract."},
+        {"FLANKSEQ", "1", "String", "Flanking sequence 10bp on either side of REF."}, {"EXACT_RU_AMBIGUOUS", "0", "Flag", "Exact motif is ambiguous."}};
+    std::string extra;
+    for (auto& t : TAGS)
+    {
+        bool present = h.info.count(t[0]) || h.fmt.count(t[0]);
+        for (const std::string& m : h.meta)
+            if (m.compare(0, 9, "##FILTER=") == 0 && attr(m, "ID") == t[0]) present = true;
+        if (present) continue;
+        if (!extra.empty()) extra.push_back('\n');
+        extra += std::string("##INFO=<ID=") + t[0] + ",Number=" + t[1] + ",Type=" + t[2] + ",Description=\"" + t[3] + "\">";
+        Tag tg;
+        tg.type = t[2][0] == 'I' ? 'I' : t[2][0] == 'F' ? (t[2][1] == 'l' && t[2][2] == 'a' ? 'L' : 'F') : 'S';
+        h.info[t[0]] = tg;
+    }
+    DeviceWriter ow;
+    ow.out = open_out(a.out);
+    ow.window = 10000; // annotate_indels.cpp:161
+    ow.ctx = ctx;
+    write_header(ow.out, h, extra.empty() ? nullptr : extra.c_str());
+
+    size_t BATCH = 1u << 18;
+    if (const char* e = getenv("VTN_CLI_BATCH"))
+        if (atol(e) > 0) BATCH = (size_t)atol(e);
+    BatchBuf bb;
+    std::map<std::string, int> rid_cache;
+    LineParser lp;
+    bool more = !line.empty();
+    uint32_t no_indels_annotated = 0;
+    while (more)
+    {
+        lp.read_batch(rd, line, more, BATCH, bb, ctx, true, rid_cache);
+        vtn_batch in = bb.view();
+        const size_t n = in.n_rec;
+        std::vector<uint8_t> flags(n + 1), vtype(n + 1);
+        std::vector<uint32_t> idx(n + 1), tl(in.n_allele + 1), tr(in.n_allele + 1), sh(in.n_allele + 1);
+        std::vector<vtn_vntr_annot> vn(n + 1);
+        std::vector<char> strs(4 * (size_t)in.n_bytes + 64 * n + 4096);
+        vtn_annot_result out;
+        memset(&out, 0, sizeof out);
+        out.flags = flags.data(), out.vtype = vtype.data(), out.indel_idx = idx.data();
+        out.trim_left = tl.data(), out.trim_right = tr.data(), out.shift = sh.data();
+        out.cap_indel = (uint32_t)n, out.cap_str = strs.size(), out.vntr = vn.data(), out.strings = strs.data();
+        if (vtn_annotate_indels(ctx, &in, &out)) die(ctx, "vtn_annotate_indels");
+        // reference windows: FLANKSEQ (three per record that gets one) and the bases right_align walked over (one per ALT)
+        std::vector<int32_t> w_rid;
+        std::vector<int64_t> w_beg, w_end;
+        std::vector<size_t> flank_at(n, (size_t)-1), shift_at(in.n_allele + 1, (size_t)-1);
+        for (size_t r = 0; r < n; ++r)
+        {
+            if (!(flags[r] & VTN_ANNOT_KEEP)) continue;
+            const uint32_t a0 = in.allele_beg[r];
+            const int64_t beg1 = in.pos1[r], end1 = beg1 + (int64_t)(in.allele_off[a0 + 1] - in.allele_off[a0]) - 1;
+            const bool indel = flags[r] & VTN_ANNOT_INDEL;
+            if (indel || vtype[r] == VTN_VT_VNTR || vtype[r] == VTN_VT_SNP || vtype[r] == VTN_VT_MNP)
+            {
+                if (in.rid[r] < 0)
+                {
+                    fprintf(stderr, "[vtn] contig of record %s:%d is not in the reference\n", std::string(bb.lines[r], 0, bb.lines[r].find('\t')).c_str(), in.pos1[r]);
+                    exit(1);
+                }
+                flank_at[r] = w_rid.size();
+                const int64_t wb[3] = {beg1 - 10, beg1, end1 + 1}, we[3] = {beg1 - 1, end1, end1 + 10};
+                for (int q = 0; q < 3; ++q) w_rid.push_back(in.rid[r]), w_beg.push_back(wb[q] - 1), w_end.push_back(we[q] - 1);
+            }
+            if (indel)
+                for (uint32_t s = a0 + 1; s < in.allele_beg[r + 1]; ++s)
+                    if (sh[s])
+                    {
+                        const int64_t e1 = beg1 + tl[s] + (int64_t)(in.allele_off[a0 + 1] - in.allele_off[a0] - tl[s] - tr[s]) - 1;
+                        shift_at[s] = w_rid.size();
+                        w_rid.push_back(in.rid[r]), w_beg.push_back(e1), w_end.push_back(e1 + sh[s] - 1);
+                    }
+        }
+        std::vector<uint64_t> w_off(w_rid.size() + 1, 0);
+        std::vector<uint8_t> w_bytes(1);
+        if (!w_rid.empty())
+        {
+            uint64_t cap = 0;
+            for (size_t k = 0; k < w_rid.size(); ++k) cap += (uint64_t)std::max<int64_t>(w_end[k] - w_beg[k] + 1, 1);
+            w_bytes.resize(cap + 1);
+            if (vtn_ref_fetch_batch(ctx, (uint32_t)w_rid.size(), w_rid.data(), w_beg.data(), w_end.data(), 1, w_off.data(), w_bytes.data(), cap)) die(ctx, "vtn_ref_fetch_batch");
+        }
+        auto window = [&](size_t k) { return std::string((const char*)w_bytes.data() + w_off[k], (size_t)(w_off[k + 1] - w_off[k])); };
+        for (size_t r = 0; r < n; ++r)
+        {
+            if (!(flags[r] & VTN_ANNOT_KEEP)) continue; // annotate_indels.cpp:306-323: dropped, not passed through
+            const std::string& ln = bb.lines[r];
+            std::vector<Tok> col = split(ln.data(), ln.size(), '\t');
+            const uint32_t a0 = in.allele_beg[r];
+            DeviceWriter::Rec rec;
+            rec.rid = in.rid[r];
+            rec.chrom.assign(col[0].first, col[0].second);
+            rec.pos1 = in.pos1[r];
+            InfoList info;
+            info.parse(col[7].first, col[7].second);
+            if (flags[r] & VTN_ANNOT_INDEL)
+            {
+                // candidate_region_extractor.cpp:195, :199: "<end1> <ref>  <alt>" after trim and after right_align, per ALT
+                const std::string REF((const char*)in.bytes + in.allele_off[a0], in.allele_off[a0 + 1] - in.allele_off[a0]);
+                for (uint32_t s = a0 + 1; s < in.allele_beg[r + 1]; ++s)
+                {
+                    const std::string ALT((const char*)in.bytes + in.allele_off[s], in.allele_off[s + 1] - in.allele_off[s]);
+                    std::string rt = REF.substr(tl[s], REF.size() - tl[s] - tr[s]), at = ALT.substr(tl[s], ALT.size() - tl[s] - tr[s]);
+                    const int64_t e1 = (int64_t)in.pos1[r] + tl[s] + (int64_t)rt.size() - 1;
+                    rec.msg += std::to_string(e1) + " " + rt + "  " + at + "\n";
+                    if (sh[s])
+                    {
+                        const std::string walked = window(shift_at[s]);
+                        rt = (rt + walked).substr(sh[s]);
+                        at = (at + walked).substr(sh[s]);
+                    }
+                    rec.msg += std::to_string(e1 + sh[s]) + " " + rt + "  " + at + "\n";
+                }
+                const vtn_vntr_annot& v = vn[idx[r]];
+                const vtn_vntr_side* sd[2] = {&v.exact, &v.fuzzy};
+                const char* pre[2] = {"EX_", "FZ_"};
+                for (int x = 0; x < 2; ++x)
+                {
+                    const vtn_vntr_side& q = *sd[x];
+                    const std::string P = pre[x];
+                    auto S = [&](int i) { return std::string(out.strings + q.str_off[i], q.str_len[i]); };
+                    info.set(P + "MOTIF", S(0));
+                    info.set(P + "MLEN", std::to_string(q.mlen));
+                    info.set(P + "RU", S(1));
+                    info.set(P + "BASIS", S(2));
+                    info.set(P + "BLEN", std::to_string(q.blen));
+                    info.set(P + "REPEAT_TRACT", std::to_string(q.beg1) + "," + std::to_string(q.end1));
+                    info.set(P + "COMP", std::to_string(q.comp[0]) + "," + std::to_string(q.comp[1]) + "," + std::to_string(q.comp[2]) + "," + std::to_string(q.comp[3]));
+                    info.set(P + "ENTROPY", fmt_float(q.entropy));
+                    info.set(P + "ENTROPY2", fmt_float(q.entropy2));
+                    info.set(P + "KL_DIVERGENCE", fmt_float(q.kl_divergence));
+                    info.set(P + "KL_DIVERGENCE2", fmt_float(q.kl_divergence2));
+                    info.set(P + "REF", fmt_float(q.ref));
+                    info.set(P + "RL", std::to_string(q.rl));
+                    info.set(P + "LL", std::to_string(q.ll));
+                    info.set(P + "RU_COUNTS", std::to_string(q.no_perfect_ru) + "," + std::to_string(q.no_ru));
+                    info.set(P + "SCORE", fmt_float(q.score));
+                    info.set(P + "TRF_SCORE", std::to_string(q.trf_score));
+                    if (x == 0 && v.exact_ru_ambiguous) info.set("EXACT_RU_AMBIGUOUS", "\x01");
+                }
+                ++no_indels_annotated;
+            }
+            if (flank_at[r] != (size_t)-1) info.set("FLANKSEQ", window(flank_at[r]) + "[" + window(flank_at[r] + 1) + "]" + window(flank_at[r] + 2));
+            std::string& o = rec.line;
+            for (int c = 0; c < 5; ++c)
+            {
+                if (c) o.push_back('\t');
+                o.append(col[c].first, col[c].second);
+            }
+            const std::string istr = info.str();
+            std::vector<Tok> c2 = col;
+            c2[7] = Tok(istr.data(), istr.size());
+            put_tail(o, h, c2, "");
+            ow.write(std::move(rec));
+        }
+        ow.drain(false);
+    }
+    ow.drain(true);
+    if (ow.out != stdout) fclose(ow.out);
+    fprintf(stderr, "\nstats: no. of indels annotated   %u\n\n", no_indels_annotated); // print_stats, :254-259
+    vtn_ctx_destroy(ctx);
+    return 0;
+}
+
 int main(int argc, char** argv)
 {
     clock_t t0 = clock();
     if (argc < 2)
     {
-        fprintf(stderr, "usage: vtn normalize|decompose|decompose_blocksub|uniq [options] <in.vcf>   (B200 drop-in for vt's decompose/normalize path)\n");
+        fprintf(stderr, "usage: vtn normalize|decompose|decompose_blocksub|uniq|annotate_indels [options] <in.vcf>   (B200 drop-in for vt's decompose/normalize path)\n");
         return 1;
     }
     std::string cmd = argv[1];
@@ -1399,6 +1672,11 @@ int main(int argc, char** argv)
     else if (cmd == "decompose_blocksub")
     {
         cmd_blocksub(argc - 1, argv + 1);
+        print = true;
+    }
+    else if (cmd == "annotate_indels")
+    {
+        cmd_annotate_indels(argc - 1, argv + 1);
         print = true;
     }
     else

@@ -186,6 +186,7 @@ struct vtn_ctx
     void* hmm_scratch = nullptr;
     size_t hmm_scratch_bytes = 0;
     unsigned* hmm_counter = nullptr;
+    std::string annot_trace; // vtn_annot_set_trace
 };
 void vtn_hmm_ctx_release(vtn_ctx* ctx);
 void vtn_uniq_dbatch_release(vtn_dbatch* d);
