@@ -181,54 +181,61 @@ def run_reference_arm(args, rank, world):
 
 
 C5_SITES = int(os.environ.get("VTN_BENCH_C5_SITES", 20000))
-C5_CPU_SAMPLE = int(os.environ.get("VTN_BENCH_C5_CPU_SAMPLE", 400))
-HMM_REF = os.path.join(ROOT, "oracle", "_ref", "hmm_ref")
+C5_CPU_SAMPLE = int(os.environ.get("VTN_BENCH_C5_CPU_SAMPLE", 800))
+C5_REF_SCALE = float(os.environ.get("VTN_BENCH_C5_REF_SCALE", 0.02))
 # warp instructions per reference proc_comp in the DP inner loop, counted from the SASS of vtn_hmm_kernel
 # (profiles/r1h_hmm_sass_count.txt, dynamic count profiles/r1h_ncu_hmm.txt): the issue-rate roofline of SURVEY.md 8d
 HMM_WARP_INSTR_PER_PROC_COMP = float(os.environ.get("VTN_HMM_IPP", 7.65))
 
 
-def hmm_cpu_reference(cases, params):
-    """The unmodified reference classes (oracle/_ref/hmm_ref) on a bounded sample, one process per host core."""
-    import hmm_helpers as H
-    if not os.path.exists(HMM_REF):
-        raise RuntimeError("oracle/_ref/hmm_ref missing: run __graft_entry__.build() in the build container")
-    cores = len(os.sched_getaffinity(0))
-    P = max(1, min(cores, 64))
-    text = H.cases_text(cases).encode()
-    t0 = time.perf_counter()
-    procs = [subprocess.Popen([HMM_REF] + [repr(float(p)) for p in params[:5]], stdin=subprocess.PIPE, stdout=subprocess.DEVNULL,
-                              stderr=subprocess.DEVNULL) for _ in range(P)]
-    for p in procs:
-        p.stdin.write(text)
-        p.stdin.close()
-    rcs = [p.wait() for p in procs]
-    dt = time.perf_counter() - t0
-    if any(rcs):
-        raise RuntimeError("hmm_ref failed: %s" % rcs)
-    return P * len(cases) / dt / 1e6, P, dt
+def normalized_unique(batch, res):
+    """the batch after vt normalize | vt uniq, sorted: (rid, pos1, [alleles]) records (tooling for C5, not timed)"""
+    k = res.n_changed
+    new = {}
+    for j in range(k):
+        r = int(res.chg_rec[j])
+        new[r] = (int(res.chg_pos1[j]), res.changed_alleles(j, [len(a) for a in batch.alleles(r)]))
+    out = set()
+    for r in range(batch.n_rec):
+        p, al = new.get(r, (int(batch.pos1[r]), batch.alleles(r)))
+        out.add((int(batch.rid[r]), p, tuple(al)))
+    return sorted(out)
 
 
 def run_c5(args, rank, world, local):
-    """C5: the (model, sequence) pairs FlankDetector's fuzzy detection issues for synthetic STR indels
-    (vt_b200/flank_detector.py drives the rounds on the GPU), then all of them re-timed as one resident batch."""
+    """C5: `vt annotate_indels` on synthetic STR indels (C4's generator, normalized first) through vtn_annotate_indels -- the pinned
+    driver (tests/test_annot_*: identical alignment tuples and INFO values to the unmodified reference) decides which (model,
+    sequence) pairs exist; value = all of them re-timed as one resident batch on the HMM kernel; e2e = the whole call."""
     import torch
     import torch.distributed as dist
-    from vt_b200 import Context, synth, flank_detector as FD, api as A
+    from vt_b200 import Context, synth, api as A
+    from vt_b200.api import Batch
+    import helpers
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ctx = Context(local)
     t_setup = time.time()
-    contig, end1, motifs = synth.make_c5_sites(C5_SITES, seed=synth.SEED_C5 + 1000 * rank)
-    sites = [FD.Site(contig, end1[i], motifs[i]) for i in range(C5_SITES)]
-    issued = FD.detect_flanks_fuzzy(sites, lambda cases: ctx.hmm_align(A.HmmBatch(cases))[0], log=log if rank == 0 else None)
-    pcases, _ = FD.purity_cases(sites)
-    cases = [c for rnd in issued for c in rnd] + pcases
-    n_large = sum(1 for s_ in sites if s_.large)
-    batch = A.HmmBatch(cases)
-    log("[rank %d] C5 setup %.1fs: %d sites -> %d alignments (%d AHMM), %d large tracts, %d sequence bytes" %
-        (rank, time.time() - t_setup, C5_SITES, batch.n, len(pcases), n_large, batch.n_bytes))
+    tracts = []
+    names, seqs = synth.make_reference(seed=synth.SEED_REF_C4, scale=C5_REF_SCALE, str_frac=0.3, tracts_out=tracts)
+    raw = synth.make_str_indels(seqs, tracts, C5_SITES, seed=synth.SEED_C5 + 1000 * rank)
+    ctx.load_reference(names, seqs)
+    recs = normalized_unique(raw, ctx.normalize(raw))
+    batch = Batch.from_records(recs)
+    tmpd = tempfile.mkdtemp(prefix="vtn_c5_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+    trace = os.path.join(tmpd, "trace.txt")
+    res = ctx.annotate_indels(batch, trace=trace, raw=True)
+    n_indel = int(res["n_indel"])
+    cases = []
+    kind_of = {"A": A.AHMM, "L": A.LFHMM, "R": A.RFHMM}
+    for l in open(trace):
+        f = l.split()
+        cases.append((kind_of[f[2]], f[3], "" if f[4] == "-" else f[4], f[5]))
+    os.remove(trace)
+    n_ahmm = sum(1 for c in cases if c[0] == A.AHMM)
+    hb = A.HmmBatch(cases)
+    log("[rank %d] C5 setup %.1fs: %d records (%d indels annotated) -> %d alignments (%d AHMM), %d sequence bytes" %
+        (rank, time.time() - t_setup, batch.n_rec, n_indel, hb.n, n_ahmm, hb.n_bytes))
 
     def barrier():
         if world > 1:
@@ -243,7 +250,7 @@ def run_c5(args, rank, world, local):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    db = ctx.hmm_upload(batch)
+    db = ctx.hmm_upload(hb)
     cells, pcs = ctx.hmm_work(db)
     for _ in range(args.warmup):
         ctx.hmm_align_resident(db)
@@ -259,59 +266,70 @@ def run_c5(args, rank, world, local):
     barrier()
     launches = ctx.launch_count() - l0
     ms_step = max_over_ranks(ms_total / args.steps)
-    value = world * batch.n / (ms_step / 1e3) / 1e6
-    res_dev, _ = ctx.hmm_fetch(db, batch.n)
-    # end to end: host buffers in, results out, through vtn_hmm_align
-    e2e_steps = max(3, min(args.steps, 10))
-    ctx.hmm_align(batch)
+    value = world * hb.n / (ms_step / 1e3) / 1e6
+    # end to end: the whole vtn_annotate_indels call (host buffers in, 34 values per indel out; regions, fetches, every round)
+    e2e_steps = max(2, min(args.steps, 3))
     barrier()
     w0 = time.perf_counter()
     for _ in range(e2e_steps):
-        res_host, _ = ctx.hmm_align(batch)
+        r2 = ctx.annotate_indels(batch, raw=True)
     barrier()
     e2e_ms = max_over_ranks(1e3 * (time.perf_counter() - w0) / e2e_steps)
     t1 = time.time()
     clocks = sampler.stop(t0, t1)
-    assert res_host.tobytes() == res_dev.tobytes()
+    assert int(r2["n_indel"]) == n_indel and int(r2["n_alignments"]) == hb.n
     ctx.hmm_free(db)
     if rank != 0:
         return
     sm_mhz = clocks.get("sm_mhz") or 1965.0
     peak_pc = 148 * 4 * 32 * sm_mhz * 1e6 / HMM_WARP_INSTR_PER_PROC_COMP / 1e9  # G proc_comp/s at full issue rate
     ach_pc = pcs / (ms_total / args.steps / 1e3) / 1e9
-    h2d = batch.n + 4 * (3 * batch.n + 1) + batch.n_bytes
-    d2h = 96 * batch.n
+    h2d = 8 * batch.n_rec + 4 * (batch.n_rec + 1) + 4 * (batch.n_allele + 1) + batch.n_bytes + hb.n + 4 * (3 * hb.n + 1) + hb.n_bytes
+    d2h = 96 * hb.n + 160 * n_indel
     line = {
         "metric": "hmm_alignments_per_s", "value": value, "unit": "M alignments/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {
-            "workload": "C5: AHMM/LFHMM/RFHMM Viterbi realignment of %d synthetic STR indel sites per GPU (sample of the 5M-site config) -> %d alignments issued by the FlankDetector fuzzy-detection rounds (%d RFHMM/LFHMM + %d AHMM), reads 105-1006 bp" % (C5_SITES, batch.n, batch.n - len(pcases), len(pcases)),
-            "alignments_per_gpu": batch.n, "dp_cells_per_step": int(cells), "reference_proc_comps_per_step": int(pcs),
+            "workload": "C5: vt annotate_indels on %d normalized synthetic STR indels per GPU (C4 generator on a %.3f Gb reference with 30%% tandem repeats; sample of the 5M-indel config) -> %d AHMM/LFHMM/RFHMM alignments issued by the FlankDetector rounds of vtn_annotate_indels (%d RFHMM/LFHMM + %d AHMM), reads up to 1006 bp" % (n_indel, sum(x.shape[0] for x in seqs) / 1e9, hb.n, hb.n - n_ahmm, n_ahmm),
+            "indels_per_gpu": n_indel, "alignments_per_gpu": hb.n, "dp_cells_per_step": int(cells), "reference_proc_comps_per_step": int(pcs),
             "g_cell_updates_per_s": world * cells / (ms_step / 1e3) / 1e9,
+            "annotate_indels_e2e_indels_per_s": world * n_indel / (e2e_ms / 1e3),
             "l2": "back-pointer scratch of the resident warps (>= 148*16 warps x up to 1.1 MB) exceeds the 126 MB L2 for long reads; no explicit flush",
-            "sharding": "independent sites per rank, no collective",
-            "tolerance": "optimal_score bit-identical to the reference's float32 (stated tolerance 1e-4 abs), paths and integer results exact",
+            "sharding": "independent records per rank, no collective",
+            "tolerance": "optimal_score bit-identical to the reference's float32 (stated tolerance 1e-4 abs), paths and integer results exact; the driver issues the reference's exact alignment list (tests/test_annot_gpu.py)",
         },
         "roofline": {
             "bound": "issue", "achieved": ach_pc, "peak": peak_pc, "unit": "G proc_comp/s", "frac": ach_pc / peak_pc,
             "traffic": None, "kernel": "vtn_hmm_kernel",
-            "peak_source": "148 SM x 4 sub-cores x 32 lanes x %.0f MHz (median SM clock sampled under load) / %.1f warp instructions per reference proc_comp (SASS count)" % (sm_mhz, HMM_WARP_INSTR_PER_PROC_COMP),
+            "peak_source": "148 SM x 4 sub-cores x 32 lanes x %.0f MHz (median SM clock sampled under load) / %.2f warp instructions per reference proc_comp (SASS count, profiles/r1h_hmm_sass_count.txt): issue-slot utilisation against the kernel's own instruction mix, not an algorithmic bound" % (sm_mhz, HMM_WARP_INSTR_PER_PROC_COMP),
         },
-        "e2e": {"value": world * batch.n / (e2e_ms / 1e3) / 1e6, "unit": "M alignments/s", "h2d_bytes_per_step": int(h2d),
+        "e2e": {"value": world * hb.n / (e2e_ms / 1e3) / 1e6, "unit": "M alignments/s", "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms, "steps": e2e_steps},
         "gpu_launches": int(launches), "clocks": clocks,
     }
     if not args.no_cpu_baseline:
         try:
-            rng = np.random.default_rng(5)
-            pick = sorted(rng.choice(len(cases), size=min(C5_CPU_SAMPLE, len(cases)), replace=False))
-            sample = [cases[i] for i in pick]
-            cv, P, dt = hmm_cpu_reference(sample, A.FLANK_DETECTOR_PARAMS)
-            line["cpu_baseline"] = {"value": cv, "unit": "M alignments/s", "cores": P, "kind": "reference",
-                                    "sample": "%d alignments drawn uniformly from this batch, each of %d concurrent single-threaded processes of the unmodified AHMM/LFHMM/RFHMM classes (oracle/_ref/hmm_ref) over the whole sample, %.1f s wall" % (len(sample), P, dt)}
+            # the unmodified `vt annotate_indels` on a bounded sample of the same records: P range shards of C5_CPU_SAMPLE indels in all
+            cores = len(os.sched_getaffinity(0))
+            P = max(1, min(cores, 64))
+            fa = os.path.join(tmpd, "ref.fa")
+            helpers.write_fasta(fa, names, seqs)
+            ns = min(C5_CPU_SAMPLE, batch.n_rec)
+            cuts = [ns * i // P for i in range(P + 1)]
+            for i in range(P):
+                with open(os.path.join(tmpd, "in%d.vcf" % i), "w") as f:
+                    f.write("##fileformat=VCFv4.2\n" + "".join("##contig=<ID=%s,length=%d>\n" % (n_, q.shape[0]) for n_, q in zip(names, seqs)) + "#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\n")
+                    for (c, p_, al) in recs[cuts[i]:cuts[i + 1]]:
+                        f.write("%s\t%d\t.\t%s\t%s\t.\t.\t.\n" % (names[c], p_, al[0].decode(), ",".join(x.decode() for x in al[1:])))
+            dt = _run_procs([[VT_REF, "annotate_indels", os.path.join(tmpd, "in%d.vcf" % i), "-r", fa, "-o", os.path.join(tmpd, "out%d.vcf" % i)] for i in range(P)])
+            frac_al = hb.n / max(batch.n_rec, 1)
+            line["cpu_baseline"] = {"value": ns * frac_al / dt / 1e6, "unit": "M alignments/s", "cores": P, "kind": "reference",
+                                    "sample": "the first %d records of this batch in %d range shards, one unmodified single-threaded `vt annotate_indels` process per shard (VCF + FASTA on tmpfs), %.1f s wall = %.1f records/s; alignments counted at this batch's %.2f alignments per record" % (ns, P, dt, ns / dt, frac_al)}
         except Exception as e:
             line["cpu_baseline"] = {"value": None, "unit": "M alignments/s", "cores": 0, "kind": "reference", "sample": "unavailable: %s" % e}
+    import shutil
+    shutil.rmtree(tmpd, ignore_errors=True)
     emit(line)
 
 

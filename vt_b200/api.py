@@ -425,7 +425,7 @@ class Context:
         self._chk(self.lib.vtn_dbatch_fetch_result(self.h, db, C.byref(res.c)), "vtn_dbatch_fetch_result")
         return res
 
-    def annotate_indels(self, batch, trace=None):
+    def annotate_indels(self, batch, trace=None, raw=False):
         """vt annotate_indels for a batch (include/vtn.h vtn_annotate_indels) -> dict: flags, vtype, indel_idx, trim_left / trim_right /
         shift per allele slot, vntr (list of dicts with the 34 INFO values per indel), n_alignments."""
         n = batch.n_rec
@@ -443,6 +443,8 @@ class Context:
             self._chk(self.lib.vtn_annotate_indels(self.h, C.byref(cb), C.byref(r)), "vtn_annotate_indels")
         finally:
             self.lib.vtn_annot_set_trace(self.h, None)
+        if raw:  # counts only (bench): no per-indel dicts
+            return {"flags": flags[:n], "vtype": vtype[:n], "indel_idx": idx[:n], "n_indel": int(r.n_indel), "n_alignments": int(r.n_alignments)}
         raw = strs.raw
         out = []
         for k in range(int(r.n_indel)):

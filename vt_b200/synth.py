@@ -256,32 +256,6 @@ def algorithmic_bytes(batch, res):
 SEED_C5 = 20260106
 
 
-def make_c5_sites(n, seed=SEED_C5):
-    """C5: n indel sites, each at the right end of a tandem-repeat tract drawn like C4's (unit 1-6,
-    40% homopolymers, tract 10-2000 bp log-uniform, 0-2% interruptions) with 1200 bp of random flank on either
-    side.  -> (contig uint8 array, exact_end1[n], motifs[n]) for vt_b200.flank_detector."""
-    rng = np.random.default_rng(seed)
-    tl = np.exp(rng.uniform(np.log(10), np.log(2000), size=n)).astype(np.int64)
-    ul = np.where(rng.random(n) < 0.4, 1, rng.integers(2, 7, size=n)).astype(np.int64)
-    units = _ACGT[rng.integers(0, 4, size=(n, 6))]
-    # a unit must not be a repeat of a shorter one in its first base at least: force unit[1] != unit[0] for ul > 1
-    units[:, 1] = np.where((ul > 1) & (units[:, 1] == units[:, 0]), _ACGT[(np.searchsorted(_ACGT, units[:, 0]) + 1) % 4], units[:, 1])
-    flank = 1200
-    blk = flank + tl
-    starts = np.concatenate([[0], np.cumsum(blk)])[:-1] + flank
-    total = int(blk.sum()) + flank
-    lut = _base_lut()
-    s = lut[rng.integers(0, 256, size=total, dtype=np.uint8)]
-    seg, within = _ragged(tl)
-    vals = units[seg, within % ul[seg]]
-    inter = rng.random(vals.shape[0]) < np.repeat(rng.uniform(0, 0.02, size=n), tl)
-    vals = np.where(inter, _ACGT[rng.integers(0, 4, size=vals.shape[0])], vals)
-    s[np.repeat(starts, tl) + within] = vals
-    exact_end1 = starts + tl  # 1-based position of the tract's last base
-    motifs = [units[i, :ul[i]].tobytes().decode() for i in range(n)]
-    return s, exact_end1, motifs
-
-
 def make_multiallelic(seqs, n, seed=SEED_VCF_C3, max_indel=50):
     """C3 records: every record multiallelic, n_alt = clip(1 + geometric(0.5), 2, 6); each ALT is an
     SNV (80%), deletion (10%) or insertion (10%) with geometric(0.4) length capped at max_indel, all sharing one REF
