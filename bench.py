@@ -867,6 +867,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--layout", default="bi", choices=["bi", "general"], help="c2 / c4: compact biallelic batch (vtn_normalize_bi, default) or the general vtn_batch")
     ap.add_argument("--resident-only", action="store_true", help="c2 / c4: only the device-resident loop (profiling passes); prints a reduced line")
+    ap.add_argument("--no-sharded", action="store_true", help="c2: skip the sharded multi-device C3 measurement (vtn_multi_decompose_normalize) added to the line")
     ap.add_argument("--no-compare", action="store_true", help="c2 / c4: skip the side measurement of the general layout")
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5", "u1", "w1", "t1", "b1"],
                     help="c2 (default, the metric's configuration), c3 = multiallelic decompose+normalize fused, c4 = STR/homopolymer reference with maximal left shifts, "
@@ -902,6 +903,7 @@ def main():
 
 
 def load_workload(workload, rank):
+    rank = int(os.environ.get("VTN_BENCH_SEED_RANK", rank))  # which rank's batch to generate (explains per-rank time differences)
     """(names, seqs, batch) of C2 / C4 for this rank.  VTN_BENCH_CACHE=<dir> keeps the generated arrays as .npy files there so
     that several bench invocations of one session (variants, the ncu passes) do not regenerate 3.1 Gb each."""
     from vt_b200 import synth
@@ -930,6 +932,58 @@ def load_workload(workload, rank):
             np.save(os.path.join(cache, "%s_b%d.npy" % (tag, i)), x)
         open(os.path.join(cache, tag + ".done"), "w").write("ok")
     return names, seqs, batch
+
+
+C3S_TOTAL = int(os.environ.get("VTN_BENCH_C3S_TOTAL", 12_500_000))
+
+
+def sharded_c3(n_dev, names, seqs, steps):
+    """Configuration C3 as north_star states it, through the product's multi-device entry (vtn_multi_decompose_normalize): ONE set of
+    multiallelic records, sharded by contig / record range over the n_dev GPUs of the box inside one process (one host thread per
+    device, reference packed once and replicated by peer copies, no NCCL), decompose fused with normalize on every device, results
+    copied by every device straight to their place in the caller's arrays (input order).  STRONG scaling: the total is fixed
+    (VTN_BENCH_C3S_TOTAL records, a sample of the 100 M-record configuration).  Timed region (wall clock, pinned host buffers):
+    shard -> H2D -> kernels -> D2H of the merged result.  The merged result is compared with the single-device call (untimed)."""
+    from vt_b200 import synth
+    from vt_b200.api import MultiContext, NormResult
+    import ctypes as C
+    from vt_b200 import _lib as L
+    t0 = time.time()
+    batch = synth.make_multiallelic(seqs, C3S_TOTAL, seed=synth.SEED_VCF_C3)
+    lens = np.diff(batch.allele_off.astype(np.int64))
+    na = np.diff(batch.allele_beg.astype(np.int64))
+    ref_len = lens[batch.allele_beg[:-1].astype(np.int64)]
+    bound = int(np.maximum(na - 1, 1).sum())
+    nb = int((np.maximum(na - 1, 1) * ref_len).sum() + lens.sum())
+    with MultiContext(list(range(n_dev))) as m:
+        m.load_reference(names, seqs)
+        hb = pinned_batch(m.ctx0, batch)
+        bufs = (m.ctx0.pinned_empty(bound + 1, np.uint32), m.ctx0.pinned_empty(bound + 1, np.uint16), NormResult(bound, nb, m.ctx0))
+        log("sharded C3 setup %.1fs: %d records -> %d biallelic, %d devices" % (time.time() - t0, batch.n_rec, bound, n_dev))
+        for _ in range(2):
+            src, alt, dcnt, res = m.decompose_normalize(hb, bufs)
+        w0 = time.perf_counter()
+        for _ in range(steps):
+            src, alt, dcnt, res = m.decompose_normalize(hb, bufs)
+        ms = 1e3 * (time.perf_counter() - w0) / steps
+        n_out, k = int(src.shape[0]), res.n_changed
+        one = (np.zeros(bound + 1, np.uint32), np.zeros(bound + 1, np.uint16), NormResult(bound, nb))
+        n1, d1 = C.c_uint64(0), L.VtnDecompCounters()
+        cb = hb.as_c()
+        m.ctx0._chk(m.ctx0.lib.vtn_decompose_normalize(m.ctx0.h, C.byref(cb), one[0].ctypes.data_as(L.c_u32p), one[1].ctypes.data_as(L.c_u16p), C.byref(n1), C.byref(d1), C.byref(one[2].c)), "vtn_decompose_normalize")
+        r1 = one[2]
+        same = (int(n1.value) == n_out and r1.n_changed == k and np.array_equal(one[0][:n_out], src) and np.array_equal(one[1][:n_out], alt)
+                and np.array_equal(r1.status[:n_out], res.status[:n_out]) and np.array_equal(r1.vtype[:n_out], res.vtype[:n_out])
+                and np.array_equal(r1.chg_rec[:k], res.chg_rec[:k]) and np.array_equal(r1.chg_pos1[:k], res.chg_pos1[:k])
+                and np.array_equal(r1.chg_off[:k + 1], res.chg_off[:k + 1]) and np.array_equal(r1.chg_bytes[:r1.n_changed_bytes], res.chg_bytes[:res.n_changed_bytes])
+                and r1.counters == res.counters)
+        assert same, "sharded C3: merged result differs from the single-device call"
+    h2d = 8 * batch.n_rec + 4 * (batch.n_rec + 1) + 4 * (batch.n_allele + 1) + batch.n_bytes
+    d2h = 6 * n_out + 2 * n_out + 20 * k + 8 * (k + 1) + res.n_changed_bytes
+    return {"workload": "C3 sharded in one process: %d multiallelic records (sample of the 100 M config) -> %d biallelic, contig/range shards over %d GPU(s), decompose fused with normalize per device, results in input order" % (batch.n_rec, n_out, n_dev),
+            "scaling": "strong", "n_gpus": n_dev, "value": n_out / (ms / 1e3) / 1e6, "unit": UNIT, "input_m_records_per_s": batch.n_rec / (ms / 1e3) / 1e6,
+            "ms_per_step": ms, "steps": steps, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "changed": int(k),
+            "merged_equals_single_device": True, "decompose_counters": [int(x) for x in dcnt]}
 
 
 def slice_batch(batch, a, b):
@@ -990,8 +1044,10 @@ def run_c2_c4(args, rank, world, local):
     from vt_b200 import Context, synth
     from vt_b200.api import NormResult, NormResultBi
     torch.cuda.set_device(local)
+    cpu_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        cpu_group = dist.new_group(backend="gloo")  # waits that must not put a spinning kernel on a GPU (the end of this function)
         import atexit
         atexit.register(lambda: dist.is_initialized() and dist.destroy_process_group())
 
@@ -1130,6 +1186,11 @@ def run_c2_c4(args, rank, world, local):
 
     if rank != 0:
         ctx.free(db)
+        if world > 1:
+            # rank 0 is still measuring (sharded C3 over ALL GPUs, CPU baseline): wait on the CPU (gloo) -- an NCCL barrier would leave a
+            # spinning kernel on this rank's GPU while rank 0's contexts run on it
+            torch.cuda.synchronize()
+            dist.barrier(group=cpu_group)
         return
     # ---------------- checker leg (untimed): a fixed slice of the timed batch against the CPU oracle ----------------
     n_chk = min(batch.n_rec, CHECK_RECORDS)
@@ -1168,6 +1229,12 @@ def run_c2_c4(args, rank, world, local):
         hist = np.bincount(np.minimum(np.floor(np.log2(np.maximum(le, 1))).astype(np.int64), 14), minlength=15)
         line["config"]["left_shift_histogram_log2_bins"] = [int(x) for x in hist]
         line["config"]["left_shift_mean"] = float(le.mean()) if k_ else 0.0
+    if args.workload == "c2" and not args.no_sharded:
+        # the other ranks wait (on the CPU) at the end of this function while rank 0 drives all `world` GPUs through vtn_multi_*
+        try:
+            line["sharded_c3"] = sharded_c3(world, names, seqs, 3)
+        except Exception as e:
+            line["sharded_c3"] = {"error": str(e)[:300]}
     if not args.no_cpu_baseline and world >= 1 and args.workload == "c2":
         try:
             cv, cms, P, sample = cpu_reference_run(CPU_SAMPLE_RECORDS, 2, 1, names, seqs, batch)
@@ -1176,6 +1243,8 @@ def run_c2_c4(args, rank, world, local):
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "unavailable: %s" % e}
     emit(line)
     ctx.free(db)
+    if world > 1:
+        dist.barrier(group=cpu_group)
 
 
 if __name__ == "__main__":

@@ -451,6 +451,29 @@ int vtn_annot_set_trace(vtn_ctx* ctx, const char* path);
 int vtn_ref_fetch_batch(vtn_ctx* ctx, uint32_t n, const int32_t* rid, const int64_t* beg0, const int64_t* end0, int upper, uint64_t* off,
                         uint8_t* out, uint64_t cap);
 
+/* ---- several GPUs of one box behind one call ----
+ * The path shards trivially (records independent, reference read-only): no collective, no NCCL.  vtn_multi holds one vtn_ctx per
+ * entry of device_ids (an id may repeat: two contexts on one device, which is how a single-GPU box tests the sharding); the
+ * reference is packed and uploaded once and replicated to the other devices by peer copies (NVLink / NVSwitch where the devices
+ * reach each other).  A call cuts the batch into one contiguous record range per device (vtn_shard_plan: by contig, then by
+ * record range -- vt's own way to go parallel is one process per interval, program.cpp:152-190), runs every range on its device
+ * from its own host thread, and puts the results back together in input order: what comes back is bit-identical to the
+ * single-device call on the whole batch. */
+typedef struct vtn_multi vtn_multi;
+int vtn_multi_create(vtn_multi** m, const int* device_ids, int n_dev);
+int vtn_multi_destroy(vtn_multi* m);
+int vtn_multi_n_dev(const vtn_multi* m);
+vtn_ctx* vtn_multi_ctx(vtn_multi* m, int slot); /* the context of one slot, for the vtn_ref_* queries and single-device calls */
+const char* vtn_multi_last_error(const vtn_multi* m);
+int vtn_multi_ref_load_fasta(vtn_multi* m, const char* fasta_path);
+int vtn_multi_ref_load_memory(vtn_multi* m, int32_t n_contig, const char* const* names, const int64_t* len, const uint8_t* const* seq);
+/* cut[0..n_shard]: shard s = records [cut[s], cut[s+1]); equal record counts, cuts on multiples of align, a cut within a sixteenth
+ * of a shard of a contig change moves onto it */
+int vtn_shard_plan(const int32_t* rid, uint32_t n_rec, uint32_t n_shard, uint32_t align, uint32_t* cut);
+int vtn_multi_normalize_bi(vtn_multi* m, const vtn_batch_bi* in, vtn_norm_result_bi* out);
+int vtn_multi_decompose_normalize(vtn_multi* m, const vtn_batch* in, uint32_t* src_rec, uint16_t* alt_idx, uint64_t* n_out,
+                                  vtn_decomp_counters* dcounters, vtn_norm_result* out);
+
 /* ---- timing on the ctx stream (CUDA events) ---- */
 int vtn_timer_start(vtn_ctx* ctx);
 int vtn_timer_stop(vtn_ctx* ctx, float* ms); /* records, synchronises, returns elapsed ms */

@@ -267,3 +267,17 @@ def test_blocksub_cli_small_batches(tmp_path):
     p = subprocess.run([VTN, "decompose_blocksub", "-m", vin, "-o", out], capture_output=True, text=True, env=dict(os.environ, VTN_CLI_BATCH="23"))
     assert p.returncode == 0, p.stderr
     assert open(out).read() == open(vout).read()
+
+
+@pytest.mark.parametrize("stem", ["unk", "renorm"])
+def test_normalize_advice_goldens(tmp_path, stem):
+    """made by the unmodified reference (tests/golden/make_advice_golden.py): two SNP-only contigs the FASTA lacks keep their order
+    (the writer flushes on the header id, not the FASTA id); input that already carries OLD_VARIANT gets the value replaced in
+    place and no second header line"""
+    g = lambda x: os.path.join(helpers.GOLDEN, "advice_%s" % x)
+    out = str(tmp_path / "out.vcf")
+    rc, err = _run(VTN, ["normalize", g(stem + "_in.vcf"), "-r", g("ref.fa"), "-o", out])
+    assert rc == 0, err
+    assert open(out).read() == open(g(stem + "_out.vcf")).read()
+    unpath = lambda e: "\n".join(re.sub(r"^\[[^\] ]*/", "[", l) for l in _strip(e).splitlines())  # the reference build's __FILE__ path
+    assert unpath(err) == unpath(open(g(stem + "_out.stderr")).read())

@@ -183,6 +183,19 @@ SIGNATURES = {
     "vtn_annotate_indels": (C.c_int, [C.c_void_p, C.POINTER(VtnBatch), C.POINTER(VtnAnnotResult)]),
     "vtn_annot_set_trace": (C.c_int, [C.c_void_p, C.c_char_p]),
     "vtn_ref_fetch_batch": (C.c_int, [C.c_void_p, C.c_uint32, c_i32p, c_i64p, c_i64p, C.c_int, c_u64p, c_u8p, C.c_uint64]),
+    "vtn_multi_create": (C.c_int, [C.POINTER(C.c_void_p), c_i32p, C.c_int]),
+    "vtn_multi_destroy": (C.c_int, [C.c_void_p]),
+    "vtn_multi_n_dev": (C.c_int, [C.c_void_p]),
+    "vtn_multi_ctx": (C.c_void_p, [C.c_void_p, C.c_int]),
+    "vtn_multi_last_error": (C.c_char_p, [C.c_void_p]),
+    "vtn_multi_ref_load_fasta": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "vtn_multi_ref_load_memory": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), c_i64p, C.POINTER(C.c_void_p)]),
+    "vtn_shard_plan": (C.c_int, [c_i32p, C.c_uint32, C.c_uint32, C.c_uint32, c_u32p]),
+    "vtn_multi_normalize_bi": (C.c_int, [C.c_void_p, C.POINTER(VtnBatchBi), C.POINTER(VtnNormResultBi)]),
+    "vtn_multi_decompose_normalize": (
+        C.c_int,
+        [C.c_void_p, C.POINTER(VtnBatch), c_u32p, c_u16p, c_u64p, C.POINTER(VtnDecompCounters), C.POINTER(VtnNormResult)],
+    ),
     "vtn_timer_start": (C.c_int, [C.c_void_p]),
     "vtn_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "vtn_launch_count": (C.c_uint64, [C.c_void_p]),

@@ -489,6 +489,82 @@ class Context:
         return int(self.lib.vtn_launch_count(self.h))
 
 
+def shard_plan(rid, n_shard, align=1):
+    """vtn_shard_plan: record cuts of one contiguous range per shard (host code, no device needed)"""
+    rid = np.ascontiguousarray(rid, np.int32)
+    cut = np.zeros(n_shard + 1, np.uint32)
+    rc = L.load().vtn_shard_plan(_p(rid, L.c_i32p), int(rid.shape[0]), int(n_shard), int(align), _p(cut, L.c_u32p))
+    if rc:
+        raise VtnError("vtn_shard_plan failed (%d)" % rc)
+    return cut
+
+
+class MultiContext:
+    """vtn_multi: several devices behind one call (one vtn_ctx per entry of device_ids; ids may repeat)."""
+
+    def __init__(self, device_ids):
+        self.lib = L.load()
+        ids = np.ascontiguousarray(device_ids, np.int32)
+        h = C.c_void_p()
+        rc = self.lib.vtn_multi_create(C.byref(h), _p(ids, L.c_i32p), int(ids.shape[0]))
+        if rc:
+            raise VtnError("vtn_multi_create: %s" % self.lib.vtn_multi_last_error(None).decode())
+        self.h = h
+        self.n_dev = int(ids.shape[0])
+        # slot 0's context through the single-device wrapper: pinned buffers, bi packing, contig ids
+        self.ctx0 = Context.__new__(Context)
+        self.ctx0.lib = self.lib
+        self.ctx0.h = C.c_void_p(self.lib.vtn_multi_ctx(self.h, 0))
+
+    def close(self):
+        if self.h:
+            self.lib.vtn_multi_destroy(self.h)
+            self.h = None
+            self.ctx0.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _chk(self, rc, what):
+        if rc < 0:
+            raise VtnError("%s failed (%d): %s" % (what, rc, self.lib.vtn_multi_last_error(self.h).decode()))
+        return rc
+
+    def load_reference(self, names, seqs):
+        arrs = [np.frombuffer(s, dtype=np.uint8) if isinstance(s, (bytes, bytearray)) else np.ascontiguousarray(s, np.uint8) for s in seqs]
+        n = len(arrs)
+        cn = (C.c_char_p * max(n, 1))(*[x.encode() for x in names])
+        ln = np.array([a.shape[0] for a in arrs], np.int64)
+        ptr = (C.c_void_p * max(n, 1))(*[a.ctypes.data if a.size else None for a in arrs])
+        self._chk(self.lib.vtn_multi_ref_load_memory(self.h, n, cn, _p(ln, L.c_i64p), ptr), "vtn_multi_ref_load_memory")
+
+    def normalize_bi(self, bi, result=None):
+        res = result or NormResultBi(bi.n_rec, bi.n_bytes)
+        self._chk(self.lib.vtn_multi_normalize_bi(self.h, bi.view, C.byref(res.c)), "vtn_multi_normalize_bi")
+        return res
+
+    def decompose_normalize(self, batch, bufs=None):
+        """-> (src_rec, alt_idx, decompose counters, NormResult indexed by output record); bufs = (src, alt, NormResult) to reuse"""
+        if bufs is None:
+            bound = int(self.lib.vtn_decompose_out_bound(C.byref(batch.as_c())))
+            lens = np.diff(batch.allele_off.astype(np.int64))
+            na = np.diff(batch.allele_beg.astype(np.int64))
+            ref_len = lens[batch.allele_beg[:-1].astype(np.int64)] if batch.n_rec else np.zeros(0, np.int64)
+            nb = int((np.maximum(na - 1, 1) * ref_len).sum() + lens.sum()) if batch.n_rec else 0
+            bufs = (np.zeros(max(bound, 1), np.uint32), np.zeros(max(bound, 1), np.uint16), NormResult(bound, nb))
+        src, alt, res = bufs
+        n_out = C.c_uint64(0)
+        dc = L.VtnDecompCounters()
+        cb = batch.as_c()
+        self._chk(self.lib.vtn_multi_decompose_normalize(self.h, C.byref(cb), _p(src, L.c_u32p), _p(alt, L.c_u16p), C.byref(n_out), C.byref(dc), C.byref(res.c)),
+                  "vtn_multi_decompose_normalize")
+        k = int(n_out.value)
+        return src[:k], alt[:k], [dc.no_variants, dc.no_biallelic, dc.no_multiallelic, dc.no_additional_biallelic], res
+
+
 # ---------------------------------------------------------------------------------------------------------
 # HMM family (AHMM / LFHMM / RFHMM): host-side mirror of set_model + align + the result members
 # ---------------------------------------------------------------------------------------------------------

@@ -1,6 +1,7 @@
 // vtn_api.cu -- context, device batches and the host-buffer entry points of the C ABI (include/vtn.h).
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
 #include "vtn_internal.h"
 
 static thread_local std::string g_create_err;
@@ -509,6 +510,112 @@ int vtn_decompose_normalize(vtn_ctx* ctx, const vtn_batch* in, uint32_t* src_rec
     if (!out) return VTN_E_ARG;
     if (!ctx || !ctx->ref_loaded) return vtn_set_err(ctx, VTN_E_STATE, "vtn_decompose_normalize: no reference loaded");
     return decompose_host(ctx, in, src_rec, alt_idx, n_out, dcounters, out);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// One shard of a multi-device decompose -> normalize (vtn_multi.cu), in two phases so that every device copies its results
+// straight into their final place in the caller's arrays: phase 1 uploads records [r0, r1) as slices of the caller's arrays,
+// re-bases the two prefix arrays ON THE DEVICE (no host pass over the batch) and runs the kernels; once every shard's totals
+// are known, phase 2 adds the shard's bases to the index arrays on the device and copies everything out.
+// ---------------------------------------------------------------------------------------------------------
+namespace
+{
+__global__ void vtn_add_u32_kernel(uint32_t* p, size_t n, uint32_t add)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] += add;
+}
+__global__ void vtn_add_u64_kernel(uint64_t* p, size_t n, uint64_t add)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] += add;
+}
+void add_u32(vtn_ctx* ctx, uint32_t* p, size_t n, uint32_t add)
+{
+    if (!n || !add) return;
+    vtn_add_u32_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 4096), 256, 0, ctx->stream>>>(p, n, add);
+    ctx->launches++;
+}
+void add_u64(vtn_ctx* ctx, uint64_t* p, size_t n, uint64_t add)
+{
+    if (!n || !add) return;
+    vtn_add_u64_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 4096), 256, 0, ctx->stream>>>(p, n, add);
+    ctx->launches++;
+}
+} // namespace
+
+int vtn_shard_decompose_run(vtn_ctx* ctx, const vtn_batch* in, uint32_t r0, uint32_t r1, uint64_t* n_out, uint64_t* n_changed, uint64_t* n_changed_bytes)
+{
+    if (!ctx || !ctx->ref_loaded) return vtn_set_err(ctx, VTN_E_STATE, "vtn_multi_decompose_normalize: no reference loaded");
+    VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    const uint32_t ns = r1 - r0;
+    *n_out = *n_changed = *n_changed_bytes = 0;
+    if (!ns) return VTN_OK;
+    const uint32_t s0 = in->allele_beg[r0], s1 = in->allele_beg[r1];
+    const uint32_t b0 = in->allele_off[s0], b1 = in->allele_off[s1];
+    int rc = ensure_scratch(ctx, ns, s1 - s0, b1 - b0);
+    if (rc) return rc;
+    vtn_dbatch* d = ctx->scratch;
+    cudaStream_t s = ctx->stream;
+    VTN_CUDA(ctx, cudaMemcpyAsync(d->pos1, in->pos1 + r0, sizeof(int32_t) * ns, cudaMemcpyHostToDevice, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(d->rid, in->rid + r0, sizeof(int32_t) * ns, cudaMemcpyHostToDevice, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(d->allele_beg, in->allele_beg + r0, sizeof(uint32_t) * ((size_t)ns + 1), cudaMemcpyHostToDevice, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(d->allele_off, in->allele_off + s0, sizeof(uint32_t) * ((size_t)(s1 - s0) + 1), cudaMemcpyHostToDevice, s));
+    if (b1 > b0) VTN_CUDA(ctx, cudaMemcpyAsync(d->bytes, in->bytes + b0, (size_t)(b1 - b0), cudaMemcpyHostToDevice, s));
+    add_u32(ctx, d->allele_beg, (size_t)ns + 1, 0u - s0);
+    add_u32(ctx, d->allele_off, (size_t)(s1 - s0) + 1, 0u - b0);
+    VTN_CUDA(ctx, cudaGetLastError());
+    rc = vtn_decompose_resident(ctx, d, 1);
+    if (rc) return rc;
+    unsigned long long tot[3] = {0, 0, 0}, nt[2] = {0, 0};
+    VTN_CUDA(ctx, cudaMemcpyAsync(tot, d->totals, sizeof tot, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(nt, d->fused->totals, sizeof nt, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaStreamSynchronize(s));
+    *n_out = tot[0];
+    *n_changed = nt[0];
+    *n_changed_bytes = nt[1];
+    return VTN_OK;
+}
+
+int vtn_shard_decompose_fetch(vtn_ctx* ctx, uint32_t rec_base, uint64_t out_base, uint64_t chg_base, uint64_t byte_base, uint64_t n_out, uint64_t n_changed,
+                              uint64_t n_changed_bytes, uint32_t* src_rec, uint16_t* alt_idx, vtn_decomp_counters* dc, vtn_norm_result* out)
+{
+    VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    memset(dc, 0, sizeof *dc);
+    memset(&out->counters, 0, sizeof out->counters);
+    if (!n_out) return VTN_OK; // an empty shard ran nothing
+    vtn_dbatch* d = ctx->scratch;
+    vtn_dbatch* f = d->fused;
+    cudaStream_t s = ctx->stream;
+    uint32_t c[4] = {0, 0, 0, 0}, nc[12];
+    VTN_CUDA(ctx, cudaMemcpyAsync(c, d->counters + 12, sizeof c, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(nc, f->counters, sizeof nc, cudaMemcpyDeviceToHost, s));
+    const size_t no = (size_t)n_out, k = (size_t)n_changed;
+    add_u32(ctx, d->src_rec, no, rec_base);
+    VTN_CUDA(ctx, cudaMemcpyAsync(src_rec + out_base, d->src_rec, no * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(alt_idx + out_base, d->alt_idx, no * sizeof(uint16_t), cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(out->status + out_base, f->status, no, cudaMemcpyDeviceToHost, s));
+    VTN_CUDA(ctx, cudaMemcpyAsync(out->vtype + out_base, f->vtype, no, cudaMemcpyDeviceToHost, s));
+    if (k)
+    {
+        add_u32(ctx, f->chg_rec, k, (uint32_t)out_base);
+        add_u64(ctx, f->chg_off, k, byte_base);
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_rec + chg_base, f->chg_rec, k * 4, cudaMemcpyDeviceToHost, s));
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_pos1 + chg_base, f->chg_pos1, k * 4, cudaMemcpyDeviceToHost, s));
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_lt + chg_base, f->chg_lt, k * 4, cudaMemcpyDeviceToHost, s));
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_le + chg_base, f->chg_le, k * 4, cudaMemcpyDeviceToHost, s));
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_rt + chg_base, f->chg_rt, k * 4, cudaMemcpyDeviceToHost, s));
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_off + chg_base, f->chg_off, k * 8, cudaMemcpyDeviceToHost, s));
+        VTN_CUDA(ctx, cudaMemcpyAsync(out->chg_bytes + byte_base, f->chg_bytes, (size_t)n_changed_bytes, cudaMemcpyDeviceToHost, s));
+    }
+    VTN_CUDA(ctx, cudaStreamSynchronize(s));
+    dc->no_variants = c[0];
+    dc->no_biallelic = c[1];
+    dc->no_multiallelic = c[2];
+    dc->no_additional_biallelic = c[3];
+    memcpy(out->counters.bi, nc, 5 * sizeof(uint32_t));
+    memcpy(out->counters.multi, nc + 5, 5 * sizeof(uint32_t));
+    out->counters.no_variants = nc[10];
+    out->counters.no_refs = nc[11];
+    return VTN_OK;
 }
 
 // Host-buffer uniq: H2D of the batch, one kernel, D2H of order / first and the two counters.

@@ -282,7 +282,8 @@ void put_sample(std::string& out, const Header& h, const std::vector<Tok>& keys,
     }
 }
 
-// columns 6.. of a record (QUAL FILTER INFO [FORMAT samples]) re-emitted; extra_info is appended to INFO
+// columns 6.. of a record (QUAL FILTER INFO [FORMAT samples]) re-emitted; extra_info ("KEY=VALUE") goes into INFO the way
+// bcf_update_info_string puts it there: an existing KEY keeps its place and gets the new value, a new KEY goes last
 void put_tail(std::string& out, const Header& h, const std::vector<Tok>& col, const std::string& extra_info)
 {
     out.push_back('\t');
@@ -292,14 +293,27 @@ void put_tail(std::string& out, const Header& h, const std::vector<Tok>& col, co
     out.push_back('\t');
     if (extra_info.empty())
         put_info(out, h, col[7].first, col[7].second);
+    else if (col[7].second == 1 && col[7].first[0] == '.')
+        out += extra_info;
     else
     {
-        if (!(col[7].second == 1 && col[7].first[0] == '.'))
+        const size_t kl = extra_info.find('=') == std::string::npos ? extra_info.size() : extra_info.find('=');
+        std::string info;
+        bool replaced = false;
+        for (const Tok& kv : split(col[7].first, col[7].second, ';'))
         {
-            put_info(out, h, col[7].first, col[7].second);
-            out.push_back(';');
+            if (!kv.second) continue;
+            if (!info.empty()) info.push_back(';');
+            if (kv.second >= kl && !memcmp(kv.first, extra_info.data(), kl) && (kv.second == kl || kv.first[kl] == '='))
+            {
+                info += extra_info;
+                replaced = true;
+            }
+            else
+                info.append(kv.first, kv.second);
         }
-        out += extra_info;
+        if (!replaced) info += (info.empty() ? "" : ";") + extra_info;
+        put_info(out, h, info.data(), info.size());
     }
     if (col.size() > 8)
     {
@@ -476,7 +490,26 @@ void write_header(FILE* out, const Header& h, const char* extra_line)
         }
     }
     if (!pass_done) fprintf(out, "%s\n", pass_line);
-    if (extra_line) fprintf(out, "%s\n", extra_line);
+    if (extra_line)
+    { // bcf_hdr_append of an ID the dictionary already holds leaves the header as it is (re-normalizing vt's own output)
+        const std::string all(extra_line);
+        size_t b = 0;
+        while (b <= all.size())
+        {
+            size_t e = all.find('\n', b);
+            if (e == std::string::npos) e = all.size();
+            const std::string l = all.substr(b, e - b);
+            bool dup = false;
+            if (l.compare(0, 7, "##INFO=") == 0 || l.compare(0, 9, "##FORMAT=") == 0)
+            {
+                const std::string id = attr(l, "ID"), cls = l.substr(0, l.find('=') + 1);
+                for (const std::string& mline : h.meta)
+                    if (mline.compare(0, cls.size(), cls) == 0 && attr(mline, "ID") == id) dup = true;
+            }
+            if (!l.empty() && !dup) fprintf(out, "%s\n", l.c_str());
+            b = e + 1;
+        }
+    }
     fprintf(out, "%s\n", h.columns.c_str());
 }
 
@@ -627,6 +660,9 @@ int cmd_normalize(int argc, char** argv)
     memset(&tot, 0, sizeof tot);
     bool more = !line.empty();
     LineParser lp;
+    std::map<std::string, int> writer_ids;
+    std::string last_chrom;
+    int last_wid = -1;
     while (more)
     {
         lp.read_batch(rd, line, more, BATCH, bb, ctx, true, rid_cache);
@@ -684,7 +720,14 @@ int cmd_normalize(int argc, char** argv)
             }
             DeviceWriter::Rec rec;
             rec.msg = std::move(msg);
-            rec.rid = in.rid[r];
+            // the ordered writer flushes when the record's header-dictionary id changes (bcf_ordered_writer.cpp:185-189); the FASTA id
+            // cannot stand in for it: contigs the FASTA lacks all have id -1 there, and two of them in a row must still flush
+            if (chrom != last_chrom)
+            {
+                last_chrom = chrom;
+                last_wid = writer_ids.emplace(chrom, (int)writer_ids.size()).first->second;
+            }
+            rec.rid = last_wid;
             rec.chrom = chrom;
             rec.pos1 = in.pos1[r];
             std::string& o = rec.line;
@@ -940,7 +983,7 @@ int cmd_decompose(int argc, char** argv)
             std::string old = "OLD_MULTIALLELIC=" + std::string(col[0].first, col[0].second) + ":" + std::string(col[1].first, col[1].second) + ":" +
                               std::string(col[3].first, col[3].second);
             for (const Tok& t : alts) old += "/" + std::string(t.first, t.second);
-            bool first = true;
+            bool first = true, old_placed = false;
             if (!(col[7].second == 1 && col[7].first[0] == '.'))
                 for (const Tok& kv : split(col[7].first, col[7].second, ';'))
                 {
@@ -950,7 +993,12 @@ int cmd_decompose(int argc, char** argv)
                     auto it = h.info.find(key);
                     const Tag* tg = it == h.info.end() ? nullptr : &it->second;
                     std::string item;
-                    if (!eq)
+                    if (key == "OLD_MULTIALLELIC")
+                    { // bcf_update_info_string on a key the record already carries: new value, same place
+                        item = old;
+                        old_placed = true;
+                    }
+                    else if (!eq)
                         item = key;
                     else
                     {
@@ -985,8 +1033,11 @@ int cmd_decompose(int argc, char** argv)
                     first = false;
                     o += item;
                 }
-            if (!first) o.push_back(';');
-            o += old;
+            if (!old_placed)
+            {
+                if (!first) o.push_back(';');
+                o += old;
+            }
             // ---- FORMAT / samples
             if (col.size() > 9)
             {

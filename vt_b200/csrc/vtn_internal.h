@@ -176,6 +176,7 @@ struct vtn_ctx
     void* d_exc_len = nullptr;
     void* d_exc_byte = nullptr;
     int64_t ref_bytes = 0;
+    uint64_t ref_n_groups = 0; // 16-byte groups behind d_groups (vtn_ref_clone)
     bool ref_loaded = false;
     // reusable device arena for the host-buffer call
     vtn_dbatch* scratch = nullptr;
@@ -189,6 +190,7 @@ struct vtn_ctx
     std::string annot_trace; // vtn_annot_set_trace
 };
 void vtn_hmm_ctx_release(vtn_ctx* ctx);
+int vtn_ref_clone(vtn_ctx* dst, const vtn_ctx* src); // replicate src's resident reference on dst's device (peer copies)
 void vtn_uniq_dbatch_release(vtn_dbatch* d);
 void vtn_order_dbatch_release(vtn_dbatch* d);
 void vtn_blocksub_dbatch_release(vtn_dbatch* d);
@@ -208,6 +210,10 @@ int vtn_launch_normalize(vtn_ctx* ctx, const VtnDevBatchView& in, const VtnDevNo
 int vtn_launch_normalize_bi(vtn_ctx* ctx, const VtnDevBiView& in, const VtnDevNormOut& out, const VtnDevNotes& notes, const VtnDevScratch& scr,
                             unsigned long long* tile_state, uint32_t* tile_counter, uint32_t n_tiles, bool accumulate = false);
 int vtn_normalize_resident_bi(vtn_ctx* ctx, vtn_dbatch* d);
+// one shard of a multi-device decompose -> normalize (vtn_api.cu; driven by vtn_multi.cu)
+int vtn_shard_decompose_run(vtn_ctx* ctx, const vtn_batch* in, uint32_t r0, uint32_t r1, uint64_t* n_out, uint64_t* n_changed, uint64_t* n_changed_bytes);
+int vtn_shard_decompose_fetch(vtn_ctx* ctx, uint32_t rec_base, uint64_t out_base, uint64_t chg_base, uint64_t byte_base, uint64_t n_out, uint64_t n_changed,
+                              uint64_t n_changed_bytes, uint32_t* src_rec, uint16_t* alt_idx, vtn_decomp_counters* dc, vtn_norm_result* out);
 uint32_t vtn_normalize_tile_records();
 size_t vtn_normalize_ctl_words(uint32_t n_tiles); // 64-bit words behind vtn_dbatch::tile_counter
 int vtn_launch_decompose(vtn_ctx* ctx, vtn_dbatch* db, bool materialise);

@@ -265,7 +265,45 @@ int vtn_ref_load_memory(vtn_ctx* ctx, int32_t n_contig, const char* const* names
     ctx->dref.n_exc = (uint32_t)exc.size();
     ctx->dref.n_contig = n_contig;
     ctx->ref_bytes = (int64_t)(n_groups * sizeof(uint4) + exc.size() * 13);
+    ctx->ref_n_groups = n_groups;
     ctx->ref_loaded = true;
+    return VTN_OK;
+}
+
+// The reference is packed once and uploaded once; the other devices of a multi-device run get it from the first one by peer
+// copies (NVLink / NVSwitch when the devices can reach each other, staged through the host otherwise) -- SURVEY 8e.
+int vtn_ref_clone(vtn_ctx* dst, const vtn_ctx* src)
+{
+    if (!dst || !src || !src->ref_loaded) return vtn_set_err(dst, VTN_E_STATE, "vtn_ref_clone: source has no reference");
+    VTN_CUDA(dst, cudaSetDevice(dst->device));
+    free_ref(dst);
+    dst->contigs = src->contigs;
+    const size_t nc = src->contigs.size() + 1, ne = (size_t)src->dref.n_exc + 1;
+    const size_t sz[6] = {(size_t)src->ref_n_groups * sizeof(uint4), nc * sizeof(uint64_t), nc * sizeof(int64_t), ne * sizeof(uint64_t), ne * sizeof(uint32_t), ne};
+    void** d[6] = {&dst->d_groups, &dst->d_contig_goff, &dst->d_contig_len, &dst->d_exc_start, &dst->d_exc_len, &dst->d_exc_byte};
+    void* const sp[6] = {src->d_groups, src->d_contig_goff, src->d_contig_len, src->d_exc_start, src->d_exc_len, src->d_exc_byte};
+    if (dst->device != src->device)
+    {
+        int can = 0;
+        if (cudaDeviceCanAccessPeer(&can, dst->device, src->device) == cudaSuccess && can) cudaDeviceEnablePeerAccess(src->device, 0);
+        cudaGetLastError(); // "already enabled" is fine; without peer access the copy below is staged by the driver
+    }
+    for (int i = 0; i < 6; ++i)
+    {
+        VTN_CUDA(dst, cudaMalloc(d[i], sz[i]));
+        VTN_CUDA(dst, cudaMemcpyPeerAsync(*d[i], dst->device, sp[i], src->device, sz[i], dst->stream));
+    }
+    VTN_CUDA(dst, cudaStreamSynchronize(dst->stream));
+    dst->dref = src->dref;
+    dst->dref.groups = (const uint4*)dst->d_groups;
+    dst->dref.contig_goff = (const uint64_t*)dst->d_contig_goff;
+    dst->dref.contig_len = (const int64_t*)dst->d_contig_len;
+    dst->dref.exc_start = (const uint64_t*)dst->d_exc_start;
+    dst->dref.exc_len = (const uint32_t*)dst->d_exc_len;
+    dst->dref.exc_byte = (const uint8_t*)dst->d_exc_byte;
+    dst->ref_bytes = src->ref_bytes;
+    dst->ref_n_groups = src->ref_n_groups;
+    dst->ref_loaded = true;
     return VTN_OK;
 }
 

@@ -1,32 +1,19 @@
-"""Sharding of a record batch over the GPUs of one box and the ordered re-merge of the results.
-The path has no exchange step: records are independent and the reference is replicated, so each rank normalizes
-a contiguous record range cut on contig boundaries where possible; only counters (summed) and the per-rank
-outputs (concatenated in rank order, which IS input order) come back.  torch.distributed is used for that
-plumbing alone (nccl on the GPUs, gloo in the CPU tests)."""
+"""Process-per-GPU plumbing around the same sharding that vtn_multi_* does inside one process (vt_b200/csrc/vtn_multi.cu, SURVEY.md
+8e): each rank takes the record range vtn_shard_plan gives it; only counters (summed) and the per-rank outputs (concatenated in
+rank order, which IS input order because the ranges are contiguous) come back.  torch.distributed is used for that plumbing alone
+(nccl on the GPUs, gloo in the CPU tests).  The product path for several GPUs is the C ABI: vtn_multi_normalize_bi /
+vtn_multi_decompose_normalize."""
 import numpy as np
 
 
-def plan_shards(rid, n_ranks, weights=None):
-    """Contiguous record ranges [lo, hi) per rank with ~equal total weight (weight 1 per record by default; C4 uses
-    an expected-shift estimate).  A cut moves to the nearest contig boundary when one lies within 2% of the ideal
-    cut, otherwise it splits the contig (ordering needs no halo: the merge is a stable sort on POS)."""
-    n = int(rid.shape[0])
-    if n_ranks <= 1 or n == 0:
-        return [(0, n)] + [(n, n)] * (max(n_ranks, 1) - 1)
-    w = np.ones(n, np.float64) if weights is None else np.asarray(weights, np.float64)
-    cum = np.concatenate([[0.0], np.cumsum(w)])
-    bounds = np.flatnonzero(np.diff(rid) != 0) + 1  # record indices where a new contig starts
-    cuts = [0]
-    for r in range(1, n_ranks):
-        ideal = int(np.searchsorted(cum, cum[-1] * r / n_ranks))
-        ideal = min(max(ideal, cuts[-1]), n)
-        if bounds.size:
-            k = int(np.argmin(np.abs(bounds - ideal)))
-            if abs(int(bounds[k]) - ideal) <= 0.02 * n and int(bounds[k]) >= cuts[-1]:
-                ideal = int(bounds[k])
-        cuts.append(ideal)
-    cuts.append(n)
-    return [(cuts[r], cuts[r + 1]) for r in range(n_ranks)]
+def plan_shards(rid, n_ranks):
+    """Contiguous record ranges [lo, hi) per rank from libvtn's planner (vtn_shard_plan, the one vtn_multi_* uses inside one
+    process): equal record counts, a cut within a sixteenth of a shard of a contig change moves onto it, otherwise the contig is
+    split.  Ranges are contiguous and in rank order, so putting results back together is concatenation in rank order."""
+    from .api import shard_plan
+    n = max(int(n_ranks), 1)
+    cut = shard_plan(np.ascontiguousarray(rid, np.int32), n)
+    return [(int(cut[r]), int(cut[r + 1])) for r in range(n)]
 
 
 def slice_batch(batch, lo, hi):
