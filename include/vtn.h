@@ -317,6 +317,23 @@ int vtn_blocksub_resident(vtn_ctx* ctx, vtn_dbatch* db, int keep_mnv, int max_mn
 int vtn_dbatch_fetch_blocksub(vtn_ctx* ctx, vtn_dbatch* db, uint32_t* src_rec, uint32_t* off, uint32_t* len, uint64_t cap_out,
                               uint64_t* n_out, vtn_blocksub_counters* counters);
 
+/* ---- decompose_blocksub without any allocation ----
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same plan as vtn_blocksub, but inputs and
+ * outputs are DEVICE pointers the caller owns, the work is queued on the ctx stream and the call returns without waiting
+ * (vtn_sync), and the scratch the kernels need (4 bytes per record + the per-tile words) is a fixed device array inside the
+ * library: at most VTN_BLOCKSUB_NOALLOC_MAX_REC records per call (4 MiB + 8 KiB held by every GPU that loads the library until
+ * exit); more are rejected with VTN_E_ARG and a text that names the limit.  The call allocates and frees nothing; the first call
+ * on a device looks the array's device address up (cudaGetSymbolAddress), so make one call per device before a capture begins.
+ * Every call shares that array: calls that overlap on one GPU (two contexts / streams) race -- run them one after the other.
+ * d_bytes must be 4-byte aligned and readable for 16 bytes past the last allele byte (the kernels load whole words);
+ * d_src_rec / d_off / d_len have capacity cap_out (outputs beyond it are not written); *d_n_out receives the number of outputs
+ * (compare it with cap_out), d_counters the four words of vtn_blocksub_counters. */
+#define VTN_BLOCKSUB_NOALLOC_MAX_REC (1u << 20)
+int vtn_blocksub_noalloc(vtn_ctx* ctx, uint32_t n_rec, const uint32_t* d_allele_beg, const uint32_t* d_allele_off, const uint8_t* d_bytes, int keep_mnv,
+                         int max_mnv_dist, uint32_t* d_src_rec, uint32_t* d_off, uint32_t* d_len, uint64_t cap_out, uint64_t* d_n_out,
+                         uint32_t* d_counters);
+
 /* ---- HMM family: AHMM / LFHMM / RFHMM Viterbi realignment (annotate_indels' FlankDetector) ----
  * Replaces <model>::set_model + <model>::align + the result members/getters:
  *   AHMM  ahmm.h:94-557, ahmm.cpp:240-247 (set_model), :468-587 (align), :592-730 (trace_path, collect_statistics)

@@ -168,6 +168,8 @@ SIGNATURES = {
     "vtn_vcf_dtext_fetch": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VtnVcfFields)]),
     "vtn_blocksub_out_bound": (C.c_uint64, [C.POINTER(VtnBatch)]),
     "vtn_blocksub": (C.c_int, [C.c_void_p, C.POINTER(VtnBatch), C.c_int, C.c_int, c_u32p, c_u32p, c_u32p, C.c_uint64, c_u64p, C.POINTER(VtnBlocksubCounters)]),
+    "vtn_blocksub_noalloc": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_uint64, C.c_void_p, C.c_void_p]),
     "vtn_blocksub_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "vtn_dbatch_fetch_blocksub": (C.c_int, [C.c_void_p, C.c_void_p, c_u32p, c_u32p, c_u32p, C.c_uint64, c_u64p, C.POINTER(VtnBlocksubCounters)]),
     "vtn_uniq_resident": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -518,3 +518,64 @@ int vtn_dbatch_fetch_blocksub(vtn_ctx* ctx, vtn_dbatch* d, uint32_t* src_rec, ui
     }
     return VTN_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// vtn_blocksub_noalloc: the same three kernels for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+// serving loops, harnesses that forbid it).  No counterpart in the reference.
+// The scratch (cnt[] per record, the per-tile aggregates) lives in a file-scope device array of fixed size, which every GPU
+// that loads the library holds until exit: VTN_BLOCKSUB_NOALLOC_MAX_REC records -> 4 MiB + 8 KiB.  In host code the array's
+// name is a host-side stand-in, not a device address; the address is looked up once per device, with that device current, by
+// cudaGetSymbolAddress (below) and that pointer is what the kernels get.
+// ---------------------------------------------------------------------------------------------------------
+#define VTB_NA_MAX_TILES (VTN_BLOCKSUB_NOALLOC_MAX_REC / VTB_TILE)
+#define VTB_NA_CNT_BYTES ((size_t)VTN_BLOCKSUB_NOALLOC_MAX_REC * 4)
+#define VTB_NA_AGG_BYTES (((size_t)VTB_NA_MAX_TILES + 1) * 8)
+static __device__ __align__(256) unsigned char vtb_noalloc_scratch[VTB_NA_CNT_BYTES + 2 * VTB_NA_AGG_BYTES];
+static_assert(VTN_BLOCKSUB_NOALLOC_MAX_REC % VTB_TILE == 0, "the maximum is a whole number of tiles");
+
+#include <mutex>
+static std::mutex vtb_na_mutex;
+static unsigned char* vtb_na_addr[64] = {nullptr}; // device address of vtb_noalloc_scratch, per device ordinal
+
+int vtn_blocksub_noalloc(vtn_ctx* ctx, uint32_t n_rec, const uint32_t* d_allele_beg, const uint32_t* d_allele_off, const uint8_t* d_bytes, int keep_mnv,
+                         int max_mnv_dist, uint32_t* d_src_rec, uint32_t* d_off, uint32_t* d_len, uint64_t cap_out, uint64_t* d_n_out, uint32_t* d_counters)
+{
+    if (!ctx) return VTN_E_ARG;
+    if (n_rec > VTN_BLOCKSUB_NOALLOC_MAX_REC)
+        return vtn_set_err(ctx, VTN_E_ARG, "vtn_blocksub_noalloc: " + std::to_string(n_rec) + " records exceed the fixed scratch (VTN_BLOCKSUB_NOALLOC_MAX_REC = " +
+                                               std::to_string((unsigned)VTN_BLOCKSUB_NOALLOC_MAX_REC) + "); cut the batch or use vtn_blocksub");
+    if (!d_n_out || !d_counters || (n_rec && (!d_allele_beg || !d_allele_off || !d_bytes || !d_src_rec || !d_off || !d_len)))
+        return vtn_set_err(ctx, VTN_E_ARG, "vtn_blocksub_noalloc: null device pointer");
+    if (ctx->device < 0 || ctx->device >= 64) return vtn_set_err(ctx, VTN_E_ARG, "vtn_blocksub_noalloc: device ordinal beyond 63");
+    VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    unsigned char* base = nullptr;
+    {
+        std::lock_guard<std::mutex> g(vtb_na_mutex);
+        if (!vtb_na_addr[ctx->device])
+        { // set-up, once per device, with that device current
+            void* p = nullptr;
+            VTN_CUDA(ctx, cudaGetSymbolAddress(&p, vtb_noalloc_scratch));
+            vtb_na_addr[ctx->device] = (unsigned char*)p;
+        }
+        base = vtb_na_addr[ctx->device];
+    }
+    uint32_t* cnt = reinterpret_cast<uint32_t*>(base);
+    unsigned long long* agg = reinterpret_cast<unsigned long long*>(base + VTB_NA_CNT_BYTES);
+    unsigned long long* tile_cnt = reinterpret_cast<unsigned long long*>(base + VTB_NA_CNT_BYTES + VTB_NA_AGG_BYTES);
+    cudaStream_t s = ctx->stream;
+    // the shared array keeps the last call's contents: cnt[0, n_rec) and agg / tile_cnt[0, n_tiles) are all assigned by the count
+    // kernel before anything reads them, the two results are cleared here (an empty batch runs no kernel)
+    VTN_CUDA(ctx, cudaMemsetAsync(d_counters, 0, 4 * sizeof(uint32_t), s));
+    VTN_CUDA(ctx, cudaMemsetAsync(d_n_out, 0, sizeof(uint64_t), s));
+    if (n_rec)
+    {
+        const uint32_t n_tiles = (n_rec + VTB_TILE - 1) / VTB_TILE;
+        BsView v{n_rec, d_allele_beg, d_allele_off, d_bytes};
+        vtb_count_kernel<<<n_tiles, VTB_THREADS, 0, s>>>(v, keep_mnv, max_mnv_dist, cnt, agg, tile_cnt);
+        vtb_scan_kernel<<<1, 1024, 0, s>>>(agg, n_tiles, reinterpret_cast<unsigned long long*>(d_n_out), tile_cnt, n_rec, d_counters);
+        vtb_emit_kernel<<<n_tiles, VTB_THREADS, 0, s>>>(v, keep_mnv, max_mnv_dist, cnt, agg, d_src_rec, d_off, d_len, cap_out);
+        VTN_CUDA(ctx, cudaGetLastError());
+        ctx->launches += 3;
+    }
+    return VTN_OK;
+}
