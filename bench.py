@@ -120,7 +120,37 @@ def _run_procs(cmds):
     return dt
 
 
-def cpu_reference_run(n_sample, steps, warmup, names=None, seqs=None, batch=None):
+CLI_RECORDS = int(os.environ.get("VTN_BENCH_CLI_RECORDS", 4_000_000))
+VTN_CLI = os.path.join(ROOT, "vt_b200", "vtn")
+
+
+def cli_wall(tmp, fa, names, seqs, batch, n):
+    """The I/O-bound end-to-end wall, parse -> write, on ONE file for both: `vtn normalize` (this repo's command, GPU) and the
+    unmodified `vt normalize` (one process, its native mode), plus `vt view` (parse + write floor); outputs compared byte for byte
+    in the same run.  VCF text and FASTA on tmpfs."""
+    import filecmp
+    vcf = os.path.join(tmp, "cli_in.vcf")
+    write_vcf(vcf, names, seqs, batch, 0, n)
+    o_vtn, o_ref = os.path.join(tmp, "cli_vtn.vcf"), os.path.join(tmp, "cli_ref.vcf")
+    walls, phases = [], {}
+    for rep in range(2):
+        t0 = time.perf_counter()
+        p = subprocess.run([VTN_CLI, "normalize", vcf, "-r", fa, "-o", o_vtn, "-q"], stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True,
+                           env=dict(os.environ, VTN_CLI_TIMING="1"))
+        walls.append(time.perf_counter() - t0)
+        if p.returncode not in (0, 1):
+            raise RuntimeError("vtn normalize failed (%d): %s" % (p.returncode, p.stderr[-500:]))
+        phases = {l.split("]")[1].rsplit(None, 2)[0].strip(): float(l.split()[-2]) for l in p.stderr.splitlines() if l.startswith("[vtn timing]")}
+    t_ref = _run_procs([[VT_REF, "normalize", vcf, "-r", fa, "-o", o_ref, "-q"]])
+    t_view = _run_procs([[VT_REF, "view", vcf, "-o", os.path.join(tmp, "cli_view.vcf")]])
+    same = filecmp.cmp(o_vtn, o_ref, shallow=False)
+    w = min(walls)
+    return {"what": "parse -> write wall of `vtn normalize` vs the unmodified `vt normalize` (one process) on the SAME %d-record VCF (first records of the C2 batch) and the same %.2f Gb FASTA, both on tmpfs" % (n, sum(x.shape[0] for x in seqs) / 1e9),
+            "records": n, "vtn_wall_s": w, "vtn_wall_first_run_s": walls[0], "vtn_m_records_per_s": n / w / 1e6, "vtn_phases_s": phases,
+            "vt_wall_s": t_ref, "vt_m_records_per_s": n / t_ref / 1e6, "vt_view_wall_s": t_view, "speedup": t_ref / w, "outputs_identical": bool(same)}
+
+
+def cpu_reference_run(n_sample, steps, warmup, names=None, seqs=None, batch=None, cli_out=None):
     """Times the unmodified reference `vt normalize` (oracle/_ref/vt_ref) on a bounded sample OF THE SAME WORKLOAD: the first
     n_sample records of the C2 batch (sorted by contig, position) against the same full synthetic reference as a FASTA + .fai
     on tmpfs, cut into P = host cores consecutive range shards, one single-threaded `vt normalize` process per shard with its
@@ -151,6 +181,11 @@ def cpu_reference_run(n_sample, steps, warmup, names=None, seqs=None, batch=None
                 times.append(dt)
         one = _run_procs(cmds[:1])
         view = _run_procs([[VT_REF, "view", os.path.join(tmp, "in0.vcf"), "-o", os.path.join(tmp, "view0.vcf")]])
+        if cli_out is not None:
+            try:
+                cli_out.update(cli_wall(tmp, fa, names, seqs, batch, min(n_sample, CLI_RECORDS)))
+            except Exception as e:
+                cli_out["error"] = str(e)[:400]
     finally:
         import shutil
         shutil.rmtree(tmp, ignore_errors=True)
@@ -1237,8 +1272,10 @@ def run_c2_c4(args, rank, world, local):
             line["sharded_c3"] = {"error": str(e)[:300]}
     if not args.no_cpu_baseline and world >= 1 and args.workload == "c2":
         try:
-            cv, cms, P, sample = cpu_reference_run(CPU_SAMPLE_RECORDS, 2, 1, names, seqs, batch)
+            cli = {}
+            cv, cms, P, sample = cpu_reference_run(CPU_SAMPLE_RECORDS, 2, 1, names, seqs, batch, cli_out=cli)
             line["cpu_baseline"] = {"value": cv, "unit": UNIT, "cores": P, "kind": "reference", "sample": sample}
+            line["e2e_cli"] = cli
         except Exception as e:  # the checker binary is missing on this box
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "unavailable: %s" % e}
     emit(line)

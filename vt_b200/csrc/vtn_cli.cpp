@@ -36,6 +36,34 @@ namespace
 {
 const char* VERSION = "0.5"; // normalize.cpp:88 / decompose.cpp:84
 
+// VTN_CLI_TIMING=1: wall-clock seconds per phase on stderr at the end of `vtn normalize` (where the command's time goes)
+struct PhaseTimer
+{
+    bool on = getenv("VTN_CLI_TIMING") != nullptr;
+    std::map<std::string, double> t;
+    std::vector<std::string> order;
+    double t0 = 0;
+    static double now()
+    {
+        timespec ts;
+        clock_gettime(CLOCK_MONOTONIC, &ts);
+        return ts.tv_sec + 1e-9 * ts.tv_nsec;
+    }
+    void start() { t0 = now(); }
+    void stop(const char* name)
+    {
+        const double x = now();
+        if (!t.count(name)) order.push_back(name);
+        t[name] += x - t0;
+        t0 = x;
+    }
+    void report()
+    {
+        if (!on) return;
+        for (const std::string& k : order) fprintf(stderr, "[vtn timing] %-22s %8.3f s\n", k.c_str(), t[k]);
+    }
+};
+
 typedef std::pair<const char*, size_t> Tok; // a slice of the current line
 
 struct Tag
@@ -625,9 +653,13 @@ int cmd_normalize(int argc, char** argv)
         fprintf(stderr, "         [d] debug                                           %s\n", a.debug ? "true" : "false");
         fprintf(stderr, "         [r] reference FASTA file                            %s\n\n", a.ref.c_str());
     }
+    PhaseTimer pt;
+    pt.start();
     vtn_ctx* ctx = nullptr;
     if (vtn_ctx_create(&ctx, a.device)) die(nullptr, "vtn_ctx_create");
+    pt.stop("context");
     if (vtn_ref_load_fasta(ctx, a.ref.c_str())) die(ctx, "loading the reference");
+    pt.stop("reference load");
     Reader rd;
     if (!rd.open(a.in))
     {
@@ -665,7 +697,9 @@ int cmd_normalize(int argc, char** argv)
     int last_wid = -1;
     while (more)
     {
+        pt.start();
         lp.read_batch(rd, line, more, BATCH, bb, ctx, true, rid_cache);
+        pt.stop("read + tokenize");
         vtn_batch in = bb.view();
         const size_t n = in.n_rec;
         status.resize(n + 1), vtype.resize(n + 1);
@@ -678,6 +712,7 @@ int cmd_normalize(int argc, char** argv)
         out.chg_rec = chg_rec.data(), out.chg_pos1 = chg_pos1.data(), out.chg_lt = chg_lt.data(), out.chg_le = chg_le.data();
         out.chg_rt = chg_rt.data(), out.chg_off = chg_off.data(), out.chg_bytes = chg_bytes.data();
         if (vtn_normalize(ctx, &in, &out)) die(ctx, "vtn_normalize");
+        pt.stop("normalize");
         size_t k = 0; // cursor in the changed list (input order)
         for (size_t r = 0; r < n; ++r)
         {
@@ -780,13 +815,18 @@ int cmd_normalize(int argc, char** argv)
             put_tail(o, h, col, extra);
             ow.write(std::move(rec));
         }
+        pt.stop("format records");
         ow.drain(false);
+        pt.stop("order + write");
         for (int c = 0; c < 5; ++c) tot.bi[c] += out.counters.bi[c], tot.multi[c] += out.counters.multi[c];
         tot.no_variants += out.counters.no_variants;
         tot.no_refs += out.counters.no_refs;
     }
+    pt.start();
     ow.drain(true);
     if (ow.out != stdout) fclose(ow.out);
+    pt.stop("order + write");
+    pt.report();
     if (print)
     { // print_stats, normalize.cpp:351-382
         const int32_t nb = tot.bi[0] + tot.bi[1] + tot.bi[2] + tot.bi[3] + tot.bi[4];
