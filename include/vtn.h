@@ -127,6 +127,15 @@ int vtn_host_free(vtn_ctx* ctx, void* p);
 /* ---- reference: replaces fai_load + faidx_fetch_* ---- */
 /* Load FASTA (+ .fai, built in memory when absent; plain or gzip/bgzip) and make it resident in HBM. */
 int vtn_ref_load_fasta(vtn_ctx* ctx, const char* fasta_path);
+/* The way the reference itself uses a FASTA (fai_load reads only the index, faidx_fetch_seq seeks into the file, variant_manip.cpp:35,
+ * 70): open the file and its index, reserve the HBM for the whole genome, and make a contig resident (packed by all host threads
+ * straight from the mapped file) the first time it is needed.  Every entry point that takes HOST contig ids (vtn_normalize,
+ * vtn_normalize_bi, vtn_decompose_normalize, vtn_dbatch_create*, vtn_annotate_indels, vtn_ref_fetch*) does that itself; a caller
+ * that builds device batches another way calls vtn_ref_require / vtn_ref_require_all first.  Contig ids, names and lengths are
+ * valid right after the open.  vtn_ref_load_fasta == vtn_ref_open_fasta + vtn_ref_require_all. */
+int vtn_ref_open_fasta(vtn_ctx* ctx, const char* fasta_path);
+int vtn_ref_require(vtn_ctx* ctx, int rid); /* no-op for a resident or unknown contig */
+int vtn_ref_require_all(vtn_ctx* ctx);
 /* Same from memory: contig c has raw FASTA bases seq[c][0..len[c]) (case preserved, any isgraph byte). */
 int vtn_ref_load_memory(vtn_ctx* ctx, int32_t n_contig, const char* const* names, const int64_t* len,
                         const uint8_t* const* seq);

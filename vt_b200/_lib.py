@@ -132,6 +132,9 @@ SIGNATURES = {
     "vtn_host_alloc": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]),
     "vtn_host_free": (C.c_int, [C.c_void_p, C.c_void_p]),
     "vtn_ref_load_fasta": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "vtn_ref_open_fasta": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "vtn_ref_require": (C.c_int, [C.c_void_p, C.c_int]),
+    "vtn_ref_require_all": (C.c_int, [C.c_void_p]),
     "vtn_ref_load_memory": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), c_i64p, C.POINTER(C.c_void_p)]),
     "vtn_ref_n_contig": (C.c_int, [C.c_void_p]),
     "vtn_ref_contig_id": (C.c_int, [C.c_void_p, C.c_char_p]),

@@ -229,6 +229,16 @@ class Context:
     def load_fasta(self, path):
         self._chk(self.lib.vtn_ref_load_fasta(self.h, path.encode()), "vtn_ref_load_fasta")
 
+    def open_fasta(self, path):
+        """index only; a contig becomes resident the first time a batch names it (vtn_ref_open_fasta)"""
+        self._chk(self.lib.vtn_ref_open_fasta(self.h, path.encode()), "vtn_ref_open_fasta")
+
+    def require(self, rid=None):
+        if rid is None:
+            self._chk(self.lib.vtn_ref_require_all(self.h), "vtn_ref_require_all")
+        else:
+            self._chk(self.lib.vtn_ref_require(self.h, int(rid)), "vtn_ref_require")
+
     def load_reference(self, names, seqs):
         """seqs: list of bytes / uint8 arrays with the raw FASTA bases of each contig"""
         arrs = [np.frombuffer(s, dtype=np.uint8) if isinstance(s, (bytes, bytearray)) else np.ascontiguousarray(s, np.uint8) for s in seqs]

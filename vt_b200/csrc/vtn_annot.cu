@@ -319,6 +319,8 @@ int vtn_ref_fetch_batch(vtn_ctx* ctx, uint32_t n, const int32_t* rid, const int6
     if (!ctx || !ctx->ref_loaded) return vtn_set_err(ctx, VTN_E_STATE, "no reference loaded");
     if (n && (!rid || !beg0 || !end0 || !off)) return vtn_set_err(ctx, VTN_E_ARG, "vtn_ref_fetch_batch: null arrays");
     VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (ctx->ref_missing)
+        if (int rc = vtn_ref_ensure(ctx, n, rid)) return rc;
     vta::FetchList L;
     for (uint32_t k = 0; k < n; ++k)
         L.add(rid[k], (rid[k] >= 0 && rid[k] < (int32_t)ctx->contigs.size()) ? ctx->contigs[rid[k]].len : -1, beg0[k] + 1, end0[k] + 1);
@@ -345,6 +347,8 @@ int vtn_annotate_indels(vtn_ctx* ctx, const vtn_batch* in, vtn_annot_result* out
     if (in->n_rec && (!in->pos1 || !in->rid || !in->allele_beg || !in->allele_off || !out->flags || !out->vtype || !out->indel_idx))
         return vtn_set_err(ctx, VTN_E_ARG, "vtn_annotate_indels: null arrays");
     VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (ctx->ref_missing)
+        if (int rc = vtn_ref_ensure(ctx, in->n_rec, in->rid)) return rc;
     DeviceBackend be(ctx);
     return vta::annotate_core(be, in, out, ctx->annot_trace);
 }

@@ -57,12 +57,8 @@ int vtn_ctx_destroy(vtn_ctx* ctx)
     if (ctx->scratch) vtn_dbatch_destroy(ctx, ctx->scratch);
     if (ctx->scratch_bi) vtn_dbatch_destroy(ctx, ctx->scratch_bi);
     vtn_hmm_ctx_release(ctx);
-    cudaFree(ctx->d_groups);
-    cudaFree(ctx->d_contig_goff);
-    cudaFree(ctx->d_contig_len);
-    cudaFree(ctx->d_exc_start);
-    cudaFree(ctx->d_exc_len);
-    cudaFree(ctx->d_exc_byte);
+    if (ctx->tok_cache) vtn_vcf_dtext_destroy(ctx, ctx->tok_cache);
+    vtn_ref_release(ctx);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
     cudaStreamDestroy(ctx->stream);
@@ -235,6 +231,7 @@ int vtn_dbatch_create(vtn_ctx* ctx, const vtn_batch* in, vtn_dbatch** db)
     int rc = check_batch(ctx, in);
     if (rc) return rc;
     VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (ctx->ref_missing && (rc = vtn_ref_ensure(ctx, in->n_rec, in->rid))) return rc;
     rc = vtn_dbatch_alloc(ctx, in->n_rec, in->n_allele, in->n_bytes, true, db);
     if (rc) return rc;
     rc = upload_inputs(ctx, in, *db, ctx->stream);
@@ -323,6 +320,7 @@ int vtn_normalize(vtn_ctx* ctx, const vtn_batch* in, vtn_norm_result* out)
     int rc = check_batch(ctx, in);
     if (rc) return rc;
     VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (ctx->ref_missing && (rc = vtn_ref_ensure(ctx, in->n_rec, in->rid))) return rc;
     rc = ensure_scratch(ctx, in->n_rec, in->n_allele, in->n_bytes);
     if (rc) return rc;
     vtn_dbatch* d = ctx->scratch;
@@ -485,6 +483,7 @@ static int decompose_host(vtn_ctx* ctx, const vtn_batch* in, uint32_t* src_rec, 
     int rc = check_batch(ctx, in);
     if (rc) return rc;
     VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (nout && ctx->ref_missing && (rc = vtn_ref_ensure(ctx, in->n_rec, in->rid))) return rc;
     rc = ensure_scratch(ctx, in->n_rec, in->n_allele, in->n_bytes);
     if (rc) return rc;
     vtn_dbatch* d = ctx->scratch;

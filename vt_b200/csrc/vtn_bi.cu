@@ -194,6 +194,7 @@ int vtn_dbatch_create_bi(vtn_ctx* ctx, const vtn_batch_bi* in, vtn_dbatch** db)
     int rc = check_bi(ctx, in);
     if (rc) return rc;
     VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (ctx->ref_missing && (rc = vtn_ref_ensure(ctx, in->n_run, in->run_rid))) return rc;
     rc = alloc_bi(ctx, in->n_rec, in->n_bytes, in->n_run, in->n_ext, db);
     if (rc) return rc;
     vtn_dbatch* d = *db;
@@ -302,6 +303,7 @@ int vtn_normalize_bi(vtn_ctx* ctx, const vtn_batch_bi* in, vtn_norm_result_bi* o
     int rc = check_bi(ctx, in);
     if (rc) return rc;
     VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (ctx->ref_missing && (rc = vtn_ref_ensure(ctx, in->n_run, in->run_rid))) return rc;
     if (!bi_fits(ctx->scratch_bi, in->n_rec, in->n_bytes, in->n_run, in->n_ext))
     {
         if (ctx->scratch_bi) vtn_dbatch_destroy(ctx, ctx->scratch_bi);

@@ -24,11 +24,15 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <condition_variable>
 #include <cstring>
 #include <ctime>
+#include <deque>
 #include <list>
 #include <map>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 #include "../../include/vtn.h"
 
@@ -633,6 +637,322 @@ struct LineParser
 };
 
 // ------------------------------------------------------------------------------------------------------------
+// Host pipeline of `normalize`: the file is read in blocks of whole lines by a reader thread, a block is tokenized and
+// normalized on the device, its records are formatted by all host threads (a record the run does not touch is passed through as the bytes
+// it came in with), ordered on the device and written with one write per block.
+// ------------------------------------------------------------------------------------------------------------
+unsigned host_threads()
+{
+    unsigned n = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    if (const char* e = getenv("VTN_HOST_THREADS"))
+        if (atoi(e) > 0) n = (unsigned)atoi(e);
+    return n;
+}
+
+// fn(t, lo, hi) over [0, n) split into one contiguous range per thread (ranges in thread order)
+template <class F>
+void parallel_ranges(size_t n, unsigned nthr, F fn)
+{
+    nthr = (unsigned)std::max<size_t>(1, std::min<size_t>(nthr, (n + 4095) / 4096));
+    if (nthr == 1)
+    {
+        fn(0u, (size_t)0, n);
+        return;
+    }
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t < nthr; ++t) th.emplace_back([=]() { fn(t, n * t / nthr, n * (t + 1) / nthr); });
+    for (auto& x : th) x.join();
+}
+
+struct TextBlock
+{
+    std::vector<char> text; // whole lines, each ended by '\n' ("\r\n" already reduced to '\n')
+    size_t n = 0, n_lines = 0, n_commas = 0;
+};
+
+// Reads the record lines of a VCF in blocks (target_bytes of whole lines, at most max_lines lines) on its own thread, two blocks ahead.
+struct BlockReader
+{
+    gzFile f = nullptr;
+    size_t target_bytes = 32u << 20, max_lines = 0;
+    std::vector<char> pend; // read but not handed out yet
+    TextBlock blocks[3];
+    std::deque<TextBlock*> free_q, ready_q;
+    std::mutex m;
+    std::condition_variable cv;
+    std::thread th;
+    bool done = false, stop = false;
+
+    void start(gzFile file, const std::string& first_line, bool have_first)
+    {
+        f = file;
+        if (have_first)
+        {
+            pend.assign(first_line.begin(), first_line.end());
+            pend.push_back('\n');
+        }
+        else
+            done = true;
+        for (auto& b : blocks) free_q.push_back(&b);
+        if (!done) th = std::thread([this]() { run(); });
+    }
+    ~BlockReader()
+    {
+        {
+            std::lock_guard<std::mutex> g(m);
+            stop = true;
+        }
+        cv.notify_all();
+        if (th.joinable()) th.join();
+    }
+    TextBlock* next() // nullptr at the end of the file
+    {
+        std::unique_lock<std::mutex> g(m);
+        cv.wait(g, [&]() { return !ready_q.empty() || done; });
+        if (ready_q.empty()) return nullptr;
+        TextBlock* b = ready_q.front();
+        ready_q.pop_front();
+        return b;
+    }
+    void release(TextBlock* b)
+    {
+        {
+            std::lock_guard<std::mutex> g(m);
+            free_q.push_back(b);
+        }
+        cv.notify_all();
+    }
+    void run()
+    {
+        bool eof = false;
+        for (;;)
+        {
+            TextBlock* b = nullptr;
+            {
+                std::unique_lock<std::mutex> g(m);
+                cv.wait(g, [&]() { return !free_q.empty() || stop; });
+                if (stop) return;
+                b = free_q.front();
+                free_q.pop_front();
+            }
+            std::vector<char>& t = b->text;
+            size_t want = std::max(target_bytes, pend.size());
+            if (t.size() < want + 2) t.resize(want + 2);
+            memcpy(t.data(), pend.data(), pend.size());
+            size_t n = pend.size(), cut = 0;
+            pend.clear();
+            for (;;)
+            {
+                while (!eof && n < want)
+                {
+                    const int got = gzread(f, t.data() + n, (unsigned)std::min<size_t>(want - n, 1u << 30));
+                    if (got <= 0)
+                        eof = true;
+                    else
+                        n += (size_t)got;
+                }
+                if (eof)
+                {
+                    if (n && t[n - 1] != '\n') t[n++] = '\n';
+                    cut = n;
+                    break;
+                }
+                const void* nl = memrchr(t.data(), '\n', n);
+                if (nl)
+                {
+                    cut = (size_t)((const char*)nl - t.data()) + 1;
+                    break;
+                }
+                want *= 2; // one line longer than the block: keep reading
+                t.resize(want + 2);
+            }
+            if (max_lines)
+            { // VTN_CLI_BATCH: at most that many lines per block
+                size_t lines = 0, p = 0;
+                while (p < cut && lines < max_lines)
+                {
+                    const void* nl = memchr(t.data() + p, '\n', cut - p);
+                    p = (size_t)((const char*)nl - t.data()) + 1;
+                    ++lines;
+                }
+                cut = p;
+            }
+            pend.assign(t.begin() + cut, t.begin() + n);
+            n = cut;
+            if (memchr(t.data(), '\r', n))
+            { // "\r\n" -> "\n" (the reference's reader drops the '\r' with the line end)
+                size_t w = 0;
+                for (size_t r = 0; r < n; ++r)
+                    if (!(t[r] == '\r' && r + 1 < n && t[r + 1] == '\n')) t[w++] = t[r];
+                n = w;
+            }
+            b->n = n;
+            b->n_lines = (size_t)std::count(t.data(), t.data() + n, '\n');
+            b->n_commas = (size_t)std::count(t.data(), t.data() + n, ',');
+            const bool last = eof && pend.empty();
+            {
+                std::lock_guard<std::mutex> g(m);
+                if (n) ready_q.push_back(b);
+                if (last) done = true;
+            }
+            cv.notify_all();
+            if (last) return;
+        }
+    }
+};
+
+// true when htslib would print the columns from QUAL on exactly as they were read: QUAL "." or a short integer, no Float-typed INFO /
+// FORMAT value to re-serialise, no empty INFO field to drop, every sample with as many values as FORMAT has keys (put_tail)
+bool tail_is_plain(const char* p, size_t n, bool float_info, bool float_fmt)
+{
+    size_t i = 0;
+    while (i < n && p[i] != '\t') ++i;
+    if (!(i == 1 && p[0] == '.'))
+    {
+        if (i == 0 || i > 6 || (i > 1 && p[0] == '0')) return false;
+        for (size_t k = 0; k < i; ++k)
+            if (p[k] < '0' || p[k] > '9') return false;
+    }
+    if (i >= n) return false;
+    ++i;
+    while (i < n && p[i] != '\t') ++i; // FILTER
+    if (i >= n) return false;
+    const size_t i0 = ++i;
+    while (i < n && p[i] != '\t')
+    {
+        if (p[i] == ';' && (i == i0 || i + 1 == n || p[i + 1] == ';' || p[i + 1] == '\t')) return false;
+        ++i;
+    }
+    if (i == i0) return false;
+    if (!(i - i0 == 1 && p[i0] == '.') && float_info) return false;
+    if (i >= n) return true; // sites only
+    if (float_fmt) return false;
+    size_t keys = 1;
+    ++i;
+    while (i < n && p[i] != '\t') keys += p[i++] == ':';
+    while (i < n)
+    {
+        size_t vals = 1;
+        ++i;
+        while (i < n && p[i] != '\t') vals += p[i++] == ':';
+        if (vals != keys) return false;
+    }
+    return true;
+}
+
+// BCFOrderedWriter (bcf_ordered_writer.cpp:141-300) over record VIEWS: a record is (contig id of the output header, POS, pointer, length
+// with its '\n'); the order comes from the device (vtn_writer_order) once per block, the bytes are gathered by all host threads into one
+// buffer and written with one call.  Records still inside the reference writer's buffer after a block are copied and replayed in
+// front of the next block, as DeviceWriter does.
+struct FastWriter
+{
+    FILE* out = stdout;
+    int window = 0;
+    vtn_ctx* ctx = nullptr;
+    unsigned nthr = 1;
+    std::vector<int32_t> rid, pos, late;
+    std::vector<const char*> ptr;
+    std::vector<uint32_t> len, order;
+    std::vector<uint64_t> ooff;
+    std::vector<char> obuf, carry_text;
+    size_t n_carry = 0;
+    // room for n_new records after the carried ones; the caller fills rid/pos/ptr/len at [base(), base() + n_new)
+    size_t begin(size_t n_new)
+    {
+        const size_t n = n_carry + n_new;
+        rid.resize(n), pos.resize(n), ptr.resize(n), len.resize(n);
+        return n_carry;
+    }
+    // msgs: (index among the new records, stderr text) ascending
+    void drain(size_t n_new, const std::vector<std::pair<uint32_t, std::string>>& msgs, bool final)
+    {
+        const size_t n = n_carry + n_new;
+        rid.resize(n), pos.resize(n), ptr.resize(n), len.resize(n);
+        if (!n) return;
+        size_t done = n;
+        uint32_t n_pending = 0;
+        const bool ordered = window > 0;
+        if (ordered)
+        {
+            late.resize(n), order.resize(n);
+            if (vtn_writer_order(ctx, (uint32_t)n, rid.data(), pos.data(), window, order.data(), late.data(), &n_pending))
+            {
+                fprintf(stderr, "[vtn] vtn_writer_order: %s\n", vtn_last_error(ctx));
+                exit(1);
+            }
+            if (!final) done = n - n_pending;
+        }
+        size_t mi = 0;
+        for (size_t k = n_carry; k < n; ++k)
+        { // stderr in arrival order: the record's own messages, then the writer's warning for it
+            const bool has_msg = mi < msgs.size() && msgs[mi].first == k - n_carry;
+            const bool is_late = ordered && late[k] != INT32_MIN;
+            if (has_msg) fputs(msgs[mi++].second.c_str(), stderr);
+            if (is_late)
+            { // bcf_ordered_writer.cpp:163-179
+                const int32_t front = late[k], cutoff = std::max(front - window, 1);
+                const char* tab = (const char*)memchr(ptr[k], '\t', len[k]);
+                std::string chrom(ptr[k], tab ? (size_t)(tab - ptr[k]) : 0);
+                fprintf(stderr, "[bcf_ordered_writer.cpp:170 write] Might not be sorted for window size %d at current record %s:%d < %d (%d [last record] - %d), please increase window size to at least %d.\n",
+                        window, chrom.c_str(), pos[k], cutoff, front, window, front - pos[k] + 1);
+            }
+        }
+        // gather the first `done` records of the order
+        ooff.resize(done + 1);
+        uint64_t tot = 0;
+        for (size_t k = 0; k < done; ++k)
+        {
+            ooff[k] = tot;
+            tot += len[ordered ? order[k] : k];
+        }
+        ooff[done] = tot;
+        if (obuf.size() < tot) obuf.resize(tot);
+        parallel_ranges(done, nthr, [&](unsigned, size_t lo, size_t hi) {
+            size_t k = lo;
+            while (k < hi)
+            { // runs of records that are neighbours in memory (an untouched stretch of the input) move with one copy
+                const size_t i = ordered ? order[k] : k;
+                const char* p = ptr[i];
+                size_t l = len[i], e = k + 1;
+                while (e < hi)
+                {
+                    const size_t j = ordered ? order[e] : e;
+                    if (ptr[j] != p + l) break;
+                    l += len[j];
+                    ++e;
+                }
+                memcpy(obuf.data() + ooff[k], p, l);
+                k = e;
+            }
+        });
+        if (tot && fwrite(obuf.data(), 1, tot, out) != tot)
+        {
+            fprintf(stderr, "[vtn] write error\n");
+            exit(1);
+        }
+        // what stays inside the buffer: copied, in arrival order, in front of the next block
+        std::vector<uint32_t> keep;
+        if (ordered) keep.assign(order.begin() + done, order.end());
+        std::sort(keep.begin(), keep.end());
+        std::vector<char> nt;
+        std::vector<uint64_t> noff;
+        std::vector<int32_t> nr, np;
+        std::vector<uint32_t> nl;
+        for (uint32_t k : keep)
+        {
+            noff.push_back(nt.size());
+            nt.insert(nt.end(), ptr[k], ptr[k] + len[k]);
+            nr.push_back(rid[k]), np.push_back(pos[k]), nl.push_back(len[k]);
+        }
+        carry_text.swap(nt);
+        n_carry = keep.size();
+        rid.assign(nr.begin(), nr.end()), pos.assign(np.begin(), np.end()), len.assign(nl.begin(), nl.end());
+        ptr.resize(n_carry);
+        for (size_t k = 0; k < n_carry; ++k) ptr[k] = carry_text.data() + noff[k];
+    }
+};
+
+// ------------------------------------------------------------------------------------------------------------
 // normalize  (Igor::normalize, normalize.cpp:174-330)
 // ------------------------------------------------------------------------------------------------------------
 int cmd_normalize(int argc, char** argv)
@@ -658,8 +978,8 @@ int cmd_normalize(int argc, char** argv)
     vtn_ctx* ctx = nullptr;
     if (vtn_ctx_create(&ctx, a.device)) die(nullptr, "vtn_ctx_create");
     pt.stop("context");
-    if (vtn_ref_load_fasta(ctx, a.ref.c_str())) die(ctx, "loading the reference");
-    pt.stop("reference load");
+    if (vtn_ref_open_fasta(ctx, a.ref.c_str())) die(ctx, "loading the reference");
+    pt.stop("reference open");
     Reader rd;
     if (!rd.open(a.in))
     {
@@ -673,35 +993,86 @@ int cmd_normalize(int argc, char** argv)
         fprintf(stderr, "[vtn] %s has no VCF header\n", a.in.c_str());
         return 1;
     }
-    DeviceWriter ow;
+    const unsigned nthr = host_threads();
+    FastWriter ow;
     ow.out = open_out(a.out);
     ow.window = a.window;
     ow.ctx = ctx;
+    ow.nthr = nthr;
     write_header(ow.out, h, "##INFO=<ID=OLD_VARIANT,Number=.,Type=String,Description=\"Original chr:pos:ref:alt encoding\">");
+    bool float_info = false, float_fmt = false;
+    for (const auto& kv : h.info) float_info = float_info || kv.second.type == 'F';
+    for (const auto& kv : h.fmt) float_fmt = float_fmt || kv.second.type == 'F';
 
-    size_t BATCH = 1u << 20;
+    BlockReader br;
     if (const char* e = getenv("VTN_CLI_BATCH")) // records per device batch (tests use a small one to exercise the carry-over)
-        if (atol(e) > 0) BATCH = (size_t)atol(e);
-    BatchBuf bb;
-    std::map<std::string, int> rid_cache;
-    std::vector<uint8_t> status, vtype, chg_bytes;
-    std::vector<uint32_t> chg_rec, chg_lt, chg_le, chg_rt;
-    std::vector<int32_t> chg_pos1;
-    std::vector<uint64_t> chg_off;
+        if (atol(e) > 0) br.max_lines = (size_t)atol(e);
+    if (const char* e = getenv("VTN_CLI_BLOCK_MB"))
+        if (atol(e) > 0) br.target_bytes = (size_t)atol(e) << 20;
+    br.start(rd.f, line, !line.empty());
+
+    std::map<std::string, int> rid_cache, writer_ids;
+    std::vector<uint64_t> line_off, chg_off;
+    std::vector<uint32_t> chrom_len, tail_off, allele_beg, allele_off, chg_rec, chg_lt, chg_le, chg_rt;
+    std::vector<int32_t> pos1, rid, wid, chg_pos1;
+    std::vector<uint8_t> tstatus, bytes, status, vtype, chg_bytes;
+    std::vector<std::string> arena(nthr);
+    std::vector<std::vector<uint32_t>> arena_recs(nthr);
+    std::vector<std::pair<uint32_t, std::string>> msgs;
     vtn_norm_counters tot;
     memset(&tot, 0, sizeof tot);
-    bool more = !line.empty();
-    LineParser lp;
-    std::map<std::string, int> writer_ids;
     std::string last_chrom;
-    int last_wid = -1;
-    while (more)
+    int last_rid = -1, last_wid = -1;
+    std::vector<int> new_contigs;
+    pt.stop("open + header");
+    while (TextBlock* blk = br.next())
     {
-        pt.start();
-        lp.read_batch(rd, line, more, BATCH, bb, ctx, true, rid_cache);
-        pt.stop("read + tokenize");
-        vtn_batch in = bb.view();
-        const size_t n = in.n_rec;
+        pt.stop("wait for reader");
+        const char* text = blk->text.data();
+        const size_t n = blk->n_lines;
+        line_off.resize(n + 1), chrom_len.resize(n), tail_off.resize(n), tstatus.resize(n), pos1.resize(n), allele_beg.resize(n + 1);
+        allele_off.resize(blk->n_commas + 2 * n + 1), bytes.resize(blk->n + 1);
+        vtn_vcf_fields f;
+        memset(&f, 0, sizeof f);
+        f.cap_rec = (uint32_t)n, f.cap_allele = (uint32_t)(blk->n_commas + 2 * n), f.cap_bytes = blk->n;
+        f.line_off = line_off.data(), f.chrom_len = chrom_len.data(), f.pos1 = pos1.data(), f.tail_off = tail_off.data();
+        f.status = tstatus.data(), f.allele_beg = allele_beg.data(), f.allele_off = allele_off.data(), f.bytes = bytes.data();
+        if (vtn_vcf_tokenize(ctx, text, blk->n, &f)) die(ctx, "vtn_vcf_tokenize");
+        pt.stop("tokenize");
+        // contig ids, once per run of equal CHROM: the FASTA's for the kernel, the order of appearance for the writer (the ordered writer
+        // flushes when the record's header-dictionary id changes, bcf_ordered_writer.cpp:185-189; the FASTA id cannot stand in for it:
+        // contigs the FASTA lacks all have id -1 there, and two of them in a row must still flush)
+        rid.resize(n), wid.resize(n);
+        for (size_t r = 0; r < n; ++r)
+        {
+            const char* c = text + line_off[r];
+            if (tstatus[r])
+            {
+                fprintf(stderr, "[vtn] malformed VCF record (fewer than 8 columns): %.*s\n", (int)(line_off[r + 1] - line_off[r] - 1), c);
+                exit(1);
+            }
+            if (!(last_chrom.size() == chrom_len[r] && !memcmp(last_chrom.data(), c, chrom_len[r])) || last_wid < 0)
+            {
+                last_chrom.assign(c, chrom_len[r]);
+                auto it = rid_cache.find(last_chrom);
+                if (it == rid_cache.end())
+                {
+                    it = rid_cache.emplace(last_chrom, vtn_ref_contig_id(ctx, last_chrom.c_str())).first;
+                    if (it->second >= 0) new_contigs.push_back(it->second);
+                }
+                last_rid = it->second;
+                last_wid = writer_ids.emplace(last_chrom, (int)writer_ids.size()).first->second;
+            }
+            rid[r] = last_rid, wid[r] = last_wid;
+        }
+        pt.stop("contig ids");
+        for (int c : new_contigs) // first record on this contig: its bases become resident now
+            if (vtn_ref_require(ctx, c)) die(ctx, "loading the reference");
+        new_contigs.clear();
+        pt.stop("reference load");
+        vtn_batch in;
+        in.n_rec = (uint32_t)n, in.n_allele = f.n_allele, in.n_bytes = f.n_bytes;
+        in.pos1 = pos1.data(), in.rid = rid.data(), in.allele_beg = allele_beg.data(), in.allele_off = allele_off.data(), in.bytes = bytes.data();
         status.resize(n + 1), vtype.resize(n + 1);
         chg_rec.resize(n + 1), chg_lt.resize(n + 1), chg_le.resize(n + 1), chg_rt.resize(n + 1), chg_pos1.resize(n + 1);
         chg_off.resize(n + 2), chg_bytes.resize(in.n_bytes + 16);
@@ -713,117 +1084,152 @@ int cmd_normalize(int argc, char** argv)
         out.chg_rt = chg_rt.data(), out.chg_off = chg_off.data(), out.chg_bytes = chg_bytes.data();
         if (vtn_normalize(ctx, &in, &out)) die(ctx, "vtn_normalize");
         pt.stop("normalize");
-        size_t k = 0; // cursor in the changed list (input order)
+
+        // records whose REF disagrees with the FASTA (rare): their stderr text, and the first one that ends the run
+        msgs.clear();
+        size_t n_fmt = n;
+        std::string fatal;
         for (size_t r = 0; r < n; ++r)
         {
-            const std::string& ln = bb.lines[r];
-            std::vector<Tok> col = split(ln.data(), ln.size(), '\t');
             const uint8_t st = status[r];
-            const uint32_t a0 = in.allele_beg[r], a1 = in.allele_beg[r + 1];
-            const int code = st & VTN_ST_REFCODE_MASK;
-            std::string chrom(col[0].first, col[0].second);
-            std::string msg;
+            if (!(st & (VTN_ST_FETCH_FAIL | VTN_ST_REFCODE_MASK))) continue;
+            const char* L = text + line_off[r];
+            const std::string chrom(L, chrom_len[r]);
+            const uint32_t a0 = allele_beg[r];
+            const int64_t rl = (int64_t)(allele_off[a0 + 1] - allele_off[a0]);
+            const char* ref = (const char*)bytes.data() + allele_off[a0];
             if (st & VTN_ST_FETCH_FAIL)
             { // faidx_fetch_seq returned NULL: variant_manip.cpp:70-75
-                ow.drain(false); // what the sequential writer had written / printed before this record
-                fprintf(stderr, "[E::faidx_adjust_position] The sequence \"%s\" was not found\n", chrom.c_str());
-                fprintf(stderr, "[variant_manip.cpp:72 is_not_ref_consistent] failure to extract base from fasta file: %s:%d-%d\n",
-                        chrom.c_str(), in.pos1[r] - 1, in.pos1[r] - 1 + (int)col[3].second - 1);
-                fprintf(stderr, "FAQ: http://genome.sph.umich.edu/wiki/Vt#1._vt_cannot_retrieve_sequences_from_my_reference_sequence_file\n");
-                exit(1);
+                char b[512];
+                fatal = "[E::faidx_adjust_position] The sequence \"" + chrom + "\" was not found\n";
+                snprintf(b, sizeof b, "[variant_manip.cpp:72 is_not_ref_consistent] failure to extract base from fasta file: %s:%d-%d\n", chrom.c_str(),
+                         pos1[r] - 1, pos1[r] - 1 + (int)rl - 1);
+                fatal += b;
+                fatal += "FAQ: http://genome.sph.umich.edu/wiki/Vt#1._vt_cannot_retrieve_sequences_from_my_reference_sequence_file\n";
+                n_fmt = r;
+                break;
             }
-            if (code)
-            { // variant_manip.cpp:94-98 then normalize.cpp:205-215
-                const int64_t pos0 = in.pos1[r] - 1, rl = (int64_t)col[3].second;
-                std::vector<uint8_t> fa((size_t)rl + 1, 0);
-                int64_t got = vtn_ref_fetch(ctx, in.rid[r], pos0, pos0 + rl - 1, 0, fa.data(), rl);
-                char hdrbuf[256];
-                snprintf(hdrbuf, sizeof hdrbuf, "[variant_manip.cpp:96 is_not_ref_consistent] reference bases not consistent: %s:%d-%d  ", chrom.c_str(), (int)pos0, (int)(pos0 + rl - 1));
-                msg = hdrbuf;
-                msg.append(col[3].first, (size_t)rl);
-                msg += "(REF) vs ";
-                msg.append((const char*)fa.data(), (size_t)(got > 0 ? got : 0));
-                msg += "(FASTA)\n";
-                if (code > 2 - strict_level)
-                {
-                    ow.drain(false);
-                    fputs(msg.c_str(), stderr);
-                    fprintf(stderr, "[normalize.cpp:209 normalize] Normalization not performed due to inconsistent reference sequences. (use -n or -m option to relax this)\n");
-                    exit(1);
-                }
-                msg += "[normalize.cpp:214 normalize] Normalization skipped due to inconsistent reference sequences\n";
-            }
-            DeviceWriter::Rec rec;
-            rec.msg = std::move(msg);
-            // the ordered writer flushes when the record's header-dictionary id changes (bcf_ordered_writer.cpp:185-189); the FASTA id
-            // cannot stand in for it: contigs the FASTA lacks all have id -1 there, and two of them in a row must still flush
-            if (chrom != last_chrom)
+            const int code = st & VTN_ST_REFCODE_MASK;
+            // variant_manip.cpp:94-98 then normalize.cpp:205-215
+            const int64_t pos0 = pos1[r] - 1;
+            std::vector<uint8_t> fa((size_t)rl + 1, 0);
+            const int64_t got = vtn_ref_fetch(ctx, rid[r], pos0, pos0 + rl - 1, 0, fa.data(), rl);
+            char hdrbuf[256];
+            snprintf(hdrbuf, sizeof hdrbuf, "[variant_manip.cpp:96 is_not_ref_consistent] reference bases not consistent: %s:%d-%d  ", chrom.c_str(), (int)pos0, (int)(pos0 + rl - 1));
+            std::string msg = hdrbuf;
+            msg.append(ref, (size_t)rl);
+            msg += "(REF) vs ";
+            msg.append((const char*)fa.data(), (size_t)(got > 0 ? got : 0));
+            msg += "(FASTA)\n";
+            if (code > 2 - strict_level)
             {
-                last_chrom = chrom;
-                last_wid = writer_ids.emplace(chrom, (int)writer_ids.size()).first->second;
+                fatal = msg + "[normalize.cpp:209 normalize] Normalization not performed due to inconsistent reference sequences. (use -n or -m option to relax this)\n";
+                n_fmt = r;
+                break;
             }
-            rec.rid = last_wid;
-            rec.chrom = chrom;
-            rec.pos1 = in.pos1[r];
-            std::string& o = rec.line;
-            o.reserve(ln.size() + 64);
-            const bool changed = (st & VTN_ST_CHANGED) && k < out.n_changed && chg_rec[k] == r;
-            std::string extra;
-            if (changed)
-            {
-                // OLD_VARIANT = CHROM:POS:REF/ALT.. of the record after the in-place upper-casing (normalize.cpp:241-243)
-                extra = "OLD_VARIANT=" + chrom + ":" + std::to_string(in.pos1[r]) + ":";
-                for (uint32_t s = a0; s < a1; ++s)
-                {
-                    if (s > a0) extra.push_back('/');
-                    for (uint32_t q = in.allele_off[s]; q < in.allele_off[s + 1]; ++q) extra.push_back((char)toupper(in.bytes[q]));
-                }
-                rec.pos1 = chg_pos1[k];
-                o += chrom;
-                o.push_back('\t');
-                o += std::to_string(rec.pos1);
-                o.push_back('\t');
-                o.append(col[2].first, col[2].second);
-                uint64_t q = chg_off[k];
-                for (uint32_t s = a0; s < a1; ++s)
-                {
-                    const uint32_t old_len = in.allele_off[s + 1] - in.allele_off[s];
-                    const uint32_t new_len = old_len - chg_rt[k] + chg_le[k] - chg_lt[k];
-                    o.push_back(s == a0 ? '\t' : (s == a0 + 1 ? '\t' : ','));
-                    o.append((const char*)chg_bytes.data() + q, new_len);
-                    q += new_len;
-                }
-                ++k;
-            }
-            else
-            {
-                o.append(col[0].first, col[0].second);
-                o.push_back('\t');
-                o.append(col[1].first, col[1].second);
-                o.push_back('\t');
-                o.append(col[2].first, col[2].second);
-                o.push_back('\t');
-                size_t b0 = o.size();
-                o.append(col[3].first, col[3].second);
-                o.push_back('\t');
-                o.append(col[4].first, col[4].second);
-                // entered the trim path but came out unchanged: the alleles were upper-cased in place and the VCF text
-                // writer prints them that way
-                if (st & VTN_ST_ENTERED)
-                    for (size_t q = b0; q < o.size(); ++q) o[q] = (char)toupper(o[q]);
-            }
-            put_tail(o, h, col, extra);
-            ow.write(std::move(rec));
+            msg += "[normalize.cpp:214 normalize] Normalization skipped due to inconsistent reference sequences\n";
+            msgs.emplace_back((uint32_t)r, std::move(msg));
         }
+        pt.stop("reference messages");
+
+        const size_t base = ow.begin(n_fmt);
+        int32_t* o_rid = ow.rid.data() + base;
+        int32_t* o_pos = ow.pos.data() + base;
+        const char** o_ptr = ow.ptr.data() + base;
+        uint32_t* o_len = ow.len.data() + base;
+        const uint32_t n_changed = out.n_changed;
+        parallel_ranges(n_fmt, nthr, [&](unsigned t, size_t lo, size_t hi) {
+            std::string& o = arena[t];
+            std::vector<uint32_t>& mine = arena_recs[t];
+            o.clear(), mine.clear();
+            size_t k = (size_t)(std::lower_bound(chg_rec.begin(), chg_rec.begin() + n_changed, (uint32_t)lo) - chg_rec.begin());
+            for (size_t r = lo; r < hi; ++r)
+            {
+                const char* L = text + line_off[r];
+                const size_t ll = (size_t)(line_off[r + 1] - line_off[r]); // with the '\n'
+                const uint8_t st = status[r];
+                const bool changed = (st & VTN_ST_CHANGED) && k < n_changed && chg_rec[k] == r;
+                o_rid[r] = wid[r];
+                o_pos[r] = pos1[r];
+                if (!changed && !(st & VTN_ST_ENTERED) && tail_is_plain(L + tail_off[r], ll - 1 - tail_off[r], float_info, float_fmt))
+                {
+                    o_ptr[r] = L;
+                    o_len[r] = (uint32_t)ll;
+                    continue;
+                }
+                const size_t o0 = o.size();
+                const std::vector<Tok> col = split(L, ll - 1, '\t');
+                const uint32_t a0 = allele_beg[r], a1 = allele_beg[r + 1];
+                std::string extra;
+                if (changed)
+                {
+                    // OLD_VARIANT = CHROM:POS:REF/ALT.. of the record after the in-place upper-casing (normalize.cpp:241-243)
+                    extra = "OLD_VARIANT=";
+                    extra.append(col[0].first, col[0].second);
+                    extra += ":" + std::to_string(pos1[r]) + ":";
+                    for (uint32_t s = a0; s < a1; ++s)
+                    {
+                        if (s > a0) extra.push_back('/');
+                        for (uint32_t q = allele_off[s]; q < allele_off[s + 1]; ++q) extra.push_back((char)toupper(bytes[q]));
+                    }
+                    o_pos[r] = chg_pos1[k];
+                    o.append(col[0].first, col[0].second);
+                    o.push_back('\t');
+                    o += std::to_string(chg_pos1[k]);
+                    o.push_back('\t');
+                    o.append(col[2].first, col[2].second);
+                    uint64_t q = chg_off[k];
+                    for (uint32_t s = a0; s < a1; ++s)
+                    {
+                        const uint32_t old_len = allele_off[s + 1] - allele_off[s];
+                        const uint32_t new_len = old_len - chg_rt[k] + chg_le[k] - chg_lt[k];
+                        o.push_back(s == a0 ? '\t' : (s == a0 + 1 ? '\t' : ','));
+                        o.append((const char*)chg_bytes.data() + q, new_len);
+                        q += new_len;
+                    }
+                    ++k;
+                }
+                else
+                {
+                    o.append(col[0].first, col[0].second);
+                    o.push_back('\t');
+                    o.append(col[1].first, col[1].second);
+                    o.push_back('\t');
+                    o.append(col[2].first, col[2].second);
+                    o.push_back('\t');
+                    const size_t b0 = o.size();
+                    o.append(col[3].first, col[3].second);
+                    o.push_back('\t');
+                    o.append(col[4].first, col[4].second);
+                    // entered the trim path but came out unchanged: the alleles were upper-cased in place and the VCF text
+                    // writer prints them that way
+                    if (st & VTN_ST_ENTERED)
+                        for (size_t q = b0; q < o.size(); ++q) o[q] = (char)toupper(o[q]);
+                }
+                put_tail(o, h, col, extra);
+                o.push_back('\n');
+                o_ptr[r] = (const char*)(uintptr_t)o0; // an offset until the arena stops growing
+                o_len[r] = (uint32_t)(o.size() - o0);
+                mine.push_back((uint32_t)r);
+            }
+            for (uint32_t r : mine) o_ptr[r] = o.data() + (uintptr_t)o_ptr[r];
+        });
         pt.stop("format records");
-        ow.drain(false);
+        ow.drain(n_fmt, msgs, false);
         pt.stop("order + write");
+        if (!fatal.empty())
+        {
+            fputs(fatal.c_str(), stderr);
+            exit(1);
+        }
+        br.release(blk);
         for (int c = 0; c < 5; ++c) tot.bi[c] += out.counters.bi[c], tot.multi[c] += out.counters.multi[c];
         tot.no_variants += out.counters.no_variants;
         tot.no_refs += out.counters.no_refs;
     }
     pt.start();
-    ow.drain(true);
+    ow.drain(0, {}, true);
+
     if (ow.out != stdout) fclose(ow.out);
     pt.stop("order + write");
     pt.report();

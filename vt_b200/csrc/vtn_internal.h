@@ -178,6 +178,8 @@ struct vtn_ctx
     int64_t ref_bytes = 0;
     uint64_t ref_n_groups = 0; // 16-byte groups behind d_groups (vtn_ref_clone)
     bool ref_loaded = false;
+    struct VtnRefSource* ref_src = nullptr; // a FASTA opened by vtn_ref_open_fasta whose contigs load on first use (vtn_ref.cu)
+    uint32_t ref_missing = 0;               // contigs of ref_src that are not resident yet; 0 for an eagerly loaded reference
     // reusable device arena for the host-buffer call
     vtn_dbatch* scratch = nullptr;
     vtn_dbatch* scratch_bi = nullptr; // the same for vtn_normalize_bi
@@ -188,9 +190,12 @@ struct vtn_ctx
     size_t hmm_scratch_bytes = 0;
     unsigned* hmm_counter = nullptr;
     std::string annot_trace; // vtn_annot_set_trace
+    struct vtn_vcf_dtext* tok_cache = nullptr; // device buffers of the host-buffer vtn_vcf_tokenize call, kept between calls
 };
 void vtn_hmm_ctx_release(vtn_ctx* ctx);
-int vtn_ref_clone(vtn_ctx* dst, const vtn_ctx* src); // replicate src's resident reference on dst's device (peer copies)
+void vtn_ref_release(vtn_ctx* ctx); // frees the resident reference and a lazily opened FASTA (vtn_ctx_destroy)
+int vtn_ref_clone(vtn_ctx* dst, const vtn_ctx* src);
+int vtn_ref_ensure(vtn_ctx* ctx, uint64_t n, const int32_t* rid); // lazy reference: make every contig named in rid[] resident // replicate src's resident reference on dst's device (peer copies)
 void vtn_uniq_dbatch_release(vtn_dbatch* d);
 void vtn_order_dbatch_release(vtn_dbatch* d);
 void vtn_blocksub_dbatch_release(vtn_dbatch* d);

@@ -306,7 +306,7 @@ __global__ void __launch_bounds__(VTK_THREADS) vtk_alleles_kernel(const uint8_t*
 // ---- device-resident text + output buffers sized by the caller's capacities ----
 struct vtn_vcf_dtext
 {
-    uint64_t n_text = 0;
+    uint64_t n_text = 0, cap_text = 0;
     bool open_tail = false;
     uint32_t cap_rec = 0, cap_allele = 0;
     uint64_t cap_bytes = 0;
@@ -333,24 +333,23 @@ int vtn_vcf_dtext_destroy(vtn_ctx* ctx, vtn_vcf_dtext* h)
     return VTN_OK;
 }
 
-int vtn_vcf_dtext_create(vtn_ctx* ctx, const char* text, uint64_t n_text, uint32_t cap_rec, uint32_t cap_allele, uint64_t cap_bytes,
-                         vtn_vcf_dtext** out)
+namespace
 {
-    if (!ctx || !out || (n_text && !text)) return vtn_set_err(ctx, VTN_E_ARG, "vtn_vcf_dtext_create: bad arguments");
-    if (n_text >= (1ull << 32)) return vtn_set_err(ctx, VTN_E_ARG, "vtn_vcf_tokenize: text must be < 4 GiB per call (allele bytes of a batch are 32-bit offsets)");
+// device buffers for texts of up to cap_text bytes with the given record / allele capacities
+int dtext_alloc(vtn_ctx* ctx, uint64_t cap_text, uint32_t cap_rec, uint32_t cap_allele, uint64_t cap_bytes, vtn_vcf_dtext** out)
+{
     VTN_CUDA(ctx, cudaSetDevice(ctx->device));
     vtn_vcf_dtext* h = new vtn_vcf_dtext();
-    h->n_text = n_text;
-    h->open_tail = n_text && text[n_text - 1] != '\n';
+    h->cap_text = cap_text;
     h->cap_rec = cap_rec;
     h->cap_allele = cap_allele;
     h->cap_bytes = cap_bytes;
-    const uint32_t n_tiles = (uint32_t)((n_text + VTK_TILE - 1) / VTK_TILE);
+    const uint32_t n_tiles = (uint32_t)((cap_text + VTK_TILE - 1) / VTK_TILE);
     const uint32_t r_tiles = (cap_rec + VTK_RTILE - 1) / VTK_RTILE;
     const size_t nr = (size_t)cap_rec + 16;
     cudaError_t e = cudaSuccess;
 #define A(p, bytes) if (e == cudaSuccess) e = cudaMalloc((void**)&(p), (bytes))
-    A(h->text, n_text + 64);
+    A(h->text, cap_text + 64);
     A(h->agg, ((size_t)n_tiles + 1) * 4);
     A(h->nl, 4);
     A(h->line, nr * 8);
@@ -366,13 +365,39 @@ int vtn_vcf_dtext_create(vtn_ctx* ctx, const char* text, uint64_t n_text, uint32
     A(h->aoff, ((size_t)cap_allele + 16) * 4);
     A(h->bytes, (size_t)cap_bytes + 16);
 #undef A
-    if (e == cudaSuccess && n_text) e = cudaMemcpyAsync(h->text, text, n_text, cudaMemcpyHostToDevice, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemsetAsync(h->text + n_text, 0, 64, ctx->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess)
     {
         vtn_vcf_dtext_destroy(ctx, h);
         return vtn_set_err(ctx, VTN_E_NOMEM, std::string("vtn_vcf_dtext_create: ") + cudaGetErrorString(e));
+    }
+    *out = h;
+    return VTN_OK;
+}
+
+int dtext_load(vtn_ctx* ctx, vtn_vcf_dtext* h, const char* text, uint64_t n_text)
+{
+    h->n_text = n_text;
+    h->open_tail = n_text && text[n_text - 1] != '\n';
+    if (n_text) VTN_CUDA(ctx, cudaMemcpyAsync(h->text, text, n_text, cudaMemcpyHostToDevice, ctx->stream));
+    VTN_CUDA(ctx, cudaMemsetAsync(h->text + n_text, 0, 64, ctx->stream));
+    VTN_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return VTN_OK;
+}
+} // namespace
+
+int vtn_vcf_dtext_create(vtn_ctx* ctx, const char* text, uint64_t n_text, uint32_t cap_rec, uint32_t cap_allele, uint64_t cap_bytes,
+                         vtn_vcf_dtext** out)
+{
+    if (!ctx || !out || (n_text && !text)) return vtn_set_err(ctx, VTN_E_ARG, "vtn_vcf_dtext_create: bad arguments");
+    if (n_text >= (1ull << 32)) return vtn_set_err(ctx, VTN_E_ARG, "vtn_vcf_tokenize: text must be < 4 GiB per call (allele bytes of a batch are 32-bit offsets)");
+    vtn_vcf_dtext* h = nullptr;
+    int rc = dtext_alloc(ctx, n_text, cap_rec, cap_allele, cap_bytes, &h);
+    if (rc) return rc;
+    rc = dtext_load(ctx, h, text, n_text);
+    if (rc)
+    {
+        vtn_vcf_dtext_destroy(ctx, h);
+        return rc;
     }
     *out = h;
     return VTN_OK;
@@ -461,15 +486,28 @@ int vtn_vcf_dtext_fetch(vtn_ctx* ctx, vtn_vcf_dtext* h, vtn_vcf_fields* out)
     return VTN_OK;
 }
 
-// Host-buffer call: H2D of the text, the kernels above, D2H of every output array.
+// Host-buffer call: H2D of the text, the kernels above, D2H of every output array.  The device buffers live in the context and are
+// reused by the next call when they are large enough (a file is tokenized batch after batch with the same capacities).
 int vtn_vcf_tokenize(vtn_ctx* ctx, const char* text, uint64_t n_text, vtn_vcf_fields* out)
 {
     if (!ctx || !out || (n_text && !text)) return vtn_set_err(ctx, VTN_E_ARG, "vtn_vcf_tokenize: bad arguments");
-    vtn_vcf_dtext* h = nullptr;
-    int rc = vtn_vcf_dtext_create(ctx, text, n_text, out->cap_rec, out->cap_allele, out->cap_bytes, &h);
-    if (rc) return rc;
-    rc = vtn_vcf_tokenize_resident(ctx, h);
+    if (n_text >= (1ull << 32)) return vtn_set_err(ctx, VTN_E_ARG, "vtn_vcf_tokenize: text must be < 4 GiB per call (allele bytes of a batch are 32-bit offsets)");
+    vtn_vcf_dtext*& h = ctx->tok_cache;
+    if (h && (h->cap_text < n_text || h->cap_rec < out->cap_rec || h->cap_allele < out->cap_allele || h->cap_bytes < out->cap_bytes))
+    {
+        vtn_vcf_dtext_destroy(ctx, h);
+        h = nullptr;
+    }
+    int rc = VTN_OK;
+    if (!h)
+    {
+        auto grow = [](uint64_t v) { return v + v / 4 + 1024; };
+        const uint64_t cr = std::min<uint64_t>(grow(out->cap_rec), 0xffffffffull), ca = std::min<uint64_t>(grow(out->cap_allele), 0xffffffffull);
+        rc = dtext_alloc(ctx, grow(n_text), (uint32_t)cr, (uint32_t)ca, grow(out->cap_bytes), &h);
+        if (rc) return rc;
+    }
+    rc = dtext_load(ctx, h, text, n_text);
+    if (rc == VTN_OK) rc = vtn_vcf_tokenize_resident(ctx, h);
     if (rc == VTN_OK) rc = vtn_vcf_dtext_fetch(ctx, h, out);
-    vtn_vcf_dtext_destroy(ctx, h);
     return rc;
 }
