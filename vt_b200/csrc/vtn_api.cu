@@ -57,6 +57,7 @@ int vtn_ctx_destroy(vtn_ctx* ctx)
     if (ctx->scratch) vtn_dbatch_destroy(ctx, ctx->scratch);
     if (ctx->scratch_bi) vtn_dbatch_destroy(ctx, ctx->scratch_bi);
     vtn_hmm_ctx_release(ctx);
+    vtn_order_ctx_release(ctx);
     if (ctx->tok_cache) vtn_vcf_dtext_destroy(ctx, ctx->tok_cache);
     vtn_ref_release(ctx);
     cudaEventDestroy(ctx->ev0);

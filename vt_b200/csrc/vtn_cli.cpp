@@ -17,6 +17,7 @@
 // (SURVEY.md 8f).  Values of Type=Float fields and QUAL are re-serialised the way htslib does when it formats a
 // record it has parsed (float32 storage, 6 significant digits), because the reference's output goes through that.
 // No CPU fallback: without a CUDA device vtn_ctx_create fails and the tool exits 1.
+#include <unistd.h>
 #include <zlib.h>
 #include <algorithm>
 #include <cctype>
@@ -664,17 +665,152 @@ void parallel_ranges(size_t n, unsigned nthr, F fn)
     for (auto& x : th) x.join();
 }
 
+bool g_quick_exit = false; // set once the output is complete: the process ends with _exit, nothing is torn down piece by piece
+
+// page-locked host array (vtn_host_alloc): what the device calls copy from / into without a staging pass; grows, never shrinks
+template <class T>
+struct PinnedBuf
+{
+    vtn_ctx* ctx = nullptr;
+    T* p = nullptr;
+    size_t cap = 0;
+    PinnedBuf() = default;
+    PinnedBuf(const PinnedBuf&) = delete;
+    PinnedBuf& operator=(const PinnedBuf&) = delete;
+    ~PinnedBuf()
+    {
+        if (p && !g_quick_exit) vtn_host_free(ctx, p);
+    }
+    void resize(size_t n) // contents are not kept
+    {
+        if (n <= cap) return;
+        if (p) vtn_host_free(ctx, p);
+        p = nullptr;
+        cap = n + n / 4 + 4096;
+        void* q = nullptr;
+        if (vtn_host_alloc(ctx, cap * sizeof(T), &q))
+        {
+            fprintf(stderr, "[vtn] vtn_host_alloc: %s\n", vtn_last_error(ctx));
+            exit(1);
+        }
+        p = (T*)q;
+    }
+    void resize_keep(size_t n, size_t keep) // the first `keep` elements survive
+    {
+        if (n <= cap) return;
+        T* old = p;
+        p = nullptr;
+        const size_t oc = cap;
+        cap = 0;
+        resize(n);
+        if (old && keep) memcpy(p, old, std::min(keep, oc) * sizeof(T));
+        if (old) vtn_host_free(ctx, old);
+    }
+    T* data() { return p; }
+    const T* data() const { return p; }
+    T& operator[](size_t i) { return p[i]; }
+    const T& operator[](size_t i) const { return p[i]; }
+    T* begin() { return p; }
+};
+
+// output on its own thread: the formatter fills one buffer while the other one is being written
+struct AsyncOut
+{
+    FILE* out = stdout;
+    std::vector<char> buf[2];
+    size_t fill[2] = {0, 0};
+    int state[2] = {0, 0}; // 0 free, 1 being filled, 2 queued for writing
+    int cur = 0, next_write = 0;
+    std::mutex m;
+    std::condition_variable cv;
+    std::thread th;
+    bool stop = false;
+    void start(FILE* f)
+    {
+        out = f;
+        th = std::thread([this]() {
+            for (;;)
+            {
+                int k;
+                {
+                    std::unique_lock<std::mutex> g(m);
+                    cv.wait(g, [&]() { return state[next_write] == 2 || stop; });
+                    if (state[next_write] != 2) return;
+                    k = next_write;
+                }
+                if (fill[k] && fwrite(buf[k].data(), 1, fill[k], out) != fill[k])
+                {
+                    fprintf(stderr, "[vtn] write error\n");
+                    _exit(1);
+                }
+                {
+                    std::lock_guard<std::mutex> g(m);
+                    state[k] = 0;
+                    next_write ^= 1;
+                }
+                cv.notify_all();
+            }
+        });
+    }
+    char* acquire(size_t bytes)
+    {
+        std::unique_lock<std::mutex> g(m);
+        cv.wait(g, [&]() { return state[cur] == 0; });
+        state[cur] = 1;
+        g.unlock();
+        if (buf[cur].size() < bytes) buf[cur].resize(bytes + bytes / 4);
+        return buf[cur].data();
+    }
+    void submit(size_t bytes)
+    {
+        {
+            std::lock_guard<std::mutex> g(m);
+            fill[cur] = bytes;
+            state[cur] = 2;
+            cur ^= 1;
+        }
+        cv.notify_all();
+    }
+    void finish()
+    {
+        {
+            std::unique_lock<std::mutex> g(m);
+            cv.wait(g, [&]() { return state[0] == 0 && state[1] == 0; });
+            stop = true;
+        }
+        cv.notify_all();
+        if (th.joinable()) th.join();
+        fflush(out);
+    }
+};
+
 struct TextBlock
 {
-    std::vector<char> text; // whole lines, each ended by '\n' ("\r\n" already reduced to '\n')
-    size_t n = 0, n_lines = 0, n_commas = 0;
+    PinnedBuf<char> pinned; // page-locked storage (the H2D copy of the text needs no staging pass)
+    std::vector<char> big;  // a block that outgrew it (one very long line)
+    char* text = nullptr;   // whole lines, each ended by '\n' ("\r\n" already reduced to '\n')
+    size_t cap = 0, n = 0, n_lines = 0, n_commas = 0;
+    void ensure(size_t bytes, size_t keep)
+    {
+        if (bytes <= cap) return;
+        if (!keep && pinned.ctx)
+        {
+            pinned.resize(bytes);
+            text = pinned.data(), cap = pinned.cap;
+            return;
+        }
+        std::vector<char> nb(bytes + bytes / 2);
+        if (keep) memcpy(nb.data(), text, keep);
+        big.swap(nb);
+        text = big.data(), cap = big.size();
+    }
 };
 
 // Reads the record lines of a VCF in blocks (target_bytes of whole lines, at most max_lines lines) on its own thread, two blocks ahead.
 struct BlockReader
 {
     gzFile f = nullptr;
-    size_t target_bytes = 32u << 20, max_lines = 0;
+    size_t target_bytes = 16u << 20, max_lines = 0;
     std::vector<char> pend; // read but not handed out yet
     TextBlock blocks[3];
     std::deque<TextBlock*> free_q, ready_q;
@@ -683,9 +819,10 @@ struct BlockReader
     std::thread th;
     bool done = false, stop = false;
 
-    void start(gzFile file, const std::string& first_line, bool have_first)
+    void start(vtn_ctx* ctx, gzFile file, const std::string& first_line, bool have_first)
     {
         f = file;
+        for (auto& b : blocks) b.pinned.ctx = ctx;
         if (have_first)
         {
             pend.assign(first_line.begin(), first_line.end());
@@ -735,17 +872,17 @@ struct BlockReader
                 b = free_q.front();
                 free_q.pop_front();
             }
-            std::vector<char>& t = b->text;
             size_t want = std::max(target_bytes, pend.size());
-            if (t.size() < want + 2) t.resize(want + 2);
-            memcpy(t.data(), pend.data(), pend.size());
+            b->ensure(want + 2, 0);
+            char* t = b->text;
+            memcpy(t, pend.data(), pend.size());
             size_t n = pend.size(), cut = 0;
             pend.clear();
             for (;;)
             {
                 while (!eof && n < want)
                 {
-                    const int got = gzread(f, t.data() + n, (unsigned)std::min<size_t>(want - n, 1u << 30));
+                    const int got = gzread(f, t + n, (unsigned)std::min<size_t>(want - n, 1u << 30));
                     if (got <= 0)
                         eof = true;
                     else
@@ -757,29 +894,30 @@ struct BlockReader
                     cut = n;
                     break;
                 }
-                const void* nl = memrchr(t.data(), '\n', n);
+                const void* nl = memrchr(t, '\n', n);
                 if (nl)
                 {
-                    cut = (size_t)((const char*)nl - t.data()) + 1;
+                    cut = (size_t)((const char*)nl - t) + 1;
                     break;
                 }
                 want *= 2; // one line longer than the block: keep reading
-                t.resize(want + 2);
+                b->ensure(want + 2, n);
+                t = b->text;
             }
             if (max_lines)
             { // VTN_CLI_BATCH: at most that many lines per block
                 size_t lines = 0, p = 0;
                 while (p < cut && lines < max_lines)
                 {
-                    const void* nl = memchr(t.data() + p, '\n', cut - p);
-                    p = (size_t)((const char*)nl - t.data()) + 1;
+                    const void* nl = memchr(t + p, '\n', cut - p);
+                    p = (size_t)((const char*)nl - t) + 1;
                     ++lines;
                 }
                 cut = p;
             }
-            pend.assign(t.begin() + cut, t.begin() + n);
+            pend.assign(t + cut, t + n);
             n = cut;
-            if (memchr(t.data(), '\r', n))
+            if (memchr(t, '\r', n))
             { // "\r\n" -> "\n" (the reference's reader drops the '\r' with the line end)
                 size_t w = 0;
                 for (size_t r = 0; r < n; ++r)
@@ -787,8 +925,8 @@ struct BlockReader
                 n = w;
             }
             b->n = n;
-            b->n_lines = (size_t)std::count(t.data(), t.data() + n, '\n');
-            b->n_commas = (size_t)std::count(t.data(), t.data() + n, ',');
+            b->n_lines = (size_t)std::count(t, t + n, '\n');
+            b->n_commas = (size_t)std::count(t, t + n, ',');
             const bool last = eof && pend.empty();
             {
                 std::lock_guard<std::mutex> g(m);
@@ -850,24 +988,26 @@ struct FastWriter
     int window = 0;
     vtn_ctx* ctx = nullptr;
     unsigned nthr = 1;
-    std::vector<int32_t> rid, pos, late;
+    PinnedBuf<int32_t> rid, pos, late; // what vtn_writer_order copies: page-locked
+    PinnedBuf<uint32_t> order;
     std::vector<const char*> ptr;
-    std::vector<uint32_t> len, order;
+    std::vector<uint32_t> len;
     std::vector<uint64_t> ooff;
-    std::vector<char> obuf, carry_text;
+    std::vector<char> carry_text;
+    AsyncOut aout;
     size_t n_carry = 0;
-    // room for n_new records after the carried ones; the caller fills rid/pos/ptr/len at [base(), base() + n_new)
+    // room for n_new records after the carried ones; the caller fills rid/pos/ptr/len at [n_carry, n_carry + n_new)
     size_t begin(size_t n_new)
     {
         const size_t n = n_carry + n_new;
-        rid.resize(n), pos.resize(n), ptr.resize(n), len.resize(n);
+        rid.ctx = pos.ctx = late.ctx = order.ctx = ctx;
+        rid.resize_keep(n, n_carry), pos.resize_keep(n, n_carry), ptr.resize(n), len.resize(n);
         return n_carry;
     }
     // msgs: (index among the new records, stderr text) ascending
     void drain(size_t n_new, const std::vector<std::pair<uint32_t, std::string>>& msgs, bool final)
     {
-        const size_t n = n_carry + n_new;
-        rid.resize(n), pos.resize(n), ptr.resize(n), len.resize(n);
+        const size_t n = begin(n_new) + n_new;
         if (!n) return;
         size_t done = n;
         uint32_t n_pending = 0;
@@ -906,7 +1046,7 @@ struct FastWriter
             tot += len[ordered ? order[k] : k];
         }
         ooff[done] = tot;
-        if (obuf.size() < tot) obuf.resize(tot);
+        char* obuf = aout.acquire(tot);
         parallel_ranges(done, nthr, [&](unsigned, size_t lo, size_t hi) {
             size_t k = lo;
             while (k < hi)
@@ -921,18 +1061,14 @@ struct FastWriter
                     l += len[j];
                     ++e;
                 }
-                memcpy(obuf.data() + ooff[k], p, l);
+                memcpy(obuf + ooff[k], p, l);
                 k = e;
             }
         });
-        if (tot && fwrite(obuf.data(), 1, tot, out) != tot)
-        {
-            fprintf(stderr, "[vtn] write error\n");
-            exit(1);
-        }
+        aout.submit(tot);
         // what stays inside the buffer: copied, in arrival order, in front of the next block
         std::vector<uint32_t> keep;
-        if (ordered) keep.assign(order.begin() + done, order.end());
+        if (ordered) keep.assign(order.data() + done, order.data() + n);
         std::sort(keep.begin(), keep.end());
         std::vector<char> nt;
         std::vector<uint64_t> noff;
@@ -946,7 +1082,8 @@ struct FastWriter
         }
         carry_text.swap(nt);
         n_carry = keep.size();
-        rid.assign(nr.begin(), nr.end()), pos.assign(np.begin(), np.end()), len.assign(nl.begin(), nl.end());
+        for (size_t k = 0; k < n_carry; ++k) rid[k] = nr[k], pos[k] = np[k]; // n_carry <= n: the arrays are large enough
+        len.assign(nl.begin(), nl.end());
         ptr.resize(n_carry);
         for (size_t k = 0; k < n_carry; ++k) ptr[k] = carry_text.data() + noff[k];
     }
@@ -1000,6 +1137,7 @@ int cmd_normalize(int argc, char** argv)
     ow.ctx = ctx;
     ow.nthr = nthr;
     write_header(ow.out, h, "##INFO=<ID=OLD_VARIANT,Number=.,Type=String,Description=\"Original chr:pos:ref:alt encoding\">");
+    ow.aout.start(ow.out);
     bool float_info = false, float_fmt = false;
     for (const auto& kv : h.info) float_info = float_info || kv.second.type == 'F';
     for (const auto& kv : h.fmt) float_fmt = float_fmt || kv.second.type == 'F';
@@ -1009,13 +1147,17 @@ int cmd_normalize(int argc, char** argv)
         if (atol(e) > 0) br.max_lines = (size_t)atol(e);
     if (const char* e = getenv("VTN_CLI_BLOCK_MB"))
         if (atol(e) > 0) br.target_bytes = (size_t)atol(e) << 20;
-    br.start(rd.f, line, !line.empty());
+    br.start(ctx, rd.f, line, !line.empty());
 
     std::map<std::string, int> rid_cache, writer_ids;
-    std::vector<uint64_t> line_off, chg_off;
-    std::vector<uint32_t> chrom_len, tail_off, allele_beg, allele_off, chg_rec, chg_lt, chg_le, chg_rt;
-    std::vector<int32_t> pos1, rid, wid, chg_pos1;
-    std::vector<uint8_t> tstatus, bytes, status, vtype, chg_bytes;
+    // every array a device call reads or fills is page-locked
+    PinnedBuf<uint64_t> line_off, chg_off;
+    PinnedBuf<uint32_t> chrom_len, tail_off, allele_beg, allele_off, chg_rec, chg_lt, chg_le, chg_rt;
+    PinnedBuf<int32_t> pos1, rid, chg_pos1;
+    PinnedBuf<uint8_t> tstatus, bytes, status, vtype, chg_bytes;
+    line_off.ctx = chg_off.ctx = chrom_len.ctx = tail_off.ctx = allele_beg.ctx = allele_off.ctx = chg_rec.ctx = chg_lt.ctx = chg_le.ctx = chg_rt.ctx = ctx;
+    pos1.ctx = rid.ctx = chg_pos1.ctx = tstatus.ctx = bytes.ctx = status.ctx = vtype.ctx = chg_bytes.ctx = ctx;
+    std::vector<int32_t> wid;
     std::vector<std::string> arena(nthr);
     std::vector<std::vector<uint32_t>> arena_recs(nthr);
     std::vector<std::pair<uint32_t, std::string>> msgs;
@@ -1028,7 +1170,7 @@ int cmd_normalize(int argc, char** argv)
     while (TextBlock* blk = br.next())
     {
         pt.stop("wait for reader");
-        const char* text = blk->text.data();
+        const char* text = blk->text;
         const size_t n = blk->n_lines;
         line_off.resize(n + 1), chrom_len.resize(n), tail_off.resize(n), tstatus.resize(n), pos1.resize(n), allele_beg.resize(n + 1);
         allele_off.resize(blk->n_commas + 2 * n + 1), bytes.resize(blk->n + 1);
@@ -1219,6 +1361,7 @@ int cmd_normalize(int argc, char** argv)
         pt.stop("order + write");
         if (!fatal.empty())
         {
+            ow.aout.finish();
             fputs(fatal.c_str(), stderr);
             exit(1);
         }
@@ -1229,7 +1372,7 @@ int cmd_normalize(int argc, char** argv)
     }
     pt.start();
     ow.drain(0, {}, true);
-
+    ow.aout.finish();
     if (ow.out != stdout) fclose(ow.out);
     pt.stop("order + write");
     pt.report();
@@ -1248,7 +1391,7 @@ int cmd_normalize(int argc, char** argv)
         fprintf(stderr, "       total no. variants observed              : %u\n", tot.no_variants);
         fprintf(stderr, "       total no. reference observed             : %u\n\n", tot.no_refs);
     }
-    vtn_ctx_destroy(ctx);
+    g_quick_exit = true; // the output file is closed: main ends the process without unmapping the pinned buffers and the context one by one
     return print ? 1 : 0; // normalize() returns `print` so that main reports the elapsed time (normalize.cpp:391-400)
 }
 
@@ -2182,5 +2325,10 @@ int main(int argc, char** argv)
         return 1;
     }
     if (print) fprintf(stderr, "Time elapsed: %.2fs\n\n", (double)(clock() - t0) / CLOCKS_PER_SEC); // main.cpp:428-433
+    if (g_quick_exit)
+    {
+        fflush(nullptr);
+        _exit(0);
+    }
     return 0;
 }

@@ -190,9 +190,11 @@ struct vtn_ctx
     size_t hmm_scratch_bytes = 0;
     unsigned* hmm_counter = nullptr;
     std::string annot_trace; // vtn_annot_set_trace
+    void* order_cache = nullptr;               // arena of the host-buffer vtn_writer_order call, kept between calls (vtn_order.cu)
     struct vtn_vcf_dtext* tok_cache = nullptr; // device buffers of the host-buffer vtn_vcf_tokenize call, kept between calls
 };
 void vtn_hmm_ctx_release(vtn_ctx* ctx);
+void vtn_order_ctx_release(vtn_ctx* ctx);
 void vtn_ref_release(vtn_ctx* ctx); // frees the resident reference and a lazily opened FASTA (vtn_ctx_destroy)
 int vtn_ref_clone(vtn_ctx* dst, const vtn_ctx* src);
 int vtn_ref_ensure(vtn_ctx* ctx, uint64_t n, const int32_t* rid); // lazy reference: make every contig named in rid[] resident // replicate src's resident reference on dst's device (peer copies)

@@ -541,9 +541,20 @@ int vtn_writer_order(vtn_ctx* ctx, uint32_t n, const int32_t* rid, const int32_t
     }
     VTN_CUDA(ctx, cudaSetDevice(ctx->device));
     cudaStream_t s = ctx->stream;
-    vtn_order_buffers* o = nullptr;
-    int rc = order_alloc(ctx, n, &o);
-    if (rc) return rc;
+    // the arena lives in the context and is reused while it is large enough (a file is written block after block)
+    vtn_order_buffers* o = static_cast<vtn_order_buffers*>(ctx->order_cache);
+    int rc = VTN_OK;
+    if (o && o->cap < n)
+    {
+        order_release(o);
+        ctx->order_cache = o = nullptr;
+    }
+    if (!o)
+    {
+        rc = order_alloc(ctx, n + n / 4 + 1024, &o);
+        if (rc) return rc;
+        ctx->order_cache = o;
+    }
     cudaError_t e = cudaMemcpyAsync(o->rid, rid, sizeof(int32_t) * n, cudaMemcpyHostToDevice, s);
     if (e == cudaSuccess) e = cudaMemcpyAsync(o->pos, pos1, sizeof(int32_t) * n, cudaMemcpyHostToDevice, s);
     if (e == cudaSuccess) rc = order_launch(ctx, o, o->rid, o->pos, n, window);
@@ -553,6 +564,11 @@ int vtn_writer_order(vtn_ctx* ctx, uint32_t n, const int32_t* rid, const int32_t
     if (e == cudaSuccess && rc == VTN_OK && n_pending) e = cudaMemcpyAsync(n_pending, o->cnt + (n - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, s);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);
     if (e != cudaSuccess) rc = vtn_set_err(ctx, VTN_E_CUDA, std::string("vtn_writer_order: ") + cudaGetErrorString(e));
-    order_release(o);
     return rc;
+}
+
+void vtn_order_ctx_release(vtn_ctx* ctx)
+{
+    if (ctx->order_cache) order_release(static_cast<vtn_order_buffers*>(ctx->order_cache));
+    ctx->order_cache = nullptr;
 }
