@@ -1,4 +1,4 @@
-// vtn_cli.cpp -- host shim that keeps vt's command surface for the path:  `vtn normalize`, `vtn decompose`, `vtn uniq`,
+// vtn_tools.cpp -- libvtn_tools.so: the host shim that keeps vt's tool entry points and command surface for the path (include/vtn_tools.h):  `vtn normalize`, `vtn decompose`, `vtn uniq`,
 // `vtn decompose_blocksub`, `vtn annotate_indels`.
 //
 // Mirrors the reference tools' flags, stderr text and VCF output (normalize.cpp:84-171, :332-382; decompose.cpp:
@@ -665,7 +665,16 @@ void parallel_ranges(size_t n, unsigned nthr, F fn)
     for (auto& x : th) x.join();
 }
 
-bool g_quick_exit = false; // set once the output is complete: the process ends with _exit, nothing is torn down piece by piece
+bool g_allow_quick_exit = false; // vtn_tools_end_process_after_output(1): the command-line program ends the process after the output is complete
+bool g_quick_exit = false;       // set by a tool once its output is closed, when allowed: nothing is torn down piece by piece
+struct CtxGuard // destroys the context after every buffer allocated through it (declare it right after vtn_ctx_create)
+{
+    vtn_ctx* c;
+    ~CtxGuard()
+    {
+        if (c && !g_quick_exit) vtn_ctx_destroy(c);
+    }
+};
 
 // page-locked host array (vtn_host_alloc): what the device calls copy from / into without a staging pass; grows, never shrinks
 template <class T>
@@ -1114,6 +1123,7 @@ int cmd_normalize(int argc, char** argv)
     pt.start();
     vtn_ctx* ctx = nullptr;
     if (vtn_ctx_create(&ctx, a.device)) die(nullptr, "vtn_ctx_create");
+    CtxGuard ctx_guard{ctx};
     pt.stop("context");
     if (vtn_ref_open_fasta(ctx, a.ref.c_str())) die(ctx, "loading the reference");
     pt.stop("reference open");
@@ -1391,7 +1401,7 @@ int cmd_normalize(int argc, char** argv)
         fprintf(stderr, "       total no. variants observed              : %u\n", tot.no_variants);
         fprintf(stderr, "       total no. reference observed             : %u\n\n", tot.no_refs);
     }
-    g_quick_exit = true; // the output file is closed: main ends the process without unmapping the pinned buffers and the context one by one
+    g_quick_exit = g_allow_quick_exit; // the output file is closed: vtn_tool_main may end the process without unmapping the pinned buffers and the context one by one
     return print ? 1 : 0; // normalize() returns `print` so that main reports the elapsed time (normalize.cpp:391-400)
 }
 
@@ -2286,7 +2296,24 @@ int cmd_annotate_indels(int argc, char** argv)
     return 0;
 }
 
-int main(int argc, char** argv)
+// ------------------------------------------------------------------------------------------------------------
+// exports (include/vtn_tools.h): the reference's tool entry points, argv[0] = sub-command (main.cpp:193-196, 221-224, 393-396)
+// ------------------------------------------------------------------------------------------------------------
+extern "C" {
+
+int vtn_tool_normalize(int argc, char** argv) { return cmd_normalize(argc, argv); }
+
+void vtn_tool_decompose(int argc, char** argv) { cmd_decompose(argc, argv); }
+
+void vtn_tool_annotate_indels(int argc, char** argv) { cmd_annotate_indels(argc, argv); }
+
+void vtn_tool_uniq(int argc, char** argv) { cmd_uniq(argc, argv); }
+
+void vtn_tool_decompose_blocksub(int argc, char** argv) { cmd_blocksub(argc, argv); }
+
+void vtn_tools_end_process_after_output(int on) { g_allow_quick_exit = on != 0; }
+
+int vtn_tool_main(int argc, char** argv)
 {
     clock_t t0 = clock();
     if (argc < 2)
@@ -2297,26 +2324,26 @@ int main(int argc, char** argv)
     std::string cmd = argv[1];
     bool print = false;
     if (cmd == "normalize")
-        print = cmd_normalize(argc - 1, argv + 1) != 0;
+        print = vtn_tool_normalize(argc - 1, argv + 1) != 0;
     else if (cmd == "decompose")
     {
-        cmd_decompose(argc - 1, argv + 1);
+        vtn_tool_decompose(argc - 1, argv + 1);
         print = true;
         for (int k = 2; k < argc; ++k) print = print && strcmp(argv[k], "-q");
     }
     else if (cmd == "uniq")
     {
-        cmd_uniq(argc - 1, argv + 1);
+        vtn_tool_uniq(argc - 1, argv + 1);
         print = true;
     }
     else if (cmd == "decompose_blocksub")
     {
-        cmd_blocksub(argc - 1, argv + 1);
+        vtn_tool_decompose_blocksub(argc - 1, argv + 1);
         print = true;
     }
     else if (cmd == "annotate_indels")
     {
-        cmd_annotate_indels(argc - 1, argv + 1);
+        vtn_tool_annotate_indels(argc - 1, argv + 1);
         print = true;
     }
     else
@@ -2326,9 +2353,11 @@ int main(int argc, char** argv)
     }
     if (print) fprintf(stderr, "Time elapsed: %.2fs\n\n", (double)(clock() - t0) / CLOCKS_PER_SEC); // main.cpp:428-433
     if (g_quick_exit)
-    {
+    { // only after vtn_tools_end_process_after_output(1): the output is on disk, the OS reclaims the context and the pinned pages at once
         fflush(nullptr);
         _exit(0);
     }
     return 0;
 }
+
+} // extern "C"
