@@ -472,6 +472,14 @@ int vtn_annotate_indels(vtn_ctx* ctx, const vtn_batch* in, vtn_annot_result* out
  * <what the driver reads back>" (stage 0 exact purity, 1 RFHMM rounds, 2 LFHMM rounds, 3 fuzzy purity) -- the format of
  * oracle/fd_trace.cpp, which taps the unmodified reference classes the same way.  NULL or "" switches it off. */
 int vtn_annot_set_trace(vtn_ctx* ctx, const char* path);
+
+/* ---- VariantManip's allele-only predicates for a batch ----
+ * Replaces, record by record: VariantManip::classify_variant's type mask (variant_manip.cpp:337-490; vtype[r], VTN_VT_* bits, may be
+ * NULL), VariantManip::is_normalized (:109-197; VTN_PROP_NORMALIZED) and VariantManip::contains_N (:202-222; VTN_PROP_CONTAINS_N)
+ * -- what annotate_indels.cpp:295-316 and normalize.cpp:218 ask of a record.  Needs no reference; in->pos1 / in->rid are not read. */
+#define VTN_PROP_NORMALIZED 1
+#define VTN_PROP_CONTAINS_N 2
+int vtn_variant_props(vtn_ctx* ctx, const vtn_batch* in, uint8_t* vtype, uint8_t* props);
 /* ReferenceSequence::fetch_seq for a list of windows (0-based inclusive, clipped like faidx.c:832-860), one kernel:
  * out[off[k] .. off[k+1]) = window k; upper != 0 = faidx_fetch_uc_seq.  An unknown contig yields an empty window. */
 int vtn_ref_fetch_batch(vtn_ctx* ctx, uint32_t n, const int32_t* rid, const int64_t* beg0, const int64_t* end0, int upper, uint64_t* off,

@@ -132,6 +132,7 @@ SIGNATURES = {
     "vtn_host_alloc": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]),
     "vtn_host_free": (C.c_int, [C.c_void_p, C.c_void_p]),
     "vtn_ref_load_fasta": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "vtn_variant_props": (C.c_int, [C.c_void_p, C.POINTER(VtnBatch), c_u8p, c_u8p]),
     "vtn_ref_open_fasta": (C.c_int, [C.c_void_p, C.c_char_p]),
     "vtn_ref_require": (C.c_int, [C.c_void_p, C.c_int]),
     "vtn_ref_require_all": (C.c_int, [C.c_void_p]),

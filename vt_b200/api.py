@@ -435,6 +435,14 @@ class Context:
         self._chk(self.lib.vtn_dbatch_fetch_result(self.h, db, C.byref(res.c)), "vtn_dbatch_fetch_result")
         return res
 
+    def variant_props(self, batch):
+        """VariantManip's allele-only predicates for a batch -> (vtype, props); props bit 0 is_normalized, bit 1 contains_N"""
+        vt = np.zeros(max(batch.n_rec, 1), np.uint8)
+        pr = np.zeros(max(batch.n_rec, 1), np.uint8)
+        cb = batch.as_c()
+        self._chk(self.lib.vtn_variant_props(self.h, C.byref(cb), _p(vt, L.c_u8p), _p(pr, L.c_u8p)), "vtn_variant_props")
+        return vt[:batch.n_rec], pr[:batch.n_rec]
+
     def annotate_indels(self, batch, trace=None, raw=False):
         """vt annotate_indels for a batch (include/vtn.h vtn_annotate_indels) -> dict: flags, vtype, indel_idx, trim_left / trim_right /
         shift per allele slot, vntr (list of dicts with the 34 INFO values per indel), n_alignments."""

@@ -54,19 +54,15 @@ struct AnnotDev
     uint32_t* a_shift;
 };
 
-__global__ void __launch_bounds__(128) vta_region_kernel(VtnDevRef R, VtnDevBatchView B, AnnotDev O)
+// what VariantManip says about a record from its alleles alone: classify_variant's type mask (variant_manip.cpp:337-490), is_normalized
+// (:109-197) and contains_N (:202-222)
+__device__ __forceinline__ void vta_site_props(const VtnDevBatchView& B, uint32_t ab, uint32_t n, const uint8_t* ref, uint32_t rlen, uint32_t& vtype,
+                                               int32_t& max_dlen, bool& normalized, bool& has_n)
 {
-    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= B.n_rec) return;
-    const uint32_t ab = B.allele_beg[r], n = B.allele_beg[r + 1] - ab;
-    const int32_t pos1 = B.pos1[r], rid = B.rid[r];
-    const uint32_t off0 = B.allele_off[ab], off1 = B.allele_off[ab + 1];
-    const uint8_t* ref = B.bytes + off0;
-    const uint32_t rlen = off1 - off0;
     // ---- classify_variant ----
-    uint32_t vtype = 0;
+    vtype = 0;
     bool homog = true;
-    int32_t max_dlen = 0;
+    max_dlen = 0;
     for (uint32_t i = 1; i < n; ++i)
     {
         const uint32_t o = B.allele_off[ab + i], l = B.allele_off[ab + i + 1] - o;
@@ -84,10 +80,8 @@ __global__ void __launch_bounds__(128) vta_region_kernel(VtnDevRef R, VtnDevBatc
         }
     }
     if (!(vtype & (VTN_VT_VNTR | VTN_VT_SV)) && vtype != VTN_VT_REF && homog && rlen > 1 && n > 1) vtype |= VTN_VT_MNP;
-    O.vtype[r] = (uint8_t)vtype;
-    O.max_dlen[r] = max_dlen;
     // ---- is_normalized (variant_manip.cpp:109-197) ----
-    bool normalized = true;
+    normalized = true;
     if (n >= 2)
     {
         bool exists_one = (rlen == 1), first_same = true, last_same = true, same = true;
@@ -114,7 +108,7 @@ __global__ void __launch_bounds__(128) vta_region_kernel(VtnDevRef R, VtnDevBatc
         else normalized = !(last_same || (!exists_one && first_same));
     }
     // ---- contains_N (variant_manip.cpp:202-222) ----
-    bool has_n = false;
+    has_n = false;
     for (uint32_t i = 0; i < n; ++i)
     {
         const uint32_t o = B.allele_off[ab + i], l = B.allele_off[ab + i + 1] - o;
@@ -122,6 +116,38 @@ __global__ void __launch_bounds__(128) vta_region_kernel(VtnDevRef R, VtnDevBatc
         for (uint32_t j = 0; j < l; ++j) f |= (B.bytes[o + j] == 'N');
         if (f && !(i && B.bytes[o] == '<')) has_n = true;
     }
+}
+
+// VariantManip's allele-only predicates for a batch (vtn_variant_props): one thread per record
+__global__ void __launch_bounds__(128) vta_props_kernel(VtnDevBatchView B, uint8_t* vtype_out, uint8_t* props_out)
+{
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= B.n_rec) return;
+    const uint32_t ab = B.allele_beg[r], n = B.allele_beg[r + 1] - ab;
+    const uint32_t off0 = B.allele_off[ab], off1 = B.allele_off[ab + 1];
+    uint32_t vtype;
+    int32_t max_dlen;
+    bool normalized, has_n;
+    vta_site_props(B, ab, n, B.bytes + off0, off1 - off0, vtype, max_dlen, normalized, has_n);
+    if (vtype_out) vtype_out[r] = (uint8_t)vtype;
+    props_out[r] = (uint8_t)((normalized ? VTN_PROP_NORMALIZED : 0) | (has_n ? VTN_PROP_CONTAINS_N : 0));
+}
+
+__global__ void __launch_bounds__(128) vta_region_kernel(VtnDevRef R, VtnDevBatchView B, AnnotDev O)
+{
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= B.n_rec) return;
+    const uint32_t ab = B.allele_beg[r], n = B.allele_beg[r + 1] - ab;
+    const int32_t pos1 = B.pos1[r], rid = B.rid[r];
+    const uint32_t off0 = B.allele_off[ab], off1 = B.allele_off[ab + 1];
+    const uint8_t* ref = B.bytes + off0;
+    const uint32_t rlen = off1 - off0;
+    uint32_t vtype;
+    int32_t max_dlen;
+    bool normalized, has_n;
+    vta_site_props(B, ab, n, ref, rlen, vtype, max_dlen, normalized, has_n);
+    O.vtype[r] = (uint8_t)vtype;
+    O.max_dlen[r] = max_dlen;
     uint32_t flags = (normalized && !has_n) ? VTA_KEEP : 0u;
     int32_t min_beg1 = pos1, max_end1 = pos1;
     if (flags && (vtype & VTN_VT_INDEL))
@@ -330,6 +356,47 @@ int vtn_ref_fetch_batch(vtn_ctx* ctx, uint32_t n, const int32_t* rid, const int6
     int rc = fetch_windows(ctx, L, upper, buf);
     if (rc) return rc;
     if (L.off.back()) memcpy(out, buf.data(), (size_t)L.off.back());
+    return VTN_OK;
+}
+
+// VariantManip's allele-only predicates for a batch: classify_variant's mask, is_normalized, contains_N.  No reference needed;
+// pos1 / rid of the batch are not read.
+int vtn_variant_props(vtn_ctx* ctx, const vtn_batch* in, uint8_t* vtype, uint8_t* props)
+{
+    if (!ctx || !in || !props) return vtn_set_err(ctx, VTN_E_ARG, "vtn_variant_props: bad arguments");
+    const uint32_t n = in->n_rec;
+    if (!n) return VTN_OK;
+    if (!in->allele_beg || !in->allele_off || (in->n_bytes && !in->bytes)) return vtn_set_err(ctx, VTN_E_ARG, "vtn_variant_props: null arrays");
+    if (in->allele_beg[0] != 0 || in->allele_beg[n] != in->n_allele || in->allele_off[in->n_allele] != in->n_bytes)
+        return vtn_set_err(ctx, VTN_E_ARG, "vtn_variant_props: allele_beg / allele_off do not describe the batch");
+    for (uint32_t r = 0; r < n; ++r)
+        if (in->allele_beg[r + 1] <= in->allele_beg[r]) return vtn_set_err(ctx, VTN_E_ARG, "vtn_variant_props: a record without alleles");
+    for (uint32_t k = 0; k < in->n_allele; ++k)
+        if (in->allele_off[k + 1] <= in->allele_off[k]) return vtn_set_err(ctx, VTN_E_ARG, "vtn_variant_props: an empty allele");
+    VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    uint32_t *d_beg = nullptr, *d_off = nullptr;
+    uint8_t *d_bytes = nullptr, *d_vt = nullptr, *d_pr = nullptr;
+    cudaError_t e = cudaMalloc(&d_beg, 4 * ((size_t)n + 1));
+    if (e == cudaSuccess) e = cudaMalloc(&d_off, 4 * ((size_t)in->n_allele + 1));
+    if (e == cudaSuccess) e = cudaMalloc(&d_bytes, (size_t)in->n_bytes + 1);
+    if (e == cudaSuccess) e = cudaMalloc(&d_vt, n);
+    if (e == cudaSuccess) e = cudaMalloc(&d_pr, n);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_beg, in->allele_beg, 4 * ((size_t)n + 1), cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_off, in->allele_off, 4 * ((size_t)in->n_allele + 1), cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_bytes, in->bytes, (size_t)in->n_bytes, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess)
+    {
+        VtnDevBatchView v{n, 0u, nullptr, nullptr, d_beg, d_off, d_bytes};
+        vta_props_kernel<<<(n + 127) / 128, 128, 0, s>>>(v, d_vt, d_pr);
+        ctx->launches++;
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess && vtype) e = cudaMemcpyAsync(vtype, d_vt, n, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(props, d_pr, n, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(d_beg), cudaFree(d_off), cudaFree(d_bytes), cudaFree(d_vt), cudaFree(d_pr);
+    if (e != cudaSuccess) return vtn_set_err(ctx, VTN_E_CUDA, std::string("vtn_variant_props: ") + cudaGetErrorString(e));
     return VTN_OK;
 }
 
