@@ -309,7 +309,7 @@ int vtn_vcf_tokenize_resident(vtn_ctx* ctx, vtn_vcf_dtext* h);
 int vtn_vcf_dtext_fetch(vtn_ctx* ctx, vtn_vcf_dtext* h, vtn_vcf_fields* out);
 
 /* ---- decompose_blocksub: block substitutions -> SNPs (or MNVs) ----
- * Replaces the record loop of Igor::decompose_blocksub() (decompose_blocksub.cpp:185-421) without its alignment mode (-a).
+ * Replaces the record loop of Igor::decompose_blocksub() (decompose_blocksub.cpp:185-421); its alignment mode (-a) is vtn_blocksub_align below.
  * Output k comes from input record src_rec[k]: len[k] == 0 -> the record itself, unchanged; otherwise a new record at
  * POS = pos1 + off[k] with alleles REF[off, off+len) / ALT[off, off+len) (one base per differing position; with keep_mnv
  * (-m) one run of differences at most max_mnv_dist (-d, default 2) apart).  Outputs are in input order; the reference then
@@ -325,6 +325,25 @@ int vtn_blocksub(vtn_ctx* ctx, const vtn_batch* in, int keep_mnv, int max_mnv_di
 int vtn_blocksub_resident(vtn_ctx* ctx, vtn_dbatch* db, int keep_mnv, int max_mnv_dist); /* async; bench / pipelines */
 int vtn_dbatch_fetch_blocksub(vtn_ctx* ctx, vtn_dbatch* db, uint32_t* src_rec, uint32_t* off, uint32_t* len, uint64_t cap_out,
                               uint64_t* n_out, vtn_blocksub_counters* counters);
+
+/* ---- decompose_blocksub -a: alignment mode ----
+ * Replaces the aggressive branch of the same loop (decompose_blocksub.cpp:190-303) and NeedlemanWunsch::align / trace_path
+ * (needle.cpp:36-133; match 0, mismatch -1, gap -1, needle.h:37): a record whose REF and first ALT differ in length, with REF longer
+ * than one base and ALT longer than one base, is cut along the global alignment of REF[1:] and ALT[1:] (first bases force-aligned)
+ * into chunks = one aligned column plus the gap columns after it, kept when they hold a mismatch or a gap.  Chunk c of record r
+ * (chunk_beg[r] <= c < chunk_beg[r] + n_chunk[r]) is the new record POS = pos1 + pos_ref[c], REF = REF[pos_ref, +len_ref),
+ * ALT = ALT[pos_alt, +len_alt); n_chunk[r] == 0 means the mode does not apply to record r (use vtn_blocksub's plan for it).  The
+ * reference counts ++no_biallelic_blocksub per such record and ++no_additional_snps, ++new_no_variants per chunk (:288-299). */
+typedef struct vtn_blocksub_align_plan
+{
+    uint64_t cap_chunk; /* in: capacity of the four chunk arrays; vtn_blocksub_align_bound(in) always suffices */
+    uint64_t n_chunks;  /* out: slots laid out (chunk_beg[n_rec]) */
+    uint32_t* chunk_beg; /* [n_rec + 1] */
+    uint32_t* n_chunk;   /* [n_rec] */
+    uint32_t *pos_ref, *pos_alt, *len_ref, *len_alt; /* [cap_chunk] */
+} vtn_blocksub_align_plan;
+uint64_t vtn_blocksub_align_bound(const vtn_batch* in);
+int vtn_blocksub_align(vtn_ctx* ctx, const vtn_batch* in, vtn_blocksub_align_plan* plan);
 
 /* ---- decompose_blocksub without any allocation ----
  * No counterpart in the reference: added for callers that cannot call cudaMalloc (code

@@ -872,3 +872,132 @@ int32_t vto_blocksub_plan(const vto_batch* in, int32_t keep_mnv, int32_t max_mnv
     *n_out = k;
     return 0;
 }
+
+/* ---------------------------------------------------------------------------------------------------------
+ * vt decompose_blocksub -a, the aggressive branch (decompose_blocksub.cpp:190-303) with NeedlemanWunsch::align and trace_path
+ * (needle.cpp:36-133; NWParameters match 0, mismatch -1, gap -1, needle.h:37), restated in the reference's own order: fill the
+ * traceback matrix row by row with one rolling score row, walk it back from the last cell, reverse, force-align the first bases,
+ * then cut the trace FORWARD into chunks (:209-246).  For record r the mode applies when ref_len != alt_len, ref_len != 1 and
+ * alt_len > 1, alt being ALT 1 only (:188-190); its chunks are written at chunk_beg[r] .. + n_chunk[r], chunk_beg laid out with
+ * min(ref_len, alt_len) slots per such record.  Pinned to the reference's fixture test/decompose_blocksub/02_* and to
+ * oracle/_ref/vt_ref runs with -a (tests/test_blocksub_oracle.py).
+ * --------------------------------------------------------------------------------------------------------- */
+int32_t vto_blocksub_align(const vto_batch* in, uint32_t* chunk_beg, uint32_t* n_chunk, uint32_t* pos_ref, uint32_t* pos_alt, uint32_t* len_ref,
+                           uint32_t* len_alt)
+{
+    enum { EMPTY, CIGAR_D, CIGAR_M, CIGAR_X, CIGAR_I };
+    uint32_t out = 0;
+    for (uint32_t r = 0; r < in->n_rec; ++r)
+    {
+        const uint32_t ab = in->allele_beg[r], n_allele = in->allele_beg[r + 1] - ab;
+        const size_t ref_len = in->allele_off[ab + 1] - in->allele_off[ab];
+        const size_t alt_len = n_allele == 1 ? 0 : in->allele_off[ab + 2] - in->allele_off[ab + 1];
+        chunk_beg[r] = out;
+        n_chunk[r] = 0;
+        if (!(ref_len != alt_len && ref_len != 1 && alt_len > 1)) continue;
+        const uint8_t* a0 = in->bytes + in->allele_off[ab];
+        const uint8_t* a1 = in->bytes + in->allele_off[ab + 1];
+        const uint8_t *ref = a0 + 1, *read = a1 + 1;
+        const int lr = (int)ref_len - 1, lq = (int)alt_len - 1;
+        uint8_t* matrix = (uint8_t*)calloc((size_t)(lr + 1) * (lq + 1), 1);
+        int* scores = (int*)malloc(sizeof(int) * (size_t)(lq + 1));
+        uint8_t* trace = (uint8_t*)malloc((size_t)lr + lq + 2);
+        for (int i = 0; i <= lr; ++i) matrix[(size_t)i * (lq + 1)] = CIGAR_D;
+        for (int i = 0; i <= lq; ++i)
+        {
+            matrix[i] = CIGAR_I;
+            scores[i] = i * -1;
+        }
+        matrix[0] = CIGAR_M;
+        size_t offset = 0;
+        int score_n = 0;
+        for (int i = 1; i <= lr; ++i)
+        {
+            offset += (size_t)lq + 1;
+            score_n += -1;
+            int best_score = 0;
+            for (int j = 1; j <= lq; ++j)
+            {
+                int score_nw = scores[j - 1], score_w = scores[j], score_diag = score_nw, best_dir;
+                if (ref[i - 1] == read[j - 1])
+                    best_dir = CIGAR_M;
+                else
+                {
+                    best_dir = CIGAR_X;
+                    score_diag += -1;
+                }
+                best_score = score_diag;
+                if (score_w + -1 > best_score)
+                {
+                    best_score = score_w + -1;
+                    best_dir = CIGAR_D;
+                }
+                else if (score_n + -1 > best_score)
+                {
+                    best_score = score_n + -1;
+                    best_dir = CIGAR_I;
+                }
+                scores[j - 1] = score_n;
+                score_n = best_score;
+                matrix[offset + j] = (uint8_t)best_dir;
+            }
+            scores[lq] = best_score;
+        }
+        /* trace_path */
+        int i = lr, j = lq;
+        long k = (long)(lq + 1) * (lr + 1) - 1;
+        size_t nt = 0;
+        while (i > 0 || j > 0)
+        {
+            trace[nt++] = matrix[k];
+            switch (matrix[k])
+            {
+            case CIGAR_X:
+            case CIGAR_M: --i; --j; k -= lq + 2; break;
+            case CIGAR_I: --j; --k; break;
+            case CIGAR_D: --i; k -= lq + 1; break;
+            }
+        }
+        trace[nt++] = a0[0] == a1[0] ? CIGAR_M : CIGAR_X; /* force-aligned first characters, inserted at the front */
+        for (size_t a = 0, b = nt - 1; a < b; ++a, --b)
+        {
+            uint8_t t = trace[a];
+            trace[a] = trace[b];
+            trace[b] = t;
+        }
+        /* break apart the alignment */
+        int has_error = 0, p_ref = 0, p_alt = 0;
+        size_t kk = 0;
+        uint32_t c_pr = 0, c_pa = 0, c_lr = 0, c_la = 0, n = 0;
+        while (p_ref <= lr || p_alt <= lq)
+        {
+            switch (trace[kk++])
+            {
+            case CIGAR_M:
+            case CIGAR_X:
+                if (has_error)
+                {
+                    pos_ref[out + n] = c_pr, pos_alt[out + n] = c_pa, len_ref[out + n] = c_lr, len_alt[out + n] = c_la;
+                    ++n;
+                }
+                c_pr = (uint32_t)p_ref++, c_pa = (uint32_t)p_alt++, c_lr = 1, c_la = 1;
+                has_error = trace[kk - 1] == CIGAR_X;
+                break;
+            case CIGAR_D: c_lr++; p_ref++; has_error = 1; break;
+            case CIGAR_I: c_la++; p_alt++; has_error = 1; break;
+            }
+        }
+        if (has_error)
+        {
+            pos_ref[out + n] = c_pr, pos_alt[out + n] = c_pa, len_ref[out + n] = c_lr, len_alt[out + n] = c_la;
+            ++n;
+        }
+        n_chunk[r] = n;
+        out += (uint32_t)(ref_len < alt_len ? ref_len : alt_len);
+        free(matrix);
+        free(scores);
+        free(trace);
+    }
+    chunk_beg[in->n_rec] = out;
+    return 0;
+}

@@ -98,6 +98,12 @@ int64_t vto_vcf_tokenize(const char* text, uint64_t n_text, uint64_t cap_rec, ui
 int32_t vto_blocksub_plan(const vto_batch* in, int32_t keep_mnv, int32_t max_mnv_dist, uint32_t* src_rec, uint32_t* off, uint32_t* len,
                           uint64_t* n_out, uint32_t counters[4]);
 
+/* vt decompose_blocksub -a (decompose_blocksub.cpp:190-303, needle.cpp:36-133): per record the chunks of the alignment of REF[1:] and
+ * ALT[1:]; chunk_beg[n_rec + 1] is laid out with min(ref_len, alt_len) slots per record the mode applies to, n_chunk[r] = chunks
+ * written (0 = mode does not apply); chunk c -> POS + pos_ref[c], REF[pos_ref, +len_ref), ALT[pos_alt, +len_alt). */
+int32_t vto_blocksub_align(const vto_batch* in, uint32_t* chunk_beg, uint32_t* n_chunk, uint32_t* pos_ref, uint32_t* pos_alt, uint32_t* len_ref,
+                           uint32_t* len_alt);
+
 #ifdef __cplusplus
 }
 #endif

@@ -134,6 +134,18 @@ class Oracle:
         k = int(n_out.value)
         return src[:k], off[:k], ln[:k], list(cnt)
 
+    def blocksub_align(self, b):
+        """decompose_blocksub -a -> per record a list of (pos_ref, pos_alt, len_ref, len_alt); [] where the mode does not apply"""
+        cap = int(b.n_bytes) + 1
+        beg, cnt = np.zeros(b.n_rec + 1, np.uint32), np.zeros(max(b.n_rec, 1), np.uint32)
+        arr = [np.zeros(cap, np.uint32) for _ in range(4)]
+        vb = self._batch(b)
+        self.lib.vto_blocksub_align.restype = C.c_int32
+        self.lib.vto_blocksub_align.argtypes = [C.POINTER(VtoBatch)] + [u32p] * 6
+        rc = self.lib.vto_blocksub_align(C.byref(vb), beg.ctypes.data_as(u32p), cnt.ctypes.data_as(u32p), *[a.ctypes.data_as(u32p) for a in arr])
+        assert rc == 0, rc
+        return [[tuple(int(a[k]) for a in arr) for k in range(int(beg[r]), int(beg[r]) + int(cnt[r]))] for r in range(b.n_rec)]
+
     def vcf_tokenize(self, text):
         n = len(text)
         cap_rec = text.count(b"\n") + 1

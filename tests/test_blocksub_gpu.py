@@ -98,3 +98,37 @@ def test_blocksub_fullsize_properties(ctx):
     assert np.all((ln == 0) == (~is_bs[src])) and np.all(off + ln <= np.maximum(L[src], 1))
     snp = ln == 1
     assert np.all(data[starts_r[src[snp]] + off[snp]] != data[starts_a[src[snp]] + off[snp]])
+
+
+@pytest.mark.parametrize("stem,flags,tag", B.ALIGN_CASES)
+def test_blocksub_align_reference_golden(ctx, stem, flags, tag):
+    vin, vout, verr = B.paths(stem, tag)
+    sites = B.read_sites(vin)
+    keep, dist = B.mode(flags)
+    batch = B.batch_of(sites)
+    src, off, ln, cnt = ctx.blocksub(batch, keep, dist)
+    align = ctx.blocksub_align(batch)
+    assert B.stable_by_pos(B.apply_plan_align(sites, src, off, ln, align)) == B.read_sites(vout)
+    assert B.align_counters(cnt, align) == B.stats_of(open(verr).read())
+
+
+@pytest.mark.parametrize("seed,n,maxlen", [(11, 4000, 30), (12, 300, 700), (13, 2000, 3)])
+def test_blocksub_align_matches_oracle(ctx, oracle, seed, n, maxlen):
+    """random REF / ALT pairs of every shape (equal, one base, empty ALT, long, lower case, multiallelic): chunk for chunk equal"""
+    rng = np.random.default_rng(seed)
+    recs = []
+    for k in range(n):
+        L = int(rng.integers(1, maxlen + 1))
+        ref = "".join(rng.choice(list("ACGT"), L))
+        alt = "".join((c if rng.random() < 0.7 else "") + ("" if rng.random() < 0.8 else str(rng.choice(list("ACGTa")))) for c in ref) or "G"
+        al = [ref, alt]
+        if k % 9 == 0:
+            al.append(ref[:1])
+        if k % 17 == 0:
+            al = [ref]
+        recs.append((0, 10 + k, [a.encode() for a in al]))
+    b = helpers.Batch.from_records(recs)
+    got, exp = ctx.blocksub_align(b), oracle.blocksub_align(b)
+    assert got == exp
+    assert sum(1 for a in exp if a) > n // 8
+    assert ctx.blocksub_align(helpers.Batch.from_records([])) == []

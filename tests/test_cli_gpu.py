@@ -250,9 +250,9 @@ def test_normalize_device_writer_order_streaming(tmp_path, window, batch):
 import blocksub_helpers as BS  # noqa: E402
 
 
-@pytest.mark.parametrize("stem,flags,tag", BS.CASES)
+@pytest.mark.parametrize("stem,flags,tag", BS.CASES + BS.ALIGN_CASES)
 def test_blocksub_cli_reference_golden_bytes(stem, flags, tag, tmp_path):
-    """vtn decompose_blocksub [-m] [-d N] [-p] against the reference's own fixtures (01, 03) and vt_ref outputs, byte for byte"""
+    """vtn decompose_blocksub [-a] [-m] [-d N] [-p] against the reference's own fixtures (01, 02, 03) and vt_ref outputs, byte for byte"""
     vin, vout, verr = BS.paths(stem, tag)
     out = str(tmp_path / "out.vcf")
     rc, err = _run(VTN, ["decompose_blocksub"] + flags + [vin, "-o", out])

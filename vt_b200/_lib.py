@@ -51,6 +51,11 @@ class VtnNormResult(C.Structure):
     ]
 
 
+class VtnBlocksubAlignPlan(C.Structure):
+    _fields_ = [("cap_chunk", C.c_uint64), ("n_chunks", C.c_uint64), ("chunk_beg", c_u32p), ("n_chunk", c_u32p), ("pos_ref", c_u32p), ("pos_alt", c_u32p),
+                ("len_ref", c_u32p), ("len_alt", c_u32p)]
+
+
 class VtnBatchBi(C.Structure):
     _fields_ = [("n_rec", C.c_uint32), ("n_run", C.c_uint32), ("n_ext", C.c_uint32), ("n_bytes", C.c_uint64), ("pos1", c_i32p),
                 ("lens", c_u16p), ("bytes", c_u8p), ("tile_off", c_u32p), ("run_start", c_u32p), ("run_rid", c_i32p),
@@ -132,6 +137,8 @@ SIGNATURES = {
     "vtn_host_alloc": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]),
     "vtn_host_free": (C.c_int, [C.c_void_p, C.c_void_p]),
     "vtn_ref_load_fasta": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "vtn_blocksub_align_bound": (C.c_uint64, [C.POINTER(VtnBatch)]),
+    "vtn_blocksub_align": (C.c_int, [C.c_void_p, C.POINTER(VtnBatch), C.POINTER(VtnBlocksubAlignPlan)]),
     "vtn_variant_props": (C.c_int, [C.c_void_p, C.POINTER(VtnBatch), c_u8p, c_u8p]),
     "vtn_ref_open_fasta": (C.c_int, [C.c_void_p, C.c_char_p]),
     "vtn_ref_require": (C.c_int, [C.c_void_p, C.c_int]),

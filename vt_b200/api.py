@@ -400,6 +400,17 @@ class Context:
         k = int(n_out.value)
         return src[:k], off[:k], ln[:k], [bc.no_variants, bc.no_biallelic_blocksub, bc.no_additional_snps, bc.new_no_variants]
 
+    def blocksub_align(self, batch):
+        """decompose_blocksub -a (vtn_blocksub_align) -> per record a list of (pos_ref, pos_alt, len_ref, len_alt); [] where the mode does not apply"""
+        cb = batch.as_c()
+        cap = int(self.lib.vtn_blocksub_align_bound(C.byref(cb)))
+        beg = np.zeros(batch.n_rec + 1, np.uint32)
+        cnt = np.zeros(max(batch.n_rec, 1), np.uint32)
+        arr = [np.zeros(max(cap, 1), np.uint32) for _ in range(4)]
+        plan = L.VtnBlocksubAlignPlan(cap, 0, _p(beg, L.c_u32p), _p(cnt, L.c_u32p), *[_p(a, L.c_u32p) for a in arr])
+        self._chk(self.lib.vtn_blocksub_align(self.h, C.byref(cb), C.byref(plan)), "vtn_blocksub_align")
+        return [[tuple(int(a[k]) for a in arr) for k in range(int(beg[r]), int(beg[r]) + int(cnt[r]))] for r in range(batch.n_rec)]
+
     def blocksub_resident(self, db, keep_mnv=False, max_mnv_dist=2):
         self._chk(self.lib.vtn_blocksub_resident(self.h, db, 1 if keep_mnv else 0, int(max_mnv_dist)), "vtn_blocksub_resident")
 

@@ -579,3 +579,230 @@ int vtn_blocksub_noalloc(vtn_ctx* ctx, uint32_t n_rec, const uint32_t* d_allele_
     }
     return VTN_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Alignment mode (-a, decompose_blocksub.cpp:190-303): a biallelic record whose REF and ALT differ in length, REF longer than one base
+// and ALT longer than one base, is cut along a global alignment of REF[1:] and ALT[1:] (NeedlemanWunsch, needle.cpp:36-101: match 0,
+// mismatch -1, gap -1; a cell prefers the diagonal, then a deletion if strictly better, else an insertion if strictly better than the
+// diagonal), the first bases force-aligned.  A chunk is one aligned column (match or mismatch) plus the gap columns that follow it; it
+// is emitted when it holds a mismatch or a gap (:209-246).
+// One thread per eligible record: these records are rare and short (tens of bases); the traceback matrix lives in global scratch.
+// ---------------------------------------------------------------------------------------------------------
+namespace
+{
+enum { NW_D = 1, NW_M = 2, NW_X = 3, NW_I = 4 }; // needle.h:44
+
+struct AlignJob
+{
+    uint32_t rec;      // record index
+    uint32_t out_base; // first chunk slot of the record
+    uint64_t mat_off;  // byte offset of its traceback matrix in the scratch
+    uint64_t row_off;  // int offset of its score row
+};
+
+__global__ void __launch_bounds__(64) vtb_align_kernel(const uint32_t* __restrict__ allele_beg, const uint32_t* __restrict__ allele_off,
+                                                        const uint8_t* __restrict__ bytes, const AlignJob* __restrict__ jobs, uint32_t n_jobs,
+                                                        uint8_t* __restrict__ mat_all, int* __restrict__ row_all, uint32_t* __restrict__ n_chunk,
+                                                        uint32_t* __restrict__ pos_ref, uint32_t* __restrict__ pos_alt, uint32_t* __restrict__ len_ref,
+                                                        uint32_t* __restrict__ len_alt)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_jobs) return;
+    const AlignJob J = jobs[t];
+    const uint32_t ab = allele_beg[J.rec];
+    const uint8_t* REF = bytes + allele_off[ab];
+    const uint8_t* ALT = bytes + allele_off[ab + 1];
+    const int lr = (int)(allele_off[ab + 1] - allele_off[ab]) - 1;     // len_ref of the alignment: REF[1:]
+    const int la = (int)(allele_off[ab + 2] - allele_off[ab + 1]) - 1; // len_read: ALT[1:]
+    const uint8_t* ref = REF + 1;
+    const uint8_t* read = ALT + 1;
+    uint8_t* mat = mat_all + J.mat_off;
+    int* scores = row_all + J.row_off;
+    const int W = la + 1;
+    const int gap = -1, mism = -1; // needle.h:37
+    for (int i = 0; i <= lr; ++i) mat[(size_t)i * W] = NW_D;
+    for (int j = 0; j <= la; ++j)
+    {
+        mat[j] = NW_I;
+        scores[j] = j * gap;
+    }
+    mat[0] = NW_M;
+    int score_n = 0;
+    for (int i = 1; i <= lr; ++i)
+    {
+        uint8_t* row = mat + (size_t)i * W;
+        score_n += gap;
+        int best_score = 0;
+        for (int j = 1; j <= la; ++j)
+        {
+            const int score_nw = scores[j - 1], score_w = scores[j];
+            int best_dir;
+            int score_diag = score_nw;
+            if (ref[i - 1] == read[j - 1])
+                best_dir = NW_M; // + score_match (0)
+            else
+            {
+                best_dir = NW_X;
+                score_diag += mism;
+            }
+            best_score = score_diag;
+            if (score_w + gap > best_score)
+            {
+                best_score = score_w + gap;
+                best_dir = NW_D;
+            }
+            else if (score_n + gap > best_score)
+            {
+                best_score = score_n + gap;
+                best_dir = NW_I;
+            }
+            scores[j - 1] = score_n;
+            score_n = best_score;
+            row[j] = (uint8_t)best_dir;
+        }
+        scores[la] = best_score;
+    }
+    // trace_path (needle.cpp:103-133) walked from the end; the chunk rule (decompose_blocksub.cpp:209-246) applied backwards: the gap
+    // columns met since the last aligned column belong to the aligned column reached next
+    int i = lr, j = la;
+    uint32_t nd = 0, ni = 0, n = 0;
+    const uint32_t base = J.out_base;
+    while (i > 0 || j > 0)
+    {
+        const int d = mat[(size_t)i * W + j];
+        if (d == NW_D)
+        {
+            ++nd;
+            --i;
+        }
+        else if (d == NW_I)
+        {
+            ++ni;
+            --j;
+        }
+        else
+        {
+            if (d == NW_X || nd || ni)
+            { // column REF[i] / ALT[j] of the full alleles
+                pos_ref[base + n] = (uint32_t)i, pos_alt[base + n] = (uint32_t)j, len_ref[base + n] = 1 + nd, len_alt[base + n] = 1 + ni;
+                ++n;
+            }
+            nd = ni = 0;
+            --i;
+            --j;
+        }
+    }
+    if (REF[0] != ALT[0] || nd || ni)
+    { // the force-aligned first bases (:200-206)
+        pos_ref[base + n] = 0, pos_alt[base + n] = 0, len_ref[base + n] = 1 + nd, len_alt[base + n] = 1 + ni;
+        ++n;
+    }
+    for (uint32_t a = 0, b = n ? n - 1 : 0; a < b; ++a, --b)
+    { // into ascending order
+        uint32_t x;
+        x = pos_ref[base + a], pos_ref[base + a] = pos_ref[base + b], pos_ref[base + b] = x;
+        x = pos_alt[base + a], pos_alt[base + a] = pos_alt[base + b], pos_alt[base + b] = x;
+        x = len_ref[base + a], len_ref[base + a] = len_ref[base + b], len_ref[base + b] = x;
+        x = len_alt[base + a], len_alt[base + a] = len_alt[base + b], len_alt[base + b] = x;
+    }
+    n_chunk[J.rec] = n;
+}
+
+inline bool align_eligible(const vtn_batch* in, uint32_t r, uint32_t& rl, uint32_t& al)
+{
+    const uint32_t ab = in->allele_beg[r], n = in->allele_beg[r + 1] - ab;
+    rl = in->allele_off[ab + 1] - in->allele_off[ab];
+    al = n == 1 ? 0 : in->allele_off[ab + 2] - in->allele_off[ab + 1];
+    return rl != al && rl != 1 && al > 1; // decompose_blocksub.cpp:190 (only ALT 1 is looked at)
+}
+} // namespace
+
+uint64_t vtn_blocksub_align_bound(const vtn_batch* in)
+{
+    if (!in || !in->allele_beg || !in->allele_off) return 0;
+    uint64_t k = 0;
+    for (uint32_t r = 0; r < in->n_rec; ++r)
+    {
+        uint32_t rl, al;
+        if (align_eligible(in, r, rl, al)) k += std::min(rl, al);
+    }
+    return k;
+}
+
+int vtn_blocksub_align(vtn_ctx* ctx, const vtn_batch* in, vtn_blocksub_align_plan* plan)
+{
+    if (!ctx || !in || !plan) return vtn_set_err(ctx, VTN_E_ARG, "vtn_blocksub_align: bad arguments");
+    const uint32_t n = in->n_rec;
+    if (n && (!in->allele_beg || !in->allele_off || !in->bytes || !plan->chunk_beg || !plan->n_chunk))
+        return vtn_set_err(ctx, VTN_E_ARG, "vtn_blocksub_align: null arrays");
+    std::vector<AlignJob> jobs;
+    uint64_t out = 0;
+    for (uint32_t r = 0; r < n; ++r)
+    {
+        uint32_t rl, al;
+        plan->chunk_beg[r] = (uint32_t)out;
+        plan->n_chunk[r] = 0;
+        if (!align_eligible(in, r, rl, al)) continue;
+        jobs.push_back(AlignJob{r, (uint32_t)out, (uint64_t)rl * al, (uint64_t)al}); // matrix bytes / row ints for now, offsets below
+        out += std::min(rl, al);
+    }
+    if (n) plan->chunk_beg[n] = (uint32_t)out;
+    plan->n_chunks = out;
+    if (out > plan->cap_chunk) return vtn_set_err(ctx, VTN_E_CAPACITY, "vtn_blocksub_align: chunk arrays too small (vtn_blocksub_align_bound)");
+    if (jobs.empty()) return VTN_OK;
+    if (!plan->pos_ref || !plan->pos_alt || !plan->len_ref || !plan->len_alt) return vtn_set_err(ctx, VTN_E_ARG, "vtn_blocksub_align: null chunk arrays");
+    VTN_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    uint32_t *d_beg = nullptr, *d_off = nullptr, *d_cnt = nullptr, *d_chunks = nullptr;
+    uint8_t *d_bytes = nullptr, *d_mat = nullptr;
+    int* d_row = nullptr;
+    AlignJob* d_jobs = nullptr;
+    const uint64_t budget = 512ull << 20; // traceback bytes per launch
+    cudaError_t e = cudaMalloc(&d_beg, 4 * ((size_t)n + 1));
+    if (e == cudaSuccess) e = cudaMalloc(&d_off, 4 * ((size_t)in->n_allele + 1));
+    if (e == cudaSuccess) e = cudaMalloc(&d_bytes, (size_t)in->n_bytes + 1);
+    if (e == cudaSuccess) e = cudaMalloc(&d_cnt, 4 * (size_t)n);
+    if (e == cudaSuccess) e = cudaMalloc(&d_chunks, 16 * (size_t)out + 16);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_beg, in->allele_beg, 4 * ((size_t)n + 1), cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_off, in->allele_off, 4 * ((size_t)in->n_allele + 1), cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_bytes, in->bytes, (size_t)in->n_bytes, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d_cnt, 0, 4 * (size_t)n, s);
+    uint32_t *d_pr = d_chunks, *d_pa = d_chunks + out, *d_lr = d_chunks + 2 * out, *d_la = d_chunks + 3 * out;
+    size_t j0 = 0;
+    while (e == cudaSuccess && j0 < jobs.size())
+    { // slices of jobs whose traceback matrices fit the budget (a single larger one goes alone)
+        size_t j1 = j0;
+        uint64_t mat = 0, row = 0;
+        while (j1 < jobs.size() && (j1 == j0 || mat + jobs[j1].mat_off <= budget))
+        {
+            const uint64_t mb = jobs[j1].mat_off, rb = jobs[j1].row_off;
+            jobs[j1].mat_off = mat, jobs[j1].row_off = row;
+            mat += mb, row += rb;
+            ++j1;
+        }
+        const uint32_t nj = (uint32_t)(j1 - j0);
+        e = cudaMalloc(&d_mat, (size_t)mat + 16);
+        if (e == cudaSuccess) e = cudaMalloc(&d_row, 4 * (size_t)row + 16);
+        if (e == cudaSuccess) e = cudaMalloc(&d_jobs, sizeof(AlignJob) * nj);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(d_jobs, jobs.data() + j0, sizeof(AlignJob) * nj, cudaMemcpyHostToDevice, s);
+        if (e == cudaSuccess)
+        {
+            vtb_align_kernel<<<(nj + 63) / 64, 64, 0, s>>>(d_beg, d_off, d_bytes, d_jobs, nj, d_mat, d_row, d_cnt, d_pr, d_pa, d_lr, d_la);
+            ctx->launches++;
+            e = cudaGetLastError();
+        }
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        cudaFree(d_mat), cudaFree(d_row), cudaFree(d_jobs);
+        d_mat = nullptr, d_row = nullptr, d_jobs = nullptr;
+        j0 = j1;
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(plan->n_chunk, d_cnt, 4 * (size_t)n, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(plan->pos_ref, d_pr, 4 * (size_t)out, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(plan->pos_alt, d_pa, 4 * (size_t)out, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(plan->len_ref, d_lr, 4 * (size_t)out, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(plan->len_alt, d_la, 4 * (size_t)out, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(d_beg), cudaFree(d_off), cudaFree(d_bytes), cudaFree(d_cnt), cudaFree(d_chunks);
+    if (e != cudaSuccess) return vtn_set_err(ctx, VTN_E_CUDA, std::string("vtn_blocksub_align: ") + cudaGetErrorString(e));
+    return VTN_OK;
+}

@@ -1873,7 +1873,7 @@ int cmd_uniq(int argc, char** argv)
 int cmd_blocksub(int argc, char** argv)
 {
     std::string in = "-", outp = "-";
-    bool keep_mnv = false, phased = false;
+    bool keep_mnv = false, phased = false, aggressive = false;
     int max_dist = 2, device = 0;
     for (int k = 1; k < argc; ++k)
     {
@@ -1883,7 +1883,7 @@ int cmd_blocksub(int argc, char** argv)
         else if (a == "--device" && k + 1 < argc) device = atoi(argv[++k]);
         else if (a == "-m") keep_mnv = true;
         else if (a == "-p") phased = true;
-        else if (a == "-a") usage_and_exit("decompose_blocksub", "the alignment mode (-a) is not available in this shim");
+        else if (a == "-a") aggressive = true;
         else if (a == "-i" || a == "-I") usage_and_exit("decompose_blocksub", "intervals are not supported by this shim");
         else if (a == "-" || a[0] != '-') in = a;
         else usage_and_exit("decompose_blocksub", ("unknown option " + a).c_str());
@@ -1891,7 +1891,7 @@ int cmd_blocksub(int argc, char** argv)
     fprintf(stderr, "decompose_blocksub v%s\n\n", VERSION); // print_options, decompose_blocksub.cpp:423-436
     fprintf(stderr, "options:     input VCF file          %s\n", in.c_str());
     fprintf(stderr, "         [o] output VCF file         %s\n", outp.c_str());
-    fprintf(stderr, "         [a] align/aggressive mode   false\n");
+    fprintf(stderr, "         [a] align/aggressive mode   %s\n", aggressive ? "true" : "false");
     fprintf(stderr, "         [m] keep MNVs (Multi-Nucleotide Variants)   %s\n", keep_mnv ? "true" : "false");
     fprintf(stderr, "         [d] MNVs max distance (when -m option is used)   %s\n", max_dist ? "true" : "false");
     fprintf(stderr, "         [p] output phased genotypes %s\n\n", phased ? "true" : "false");
@@ -1923,7 +1923,7 @@ int cmd_blocksub(int argc, char** argv)
     BatchBuf bb;
     std::map<std::string, int> rid_cache;
     LineParser lp;
-    std::vector<uint32_t> src, off, len;
+    std::vector<uint32_t> src, off, len, a_beg, a_cnt, a_pr, a_pa, a_lr, a_la;
     vtn_blocksub_counters tot = {0, 0, 0, 0};
     bool more = !line.empty();
     while (more)
@@ -1935,24 +1935,62 @@ int cmd_blocksub(int argc, char** argv)
         uint64_t n_out = 0;
         vtn_blocksub_counters c;
         if (vtn_blocksub(ctx, &b, keep_mnv ? 1 : 0, max_dist, src.data(), off.data(), len.data(), bound, &n_out, &c)) die(ctx, "vtn_blocksub");
+        if (aggressive)
+        { // -a: records with REF / ALT of different lengths are cut along an alignment (decompose_blocksub.cpp:190-303)
+            const uint64_t cap = vtn_blocksub_align_bound(&b);
+            a_beg.resize((size_t)b.n_rec + 1), a_cnt.resize((size_t)b.n_rec + 1);
+            a_pr.resize(cap + 1), a_pa.resize(cap + 1), a_lr.resize(cap + 1), a_la.resize(cap + 1);
+            vtn_blocksub_align_plan ap;
+            memset(&ap, 0, sizeof ap);
+            ap.cap_chunk = cap;
+            ap.chunk_beg = a_beg.data(), ap.n_chunk = a_cnt.data();
+            ap.pos_ref = a_pr.data(), ap.pos_alt = a_pa.data(), ap.len_ref = a_lr.data(), ap.len_alt = a_la.data();
+            if (vtn_blocksub_align(ctx, &b, &ap)) die(ctx, "vtn_blocksub_align");
+        }
         uint32_t cur = 0xffffffffu;
         std::vector<Tok> col;
         int32_t ps = 0;
-        for (uint64_t k = 0; k < n_out; ++k)
+        // one output of the plan; a record in alignment mode turns its single pass-through entry into its chunks
+        uint64_t k = 0;
+        uint32_t chunk = 0;
+        while (k < n_out)
         {
             const uint32_t r = src[k];
             const std::string& ln = bb.lines[r];
+            const bool aligned = aggressive && a_cnt[r] > 0;
+            uint32_t p_ref = off[k], p_alt = off[k], l_ref = len[k], l_alt = len[k];
+            if (aligned)
+            {
+                const uint32_t c = a_beg[r] + chunk;
+                p_ref = a_pr[c], p_alt = a_pa[c], l_ref = a_lr[c], l_alt = a_la[c];
+            }
             if (r != cur)
             {
                 col = split(ln.data(), ln.size(), '\t');
                 cur = r;
-                ps = b.pos1[r] + (int32_t)off[k]; // the PS vector is sized at the record's first SNP and keeps that value (:343, resize)
+                ps = b.pos1[r] + (int32_t)p_ref; // the PS vector is sized at the record's first SNP and keeps that value (:343, resize; :263)
+                if (aligned)
+                { // counted as a pass-through by vtn_blocksub; the reference counts it as a block substitution and its chunks as SNPs (:288-299)
+                    c.new_no_variants += a_cnt[r] - 1;
+                    c.no_additional_snps += a_cnt[r];
+                    c.no_biallelic_blocksub += 1;
+                }
             }
+            if (aligned)
+            {
+                if (++chunk == a_cnt[r])
+                {
+                    chunk = 0;
+                    ++k;
+                }
+            }
+            else
+                ++k;
             DeviceWriter::Rec rec;
             rec.rid = b.rid[r];
             rec.chrom.assign(col[0].first, col[0].second);
             std::string& o = rec.line;
-            if (!len[k])
+            if (!l_ref && !aligned)
             {
                 rec.pos1 = b.pos1[r];
                 for (int q = 0; q < 5; ++q)
@@ -1964,18 +2002,18 @@ int cmd_blocksub(int argc, char** argv)
             }
             else
             {
-                rec.pos1 = b.pos1[r] + (int32_t)off[k];
+                rec.pos1 = b.pos1[r] + (int32_t)p_ref;
                 o = rec.chrom + "\t" + std::to_string(rec.pos1) + "\t";
                 o.append(col[2].first, col[2].second);
                 o.push_back('\t');
-                o.append(col[3].first + off[k], len[k]);
+                o.append(col[3].first + p_ref, l_ref);
                 o.push_back('\t');
-                o.append(col[4].first + off[k], len[k]);
+                o.append(col[4].first + p_alt, l_alt);
                 std::string extra = "OLD_CLUMPED=" + rec.chrom + ":" + std::to_string(b.pos1[r]) + ":";
                 extra.append(col[3].first, col[3].second);
                 extra.push_back('/');
-                extra.append(col[4].first, col[4].second);
-                if (phased && !keep_mnv && col.size() > 9)
+                for (size_t q = 0; q < col[4].second; ++q) extra.push_back(col[4].first[q] == ',' ? '/' : col[4].first[q]); // bcf_variant2string
+                if (phased && (!keep_mnv || aligned) && col.size() > 9)
                 { // FORMAT gains PS, every GT separator becomes '|' (:346-366)
                     std::vector<Tok> c2(col.begin(), col.begin() + 8);
                     put_tail(o, h, c2, extra);
