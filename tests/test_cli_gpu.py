@@ -281,3 +281,29 @@ def test_normalize_advice_goldens(tmp_path, stem):
     assert open(out).read() == open(g(stem + "_out.vcf")).read()
     unpath = lambda e: "\n".join(re.sub(r"^\[[^\] ]*/", "[", l) for l in _strip(e).splitlines())  # the reference build's __FILE__ path
     assert unpath(err) == unpath(open(g(stem + "_out.stderr")).read())
+
+
+# ---- -f: the filter expression in front of normalize / decompose (filter.cpp; goldens by tests/golden/make_filter_golden.py) ----
+def _filter_cases():
+    p = os.path.join(helpers.GOLDEN, "filter_cases.tsv")
+    return [tuple(l.rstrip("\n").split("\t")) for l in open(p)] if os.path.exists(p) else []
+
+
+@pytest.mark.parametrize("k,tool,exp", _filter_cases())
+def test_filter_expression_goldens(k, tool, exp, tmp_path):
+    """vtn normalize / decompose -f <exp> byte for byte against the unmodified reference, including its evaluation quirks (&& binds looser than
+    ||, a <= between QUAL and an integer keeps its first answer, an undeclared FILTER id is true on every record that has a filter)"""
+    vin, fa = os.path.join(helpers.GOLDEN, "filter_in.vcf"), os.path.join(helpers.GOLDEN, "advice_ref.fa")
+    out = str(tmp_path / "out.vcf")
+    args = tool.split() + ["-f", exp, vin, "-o", out] + (["-r", fa, "-n"] if tool == "normalize" else [])
+    rc, err = _run(VTN, args)
+    assert rc == 0, err
+    assert open(out).read() == open(os.path.join(helpers.GOLDEN, "filter_%s_out.vcf" % k)).read()
+    assert _strip(err) == _strip(open(os.path.join(helpers.GOLDEN, "filter_%s_out.stderr" % k)).read())
+
+
+@pytest.mark.parametrize("exp", ["INFO.K>3", "VTYPE==REF", "QUAL+1>3", "VTYPE==(SNP|INDEL)", "DLEN>0"])
+def test_filter_expression_outside_the_subset_fails_loudly(exp, tmp_path):
+    vin, fa = os.path.join(helpers.GOLDEN, "filter_in.vcf"), os.path.join(helpers.GOLDEN, "advice_ref.fa")
+    rc, err = _run(VTN, ["normalize", "-f", exp, vin, "-o", str(tmp_path / "o.vcf"), "-r", fa, "-n"])
+    assert rc != 0 and "not handled" in err

@@ -21,6 +21,7 @@
 #include <zlib.h>
 #include <algorithm>
 #include <cctype>
+#include <climits>
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
@@ -432,7 +433,7 @@ struct DeviceWriter
 
 struct Args
 {
-    std::string in = "-", out = "-", ref;
+    std::string in = "-", out = "-", ref, fexp;
     int window = 10000;
     bool quiet = false, debug = false, smart = false, opt_n = false, opt_m = false;
     int device = 0;
@@ -474,8 +475,10 @@ Args parse_args(const char* cmd, int argc, char** argv)
             a.opt_m = true;
         else if (s == "--device")
             a.device = atoi(need("--device").c_str());
-        else if (s == "-f" || s == "-i" || s == "-I")
-            usage_and_exit(cmd, "filters and intervals are not supported by this shim");
+        else if (s == "-f")
+            a.fexp = need("-f");
+        else if (s == "-i" || s == "-I")
+            usage_and_exit(cmd, "intervals are not supported by this shim");
         else if (s == "-" || s[0] != '-')
         {
             a.in = s;
@@ -546,6 +549,435 @@ void write_header(FILE* out, const Header& h, const char* extra_line)
     fprintf(out, "%s\n", h.columns.c_str());
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// -f: the reference's filter expression (filter.cpp) for the fields this path knows on the host side of the boundary: VTYPE (from
+// the device's classify_variant mask, vtn_variant_props), N_ALLELE, QUAL, PASS / FILTER.<id> / N_FILTER, integer and float literals and
+// the type names SNP MNP INDEL CLUMPED VNTR SV REF, joined by && || ~ == != < <= > >= & and brackets.  The expression tree is built
+// the way Filter::parse builds it (filter.cpp:1563-1650: the binary operator with the LOWEST code outside brackets, first occurrence,
+// becomes the root, so && splits before || before the comparisons before &) and evaluated with Node::evaluate's rules (:56-478,
+// :509-545, :1129-1165, :1322-1332; missing QUAL makes a comparison false and a ~ true), including the state it keeps between
+// records: a <= between a float and an integer marks its node on the first evaluation and keeps that answer afterwards (:307).
+// A record the filter rejects is skipped entirely, like `continue` in normalize.cpp:196-202.  INFO.*, strings, regular expressions,
+// arithmetic, DLEN / LEN and | are not handled: the tool exits with a message that says so.
+// ------------------------------------------------------------------------------------------------------------
+struct Filter
+{
+    enum
+    {
+        F_BOOL = 64, F_INT = 128, F_FLT = 256, F_LOGIC = 2048, F_CMP = 4096, F_MATH = 8192, F_BCF = 16384,
+        F_NOT = 0 | F_LOGIC | F_BOOL, F_AND = 1 | F_LOGIC | F_BOOL, F_OR = 2 | F_LOGIC | F_BOOL,
+        F_EQ = 3 | F_CMP | F_BOOL, F_NE = 4 | F_CMP | F_BOOL, F_LT = 5 | F_CMP | F_BOOL, F_LE = 6 | F_CMP | F_BOOL, F_GT = 7 | F_CMP | F_BOOL,
+        F_GE = 8 | F_CMP | F_BOOL, F_MATCH = 9 | F_CMP | F_BOOL, F_NO_MATCH = 10 | F_CMP | F_BOOL,
+        F_ADD = 11 | F_MATH | F_FLT, F_SUB = 12 | F_MATH | F_FLT, F_MUL = 13 | F_MATH | F_FLT, F_DIV = 14 | F_MATH | F_FLT,
+        F_BIT_AND = 15 | F_INT | F_MATH | F_BOOL, F_BIT_OR = 16 | F_INT | F_MATH | F_BOOL,
+        F_VTYPE = 33 | F_INT | F_BCF | F_BOOL, F_N_ALLELE = 37 | F_INT | F_BCF, F_QUAL = 38 | F_BCF | F_FLT, F_FILTER = 39 | F_BCF | F_BOOL,
+        F_N_FILTER = 40 | F_INT | F_BCF
+    };
+    struct Node
+    {
+        int type = -1;
+        Node *left = nullptr, *right = nullptr;
+        bool value_exists = false, b = false;
+        int32_t i = 0;
+        float f = 0;
+        std::string tag;
+    };
+    struct Rec // what a record offers the filter
+    {
+        int32_t vtype = 0, n_allele = 0;
+        const char* qual = nullptr; // QUAL and FILTER columns as written
+        size_t qual_len = 0;
+        const char* filt = nullptr;
+        size_t filt_len = 0;
+    };
+    Node* tree = nullptr;
+    std::vector<std::string> header_filters; // IDs the header declares (bcf_has_filter answers -1, which is true, for any other)
+
+    [[noreturn]] static void unsupported(const std::string& what)
+    {
+        fprintf(stderr, "[vtn] filter expression: %s is not handled by this tool (VTYPE, N_ALLELE, QUAL, PASS, FILTER.<id>, N_FILTER, numbers, type names, && || ~ == != < <= > >= & and brackets are)\n",
+                what.c_str());
+        exit(1);
+    }
+    static bool is_literal(const char* e, int len)
+    {
+        if (len > 1 && e[0] == '\'' && memchr(e + 1, '\'', len - 1) == e + len - 1) return true;
+        for (int k = 0; k < len; ++k)
+        {
+            const char c = e[k];
+            if (c == '=' || c == '&' || c == '|' || c == '>' || c == '<' || c == '!' || c == '+' || c == '*' || c == '/' || c == '~' || (c == '-' && k)) return false;
+        }
+        return true;
+    }
+    static bool is_bracketed(const char* e, int len)
+    {
+        if (len < 2 || e[0] != '(' || e[len - 1] != ')') return false;
+        int open = 1;
+        for (int j = 1; j < len - 1; ++j)
+        {
+            if (e[j] == '(') ++open;
+            else if (e[j] == ')')
+            {
+                if (open <= 0) unsupported("an expression with unbalanced brackets");
+                --open;
+            }
+        }
+        return open == 1;
+    }
+    static void trim_brackets(const char*& e, int& len)
+    { // only a pair that encloses the whole expression is removed (filter.cpp:2069-2133)
+        while (len >= 2 && e[0] == '(' && e[len - 1] == ')')
+        {
+            int open = 1;
+            bool nested = true;
+            for (int j = 1; j < len - 1; ++j)
+            {
+                if (e[j] == '(') ++open;
+                else if (e[j] == ')') --open;
+                if (open == 0)
+                {
+                    nested = false;
+                    break;
+                }
+            }
+            if (!nested || open != 1) return;
+            ++e;
+            len -= 2;
+        }
+    }
+    static int peek_op(const char* s, int left, int& oplen)
+    {
+        const bool two = left > 1;
+        oplen = 2;
+        if (s[0] == '&' && two && s[1] == '&') return F_AND;
+        if (s[0] == '|' && two && s[1] == '|') return F_OR;
+        if (s[0] == '=' && two && s[1] == '=') return F_EQ;
+        if (s[0] == '=' && two && s[1] == '~') return F_MATCH;
+        if (s[0] == '~' && two && s[1] == '~') return F_NO_MATCH;
+        if (s[0] == '>' && two && s[1] == '=') return F_GE;
+        if (s[0] == '<' && two && s[1] == '=') return F_LE;
+        if (s[0] == '!' && two && s[1] == '=') return F_NE;
+        oplen = 1;
+        switch (s[0])
+        {
+        case '+': return F_ADD;
+        case '-': return F_SUB;
+        case '*': return F_MUL;
+        case '/': return F_DIV;
+        case '&': return F_BIT_AND;
+        case '|': return F_BIT_OR;
+        case '>': return F_GT;
+        case '<': return F_LT;
+        }
+        oplen = -1;
+        return -1;
+    }
+    void parse_literal(const char* e, int len, Node* n)
+    { // filter.cpp:1818-2010, in its order (strncmp with the LITERAL's length, so a prefix of a keyword matches it, like there)
+        auto is = [&](const char* kw) { return strncmp(e, kw, (size_t)len) == 0; };
+        const std::string lit(e, (size_t)len);
+        if (is("PASS"))
+        {
+            n->type = F_FILTER;
+            n->tag = lit;
+            return;
+        }
+        if (!strncmp(e, "REF", 3) && len >= 3) unsupported("REF"); // REF as a column wins over REF as a type name (:1828)
+        if (!strncmp(e, "ALT", 3) && len >= 3) unsupported("ALT");
+        if (!strncmp(e, "QUAL", 4) && len >= 4)
+        {
+            n->type = F_QUAL;
+            return;
+        }
+        if (!strncmp(e, "FILTER.", 7) && len >= 7)
+        {
+            n->type = F_FILTER;
+            n->tag.assign(e + 7, (size_t)len - 7);
+            return;
+        }
+        if (is("N_FILTER"))
+        {
+            n->type = F_N_FILTER;
+            return;
+        }
+        if (!strncmp(e, "INFO.", 5) && len >= 5) unsupported("INFO." + lit.substr(5));
+        if (!strncmp(e, "VTYPE", 5) && len >= 5)
+        {
+            n->type = F_VTYPE;
+            return;
+        }
+        if (is("N_ALLELE"))
+        {
+            n->type = F_N_ALLELE;
+            return;
+        }
+        static const struct { const char* kw; int v; } names[] = {{"INDEL", VTN_VT_INDEL}, {"SNP", VTN_VT_SNP}, {"MNP", VTN_VT_MNP}, {"CLUMPED", VTN_VT_CLUMPED},
+                                                                   {"VNTR", VTN_VT_VNTR}, {"SV", VTN_VT_SV}, {"REF", VTN_VT_REF}};
+        for (const auto& k : names)
+            if (is(k.kw))
+            {
+                n->type = F_INT;
+                n->i = k.v;
+                n->f = (float)k.v;
+                return;
+            }
+        if (is("DLEN") || is("LEN") || is("VARIANT_CONTAINS_N")) unsupported(lit);
+        char* end = nullptr;
+        const std::string z(lit);
+        const int32_t iv = (int32_t)strtoul(z.c_str(), &end, 10);
+        if (end == z.c_str() + len)
+        {
+            n->type = F_INT;
+            n->i = iv;
+            n->f = (float)iv;
+            return;
+        }
+        const float fv = (float)strtod(z.c_str(), &end);
+        if (end == z.c_str() + len)
+        {
+            n->type = F_FLT;
+            n->f = fv;
+            return;
+        }
+        unsupported("'" + lit + "'");
+    }
+    void parse(const char* e, int len, Node* n)
+    {
+        while (len && *e == ' ') ++e, --len;
+        while (len && e[len - 1] == ' ') --len;
+        if (len <= 0) unsupported("an empty sub-expression");
+        trim_brackets(e, len);
+        if (is_literal(e, len)) return parse_literal(e, len, n);
+        if (e[0] == '~' && (is_literal(e + 1, len - 1) || is_bracketed(e + 1, len - 1)))
+        {
+            n->type = F_NOT;
+            n->left = new Node();
+            return parse(e + 1, len - 1, n->left);
+        }
+        int type = INT_MAX, p = 0, q = 0;
+        for (int r = 0; r < len; ++r)
+        {
+            if (e[r] == '(')
+            { // bypass a bracketed expression
+                int open = 0, s = r;
+                for (; s < len; ++s)
+                {
+                    if (e[s] == '(') ++open;
+                    else if (e[s] == ')' && --open == 0) break;
+                }
+                if (s >= len) unsupported("an expression with unbalanced brackets");
+                r = s;
+            }
+            int oplen = -1;
+            const int c = peek_op(e + r, len, oplen);
+            if (c != -1)
+            {
+                if (c < type)
+                {
+                    type = c;
+                    p = r - 1;
+                    q = r + oplen;
+                }
+                r += oplen - 1;
+            }
+        }
+        if (type == INT_MAX)
+        {
+            fprintf(stderr, "[filter.cpp:1636 parse] binary operator not found in \"%.*s\". Valid operators are  ==,!=,=~,~~,&&,||,&,|,+,-,*,/\n", len, e);
+            exit(1);
+        }
+        if (type == F_MATCH || type == F_NO_MATCH || type == F_ADD || type == F_SUB || type == F_MUL || type == F_DIV || type == F_BIT_OR)
+            unsupported(std::string("the operator in \"") + std::string(e, (size_t)len) + "\"");
+        n->type = type;
+        n->left = new Node();
+        parse(e, p + 1, n->left);
+        n->right = new Node();
+        parse(e + q, len - q, n->right);
+    }
+    bool set(const std::string& exp, const std::vector<std::string>& header_meta)
+    {
+        if (exp.empty()) return false;
+        tree = new Node();
+        parse(exp.c_str(), (int)exp.size(), tree);
+        header_filters.push_back("PASS");
+        for (const std::string& m : header_meta)
+            if (m.compare(0, 13, "##FILTER=<ID=") == 0)
+            {
+                const size_t e = m.find_first_of(",>", 13);
+                header_filters.push_back(m.substr(13, e == std::string::npos ? std::string::npos : e - 13));
+            }
+        return true;
+    }
+    void evaluate(Node* n, const Rec& v)
+    { // Node::evaluate
+        n->value_exists = true;
+        Node *L = n->left, *R = n->right;
+        if (n->type & F_LOGIC)
+        {
+            if (!L->value_exists && n->type == F_NOT)
+            {
+                n->b = true;
+                return;
+            }
+            if (!L->value_exists)
+            {
+                n->b = false;
+                n->value_exists = false;
+                return;
+            }
+            if (n->type == F_NOT)
+            {
+                n->b = !L->b;
+                return;
+            }
+            if (!R->value_exists)
+            {
+                n->b = false;
+                n->value_exists = false;
+                return;
+            }
+            n->b = n->type == F_AND ? (L->b && R->b) : (L->b || R->b);
+        }
+        else if (n->type & F_CMP)
+        {
+            if (!L->value_exists && !R->value_exists)
+            {
+                n->value_exists = false;
+                return;
+            }
+            const int op = n->type;
+            if (op != F_EQ && op != F_NE && op != F_LE && op != F_GE && op != F_GT && op != F_LT) return; // a <= that was marked (:307): b stays
+            if (!L->value_exists || !R->value_exists)
+            {
+                n->b = false;
+                return;
+            }
+            const bool li = (L->type & F_INT) != 0, lf = (L->type & F_FLT) != 0, ri = (R->type & F_INT) != 0, rf = (R->type & F_FLT) != 0;
+            // int with int as integers; a mixed pair as floats (the integer side converted), like the reference's C++ expressions
+            int c = 2; // -1 less, 0 equal, 1 greater, 2 unordered
+            float x = 0, y = 0;
+            bool as_int = false;
+            if (li && ri)
+                as_int = true;
+            else if (li && rf)
+                x = (float)L->i, y = R->f;
+            else if (!li && lf && ri)
+                x = L->f, y = (float)R->i;
+            else if (!li && lf && rf)
+                x = L->f, y = R->f;
+            else
+                unsupported("a comparison between these operands");
+            if (as_int)
+                c = L->i < R->i ? -1 : (L->i > R->i ? 1 : 0);
+            else
+                c = x < y ? -1 : (x > y ? 1 : (x == y ? 0 : 2));
+            switch (op)
+            {
+            case F_EQ: n->b = c == 0; break;
+            case F_NE: n->b = c != 0; break;
+            case F_LE:
+                if (!li && ri) n->type |= F_INT; // filter.cpp:307
+                n->b = c == -1 || c == 0;
+                break;
+            case F_GE: n->b = c == 1 || c == 0; break;
+            case F_GT: n->b = c == 1; break;
+            case F_LT: n->b = c == -1; break;
+            }
+        }
+        else if (n->type & F_BCF)
+        {
+            if (n->type == F_QUAL)
+            {
+                if (v.qual_len == 1 && v.qual[0] == '.')
+                {
+                    n->f = -1;
+                    n->value_exists = false;
+                }
+                else
+                    n->f = strtof(std::string(v.qual, v.qual_len).c_str(), nullptr);
+            }
+            else if (n->type == F_FILTER)
+            {
+                const bool none = v.filt_len == 1 && v.filt[0] == '.';
+                bool has = false, declared = false;
+                for (const std::string& id : header_filters) declared = declared || id == n->tag;
+                if (!none)
+                {
+                    if (!declared)
+                        has = true; // bcf_has_filter returns -1 for an id the header lacks, and -1 is true (:524)
+                    else
+                        for (const Tok& t : split(v.filt, v.filt_len, ';')) has = has || (t.second == n->tag.size() && !memcmp(t.first, n->tag.data(), t.second));
+                }
+                n->b = has;
+            }
+            else if (n->type == F_N_FILTER)
+            {
+                n->i = (v.filt_len == 1 && v.filt[0] == '.') ? 0 : (int32_t)split(v.filt, v.filt_len, ';').size();
+                n->f = (float)n->i;
+                n->b = true;
+            }
+            else if (n->type == F_VTYPE)
+            {
+                n->i = v.vtype;
+                n->b = n->i != 0;
+            }
+            else if (n->type == F_N_ALLELE)
+            {
+                n->i = v.n_allele;
+                n->f = (float)n->i;
+            }
+        }
+        else if (n->type & F_MATH)
+        { // only & reaches here
+            if (!L->value_exists && !R->value_exists)
+            {
+                n->value_exists = false;
+                return;
+            }
+            if (!((L->type & F_INT) && (R->type & F_INT))) unsupported("& between operands that are not integers");
+            n->i = L->i & R->i;
+            n->b = n->i != 0;
+        }
+    }
+    void apply(Node* n, const Rec& v)
+    { // Filter::apply(Node*), filter.cpp:2308-2358: && and || do not look at the right side when the left one decides
+        n->value_exists = false;
+        if (n->left) apply(n->left, v);
+        if (n->type & F_LOGIC)
+        {
+            if (n->type == F_AND)
+            {
+                if (n->left->value_exists && !n->left->b)
+                {
+                    n->b = false;
+                    n->value_exists = true;
+                    return;
+                }
+                apply(n->right, v);
+            }
+            else if (n->type == F_OR)
+            {
+                if (n->left->value_exists && n->left->b)
+                {
+                    n->b = true;
+                    n->value_exists = true;
+                    return;
+                }
+                apply(n->right, v);
+            }
+        }
+        else if (n->right)
+            apply(n->right, v);
+        evaluate(n, v);
+    }
+    bool pass(const Rec& v)
+    {
+        if (!tree) return true;
+        apply(tree, v);
+        return tree->value_exists ? tree->b : false;
+    }
+};
+
 // SoA batch under construction (vtn_batch)
 struct BatchBuf
 {
@@ -577,6 +1009,36 @@ struct BatchBuf
     }
 };
 
+// -f over a tokenized batch: keep[r] = the filter accepts record r; VTYPE comes from the device (vtn_variant_props), QUAL / FILTER from
+// the text.  Returns true when at least one record is rejected.
+bool filter_records(Filter& flt, vtn_ctx* ctx, vtn_batch b, const char* text, const uint64_t* line_off, const uint32_t* tail_off, std::vector<uint8_t>& keep)
+{
+    const size_t n = b.n_rec;
+    std::vector<uint8_t> vtype(n + 1), props(n + 1);
+    if (vtn_variant_props(ctx, &b, vtype.data(), props.data())) die(ctx, "vtn_variant_props");
+    keep.assign(n, 1);
+    bool dropped = false;
+    for (size_t r = 0; r < n; ++r)
+    {
+        Filter::Rec v;
+        v.vtype = vtype[r];
+        v.n_allele = (int32_t)(b.allele_beg[r + 1] - b.allele_beg[r]);
+        const char* q = text + line_off[r] + tail_off[r];
+        const char* e = text + line_off[r + 1];
+        const char* t1 = (const char*)memchr(q, '\t', (size_t)(e - q));
+        v.qual = q, v.qual_len = t1 ? (size_t)(t1 - q) : 0;
+        const char* f0 = t1 ? t1 + 1 : q;
+        const char* t2 = (const char*)memchr(f0, '\t', (size_t)(e - f0));
+        v.filt = f0, v.filt_len = t2 ? (size_t)(t2 - f0) : 0;
+        if (!flt.pass(v))
+        {
+            keep[r] = 0;
+            dropped = true;
+        }
+    }
+    return dropped;
+}
+
 // The site columns of a batch of record lines, parsed on the DEVICE (vtn_vcf_tokenize) instead of line by line on the host:
 // reads up to max_lines lines (the first one is already in `line`), fills the SoA batch; rid comes from the reference
 // (ref_ids) or from the order of appearance / the header dictionary in rid_cache, looked up once per run of equal CHROM.
@@ -586,22 +1048,18 @@ struct LineParser
     std::vector<uint64_t> line_off;
     std::vector<uint32_t> chrom_len, tail_off;
     std::vector<uint8_t> status;
-    bool read_batch(Reader& rd, std::string& line, bool& more, size_t max_lines, BatchBuf& bb, vtn_ctx* ctx, bool ref_ids,
-                    std::map<std::string, int>& rid_cache)
+    Filter* filter = nullptr; // -f: records it rejects are dropped right after the parse, before the tool sees them
+    void tokenize(BatchBuf& bb, vtn_ctx* ctx)
     {
-        bb.clear();
         text.clear();
         size_t commas = 0;
-        while (more && bb.lines.size() < max_lines)
+        for (const std::string& l : bb.lines)
         {
-            text += line;
+            text += l;
             text.push_back('\n');
-            commas += (size_t)std::count(line.begin(), line.end(), ',');
-            bb.lines.push_back(std::move(line));
-            more = rd.getline(line);
+            commas += (size_t)std::count(l.begin(), l.end(), ',');
         }
         const size_t n = bb.lines.size();
-        if (!n) return false;
         line_off.resize(n + 1), chrom_len.resize(n), tail_off.resize(n), status.resize(n);
         bb.pos1.resize(n), bb.allele_beg.resize(n + 1), bb.allele_off.resize(commas + 2 * n + 1), bb.bytes.resize(text.size() + 1);
         vtn_vcf_fields f;
@@ -612,17 +1070,53 @@ struct LineParser
         if (vtn_vcf_tokenize(ctx, text.data(), text.size(), &f)) die(ctx, "vtn_vcf_tokenize");
         bb.allele_off.resize((size_t)f.n_allele + 1);
         bb.bytes.resize((size_t)f.n_bytes);
-        bb.rid.resize(n);
-        const char* prev = nullptr;
-        uint32_t prev_len = 0;
-        int prev_rid = -1;
         for (size_t r = 0; r < n; ++r)
-        {
             if (status[r])
             {
                 fprintf(stderr, "[vtn] malformed VCF record (fewer than 8 columns): %s\n", bb.lines[r].c_str());
                 exit(1);
             }
+    }
+    bool read_batch(Reader& rd, std::string& line, bool& more, size_t max_lines, BatchBuf& bb, vtn_ctx* ctx, bool ref_ids,
+                    std::map<std::string, int>& rid_cache)
+    {
+        bb.clear();
+        size_t bytes = 0;
+        const size_t max_bytes = max_lines == (size_t)-1 ? (size_t)-1 : (size_t)1 << 30; // a batch is also cut by bytes (the tokenizer takes less than 4 GiB per
+                                                                                          // call); uniq asks for the whole file: a position group must stay in one batch
+        while (more && bb.lines.size() < max_lines && bytes < max_bytes)
+        {
+            bytes += line.size() + 1;
+            bb.lines.push_back(std::move(line));
+            more = rd.getline(line);
+        }
+        if (bb.lines.empty()) return false;
+        tokenize(bb, ctx);
+        if (filter)
+        {
+            std::vector<uint8_t> keep;
+            if (filter_records(*filter, ctx, bb.view(), text.data(), line_off.data(), tail_off.data(), keep))
+            {
+                std::vector<std::string> kept;
+                for (size_t r = 0; r < bb.lines.size(); ++r)
+                    if (keep[r]) kept.push_back(std::move(bb.lines[r]));
+                bb.lines.swap(kept);
+                if (!bb.lines.empty()) tokenize(bb, ctx);
+            }
+        }
+        const size_t n = bb.lines.size();
+        bb.rid.resize(n);
+        if (!n)
+        { // everything filtered out: an empty batch
+            bb.pos1.clear(), bb.bytes.clear();
+            bb.allele_beg.assign(1, 0), bb.allele_off.assign(1, 0);
+            return true;
+        }
+        const char* prev = nullptr;
+        uint32_t prev_len = 0;
+        int prev_rid = -1;
+        for (size_t r = 0; r < n; ++r)
+        {
             const char* c = text.data() + line_off[r];
             if (!(prev && prev_len == chrom_len[r] && !memcmp(prev, c, prev_len)))
             {
@@ -1113,6 +1607,7 @@ int cmd_normalize(int argc, char** argv)
         fprintf(stderr, "options:     input VCF file                                  %s\n", a.in.c_str());
         fprintf(stderr, "         [o] output VCF file                                 %s\n", a.out.c_str());
         fprintf(stderr, "         [w] sorting window size                             %d\n", a.window);
+        if (!a.fexp.empty()) fprintf(stderr, "         [f] filter                                          %s\n", a.fexp.c_str());
         fprintf(stderr, "         [m] no fail on masked reference inconsistency       %s\n", strict_level == 1 ? "true" : "false");
         fprintf(stderr, "         [n] no fail on reference inconsistency              %s\n", strict_level == 0 ? "true" : "false");
         fprintf(stderr, "         [q] quiet                                           %s\n", "false");
@@ -1158,6 +1653,9 @@ int cmd_normalize(int argc, char** argv)
     if (const char* e = getenv("VTN_CLI_BLOCK_MB"))
         if (atol(e) > 0) br.target_bytes = (size_t)atol(e) << 20;
     br.start(ctx, rd.f, line, !line.empty());
+    Filter flt;
+    const bool have_filter = flt.set(a.fexp, h.meta);
+    std::vector<char> ftext; // the lines of a block that pass -f
 
     std::map<std::string, int> rid_cache, writer_ids;
     // every array a device call reads or fills is page-locked
@@ -1181,16 +1679,50 @@ int cmd_normalize(int argc, char** argv)
     {
         pt.stop("wait for reader");
         const char* text = blk->text;
-        const size_t n = blk->n_lines;
-        line_off.resize(n + 1), chrom_len.resize(n), tail_off.resize(n), tstatus.resize(n), pos1.resize(n), allele_beg.resize(n + 1);
-        allele_off.resize(blk->n_commas + 2 * n + 1), bytes.resize(blk->n + 1);
+        size_t n = blk->n_lines, text_n = blk->n;
         vtn_vcf_fields f;
-        memset(&f, 0, sizeof f);
-        f.cap_rec = (uint32_t)n, f.cap_allele = (uint32_t)(blk->n_commas + 2 * n), f.cap_bytes = blk->n;
-        f.line_off = line_off.data(), f.chrom_len = chrom_len.data(), f.pos1 = pos1.data(), f.tail_off = tail_off.data();
-        f.status = tstatus.data(), f.allele_beg = allele_beg.data(), f.allele_off = allele_off.data(), f.bytes = bytes.data();
-        if (vtn_vcf_tokenize(ctx, text, blk->n, &f)) die(ctx, "vtn_vcf_tokenize");
+        auto tokenize = [&]() {
+            line_off.resize(n + 1), chrom_len.resize(n), tail_off.resize(n), tstatus.resize(n), pos1.resize(n), allele_beg.resize(n + 1);
+            allele_off.resize(blk->n_commas + 2 * n + 1), bytes.resize(text_n + 1);
+            memset(&f, 0, sizeof f);
+            f.cap_rec = (uint32_t)n, f.cap_allele = (uint32_t)(blk->n_commas + 2 * n), f.cap_bytes = text_n;
+            f.line_off = line_off.data(), f.chrom_len = chrom_len.data(), f.pos1 = pos1.data(), f.tail_off = tail_off.data();
+            f.status = tstatus.data(), f.allele_beg = allele_beg.data(), f.allele_off = allele_off.data(), f.bytes = bytes.data();
+            if (vtn_vcf_tokenize(ctx, text, text_n, &f)) die(ctx, "vtn_vcf_tokenize");
+            for (size_t r = 0; r < n; ++r)
+                if (tstatus[r])
+                {
+                    fprintf(stderr, "[vtn] malformed VCF record (fewer than 8 columns): %.*s\n", (int)(line_off[r + 1] - line_off[r] - 1), text + line_off[r]);
+                    exit(1);
+                }
+        };
+        tokenize();
+        if (have_filter)
+        { // -f: the records the filter rejects leave the block before anything else sees them (normalize.cpp:196-202)
+            vtn_batch fb;
+            fb.n_rec = (uint32_t)n, fb.n_allele = f.n_allele, fb.n_bytes = f.n_bytes;
+            fb.pos1 = pos1.data(), fb.rid = nullptr, fb.allele_beg = allele_beg.data(), fb.allele_off = allele_off.data(), fb.bytes = bytes.data();
+            std::vector<uint8_t> keep;
+            if (filter_records(flt, ctx, fb, text, line_off.data(), tail_off.data(), keep))
+            {
+                ftext.clear();
+                size_t kept = 0;
+                for (size_t r = 0; r < n; ++r)
+                    if (keep[r])
+                    {
+                        ftext.insert(ftext.end(), text + line_off[r], text + line_off[r + 1]);
+                        ++kept;
+                    }
+                text = ftext.data(), text_n = ftext.size(), n = kept;
+                if (n) tokenize();
+            }
+        }
         pt.stop("tokenize");
+        if (!n)
+        {
+            br.release(blk);
+            continue;
+        }
         // contig ids, once per run of equal CHROM: the FASTA's for the kernel, the order of appearance for the writer (the ordered writer
         // flushes when the record's header-dictionary id changes, bcf_ordered_writer.cpp:185-189; the FASTA id cannot stand in for it:
         // contigs the FASTA lacks all have id -1 there, and two of them in a row must still flush)
@@ -1198,11 +1730,6 @@ int cmd_normalize(int argc, char** argv)
         for (size_t r = 0; r < n; ++r)
         {
             const char* c = text + line_off[r];
-            if (tstatus[r])
-            {
-                fprintf(stderr, "[vtn] malformed VCF record (fewer than 8 columns): %.*s\n", (int)(line_off[r + 1] - line_off[r] - 1), c);
-                exit(1);
-            }
             if (!(last_chrom.size() == chrom_len[r] && !memcmp(last_chrom.data(), c, chrom_len[r])) || last_wid < 0)
             {
                 last_chrom.assign(c, chrom_len[r]);
@@ -1543,6 +2070,8 @@ int cmd_decompose(int argc, char** argv)
     bool more = !line.empty();
     std::string o;
     LineParser lp;
+    Filter flt;
+    if (flt.set(a.fexp, h.meta)) lp.filter = &flt;
     while (more)
     {
         lp.read_batch(rd, line, more, BATCH, bb, ctx, false, rid_cache);
@@ -2132,7 +2661,7 @@ int cmd_annotate_indels(int argc, char** argv)
     fprintf(stderr, "         [r] ref FASTA file           %s\n\n", a.ref.c_str());
     vtn_ctx* ctx = nullptr;
     if (vtn_ctx_create(&ctx, a.device)) die(nullptr, "vtn_ctx_create");
-    if (vtn_ref_load_fasta(ctx, a.ref.c_str())) die(ctx, "loading the reference");
+    if (vtn_ref_open_fasta(ctx, a.ref.c_str())) die(ctx, "loading the reference");
     Reader rd;
     if (!rd.open(a.in))
     {
@@ -2196,6 +2725,8 @@ int cmd_annotate_indels(int argc, char** argv)
     BatchBuf bb;
     std::map<std::string, int> rid_cache;
     LineParser lp;
+    Filter flt;
+    if (flt.set(a.fexp, h.meta)) lp.filter = &flt;
     bool more = !line.empty();
     uint32_t no_indels_annotated = 0;
     while (more)
