@@ -307,3 +307,77 @@ def test_filter_expression_outside_the_subset_fails_loudly(exp, tmp_path):
     vin, fa = os.path.join(helpers.GOLDEN, "filter_in.vcf"), os.path.join(helpers.GOLDEN, "advice_ref.fa")
     rc, err = _run(VTN, ["normalize", "-f", exp, vin, "-o", str(tmp_path / "o.vcf"), "-r", fa, "-n"])
     assert rc != 0 and "not handled" in err
+
+
+# ---- compressed files either side: .vcf.gz in (gzip or BGZF) and out (BGZF), chosen like bcf_ordered_writer.cpp:35-83 ----
+def _bgzf_blocks(raw):
+    """walks the BGZF members of a file: [(total size, uncompressed size)]; raises if the structure is off"""
+    out, p = [], 0
+    while p < len(raw):
+        assert raw[p:p + 4] == b"\x1f\x8b\x08\x04" and raw[p + 12:p + 16] == b"BC\x02\x00", p
+        size = raw[p + 16] + 256 * raw[p + 17] + 1
+        out.append((size, int.from_bytes(raw[p + size - 4:p + size], "little")))
+        p += size
+    assert p == len(raw)
+    return out
+
+
+def test_bgzf_output_and_compressed_input(chr20_fasta, tmp_path):
+    import gzip
+    golden = open(os.path.join(helpers.GOLDEN, "c1_normalize_out.vcf"), "rb").read()
+    vin = os.path.join(helpers.GOLDEN, "c1_normalize_in.vcf")
+    out = str(tmp_path / "out.vcf.gz")
+    rc, err = _run(VTN, ["normalize", vin, "-r", chr20_fasta, "-o", out])
+    assert rc == 0, err
+    raw = open(out, "rb").read()
+    assert gzip.decompress(raw) == golden
+    blocks = _bgzf_blocks(raw)
+    assert blocks[-1] == (28, 0) and all(u <= 0xff00 for _, u in blocks)  # the end-of-file member; htslib's block size
+    # the same input as ordinary gzip and as BGZF (written by this tool: `vtn uniq` passes a sorted file without duplicates through)
+    gz_in = str(tmp_path / "in.vcf.gz")
+    with gzip.open(gz_in, "wb") as g:
+        g.write(open(vin, "rb").read())
+    out2 = str(tmp_path / "out2.vcf")
+    rc, err = _run(VTN, ["normalize", gz_in, "-r", chr20_fasta, "-o", out2])
+    assert rc == 0 and open(out2, "rb").read() == golden, err
+    out3 = str(tmp_path / "out3.vcf")
+    rc, err = _run(VTN, ["uniq", out, "-o", out3])  # BGZF in
+    assert rc == 0, err
+    plain = str(tmp_path / "plain.vcf")
+    open(plain, "wb").write(golden)
+    out4 = str(tmp_path / "out4.vcf")
+    rc, err = _run(VTN, ["uniq", plain, "-o", out4])
+    assert rc == 0 and open(out3, "rb").read() == open(out4, "rb").read()
+    if os.path.exists(helpers.VT_REF):  # the unmodified reference reads what this tool wrote
+        out5 = str(tmp_path / "view.vcf")
+        p = subprocess.run([helpers.VT_REF, "view", out, "-o", out5], capture_output=True, text=True)
+        assert p.returncode == 0, p.stderr
+        assert [l for l in open(out5) if not l.startswith("##")] == [l for l in golden.decode().splitlines(True) if not l.startswith("##")]
+
+
+def test_output_name_decides_the_format(tmp_path):
+    vin = os.path.join(helpers.GOLDEN, "blocksub_01_in.vcf")
+    rc, err = _run(VTN, ["decompose_blocksub", vin, "-o", str(tmp_path / "out.txt")])
+    assert rc != 0 and "Not a VCF/BCF file" in err
+
+
+def test_bgzf_large_multiblock_roundtrip(tmp_path):
+    """a file of several hundred blocks: written compressed by one tool, read back block-parallel by the next, equal to the plain run"""
+    import gzip
+    lines = ["##fileformat=VCFv4.2", "##contig=<ID=1,length=100000000>", "##INFO=<ID=K,Number=1,Type=Integer,Description=\"k\">",
+             "#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO"]
+    rng = np.random.default_rng(5)
+    for k in range(400000):
+        ref = "ACGT"[k % 4] + "".join(rng.choice(list("ACGT"), 3))
+        lines.append("1\t%d\trs%d\t%s\t%s\t.\t.\tK=%d" % (100 + 5 * k, k, ref, ref[::-1] if k % 3 else ref[:1], k))
+    vin = str(tmp_path / "in.vcf")
+    open(vin, "w").write("\n".join(lines) + "\n")
+    a, b, c = str(tmp_path / "a.vcf.gz"), str(tmp_path / "b.vcf"), str(tmp_path / "c.vcf")
+    assert _run(VTN, ["decompose_blocksub", vin, "-o", a])[0] == 0
+    assert _run(VTN, ["decompose_blocksub", vin, "-o", b])[0] == 0
+    assert gzip.decompress(open(a, "rb").read()) == open(b, "rb").read()
+    assert len(_bgzf_blocks(open(a, "rb").read())) > 200
+    assert _run(VTN, ["uniq", a, "-o", c])[0] == 0
+    d = str(tmp_path / "d.vcf")
+    assert _run(VTN, ["uniq", b, "-o", d])[0] == 0
+    assert open(c, "rb").read() == open(d, "rb").read()

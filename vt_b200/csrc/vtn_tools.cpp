@@ -37,6 +37,7 @@
 #include <thread>
 #include <vector>
 #include "../../include/vtn.h"
+#include "vtn_bgzf.h"
 
 namespace
 {
@@ -114,38 +115,93 @@ void add_tag(std::map<std::string, Tag>& m, const std::string& line)
     m[id] = t;
 }
 
-// gz/plain line reader
+// line reader over a byte source: plain, gzip, or BGZF inflated block-parallel (vtn_bgzf.h)
 struct Reader
 {
-    gzFile f = nullptr;
+    vtz::ByteSource* src = nullptr;
     std::vector<char> buf;
+    size_t pos = 0, end = 0;
+    bool at_eof = false;
     bool open(const std::string& path)
     {
-        f = path == "-" ? gzdopen(0, "rb") : gzopen(path.c_str(), "rb");
-        if (f) gzbuffer(f, 1 << 20);
-        buf.resize(1 << 16);
-        return f != nullptr;
+        src = vtz::open_source(path);
+        buf.resize(1 << 20);
+        return src != nullptr;
+    }
+    bool refill()
+    { // keeps the unread bytes, appends more; false at the end of the input
+        if (at_eof) return false;
+        if (pos && pos == end) pos = end = 0;
+        if (end == buf.size())
+        {
+            if (pos)
+            {
+                memmove(buf.data(), buf.data() + pos, end - pos);
+                end -= pos, pos = 0;
+            }
+            else
+                buf.resize(buf.size() * 2);
+        }
+        const long got = src->read(buf.data() + end, buf.size() - end);
+        if (got < 0)
+        {
+            fprintf(stderr, "[vtn] read error (damaged compressed input?)\n");
+            exit(1);
+        }
+        if (got == 0)
+        {
+            at_eof = true;
+            return false;
+        }
+        end += (size_t)got;
+        return true;
     }
     bool getline(std::string& out)
     {
         out.clear();
+        size_t scanned = pos;
         for (;;)
         {
-            if (!gzgets(f, buf.data(), (int)buf.size())) return !out.empty();
-            size_t n = strlen(buf.data());
-            out.append(buf.data(), n);
-            if (n && out.back() == '\n')
+            const char* nl = (const char*)memchr(buf.data() + scanned, '\n', end - scanned);
+            if (nl)
             {
-                out.pop_back();
+                out.assign((const char*)buf.data() + pos, nl);
+                pos = (size_t)(nl - buf.data()) + 1;
                 if (!out.empty() && out.back() == '\r') out.pop_back();
                 return true;
             }
+            const size_t have = end - pos;
+            if (!refill())
+            {
+                if (!have) return false;
+                out.assign(buf.data() + pos, buf.data() + end);
+                pos = end;
+                return true;
+            }
+            scanned = pos + have; // refill may have moved the unread bytes to the front
         }
     }
-    ~Reader()
+    // raw bytes for the block reader: what is buffered first, then straight from the source
+    long read(char* dst, size_t n)
     {
-        if (f) gzclose(f);
+        if (pos < end)
+        {
+            const size_t k = std::min(n, end - pos);
+            memcpy(dst, buf.data() + pos, k);
+            pos += k;
+            return (long)k;
+        }
+        if (at_eof) return 0;
+        const long got = src->read(dst, n);
+        if (got < 0)
+        {
+            fprintf(stderr, "[vtn] read error (damaged compressed input?)\n");
+            exit(1);
+        }
+        if (got == 0) at_eof = true;
+        return got;
     }
+    ~Reader() { delete src; }
 };
 
 bool read_header(Reader& rd, Header& h, std::string& first_record)
@@ -497,16 +553,71 @@ void die(vtn_ctx* ctx, const char* what)
     exit(1);
 }
 
+// The output by file name, like BCFOrderedWriter (bcf_ordered_writer.cpp:35-83): "-" and .vcf plain text, .vcf.gz BGZF (deflated by all
+// host threads, vtn_bgzf.h).  The tools write text into the FILE* they get; for a compressed output that FILE* is a stream whose write
+// function feeds the block writer (fopencookie), and fclose finishes the file (last blocks + the end-of-file member).
+struct BgzfCookie
+{
+    vtz::BgzfWriter w;
+    FILE* under = nullptr;
+};
+ssize_t bgzf_cookie_write(void* c, const char* p, size_t n)
+{
+    BgzfCookie* k = (BgzfCookie*)c;
+    return k->w.write(p, n) ? (ssize_t)n : 0;
+}
+int bgzf_cookie_close(void* c)
+{
+    BgzfCookie* k = (BgzfCookie*)c;
+    const bool ok = k->w.close();
+    const int rc = fclose(k->under);
+    delete k;
+    if (!ok || rc)
+    {
+        fprintf(stderr, "[vtn] write error\n");
+        _exit(1);
+    }
+    return 0;
+}
+bool ends_with(const std::string& s, const char* suf)
+{
+    const size_t n = strlen(suf);
+    return s.size() >= n && !s.compare(s.size() - n, n, suf);
+}
+
 FILE* open_out(const std::string& path)
 {
     if (path == "-") return stdout;
+    const bool gz = ends_with(path, ".vcf.gz");
+    if (path == "+" || ends_with(path, ".bcf") || ends_with(path, ".ubcf"))
+    {
+        fprintf(stderr, "[vtn] BCF output (%s) is not written by this tool: use .vcf or .vcf.gz\n", path.c_str());
+        exit(1);
+    }
+    if (!gz && !ends_with(path, ".vcf"))
+    {
+        fprintf(stderr, "[bcf_ordered_writer.cpp:78 BCFOrderedWriter] Not a VCF/BCF file: %s\n", path.c_str());
+        exit(1);
+    }
     FILE* f = fopen(path.c_str(), "w");
     if (!f)
+    {
+        fprintf(stderr, "[bcf_ordered_writer.cpp:86 BCFOrderedWriter] Cannot open VCF/BCF file for writing: %s\n", path.c_str());
+        exit(1);
+    }
+    if (!gz) return f;
+    BgzfCookie* k = new BgzfCookie();
+    k->under = f;
+    k->w.open(f, -1);
+    cookie_io_functions_t io = {nullptr, bgzf_cookie_write, nullptr, bgzf_cookie_close};
+    FILE* s = fopencookie(k, "w", io);
+    if (!s)
     {
         fprintf(stderr, "[vtn] cannot open %s for writing\n", path.c_str());
         exit(1);
     }
-    return f;
+    setvbuf(s, nullptr, _IOFBF, 1 << 20);
+    return s;
 }
 
 void write_header(FILE* out, const Header& h, const char* extra_line)
@@ -1312,7 +1423,7 @@ struct TextBlock
 // Reads the record lines of a VCF in blocks (target_bytes of whole lines, at most max_lines lines) on its own thread, two blocks ahead.
 struct BlockReader
 {
-    gzFile f = nullptr;
+    Reader* f = nullptr;
     size_t target_bytes = 16u << 20, max_lines = 0;
     std::vector<char> pend; // read but not handed out yet
     TextBlock blocks[3];
@@ -1322,7 +1433,7 @@ struct BlockReader
     std::thread th;
     bool done = false, stop = false;
 
-    void start(vtn_ctx* ctx, gzFile file, const std::string& first_line, bool have_first)
+    void start(vtn_ctx* ctx, Reader* file, const std::string& first_line, bool have_first)
     {
         f = file;
         for (auto& b : blocks) b.pinned.ctx = ctx;
@@ -1385,7 +1496,7 @@ struct BlockReader
             {
                 while (!eof && n < want)
                 {
-                    const int got = gzread(f, t + n, (unsigned)std::min<size_t>(want - n, 1u << 30));
+                    const long got = f->read(t + n, want - n);
                     if (got <= 0)
                         eof = true;
                     else
@@ -1652,7 +1763,7 @@ int cmd_normalize(int argc, char** argv)
         if (atol(e) > 0) br.max_lines = (size_t)atol(e);
     if (const char* e = getenv("VTN_CLI_BLOCK_MB"))
         if (atol(e) > 0) br.target_bytes = (size_t)atol(e) << 20;
-    br.start(ctx, rd.f, line, !line.empty());
+    br.start(ctx, &rd, line, !line.empty());
     Filter flt;
     const bool have_filter = flt.set(a.fexp, h.meta);
     std::vector<char> ftext; // the lines of a block that pass -f
