@@ -381,3 +381,33 @@ def test_bgzf_large_multiblock_roundtrip(tmp_path):
     d = str(tmp_path / "d.vcf")
     assert _run(VTN, ["uniq", b, "-o", d])[0] == 0
     assert open(c, "rb").read() == open(d, "rb").read()
+
+
+@pytest.mark.parametrize("ext", [".bcf", ".ubcf"])
+def test_bcf_in_and_out(chr20_fasta, tmp_path, ext):
+    """BCF2 either side: the reference's own BCF of the C1 input goes in, BCF comes out; decoded by this tool (uniq passes a sorted
+    duplicate-free file through) and by the unmodified reference, the records equal the golden VCF"""
+    golden = [l for l in open(os.path.join(helpers.GOLDEN, "c1_normalize_out.vcf")) if not l.startswith("##")]
+    out = str(tmp_path / ("out" + ext))
+    rc, err = _run(VTN, ["normalize", os.path.join(helpers.GOLDEN, "bcf_c1_normalize.bcf"), "-r", chr20_fasta, "-o", out])
+    assert rc == 0, err
+    assert _strip(err) == _strip(open(os.path.join(helpers.GOLDEN, "c1_normalize_out.stderr")).read())
+    back = str(tmp_path / "back.vcf")
+    rc, err = _run(VTN, ["uniq", out, "-o", back])
+    assert rc == 0, err
+    plain = str(tmp_path / "plain.vcf")
+    assert _run(VTN, ["uniq", os.path.join(helpers.GOLDEN, "c1_normalize_out.vcf"), "-o", plain])[0] == 0
+    assert [l for l in open(back) if not l.startswith("##")] == [l for l in open(plain) if not l.startswith("##")]
+    if os.path.exists(helpers.VT_REF):
+        view = str(tmp_path / "view.vcf")
+        p = subprocess.run([helpers.VT_REF, "view", out, "-o", view], capture_output=True, text=True)
+        assert p.returncode == 0, p.stderr
+        assert [l for l in open(view) if not l.startswith("##")] == golden
+
+
+def test_bcf_with_samples_through_decompose(tmp_path):
+    vin = os.path.join(helpers.GOLDEN, "bcf_c1_decompose.bcf")
+    a, b = str(tmp_path / "a.vcf"), str(tmp_path / "b.vcf")
+    assert _run(VTN, ["decompose", "-s", vin, "-o", a])[0] == 0
+    assert _run(VTN, ["decompose", "-s", os.path.join(helpers.GOLDEN, "c1_decompose_in.vcf"), "-o", b])[0] == 0
+    assert [l for l in open(a) if not l.startswith("##")] == [l for l in open(b) if not l.startswith("##")]

@@ -37,6 +37,7 @@
 #include <thread>
 #include <vector>
 #include "../../include/vtn.h"
+#include "vtn_bcf.h"
 #include "vtn_bgzf.h"
 
 namespace
@@ -115,7 +116,7 @@ void add_tag(std::map<std::string, Tag>& m, const std::string& line)
     m[id] = t;
 }
 
-// line reader over a byte source: plain, gzip, or BGZF inflated block-parallel (vtn_bgzf.h)
+// line reader over a byte source: plain, gzip, or BGZF inflated block-parallel (vtn_bgzf.h); BCF2 arrives as text (vtn_bcf.h)
 struct Reader
 {
     vtz::ByteSource* src = nullptr;
@@ -124,7 +125,7 @@ struct Reader
     bool at_eof = false;
     bool open(const std::string& path)
     {
-        src = vtz::open_source(path);
+        src = vtb2::open_any(path); // plain / gzip / BGZF text, or BCF2 (raw or BGZF) turned into text
         buf.resize(1 << 20);
         return src != nullptr;
     }
@@ -554,23 +555,27 @@ void die(vtn_ctx* ctx, const char* what)
 }
 
 // The output by file name, like BCFOrderedWriter (bcf_ordered_writer.cpp:35-83): "-" and .vcf plain text, .vcf.gz BGZF (deflated by all
-// host threads, vtn_bgzf.h).  The tools write text into the FILE* they get; for a compressed output that FILE* is a stream whose write
-// function feeds the block writer (fopencookie), and fclose finishes the file (last blocks + the end-of-file member).
-struct BgzfCookie
+// host threads, vtn_bgzf.h), .bcf BGZF-compressed BCF2, .ubcf and "+" (stdout) uncompressed BCF2 (vtn_bcf.h).  The tools write text into
+// the FILE* they get; for the other formats that FILE* is a stream whose write function feeds the encoder / block writer (fopencookie),
+// and fclose finishes the file (last blocks + the end-of-file member).
+struct OutCookie
 {
-    vtz::BgzfWriter w;
+    vtz::BgzfWriter bz;
+    vtb2::BcfSink bcf;
+    bool use_bz = false, use_bcf = false;
     FILE* under = nullptr;
 };
-ssize_t bgzf_cookie_write(void* c, const char* p, size_t n)
+ssize_t out_cookie_write(void* c, const char* p, size_t n)
 {
-    BgzfCookie* k = (BgzfCookie*)c;
-    return k->w.write(p, n) ? (ssize_t)n : 0;
+    OutCookie* k = (OutCookie*)c;
+    const bool ok = k->use_bcf ? k->bcf.write(p, n) : k->bz.write(p, n);
+    return ok ? (ssize_t)n : 0;
 }
-int bgzf_cookie_close(void* c)
+int out_cookie_close(void* c)
 {
-    BgzfCookie* k = (BgzfCookie*)c;
-    const bool ok = k->w.close();
-    const int rc = fclose(k->under);
+    OutCookie* k = (OutCookie*)c;
+    const bool ok = k->use_bcf ? k->bcf.close() : k->bz.close();
+    const int rc = k->under == stdout ? fflush(stdout) : fclose(k->under);
     delete k;
     if (!ok || rc)
     {
@@ -588,28 +593,26 @@ bool ends_with(const std::string& s, const char* suf)
 FILE* open_out(const std::string& path)
 {
     if (path == "-") return stdout;
-    const bool gz = ends_with(path, ".vcf.gz");
-    if (path == "+" || ends_with(path, ".bcf") || ends_with(path, ".ubcf"))
-    {
-        fprintf(stderr, "[vtn] BCF output (%s) is not written by this tool: use .vcf or .vcf.gz\n", path.c_str());
-        exit(1);
-    }
-    if (!gz && !ends_with(path, ".vcf"))
+    const bool gz = ends_with(path, ".vcf.gz"), bcf = ends_with(path, ".bcf"), ubcf = path == "+" || ends_with(path, ".ubcf");
+    if (!gz && !bcf && !ubcf && !ends_with(path, ".vcf"))
     {
         fprintf(stderr, "[bcf_ordered_writer.cpp:78 BCFOrderedWriter] Not a VCF/BCF file: %s\n", path.c_str());
         exit(1);
     }
-    FILE* f = fopen(path.c_str(), "w");
+    FILE* f = path == "+" ? stdout : fopen(path.c_str(), "w");
     if (!f)
     {
         fprintf(stderr, "[bcf_ordered_writer.cpp:86 BCFOrderedWriter] Cannot open VCF/BCF file for writing: %s\n", path.c_str());
         exit(1);
     }
-    if (!gz) return f;
-    BgzfCookie* k = new BgzfCookie();
+    if (!gz && !bcf && !ubcf) return f;
+    OutCookie* k = new OutCookie();
     k->under = f;
-    k->w.open(f, -1);
-    cookie_io_functions_t io = {nullptr, bgzf_cookie_write, nullptr, bgzf_cookie_close};
+    k->use_bz = gz || bcf, k->use_bcf = bcf || ubcf;
+    if (k->use_bz) k->bz.open(f, -1);
+    k->bcf.f = f;
+    k->bcf.bz = bcf ? &k->bz : nullptr;
+    cookie_io_functions_t io = {nullptr, out_cookie_write, nullptr, out_cookie_close};
     FILE* s = fopencookie(k, "w", io);
     if (!s)
     {
