@@ -411,3 +411,20 @@ def test_bcf_with_samples_through_decompose(tmp_path):
     assert _run(VTN, ["decompose", "-s", vin, "-o", a])[0] == 0
     assert _run(VTN, ["decompose", "-s", os.path.join(helpers.GOLDEN, "c1_decompose_in.vcf"), "-o", b])[0] == 0
     assert [l for l in open(a) if not l.startswith("##")] == [l for l in open(b) if not l.startswith("##")]
+
+
+# ---- -i / -I (goldens by tests/golden/make_interval_golden.py from the unmodified reference) ----
+def _interval_cases():
+    p = os.path.join(helpers.GOLDEN, "interval_cases.tsv")
+    return [tuple(l.rstrip("\n").split("\t")) for l in open(p)] if os.path.exists(p) else []
+
+
+@pytest.mark.parametrize("name,vin,extra", _interval_cases())
+def test_intervals_goldens(name, vin, extra, tmp_path):
+    """plain VCF / no index: the reference's message, everything read; with .tbi / .csi: the records that overlap, interval after interval
+    (one linear pass per interval here instead of the index walk), repeated where intervals overlap"""
+    out = str(tmp_path / "out.vcf")
+    p = subprocess.run([VTN, "decompose"] + extra.split() + [vin, "-o", out], capture_output=True, text=True, cwd=helpers.GOLDEN)
+    assert p.returncode == 0, p.stderr
+    assert open(out).read() == open(os.path.join(helpers.GOLDEN, "interval_%s_out.vcf" % name)).read()
+    assert _strip(p.stderr) == _strip(open(os.path.join(helpers.GOLDEN, "interval_%s_out.stderr" % name)).read())

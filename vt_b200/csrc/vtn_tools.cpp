@@ -116,6 +116,190 @@ void add_tag(std::map<std::string, Tag>& m, const std::string& line)
     m[id] = t;
 }
 
+// -i / -I: genomic intervals (genome_interval.cpp:50-103: "X", "X:2000", "X:2000-4000").  The reference reads by interval only
+// through an index (bcf_ordered_reader.cpp:45-130): a plain VCF, or a compressed file without .tbi / .csi, is read from the start with a
+// message and the intervals are ignored.  With an index it returns, interval after interval, the records whose span [POS, POS +
+// len(REF) - 1] (INFO/END when given) overlaps.  This tool does not walk the index: when one exists it makes one linear pass over the
+// file per interval and keeps the overlapping records, which gives the same records in the same order.
+struct Interval
+{
+    std::string seq;
+    int32_t start1 = 1, end1 = (1 << 29) - 1;
+    std::string to_string() const // genome_interval.cpp:123-137: a whole contig prints as its name
+    {
+        return (start1 != 1 || end1 != (1 << 29) - 1) ? seq + ":" + std::to_string(start1) + "-" + std::to_string(end1) : seq;
+    }
+};
+void add_interval(std::vector<Interval>& v, std::map<std::string, int>& seen, const std::string& text)
+{
+    if (text.empty() || seen.count(text)) return;
+    seen[text] = 1;
+    std::vector<std::string> part;
+    size_t b = 0;
+    for (size_t k = 0; k <= text.size(); ++k)
+        if (k == text.size() || text[k] == ':' || text[k] == '-' || text[k] == '\t')
+        {
+            if (k > b) part.push_back(text.substr(b, k - b));
+            b = k + 1;
+        }
+    Interval iv;
+    auto num = [&](const std::string& x, int32_t& out) {
+        char* e = nullptr;
+        const long val = strtol(x.c_str(), &e, 10);
+        if (x.empty() || *e)
+        {
+            fprintf(stderr, "[genome_interval.cpp:95 set] Invalid genomic interval: %s\n", text.c_str());
+            exit(1);
+        }
+        out = (int32_t)val;
+    };
+    if (part.empty() || part.size() > 3)
+    {
+        fprintf(stderr, "[genome_interval.cpp:101 set] Invalid genomic interval: %s\n", text.c_str());
+        exit(1);
+    }
+    iv.seq = part[0];
+    if (part.size() == 2)
+    {
+        num(part[1], iv.start1);
+        iv.end1 = iv.start1;
+    }
+    else if (part.size() == 3)
+    {
+        num(part[1], iv.start1);
+        num(part[2], iv.end1);
+    }
+    v.push_back(iv);
+}
+// Program::parse_intervals (program.cpp:152-190): the list file first, then the comma separated string, duplicates dropped
+std::vector<Interval> parse_intervals(const std::string& list_file, const std::string& str)
+{
+    std::vector<Interval> v;
+    std::map<std::string, int> seen;
+    if (!list_file.empty())
+    {
+        FILE* f = fopen(list_file.c_str(), "r");
+        if (f)
+        {
+            char line[65536];
+            while (fgets(line, sizeof line, f))
+            {
+                std::string t(line);
+                while (!t.empty() && (t.back() == '\n' || t.back() == '\r')) t.pop_back();
+                add_interval(v, seen, t);
+            }
+            fclose(f);
+        }
+    }
+    size_t b = 0;
+    for (size_t k = 0; k <= str.size(); ++k)
+        if (k == str.size() || str[k] == ',')
+        {
+            if (k > b) add_interval(v, seen, str.substr(b, k - b));
+            b = k + 1;
+        }
+    return v;
+}
+void print_intervals(const char* option_line, const std::vector<Interval>& iv)
+{ // Program::print_int_op, program.cpp:315-334
+    if (iv.empty()) return;
+    fputs(option_line, stderr);
+    for (size_t i = 0; i < std::min<size_t>(iv.size(), 5); ++i) fprintf(stderr, "%s%s", i ? "," : "", iv[i].to_string().c_str());
+    if (iv.size() > 5) fprintf(stderr, " and %zu other intervals\n", iv.size() - 5);
+    else fputc('\n', stderr);
+}
+
+// text of the records that overlap the intervals: one pass over the file per interval, the header from the first pass
+struct IntervalSource : vtz::ByteSource
+{
+    std::string path;
+    std::vector<Interval> iv;
+    size_t cur = 0;
+    vtz::ByteSource* in = nullptr;
+    std::string pend, out;
+    size_t out_pos = 0;
+    bool in_eof = false;
+    IntervalSource(const std::string& p, const std::vector<Interval>& v, vtz::ByteSource* first) : path(p), iv(v), in(first) {}
+    ~IntervalSource() override { delete in; }
+    void take_line(const char* l, size_t n)
+    { // n without the line end
+        if (n && l[0] == '#')
+        {
+            if (cur == 0) out.append(l, n), out.push_back('\n');
+            return;
+        }
+        const Interval& I = iv[cur];
+        const char* t1 = (const char*)memchr(l, '\t', n);
+        if (!t1 || (size_t)(t1 - l) != I.seq.size() || memcmp(l, I.seq.data(), I.seq.size())) return;
+        const char* e = l + n;
+        const char* t2 = (const char*)memchr(t1 + 1, '\t', (size_t)(e - t1 - 1));
+        if (!t2) return;
+        const long pos1 = strtol(std::string(t1 + 1, t2).c_str(), nullptr, 10);
+        const char* t3 = (const char*)memchr(t2 + 1, '\t', (size_t)(e - t2 - 1));
+        const char* t4 = t3 ? (const char*)memchr(t3 + 1, '\t', (size_t)(e - t3 - 1)) : nullptr;
+        if (!t4) return;
+        long end1 = pos1 + (t4 - t3 - 1) - 1;
+        // INFO/END (tbx_parse1 for the VCF preset; vcf_parse for BCF)
+        const char* c = t4;
+        for (int k = 0; k < 3 && c; ++k) c = (const char*)memchr(c + 1, '\t', (size_t)(e - c - 1));
+        if (c)
+        {
+            const char* ie = (const char*)memchr(c + 1, '\t', (size_t)(e - c - 1));
+            if (!ie) ie = e;
+            const std::string info(c + 1, ie);
+            size_t q = info.compare(0, 4, "END=") == 0 ? 0 : info.find(";END=");
+            if (q != std::string::npos)
+            {
+                const long v = strtol(info.c_str() + q + (q ? 5 : 4), nullptr, 10);
+                if (v >= pos1) end1 = v;
+            }
+        }
+        if (pos1 <= I.end1 && end1 >= I.start1) out.append(l, n), out.push_back('\n');
+    }
+    long read(char* dst, size_t n) override
+    {
+        while (out_pos == out.size())
+        {
+            out.clear();
+            out_pos = 0;
+            if (in_eof)
+            {
+                if (++cur >= iv.size()) return 0;
+                delete in;
+                in = vtb2::open_any(path);
+                if (!in) return -1;
+                in_eof = false;
+                pend.clear();
+            }
+            char buf[1 << 16];
+            const long got = in->read(buf, sizeof buf);
+            if (got < 0) return -1;
+            if (got == 0)
+            {
+                in_eof = true;
+                if (!pend.empty()) take_line(pend.data(), pend.size());
+                pend.clear();
+                continue;
+            }
+            pend.append(buf, (size_t)got);
+            size_t b = 0;
+            for (;;)
+            {
+                const char* nl = (const char*)memchr(pend.data() + b, '\n', pend.size() - b);
+                if (!nl) break;
+                size_t e = (size_t)(nl - pend.data());
+                take_line(pend.data() + b, (e > b && pend[e - 1] == '\r') ? e - b - 1 : e - b);
+                b = e + 1;
+            }
+            pend.erase(0, b);
+        }
+        const size_t k = std::min(n, out.size() - out_pos);
+        memcpy(dst, out.data() + out_pos, k);
+        out_pos += k;
+        return (long)k;
+    }
+};
+
 // line reader over a byte source: plain, gzip, or BGZF inflated block-parallel (vtn_bgzf.h); BCF2 arrives as text (vtn_bcf.h)
 struct Reader
 {
@@ -123,10 +307,26 @@ struct Reader
     std::vector<char> buf;
     size_t pos = 0, end = 0;
     bool at_eof = false;
-    bool open(const std::string& path)
+    bool open(const std::string& path, const std::vector<Interval>& intervals = std::vector<Interval>())
     {
         src = vtb2::open_any(path); // plain / gzip / BGZF text, or BCF2 (raw or BGZF) turned into text
         buf.resize(1 << 20);
+        if (src && !intervals.empty())
+        { // BCFOrderedReader's constructor, bcf_ordered_reader.cpp:84-128
+            const bool bgzf = path != "-" && vtz::BgzfSource::sniff(path);
+            auto exists = [](const std::string& p) {
+                FILE* f = fopen(p.c_str(), "rb");
+                if (f) fclose(f);
+                return f != nullptr;
+            };
+            if (!bgzf && !dynamic_cast<vtb2::BcfTextSource*>(src))
+                fprintf(stderr, "[E:BCFOrderedReader] no random access support for VCF file: %s\n", path.c_str());
+            else if (!exists(path + ".tbi") && !exists(path + ".csi"))
+                fprintf(stderr, "[E::idx_find_and_load] Could not retrieve index file for '%s'\n", path.c_str()), // htslib's own line comes first
+                    fprintf(stderr, "[E:BCFOrderedReader] index cannot be loaded for %s for random access, ignoring specified intervals and reading from start.\n", path.c_str());
+            else
+                src = new IntervalSource(path, intervals, src);
+        }
         return src != nullptr;
     }
     bool refill()
@@ -490,7 +690,8 @@ struct DeviceWriter
 
 struct Args
 {
-    std::string in = "-", out = "-", ref, fexp;
+    std::string in = "-", out = "-", ref, fexp, interval_list, interval_str;
+    std::vector<Interval> intervals;
     int window = 10000;
     bool quiet = false, debug = false, smart = false, opt_n = false, opt_m = false;
     int device = 0;
@@ -534,8 +735,10 @@ Args parse_args(const char* cmd, int argc, char** argv)
             a.device = atoi(need("--device").c_str());
         else if (s == "-f")
             a.fexp = need("-f");
-        else if (s == "-i" || s == "-I")
-            usage_and_exit(cmd, "intervals are not supported by this shim");
+        else if (s == "-i")
+            a.interval_str = need("-i");
+        else if (s == "-I")
+            a.interval_list = need("-I");
         else if (s == "-" || s[0] != '-')
         {
             a.in = s;
@@ -545,6 +748,7 @@ Args parse_args(const char* cmd, int argc, char** argv)
             usage_and_exit(cmd, ("unknown option " + s).c_str());
     }
     (void)have_in;
+    a.intervals = parse_intervals(a.interval_list, a.interval_str);
     return a;
 }
 
@@ -1726,7 +1930,9 @@ int cmd_normalize(int argc, char** argv)
         fprintf(stderr, "         [n] no fail on reference inconsistency              %s\n", strict_level == 0 ? "true" : "false");
         fprintf(stderr, "         [q] quiet                                           %s\n", "false");
         fprintf(stderr, "         [d] debug                                           %s\n", a.debug ? "true" : "false");
-        fprintf(stderr, "         [r] reference FASTA file                            %s\n\n", a.ref.c_str());
+        fprintf(stderr, "         [r] reference FASTA file                            %s\n", a.ref.c_str());
+        print_intervals("         [i] intervals                                       ", a.intervals);
+        fputc('\n', stderr);
     }
     PhaseTimer pt;
     pt.start();
@@ -1737,7 +1943,7 @@ int cmd_normalize(int argc, char** argv)
     if (vtn_ref_open_fasta(ctx, a.ref.c_str())) die(ctx, "loading the reference");
     pt.stop("reference open");
     Reader rd;
-    if (!rd.open(a.in))
+    if (!rd.open(a.in, a.intervals))
     {
         fprintf(stderr, "[vtn] cannot open %s\n", a.in.c_str());
         return 1;
@@ -2155,12 +2361,14 @@ int cmd_decompose(int argc, char** argv)
         fprintf(stderr, "decompose v%s\n\n", VERSION);
         fprintf(stderr, "options:     input VCF file        %s\n", a.in.c_str());
         fprintf(stderr, "         [s] smart decomposition   %s (experimental)\n", a.smart ? "true" : "false");
-        fprintf(stderr, "         [o] output VCF file       %s\n\n", a.out.c_str());
+        fprintf(stderr, "         [o] output VCF file       %s\n", a.out.c_str());
+        print_intervals("         [i] intervals             ", a.intervals);
+        fputc('\n', stderr);
     }
     vtn_ctx* ctx = nullptr;
     if (vtn_ctx_create(&ctx, a.device)) die(nullptr, "vtn_ctx_create");
     Reader rd;
-    if (!rd.open(a.in))
+    if (!rd.open(a.in, a.intervals))
     {
         fprintf(stderr, "[vtn] cannot open %s\n", a.in.c_str());
         return 1;
@@ -2403,7 +2611,7 @@ int cmd_uniq(int argc, char** argv)
     vtn_ctx* ctx = nullptr;
     if (vtn_ctx_create(&ctx, a.device)) die(nullptr, "vtn_ctx_create");
     Reader rd;
-    if (!rd.open(a.in))
+    if (!rd.open(a.in, a.intervals))
     {
         fprintf(stderr, "[vtn] cannot open %s\n", a.in.c_str());
         return 1;
@@ -2515,7 +2723,7 @@ int cmd_uniq(int argc, char** argv)
 // ------------------------------------------------------------------------------------------------------------
 int cmd_blocksub(int argc, char** argv)
 {
-    std::string in = "-", outp = "-";
+    std::string in = "-", outp = "-", interval_str, interval_list;
     bool keep_mnv = false, phased = false, aggressive = false;
     int max_dist = 2, device = 0;
     for (int k = 1; k < argc; ++k)
@@ -2527,13 +2735,16 @@ int cmd_blocksub(int argc, char** argv)
         else if (a == "-m") keep_mnv = true;
         else if (a == "-p") phased = true;
         else if (a == "-a") aggressive = true;
-        else if (a == "-i" || a == "-I") usage_and_exit("decompose_blocksub", "intervals are not supported by this shim");
+        else if (a == "-i" && k + 1 < argc) interval_str = argv[++k];
+        else if (a == "-I" && k + 1 < argc) interval_list = argv[++k];
         else if (a == "-" || a[0] != '-') in = a;
         else usage_and_exit("decompose_blocksub", ("unknown option " + a).c_str());
     }
     fprintf(stderr, "decompose_blocksub v%s\n\n", VERSION); // print_options, decompose_blocksub.cpp:423-436
     fprintf(stderr, "options:     input VCF file          %s\n", in.c_str());
     fprintf(stderr, "         [o] output VCF file         %s\n", outp.c_str());
+    const std::vector<Interval> intervals = parse_intervals(interval_list, interval_str);
+    print_intervals("         [i] intervals               ", intervals);
     fprintf(stderr, "         [a] align/aggressive mode   %s\n", aggressive ? "true" : "false");
     fprintf(stderr, "         [m] keep MNVs (Multi-Nucleotide Variants)   %s\n", keep_mnv ? "true" : "false");
     fprintf(stderr, "         [d] MNVs max distance (when -m option is used)   %s\n", max_dist ? "true" : "false");
@@ -2541,7 +2752,7 @@ int cmd_blocksub(int argc, char** argv)
     vtn_ctx* ctx = nullptr;
     if (vtn_ctx_create(&ctx, device)) die(nullptr, "vtn_ctx_create");
     Reader rd;
-    if (!rd.open(in))
+    if (!rd.open(in, intervals))
     {
         fprintf(stderr, "[vtn] cannot open %s\n", in.c_str());
         return 1;
@@ -2772,12 +2983,14 @@ int cmd_annotate_indels(int argc, char** argv)
     fprintf(stderr, "         [o] output VCF file          %s\n", a.out.c_str());
     fprintf(stderr, "         [k] add_flank_annotation     false\n");
     fprintf(stderr, "         [d] debug                    %s\n", a.debug ? "true" : "false");
-    fprintf(stderr, "         [r] ref FASTA file           %s\n\n", a.ref.c_str());
+    fprintf(stderr, "         [r] ref FASTA file           %s\n", a.ref.c_str());
+    print_intervals("         [i] intervals                ", a.intervals);
+    fputc('\n', stderr);
     vtn_ctx* ctx = nullptr;
     if (vtn_ctx_create(&ctx, a.device)) die(nullptr, "vtn_ctx_create");
     if (vtn_ref_open_fasta(ctx, a.ref.c_str())) die(ctx, "loading the reference");
     Reader rd;
-    if (!rd.open(a.in))
+    if (!rd.open(a.in, a.intervals))
     {
         fprintf(stderr, "[vtn] cannot open %s\n", a.in.c_str());
         return 1;
