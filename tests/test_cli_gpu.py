@@ -218,6 +218,26 @@ def test_uniq_cli_reference_golden_bytes(name, tmp_path):
     assert _strip(err) == _strip(exp)
 
 
+@pytest.mark.parametrize("name", ["uniq_a", "uniq_b"])
+@pytest.mark.parametrize("batch", ["1", "7", "50"])
+def test_uniq_cli_in_batches(name, batch, tmp_path):
+    """the file in batches that end between position groups (a group larger than the batch stays whole): same bytes, same counts"""
+    out = str(tmp_path / "out.vcf")
+    p = subprocess.run([VTN, "uniq", os.path.join(helpers.GOLDEN, name + "_in.vcf"), "-o", out], capture_output=True, text=True,
+                       env=dict(os.environ, VTN_CLI_BATCH=batch))
+    assert p.returncode == 0, p.stderr
+    assert open(out).read() == open(os.path.join(helpers.GOLDEN, name + "_out.vcf")).read()
+    assert _strip(p.stderr) == _strip(open(os.path.join(helpers.GOLDEN, name + "_out.stderr")).read())
+
+
+def test_uniq_cli_not_in_order_across_batches(tmp_path):
+    import uniq_helpers as U
+    vin = str(tmp_path / "in.vcf")
+    U.write_uniq_vcf(vin, [(0, 10, ["A", "C"], None), (0, 10, ["A", "G"], None), (0, 12, ["A", "C"], None), (0, 11, ["A", "C"], None)])
+    p = subprocess.run([VTN, "uniq", vin, "-o", str(tmp_path / "o.vcf")], capture_output=True, text=True, env=dict(os.environ, VTN_CLI_BATCH="3"))
+    assert p.returncode == 1 and "VCF file not in order" in p.stderr
+
+
 def test_uniq_cli_not_in_order(tmp_path):
     import uniq_helpers as U
     vin = str(tmp_path / "in.vcf")

@@ -1367,6 +1367,13 @@ struct LineParser
     std::vector<uint32_t> chrom_len, tail_off;
     std::vector<uint8_t> status;
     Filter* filter = nullptr; // -f: records it rejects are dropped right after the parse, before the tool sees them
+    bool keep_groups = false; // uniq: a batch never ends inside a run of records at one CHROM / POS
+    // uniq: which duplicate leaves the reference's reader first depends on whether a record comes before / after the group, so a batch
+    // carries one record of context on either side: lead_line goes in front, and with peek_next a copy of the next unread line is
+    // appended (n_lead / n_peek say how many of the batch's records are such context)
+    std::string lead_line;
+    bool peek_next = false;
+    size_t n_lead = 0, n_peek = 0;
     void tokenize(BatchBuf& bb, vtn_ctx* ctx)
     {
         text.clear();
@@ -1399,16 +1406,38 @@ struct LineParser
                     std::map<std::string, int>& rid_cache)
     {
         bb.clear();
-        size_t bytes = 0;
-        const size_t max_bytes = max_lines == (size_t)-1 ? (size_t)-1 : (size_t)1 << 30; // a batch is also cut by bytes (the tokenizer takes less than 4 GiB per
-                                                                                          // call); uniq asks for the whole file: a position group must stay in one batch
-        while (more && bb.lines.size() < max_lines && bytes < max_bytes)
+        n_lead = n_peek = 0;
+        if (!lead_line.empty())
         {
+            bb.lines.push_back(lead_line);
+            n_lead = 1;
+        }
+        size_t bytes = 0;
+        const size_t max_bytes = (size_t)1 << 30; // a batch is also cut by bytes (the tokenizer takes less than 4 GiB per call)
+        auto site_len = [](const std::string& l) { // length of "CHROM\tPOS"
+            const size_t t1 = l.find('\t');
+            const size_t t2 = t1 == std::string::npos ? t1 : l.find('\t', t1 + 1);
+            return t2 == std::string::npos ? l.size() : t2;
+        };
+        while (more)
+        {
+            if (bb.lines.size() >= max_lines + n_lead || bytes >= max_bytes)
+            { // full; with keep_groups the records at the last position stay together
+                if (!keep_groups) break;
+                const std::string& last = bb.lines.back();
+                const size_t a = site_len(last), b = site_len(line);
+                if (a != b || last.compare(0, a, line, 0, b)) break;
+            }
             bytes += line.size() + 1;
             bb.lines.push_back(std::move(line));
             more = rd.getline(line);
         }
-        if (bb.lines.empty()) return false;
+        if (bb.lines.size() == n_lead) return false;
+        if (peek_next && more)
+        {
+            bb.lines.push_back(line);
+            n_peek = 1;
+        }
         tokenize(bb, ctx);
         if (filter)
         {
@@ -2637,28 +2666,48 @@ int cmd_uniq(int argc, char** argv)
                 rid_cache[id] = k;
             }
         }
-    // the whole file is one batch: a position group must not be cut (see vtn_uniq.cu)
+    // The file goes through in batches that end between position groups: duplicates share CHROM and POS, and inside a group the
+    // device reproduces the reader's order (vtn_uniq.cu), so groups are independent and the outputs concatenate.
+    size_t BATCH = 1u << 20;
+    if (const char* e = getenv("VTN_CLI_BATCH"))
+        if (atol(e) > 0) BATCH = (size_t)atol(e);
     BatchBuf bb;
     bool more = !line.empty();
     LineParser lp;
-    lp.read_batch(rd, line, more, (size_t)-1, bb, ctx, false, rid_cache);
+    lp.keep_groups = true;
+    lp.peek_next = true;
+    std::vector<uint32_t> order;
+    std::vector<uint8_t> first;
+    vtn_uniq_counters cnt = {0, 0};
+    std::string o;
+    while (more)
+    {
+    lp.read_batch(rd, line, more, BATCH, bb, ctx, false, rid_cache);
     vtn_batch in = bb.view();
     const size_t n = in.n_rec;
-    std::vector<uint32_t> order(n + 1);
-    std::vector<uint8_t> first(n + 1);
-    vtn_uniq_counters cnt = {0, 0};
+    if (!n) continue;
+    order.resize(n + 1), first.resize(n + 1);
+    vtn_uniq_counters c1 = {0, 0};
     int64_t bad = -1;
-    if (vtn_uniq(ctx, &in, order.data(), first.data(), &cnt, &bad)) die(ctx, "vtn_uniq");
+    if (vtn_uniq(ctx, &in, order.data(), first.data(), &c1, &bad)) die(ctx, "vtn_uniq");
     if (bad >= 0)
     { // fill_buffer, bcf_synced_reader.cpp:597-601
         fprintf(stderr, "[E:bcf_synced_reader.cpp:599 fill_buffer] VCF file not in order: %s\n", a.in.c_str());
         exit(1);
     }
-    std::string o;
+    // the context records are position groups of their own: the first and the last one to come out; they are neither written nor counted
+    const uint32_t ctx_recs = (uint32_t)(lp.n_lead + lp.n_peek);
+    cnt.no_total_variants += c1.no_total_variants - ctx_recs, cnt.no_unique_variants += c1.no_unique_variants - ctx_recs;
+    lp.lead_line = bb.lines[n - 1 - lp.n_peek];
     for (size_t k = 0; k < n;)
     {
         size_t e = k + 1;
         while (e < n && !first[e]) ++e;
+        if ((lp.n_lead && order[k] == 0) || (lp.n_peek && order[k] == n - 1))
+        {
+            k = e;
+            continue;
+        }
         const std::string& ln = bb.lines[order[k]];
         std::vector<Tok> col = split(ln.data(), ln.size(), '\t');
         std::string merged;
@@ -2708,6 +2757,7 @@ int cmd_uniq(int argc, char** argv)
         fwrite(o.data(), 1, o.size(), out);
         fputc('\n', out);
         k = e;
+    }
     }
     if (out != stdout) fclose(out);
     fprintf(stderr, "\nstats: Total number of observed variants   %u\n", cnt.no_total_variants); // print_stats, uniq.cpp:167-171
