@@ -170,6 +170,8 @@ def cpu_reference_run(n_sample, steps, warmup, names=None, seqs=None, batch=None
     import helpers
     if not os.path.exists(VT_REF):
         raise RuntimeError("oracle/_ref/vt_ref missing: run __graft_entry__.build() in the build container")
+    if ORIG_AFFINITY is not None:
+        os.sched_setaffinity(0, ORIG_AFFINITY)  # the GPU legs ran on the GPU's NUMA node; the reference gets every core of the box
     cores = len(os.sched_getaffinity(0))
     P = max(1, min(cores, 64))
     if seqs is None:
@@ -902,6 +904,39 @@ def pinned_batch(ctx, batch):
     return Batch(pin(batch.pos1), pin(batch.rid), pin(batch.allele_beg), pin(batch.allele_off), pin(batch.data))
 
 
+NUMA_NOTE = None
+ORIG_AFFINITY = None  # the cores the process started with: the CPU baseline gets all of them back
+
+
+def bind_to_gpu_numa_node(dev):
+    """Runs this rank on the cores of the NUMA node its GPU hangs off, BEFORE any page-locked buffer exists: the pinned batches are then
+    allocated on that node (first touch, local policy) and the H2D / D2H DMA does not cross the socket link (round 1's SCALE had all
+    eight ranks' pinned buffers on node 0).  Returns what was done, for the bench line."""
+    try:
+        try:
+            from cuda.bindings import runtime as cudart
+        except ImportError:
+            from cuda import cudart
+        err, bus = cudart.cudaDeviceGetPCIBusId(32, dev)
+        bus = (bus.decode(errors="replace") if isinstance(bus, bytes) else str(bus)).split("\x00")[0].strip().lower()
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bus).read())
+        if node < 0:
+            return "gpu %s: no NUMA node reported, not bound" % bus
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        global ORIG_AFFINITY
+        ORIG_AFFINITY = os.sched_getaffinity(0)
+        cpus &= ORIG_AFFINITY
+        if not cpus:
+            return "gpu %s on node %d: none of its cores are available to this process, not bound" % (bus, node)
+        os.sched_setaffinity(0, cpus)
+        return "gpu %s on NUMA node %d: process bound to its %d cores before the pinned buffers were allocated" % (bus, node, len(cpus))
+    except Exception as e:  # no sysfs entry, no cuda-python: run unbound
+        return "not bound (%s)" % str(e)[:80]
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -924,6 +959,8 @@ def main():
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
         return
+    global NUMA_NOTE
+    NUMA_NOTE = bind_to_gpu_numa_node(local)
     if args.workload == "c5":
         run_c5(args, rank, world, local)
         return
@@ -1252,6 +1289,7 @@ def run_c2_c4(args, rank, world, local):
             "records_per_gpu": batch.n_rec, "changed_per_gpu": res.n_changed,
             "l2": "inputs+outputs per step (%d MB) exceed the 126 MB L2; no explicit flush" % ((h2d + d2h) // 1000000),
             "sharding": "independent batch per rank, reference replicated, no collective",
+            "numa": "every rank: " + str(NUMA_NOTE) + " (rank 0's note)",
             "per_rank_ms_per_step": per_rank_ms, "per_rank_e2e_ms_per_step": per_rank_e2e,
             "checked_against_oracle": "%d records [%d, %d) of the timed batch: status, vtype, changed records and new allele bytes bit-exact (untimed checker leg)" % (checked, a_chk, a_chk + n_chk),
         },
