@@ -912,6 +912,8 @@ def bind_to_gpu_numa_node(dev):
     """Runs this rank on the cores of the NUMA node its GPU hangs off, BEFORE any page-locked buffer exists: the pinned batches are then
     allocated on that node (first touch, local policy) and the H2D / D2H DMA does not cross the socket link (round 1's SCALE had all
     eight ranks' pinned buffers on node 0).  Returns what was done, for the bench line."""
+    if os.environ.get("VTN_BENCH_NO_NUMA"):
+        return "not bound (VTN_BENCH_NO_NUMA set)"
     try:
         try:
             from cuda.bindings import runtime as cudart
