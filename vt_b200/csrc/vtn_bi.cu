@@ -215,7 +215,8 @@ int vtn_dbatch_create_bi(vtn_ctx* ctx, const vtn_batch_bi* in, vtn_dbatch** db)
 static VtnDevBiView bi_view(const vtn_dbatch* d, uint32_t r0, uint32_t nr)
 {
     const uint32_t tile = vtn_normalize_tile_records();
-    return VtnDevBiView{nr, r0, d->pos1 + r0, d->lens + r0, d->bytes, d->tile_off + r0 / tile, d->run_start, d->run_rid, d->n_run, d->ext_rec, d->ext_len, d->n_ext};
+    return VtnDevBiView{nr, r0, d->pos1 + r0, d->lens + r0, d->bytes, d->tile_off + r0 / tile, d->run_start, d->run_rid, d->n_run, d->ext_rec, d->ext_len, d->n_ext,
+                        d->n_bytes > 6ull * d->n_rec ? 1u : 0u};
 }
 
 int vtn_normalize_resident_bi(vtn_ctx* ctx, vtn_dbatch* d)

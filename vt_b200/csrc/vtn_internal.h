@@ -63,6 +63,7 @@ struct VtnDevBiView
     const uint32_t* ext_rec;
     const uint32_t* ext_len;
     uint32_t n_ext;
+    uint32_t wide; // the batch averages more than 6 allele bytes per record (STR indels, C4): the fast launch stages a 24-byte-per-record window
 };
 
 struct VtnDevNotes

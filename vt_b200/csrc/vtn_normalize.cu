@@ -1228,17 +1228,23 @@ __global__ void __launch_bounds__(VTC_THREADS, 2) vtn_compact_kernel(VtnDevBatch
 // refuses is appended to defer_list and redone by the <false> launch, which lays a small vtn_batch view of the tile
 // (allele_beg / allele_off / rid in shared memory) under normalize_record.
 // ---------------------------------------------------------------------------------------------------------
-#define VTB_BYTES_CAP (VTN_WTILE * 8 + 64)
+// staging window of the fast launch: mean allele bytes per record a tile may hold before it is deferred.  8 for ordinary call sets (C2
+// averages 2.9), 24 for batches of long alleles (the STR indels of C4 average ~12; with the small window every tile was deferred and C4
+// ran 2.6x slower than in the general layout).  The launcher picks the instantiation from the batch's own mean (VtnDevBiView::wide).
+#define VTB_BPR_NARROW 8
+#define VTB_BPR_WIDE 24
 #ifndef VTB_MIN_BLOCKS_FAST
 #define VTB_MIN_BLOCKS_FAST 8
 #endif
 
+template <int BPR>
 struct __align__(16) BiWarpSmem
 {
-    uint8_t bytes[VTB_BYTES_CAP];
+    enum { BYTES_CAP = VTN_WTILE * BPR + 64 };
+    uint8_t bytes[BYTES_CAP];
     int32_t pos1[VTN_WTILE];
     uint32_t queue[VTN_WTILE]; // record index in the tile | REF length << 8 | ALT length << 16 (lengths < 255 on the fast launch)
-    uint16_t qoff[VTN_WTILE];  // byte offset of the queued record inside the tile (fast launch: tile bytes <= VTB_BYTES_CAP)
+    uint16_t qoff[VTN_WTILE];  // byte offset of the queued record inside the tile (fast launch: tile bytes <= BYTES_CAP)
     uint8_t sv[VTN_WTILE];
 };
 struct BiWarpGen // the generic launch's view of one tile as a vtn_batch
@@ -1258,19 +1264,19 @@ __device__ __forceinline__ void vtn_note(const VtnDevNotes& N, uint32_t rec, uin
     }
 }
 
-template <bool FAST_ONLY>
-__global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTB_MIN_BLOCKS_FAST : VTN_MIN_BLOCKS) vtn_normalize_bi_kernel(
+template <bool FAST_ONLY, int BPR>
+__global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? (BPR > VTB_BPR_NARROW ? 6 : VTB_MIN_BLOCKS_FAST) : VTN_MIN_BLOCKS) vtn_normalize_bi_kernel(
     VtnDevRef R, VtnDevBiView B, VtnDevNormOut O, VtnDevNotes NT, VtnDevScratch X, uint32_t* defer_list, uint32_t* defer_count,
     uint32_t n_tiles_all, unsigned long long* k2_ctl, uint32_t tpb, int fresh)
 {
-    __shared__ BiWarpSmem SM[VTN_WARPS];
+    __shared__ BiWarpSmem<BPR> SM[VTN_WARPS];
     __shared__ BiWarpGen GM[FAST_ONLY ? 1 : VTN_WARPS];
     __shared__ uint32_t s_lut[256];
     __shared__ uint64_t s_gbase[VTN_CONTIG_CAP];
     __shared__ int64_t s_clen[VTN_CONTIG_CAP];
     const int lane = threadIdx.x & 31;
-    if (!FAST_ONLY && *defer_count == 0) return;
-    BiWarpSmem& S = SM[threadIdx.x >> 5];
+    if (!FAST_ONLY && blockIdx.x * VTN_WARPS >= *defer_count) return; // the list is usually empty or short: most blocks leave here
+    BiWarpSmem<BPR>& S = SM[threadIdx.x >> 5];
     BiWarpGen& G = GM[FAST_ONLY ? 0 : (threadIdx.x >> 5)];
     uint32_t my_counter = 0;
     const uint32_t cat_shift = 6u * (uint32_t)(lane < 5 ? lane : 0);
@@ -1382,7 +1388,7 @@ __global__ void __launch_bounds__(32 * VTN_WARPS, FAST_ONLY ? VTB_MIN_BLOCKS_FAS
             }
         }
         const uint32_t b0 = b_lo & ~15u;
-        const bool bytes_staged = (b_lo - b0) + tile_bytes + 16 <= VTB_BYTES_CAP;
+        const bool bytes_staged = (b_lo - b0) + tile_bytes + 16 <= (uint32_t)BiWarpSmem<BPR>::BYTES_CAP;
         if (FAST_ONLY && !bytes_staged) deferred = true;
         if (FAST_ONLY && deferred)
         {
@@ -1701,23 +1707,29 @@ int vtn_launch_normalize_bi(vtn_ctx* ctx, const VtnDevBiView& in, const VtnDevNo
     const uint32_t n_blocks2 = (n_tiles + tpb - 1) / tpb;
     unsigned long long* ctl = reinterpret_cast<unsigned long long*>(tile_counter);
     VTN_CUDA(ctx, cudaMemsetAsync(ctl, 0, (VTC_CTL_AGG + (size_t)n_blocks2) * sizeof(unsigned long long), s));
-    static int per_sm = 0, per_sm_slow = 0;
+    static int per_sm = 0, per_sm_wide = 0, per_sm_slow = 0;
     if (!per_sm)
     {
-        VTN_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vtn_normalize_bi_kernel<true>, 32 * VTN_WARPS, 0));
-        VTN_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_slow, vtn_normalize_bi_kernel<false>, 32 * VTN_WARPS, 0));
+        VTN_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vtn_normalize_bi_kernel<true, VTB_BPR_NARROW>, 32 * VTN_WARPS, 0));
+        VTN_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_wide, vtn_normalize_bi_kernel<true, VTB_BPR_WIDE>, 32 * VTN_WARPS, 0));
+        VTN_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_slow, vtn_normalize_bi_kernel<false, VTB_BPR_NARROW>, 32 * VTN_WARPS, 0));
         if (per_sm < 1) per_sm = 1;
+        if (per_sm_wide < 1) per_sm_wide = 1;
         if (per_sm_slow < 1) per_sm_slow = 1;
     }
-    uint32_t grid = (uint32_t)(ctx->sm_count * per_sm);
+    uint32_t grid = (uint32_t)(ctx->sm_count * (in.wide ? per_sm_wide : per_sm));
     const uint32_t need = (n_tiles + VTN_WARPS - 1) / VTN_WARPS;
     if (grid > need) grid = need;
     uint32_t* defer_list = reinterpret_cast<uint32_t*>(tile_state);
-    vtn_normalize_bi_kernel<true><<<grid, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, notes, scr, defer_list, tile_counter, n_tiles, ctl, tpb, accumulate ? 0 : 1);
+    if (in.wide)
+        vtn_normalize_bi_kernel<true, VTB_BPR_WIDE><<<grid, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, notes, scr, defer_list, tile_counter, n_tiles, ctl, tpb, accumulate ? 0 : 1);
+    else
+        vtn_normalize_bi_kernel<true, VTB_BPR_NARROW><<<grid, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, notes, scr, defer_list, tile_counter, n_tiles, ctl, tpb, accumulate ? 0 : 1);
     VTN_CUDA(ctx, cudaGetLastError());
-    uint32_t grid2 = (uint32_t)(ctx->sm_count * 2); // the deferred tiles are few: two blocks per SM walk the list
+    // the deferred tiles: a full wave is launched, and a block whose first tile lies beyond the list's end returns at once
+    uint32_t grid2 = (uint32_t)(ctx->sm_count * per_sm_slow);
     if (grid2 > need) grid2 = need;
-    vtn_normalize_bi_kernel<false><<<grid2, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, notes, scr, defer_list, tile_counter, n_tiles, ctl, tpb, 0);
+    vtn_normalize_bi_kernel<false, VTB_BPR_NARROW><<<grid2, 32 * VTN_WARPS, 0, s>>>(ctx->dref, in, out, notes, scr, defer_list, tile_counter, n_tiles, ctl, tpb, 0);
     VTN_CUDA(ctx, cudaGetLastError());
     vtn_compact_kernel<<<n_blocks2, VTC_THREADS, 0, s>>>(VtnDevBatchView{}, scr, out, n_tiles, ctl, n_blocks2, tpb);
     VTN_CUDA(ctx, cudaGetLastError());
