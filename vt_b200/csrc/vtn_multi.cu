@@ -7,6 +7,8 @@
 // single-device path on its device, and the results put back together in input order.
 #include <string.h>
 #include <algorithm>
+#include <condition_variable>
+#include <mutex>
 #include <thread>
 #include "vtn_internal.h"
 
@@ -330,62 +332,100 @@ int vtn_multi_decompose_normalize(vtn_multi* m, const vtn_batch* in, uint32_t* s
         return VTN_OK;
     }
     if (n && (!in->pos1 || !in->rid || !in->allele_beg || !in->allele_off || (in->n_bytes && !in->bytes))) return multi_err(m, VTN_E_ARG, "batch has null arrays");
-    std::vector<uint32_t> cut(S + 1);
-    int rc = vtn_shard_plan(in->rid, n, S, 1, cut.data());
+    // More chunks than slots: slot s takes chunks s, s + S, ... in order.  A chunk's kernels need nothing from the others; only its
+    // copy-out needs the totals of every chunk before it (its place in the caller's arrays), so a slot waits for the earlier chunks'
+    // RUNS, not for their copies: one slot's H2D overlaps another slot's D2H, on one device (repeat its id in vtn_multi_create) as
+    // well as across devices.
+    // One chunk per slot unless VTN_MULTI_CHUNK_REC asks for smaller ones (tests): measured on B200, more rounds of smaller chunks cost
+    // more in per-chunk synchronisation than their finer overlap gains (12.5 M records over 2 GPUs: 10.5 ms with 2 chunks, 14.1 ms
+    // with 6); the overlap comes from giving a device two or three slots.
+    uint32_t rounds = 1;
+    if (const char* e = getenv("VTN_MULTI_CHUNK_REC"))
+        if (atol(e) > 0)
+        {
+            const uint64_t per_round = (uint64_t)atol(e) * S;
+            rounds = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(64, (n + per_round / 2) / per_round));
+        }
+    const uint32_t C = S * rounds;
+    std::vector<uint32_t> cut(C + 1);
+    int rc = vtn_shard_plan(in->rid, n, C, 1, cut.data());
     if (rc) return multi_err(m, rc, "vtn_shard_plan failed");
     struct Shard
     {
         uint64_t n_out = 0, n_changed = 0, n_changed_bytes = 0;
         vtn_decomp_counters dc{};
         vtn_norm_counters nc{};
-        int rc = 0;
-        std::string err;
+        bool run_done = false;
     };
-    std::vector<Shard> sh(S);
+    std::vector<Shard> sh(C);
+    std::mutex mu;
+    std::condition_variable cv;
+    int fail_rc = 0;
+    std::string fail_msg;
+    auto fail = [&](int code, const std::string& msg) {
+        std::lock_guard<std::mutex> g(mu);
+        if (!fail_rc) fail_rc = code, fail_msg = msg;
+        cv.notify_all();
+    };
     std::vector<std::thread> th;
     for (uint32_t s = 0; s < S; ++s)
         th.emplace_back([&, s]() {
-            Shard& H = sh[s];
-            H.rc = vtn_shard_decompose_run(m->ctx[s], in, cut[s], cut[s + 1], &H.n_out, &H.n_changed, &H.n_changed_bytes);
-            if (H.rc) H.err = vtn_last_error(m->ctx[s]);
+            for (uint32_t c = s; c < C; c += S)
+            {
+                Shard& H = sh[c];
+                const int r1 = vtn_shard_decompose_run(m->ctx[s], in, cut[c], cut[c + 1], &H.n_out, &H.n_changed, &H.n_changed_bytes);
+                if (r1)
+                {
+                    fail(r1, "device " + std::to_string(m->ctx[s]->device) + ": " + vtn_last_error(m->ctx[s]));
+                    return;
+                }
+                uint64_t ko = 0, kc = 0, kb = 0;
+                {
+                    std::unique_lock<std::mutex> g(mu);
+                    H.run_done = true;
+                    cv.notify_all();
+                    cv.wait(g, [&]() {
+                        if (fail_rc) return true;
+                        for (uint32_t j = 0; j < c; ++j)
+                            if (!sh[j].run_done) return false;
+                        return true;
+                    });
+                    if (fail_rc) return;
+                    for (uint32_t j = 0; j < c; ++j) ko += sh[j].n_out, kc += sh[j].n_changed, kb += sh[j].n_changed_bytes;
+                }
+                if (kc + H.n_changed > out->cap_changed || kb + H.n_changed_bytes > out->cap_changed_bytes)
+                {
+                    fail(VTN_E_CAPACITY, "vtn_multi_decompose_normalize: result capacity too small");
+                    return;
+                }
+                vtn_norm_result view = *out;
+                const int r2 = vtn_shard_decompose_fetch(m->ctx[s], cut[c], ko, kc, kb, H.n_out, H.n_changed, H.n_changed_bytes, src_rec, alt_idx, &H.dc, &view);
+                H.nc = view.counters;
+                if (r2)
+                {
+                    fail(r2, "device " + std::to_string(m->ctx[s]->device) + ": " + vtn_last_error(m->ctx[s]));
+                    return;
+                }
+            }
         });
     for (auto& t : th) t.join();
-    th.clear();
-    for (uint32_t s = 0; s < S; ++s)
-        if (sh[s].rc) return multi_err(m, sh[s].rc, "device " + std::to_string(m->ctx[s]->device) + ": " + sh[s].err);
-    std::vector<uint64_t> ko(S + 1, 0), kc(S + 1, 0), kb(S + 1, 0);
-    for (uint32_t s = 0; s < S; ++s)
-    {
-        ko[s + 1] = ko[s] + sh[s].n_out;
-        kc[s + 1] = kc[s] + sh[s].n_changed;
-        kb[s + 1] = kb[s] + sh[s].n_changed_bytes;
-    }
-    *n_out = ko[S];
-    out->n_changed = (uint32_t)kc[S];
-    out->n_changed_bytes = kb[S];
-    if (kc[S] > out->cap_changed || kb[S] > out->cap_changed_bytes) return multi_err(m, VTN_E_CAPACITY, "vtn_multi_decompose_normalize: result capacity too small (n_changed / n_changed_bytes are set)");
-    for (uint32_t s = 0; s < S; ++s)
-        th.emplace_back([&, s]() {
-            Shard& H = sh[s];
-            vtn_norm_result view = *out;
-            H.rc = vtn_shard_decompose_fetch(m->ctx[s], cut[s], ko[s], kc[s], kb[s], H.n_out, H.n_changed, H.n_changed_bytes, src_rec, alt_idx, &H.dc, &view);
-            H.nc = view.counters;
-            if (H.rc) H.err = vtn_last_error(m->ctx[s]);
-        });
-    for (auto& t : th) t.join();
-    for (uint32_t s = 0; s < S; ++s)
-        if (sh[s].rc) return multi_err(m, sh[s].rc, "device " + std::to_string(m->ctx[s]->device) + ": " + sh[s].err);
+    if (fail_rc) return multi_err(m, fail_rc, fail_msg);
+    uint64_t ko = 0, kc = 0, kb = 0;
     vtn_decomp_counters dtot{};
     memset(&out->counters, 0, sizeof out->counters);
-    for (uint32_t s = 0; s < S; ++s)
+    for (uint32_t c = 0; c < C; ++c)
     {
-        add_counters(out->counters, sh[s].nc);
-        dtot.no_variants += sh[s].dc.no_variants;
-        dtot.no_biallelic += sh[s].dc.no_biallelic;
-        dtot.no_multiallelic += sh[s].dc.no_multiallelic;
-        dtot.no_additional_biallelic += sh[s].dc.no_additional_biallelic;
+        ko += sh[c].n_out, kc += sh[c].n_changed, kb += sh[c].n_changed_bytes;
+        add_counters(out->counters, sh[c].nc);
+        dtot.no_variants += sh[c].dc.no_variants;
+        dtot.no_biallelic += sh[c].dc.no_biallelic;
+        dtot.no_multiallelic += sh[c].dc.no_multiallelic;
+        dtot.no_additional_biallelic += sh[c].dc.no_additional_biallelic;
     }
+    *n_out = ko;
+    out->n_changed = (uint32_t)kc;
+    out->n_changed_bytes = kb;
+    out->chg_off[kc] = kb;
     if (dcounters) *dcounters = dtot;
-    out->chg_off[kc[S]] = kb[S];
     return VTN_OK;
 }
