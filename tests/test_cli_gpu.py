@@ -448,3 +448,63 @@ def test_intervals_goldens(name, vin, extra, tmp_path):
     assert p.returncode == 0, p.stderr
     assert open(out).read() == open(os.path.join(helpers.GOLDEN, "interval_%s_out.vcf" % name)).read()
     assert _strip(p.stderr) == _strip(open(os.path.join(helpers.GOLDEN, "interval_%s_out.stderr" % name)).read())
+
+
+# ---- the block reader of `vtn normalize`: line ends, block cuts, window 0 ----
+def _small_normalize_input(tmp_path, n=700, big_info=0):
+    rng = np.random.default_rng(81)
+    names, seqs = helpers.synth_reference(rng, n_contig=2, length=9000, n_runs=False)
+    fa = str(tmp_path / "ref.fa")
+    helpers.write_fasta(fa, names, seqs)
+    lines = ["##fileformat=VCFv4.2"] + ["##contig=<ID=%s,length=%d>" % (nm, s.shape[0]) for nm, s in zip(names, seqs)]
+    lines += ['##INFO=<ID=S,Number=1,Type=String,Description="s">', '##INFO=<ID=AF,Number=A,Type=Float,Description="f">',
+              "#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO"]
+    for c, s in enumerate(seqs):
+        for p in np.sort(rng.choice(np.arange(60, s.shape[0] - 60), size=n, replace=False)):
+            p = int(p)
+            ref = bytes(s[p:p + 3]).decode()
+            k = int(rng.integers(0, 4))
+            alt = ["ACGT"[(("ACGT".index(ref[0])) + 1) % 4] + ref[1:], ref[:1], ref + ref[-1], ref[:2]][k]
+            info = [".", "AF=0.12345678", "S=x", "AF=0.5;S=" + "y" * big_info if big_info else "S=z"][int(rng.integers(0, 4))]
+            lines.append("%s\t%d\t.\t%s\t%s\t%s\t.\t%s" % (names[c], p + 1, ref, alt, [".", "30", "12.5"][k % 3], info))
+    return fa, lines
+
+
+@pytest.mark.parametrize("variant", ["crlf", "no_final_newline", "line_longer_than_block", "tiny_batches"])
+def test_normalize_block_reader_variants(tmp_path, variant):
+    """the same records as LF text in one block, and as CRLF text / without the last line end / with a 1.3 MB line at 1 MB blocks /
+    in 5-record blocks: identical output"""
+    fa, lines = _small_normalize_input(tmp_path, big_info=1300000 if variant == "line_longer_than_block" else 0)
+    plain, other = str(tmp_path / "plain.vcf"), str(tmp_path / "other.vcf")
+    open(plain, "w").write("\n".join(lines) + "\n")
+    env = dict(os.environ)
+    if variant == "crlf":
+        open(other, "wb").write(("\r\n".join(lines) + "\r\n").encode())
+    elif variant == "no_final_newline":
+        open(other, "w").write("\n".join(lines))
+    elif variant == "line_longer_than_block":
+        open(other, "w").write("\n".join(lines) + "\n")
+        env["VTN_CLI_BLOCK_MB"] = "1"
+    else:
+        open(other, "w").write("\n".join(lines) + "\n")
+        env["VTN_CLI_BATCH"] = "5"
+    o1, o2 = str(tmp_path / "o1.vcf"), str(tmp_path / "o2.vcf")
+    p1 = subprocess.run([VTN, "normalize", plain, "-r", fa, "-o", o1], capture_output=True, text=True)
+    p2 = subprocess.run([VTN, "normalize", other, "-r", fa, "-o", o2], capture_output=True, text=True, env=env)
+    assert p1.returncode == 0 and p2.returncode == 0, (p1.stderr[-1500:], p2.stderr[-1500:])
+    assert open(o1, "rb").read() == open(o2, "rb").read()
+    assert [l for l in _strip(p1.stderr).splitlines() if "file" not in l] == [l for l in _strip(p2.stderr).splitlines() if "file" not in l]
+
+
+@needs_ref
+@pytest.mark.parametrize("window", ["0", "1"])
+def test_normalize_window_zero_and_one(tmp_path, window):
+    fa, lines = _small_normalize_input(tmp_path, n=300)
+    vin = str(tmp_path / "in.vcf")
+    open(vin, "w").write("\n".join(lines) + "\n")
+    o1, o2 = str(tmp_path / "o1.vcf"), str(tmp_path / "o2.vcf")
+    p1 = subprocess.run([VTN, "normalize", vin, "-r", fa, "-o", o1, "-w", window], capture_output=True, text=True)
+    p2 = subprocess.run([helpers.VT_REF, "normalize", vin, "-r", fa, "-o", o2, "-w", window], capture_output=True, text=True)
+    assert p1.returncode == p2.returncode == 0, (p1.stderr[-1500:], p2.stderr[-1500:])
+    assert open(o1).read() == open(o2).read()
+    assert _msgs(p1.stderr) == _msgs(p2.stderr)
