@@ -508,3 +508,40 @@ def test_normalize_window_zero_and_one(tmp_path, window):
     assert p1.returncode == p2.returncode == 0, (p1.stderr[-1500:], p2.stderr[-1500:])
     assert open(o1).read() == open(o2).read()
     assert _msgs(p1.stderr) == _msgs(p2.stderr)
+
+
+def test_tool_entry_points_in_process(chr20_fasta, tmp_path):
+    """libvtn_tools.so used as a library (include/vtn_tools.h): vtn_tool_normalize called twice in one process, then vtn_tool_decompose;
+    every resource comes back (no quick exit), the outputs equal the goldens"""
+    import ctypes as C
+    code = r'''
+import ctypes as C, os, sys
+lib = C.CDLL(sys.argv[1])
+def call(fn, args):
+    arr = (C.c_char_p * (len(args) + 1))(*[a.encode() for a in args], None)
+    f = getattr(lib, fn)
+    f.argtypes = [C.c_int, C.POINTER(C.c_char_p)]
+    f.restype = C.c_int if fn == "vtn_tool_normalize" else None
+    return f(len(args), arr)
+for k in (1, 2):
+    r = call("vtn_tool_normalize", ["normalize", sys.argv[2], "-r", sys.argv[3], "-o", sys.argv[4] + str(k) + ".vcf"])
+    assert r == 1, r   # print == true: the caller prints the elapsed time
+call("vtn_tool_decompose", ["decompose", sys.argv[5], "-o", sys.argv[4] + "d.vcf"])
+print("done")
+'''
+    script = str(tmp_path / "drive.py")
+    open(script, "w").write(code)
+    import sys
+    p = subprocess.run([sys.executable, script, os.path.join(helpers.ROOT, "vt_b200", "libvtn_tools.so"), os.path.join(helpers.GOLDEN, "c1_normalize_in.vcf"),
+                        chr20_fasta, str(tmp_path / "out"), os.path.join(helpers.GOLDEN, "c1_decompose_in.vcf")], capture_output=True, text=True)
+    assert p.returncode == 0 and "done" in p.stdout, p.stderr[-2000:]
+    golden = open(os.path.join(helpers.GOLDEN, "c1_normalize_out.vcf")).read()
+    assert open(str(tmp_path / "out1.vcf")).read() == golden and open(str(tmp_path / "out2.vcf")).read() == golden
+    assert open(str(tmp_path / "outd.vcf")).read() == open(os.path.join(helpers.GOLDEN, "c1_decompose_out.vcf")).read()
+
+
+def test_normalize_stdin_to_stdout(chr20_fasta):
+    vin = open(os.path.join(helpers.GOLDEN, "c1_normalize_in.vcf"), "rb").read()
+    p = subprocess.run([VTN, "normalize", "-", "-r", chr20_fasta, "-o", "-", "-q"], input=vin, capture_output=True)
+    assert p.returncode == 0, p.stderr[-1000:]
+    assert p.stdout == open(os.path.join(helpers.GOLDEN, "c1_normalize_out.vcf"), "rb").read()
