@@ -34,6 +34,7 @@
 #include <map>
 #include <mutex>
 #include <string>
+#include <string_view>
 #include <thread>
 #include <vector>
 #include "../../include/vtn.h"
@@ -81,12 +82,26 @@ struct Tag
     char type = 'S'; // I(nteger) F(loat) S(tring) C(haracter) f(L)ag
 };
 
+typedef std::map<std::string, Tag, std::less<>> TagMap;
+
 struct Header
 {
     std::vector<std::string> meta; // ## lines
     std::string columns;           // #CHROM line
-    std::map<std::string, Tag> info, fmt;
+    TagMap info, fmt; // looked up by string_view: no temporary strings on the per-record paths
     int n_samples = 0;
+    bool float_info() const
+    {
+        for (const auto& kv : info)
+            if (kv.second.type == 'F') return true;
+        return false;
+    }
+    bool float_fmt() const
+    {
+        for (const auto& kv : fmt)
+            if (kv.second.type == 'F') return true;
+        return false;
+    }
 };
 
 std::string attr(const std::string& line, const char* key)
@@ -101,7 +116,7 @@ std::string attr(const std::string& line, const char* key)
     return line.substr(p, e - p);
 }
 
-void add_tag(std::map<std::string, Tag>& m, const std::string& line)
+void add_tag(TagMap& m, const std::string& line)
 {
     Tag t;
     std::string id = attr(line, "ID"), num = attr(line, "Number"), ty = attr(line, "Type");
@@ -522,6 +537,131 @@ std::vector<Tok> split(const char* s, size_t n, char sep)
     return v;
 }
 
+// true when htslib would print this Float value exactly as it is written: "." or a plain decimal -?(0|[1-9]d*)(.d*[1-9])? with at most
+// six significant digits inside [0.0001, 999999] (float32 keeps such a decimal and kputd prints its six-digit rounding without
+// trailing zeros: the same characters).  Anything else (exponents, more digits, trailing zeros, "+", "nan") goes through put_float.
+bool canon_float(const char* p, size_t n)
+{
+    if (n == 1 && p[0] == '.') return true;
+    size_t i = 0;
+    if (i < n && p[i] == '-') ++i;
+    if (i >= n) return false;
+    size_t int_digits = 0, sig = 0;
+    bool started = false; // a non-zero digit has been seen
+    if (p[i] == '0')
+    {
+        ++i;
+        int_digits = 1;
+        if (i < n && p[i] != '.') return false; // "00", "01"
+    }
+    else
+    {
+        while (i < n && p[i] >= '0' && p[i] <= '9') ++i, ++int_digits, ++sig, started = true;
+        if (!int_digits || int_digits > 6) return false;
+    }
+    if (i == n) return true; // an integer of at most six digits, or "0"
+    if (p[i] != '.') return false;
+    ++i;
+    if (i == n) return false; // "1."
+    size_t lead_zeros = 0;
+    for (; i < n; ++i)
+    {
+        if (p[i] < '0' || p[i] > '9') return false;
+        if (!started && p[i] == '0')
+        {
+            ++lead_zeros;
+            continue;
+        }
+        started = true;
+        ++sig;
+    }
+    if (p[n - 1] == '0') return false; // trailing zero ("0.0", "1.50")
+    return sig <= 6 && lead_zeros <= 3;
+}
+bool canon_float_list(const char* p, size_t n)
+{
+    size_t b = 0;
+    for (size_t k = 0; k <= n; ++k)
+        if (k == n || p[k] == ',')
+        {
+            if (!canon_float(p + b, k - b)) return false;
+            b = k + 1;
+        }
+    return true;
+}
+
+// true when htslib would print the columns from QUAL on exactly as they were read (what put_tail would produce is the input): QUAL and
+// every Float-typed INFO / FORMAT value already in htslib's form, no empty INFO field to drop, every sample with as many values as
+// FORMAT has keys.  p[0..n) = the line from QUAL to its end, without the line end.
+bool tail_is_plain(const Header& h, bool float_info, bool float_fmt, const char* p, size_t n)
+{
+    size_t i = 0;
+    while (i < n && p[i] != '\t') ++i;
+    if (!canon_float(p, i)) return false;
+    if (i >= n) return false;
+    ++i;
+    while (i < n && p[i] != '\t') ++i; // FILTER
+    if (i >= n) return false;
+    const size_t i0 = ++i;
+    size_t f0 = i0; // start of the current INFO field
+    while (i <= n)
+    {
+        if (i == n || p[i] == '\t' || p[i] == ';')
+        {
+            if (i == f0) return false; // an empty field (";;", leading or trailing ';') or an empty column
+            if (float_info)
+            {
+                const char* eq = (const char*)memchr(p + f0, '=', i - f0);
+                if (eq)
+                {
+                    auto it = h.info.find(std::string_view(p + f0, (size_t)(eq - (p + f0))));
+                    if (it != h.info.end() && it->second.type == 'F' && !canon_float_list(eq + 1, (size_t)(p + i - eq - 1))) return false;
+                }
+            }
+            if (i == n || p[i] == '\t') break;
+            f0 = i + 1;
+        }
+        ++i;
+    }
+    if (i >= n) return true; // sites only
+    // FORMAT
+    ++i;
+    const size_t k0 = i;
+    size_t keys = 1;
+    while (i < n && p[i] != '\t') keys += p[i++] == ':';
+    uint64_t fl = 0; // bit k: key k is Float-typed
+    if (float_fmt)
+    {
+        if (keys > 64) return false;
+        size_t b = k0, k = 0;
+        for (size_t q = k0; q <= i; ++q)
+            if (q == i || p[q] == ':')
+            {
+                auto it = h.fmt.find(std::string_view(p + b, q - b));
+                if (it != h.fmt.end() && it->second.type == 'F') fl |= 1ull << k;
+                b = q + 1;
+                ++k;
+            }
+    }
+    while (i < n)
+    {
+        ++i;
+        size_t vals = 1, b = i;
+        for (;; ++i)
+        {
+            if (i == n || p[i] == '\t' || p[i] == ':')
+            {
+                if (fl && ((fl >> (vals - 1)) & 1) && !canon_float_list(p + b, i - b)) return false;
+                if (i == n || p[i] == '\t') break;
+                ++vals;
+                b = i + 1;
+            }
+        }
+        if (vals != keys) return false;
+    }
+    return true;
+}
+
 // INFO column as htslib re-emits it: Float-typed values canonicalised, everything else as written
 void put_info(std::string& out, const Header& h, const char* s, size_t n)
 {
@@ -542,8 +682,7 @@ void put_info(std::string& out, const Header& h, const char* s, size_t n)
             out.append(kv.first, kv.second);
             continue;
         }
-        std::string key(kv.first, eq - kv.first);
-        auto it = h.info.find(key);
+        auto it = h.info.find(std::string_view(kv.first, (size_t)(eq - kv.first)));
         out.append(kv.first, eq - kv.first + 1);
         if (it != h.info.end() && it->second.type == 'F')
             put_float_list(out, eq + 1, kv.second - (eq - kv.first) - 1);
@@ -565,7 +704,7 @@ void put_sample(std::string& out, const Header& h, const std::vector<Tok>& keys,
             out.push_back('.');
             continue;
         }
-        auto it = h.fmt.find(std::string(keys[k].first, keys[k].second));
+        auto it = h.fmt.find(std::string_view(keys[k].first, keys[k].second));
         if (it != h.fmt.end() && it->second.type == 'F')
             put_float_list(out, vals[k].first, vals[k].second);
         else
@@ -577,6 +716,19 @@ void put_sample(std::string& out, const Header& h, const std::vector<Tok>& keys,
 // bcf_update_info_string puts it there: an existing KEY keeps its place and gets the new value, a new KEY goes last
 void put_tail(std::string& out, const Header& h, const std::vector<Tok>& col, const std::string& extra_info)
 {
+    if (extra_info.empty() && col.size() >= 8)
+    { // nothing to add and nothing htslib would print differently: the columns go out as they came in
+        const char* t0 = col[5].first;
+        const size_t tn = (size_t)(col.back().first + col.back().second - t0);
+        bool contiguous = true; // the columns are slices of one line (a caller may have swapped one for a rebuilt string)
+        for (size_t c = 6; c < col.size() && contiguous; ++c) contiguous = col[c].first == col[c - 1].first + col[c - 1].second + 1;
+        if (contiguous && tail_is_plain(h, true, true, t0, tn))
+        {
+            out.push_back('\t');
+            out.append(t0, tn);
+            return;
+        }
+    }
     out.push_back('\t');
     put_float(out, col[5].first, col[5].second);
     out.push_back('\t');
@@ -1789,45 +1941,6 @@ struct BlockReader
     }
 };
 
-// true when htslib would print the columns from QUAL on exactly as they were read: QUAL "." or a short integer, no Float-typed INFO /
-// FORMAT value to re-serialise, no empty INFO field to drop, every sample with as many values as FORMAT has keys (put_tail)
-bool tail_is_plain(const char* p, size_t n, bool float_info, bool float_fmt)
-{
-    size_t i = 0;
-    while (i < n && p[i] != '\t') ++i;
-    if (!(i == 1 && p[0] == '.'))
-    {
-        if (i == 0 || i > 6 || (i > 1 && p[0] == '0')) return false;
-        for (size_t k = 0; k < i; ++k)
-            if (p[k] < '0' || p[k] > '9') return false;
-    }
-    if (i >= n) return false;
-    ++i;
-    while (i < n && p[i] != '\t') ++i; // FILTER
-    if (i >= n) return false;
-    const size_t i0 = ++i;
-    while (i < n && p[i] != '\t')
-    {
-        if (p[i] == ';' && (i == i0 || i + 1 == n || p[i + 1] == ';' || p[i + 1] == '\t')) return false;
-        ++i;
-    }
-    if (i == i0) return false;
-    if (!(i - i0 == 1 && p[i0] == '.') && float_info) return false;
-    if (i >= n) return true; // sites only
-    if (float_fmt) return false;
-    size_t keys = 1;
-    ++i;
-    while (i < n && p[i] != '\t') keys += p[i++] == ':';
-    while (i < n)
-    {
-        size_t vals = 1;
-        ++i;
-        while (i < n && p[i] != '\t') vals += p[i++] == ':';
-        if (vals != keys) return false;
-    }
-    return true;
-}
-
 // BCFOrderedWriter (bcf_ordered_writer.cpp:141-300) over record VIEWS: a record is (contig id of the output header, POS, pointer, length
 // with its '\n'); the order comes from the device (vtn_writer_order) once per block, the bytes are gathered by all host threads into one
 // buffer and written with one call.  Records still inside the reference writer's buffer after a block are copied and replayed in
@@ -2179,7 +2292,7 @@ int cmd_normalize(int argc, char** argv)
                 const bool changed = (st & VTN_ST_CHANGED) && k < n_changed && chg_rec[k] == r;
                 o_rid[r] = wid[r];
                 o_pos[r] = pos1[r];
-                if (!changed && !(st & VTN_ST_ENTERED) && tail_is_plain(L + tail_off[r], ll - 1 - tail_off[r], float_info, float_fmt))
+                if (!changed && !(st & VTN_ST_ENTERED) && tail_is_plain(h, float_info, float_fmt, L + tail_off[r], ll - 1 - tail_off[r]))
                 {
                     o_ptr[r] = L;
                     o_len[r] = (uint32_t)ll;
@@ -2394,8 +2507,11 @@ int cmd_decompose(int argc, char** argv)
         print_intervals("         [i] intervals             ", a.intervals);
         fputc('\n', stderr);
     }
+    PhaseTimer pt;
+    pt.start();
     vtn_ctx* ctx = nullptr;
     if (vtn_ctx_create(&ctx, a.device)) die(nullptr, "vtn_ctx_create");
+    pt.stop("context");
     Reader rd;
     if (!rd.open(a.in, a.intervals))
     {
@@ -2419,35 +2535,37 @@ int cmd_decompose(int argc, char** argv)
     vtn_decomp_counters tot;
     memset(&tot, 0, sizeof tot);
     bool more = !line.empty();
-    std::string o;
+    const unsigned nthr = host_threads();
+    std::vector<std::string> obuf(nthr);
     LineParser lp;
     Filter flt;
     if (flt.set(a.fexp, h.meta)) lp.filter = &flt;
     while (more)
     {
+        pt.start();
         lp.read_batch(rd, line, more, BATCH, bb, ctx, false, rid_cache);
+        pt.stop("read + tokenize");
         vtn_batch in = bb.view();
         const uint64_t bound = vtn_decompose_out_bound(&in);
         src_rec.resize(bound + 1), alt_idx.resize(bound + 1);
         uint64_t n_out = 0;
         vtn_decomp_counters c;
         if (vtn_decompose(ctx, &in, src_rec.data(), alt_idx.data(), &n_out, &c)) die(ctx, "vtn_decompose");
+        pt.stop("decompose plan");
         tot.no_variants += c.no_variants, tot.no_biallelic += c.no_biallelic, tot.no_multiallelic += c.no_multiallelic;
         tot.no_additional_biallelic += c.no_additional_biallelic;
-        for (uint64_t q = 0; q < n_out; ++q)
-        {
+        // output q of the plan appended to o as one line; outputs are independent, so ranges of them are formatted by all host threads
+        auto format_output = [&](uint64_t q, std::string& o) {
             const uint32_t r = src_rec[q], i = alt_idx[q];
             const std::string& ln = bb.lines[r];
             std::vector<Tok> col = split(ln.data(), ln.size(), '\t');
             const uint32_t n_allele = in.allele_beg[r + 1] - in.allele_beg[r];
-            o.clear();
             if (n_allele <= 2)
             { // passes through (decompose.cpp:946-951); still re-serialised by the writer
                 o.append(col[0].first, col[4].first + col[4].second - col[0].first);
                 put_tail(o, h, col, "");
-                fwrite(o.data(), 1, o.size(), out);
-                fputc('\n', out);
-                continue;
+                o.push_back('\n');
+                return;
             }
             std::vector<Tok> alts = split(col[4].first, col[4].second, ',');
             o.append(col[0].first, col[3].first + col[3].second - col[0].first);
@@ -2601,11 +2719,22 @@ int cmd_decompose(int argc, char** argv)
                     }
                 }
             }
-            fwrite(o.data(), 1, o.size(), out);
-            fputc('\n', out);
-        }
+            o.push_back('\n');
+        };
+        for (auto& b : obuf) b.clear();
+        parallel_ranges((size_t)n_out, nthr, [&](unsigned t, size_t lo, size_t hi) {
+            for (size_t q = lo; q < hi; ++q) format_output(q, obuf[t]);
+        });
+        for (const std::string& b : obuf) // ranges are in thread order = output order
+            if (!b.empty() && fwrite(b.data(), 1, b.size(), out) != b.size())
+            {
+                fprintf(stderr, "[vtn] write error\n");
+                exit(1);
+            }
     }
     if (out != stdout) fclose(out);
+    pt.stop("format + write");
+    pt.report();
     if (print)
     { // print_stats, decompose.cpp:977-993
         fprintf(stderr, "\nstats: no. variants                 : %u\n", tot.no_variants);
@@ -2679,7 +2808,9 @@ int cmd_uniq(int argc, char** argv)
     std::vector<uint32_t> order;
     std::vector<uint8_t> first;
     vtn_uniq_counters cnt = {0, 0};
-    std::string o;
+    const unsigned nthr = host_threads();
+    std::vector<std::string> obuf(nthr);
+    std::vector<uint32_t> gstart;
     while (more)
     {
     lp.read_batch(rd, line, more, BATCH, bb, ctx, false, rid_cache);
@@ -2699,15 +2830,19 @@ int cmd_uniq(int argc, char** argv)
     const uint32_t ctx_recs = (uint32_t)(lp.n_lead + lp.n_peek);
     cnt.no_total_variants += c1.no_total_variants - ctx_recs, cnt.no_unique_variants += c1.no_unique_variants - ctx_recs;
     lp.lead_line = bb.lines[n - 1 - lp.n_peek];
+    // the groups of this batch (the context records' groups left out), formatted by all host threads, written in order
+    gstart.clear();
     for (size_t k = 0; k < n;)
     {
         size_t e = k + 1;
         while (e < n && !first[e]) ++e;
-        if ((lp.n_lead && order[k] == 0) || (lp.n_peek && order[k] == n - 1))
-        {
-            k = e;
-            continue;
-        }
+        if (!((lp.n_lead && order[k] == 0) || (lp.n_peek && order[k] == n - 1))) gstart.push_back((uint32_t)k);
+        k = e;
+    }
+    auto format_group = [&](size_t k, std::string& out_buf) {
+        size_t e = k + 1;
+        while (e < n && !first[e]) ++e;
+        std::string o;
         const std::string& ln = bb.lines[order[k]];
         std::vector<Tok> col = split(ln.data(), ln.size(), '\t');
         std::string merged;
@@ -2754,10 +2889,19 @@ int cmd_uniq(int argc, char** argv)
             c2[7] = Tok(info.data(), info.size());
             put_tail(o, h, c2, "");
         }
-        fwrite(o.data(), 1, o.size(), out);
-        fputc('\n', out);
-        k = e;
-    }
+        out_buf += o;
+        out_buf.push_back('\n');
+    };
+    for (auto& b : obuf) b.clear();
+    parallel_ranges(gstart.size(), nthr, [&](unsigned t, size_t lo, size_t hi) {
+        for (size_t g = lo; g < hi; ++g) format_group(gstart[g], obuf[t]);
+    });
+    for (const std::string& b : obuf)
+        if (!b.empty() && fwrite(b.data(), 1, b.size(), out) != b.size())
+        {
+            fprintf(stderr, "[vtn] write error\n");
+            exit(1);
+        }
     }
     if (out != stdout) fclose(out);
     fprintf(stderr, "\nstats: Total number of observed variants   %u\n", cnt.no_total_variants); // print_stats, uniq.cpp:167-171
@@ -3291,6 +3435,19 @@ int vtn_tool_main(int argc, char** argv)
     {
         vtn_tool_annotate_indels(argc - 1, argv + 1);
         print = true;
+    }
+    else if (cmd == "_floats")
+    { // self-test hook (no GPU needed): every stdin line -> "<1 if canon_float says htslib prints it as written>\t<put_float's text>"
+        char buf[4096];
+        while (fgets(buf, sizeof buf, stdin))
+        {
+            size_t n = strlen(buf);
+            while (n && (buf[n - 1] == '\n' || buf[n - 1] == '\r')) --n;
+            std::string o;
+            put_float(o, buf, n);
+            printf("%d\t%s\n", canon_float(buf, n) ? 1 : 0, o.c_str());
+        }
+        return 0;
     }
     else
     {
