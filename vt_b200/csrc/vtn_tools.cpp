@@ -1449,9 +1449,40 @@ struct Filter
 };
 
 // SoA batch under construction (vtn_batch)
+// the record lines of a batch in one buffer, each followed by '\n' (exactly the text the device tokenizer takes); a line is a view
+struct LineRef
+{
+    const char* p;
+    size_t n;
+    const char* data() const { return p; }
+    size_t size() const { return n; }
+    std::string str() const { return std::string(p, n); }
+};
+struct Lines
+{
+    std::string text;
+    std::vector<size_t> off{0};
+    size_t size() const { return off.size() - 1; }
+    bool empty() const { return off.size() == 1; }
+    void clear()
+    {
+        text.clear();
+        off.assign(1, 0);
+    }
+    void push_back(const char* p, size_t n)
+    {
+        text.append(p, n);
+        text.push_back('\n');
+        off.push_back(text.size());
+    }
+    void push_back(const std::string& l) { push_back(l.data(), l.size()); }
+    LineRef operator[](size_t r) const { return LineRef{text.data() + off[r], off[r + 1] - off[r] - 1}; }
+    LineRef back() const { return (*this)[size() - 1]; }
+};
+
 struct BatchBuf
 {
-    std::vector<std::string> lines;
+    Lines lines;
     std::vector<int32_t> pos1, rid;
     std::vector<uint32_t> allele_beg{0}, allele_off{0};
     std::vector<uint8_t> bytes;
@@ -1514,7 +1545,6 @@ bool filter_records(Filter& flt, vtn_ctx* ctx, vtn_batch b, const char* text, co
 // (ref_ids) or from the order of appearance / the header dictionary in rid_cache, looked up once per run of equal CHROM.
 struct LineParser
 {
-    std::string text;
     std::vector<uint64_t> line_off;
     std::vector<uint32_t> chrom_len, tail_off;
     std::vector<uint8_t> status;
@@ -1528,14 +1558,8 @@ struct LineParser
     size_t n_lead = 0, n_peek = 0;
     void tokenize(BatchBuf& bb, vtn_ctx* ctx)
     {
-        text.clear();
-        size_t commas = 0;
-        for (const std::string& l : bb.lines)
-        {
-            text += l;
-            text.push_back('\n');
-            commas += (size_t)std::count(l.begin(), l.end(), ',');
-        }
+        const std::string& text = bb.lines.text; // already the tokenizer's input: no second copy
+        const size_t commas = (size_t)std::count(text.begin(), text.end(), ',');
         const size_t n = bb.lines.size();
         line_off.resize(n + 1), chrom_len.resize(n), tail_off.resize(n), status.resize(n);
         bb.pos1.resize(n), bb.allele_beg.resize(n + 1), bb.allele_off.resize(commas + 2 * n + 1), bb.bytes.resize(text.size() + 1);
@@ -1550,7 +1574,7 @@ struct LineParser
         for (size_t r = 0; r < n; ++r)
             if (status[r])
             {
-                fprintf(stderr, "[vtn] malformed VCF record (fewer than 8 columns): %s\n", bb.lines[r].c_str());
+                fprintf(stderr, "[vtn] malformed VCF record (fewer than 8 columns): %.*s\n", (int)bb.lines[r].size(), bb.lines[r].data());
                 exit(1);
             }
     }
@@ -1566,22 +1590,22 @@ struct LineParser
         }
         size_t bytes = 0;
         const size_t max_bytes = (size_t)1 << 30; // a batch is also cut by bytes (the tokenizer takes less than 4 GiB per call)
-        auto site_len = [](const std::string& l) { // length of "CHROM\tPOS"
-            const size_t t1 = l.find('\t');
-            const size_t t2 = t1 == std::string::npos ? t1 : l.find('\t', t1 + 1);
-            return t2 == std::string::npos ? l.size() : t2;
+        auto site_len = [](const char* p, size_t n) { // length of "CHROM\tPOS"
+            const char* t1 = (const char*)memchr(p, '\t', n);
+            const char* t2 = t1 ? (const char*)memchr(t1 + 1, '\t', n - (size_t)(t1 + 1 - p)) : nullptr;
+            return t2 ? (size_t)(t2 - p) : n;
         };
         while (more)
         {
             if (bb.lines.size() >= max_lines + n_lead || bytes >= max_bytes)
             { // full; with keep_groups the records at the last position stay together
                 if (!keep_groups) break;
-                const std::string& last = bb.lines.back();
-                const size_t a = site_len(last), b = site_len(line);
-                if (a != b || last.compare(0, a, line, 0, b)) break;
+                const LineRef last = bb.lines.back();
+                const size_t a = site_len(last.data(), last.size()), b = site_len(line.data(), line.size());
+                if (a != b || memcmp(last.data(), line.data(), a)) break;
             }
             bytes += line.size() + 1;
-            bb.lines.push_back(std::move(line));
+            bb.lines.push_back(line);
             more = rd.getline(line);
         }
         if (bb.lines.size() == n_lead) return false;
@@ -1594,12 +1618,13 @@ struct LineParser
         if (filter)
         {
             std::vector<uint8_t> keep;
-            if (filter_records(*filter, ctx, bb.view(), text.data(), line_off.data(), tail_off.data(), keep))
+            if (filter_records(*filter, ctx, bb.view(), bb.lines.text.data(), line_off.data(), tail_off.data(), keep))
             {
-                std::vector<std::string> kept;
+                Lines kept;
                 for (size_t r = 0; r < bb.lines.size(); ++r)
-                    if (keep[r]) kept.push_back(std::move(bb.lines[r]));
-                bb.lines.swap(kept);
+                    if (keep[r]) kept.push_back(bb.lines[r].data(), bb.lines[r].size());
+                bb.lines.text.swap(kept.text);
+                bb.lines.off.swap(kept.off);
                 if (!bb.lines.empty()) tokenize(bb, ctx);
             }
         }
@@ -1616,7 +1641,7 @@ struct LineParser
         int prev_rid = -1;
         for (size_t r = 0; r < n; ++r)
         {
-            const char* c = text.data() + line_off[r];
+            const char* c = bb.lines.text.data() + line_off[r];
             if (!(prev && prev_len == chrom_len[r] && !memcmp(prev, c, prev_len)))
             {
                 std::string chrom(c, chrom_len[r]);
@@ -2557,7 +2582,7 @@ int cmd_decompose(int argc, char** argv)
         // output q of the plan appended to o as one line; outputs are independent, so ranges of them are formatted by all host threads
         auto format_output = [&](uint64_t q, std::string& o) {
             const uint32_t r = src_rec[q], i = alt_idx[q];
-            const std::string& ln = bb.lines[r];
+            const LineRef ln = bb.lines[r];
             std::vector<Tok> col = split(ln.data(), ln.size(), '\t');
             const uint32_t n_allele = in.allele_beg[r + 1] - in.allele_beg[r];
             if (n_allele <= 2)
@@ -2829,7 +2854,7 @@ int cmd_uniq(int argc, char** argv)
     // the context records are position groups of their own: the first and the last one to come out; they are neither written nor counted
     const uint32_t ctx_recs = (uint32_t)(lp.n_lead + lp.n_peek);
     cnt.no_total_variants += c1.no_total_variants - ctx_recs, cnt.no_unique_variants += c1.no_unique_variants - ctx_recs;
-    lp.lead_line = bb.lines[n - 1 - lp.n_peek];
+    lp.lead_line = bb.lines[n - 1 - lp.n_peek].str();
     // the groups of this batch (the context records' groups left out), formatted by all host threads, written in order
     gstart.clear();
     for (size_t k = 0; k < n;)
@@ -2843,7 +2868,7 @@ int cmd_uniq(int argc, char** argv)
         size_t e = k + 1;
         while (e < n && !first[e]) ++e;
         std::string o;
-        const std::string& ln = bb.lines[order[k]];
+        const LineRef ln = bb.lines[order[k]];
         std::vector<Tok> col = split(ln.data(), ln.size(), '\t');
         std::string merged;
         if (e - k > 1)
@@ -2851,7 +2876,7 @@ int cmd_uniq(int argc, char** argv)
             std::vector<std::string> seen;
             for (size_t j = k; j < e; ++j)
             {
-                const std::string& lj = bb.lines[order[j]];
+                const LineRef lj = bb.lines[order[j]];
                 std::vector<Tok> cj = split(lj.data(), lj.size(), '\t');
                 std::string v = info_value(cj[7], "OLD_VARIANT");
                 if (v.empty() || std::find(seen.begin(), seen.end(), v) != seen.end()) continue;
@@ -3004,7 +3029,7 @@ int cmd_blocksub(int argc, char** argv)
         while (k < n_out)
         {
             const uint32_t r = src[k];
-            const std::string& ln = bb.lines[r];
+            const LineRef ln = bb.lines[r];
             const bool aligned = aggressive && a_cnt[r] > 0;
             uint32_t p_ref = off[k], p_alt = off[k], l_ref = len[k], l_alt = len[k];
             if (aligned)
@@ -3279,7 +3304,7 @@ int cmd_annotate_indels(int argc, char** argv)
             {
                 if (in.rid[r] < 0)
                 {
-                    fprintf(stderr, "[vtn] contig of record %s:%d is not in the reference\n", std::string(bb.lines[r], 0, bb.lines[r].find('\t')).c_str(), in.pos1[r]);
+                    fprintf(stderr, "[vtn] contig of record %s:%d is not in the reference\n", std::string(bb.lines[r].data(), (size_t)((const char*)memchr(bb.lines[r].data(), '\t', bb.lines[r].size()) - bb.lines[r].data())).c_str(), in.pos1[r]);
                     exit(1);
                 }
                 flank_at[r] = w_rid.size();
@@ -3308,7 +3333,7 @@ int cmd_annotate_indels(int argc, char** argv)
         for (size_t r = 0; r < n; ++r)
         {
             if (!(flags[r] & VTN_ANNOT_KEEP)) continue; // annotate_indels.cpp:306-323: dropped, not passed through
-            const std::string& ln = bb.lines[r];
+            const LineRef ln = bb.lines[r];
             std::vector<Tok> col = split(ln.data(), ln.size(), '\t');
             const uint32_t a0 = in.allele_beg[r];
             DeviceWriter::Rec rec;
