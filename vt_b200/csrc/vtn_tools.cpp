@@ -3021,15 +3021,21 @@ int cmd_blocksub(int argc, char** argv)
             if (vtn_blocksub_align(ctx, &b, &ap)) die(ctx, "vtn_blocksub_align");
         }
         uint32_t cur = 0xffffffffu;
-        std::vector<Tok> col;
         int32_t ps = 0;
+        struct OutDesc
+        {
+            uint32_t r, p_ref, p_alt, l_ref, l_alt;
+            int32_t ps;
+            bool aligned;
+        };
+        std::vector<OutDesc> descs;
+        descs.reserve((size_t)n_out);
         // one output of the plan; a record in alignment mode turns its single pass-through entry into its chunks
         uint64_t k = 0;
         uint32_t chunk = 0;
         while (k < n_out)
         {
             const uint32_t r = src[k];
-            const LineRef ln = bb.lines[r];
             const bool aligned = aggressive && a_cnt[r] > 0;
             uint32_t p_ref = off[k], p_alt = off[k], l_ref = len[k], l_alt = len[k];
             if (aligned)
@@ -3039,7 +3045,6 @@ int cmd_blocksub(int argc, char** argv)
             }
             if (r != cur)
             {
-                col = split(ln.data(), ln.size(), '\t');
                 cur = r;
                 ps = b.pos1[r] + (int32_t)p_ref; // the PS vector is sized at the record's first SNP and keeps that value (:343, resize; :263)
                 if (aligned)
@@ -3059,7 +3064,26 @@ int cmd_blocksub(int argc, char** argv)
             }
             else
                 ++k;
-            DeviceWriter::Rec rec;
+            descs.push_back(OutDesc{r, p_ref, p_alt, l_ref, l_alt, ps, aligned});
+        }
+        // the outputs are independent: formatted by all host threads, handed to the ordered writer in plan order
+        std::vector<DeviceWriter::Rec> recs(descs.size());
+        parallel_ranges(descs.size(), host_threads(), [&](unsigned, size_t lo, size_t hi) {
+          uint32_t last_r = 0xffffffffu;
+          std::vector<Tok> col;
+          for (size_t d = lo; d < hi; ++d)
+          {
+            const OutDesc& D = descs[d];
+            const uint32_t r = D.r, p_ref = D.p_ref, p_alt = D.p_alt, l_ref = D.l_ref, l_alt = D.l_alt;
+            const int32_t ps = D.ps;
+            const bool aligned = D.aligned;
+            if (r != last_r)
+            {
+                const LineRef ln = bb.lines[r];
+                col = split(ln.data(), ln.size(), '\t');
+                last_r = r;
+            }
+            DeviceWriter::Rec& rec = recs[d];
             rec.rid = b.rid[r];
             rec.chrom.assign(col[0].first, col[0].second);
             std::string& o = rec.line;
@@ -3118,8 +3142,9 @@ int cmd_blocksub(int argc, char** argv)
                 else
                     put_tail(o, h, col, extra);
             }
-            ow.write(std::move(rec));
-        }
+          }
+        });
+        for (DeviceWriter::Rec& rec : recs) ow.write(std::move(rec));
         ow.drain(false);
         tot.no_variants += c.no_variants, tot.no_biallelic_blocksub += c.no_biallelic_blocksub;
         tot.no_additional_snps += c.no_additional_snps, tot.new_no_variants += c.new_no_variants;
