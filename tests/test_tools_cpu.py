@@ -47,3 +47,55 @@ def test_canonical_floats_are_fixed_points_of_put_float():
     p = subprocess.run([VTN, "_floats"], input="\n".join(exp) + "\n", capture_output=True, text=True)
     got = {k: int(l.split("\t")[0]) for k, l in zip(exp, p.stdout.splitlines())}
     assert got == exp
+
+
+def _filter_keep(exp, recs, meta):
+    p = subprocess.run([VTN, "_filter", exp] + meta, input="".join("%d\t%d\t%s\t%s\n" % r for r in recs), capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr
+    return [int(x) for x in p.stdout.split()]
+
+
+def test_filter_expression_goldens_on_the_cpu():
+    """the -f engine of the tools (vtn_tools.cpp: Filter, restating filter.cpp's parse and evaluate) without a GPU: the variant types come
+    from the CPU oracle instead of the device, and the records it keeps must be the ones the unmodified reference wrote for the same
+    expression (tests/golden/filter_*: `vt normalize -f`; the K INFO value identifies a record)"""
+    import re
+    vin = os.path.join(helpers.GOLDEN, "filter_in.vcf")
+    meta = [l.rstrip("\n") for l in open(vin) if l.startswith("##FILTER")]
+    fields = [l.rstrip("\n").split("\t") for l in open(vin) if not l.startswith("#")]
+    seq = "".join(l.strip() for l in open(os.path.join(helpers.GOLDEN, "advice_ref.fa")) if not l.startswith(">"))
+    recs = [(0, int(f[1]), [f[3].encode()] + ([] if f[4] == "." else [a.encode() for a in f[4].split(",")])) for f in fields]
+    b = helpers.Batch.from_records(recs)
+    vtype = helpers.Oracle().normalize([np.frombuffer(seq.encode(), np.uint8)], b).vtype
+    rows = [(int(vtype[r]), len(recs[r][2]), fields[r][5], fields[r][6]) for r in range(len(recs))]
+    cases = [l.rstrip("\n").split("\t") for l in open(os.path.join(helpers.GOLDEN, "filter_cases.tsv"))]
+    n = 0
+    for k, tool, exp in cases:
+        if tool != "normalize":
+            continue
+        kept = {int(re.search(r"K=(\d+)", l).group(1)) for l in open(os.path.join(helpers.GOLDEN, "filter_%s_out.vcf" % k)) if not l.startswith("#")}
+        got = _filter_keep(exp, rows, meta)
+        assert {r for r in range(len(rows)) if got[r]} == kept, (k, exp)
+        n += 1
+    assert n >= 25
+
+
+def test_filter_parse_rules():
+    rows = [(1, 2, "50", "PASS"), (4, 3, ".", "q10"), (5, 2, "5", "."), (2, 2, "10.5", "q10;s50")]
+    meta = ["##FILTER=<ID=q10,Description=\"q\">", "##FILTER=<ID=s50,Description=\"s\">"]
+    # && is the root before || (filter.cpp:1563-1650: the operator with the lowest code splits first)
+    assert _filter_keep("VTYPE==SNP||N_ALLELE>2&&QUAL>5", rows, meta) == [1, 0, 0, 0]
+    assert _filter_keep("(VTYPE==SNP)||(N_ALLELE>2&&QUAL>5)", rows, meta) == [1, 0, 0, 0]
+    # a missing QUAL: comparisons are false, ~ of them is true
+    assert _filter_keep("QUAL<100", rows, meta) == [1, 0, 1, 1]
+    assert _filter_keep("~(QUAL<100)", rows, meta) == [0, 1, 0, 0]
+    # <= between QUAL and an integer keeps the answer of its first evaluation with a QUAL present (filter.cpp:307)
+    assert _filter_keep("QUAL<=20", rows, meta) == [0, 0, 0, 0]
+    assert _filter_keep("QUAL<=20.0", rows, meta) == [0, 0, 1, 1]
+    # an undeclared FILTER id is true wherever a filter is set
+    assert _filter_keep("FILTER.nope", rows, meta) == [1, 1, 0, 1]
+    assert _filter_keep("FILTER.s50", rows, meta) == [0, 0, 0, 1]
+    assert _filter_keep("VTYPE&INDEL", rows, meta) == [0, 1, 1, 0]
+    for bad in ("INFO.AC>1", "QUAL+1>2", "VTYPE==REF"):
+        p = subprocess.run([VTN, "_filter", bad], input="1\t2\t.\t.\n", capture_output=True, text=True)
+        assert p.returncode != 0 and "not handled" in p.stderr

@@ -3486,6 +3486,28 @@ int vtn_tool_main(int argc, char** argv)
         vtn_tool_annotate_indels(argc - 1, argv + 1);
         print = true;
     }
+    else if (cmd == "_filter" && argc >= 3)
+    { // self-test hook (no GPU needed): vtn _filter <expression> [header line ...] ; stdin lines "vtype<TAB>n_allele<TAB>QUAL<TAB>FILTER" -> 1 / 0
+        Filter flt;
+        std::vector<std::string> meta;
+        for (int k = 3; k < argc; ++k) meta.push_back(argv[k]);
+        flt.set(argv[2], meta);
+        char buf[4096];
+        while (fgets(buf, sizeof buf, stdin))
+        {
+            size_t n = strlen(buf);
+            while (n && (buf[n - 1] == '\n' || buf[n - 1] == '\r')) --n;
+            std::vector<Tok> c = split(buf, n, '\t');
+            if (c.size() < 4) continue;
+            Filter::Rec v;
+            v.vtype = atoi(std::string(c[0].first, c[0].second).c_str());
+            v.n_allele = atoi(std::string(c[1].first, c[1].second).c_str());
+            v.qual = c[2].first, v.qual_len = c[2].second;
+            v.filt = c[3].first, v.filt_len = c[3].second;
+            printf("%d\n", flt.pass(v) ? 1 : 0);
+        }
+        return 0;
+    }
     else if (cmd == "_floats")
     { // self-test hook (no GPU needed): every stdin line -> "<1 if canon_float says htslib prints it as written>\t<put_float's text>"
         char buf[4096];
