@@ -305,8 +305,11 @@ def test_normalize_advice_goldens(tmp_path, stem):
 
 # ---- -f: the filter expression in front of normalize / decompose (filter.cpp; goldens by tests/golden/make_filter_golden.py) ----
 def _filter_cases():
+    """every third `normalize` expression and all the `decompose` ones: tests/test_tools_cpu.py pins the engine itself on all of them
+    (without a GPU); here the point is the plumbing -- VTYPE from the device, records leaving the block, counters, option lines"""
     p = os.path.join(helpers.GOLDEN, "filter_cases.tsv")
-    return [tuple(l.rstrip("\n").split("\t")) for l in open(p)] if os.path.exists(p) else []
+    rows = [tuple(l.rstrip("\n").split("\t")) for l in open(p)] if os.path.exists(p) else []
+    return [r for r in rows if r[1] != "normalize" or int(r[0]) % 3 == 0 or r[2] in ("QUAL<=30", "FILTER.nope")]
 
 
 @pytest.mark.parametrize("k,tool,exp", _filter_cases())
