@@ -136,6 +136,20 @@ int vtn_ref_load_fasta(vtn_ctx* ctx, const char* fasta_path);
 int vtn_ref_open_fasta(vtn_ctx* ctx, const char* fasta_path);
 int vtn_ref_require(vtn_ctx* ctx, int rid); /* no-op for a resident or unknown contig */
 int vtn_ref_require_all(vtn_ctx* ctx);
+/* The host half on its own.  Creating a CUDA context takes 0.25-2 s; a tool that starts it on another thread can meanwhile open the
+ * FASTA (vtn_fasta_open: mapping + index, no device), read the first records of its input and pack their contig on the host
+ * (vtn_fasta_prepack), then hand the handle to the context (vtn_ref_attach == what vtn_ref_open_fasta does after its own open; the
+ * context owns the handle from then on, also when the call fails).  vtn_ref_prefetch packs one more contig on a background thread:
+ * a sorted call set walks the contigs in order, so asking for contig c + 1 when c first appears leaves vtn_ref_require only the
+ * upload.  vtn_last_error(NULL) has the text of a failed vtn_fasta_open. */
+typedef struct vtn_fasta vtn_fasta;
+int vtn_fasta_open(const char* fasta_path, vtn_fasta** out);
+int vtn_fasta_n_contig(const vtn_fasta* f);
+int vtn_fasta_contig_id(const vtn_fasta* f, const char* name); /* -1 when unknown */
+int vtn_fasta_prepack(vtn_fasta* f, int rid);
+void vtn_fasta_close(vtn_fasta* f); /* only for a handle that was never attached */
+int vtn_ref_attach(vtn_ctx* ctx, vtn_fasta* f);
+int vtn_ref_prefetch(vtn_ctx* ctx, int rid);
 /* Same from memory: contig c has raw FASTA bases seq[c][0..len[c]) (case preserved, any isgraph byte). */
 int vtn_ref_load_memory(vtn_ctx* ctx, int32_t n_contig, const char* const* names, const int64_t* len,
                         const uint8_t* const* seq);

@@ -106,3 +106,33 @@ def test_lazy_index_built_when_fai_is_absent_and_short_file(tmp_path):
             c.fetch(1, 0, 10)
     finally:
         c.close()
+
+
+def test_host_half_first_then_attach_and_prefetch(oracle, tmp_path):
+    """vtn_fasta_open / vtn_fasta_prepack without a context, vtn_ref_attach, vtn_ref_prefetch of later contigs (also of one that is never
+    used, of one that is already resident, and out of range): every result equals the oracle's"""
+    rng, names, seqs, p = _fasta(tmp_path, seed=6, n_contig=5, length=60000)
+    recs = [r for r in helpers.synth_records(rng, seqs, 30000) if r[0] >= 0]
+    c = Context(0)
+    try:
+        c.attach_fasta(p, prepack=[names[1], names[1], "nope"])
+        c.prefetch(2)
+        c.prefetch(2)
+        c.prefetch(4)   # never required: joined when the context is closed
+        c.prefetch(99)
+        for k in (1, 2, 3, 0):
+            part = [r for r in recs if r[0] == k]
+            b = Batch.from_records(part)
+            helpers.assert_norm_equal(c.normalize(b), oracle.normalize(seqs, b), b.n_rec)
+            c.prefetch(k)  # already resident: nothing to do
+        assert c.fetch(1, 0, len(seqs[1]) - 1) == bytes(seqs[1])
+        assert c.fetch(4, 10, 2000) == bytes(seqs[4][10:2001])
+    finally:
+        c.close()
+    from vt_b200.api import VtnError
+    c = Context(0)
+    try:
+        with pytest.raises(VtnError):
+            c.attach_fasta(str(tmp_path / "missing.fa"))
+    finally:
+        c.close()

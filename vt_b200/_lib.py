@@ -143,6 +143,13 @@ SIGNATURES = {
     "vtn_ref_open_fasta": (C.c_int, [C.c_void_p, C.c_char_p]),
     "vtn_ref_require": (C.c_int, [C.c_void_p, C.c_int]),
     "vtn_ref_require_all": (C.c_int, [C.c_void_p]),
+    "vtn_fasta_open": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
+    "vtn_fasta_n_contig": (C.c_int, [C.c_void_p]),
+    "vtn_fasta_contig_id": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "vtn_fasta_prepack": (C.c_int, [C.c_void_p, C.c_int]),
+    "vtn_fasta_close": (None, [C.c_void_p]),
+    "vtn_ref_attach": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "vtn_ref_prefetch": (C.c_int, [C.c_void_p, C.c_int]),
     "vtn_ref_load_memory": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), c_i64p, C.POINTER(C.c_void_p)]),
     "vtn_ref_n_contig": (C.c_int, [C.c_void_p]),
     "vtn_ref_contig_id": (C.c_int, [C.c_void_p, C.c_char_p]),

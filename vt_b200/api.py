@@ -233,6 +233,19 @@ class Context:
         """index only; a contig becomes resident the first time a batch names it (vtn_ref_open_fasta)"""
         self._chk(self.lib.vtn_ref_open_fasta(self.h, path.encode()), "vtn_ref_open_fasta")
 
+    def attach_fasta(self, path, prepack=()):
+        """vtn_fasta_open + vtn_fasta_prepack (host only) + vtn_ref_attach: what a tool does while its context is still being created"""
+        h = C.c_void_p()
+        rc = self.lib.vtn_fasta_open(path.encode(), C.byref(h))
+        if rc:
+            raise VtnError("vtn_fasta_open: %s" % self.lib.vtn_last_error(None).decode())
+        for name in prepack:
+            self.lib.vtn_fasta_prepack(h, self.lib.vtn_fasta_contig_id(h, name.encode()))
+        self._chk(self.lib.vtn_ref_attach(self.h, h), "vtn_ref_attach")
+
+    def prefetch(self, rid):
+        self._chk(self.lib.vtn_ref_prefetch(self.h, int(rid)), "vtn_ref_prefetch")
+
     def require(self, rid=None):
         if rid is None:
             self._chk(self.lib.vtn_ref_require_all(self.h), "vtn_ref_require_all")

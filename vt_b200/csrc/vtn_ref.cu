@@ -7,6 +7,7 @@
 #include <string.h>
 #include <zlib.h>
 #include <algorithm>
+#include <map>
 #include <thread>
 #include "vtn_fasta_pack.h"
 #include "vtn_internal.h"
@@ -14,13 +15,28 @@
 
 using vtf::ExcRun;
 
-// what a lazily opened FASTA keeps on the host: the mapped text, its index, which contigs are resident, their exception runs
+// what a lazily opened FASTA keeps on the host: the mapped text, its index, which contigs are resident, their exception runs, and
+// contigs that were packed on the host ahead of their upload (before a context existed, or by a background prefetch)
 struct VtnRefSource
 {
     vtf::FastaText text;
     std::vector<vtf::FaiEntry> fai;
+    std::vector<uint64_t> goff; // group offset of every contig: the same layout ref_alloc_tables gives the device array
     std::vector<char> loaded;
     std::vector<std::vector<ExcRun>> exc;
+    std::vector<std::vector<vtf::Group>> packed; // host-packed, not uploaded yet
+    std::vector<char> packed_ok;                 // 1 packed, -1 the text was shorter than the index says
+    std::vector<char> uploaded;                  // 1 a background task has copied the packed groups to the device (not yet accounted)
+    std::vector<std::string> bg_err;             // what went wrong in a background task
+    std::map<int, std::thread> inflight;         // background tasks: pack (unless packed already) and, once attached, upload
+    ~VtnRefSource()
+    {
+        for (auto& kv : inflight)
+            if (kv.second.joinable()) kv.second.join();
+    }
+};
+struct vtn_fasta : VtnRefSource
+{
 };
 
 namespace
@@ -37,6 +53,8 @@ __global__ void vtn_ref_fetch_kernel(VtnDevRef R, int rid, int64_t beg, int64_t 
 
 void free_ref(vtn_ctx* ctx)
 {
+    delete ctx->ref_src; // joins the background tasks first: they copy into d_groups
+    ctx->ref_src = nullptr;
     cudaFree(ctx->d_groups);
     cudaFree(ctx->d_contig_goff);
     cudaFree(ctx->d_contig_len);
@@ -48,8 +66,6 @@ void free_ref(vtn_ctx* ctx)
     ctx->ref_loaded = false;
     ctx->ref_bytes = 0;
     ctx->ref_missing = 0;
-    delete ctx->ref_src;
-    ctx->ref_src = nullptr;
 }
 
 
@@ -123,35 +139,136 @@ int ref_upload_exc(vtn_ctx* ctx, const std::vector<ExcRun>& exc)
     return VTN_OK;
 }
 
-// pack the listed contigs of an opened FASTA (all worker threads on one contig after the other) and upload each one as soon as
-// it is complete, while the workers pack the next
-int ref_load_contigs(vtn_ctx* ctx, const std::vector<int>& which)
+// host only: pack contig c of an opened FASTA into S->packed[c] (all host threads); the upload happens later
+void src_pack(VtnRefSource* S, int c, unsigned nthr)
+{
+    const size_t nc = S->fai.size();
+    std::vector<uint64_t> hoff(nc, 0);
+    S->packed[c].assign((size_t)((std::max<int64_t>(S->fai[c].len, 0) + 31) / 32) + 1, vtf::Group{0, 0, 0, 0});
+    const int bad = vtf::pack_contigs_ol(S->text.data, S->text.size, S->fai, std::vector<int>(1, c), S->goff, hoff, S->packed[c].data(), S->exc, nthr, [](int) {});
+    S->packed_ok[c] = bad >= 0 ? -1 : 1;
+}
+
+// background task for contig c: pack it unless that was done ahead, then copy it to the device on a stream of its own (the copy
+// comes from pageable memory: it keeps THIS thread busy, not the tool's).  d_groups = the context's group array.
+void bg_pack_upload(VtnRefSource* S, int c, unsigned nthr, int device, void* d_groups)
+{
+    if (!S->packed_ok[c]) src_pack(S, c, nthr);
+    if (S->packed_ok[c] <= 0 || !d_groups) return;
+    const uint64_t ng = (uint64_t)((std::max<int64_t>(S->fai[c].len, 0) + 31) / 32);
+    cudaError_t e = cudaSetDevice(device);
+    cudaStream_t st = nullptr;
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
+    if (e == cudaSuccess && ng) e = cudaMemcpyAsync((uint4*)d_groups + S->goff[c], S->packed[c].data(), ng * sizeof(uint4), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (st) cudaStreamDestroy(st);
+    if (e != cudaSuccess)
+    {
+        S->bg_err[c] = cudaGetErrorString(e);
+        return;
+    }
+    std::vector<vtf::Group>().swap(S->packed[c]);
+    S->packed_ok[c] = 0;
+    S->uploaded[c] = 1;
+}
+
+VtnRefSource* src_open(const char* fasta_path, std::string& err)
+{
+    VtnRefSource* S = new vtn_fasta();
+    if (!S->text.open(fasta_path))
+    {
+        delete S;
+        err = std::string("Cannot load genome index: ") + fasta_path;
+        return nullptr;
+    }
+    if (!vtf::read_fai(std::string(fasta_path) + ".fai", S->fai)) vtf::build_fai(S->text.data, S->text.size, S->fai);
+    if (S->fai.empty())
+    {
+        delete S;
+        err = std::string("Cannot load genome index: ") + fasta_path;
+        return nullptr;
+    }
+    const size_t nc = S->fai.size();
+    uint64_t g = 0;
+    S->goff.resize(nc);
+    for (size_t c = 0; c < nc; ++c)
+    { // ref_alloc_tables' layout
+        S->goff[c] = g;
+        g += (uint64_t)((std::max<int64_t>(S->fai[c].len, 0) + 31) / 32) + 2;
+    }
+    S->loaded.assign(nc, 0);
+    S->packed_ok.assign(nc, 0);
+    S->uploaded.assign(nc, 0);
+    S->bg_err.resize(nc);
+    S->exc.resize(nc);
+    S->packed.resize(nc);
+    return S;
+}
+
+// Make the listed contigs resident.  A contig that was packed ahead (vtn_fasta_prepack, vtn_ref_prefetch) is only uploaded; the others
+// are packed now (all worker threads on one contig after the other), each uploaded as soon as it is complete while the workers pack
+// the next.
+int ref_load_contigs(vtn_ctx* ctx, const std::vector<int>& which_all)
 {
     VtnRefSource* S = ctx->ref_src;
-    if (which.empty()) return VTN_OK;
+    if (which_all.empty()) return VTN_OK;
     VTN_CUDA(ctx, cudaSetDevice(ctx->device));
     const size_t nc = ctx->contigs.size();
-    std::vector<uint64_t> goff(nc), hoff(nc, 0);
-    for (size_t c = 0; c < nc; ++c) goff[c] = ctx->contigs[c].goff;
-    uint64_t n_host = 0;
-    for (int c : which)
+    std::vector<int> which, ahead;
+    for (int c : which_all)
     {
-        hoff[c] = n_host;
-        n_host += (uint64_t)((ctx->contigs[c].len + 31) / 32);
+        auto it = S->inflight.find(c);
+        if (it != S->inflight.end())
+        {
+            if (it->second.joinable()) it->second.join();
+            S->inflight.erase(it);
+        }
+        if (S->loaded[c]) continue;
+        if (!S->bg_err[c].empty()) return vtn_set_err(ctx, VTN_E_CUDA, "reference upload (background): " + S->bg_err[c]);
+        if (S->packed_ok[c] < 0) return vtn_set_err(ctx, VTN_E_IO, std::string("FASTA shorter than its index: ") + S->fai[c].name);
+        if (S->uploaded[c])
+        { // a background task brought it over: only the bookkeeping below is left
+            S->uploaded[c] = 0;
+            continue;
+        }
+        (S->packed_ok[c] > 0 ? ahead : which).push_back(c);
     }
-    vtf::Group* h = (vtf::Group*)malloc(std::max<uint64_t>(n_host, 1) * sizeof(vtf::Group));
-    if (!h) return vtn_set_err(ctx, VTN_E_NOMEM, "reference packing: out of host memory");
     cudaError_t ce = cudaSuccess;
-    const int bad = vtf::pack_contigs_ol(S->text.data, S->text.size, S->fai, which, goff, hoff, h, S->exc, host_threads(), [&](int c) {
+    for (int c : ahead)
+    {
         const uint64_t ng = (uint64_t)((ctx->contigs[c].len + 31) / 32);
         if (ng && ce == cudaSuccess)
-            ce = cudaMemcpyAsync((uint4*)ctx->d_groups + goff[c], h + hoff[c], ng * sizeof(uint4), cudaMemcpyHostToDevice, ctx->stream);
-    });
+            ce = cudaMemcpyAsync((uint4*)ctx->d_groups + S->goff[c], S->packed[c].data(), ng * sizeof(uint4), cudaMemcpyHostToDevice, ctx->stream);
+    }
+    vtf::Group* h = nullptr;
+    int bad = -1;
+    if (!which.empty())
+    {
+        std::vector<uint64_t> hoff(nc, 0);
+        uint64_t n_host = 0;
+        for (int c : which)
+        {
+            hoff[c] = n_host;
+            n_host += (uint64_t)((ctx->contigs[c].len + 31) / 32);
+        }
+        h = (vtf::Group*)malloc(std::max<uint64_t>(n_host, 1) * sizeof(vtf::Group));
+        if (!h) return vtn_set_err(ctx, VTN_E_NOMEM, "reference packing: out of host memory");
+        bad = vtf::pack_contigs_ol(S->text.data, S->text.size, S->fai, which, S->goff, hoff, h, S->exc, host_threads(), [&](int c) {
+            const uint64_t ng = (uint64_t)((ctx->contigs[c].len + 31) / 32);
+            if (ng && ce == cudaSuccess)
+                ce = cudaMemcpyAsync((uint4*)ctx->d_groups + S->goff[c], h + hoff[c], ng * sizeof(uint4), cudaMemcpyHostToDevice, ctx->stream);
+        });
+    }
     if (ce == cudaSuccess) ce = cudaStreamSynchronize(ctx->stream);
     free(h);
+    for (int c : ahead)
+    {
+        std::vector<vtf::Group>().swap(S->packed[c]);
+        S->packed_ok[c] = 0;
+    }
     if (bad >= 0) return vtn_set_err(ctx, VTN_E_IO, std::string("FASTA shorter than its index: ") + S->fai[bad].name);
     if (ce != cudaSuccess) return vtn_set_err(ctx, VTN_E_CUDA, std::string("reference upload: ") + cudaGetErrorString(ce));
-    for (int c : which)
+    for (int c : which_all)
         if (!S->loaded[c])
         {
             S->loaded[c] = 1;
@@ -163,20 +280,9 @@ int ref_load_contigs(vtn_ctx* ctx, const std::vector<int>& which)
     return ref_upload_exc(ctx, all);
 }
 
-int ref_open(vtn_ctx* ctx, const char* fasta_path)
+// device side of opening: contig table + group array for the whole genome; contigs packed ahead are uploaded at once
+int ref_attach(vtn_ctx* ctx, VtnRefSource* S)
 {
-    VtnRefSource* S = new VtnRefSource();
-    if (!S->text.open(fasta_path))
-    {
-        delete S;
-        return vtn_set_err(ctx, VTN_E_IO, std::string("Cannot load genome index: ") + fasta_path);
-    }
-    if (!vtf::read_fai(std::string(fasta_path) + ".fai", S->fai)) vtf::build_fai(S->text.data, S->text.size, S->fai);
-    if (S->fai.empty())
-    {
-        delete S;
-        return vtn_set_err(ctx, VTN_E_IO, std::string("Cannot load genome index: ") + fasta_path);
-    }
     const size_t nc = S->fai.size();
     std::vector<const char*> names(nc);
     std::vector<int64_t> lens(nc);
@@ -187,14 +293,26 @@ int ref_open(vtn_ctx* ctx, const char* fasta_path)
         delete S;
         return rc;
     }
-    S->loaded.assign(nc, 0);
-    S->exc.resize(nc);
     ctx->ref_src = S;
     ctx->ref_missing = (uint32_t)nc;
+    for (size_t c = 0; c < nc; ++c)
+        if (S->loaded[c]) S->loaded[c] = 0; // a source comes in with nothing resident
     rc = ref_upload_exc(ctx, {});
     if (rc) return rc;
     ctx->ref_loaded = true;
+    // contigs packed ahead go over in the background, each on its own thread and stream; whoever needs one joins its task
+    for (size_t c = 0; c < nc; ++c)
+        if (S->packed_ok[c] > 0 && !S->inflight.count((int)c))
+            S->inflight[(int)c] = std::thread(bg_pack_upload, S, (int)c, 1u, ctx->device, ctx->d_groups);
     return VTN_OK;
+}
+
+int ref_open(vtn_ctx* ctx, const char* fasta_path)
+{
+    std::string err;
+    VtnRefSource* S = src_open(fasta_path, err);
+    if (!S) return vtn_set_err(ctx, VTN_E_IO, err);
+    return ref_attach(ctx, S);
 }
 
 } // namespace
@@ -273,6 +391,60 @@ int vtn_ref_clone(vtn_ctx* dst, const vtn_ctx* src)
     dst->ref_bytes = src->ref_bytes;
     dst->ref_n_groups = src->ref_n_groups;
     dst->ref_loaded = true;
+    return VTN_OK;
+}
+
+// ---- the host half on its own: open and pack before a context exists (CUDA context creation takes 0.25-2 s: a tool opens the FASTA,
+// reads its input's first records and packs their contig meanwhile), then hand everything to the context ----
+int vtn_fasta_open(const char* fasta_path, vtn_fasta** out)
+{
+    if (!fasta_path || !out) return VTN_E_ARG;
+    std::string err;
+    VtnRefSource* S = src_open(fasta_path, err);
+    *out = static_cast<vtn_fasta*>(S);
+    if (!S) return vtn_set_err(nullptr, VTN_E_IO, err);
+    return VTN_OK;
+}
+
+int vtn_fasta_contig_id(const vtn_fasta* f, const char* name)
+{
+    if (!f || !name) return -1;
+    for (size_t c = 0; c < f->fai.size(); ++c)
+        if (f->fai[c].name == name) return (int)c;
+    return -1;
+}
+
+int vtn_fasta_n_contig(const vtn_fasta* f) { return f ? (int)f->fai.size() : 0; }
+
+int vtn_fasta_prepack(vtn_fasta* f, int rid)
+{
+    if (!f) return VTN_E_ARG;
+    if (rid < 0 || rid >= (int)f->fai.size() || f->packed_ok[rid] || f->inflight.count(rid)) return VTN_OK;
+    src_pack(f, rid, host_threads());
+    return f->packed_ok[rid] > 0 ? VTN_OK : VTN_E_IO;
+}
+
+void vtn_fasta_close(vtn_fasta* f) { delete f; }
+
+int vtn_ref_attach(vtn_ctx* ctx, vtn_fasta* f)
+{
+    if (!ctx || !f)
+    {
+        delete f;
+        return vtn_set_err(ctx, VTN_E_ARG, "vtn_ref_attach: bad argument");
+    }
+    return ref_attach(ctx, f);
+}
+
+// background host pack of one contig of a lazily opened reference; vtn_ref_require (or any call that needs the contig) joins it and
+// only has the upload left.  A sorted call set walks the contigs in order, so a tool prefetches contig c + 1 when c first appears.
+int vtn_ref_prefetch(vtn_ctx* ctx, int rid)
+{
+    if (!ctx || !ctx->ref_loaded) return vtn_set_err(ctx, VTN_E_STATE, "no reference loaded");
+    VtnRefSource* S = ctx->ref_src;
+    if (!S || !ctx->ref_missing || rid < 0 || rid >= (int)S->fai.size() || S->inflight.count(rid) || S->loaded[rid] || S->packed_ok[rid]) return VTN_OK;
+    const unsigned nthr = std::max(1u, host_threads() / 2); // the foreground keeps half of the cores
+    S->inflight[rid] = std::thread(bg_pack_upload, S, rid, nthr, ctx->device, ctx->d_groups);
     return VTN_OK;
 }
 

@@ -20,6 +20,7 @@
 #include <unistd.h>
 #include <zlib.h>
 #include <algorithm>
+#include <atomic>
 #include <cctype>
 #include <climits>
 #include <cmath>
@@ -1685,6 +1686,37 @@ void parallel_ranges(size_t n, unsigned nthr, F fn)
 
 bool g_allow_quick_exit = false; // vtn_tools_end_process_after_output(1): the command-line program ends the process after the output is complete
 bool g_quick_exit = false;       // set by a tool once its output is closed, when allowed: nothing is torn down piece by piece
+struct CtxStarter // vtn_ctx_create on its own thread; get() joins and ends the process like die() when there is no device
+{
+    std::thread th;
+    vtn_ctx* ctx = nullptr;
+    int rc = 0;
+    std::string err;
+    std::atomic<bool> done{false};
+    void start(int device)
+    {
+        th = std::thread([this, device]() {
+            rc = vtn_ctx_create(&ctx, device);
+            if (rc) err = vtn_last_error(nullptr); // the text lives in the creating thread
+            done.store(true);
+        });
+    }
+    bool ready() const { return done.load(); }
+    vtn_ctx* get()
+    {
+        if (th.joinable()) th.join();
+        if (rc)
+        {
+            fprintf(stderr, "[vtn] vtn_ctx_create: %s\n", err.c_str());
+            exit(1);
+        }
+        return ctx;
+    }
+    ~CtxStarter()
+    {
+        if (th.joinable()) th.join();
+    }
+};
 struct CtxGuard // destroys the context after every buffer allocated through it (declare it right after vtn_ctx_create)
 {
     vtn_ctx* c;
@@ -2103,12 +2135,13 @@ int cmd_normalize(int argc, char** argv)
     }
     PhaseTimer pt;
     pt.start();
-    vtn_ctx* ctx = nullptr;
-    if (vtn_ctx_create(&ctx, a.device)) die(nullptr, "vtn_ctx_create");
-    CtxGuard ctx_guard{ctx};
-    pt.stop("context");
-    if (vtn_ref_open_fasta(ctx, a.ref.c_str())) die(ctx, "loading the reference");
-    pt.stop("reference open");
+    // The CUDA context comes up on its own thread (0.25-2 s); meanwhile the host opens the FASTA (mapping + index), opens the input,
+    // reads its header and packs the contig of the first record.
+    CtxGuard ctx_guard{nullptr};
+    CtxStarter starter;
+    starter.start(a.device);
+    vtn_fasta* fa = nullptr;
+    const int fa_rc = vtn_fasta_open(a.ref.c_str(), &fa);
     Reader rd;
     if (!rd.open(a.in, a.intervals))
     {
@@ -2122,6 +2155,28 @@ int cmd_normalize(int argc, char** argv)
         fprintf(stderr, "[vtn] %s has no VCF header\n", a.in.c_str());
         return 1;
     }
+    if (fa && !line.empty())
+    {
+        const size_t t = line.find('\t');
+        const int c = vtn_fasta_contig_id(fa, line.substr(0, t == std::string::npos ? line.size() : t).c_str());
+        if (c >= 0)
+        {
+            vtn_fasta_prepack(fa, c); // a short FASTA is reported when the contig is required
+            // a sorted input walks on to the next contigs: the host has nothing else to do until the context is there
+            for (int k = c + 1; k < vtn_fasta_n_contig(fa) && !starter.ready(); ++k) vtn_fasta_prepack(fa, k);
+        }
+    }
+    pt.stop("host: FASTA index, header, first contig");
+    vtn_ctx* ctx = starter.get();
+    ctx_guard.c = ctx;
+    pt.stop("context (what was left of it)");
+    if (fa_rc)
+    { // the same call on the context gives the same failure and leaves its text where die() prints it from
+        if (vtn_ref_open_fasta(ctx, a.ref.c_str())) die(ctx, "loading the reference");
+    }
+    else if (vtn_ref_attach(ctx, fa))
+        die(ctx, "loading the reference");
+    pt.stop("reference attach");
     const unsigned nthr = host_threads();
     FastWriter ow;
     ow.out = open_out(a.out);
@@ -2232,8 +2287,11 @@ int cmd_normalize(int argc, char** argv)
             rid[r] = last_rid, wid[r] = last_wid;
         }
         pt.stop("contig ids");
-        for (int c : new_contigs) // first record on this contig: its bases become resident now
+        for (int c : new_contigs) // first record on this contig: its bases become resident now; the next contig is packed in the background
+        {
             if (vtn_ref_require(ctx, c)) die(ctx, "loading the reference");
+            vtn_ref_prefetch(ctx, c + 1);
+        }
         new_contigs.clear();
         pt.stop("reference load");
         vtn_batch in;
