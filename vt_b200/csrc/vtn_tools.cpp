@@ -1579,8 +1579,9 @@ struct LineParser
                 exit(1);
             }
     }
-    bool read_batch(Reader& rd, std::string& line, bool& more, size_t max_lines, BatchBuf& bb, vtn_ctx* ctx, bool ref_ids,
-                    std::map<std::string, int>& rid_cache)
+    bool lines_ready = false; // read_lines has filled the batch's lines already (done while the CUDA context was still coming up)
+    // host only: the lines of the next batch
+    void read_lines(Reader& rd, std::string& line, bool& more, size_t max_lines, BatchBuf& bb)
     {
         bb.clear();
         n_lead = n_peek = 0;
@@ -1609,12 +1610,19 @@ struct LineParser
             bb.lines.push_back(line);
             more = rd.getline(line);
         }
-        if (bb.lines.size() == n_lead) return false;
-        if (peek_next && more)
+        if (bb.lines.size() > n_lead && peek_next && more)
         {
             bb.lines.push_back(line);
             n_peek = 1;
         }
+        lines_ready = bb.lines.size() > n_lead;
+    }
+    bool read_batch(Reader& rd, std::string& line, bool& more, size_t max_lines, BatchBuf& bb, vtn_ctx* ctx, bool ref_ids,
+                    std::map<std::string, int>& rid_cache)
+    {
+        if (!lines_ready) read_lines(rd, line, more, max_lines, bb);
+        lines_ready = false;
+        if (bb.lines.size() == n_lead) return false;
         tokenize(bb, ctx);
         if (filter)
         {
@@ -2592,9 +2600,8 @@ int cmd_decompose(int argc, char** argv)
     }
     PhaseTimer pt;
     pt.start();
-    vtn_ctx* ctx = nullptr;
-    if (vtn_ctx_create(&ctx, a.device)) die(nullptr, "vtn_ctx_create");
-    pt.stop("context");
+    CtxStarter starter; // the context comes up on its own thread while the header and the first batch's lines are read
+    starter.start(a.device);
     Reader rd;
     if (!rd.open(a.in, a.intervals))
     {
@@ -2623,7 +2630,11 @@ int cmd_decompose(int argc, char** argv)
     LineParser lp;
     Filter flt;
     if (flt.set(a.fexp, h.meta)) lp.filter = &flt;
-    while (more)
+    lp.read_lines(rd, line, more, BATCH, bb);
+    pt.stop("header + first lines");
+    vtn_ctx* ctx = starter.get();
+    pt.stop("context (what was left of it)");
+    while (more || lp.lines_ready)
     {
         pt.start();
         lp.read_batch(rd, line, more, BATCH, bb, ctx, false, rid_cache);
@@ -2849,8 +2860,8 @@ int cmd_uniq(int argc, char** argv)
     fprintf(stderr, "uniq v0.57\n\n"); // print_options, uniq.cpp:158-165
     fprintf(stderr, "options:     input VCF file        %s\n", a.in.c_str());
     fprintf(stderr, "         [o] output VCF file       %s\n", a.out.c_str());
-    vtn_ctx* ctx = nullptr;
-    if (vtn_ctx_create(&ctx, a.device)) die(nullptr, "vtn_ctx_create");
+    CtxStarter starter;
+    starter.start(a.device);
     Reader rd;
     if (!rd.open(a.in, a.intervals))
     {
@@ -2894,7 +2905,9 @@ int cmd_uniq(int argc, char** argv)
     const unsigned nthr = host_threads();
     std::vector<std::string> obuf(nthr);
     std::vector<uint32_t> gstart;
-    while (more)
+    lp.read_lines(rd, line, more, BATCH, bb);
+    vtn_ctx* ctx = starter.get();
+    while (more || lp.lines_ready)
     {
     lp.read_batch(rd, line, more, BATCH, bb, ctx, false, rid_cache);
     vtn_batch in = bb.view();
