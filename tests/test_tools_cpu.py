@@ -99,3 +99,57 @@ def test_filter_parse_rules():
     for bad in ("INFO.AC>1", "QUAL+1>2", "VTYPE==REF"):
         p = subprocess.run([VTN, "_filter", bad], input="1\t2\t.\t.\n", capture_output=True, text=True)
         assert p.returncode != 0 and "not handled" in p.stderr
+
+
+def test_tail_pass_through_rule(tmp_path):
+    """tail_is_plain (which records' columns from QUAL on go out as they came in) against put_tail (what would be written otherwise):
+    plain must imply identical text; the forms htslib rewrites must not be plain"""
+    hdr = str(tmp_path / "h.vcf")
+    open(hdr, "w").write('##fileformat=VCFv4.2\n##INFO=<ID=AF,Number=A,Type=Float,Description="f">\n##INFO=<ID=AC,Number=A,Type=Integer,Description="i">\n'
+                         '##INFO=<ID=DB,Number=0,Type=Flag,Description="d">\n##FORMAT=<ID=GT,Number=1,Type=String,Description="g">\n'
+                         '##FORMAT=<ID=GQ,Number=1,Type=Float,Description="q">\n##FORMAT=<ID=AD,Number=R,Type=Integer,Description="a">\n'
+                         "#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\tFORMAT\tS1\tS2\n")
+    cases = [
+        (".\t.\t.", 1), ("30\tPASS\tAF=0.25;AC=3;DB", 1), ("12.5\tq10\tAF=0.5,0.125", 1), ("30.0\t.\t.", 0), ("1e3\t.\t.", 0), ("30\t.\tAF=0.250", 0),
+        ("30\t.\tAF=1e-3", 0), ("30\t.\tAF=0.1234567", 0), ("30\t.\tAC=3;;DB", 0), ("30\t.\t;AC=3", 0), ("30\t.\tAC=3;", 0), ("30\t.\tAF=.", 1),
+        ("30\t.\tXX=0.250", 1),  # an undeclared key is a string to htslib: as written
+        (".\t.\t.\tGT:GQ:AD\t0/1:30:1,2\t1/1:12.5:3,4", 1), (".\t.\t.\tGT:GQ:AD\t0/1:30.0:1,2\t1/1:12.5:3,4", 0), (".\t.\t.\tGT:GQ:AD\t0/1:30\t1/1:12.5:3,4", 0),
+        (".\t.\t.\tGT:GQ:AD\t0/1:.:1,2\t.:.:.", 1), (".\t.\tAF=0.5\tGT\t0/1\t1|1", 1), ("0\t.\t.", 1), ("00\t.\t.", 0), ("-1\t.\t.", 1),
+    ]
+    p = subprocess.run([VTN, "_plain", hdr], input="".join(c + "\n" for c, _ in cases), capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr
+    out = p.stdout.splitlines()
+    assert len(out) == len(cases)
+    for (tail, exp), l in zip(cases, out):
+        assert int(l[0]) == exp, (tail, l)
+        if l[0] == "1":
+            assert l[1:] == "\t" + tail, (tail, l)
+    # a random sweep: wherever the rule says plain, put_tail agrees byte for byte
+    rng = np.random.default_rng(3)
+    fl = ["0.5", "0.25", "0.250", "1e-5", "3", "12.125", ".", "0.1234567", "100000", "0.00001", "-2.5", "7.0"]
+    tails = []
+    for _ in range(20000):
+        info = ";".join(str(rng.choice(["AF=" + ",".join(rng.choice(fl, int(rng.integers(1, 3)))), "AC=%d" % rng.integers(0, 9), "DB", "", "ZZ=1.50"]))
+                        for _ in range(int(rng.integers(1, 4)))) or "."
+        smp = "" if rng.random() < 0.5 else "\tGT:GQ\t" + "\t".join("0/1:%s" % rng.choice(fl) if rng.random() < 0.9 else "0/1" for _ in range(2))
+        tails.append("%s\t%s\t%s%s" % (rng.choice(fl), rng.choice([".", "PASS", "q10;s50"]), info, smp))
+    p = subprocess.run([VTN, "_plain", hdr], input="".join(t + "\n" for t in tails), capture_output=True, text=True)
+    out = p.stdout.splitlines()
+    assert len(out) == len(tails)
+    n_plain = 0
+    for t, l in zip(tails, out):
+        if l[0] == "1":
+            n_plain += 1
+            assert l[1:] == "\t" + t, (t, l)
+    assert 500 < n_plain < 19000
+
+
+def test_interval_parsing(tmp_path):
+    """GenomeInterval::set / to_string and Program::parse_intervals (genome_interval.cpp:50-137, program.cpp:152-190)"""
+    lst = str(tmp_path / "l.txt")
+    open(lst, "w").write("2:100-400\n1:1000-1300\n2:100-400\nX\n")
+    p = subprocess.run([VTN, "_intervals", "1:60-90,Y:5,2:100-400,chrUn_x", lst], capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr
+    assert p.stdout.splitlines() == ["2:100-400\t100\t400", "1:1000-1300\t1000\t1300", "X\t1\t536870911", "1:60-90\t60\t90", "Y:5-5\t5\t5", "chrUn_x\t1\t536870911"]
+    p = subprocess.run([VTN, "_intervals", "1:a-b"], capture_output=True, text=True)
+    assert p.returncode != 0 and "Invalid genomic interval" in p.stderr

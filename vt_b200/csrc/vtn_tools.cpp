@@ -3579,6 +3579,33 @@ int vtn_tool_main(int argc, char** argv)
         }
         return 0;
     }
+    else if (cmd == "_plain" && argc >= 3)
+    { // self-test hook (no GPU needed): vtn _plain <header.vcf> ; stdin lines = the columns of a record from QUAL on -> 1 when they
+      // would be written as they are (tail_is_plain), else 0 followed by what put_tail writes instead
+        Reader rd;
+        Header h;
+        std::string first;
+        if (!rd.open(argv[2]) || !read_header(rd, h, first)) return 1;
+        char buf[65536];
+        while (fgets(buf, sizeof buf, stdin))
+        {
+            size_t n = strlen(buf);
+            while (n && (buf[n - 1] == '\n' || buf[n - 1] == '\r')) --n;
+            const std::string line = std::string("1\t1\t.\tA\tC\t") + std::string(buf, n);
+            std::vector<Tok> col = split(line.data(), line.size(), '\t');
+            if (col.size() < 8) continue;
+            const bool plain = tail_is_plain(h, true, true, col[5].first, (size_t)(line.data() + line.size() - col[5].first));
+            std::string o;
+            put_tail(o, h, col, "");
+            printf("%d%s\n", plain ? 1 : 0, o.c_str());
+        }
+        return 0;
+    }
+    else if (cmd == "_intervals")
+    { // self-test hook: vtn _intervals <comma separated intervals> [list file] -> one parsed interval per line (GenomeInterval::to_string)
+        for (const Interval& iv : parse_intervals(argc > 3 ? argv[3] : "", argc > 2 ? argv[2] : "")) printf("%s\t%d\t%d\n", iv.to_string().c_str(), iv.start1, iv.end1);
+        return 0;
+    }
     else if (cmd == "_floats")
     { // self-test hook (no GPU needed): every stdin line -> "<1 if canon_float says htslib prints it as written>\t<put_float's text>"
         char buf[4096];
