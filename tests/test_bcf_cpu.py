@@ -9,7 +9,7 @@ import pytest
 import helpers
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-STEMS = ["blocksub_02", "c1_decompose", "filter", "blocksub_uneven", "blocksub_03", "vcftext", "c1_normalize"]
+STEMS = ["blocksub_02", "c1_decompose", "filter", "blocksub_uneven", "blocksub_03", "vcftext", "c1_normalize", "stress"]
 
 
 @pytest.fixture(scope="module")

@@ -580,10 +580,14 @@ struct BcfSink
             enc_size(o, 0, BT_NULL);
             return;
         }
-        int32_t mn = INT32_MAX, mx = INT32_MIN + 2;
+        int32_t mn = 0, mx = 0;
+        bool any = false; // a value that is neither missing nor end-of-vector
         for (int32_t x : v)
-            if (x != INT32_MIN && x != INT32_MIN + 1) mn = std::min(mn, x), mx = std::max(mx, x);
-        if (mn == INT32_MAX) mn = mx = 0;
+            if (x != INT32_MIN && x != INT32_MIN + 1)
+            {
+                mn = any ? std::min(mn, x) : x, mx = any ? std::max(mx, x) : x;
+                any = true;
+            }
         const int t = int_type(mn, mx);
         enc_size(o, (int)v.size(), t);
         for (int32_t x : v) put_int(o, x, t);
@@ -758,16 +762,20 @@ struct BcfSink
                     }
                     if (ty == 'I')
                     {
-                        int32_t mn = INT32_MAX, mx = INT32_MIN + 2;
+                        int32_t mn = 0, mx = 0;
+                        bool any = false;
                         std::vector<int32_t> all;
                         for (int s = 0; s < n_sample; ++s)
                             for (size_t a = 0; a < w; ++a)
                             {
                                 const int32_t x = a < V[(size_t)s].size() ? int_of(V[(size_t)s][a].first, V[(size_t)s][a].second) : INT32_MIN + 1;
                                 all.push_back(x);
-                                if (x != INT32_MIN && x != INT32_MIN + 1) mn = std::min(mn, x), mx = std::max(mx, x);
+                                if (x != INT32_MIN && x != INT32_MIN + 1)
+                                {
+                                    mn = any ? std::min(mn, x) : x, mx = any ? std::max(mx, x) : x;
+                                    any = true;
+                                }
                             }
-                        if (mn == INT32_MAX) mn = mx = 0;
                         const int t = int_type(mn, mx);
                         enc_size(ind, (int)w, t);
                         for (int32_t x : all) put_int(ind, x, t);
