@@ -153,3 +153,17 @@ def test_interval_parsing(tmp_path):
     assert p.stdout.splitlines() == ["2:100-400\t100\t400", "1:1000-1300\t1000\t1300", "X\t1\t536870911", "1:60-90\t60\t90", "Y:5-5\t5\t5", "chrUn_x\t1\t536870911"]
     p = subprocess.run([VTN, "_intervals", "1:a-b"], capture_output=True, text=True)
     assert p.returncode != 0 and "Invalid genomic interval" in p.stderr
+
+
+def test_put_tail_equals_the_reference_on_the_stress_file():
+    """the tools' re-serialisation of QUAL / INFO / FORMAT (put_tail: htslib's float format, dropped trailing sample fields padded, ...)
+    against what the unmodified reference printed for the same records (tests/golden/bcf_stress_view.vcf = `vt view` of stress_in.vcf)"""
+    src = [l.rstrip("\n") for l in open(os.path.join(helpers.GOLDEN, "stress_in.vcf")) if not l.startswith("#")]
+    ref = [l.rstrip("\n") for l in open(os.path.join(helpers.GOLDEN, "bcf_stress_view.vcf")) if not l.startswith("#")]
+    tails = ["\t".join(l.split("\t")[5:]) for l in src]
+    p = subprocess.run([VTN, "_plain", os.path.join(helpers.GOLDEN, "stress_in.vcf")], input="\n".join(tails) + "\n", capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr
+    out = p.stdout.splitlines()
+    assert len(out) == len(src) == len(ref) == 400
+    for o, r in zip(out, ref):
+        assert o[2:] == "\t".join(r.split("\t")[5:])
