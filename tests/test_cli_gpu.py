@@ -548,3 +548,18 @@ def test_normalize_stdin_to_stdout(chr20_fasta):
     p = subprocess.run([VTN, "normalize", "-", "-r", chr20_fasta, "-o", "-", "-q"], input=vin, capture_output=True)
     assert p.returncode == 0, p.stderr[-1000:]
     assert p.stdout == open(os.path.join(helpers.GOLDEN, "c1_normalize_out.vcf"), "rb").read()
+
+
+# ---- the stress file (tests/golden/make_stress_golden.py): every tool on records that walk the corners of the format ----
+@pytest.mark.parametrize("name,args", [("blocksub_a", ["decompose_blocksub", "-a"]), ("blocksub_p", ["decompose_blocksub", "-p"]), ("uniq", ["uniq"])])
+def test_tools_on_the_stress_file(name, args, tmp_path):
+    """(decompose is not among them: on this file's partial GL vectors and ploidy-3/4 genotypes the reference reads past its arrays and
+    prints what it finds there, see make_stress_golden.py)"""
+    out = str(tmp_path / "out.vcf")
+    p = subprocess.run([VTN] + args + ["stress_in.vcf", "-o", out], capture_output=True, text=True, cwd=helpers.GOLDEN)
+    assert p.returncode == 0, p.stderr[-2000:]
+    exp = open(os.path.join(helpers.GOLDEN, "stress_%s_out.vcf" % name)).read().splitlines()
+    got = open(out).read().splitlines()
+    diff = [(g, e) for g, e in zip(got, exp) if g != e]
+    assert len(got) == len(exp) and not diff, (len(got), len(exp), diff[:3])
+    assert _strip(p.stderr) == _strip(open(os.path.join(helpers.GOLDEN, "stress_%s_out.stderr" % name)).read())
