@@ -563,3 +563,17 @@ def test_tools_on_the_stress_file(name, args, tmp_path):
     diff = [(g, e) for g, e in zip(got, exp) if g != e]
     assert len(got) == len(exp) and not diff, (len(got), len(exp), diff[:3])
     assert _strip(p.stderr) == _strip(open(os.path.join(helpers.GOLDEN, "stress_%s_out.stderr" % name)).read())
+
+
+@pytest.mark.parametrize("name,args", [("decompose", ["decompose"]), ("decompose_s", ["decompose", "-s"])])
+def test_decompose_on_the_well_formed_stress_file(name, args, tmp_path):
+    """600 records with 1 to 6 ALTs, INFO / FORMAT fields of every Number kind and type, missing elements and fields, haploid and diploid
+    genotypes (tests/golden/make_decompose_stress_golden.py): byte for byte the unmodified reference's output"""
+    out = str(tmp_path / "out.vcf")
+    p = subprocess.run([VTN] + args + ["dstress_in.vcf", "-o", out], capture_output=True, text=True, cwd=helpers.GOLDEN)
+    assert p.returncode == 0, p.stderr[-2000:]
+    exp = open(os.path.join(helpers.GOLDEN, "dstress_%s_out.vcf" % name)).read().splitlines()
+    got = open(out).read().splitlines()
+    diff = [(g, e) for g, e in zip(got, exp) if g != e]
+    assert len(got) == len(exp) and not diff, (len(got), len(exp), len(diff), diff[:2])
+    assert _strip(p.stderr) == _strip(open(os.path.join(helpers.GOLDEN, "dstress_%s_out.stderr" % name)).read())
